@@ -1,0 +1,320 @@
+// Screening metric and per-label statistics (integer work, HBM-bound).
+//
+//   be_label_overlap_i32   sparse (true, pred) pair histogram in an open-addressing table; one atomic per
+//                          run of equal pairs (warp ballot run detection), areas/max labels from the table
+//   be_match_counts        IoU >= thr pair counting with "second partner" detection (exact tp for thr >= 0.5)
+//   be_label_stats_i32     exact integer raw moments + bounding boxes, one set of atomics per x-run
+#include "be_common.cuh"
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr unsigned long long kEmpty = ~0ull;
+
+__device__ __forceinline__ unsigned long long mix64(unsigned long long k) {
+    k ^= k >> 33;
+    k *= 0xff51afd7ed558ccdull;
+    k ^= k >> 33;
+    k *= 0xc4ceb9fe1a85ec53ull;
+    k ^= k >> 33;
+    return k;
+}
+
+__device__ __forceinline__ void table_add(unsigned long long* keys, unsigned* counts, int64_t capacity,
+                                          unsigned long long key, unsigned cnt, int32_t* status) {
+    const unsigned long long maskc = (unsigned long long)capacity - 1ull;
+    unsigned long long slot = mix64(key) & maskc;
+    for (int64_t probe = 0; probe < capacity; ++probe) {
+        unsigned long long old = keys[slot];
+        if (old != key) {
+            if (old != kEmpty) {
+                slot = (slot + 1) & maskc;
+                continue;
+            }
+            old = atomicCAS(&keys[slot], kEmpty, key);
+            if (old != kEmpty && old != key) {
+                slot = (slot + 1) & maskc;
+                continue;
+            }
+        }
+        atomicAdd(&counts[slot], cnt);
+        return;
+    }
+    *status = 1;  // table full
+}
+
+// Each lane owns 4 consecutive pixels.  A lane whose 4 pairs are equal joins a warp-level run with its
+// neighbours (one table update per run); mixed lanes insert their own sub-runs.
+__global__ void __launch_bounds__(kThreads) overlap_kernel(const int32_t* __restrict__ lab_true,
+                                                           const int32_t* __restrict__ lab_pred, int64_t n_px,
+                                                           unsigned long long* __restrict__ keys,
+                                                           unsigned* __restrict__ counts, int64_t capacity,
+                                                           int32_t* __restrict__ status) {
+    const int64_t img = blockIdx.y;
+    const int32_t* t = lab_true + img * n_px;
+    const int32_t* p = lab_pred + img * n_px;
+    unsigned long long* K = keys + img * capacity;
+    unsigned* Cn = counts + img * capacity;
+    int32_t* st = status + img;
+    const int lane = threadIdx.x & 31;
+    const int64_t n4 = (n_px + 3) >> 2;
+    const int64_t stride = (int64_t)gridDim.x * kThreads;
+    const bool vec_ok = ((((uintptr_t)t | (uintptr_t)p) & 15) == 0);
+    // all lanes of a warp iterate together (the bound is rounded up to a warp multiple)
+    const int64_t n4_pad = (n4 + 31) & ~(int64_t)31;
+    for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n4_pad; i += stride) {
+        unsigned long long k[4];
+        int cnt = 0;
+        if (i < n4) {
+            const int64_t b = i << 2;
+            int32_t tv[4], pv[4];
+            if (vec_ok && b + 4 <= n_px) {
+                const int4 a = __ldg(reinterpret_cast<const int4*>(t + b));
+                const int4 c = __ldg(reinterpret_cast<const int4*>(p + b));
+                tv[0] = a.x; tv[1] = a.y; tv[2] = a.z; tv[3] = a.w;
+                pv[0] = c.x; pv[1] = c.y; pv[2] = c.z; pv[3] = c.w;
+                cnt = 4;
+            } else {
+                for (int j = 0; j < 4 && b + j < n_px; ++j) {
+                    tv[j] = t[b + j];
+                    pv[j] = p[b + j];
+                    cnt = j + 1;
+                }
+            }
+            for (int j = 0; j < cnt; ++j) {
+                if ((tv[j] | pv[j]) < 0) *st = 2;
+                k[j] = ((unsigned long long)(unsigned)tv[j] << 32) | (unsigned)pv[j];
+            }
+        }
+        const bool uniform = (cnt == 4) && k[0] == k[1] && k[1] == k[2] && k[2] == k[3];
+        const unsigned long long k0 = uniform ? k[0] : kEmpty;
+        const unsigned long long prev = __shfl_up_sync(0xffffffffu, k0, 1);
+        const bool start = uniform && (lane == 0 || prev != k0);
+        const unsigned starts = __ballot_sync(0xffffffffu, start);
+        const unsigned unif = __ballot_sync(0xffffffffu, uniform);
+        if (start) {
+            // run = consecutive uniform lanes up to the next start or the first non-uniform lane
+            const unsigned stop = (starts | ~unif) & (lane == 31 ? 0u : (0xffffffffu << (lane + 1)));
+            const int end = stop ? (__ffs(stop) - 1) : 32;
+            table_add(K, Cn, capacity, k0, 4u * (unsigned)(end - lane), st);
+        } else if (!uniform && cnt > 0) {
+            unsigned long long cur = k[0];
+            unsigned c = 1;
+            for (int j = 1; j < cnt; ++j) {
+                if (k[j] == cur) {
+                    ++c;
+                } else {
+                    table_add(K, Cn, capacity, cur, c, st);
+                    cur = k[j];
+                    c = 1;
+                }
+            }
+            table_add(K, Cn, capacity, cur, c, st);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kThreads) areas_kernel(const unsigned long long* __restrict__ keys,
+                                                         const unsigned* __restrict__ counts, int64_t capacity,
+                                                         int32_t* __restrict__ area_true, int64_t cap_true,
+                                                         int32_t* __restrict__ area_pred, int64_t cap_pred,
+                                                         int32_t* __restrict__ max_lbl, int32_t* __restrict__ status) {
+    const int64_t img = blockIdx.y;
+    const int64_t s = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+    if (s >= capacity) return;
+    const unsigned long long k = keys[img * capacity + s];
+    if (k == kEmpty) return;
+    const unsigned c = counts[img * capacity + s];
+    const int64_t t = (int64_t)(k >> 32), p = (int64_t)(k & 0xffffffffull);
+    if (t >= cap_true || p >= cap_pred) {
+        status[img] = 2;
+        return;
+    }
+    atomicAdd(&area_true[img * cap_true + t], (int)c);
+    atomicAdd(&area_pred[img * cap_pred + p], (int)c);
+    atomicMax(&max_lbl[img * 2 + 0], (int)t);
+    atomicMax(&max_lbl[img * 2 + 1], (int)p);
+}
+
+__global__ void __launch_bounds__(kThreads) match_kernel(const unsigned long long* __restrict__ keys,
+                                                         const unsigned* __restrict__ counts, int64_t capacity,
+                                                         const int32_t* __restrict__ area_true, int64_t cap_true,
+                                                         const int32_t* __restrict__ area_pred, int64_t cap_pred,
+                                                         const double* __restrict__ thr, int n_thr,
+                                                         unsigned long long* __restrict__ out,
+                                                         unsigned* __restrict__ bits, int64_t words_true,
+                                                         int64_t words_pred) {
+    const int64_t img = blockIdx.y;
+    const int64_t s = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+    if (s >= capacity) return;
+    const unsigned long long k = keys[img * capacity + s];
+    if (k == kEmpty) return;
+    const int64_t t = (int64_t)(k >> 32), p = (int64_t)(k & 0xffffffffull);
+    if (t == 0 || p == 0 || t >= cap_true || p >= cap_pred) return;
+    const unsigned c = counts[img * capacity + s];
+    const long long uni = (long long)area_true[img * cap_true + t] + (long long)area_pred[img * cap_pred + p] - (long long)c;
+    // the reference's comparison: fp64 quotient against the fp64 threshold
+    const double iou = __ddiv_rn((double)c, (double)uni);
+    for (int j = 0; j < n_thr; ++j) {
+        if (iou >= thr[j]) {
+            unsigned long long* o = out + (img * n_thr + j) * 2;
+            atomicAdd(&o[0], 1ull);
+            unsigned* bt = bits + (img * n_thr + j) * (words_true + words_pred);
+            unsigned* bp = bt + words_true;
+            const unsigned mt = 1u << (t & 31), mp = 1u << (p & 31);
+            unsigned extra = 0;
+            if (atomicOr(&bt[t >> 5], mt) & mt) ++extra;
+            if (atomicOr(&bp[p >> 5], mp) & mp) ++extra;
+            if (extra) atomicAdd(&o[1], (unsigned long long)extra);
+        }
+    }
+}
+
+// ---- label statistics ----
+
+__device__ __forceinline__ unsigned long long series_sum(unsigned long long a, unsigned long long b) {
+    return (a + b) * (b - a + 1) / 2;  // a + (a+1) + ... + b
+}
+__device__ __forceinline__ unsigned long long squares_below(unsigned long long n) {
+    return n ? (n - 1) * n * (2 * n - 1) / 6 : 0;  // 0^2 + ... + (n-1)^2
+}
+
+__global__ void __launch_bounds__(kThreads) label_stats_kernel(const int32_t* __restrict__ labels, int64_t Z, int64_t Y,
+                                                               int64_t X, int64_t cap,
+                                                               unsigned long long* __restrict__ sums,
+                                                               int32_t* __restrict__ bbox, int32_t* __restrict__ status) {
+    const int64_t img = blockIdx.y;
+    const int64_t vol = Z * Y * X;
+    const int32_t* lab = labels + img * vol;
+    const int lane = threadIdx.x & 31;
+    const int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+    // whole warps stay alive so the shuffles below are full-mask
+    const bool in = i < vol;
+    const int32_t l = in ? lab[i] : 0;
+    const int64_t rowi = in ? i / X : -1;
+    const int x = in ? (int)(i - rowi * X) : 0;
+    const int32_t lp = __shfl_up_sync(0xffffffffu, l, 1);
+    const int64_t rp = __shfl_up_sync(0xffffffffu, rowi, 1);
+    const bool fg = in && l > 0;
+    const bool start = fg && (lane == 0 || lp != l || rp != rowi);
+    const bool brk = !fg || start;  // anything that ends the run of the lane before it
+    const unsigned brks = __ballot_sync(0xffffffffu, brk);
+    if (!start) return;
+    if (l >= cap) {
+        status[img] = 2;
+        return;
+    }
+    const unsigned stop = brks & (lane == 31 ? 0u : (0xffffffffu << (lane + 1)));
+    const int end = stop ? (__ffs(stop) - 1) : 32;
+    const unsigned long long len = (unsigned long long)(end - lane);
+    const unsigned long long xa = (unsigned long long)x, xb = xa + len - 1;
+    const unsigned long long y = (unsigned long long)(rowi % Y), z = (unsigned long long)(rowi / Y);
+    const unsigned long long sx = series_sum(xa, xb);
+    const unsigned long long sxx = squares_below(xb + 1) - squares_below(xa);
+    unsigned long long* S = sums + (img * cap + l) * 10;
+    atomicAdd(&S[0], len);
+    if (z) atomicAdd(&S[1], z * len);
+    atomicAdd(&S[2], y * len);
+    atomicAdd(&S[3], sx);
+    if (z) atomicAdd(&S[4], z * z * len);
+    atomicAdd(&S[5], y * y * len);
+    atomicAdd(&S[6], sxx);
+    if (z) atomicAdd(&S[7], z * y * len);
+    if (z) atomicAdd(&S[8], z * sx);
+    atomicAdd(&S[9], y * sx);
+    int32_t* B = bbox + (img * cap + l) * 6;
+    atomicMin(&B[0], (int)z);
+    atomicMin(&B[1], (int)y);
+    atomicMin(&B[2], (int)xa);
+    atomicMax(&B[3], (int)z);
+    atomicMax(&B[4], (int)y);
+    atomicMax(&B[5], (int)xb);
+}
+
+__global__ void bbox_init_kernel(int32_t* bbox, int64_t n_labels_total) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_labels_total) return;
+    int32_t* B = bbox + i * 6;
+    B[0] = B[1] = B[2] = 0x7fffffff;
+    B[3] = B[4] = B[5] = -1;
+}
+
+inline bool is_pow2(int64_t v) { return v > 0 && (v & (v - 1)) == 0; }
+
+}  // namespace
+
+extern "C" int be_label_overlap_i32(const int32_t* lab_true, const int32_t* lab_pred, int64_t N, int64_t n_px,
+                                    uint64_t* keys, uint32_t* counts, int64_t capacity, int32_t* area_true,
+                                    int64_t cap_true, int32_t* area_pred, int64_t cap_pred, int32_t* max_lbl,
+                                    int32_t* status, be_stream_t stream) {
+    BE_REQUIRE(lab_true && lab_pred && keys && counts && area_true && area_pred && max_lbl && status, BE_ERR_INVALID_ARG,
+               "be_label_overlap_i32: null pointer");
+    BE_REQUIRE(N > 0 && n_px > 0, BE_ERR_INVALID_ARG, "be_label_overlap_i32: empty input");
+    BE_REQUIRE(is_pow2(capacity), BE_ERR_INVALID_ARG, "be_label_overlap_i32: capacity %lld is not a power of two",
+               (long long)capacity);
+    BE_REQUIRE(cap_true > 0 && cap_pred > 0, BE_ERR_INVALID_ARG, "be_label_overlap_i32: label capacities must be positive");
+    BE_REQUIRE(N <= 65535, BE_ERR_TOO_LARGE, "be_label_overlap_i32: N %lld > 65535", (long long)N);
+    BE_REQUIRE(n_px < ((int64_t)1 << 31), BE_ERR_TOO_LARGE, "be_label_overlap_i32: n_px >= 2^31");
+    cudaStream_t s = (cudaStream_t)stream;
+    BE_CUDA(cudaMemsetAsync(keys, 0xff, sizeof(uint64_t) * N * capacity, s));
+    BE_CUDA(cudaMemsetAsync(counts, 0, sizeof(uint32_t) * N * capacity, s));
+    BE_CUDA(cudaMemsetAsync(area_true, 0, sizeof(int32_t) * N * cap_true, s));
+    BE_CUDA(cudaMemsetAsync(area_pred, 0, sizeof(int32_t) * N * cap_pred, s));
+    BE_CUDA(cudaMemsetAsync(max_lbl, 0, sizeof(int32_t) * N * 2, s));
+    BE_CUDA(cudaMemsetAsync(status, 0, sizeof(int32_t) * N, s));
+    const int64_t n4 = (n_px + 3) / 4;
+    int64_t gx = (n4 + kThreads - 1) / kThreads;
+    const int64_t cap_blocks = max((int64_t)1, (int64_t)BE_SM_COUNT * 16 / N);
+    if (gx > cap_blocks) gx = cap_blocks;
+    overlap_kernel<<<dim3((unsigned)gx, (unsigned)N), kThreads, 0, s>>>(
+        lab_true, lab_pred, n_px, (unsigned long long*)keys, counts, capacity, status);
+    BE_LAUNCH_CHECK();
+    areas_kernel<<<dim3((unsigned)((capacity + kThreads - 1) / kThreads), (unsigned)N), kThreads, 0, s>>>(
+        (const unsigned long long*)keys, counts, capacity, area_true, cap_true, area_pred, cap_pred, max_lbl, status);
+    BE_LAUNCH_CHECK();
+    return BE_OK;
+}
+
+extern "C" size_t be_match_workspace_bytes(int64_t N, int64_t cap_true, int64_t cap_pred, int n_thr) {
+    if (N <= 0 || cap_true <= 0 || cap_pred <= 0 || n_thr <= 0) return 256;
+    const int64_t words = (cap_true + 31) / 32 + (cap_pred + 31) / 32;
+    return be_align_up(sizeof(uint32_t) * N * n_thr * words, 256);
+}
+
+extern "C" int be_match_counts(const uint64_t* keys, const uint32_t* counts, int64_t N, int64_t capacity,
+                               const int32_t* area_true, int64_t cap_true, const int32_t* area_pred, int64_t cap_pred,
+                               const double* thr, int n_thr, int64_t* counts_out, void* ws, be_stream_t stream) {
+    BE_REQUIRE(keys && counts && area_true && area_pred && thr && counts_out && ws, BE_ERR_INVALID_ARG,
+               "be_match_counts: null pointer");
+    BE_REQUIRE(N > 0 && is_pow2(capacity) && cap_true > 0 && cap_pred > 0, BE_ERR_INVALID_ARG,
+               "be_match_counts: bad sizes");
+    BE_REQUIRE(n_thr >= 1 && n_thr <= 16, BE_ERR_INVALID_ARG, "be_match_counts: n_thr %d not in 1..16", n_thr);
+    BE_REQUIRE(N <= 65535, BE_ERR_TOO_LARGE, "be_match_counts: N %lld > 65535", (long long)N);
+    cudaStream_t s = (cudaStream_t)stream;
+    const int64_t wt = (cap_true + 31) / 32, wp = (cap_pred + 31) / 32;
+    BE_CUDA(cudaMemsetAsync(ws, 0, sizeof(uint32_t) * N * n_thr * (wt + wp), s));
+    BE_CUDA(cudaMemsetAsync(counts_out, 0, sizeof(int64_t) * N * n_thr * 2, s));
+    match_kernel<<<dim3((unsigned)((capacity + kThreads - 1) / kThreads), (unsigned)N), kThreads, 0, s>>>(
+        (const unsigned long long*)keys, counts, capacity, area_true, cap_true, area_pred, cap_pred, thr, n_thr,
+        (unsigned long long*)counts_out, (unsigned*)ws, wt, wp);
+    BE_LAUNCH_CHECK();
+    return BE_OK;
+}
+
+extern "C" int be_label_stats_i32(const int32_t* labels, int64_t N, int64_t Z, int64_t Y, int64_t X, int64_t cap,
+                                  int64_t* sums, int32_t* bbox, int32_t* status, be_stream_t stream) {
+    BE_REQUIRE(labels && sums && bbox && status, BE_ERR_INVALID_ARG, "be_label_stats_i32: null pointer");
+    BE_REQUIRE(N > 0 && Z > 0 && Y > 0 && X > 0 && cap > 0, BE_ERR_INVALID_ARG, "be_label_stats_i32: empty input");
+    BE_REQUIRE(N <= 65535, BE_ERR_TOO_LARGE, "be_label_stats_i32: N %lld > 65535", (long long)N);
+    const int64_t vol = Z * Y * X;
+    BE_REQUIRE(vol < ((int64_t)1 << 31), BE_ERR_TOO_LARGE, "be_label_stats_i32: image >= 2^31 voxels");
+    cudaStream_t s = (cudaStream_t)stream;
+    BE_CUDA(cudaMemsetAsync(sums, 0, sizeof(int64_t) * N * cap * 10, s));
+    BE_CUDA(cudaMemsetAsync(status, 0, sizeof(int32_t) * N, s));
+    bbox_init_kernel<<<(unsigned)((N * cap + 255) / 256), 256, 0, s>>>(bbox, N * cap);
+    BE_LAUNCH_CHECK();
+    label_stats_kernel<<<dim3((unsigned)((vol + kThreads - 1) / kThreads), (unsigned)N), kThreads, 0, s>>>(
+        labels, Z, Y, X, cap, (unsigned long long*)sums, bbox, status);
+    BE_LAUNCH_CHECK();
+    return BE_OK;
+}

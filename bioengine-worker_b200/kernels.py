@@ -1,0 +1,264 @@
+"""Thin torch-tensor front end of the C-ABI: shape checks, workspace allocation, stream plumbing.
+
+Every function takes CUDA tensors, launches on torch's current stream and returns CUDA tensors.  PyTorch is
+used for device memory and streams only; all arithmetic happens in libbe_b200.so.
+"""
+from __future__ import annotations
+
+from typing import Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from . import _lib
+from .geometry import AxisBlocks
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _p(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _check(t: torch.Tensor, dtype: torch.dtype, name: str) -> torch.Tensor:
+    if not t.is_cuda:
+        raise ValueError(f"{name} must be a CUDA tensor")
+    if t.dtype != dtype:
+        raise ValueError(f"{name} must be {dtype}, got {t.dtype}")
+    if not t.is_contiguous():
+        raise ValueError(f"{name} must be contiguous")
+    return t
+
+
+class Workspace:
+    """Grow-only byte arena reused across calls on one stream (the replica is single-stream: max_ongoing_requests=1,
+    ref: apps/model-runner/runtime_deployment.py:40)."""
+
+    def __init__(self):
+        self._buf: Optional[torch.Tensor] = None
+
+    def get(self, nbytes: int, device) -> torch.Tensor:
+        if self._buf is None or self._buf.numel() < nbytes or self._buf.device != torch.device(device):
+            self._buf = torch.empty(max(nbytes, 256), dtype=torch.uint8, device=device)
+        return self._buf
+
+
+_default_ws = Workspace()
+
+
+def _segments(x: torch.Tensor, n_seg: int) -> Tuple[int, int]:
+    n = x.numel()
+    if n_seg <= 0 or n % n_seg:
+        raise ValueError(f"{n} elements do not split into {n_seg} segments")
+    return n_seg, n // n_seg
+
+
+def meanvar(x: torch.Tensor, n_seg: int, eps: float = 1e-6, ws: Workspace = _default_ws):
+    """→ (stats [n_seg,2] fp64 {mean,var}, norm [n_seg,2] fp64 {mean, std+eps})."""
+    _check(x, torch.float32, "x")
+    n_seg, seg_len = _segments(x, n_seg)
+    stats = torch.empty((n_seg, 2), dtype=torch.float64, device=x.device)
+    norm = torch.empty((n_seg, 2), dtype=torch.float64, device=x.device)
+    w = ws.get(_lib.query("be_meanvar_workspace_bytes", n_seg, seg_len), x.device)
+    _lib.call("be_meanvar_f32", x.data_ptr(), n_seg, seg_len, float(eps), stats.data_ptr(), norm.data_ptr(),
+              w.data_ptr(), _stream())
+    return stats, norm
+
+
+def quantile(x: torch.Tensor, n_seg: int, q: torch.Tensor, eps: float = 1e-6, want_norm: bool = True,
+             ws: Workspace = _default_ws):
+    """Exact nanquantile(method="linear") per segment.  q: fp64 CUDA tensor of 1 or 2 fractions.
+    → (quant [n_seg, n_q] fp64, norm [n_seg,2] fp64 {q0, q1-q0+eps} or None)."""
+    _check(x, torch.float32, "x")
+    _check(q, torch.float64, "q")
+    n_seg, seg_len = _segments(x, n_seg)
+    n_q = q.numel()
+    quant = torch.empty((n_seg, n_q), dtype=torch.float64, device=x.device)
+    norm = torch.empty((n_seg, 2), dtype=torch.float64, device=x.device) if (want_norm and n_q == 2) else None
+    w = ws.get(_lib.query("be_quantile_workspace_bytes", n_seg, seg_len), x.device)
+    _lib.call("be_quantile_f32", x.data_ptr(), n_seg, seg_len, q.data_ptr(), n_q, float(eps), quant.data_ptr(),
+              _p(norm), w.data_ptr(), _stream())
+    return quant, norm
+
+
+def normalize(x: torch.Tensor, norm: torch.Tensor, clip: Optional[Tuple[float, float]] = None,
+              out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    _check(x, torch.float32, "x")
+    _check(norm, torch.float64, "norm")
+    n_seg, seg_len = _segments(x, norm.shape[0])
+    out = torch.empty_like(x) if out is None else _check(out, torch.float32, "out")
+    lo, hi = clip if clip is not None else (0.0, 0.0)
+    _lib.call("be_normalize_f32", x.data_ptr(), out.data_ptr(), n_seg, seg_len, norm.data_ptr(),
+              int(clip is not None), float(lo), float(hi), _stream())
+    return out
+
+
+def elementwise(x: torch.Tensor, op: int, a: float = 0.0, b: float = 0.0, out: Optional[torch.Tensor] = None):
+    _check(x, torch.float32, "x")
+    out = torch.empty_like(x) if out is None else _check(out, torch.float32, "out")
+    _lib.call("be_elementwise_f32", x.data_ptr(), out.data_ptr(), x.numel(), int(op), float(a), float(b), _stream())
+    return out
+
+
+def clip(x, lo, hi, out=None):
+    return elementwise(x, _lib.BE_OP_CLIP, lo, hi, out)
+
+
+def scale_linear(x, gain, offset, out=None):
+    return elementwise(x, _lib.BE_OP_SCALE_LINEAR, gain, offset, out)
+
+
+def sigmoid(x, out=None):
+    return elementwise(x, _lib.BE_OP_SIGMOID, 0.0, 0.0, out)
+
+
+def binarize(x: torch.Tensor, thr: float) -> torch.Tensor:
+    _check(x, torch.float32, "x")
+    out = torch.empty(x.shape, dtype=torch.uint8, device=x.device)
+    _lib.call("be_binarize_f32_u8", x.data_ptr(), out.data_ptr(), x.numel(), float(thr), _stream())
+    return out
+
+
+class DeviceAxis:
+    """An AxisBlocks with its tables resident on the device."""
+
+    def __init__(self, ax: AxisBlocks, device):
+        self.ax = ax
+        self.src = torch.from_numpy(ax.src).to(device)
+        self.sel = torch.from_numpy(ax.sel).to(device) if ax.sel.size else None
+
+
+def _as5d(img: torch.Tensor) -> Tuple[int, int, int, int, int]:
+    if img.dim() == 4:
+        N, C, Y, X = img.shape
+        return N, C, 1, Y, X
+    if img.dim() == 5:
+        return tuple(img.shape)
+    raise ValueError(f"expected (N,C,Y,X) or (N,C,Z,Y,X), got {tuple(img.shape)}")
+
+
+def tile_gather(img: torch.Tensor, axes: Sequence[DeviceAxis], norm: Optional[torch.Tensor] = None, norm_mode: int = 0,
+                clip: Optional[Tuple[float, float]] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """img (N,C,[Z,]Y,X) fp32 → tiles (N*T, C, [Bz,] By, Bx) fp32.  axes = (z, y, x) DeviceAxis (z = identity for 2-D)."""
+    _check(img, torch.float32, "img")
+    N, C, Z, Y, X = _as5d(img)
+    az, ay, ax = axes
+    if (az.ax.S, ay.ax.S, ax.ax.S) != (Z, Y, X):
+        raise ValueError("axis tables do not match the image shape")
+    T = az.ax.T * ay.ax.T * ax.ax.T
+    shape = (N * T, C, az.ax.B, ay.ax.B, ax.ax.B) if img.dim() == 5 else (N * T, C, ay.ax.B, ax.ax.B)
+    out = torch.empty(shape, dtype=torch.float32, device=img.device) if out is None else _check(out, torch.float32, "out")
+    lo, hi = clip if clip is not None else (0.0, 0.0)
+    _lib.call("be_tile_gather_f32", img.data_ptr(), out.data_ptr(), N, C, Z, Y, X, az.ax.T, ay.ax.T, ax.ax.T,
+              az.ax.B, ay.ax.B, ax.ax.B, az.src.data_ptr(), ay.src.data_ptr(), ax.src.data_ptr(), _p(norm),
+              int(norm_mode if norm is not None else 0), int(clip is not None), float(lo), float(hi), _stream())
+    return out
+
+
+def _stitch_outputs(shape, device, want_out, want_mask):
+    out = torch.empty(shape, dtype=torch.float32, device=device) if want_out else None
+    mask = torch.empty(shape, dtype=torch.uint8, device=device) if want_mask else None
+    return out, mask
+
+
+def stitch_crop(tiles: torch.Tensor, sample_shape: Sequence[int], axes: Sequence[DeviceAxis], epilogue: int = 0,
+                thr: float = 0.5, want_out: bool = True, want_mask: bool = False):
+    """bioimageio inner-region reassembly.  → (out fp32 or None, mask uint8 or None), each of sample_shape."""
+    _check(tiles, torch.float32, "tiles")
+    N, C, Z, Y, X = (sample_shape[0], sample_shape[1], 1, *sample_shape[2:]) if len(sample_shape) == 4 else sample_shape
+    az, ay, ax = axes
+    out, mask = _stitch_outputs(tuple(sample_shape), tiles.device, want_out, want_mask)
+    _lib.call("be_stitch_crop_f32", tiles.data_ptr(), _p(out), _p(mask), N, C, Z, Y, X, az.ax.T, ay.ax.T, ax.ax.T,
+              az.ax.B, ay.ax.B, ax.ax.B, az.sel.data_ptr(), ay.sel.data_ptr(), ax.sel.data_ptr(), int(epilogue),
+              float(thr), _stream())
+    return out, mask
+
+
+def stitch_blend(tiles: torch.Tensor, sample_shape: Sequence[int], axes: Sequence[DeviceAxis],
+                 windows: Sequence[torch.Tensor], epilogue: int = 0, thr: float = 0.5, want_out: bool = True,
+                 want_mask: bool = False):
+    """fibsem Gaussian blend.  windows = (wz, wy, wx) fp64 CUDA tensors (wz = [1.0] for 2-D)."""
+    _check(tiles, torch.float32, "tiles")
+    N, C, Z, Y, X = (sample_shape[0], sample_shape[1], 1, *sample_shape[2:]) if len(sample_shape) == 4 else sample_shape
+    az, ay, ax = axes
+    out, mask = _stitch_outputs(tuple(sample_shape), tiles.device, want_out, want_mask)
+    _lib.call("be_stitch_blend_f32", tiles.data_ptr(), _p(out), _p(mask), N, C, Z, Y, X, az.ax.T, ay.ax.T, ax.ax.T,
+              az.ax.B, ay.ax.B, ax.ax.B, az.ax.stride, ay.ax.stride, ax.ax.stride, windows[0].data_ptr(),
+              windows[1].data_ptr(), windows[2].data_ptr(), int(epilogue), float(thr), _stream())
+    return out, mask
+
+
+def ccl(mask: torch.Tensor, connectivity: Optional[int] = None, ws: Workspace = _default_ws):
+    """mask (N,[Z,]Y,X) uint8 → (labels int32 same shape, n_labels int32 [N] on device)."""
+    _check(mask, torch.uint8, "mask")
+    if mask.dim() == 3:
+        N, Y, X = mask.shape
+        Z = 1
+    elif mask.dim() == 4:
+        N, Z, Y, X = mask.shape
+    else:
+        raise ValueError(f"expected (N,Y,X) or (N,Z,Y,X), got {tuple(mask.shape)}")
+    ndim = 3 if Z > 1 else 2
+    conn = ndim if connectivity is None else int(connectivity)
+    labels = torch.empty(mask.shape, dtype=torch.int32, device=mask.device)
+    n_labels = torch.empty((N,), dtype=torch.int32, device=mask.device)
+    w = ws.get(_lib.query("be_ccl_workspace_bytes", N, Z, Y, X), mask.device)
+    _lib.call("be_ccl_u8_i32", mask.data_ptr(), labels.data_ptr(), N, Z, Y, X, conn, n_labels.data_ptr(),
+              w.data_ptr(), _stream())
+    return labels, n_labels
+
+
+def label_overlap(lab_true: torch.Tensor, lab_pred: torch.Tensor, capacity: int, cap_true: int, cap_pred: int):
+    """(N, ...) int32 label maps → dict of device tensors: keys, counts, area_true, area_pred, max_lbl, status."""
+    _check(lab_true, torch.int32, "lab_true")
+    _check(lab_pred, torch.int32, "lab_pred")
+    if lab_true.shape != lab_pred.shape:
+        raise ValueError("label maps differ in shape")
+    N = lab_true.shape[0]
+    n_px = lab_true.numel() // N
+    dev = lab_true.device
+    r = dict(
+        keys=torch.empty((N, capacity), dtype=torch.int64, device=dev),
+        counts=torch.empty((N, capacity), dtype=torch.int32, device=dev),
+        area_true=torch.empty((N, cap_true), dtype=torch.int32, device=dev),
+        area_pred=torch.empty((N, cap_pred), dtype=torch.int32, device=dev),
+        max_lbl=torch.empty((N, 2), dtype=torch.int32, device=dev),
+        status=torch.empty((N,), dtype=torch.int32, device=dev),
+    )
+    _lib.call("be_label_overlap_i32", lab_true.data_ptr(), lab_pred.data_ptr(), N, n_px, r["keys"].data_ptr(),
+              r["counts"].data_ptr(), capacity, r["area_true"].data_ptr(), cap_true, r["area_pred"].data_ptr(),
+              cap_pred, r["max_lbl"].data_ptr(), r["status"].data_ptr(), _stream())
+    return r
+
+
+def match_counts(table: dict, thr: torch.Tensor, ws: Workspace = _default_ws) -> torch.Tensor:
+    """→ int64 [N, n_thr, 2] {pairs with IoU >= thr, extra partners}."""
+    _check(thr, torch.float64, "thr")
+    N, capacity = table["keys"].shape
+    cap_true, cap_pred = table["area_true"].shape[1], table["area_pred"].shape[1]
+    n_thr = thr.numel()
+    out = torch.empty((N, n_thr, 2), dtype=torch.int64, device=thr.device)
+    w = ws.get(_lib.query("be_match_workspace_bytes", N, cap_true, cap_pred, n_thr), thr.device)
+    _lib.call("be_match_counts", table["keys"].data_ptr(), table["counts"].data_ptr(), N, capacity,
+              table["area_true"].data_ptr(), cap_true, table["area_pred"].data_ptr(), cap_pred, thr.data_ptr(), n_thr,
+              out.data_ptr(), w.data_ptr(), _stream())
+    return out
+
+
+def label_stats(labels: torch.Tensor, cap: int):
+    """labels (N,[Z,]Y,X) int32 → (sums int64 [N,cap,10], bbox int32 [N,cap,6], status int32 [N])."""
+    _check(labels, torch.int32, "labels")
+    if labels.dim() == 3:
+        N, Y, X = labels.shape
+        Z = 1
+    else:
+        N, Z, Y, X = labels.shape
+    dev = labels.device
+    sums = torch.empty((N, cap, 10), dtype=torch.int64, device=dev)
+    bbox = torch.empty((N, cap, 6), dtype=torch.int32, device=dev)
+    status = torch.empty((N,), dtype=torch.int32, device=dev)
+    _lib.call("be_label_stats_i32", labels.data_ptr(), N, Z, Y, X, cap, sums.data_ptr(), bbox.data_ptr(),
+              status.data_ptr(), _stream())
+    return sums, bbox, status

@@ -1,0 +1,172 @@
+/*
+ * be_b200.h — C-ABI of the B200-native tiled bioimage inference kernels.
+ *
+ * This is the drop-in boundary: every entry point is `extern "C"`, takes plain device
+ * pointers + sizes + a cudaStream_t (passed as void*), returns 0 on success or a negative BE_ERR_* code,
+ * and never allocates device memory — scratch is a caller-provided workspace whose size comes from the
+ * matching *_workspace_bytes() query.  All pointers are DEVICE pointers unless a comment says "host".
+ *
+ * The reference (aicell-lab/bioengine-worker) is pure Python; the arithmetic each entry point replaces
+ * lives in its apps/ directory or in the third-party packages those apps pin.  Every declaration cites
+ * the reference call site (file:line under the reference tree) it stands in for.
+ *
+ * Layout conventions: images are (N, C, Z, Y, X) C-contiguous fp32 (2-D images have Z = 1); tile tensors
+ * are (N*T, C, Bz, By, Bx) with tile index t = ((n*Tz + kz)*Ty + ky)*Tx + kx — i.e. exactly the batched
+ * NCHW / NCDHW tensor the torch UNet forward consumes; masks are uint8, labels int32.
+ */
+#ifndef BE_B200_H_
+#define BE_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BE_OK 0
+#define BE_ERR_INVALID_ARG (-1) /* bad size / null pointer / unsupported parameter */
+#define BE_ERR_CUDA (-2)        /* a CUDA runtime call or launch failed; see be_last_error_string() */
+#define BE_ERR_TOO_LARGE (-3)   /* size exceeds what the entry point supports */
+
+typedef void* be_stream_t; /* cudaStream_t */
+
+/* ---- library ------------------------------------------------------------------------------------ */
+
+/* ABI version (major*1000 + minor). */
+int be_version(void);
+/* Last error message of the calling thread ("" if none). Host pointer, valid until the next failing call. */
+const char* be_last_error_string(void);
+
+/* ---- pre-processing statistics ------------------------------------------------------------------ */
+
+/* Per-segment mean / population variance, fp64 accumulation in one pass.
+ * Replaces bioimageio.core MeanVarStdCalculator used by `zero_mean_unit_variance`
+ * (pinned at apps/model-runner/runtime_deployment.py:17, invoked through :278/:280).
+ *   x        [n_seg * seg_len] fp32, segment s = x[s*seg_len .. (s+1)*seg_len)
+ *   stats    [n_seg * 2] fp64 out: {mean, var(ddof=0)}
+ *   norm     [n_seg * 2] fp64 out or NULL: {sub = mean, div = sqrt(var) + eps} for be_normalize / be_tile_gather
+ *   ws       be_meanvar_workspace_bytes(n_seg, seg_len) bytes */
+size_t be_meanvar_workspace_bytes(int64_t n_seg, int64_t seg_len);
+int be_meanvar_f32(const float* x, int64_t n_seg, int64_t seg_len, double eps, double* stats, double* norm,
+                   void* ws, be_stream_t stream);
+
+/* Exact per-segment quantiles, numpy `nanquantile(..., method="linear")` semantics (NaNs dropped, fp64
+ * virtual index q*(n-1), numpy's two-sided lerp), by 3-level radix select on the order-preserving uint32
+ * key of fp32.  Replaces bioimageio.core SamplePercentilesCalculator / `scale_range`
+ * (runtime_deployment.py:17,:278; Appendix A.2/A.3) and `np.percentile(image_np, [1, 99])`
+ * (apps/fibsem-mito-analysis/analysis_deployment.py:241).
+ *   q        [n_q] fp64 in [0,1], DEVICE pointer, 1 <= n_q <= 2
+ *   quant    [n_seg * n_q] fp64 out
+ *   norm     [n_seg * 2] fp64 out or NULL (requires n_q == 2): {sub = q0, div = q1 - q0 + eps}
+ *   ws       be_quantile_workspace_bytes(n_seg, seg_len) bytes */
+size_t be_quantile_workspace_bytes(int64_t n_seg, int64_t seg_len);
+int be_quantile_f32(const float* x, int64_t n_seg, int64_t seg_len, const double* q, int n_q, double eps,
+                    double* quant, double* norm, void* ws, be_stream_t stream);
+
+/* ---- elementwise -------------------------------------------------------------------------------- */
+
+/* y = (float)(((double)x - norm[2s]) / norm[2s+1]), optionally clipped to [clip_lo, clip_hi].
+ * The apply step of `scale_range` / `zero_mean_unit_variance` / `fixed_zero_mean_unit_variance`
+ * (Appendix A.2) and of analysis_deployment.py:242 (clip 0..1).  x and y may alias. */
+int be_normalize_f32(const float* x, float* y, int64_t n_seg, int64_t seg_len, const double* norm, int clip,
+                     float clip_lo, float clip_hi, be_stream_t stream);
+
+#define BE_OP_CLIP 0         /* y = min(max(x, a), b)              bioimageio `clip`          */
+#define BE_OP_SCALE_LINEAR 1 /* y = x*a + b (two fp32 roundings)   bioimageio `scale_linear`  */
+#define BE_OP_SIGMOID 2      /* y = 1/(1+exp(-x)), fp32 semantics  bioimageio `sigmoid`       */
+int be_elementwise_f32(const float* x, float* y, int64_t n, int op, float a, float b, be_stream_t stream);
+
+/* y = x > thr (strict), 0/1 uint8.  bioimageio `binarize` (Appendix A.2); `prob > 0.5`
+ * at analysis_deployment.py:166. */
+int be_binarize_f32_u8(const float* x, uint8_t* y, int64_t n, float thr, be_stream_t stream);
+
+/* ---- halo tiles --------------------------------------------------------------------------------- */
+
+/* Gather halo tiles (any padding rule) into the batched tile tensor, fused with the normalise-apply so
+ * the image is read once.  Source coordinates come from three small per-axis tables built by the host
+ * (zsrc[Tz*Bz], ysrc[Ty*By], xsrc[Tx*Bx]: image coordinate feeding in-tile offset i of tile k along that
+ * axis), which expresses both the bioimageio.core convention (halo inside the block, last block shifted,
+ * reflect pad; Appendix A.4, `predict_sample_with_blocking` at runtime_deployment.py:278) and the fibsem
+ * convention (stride tiles, bottom/right reflect pad; analysis_deployment.py:132-138).
+ *   norm_mode 0: copy only; 1: norm[2*(n*C+c)]; 2: norm[2*n] (statistics joint over channels)
+ *   clip      as be_normalize_f32 */
+int be_tile_gather_f32(const float* img, float* tiles, int64_t N, int64_t C, int64_t Z, int64_t Y, int64_t X,
+                       int Tz, int Ty, int Tx, int Bz, int By, int Bx, const int32_t* zsrc, const int32_t* ysrc,
+                       const int32_t* xsrc, const double* norm, int norm_mode, int clip, float clip_lo,
+                       float clip_hi, be_stream_t stream);
+
+#define BE_EPI_NONE 0
+#define BE_EPI_SIGMOID 1
+
+/* Inner-region reassembly (bioimageio `Sample.from_blocks`: out[inner_slice] = block[local_inner],
+ * last writer wins; Appendix A.4, runtime_deployment.py:278).  Per-axis tables zsel[Z], ysel[Y], xsel[X]
+ * hold k*B + i of the winning block for every output coordinate.  Optional fused epilogue: sigmoid on the
+ * stitched value, and/or a uint8 mask = value > thr (the `sigmoid` / `binarize` post-processing ops).
+ * Either of out / mask may be NULL. */
+int be_stitch_crop_f32(const float* tiles, float* out, uint8_t* mask, int64_t N, int64_t C, int64_t Z, int64_t Y,
+                       int64_t X, int Tz, int Ty, int Tx, int Bz, int By, int Bx, const int32_t* zsel,
+                       const int32_t* ysel, const int32_t* xsel, int epilogue, float thr, be_stream_t stream);
+
+/* Gaussian-weighted overlap blend, gather form of analysis_deployment.py:125-156: tiles sit at
+ * k*stride, window w = (float)(wz[iz]*wy[iy]*wx[ix]) from host-computed fp64 1-D tables
+ * (exp(-2*linspace(-1,1,B)^2); wz = {1.0} for 2-D), acc += (double)(tile*w), wacc += (double)w in
+ * ascending tile order, value = (float)(acc/wacc).  Epilogue / mask as be_stitch_crop_f32. */
+int be_stitch_blend_f32(const float* tiles, float* out, uint8_t* mask, int64_t N, int64_t C, int64_t Z, int64_t Y,
+                        int64_t X, int Tz, int Ty, int Tx, int Bz, int By, int Bx, int Sz, int Sy, int Sx,
+                        const double* wz, const double* wy, const double* wx, int epilogue, float thr,
+                        be_stream_t stream);
+
+/* ---- connected components ----------------------------------------------------------------------- */
+
+/* Connected-component labelling of N independent (Z,Y,X) uint8 masks (non-zero = foreground): background 0,
+ * components numbered 1..n in raster order of their first voxel — the numbering of
+ * `skimage.measure.label` / `scipy.ndimage.label` (analysis_deployment.py:175; Appendix C).
+ * connectivity = maximum number of orthogonal steps to a neighbour (skimage's meaning):
+ * 2-D (Z == 1): 1 → 4-conn, 2 → 8-conn; 3-D: 1 → 6, 2 → 18, 3 → 26.
+ *   labels    [N*Z*Y*X] int32 out      n_labels [N] int32 out (device)
+ *   ws        be_ccl_workspace_bytes(N, Z, Y, X) bytes */
+size_t be_ccl_workspace_bytes(int64_t N, int64_t Z, int64_t Y, int64_t X);
+int be_ccl_u8_i32(const uint8_t* mask, int32_t* labels, int64_t N, int64_t Z, int64_t Y, int64_t X,
+                  int connectivity, int32_t* n_labels, void* ws, be_stream_t stream);
+
+/* ---- screening metric --------------------------------------------------------------------------- */
+
+/* Sparse label-pair overlap histogram of N (true, pred) label-map pairs of n_px pixels each — the
+ * `_label_overlap` / `_intersection_over_union` step of cellpose.metrics.average_precision
+ * (apps/cellpose-finetuning/main.py:2002; Appendix B.1).  Per image an open-addressing table of
+ * `capacity` (power of two) slots: keys[slot] = (true << 32) | pred, or ~0 if empty; counts[slot] = #pixels.
+ * Also fills the per-label pixel counts (row / column sums of the overlap matrix, background included) and
+ * the max labels.  All outputs are (re)initialised by the call.
+ *   keys      [N * capacity] uint64 out     counts [N * capacity] uint32 out
+ *   area_true [N * cap_true], area_pred [N * cap_pred] int32 out (index = label)
+ *   max_lbl   [N * 2] int32 out {max true, max pred}
+ *   status    [N] int32 out: 0 ok, 1 table full (retry with a larger capacity), 2 label negative or >= cap */
+int be_label_overlap_i32(const int32_t* lab_true, const int32_t* lab_pred, int64_t N, int64_t n_px, uint64_t* keys,
+                         uint32_t* counts, int64_t capacity, int32_t* area_true, int64_t cap_true, int32_t* area_pred,
+                         int64_t cap_pred, int32_t* max_lbl, int32_t* status, be_stream_t stream);
+
+/* Threshold matching on the sparse table: for every image and threshold, the number of (true, pred) pairs
+ * (both > 0) with (double)ov / (double)(a_t + a_p - ov) >= thr, and `extra` = the number of times a label
+ * received a second (third, ...) such partner.  tp = pairs - extra is exact for thr >= 0.5 (Appendix B.2/B.3;
+ * replaces the Hungarian assignment in cellpose `_true_positive`); for thr < 0.5 a non-zero `extra` means the
+ * caller must solve the assignment for that image.
+ *   thr        [n_thr] fp64, device          counts_out [N * n_thr * 2] int64 out {pairs, extra}
+ *   ws         be_match_workspace_bytes(N, cap_true, cap_pred, n_thr) bytes */
+size_t be_match_workspace_bytes(int64_t N, int64_t cap_true, int64_t cap_pred, int n_thr);
+int be_match_counts(const uint64_t* keys, const uint32_t* counts, int64_t N, int64_t capacity,
+                    const int32_t* area_true, int64_t cap_true, const int32_t* area_pred, int64_t cap_pred,
+                    const double* thr, int n_thr, int64_t* counts_out, void* ws, be_stream_t stream);
+
+/* Per-label integer raw moments of N label maps (Z,Y,X): for label l in 1..cap-1,
+ * sums[((n*cap + l)*10 + j)] = {area, Σz, Σy, Σx, Σzz, Σyy, Σxx, Σzy, Σzx, Σyx} (int64, exact) and
+ * bbox[((n*cap + l)*6 + j)] = {zmin, ymin, xmin, zmax, ymax, xmax} (int32, inclusive).  The integer core of
+ * skimage `regionprops` area / centroid / inertia-tensor properties (analysis_deployment.py:258-267).
+ * sums/bbox are (re)initialised by the call. */
+int be_label_stats_i32(const int32_t* labels, int64_t N, int64_t Z, int64_t Y, int64_t X, int64_t cap,
+                       int64_t* sums, int32_t* bbox, int32_t* status, be_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BE_B200_H_ */

@@ -1,0 +1,147 @@
+"""CUDA statistics / elementwise kernels against the oracle (bit-exact order statistics, <= 1e-5 rel floats)."""
+import warnings
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+
+RTOL = 1e-5  # north_star: "within 1e-5 relative for normalised floats"
+
+
+def K():
+    from bioengine_worker_b200 import kernels
+
+    return kernels
+
+
+def _quant(x_np, q, n_seg, dev, eps=1e-6):
+    x = torch.from_numpy(x_np).to(dev)
+    qd = torch.tensor(q, dtype=torch.float64, device=dev)
+    quant, norm = K().quantile(x, n_seg, qd, eps)
+    torch.cuda.synchronize()
+    return quant.cpu().numpy(), (None if norm is None else norm.cpu().numpy())
+
+
+@pytest.mark.parametrize("n", [1, 2, 3, 5, 31, 1000, 4099, 1 << 16, (1 << 20) + 7])
+@pytest.mark.parametrize("q", [(0.01, 0.998), (0.0, 1.0), (0.5,), (0.25, 0.75)])
+def test_quantile_is_numpy_nanquantile_bit_exact(n, q, dev, rng):
+    x = (rng.standard_normal(n) * 100 + 50).astype(np.float32)
+    got, _ = _quant(x, q, 1, dev)
+    want = np.nanquantile(x, np.asarray(q, np.float64), method="linear")
+    assert np.array_equal(got[0], want)
+
+
+def test_quantile_segments_ties_negatives_and_nans(dev, rng):
+    n_seg, seg_len = 7, 50_001
+    x = rng.integers(-40, 40, size=(n_seg, seg_len)).astype(np.float32)  # heavy ties, both signs, +-0
+    x[1] *= 1e-30
+    x[2] = 7.0  # constant segment
+    x[3, ::3] = np.nan
+    x[4, :] = np.nan  # all-NaN segment → NaN
+    x[5, 5] = np.inf
+    x[5, 6] = -np.inf
+    x[6] = np.abs(x[6]) * 0.0 - 0.0
+    q = (0.01, 0.99)
+    got, norm = _quant(x, q, n_seg, dev)
+    with warnings.catch_warnings(), np.errstate(all="ignore"):
+        warnings.simplefilter("ignore")  # all-NaN slice
+        want = np.nanquantile(x, np.asarray(q, np.float64), axis=1, method="linear").T
+    assert np.array_equal(got, want, equal_nan=True)
+    ok = ~np.isnan(want[:, 0])
+    assert np.array_equal(norm[ok, 0], want[ok, 0])
+    assert np.array_equal(norm[ok, 1], want[ok, 1] - want[ok, 0] + 1e-6)
+
+
+def test_quantile_c2_image_full_size(dev):
+    """BASELINE config 2 input: 4096^2, p1.0 / p99.8 with hot pixels; numpy on the same data is the checker."""
+    img = O.synthetic_image((2048, 2048), 1000, seed=2)
+    img = np.tile(img, (2, 2))  # 4096^2 without paying 4x generation time
+    got, _ = _quant(img, (0.01, 0.998), 1, dev)
+    want = np.nanquantile(img, np.asarray((0.01, 0.998)), method="linear")
+    assert np.array_equal(got[0], want)
+
+
+def test_percentile_fibsem_call_site(dev, rng):
+    img = (rng.random((700, 900)) * 255).astype(np.float32)
+    got, _ = _quant(img, (0.01, 0.99), 1, dev)
+    p1, p99 = np.percentile(img, [1, 99])
+    assert got[0, 0] == p1 and got[0, 1] == p99
+
+
+@pytest.mark.parametrize("shape,n_seg", [((1, 1, 512, 512), 1), ((3, 2, 129, 77), 6), ((1, 1, 5), 1)])
+def test_meanvar_and_zmuv(shape, n_seg, dev, rng):
+    x = (rng.standard_normal(shape) * 37 + 1000).astype(np.float32)
+    xd = torch.from_numpy(x).to(dev)
+    stats, norm = K().meanvar(xd, n_seg, 1e-6)
+    y = K().normalize(xd, norm)
+    torch.cuda.synchronize()
+    x64 = x.reshape(n_seg, -1).astype(np.float64)
+    np.testing.assert_allclose(stats[:, 0].cpu().numpy(), x64.mean(1), rtol=1e-12)
+    np.testing.assert_allclose(stats[:, 1].cpu().numpy(), x64.var(1), rtol=1e-9)
+    axes = tuple(range(2, x.ndim)) if n_seg > 1 else None
+    want = O.zero_mean_unit_variance(x, axes=axes)
+    np.testing.assert_allclose(y.cpu().numpy(), want, rtol=RTOL, atol=RTOL)
+    # bitwise reproducible statistics
+    stats2, _ = K().meanvar(xd, n_seg, 1e-6)
+    assert torch.equal(stats, stats2)
+
+
+def test_scale_range_apply_matches_both_reference_arithmetics(dev):
+    img = O.synthetic_image((1, 1, 600, 1000), 200, seed=3)
+    xd = torch.from_numpy(img).to(dev)
+    q = torch.tensor([0.01, 0.998], dtype=torch.float64, device=dev)
+    _, norm = K().quantile(xd, 1, q, 1e-6)
+    y = K().normalize(xd, norm).cpu().numpy()
+    want64 = O.scale_range(img, 1.0, 99.8, axes=None, arithmetic="float64")
+    want32 = O.scale_range(img, 1.0, 99.8, axes=None, arithmetic="float32")
+    assert np.array_equal(y, want64)  # same fp64 operations → same bits
+    np.testing.assert_allclose(y, want32, rtol=RTOL, atol=RTOL)
+
+
+def test_fibsem_normalise_clip(dev, rng):
+    img = (rng.random((513, 300)) * 255).astype(np.float32)
+    xd = torch.from_numpy(img).to(dev)
+    q = torch.tensor([0.01, 0.99], dtype=torch.float64, device=dev)
+    _, norm = K().quantile(xd, 1, q, 1e-6)
+    y = K().normalize(xd, norm, clip=(0.0, 1.0)).cpu().numpy()
+    assert np.array_equal(y, O.fibsem_normalize(img))
+
+
+def test_elementwise_ops_bit_exact(dev, rng):
+    x = (rng.standard_normal(100_003) * 4).astype(np.float32)
+    x[:64] = np.linspace(-3e-7, 3e-7, 64, dtype=np.float32)  # straddles the sigmoid(x) == 0.5 rounding boundary
+    x[64:70] = [np.nan, np.inf, -np.inf, 0.0, -0.0, 88.9]
+    x[70:74] = [-88.0, -104.0, 17.0, -17.0]
+    xd = torch.from_numpy(x).to(dev)
+    k = K()
+    with np.errstate(all="ignore"):
+        assert np.array_equal(k.clip(xd, -1.5, 2.25).cpu().numpy(), O.clip(x, -1.5, 2.25), equal_nan=True)
+        assert np.array_equal(k.scale_linear(xd, 1.7, -0.3).cpu().numpy(), O.scale_linear(x, 1.7, -0.3), equal_nan=True)
+        s = k.sigmoid(xd).cpu().numpy()
+        want = O.sigmoid(x)
+        np.testing.assert_allclose(s, want, rtol=RTOL, equal_nan=True)
+        # the binarised mask of the sigmoid must be bit-exact
+        assert np.array_equal(k.binarize(k.sigmoid(xd), 0.5).cpu().numpy(), O.binarize(want, 0.5))
+        assert np.array_equal(k.binarize(xd, 0.5).cpu().numpy(), O.binarize(x, 0.5))
+
+
+def test_unaligned_views(dev, rng):
+    x = (rng.standard_normal(10_007)).astype(np.float32)
+    xd = torch.from_numpy(x).to(dev)[3:]  # 12-byte offset: exercises the scalar head/tail paths
+    got, _ = K().quantile(xd, 1, torch.tensor([0.3, 0.9], dtype=torch.float64, device=dev))
+    assert np.array_equal(got.cpu().numpy()[0], np.nanquantile(x[3:], np.array([0.3, 0.9])))
+    assert np.array_equal(K().binarize(xd, 0.1).cpu().numpy(), O.binarize(x[3:], 0.1))
+
+
+def test_errors_are_loud(dev):
+    from bioengine_worker_b200._lib import BeError
+
+    x = torch.zeros(16, dtype=torch.float32, device=dev)
+    with pytest.raises(BeError):
+        K().quantile(x, 1, torch.tensor([0.1, 0.2, 0.3], dtype=torch.float64, device=dev))
+    with pytest.raises(ValueError):
+        K().quantile(x.cpu(), 1, torch.tensor([0.1], dtype=torch.float64, device=dev))

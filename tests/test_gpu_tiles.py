@@ -1,0 +1,125 @@
+"""Tile gather and both stitchers against the oracle: bit-exact tiles, bit-exact crop stitch, blend within 1e-5
+(observed: bit-exact — same fp64 operation order)."""
+import numpy as np
+import pytest
+import torch
+
+from bioengine_worker_b200 import geometry as G
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+def K():
+    from bioengine_worker_b200 import kernels
+
+    return kernels
+
+
+def dev_axes(axes, dev):
+    return [K().DeviceAxis(a, dev) for a in axes]
+
+
+@pytest.mark.parametrize("shape,B,halo", [((2, 3, 200, 333), 64, 8), ((1, 1, 512, 512), 256, 32), ((1, 2, 97, 130), 33, 5)])
+def test_gather_2d_bioimageio_bit_exact(shape, B, halo, dev, rng):
+    x = rng.standard_normal(shape).astype(np.float32)
+    axes = dev_axes([G.identity_axis(1), G.bioimageio_axis(shape[2], B, halo), G.bioimageio_axis(shape[3], B, halo)], dev)
+    tiles = K().tile_gather(torch.from_numpy(x).to(dev), axes).cpu().numpy()
+    assert np.array_equal(tiles, O.blocks_tensor(x, (B, B), (halo, halo)))
+
+
+def test_gather_3d_bioimageio_bit_exact(dev, rng):
+    shape, B, halo = (1, 2, 70, 90, 100), 32, 4
+    x = rng.standard_normal(shape).astype(np.float32)
+    axes = dev_axes([G.bioimageio_axis(s, B, halo) for s in shape[2:]], dev)
+    tiles = K().tile_gather(torch.from_numpy(x).to(dev), axes).cpu().numpy()
+    assert np.array_equal(tiles, O.blocks_tensor(x, (B,) * 3, (halo,) * 3))
+
+
+def test_gather_fused_normalise_equals_normalise_then_gather(dev):
+    img = O.synthetic_image((2, 1, 300, 420), 80, seed=5)
+    xd = torch.from_numpy(img).to(dev)
+    q = torch.tensor([0.01, 0.998], dtype=torch.float64, device=dev)
+    _, norm = K().quantile(xd, 2, q, 1e-6)
+    axes = dev_axes([G.identity_axis(1), G.bioimageio_axis(300, 128, 16), G.bioimageio_axis(420, 128, 16)], dev)
+    fused = K().tile_gather(xd, axes, norm=norm, norm_mode=1).cpu().numpy()
+    want = O.blocks_tensor(O.scale_range(img, 1.0, 99.8, axes=(1, 2, 3)), (128, 128), (16, 16))
+    assert np.array_equal(fused, want)
+
+
+@pytest.mark.parametrize("H,W,B,ov", [(700, 900, 256, 64), (513, 512, 512, 64), (300, 449, 64, 16)])
+def test_fibsem_gather_and_blend_2d(H, W, B, ov, dev, rng):
+    img = rng.random((H, W)).astype(np.float32)
+    axes = dev_axes([G.identity_axis(1), G.fibsem_axis(H, B, ov), G.fibsem_axis(W, B, ov)], dev)
+    tiles = K().tile_gather(torch.from_numpy(img).to(dev)[None, None], axes)
+    want_tiles = O.fibsem_tiles(img, B, ov)
+    assert np.array_equal(tiles.cpu().numpy()[:, 0], want_tiles)
+    # a fake "network": a fixed nonlinear map per tile, so overlapping tiles disagree and blending matters
+    probs = torch.sin(tiles * 3.0) * (1.0 + 0.01 * torch.arange(tiles.shape[0], device=dev).view(-1, 1, 1, 1))
+    probs = probs.contiguous()
+    w1 = torch.from_numpy(G.gauss_window_1d(B)).to(dev)
+    one = torch.ones(1, dtype=torch.float64, device=dev)
+    out, mask = K().stitch_blend(probs, (1, 1, H, W), axes, (one, w1, w1), want_mask=True, thr=0.5)
+    want = O.fibsem_blend(probs.cpu().numpy()[:, 0], (H, W), B, ov)
+    np.testing.assert_allclose(out.cpu().numpy()[0, 0], want, rtol=1e-5, atol=0)
+    assert np.array_equal(out.cpu().numpy()[0, 0], want)
+    assert np.array_equal(mask.cpu().numpy()[0, 0], O.binarize(want, 0.5))
+
+
+def test_fibsem_blend_3d(dev, rng):
+    shape, B, ov = (70, 81, 90), 32, 8
+    vol = rng.random(shape).astype(np.float32)
+    axes = dev_axes([G.fibsem_axis(s, B, ov) for s in shape], dev)
+    tiles = K().tile_gather(torch.from_numpy(vol).to(dev)[None, None], axes)
+    assert np.array_equal(tiles.cpu().numpy()[:, 0], O.fibsem_tiles(vol, B, ov))
+    probs = (tiles * tiles).contiguous()
+    w1 = torch.from_numpy(G.gauss_window_1d(B)).to(dev)
+    out, _ = K().stitch_blend(probs, (1, 1) + shape, axes, (w1, w1, w1))
+    want = O.fibsem_blend(probs.cpu().numpy()[:, 0], shape, B, ov)
+    assert np.array_equal(out.cpu().numpy()[0, 0], want)
+
+
+@pytest.mark.parametrize("shape,B,halo", [((2, 2, 200, 333), 64, 8), ((1, 1, 512, 512), 256, 32)])
+def test_crop_stitch_round_trip_and_last_writer(shape, B, halo, dev, rng):
+    x = rng.standard_normal(shape).astype(np.float32)
+    axes = dev_axes([G.identity_axis(1), G.bioimageio_axis(shape[2], B, halo), G.bioimageio_axis(shape[3], B, halo)], dev)
+    tiles = K().tile_gather(torch.from_numpy(x).to(dev), axes)
+    out, _ = K().stitch_crop(tiles, shape, axes)
+    assert np.array_equal(out.cpu().numpy(), x)  # gather → crop is the identity
+    # distinct per-tile content shows which block wins in the shifted-last-block overlap
+    t2 = torch.from_numpy(rng.standard_normal(tuple(tiles.shape)).astype(np.float32)).to(dev)
+    out2, mask2 = K().stitch_crop(t2, shape, axes, want_mask=True, thr=0.25)
+    want = O.from_blocks(t2.cpu().numpy(), shape, (B, B), (halo, halo))
+    assert np.array_equal(out2.cpu().numpy(), want)
+    assert np.array_equal(mask2.cpu().numpy(), O.binarize(want, 0.25))
+    # fused sigmoid epilogue == stitch then sigmoid op
+    out3, mask3 = K().stitch_crop(t2, shape, axes, epilogue=1, want_mask=True, thr=0.5)
+    assert np.array_equal(out3.cpu().numpy(), K().sigmoid(out2).cpu().numpy())
+    assert np.array_equal(mask3.cpu().numpy(), O.binarize(O.sigmoid(want), 0.5))
+
+
+def test_crop_stitch_3d(dev, rng):
+    shape, B, halo = (1, 1, 70, 90, 100), 32, 4
+    axes = dev_axes([G.bioimageio_axis(s, B, halo) for s in shape[2:]], dev)
+    T = axes[0].ax.T * axes[1].ax.T * axes[2].ax.T
+    t = torch.from_numpy(rng.standard_normal((T, 1, B, B, B)).astype(np.float32)).to(dev)
+    out, _ = K().stitch_crop(t, shape, axes)
+    assert np.array_equal(out.cpu().numpy(), O.from_blocks(t.cpu().numpy(), shape, (B,) * 3, (halo,) * 3))
+
+
+def test_c2_geometry_full_size_round_trip(dev):
+    """BASELINE config 2: 4096^2, 256-px blocks incl. 32-px halo → 484 tiles; gather→crop must return the image."""
+    g = torch.Generator(device=dev).manual_seed(2)
+    x = torch.randn((1, 1, 4096, 4096), device=dev, generator=g)
+    axes = dev_axes([G.identity_axis(1), G.bioimageio_axis(4096, 256, 32), G.bioimageio_axis(4096, 256, 32)], dev)
+    tiles = K().tile_gather(x, axes)
+    assert tuple(tiles.shape) == (484, 1, 256, 256)
+    out, _ = K().stitch_crop(tiles, (1, 1, 4096, 4096), axes)
+    assert torch.equal(out, x)
+    # blend of tiles cut from one image returns that image up to rounding (weights cancel)
+    faxes = dev_axes([G.identity_axis(1), G.fibsem_axis(4096, 256, 64), G.fibsem_axis(4096, 256, 64)], dev)
+    ft = K().tile_gather(x, faxes)
+    w1 = torch.from_numpy(G.gauss_window_1d(256)).to(dev)
+    one = torch.ones(1, dtype=torch.float64, device=dev)
+    bl, _ = K().stitch_blend(ft, (1, 1, 4096, 4096), faxes, (one, w1, w1))
+    torch.testing.assert_close(bl, x, rtol=1e-5, atol=1e-6)
