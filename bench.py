@@ -1,0 +1,365 @@
+#!/usr/bin/env python
+"""bench.py — BASELINE.json metric on BASELINE.json config 2 (the largest single-GPU configuration the metric is
+quoted on): one 4096x4096 synthetic image, scale_range percentile normalisation, 256-px tiles with 32-px halo per
+side (overlap 64 → stride 192 → 484 tiles), Gaussian overlap-blend stitch, sigmoid, binarize 0.5, 8-connected labels.
+
+A "step" = one pass of the hot path over one image:  quantile select → fused normalise + tile gather →
+[UNet forward: unchanged torch, run once outside the timed region, timed separately] → blend stitch + sigmoid +
+binarize → connected components.  `value` times the kernels with the image resident in HBM; `e2e` adds the pinned-host
+→ device copy of the image and the device → host read of the labels, through the public TiledPipeline API.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+N > 1 (torchrun): the path does not shard one image (global quantile + global labelling), so every rank runs an
+independent replica on its own image ("replicas only", weak scaling); value = N images / max-over-ranks time.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+H = W = 4096
+TILE, HALO = 256, 32
+OVERLAP = 2 * HALO
+N_BLOBS = 4000
+SEED = 2
+METRIC = "Mpx/s tiled pre/stitch/post (scale_range→tile→blend-stitch→sigmoid→binarize→CC labels), kernels only"
+UNIT = "Mpx/s"
+
+
+def workload_config(extra=None):
+    cfg = {
+        "workload": "C2: 4096x4096 f32 synthetic image, scale_range p1.0/p99.8, 256px tiles / 32px halo (overlap 64, "
+                    "484 tiles), Gaussian overlap-blend stitch, sigmoid, binarize 0.5, CC 8-conn",
+        "unet_forward": "excluded from the timed region (unchanged torch UNet2d feat=16 depth=4 fp32, timed separately)",
+        "l2": "L2 flushed (256 MiB write) before every timed step",
+        "parallelism": "replicas only",
+    }
+    if extra:
+        cfg.update(extra)
+    return cfg
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons while the timed region runs."""
+
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx = float(r[1])
+            except Exception:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def synthetic_inputs(rank: int):
+    from oracle import oracle as O
+
+    return O.synthetic_image((1, 1, H, W), N_BLOBS, seed=SEED + 101 * rank)
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# reference arm: the CPU restatement of the reference path on the host cores
+# ----------------------------------------------------------------------------------------------------------------
+
+_REF_STATE = {}
+
+
+def _ref_worker_init(img, logits):
+    _REF_STATE["img"], _REF_STATE["logits"] = img, logits
+    os.environ["OMP_NUM_THREADS"] = "1"
+
+
+def _ref_worker(_):
+    from oracle import paths as P
+
+    return P.timed_c2(_REF_STATE["img"], _REF_STATE["logits"], TILE, OVERLAP)[0]
+
+
+def make_logits_for_reference(img):
+    """Logits for the CPU arm: the same UNet on oracle-normalised tiles, by plain torch (GPU if present), untimed."""
+    import torch
+
+    from bioengine_worker_b200 import models
+    from oracle import paths as P
+
+    models.strict_fp32()
+    tiles = P.c2_pre(img, TILE, OVERLAP)
+    dev = torch.device("cuda:0" if torch.cuda.is_available() else "cpu")
+    model = models.build_model("UNet2d", seed=1).to(dev)
+    out = np.empty_like(tiles)
+    with torch.no_grad():
+        for i in range(0, tiles.shape[0], 32):
+            out[i:i + 32] = model(torch.from_numpy(tiles[i:i + 32]).to(dev)).cpu().numpy()
+    return out
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import multiprocessing as mp
+
+    img = synthetic_inputs(0)
+    logits = make_logits_for_reference(img)
+    cores = os.cpu_count() or 1
+    procs = max(1, min(cores, 16))
+    ctx = mp.get_context("fork")
+    with ctx.Pool(procs, initializer=_ref_worker_init, initargs=(img, logits)) as pool:
+        for _ in range(args.warmup):
+            pool.map(_ref_worker, range(procs))
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            pool.map(_ref_worker, range(procs))
+        dt = time.perf_counter() - t0
+    value = args.steps * procs * H * W / dt / 1e6
+    sample = f"{procs} full 4096^2 images per step, one per process (numpy/scipy oracle, 1 thread each), forward excluded"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": procs, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "host_cpus": cores,
+    }
+    print(json.dumps(line))
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# B200 arm
+# ----------------------------------------------------------------------------------------------------------------
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+
+    from bioengine_worker_b200 import kernels as K
+    from bioengine_worker_b200 import models
+    from bioengine_worker_b200.pipeline import PipelineSpec, TiledPipeline
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    models.strict_fp32()
+
+    img = synthetic_inputs(rank)
+    spec = PipelineSpec(block=(TILE, TILE), halo=(HALO, HALO), convention="fibsem", overlap=(OVERLAP, OVERLAP),
+                        preprocess="scale_range", min_percentile=1.0, max_percentile=99.8, sigmoid=True, threshold=0.5,
+                        connectivity=2, label=True, forward_batch=44)
+    pipe = TiledPipeline((1, 1, H, W), spec, device=dev)
+    model = models.build_model("UNet2d", seed=1).to(dev)
+
+    host_img = torch.from_numpy(img).pin_memory()
+    host_labels = torch.empty((1, 1, H, W), dtype=torch.int32).pin_memory()
+    host_n = torch.empty((1,), dtype=torch.int32).pin_memory()
+    x = host_img.to(dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    # the forward: once, outside the timed region (and timed on its own)
+    tiles = pipe.preprocess_and_tile(x)
+    logits = pipe.forward(model, tiles)
+    torch.cuda.synchronize()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    ev[0].record()
+    pipe.forward(model, tiles, out=logits)
+    ev[1].record()
+    torch.cuda.synchronize()
+    forward_ms = ev[0].elapsed_time(ev[1])
+
+    def kernels_step():
+        pipe.preprocess_and_tile(x)
+        return pipe.stitch_and_label(logits)
+
+    def e2e_step():
+        xd = host_img.to(dev, non_blocking=True)
+        pipe.preprocess_and_tile(xd)
+        res = pipe.stitch_and_label(logits)
+        host_labels.copy_(res["labels"], non_blocking=True)
+        host_n.copy_(res["n_labels"], non_blocking=True)
+
+    stage_names = ["quantile_select", "normalise+tile_gather", "blend_stitch+sigmoid+binarize", "ccl"]
+
+    def staged_step(events):
+        sp = pipe.spec
+        events[0].record()
+        _, norm = K.quantile(x, 1, pipe.q, sp.eps, ws=pipe.ws)
+        events[1].record()
+        K.tile_gather(x, pipe.axes, norm=norm, norm_mode=1, out=pipe.tiles)
+        events[2].record()
+        _, mask = K.stitch_blend(logits, (1, 1, H, W), pipe.axes, pipe.windows, 1, 0.5, want_out=False, want_mask=True)
+        events[3].record()
+        K.ccl(mask.reshape(1, H, W), 2, ws=pipe.ws)
+        events[4].record()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            flush.fill_(1)
+            fn()
+        barrier()
+        times = []
+        for _ in range(steps):
+            flush.fill_(1)  # evict the image / logits / previous results from the 126 MB L2
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            fn()
+            b.record()
+            times.append((a, b))
+        barrier()
+        return sum(a.elapsed_time(b) for a, b in times)  # ms over exactly `steps` steps
+
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    total_ms = timed(kernels_step, args.steps, args.warmup)
+    clocks = sampler.stop() if rank == 0 else None
+    e2e_ms = timed(e2e_step, args.steps, max(1, args.warmup // 2))
+
+    # per-stage device times (same kernels, events between the C-ABI calls)
+    stage_ms = np.zeros(4)
+    for it in range(args.warmup + args.steps):
+        flush.fill_(1)
+        evs = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
+        staged_step(evs)
+        torch.cuda.synchronize()
+        if it >= args.warmup:
+            stage_ms += [evs[i].elapsed_time(evs[i + 1]) for i in range(4)]
+    stage_ms /= args.steps
+
+    if world > 1:
+        t = torch.tensor([total_ms, e2e_ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_ms, e2e_ms = t.tolist()
+
+    if rank == 0:
+        px = H * W
+        n_tiles = pipe.n_tiles
+        E = n_tiles * TILE * TILE / px
+        peak, peak_src = load_peaks()
+        ms_per_step = total_ms / args.steps
+        value = world * px / (ms_per_step * 1e-3) / 1e6
+        alg_bytes = {"quantile_select": 4.0 * px, "normalise+tile_gather": (4 + 4 * E) * px,
+                     "blend_stitch+sigmoid+binarize": (4 * E + 1) * px, "ccl": 5.0 * px}
+        stages = {}
+        for name, ms in zip(stage_names, stage_ms):
+            gbs = alg_bytes[name] / (ms * 1e-3) / 1e9
+            stages[name] = {"ms": round(float(ms), 4), "alg_bytes": alg_bytes[name], "alg_GBps": round(gbs, 1),
+                            "frac_of_peak": round(gbs / peak, 4)}
+        dom = max(stage_names, key=lambda n: stages[n]["ms"])
+        path_bytes = sum(alg_bytes.values())
+        path_gbs = path_bytes / (ms_per_step * 1e-3) / 1e9
+
+        # CPU baseline: the oracle on this box's host cores, one core (the reference replica has num_cpus: 1)
+        from oracle import paths as P
+
+        os.environ.setdefault("OMP_NUM_THREADS", "1")
+        logits_h = logits.cpu().numpy()
+        best = None
+        for _ in range(2):
+            dt, parts = P.timed_c2(img, logits_h, TILE, OVERLAP)
+            best = dt if best is None else min(best, dt)
+        cpu_value = px / best / 1e6
+
+        launches_per_step = 3 + 1 + 1 + 6  # quantile levels, gather, blend, ccl (tile/border/count/scan/assign/resolve)
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": workload_config({"tiles": n_tiles, "tile_expansion": round(E, 4)}),
+            "roofline": {"bound": "hbm", "kernel": dom, "achieved": stages[dom]["alg_GBps"], "peak": peak,
+                         "unit": "GB/s", "frac": stages[dom]["frac_of_peak"], "traffic": None, "peak_source": peak_src},
+            "path_roofline": {"alg_bytes_per_px": round(path_bytes / px, 3), "achieved": round(path_gbs, 1), "peak": peak,
+                              "unit": "GB/s", "frac": round(path_gbs / peak, 4)},
+            "stages": stages,
+            "cpu_baseline": {"value": cpu_value, "unit": UNIT, "cores": 1, "kind": "port",
+                             "sample": "1 full 4096^2 image, pre+tile+blend+sigmoid+binarize+label, best of 2, "
+                                       "logits taken from the GPU run", "seconds": best},
+            "e2e": {"value": world * px / (e2e_ms / args.steps * 1e-3) / 1e6, "unit": UNIT,
+                    "h2d_bytes_per_step": px * 4, "d2h_bytes_per_step": px * 4 + 4, "ms_per_step": e2e_ms / args.steps},
+            "gpu_launches": launches_per_step * args.steps,
+            "unet_forward_ms": forward_ms,
+            "with_forward_Mpx_s": px / ((ms_per_step + forward_ms) * 1e-3) / 1e6,
+            "clocks": clocks,
+            "host_cpus": os.cpu_count(),
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    args = ap.parse_args()
+    if args.impl == "reference":
+        if args.steps == 20 and args.warmup == 5:  # CPU steps take seconds: keep the default run to ~a minute
+            args.steps, args.warmup = 3, 1
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -51,11 +51,34 @@ __device__ __forceinline__ void st_stream_f4(float4* p, float4 v) {
                  "f"(v.w));
 }
 
-// numpy fp32 sigmoid 1/(1+exp(-x)): exp rounded to fp32 (computed in fp64 so the rounding is the correct
-// one), then an fp32 add and an fp32 divide, none contracted.
+// numpy's float32 `exp` ufunc, operation for operation (AVX2+FMA3 / AVX512F loops of numpy >= 1.17, the only ones
+// x86 hosts of the reference dispatch to): Cody-Waite reduction by round(x*log2e), a degree-5 / degree-2 rational
+// in fused multiply-adds, one division, scale by 2^k.  It is faithfully — not correctly — rounded (about 39 % of
+// inputs differ from the correctly rounded result by 1 ulp), so a sigmoid → binarize mask can only match the
+// reference's bit for bit if the same roundings are made.  Verified against np.exp on 10^7 inputs
+// (tests/test_numpy_exp_emulation.py restates this function in numpy).
+__device__ __forceinline__ float be_numpy_expf(float x) {
+    if (x != x) return x;
+    if (x >= 88.72283935546875f) return __int_as_float(0x7f800000);
+    if (x <= -103.97208404541015625f) return 0.0f;
+    const float magic = 12582912.0f;  // 0x1.8p23: add/subtract rounds to nearest integer
+    float k = __fmul_rn(x, 1.442695040888963407359924681001892137f);
+    k = __fsub_rn(__fadd_rn(k, magic), magic);
+    float r = __fmaf_rn(k, -6.93145752e-1f, x);
+    r = __fmaf_rn(k, -1.42860677e-6f, r);
+    float num = __fmaf_rn(5.082762527590693718096e-04f, r, 6.757896990527504603057e-03f);
+    num = __fmaf_rn(num, r, 5.114512081637298353406e-02f);
+    num = __fmaf_rn(num, r, 2.473615434895520810817e-01f);
+    num = __fmaf_rn(num, r, 7.257664613233124478488e-01f);
+    num = __fmaf_rn(num, r, 9.999999999980870924916e-01f);
+    float den = __fmaf_rn(2.159509375685829852307e-02f, r, -2.742335390411667452936e-01f);
+    den = __fmaf_rn(den, r, 1.0f);
+    return ldexpf(__fdiv_rn(num, den), (int)k);
+}
+
+// bioimageio `sigmoid` on an fp32 tensor: 1 / (1 + np.exp(-x)), every step rounded to fp32 as numpy does.
 __device__ __forceinline__ float be_sigmoid_f32(float x) {
-    float e = (float)exp(-(double)x);
-    return __fdiv_rn(1.0f, __fadd_rn(1.0f, e));
+    return __fdiv_rn(1.0f, __fadd_rn(1.0f, be_numpy_expf(-x)));
 }
 
 __device__ __forceinline__ double warp_sum(double v) {

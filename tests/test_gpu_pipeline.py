@@ -1,0 +1,91 @@
+"""Whole path on the device against the whole-path oracle.  Downstream integer results are compared on identical
+logits (the GPU forward's output is handed to the CPU oracle), as SURVEY.md Appendix C prescribes."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import oracle as O
+from oracle import paths as P
+
+pytestmark = pytest.mark.gpu
+
+
+def make(shape, spec_kwargs, dev, seed=1, arch="UNet2d", **model_kwargs):
+    from bioengine_worker_b200 import models
+    from bioengine_worker_b200.pipeline import PipelineSpec, TiledPipeline
+
+    models.strict_fp32()
+    pipe = TiledPipeline(shape, PipelineSpec(**spec_kwargs), device=dev)
+    model = models.build_model(arch, seed=seed, **model_kwargs).to(dev)
+    return pipe, model
+
+
+def test_c2_shape_path_fibsem_blend(dev):
+    H, W, B, ov = 700, 900, 256, 64
+    img = O.synthetic_image((1, 1, H, W), 120, seed=2)
+    pipe, model = make((1, 1, H, W), dict(block=(B, B), halo=(32, 32), convention="fibsem", overlap=(ov, ov),
+                                          preprocess="scale_range", return_prob=True, connectivity=2), dev)
+    x = torch.from_numpy(img).to(dev)
+    tiles = pipe.preprocess_and_tile(x)
+    assert np.array_equal(tiles.cpu().numpy(), P.c2_pre(img, B, ov))
+    logits = pipe.forward(model, tiles)
+    res = pipe.stitch_and_label(logits)
+    prob, mask, labels = P.c2_post(logits.cpu().numpy(), (H, W), B, ov, 2)
+    np.testing.assert_allclose(res["prob"].cpu().numpy()[0, 0], prob, rtol=1e-5)
+    assert np.array_equal(res["mask"].cpu().numpy()[0, 0], mask)
+    assert np.array_equal(res["labels"].cpu().numpy()[0, 0], labels)
+    assert res["n_labels"].item() == labels.max() > 0
+    # the public one-call API gives the same answer from a host array
+    res2 = pipe.run(img, model)
+    assert torch.equal(res2["labels"], res["labels"])
+
+
+def test_bioimageio_crop_path_batch(dev):
+    shape, B, halo = (2, 1, 300, 420), 128, 16
+    img = O.synthetic_image(shape, 90, seed=7)
+    pipe, model = make(shape, dict(block=(B, B), halo=(halo, halo), convention="bioimageio", preprocess="scale_range",
+                                   return_prob=True), dev)
+    x = torch.from_numpy(img).to(dev)
+    tiles = pipe.preprocess_and_tile(x)
+    assert np.array_equal(tiles.cpu().numpy(), P.crop_pre(img, (B, B), (halo, halo)))
+    logits = pipe.forward(model, tiles)
+    res = pipe.stitch_and_label(logits)
+    prob, mask, labels = P.crop_post(logits.cpu().numpy(), shape, (B, B), (halo, halo))
+    assert np.array_equal(res["prob"].cpu().numpy(), prob)
+    assert np.array_equal(res["mask"].cpu().numpy(), mask)
+    assert np.array_equal(res["labels"].cpu().numpy()[:, 0], labels)
+
+
+def test_c1_zmuv_binarize_untiled(dev):
+    """BASELINE config 1 shape: 512^2, zero_mean_unit_variance, binarize, CC — one block covering the image."""
+    shape = (1, 1, 512, 512)
+    img = O.synthetic_image(shape, 60, seed=1, microscope=False)
+    pipe, model = make(shape, dict(block=(512, 512), halo=(0, 0), convention="bioimageio",
+                                   preprocess="zero_mean_unit_variance", sigmoid=False, return_prob=True), dev)
+    x = torch.from_numpy(img).to(dev)
+    tiles = pipe.preprocess_and_tile(x)
+    np.testing.assert_allclose(tiles.cpu().numpy(), O.zero_mean_unit_variance(img, axes=(1, 2, 3)), rtol=1e-5, atol=1e-5)
+    logits = pipe.forward(model, tiles)
+    res = pipe.stitch_and_label(logits)
+    raw = logits.cpu().numpy()
+    mask = O.binarize(raw, 0.5)
+    assert np.array_equal(res["mask"].cpu().numpy(), mask)
+    assert np.array_equal(res["labels"].cpu().numpy()[0, 0], O.label(mask[0, 0]))
+
+
+def test_c3_shape_path_3d(dev):
+    """BASELINE config 3 in miniature: fibsem p1/p99 + clip, 3-D tiles with overlap, blend, > 0.5, 26-connected labels."""
+    D, B, ov = (80, 96, 112), 32, 8
+    vol = O.synthetic_image((1, 1) + D, 60, seed=3)
+    pipe, model = make((1, 1) + D, dict(block=(B,) * 3, halo=(4,) * 3, convention="fibsem", overlap=(ov,) * 3,
+                                        preprocess="fibsem", sigmoid=True, return_prob=True, forward_batch=16), dev,
+                       arch="UNet3d", depth=3, initial_features=8)
+    x = torch.from_numpy(vol).to(dev)
+    tiles = pipe.preprocess_and_tile(x)
+    want_tiles = O.fibsem_tiles(O.fibsem_normalize(vol[0, 0]), B, ov)
+    assert np.array_equal(tiles.cpu().numpy()[:, 0], want_tiles)
+    logits = pipe.forward(model, tiles)
+    res = pipe.stitch_and_label(logits)
+    prob, mask, labels = P.c2_post(logits.cpu().numpy(), D, B, ov, 3)
+    assert np.array_equal(res["mask"].cpu().numpy()[0, 0], mask)
+    assert np.array_equal(res["labels"].cpu().numpy()[0, 0], labels)
