@@ -135,6 +135,7 @@ def make_logits_for_reference(img):
     tiles = P.c2_pre(img, TILE, OVERLAP)
     dev = torch.device("cuda:0" if torch.cuda.is_available() else "cpu")
     model = models.build_model("UNet2d", seed=1).to(dev)
+    models.calibrate_head(model, torch.from_numpy(tiles[::61]))
     out = np.empty_like(tiles)
     with torch.no_grad():
         for i in range(0, tiles.shape[0], 32):
@@ -212,6 +213,7 @@ def run_b200(args):
 
     # the forward: once, outside the timed region (and timed on its own)
     tiles = pipe.preprocess_and_tile(x)
+    models.calibrate_head(model, tiles[::61].contiguous())  # random weights, head re-centred so the mask is not trivial
     logits = pipe.forward(model, tiles)
     torch.cuda.synchronize()
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
@@ -290,6 +292,10 @@ def run_b200(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         total_ms, e2e_ms = t.tolist()
 
+    res = kernels_step()
+    n_components = int(res["n_labels"].item())
+    fg_fraction = float(res["mask"].float().mean().item())
+
     if rank == 0:
         px = H * W
         n_tiles = pipe.n_tiles
@@ -337,6 +343,7 @@ def run_b200(args):
                     "h2d_bytes_per_step": px * 4, "d2h_bytes_per_step": px * 4 + 4, "ms_per_step": e2e_ms / args.steps},
             "gpu_launches": launches_per_step * args.steps,
             "unet_forward_ms": forward_ms,
+            "result": {"n_components": n_components, "foreground_fraction": round(fg_fraction, 4)},
             "with_forward_Mpx_s": px / ((ms_per_step + forward_ms) * 1e-3) / 1e6,
             "clocks": clocks,
             "host_cpus": os.cpu_count(),

@@ -1,23 +1,31 @@
 // Connected-component labelling with raster-order numbering (scipy.ndimage.label / skimage.measure.label).
 //
 // Pipeline (all int/bit work, HBM-bound):
-//   1. ccl_tile_kernel     one CTA per 64x64 (2-D) / 64x8x8 (3-D) tile: rows become 64-bit masks by warp
-//                          ballot, a pixel's first parent is the start of its run (pure bit arithmetic, so
-//                          x-links cost nothing), rows are linked with a shared-memory union-find where only
-//                          one lane per touching run pair issues the union; writes parent = global index of
-//                          the tile-local root (minimum linear index) to scratch, -1 for background.
-//   2. ccl_border_kernel   unions across tile faces in global memory (atomicMin union-find).
-//   3. ccl_count / scan / assign   roots (parent == self) are numbered in raster order; a root's scratch
-//                          entry becomes -(id) - 1.
-//   4. ccl_resolve_kernel  every pixel walks to its root and writes id (background decodes to 0).
+//   1. ccl_tile_kernel      one CTA per 64x64 (2-D) / 64x8x8 (3-D) tile.  Rows become 64-bit masks (16-byte loads +
+//                           byte->bit multiply trick, or warp ballots at ragged edges).  The union-find nodes are the
+//                           RUNS of a row (<= 32 per row, 2048 per tile, uint16 parents in shared memory): x-links cost
+//                           nothing, and rows are linked with bit arithmetic that leaves exactly one lane per touching
+//                           run pair to issue the union (atomicMin, path halving).  After a per-run flatten every pixel
+//                           gets parent = global index of its tile-local root pixel (minimum raster index), -1 for
+//                           background; tile roots are also flagged in a 1-bit-per-pixel bitmap and the tile's four
+//                           edge masks are kept for step 2.
+//   2. ccl_edge_kernel      (2-D) one warp per tile links its top and left edge to the neighbouring tiles from the edge
+//                           masks alone, again one union per touching run pair;  ccl_face_kernel (3-D) does it per face
+//                           voxel.  Unions are atomicMin on the global parent array with path halving.
+//   3. ccl_count / scan / assign   surviving roots are numbered in raster order from the root bitmap (2 MB instead of
+//                           a second pass over all parents); a root's entry becomes -(id) - 1.
+//   4. ccl_resolve_kernel   every pixel walks to its root (<= 2-3 hops) and writes id; background decodes to 0.
 #include "be_common.cuh"
 
 namespace {
 
+typedef unsigned long long u64;
+
 constexpr int kThreads = 256;
-constexpr int kTX = 64;          // tile width = one 64-bit row mask
-constexpr int kRows = 64;        // rows per tile (TY * TZ)
-constexpr int kChunk = 2048;     // pixels per block in the numbering passes
+constexpr int kTX = 64;            // tile width = one 64-bit row mask
+constexpr int kRows = 64;          // rows per tile (TY * TZ)
+constexpr int kMaxRuns = kRows * 32;
+constexpr int kWordsPerBlock = 256;  // bitmap words per block in the numbering passes
 
 struct Geom {
     int64_t Z, Y, X;
@@ -26,54 +34,130 @@ struct Geom {
     int conn;
 };
 
-__device__ __forceinline__ int run_start(unsigned long long m, int x) {
-    const unsigned long long zeros_below = ~m & ((1ull << x) - 1ull);
-    return zeros_below ? 64 - __clzll((long long)zeros_below) : 0;
-}
+struct TileEdges {
+    u64 top, bottom, left, right;
+};
+
+// index (within its row) of the run containing set bit x: number of run starts at positions <= x, minus one
+__device__ __forceinline__ int run_index(u64 starts, int x) { return __popcll(starts & ((2ull << x) - 1ull)) - 1; }
 
 __device__ __forceinline__ unsigned sm_find(volatile unsigned* parent, unsigned i) {
+    while (true) {
+        const unsigned p = parent[i];
+        if (p == i) return i;
+        const unsigned gp = parent[p];
+        if (gp != p) parent[i] = gp;  // path halving: any ancestor is a valid parent
+        i = gp;
+    }
+}
+
+// read-only walk, for the flatten phase: there the forest is final and each thread overwrites its own entry with the
+// root, which a concurrent path-halving store could replace by a mere ancestor
+__device__ __forceinline__ unsigned sm_find_ro(const volatile unsigned* parent, unsigned i) {
     unsigned p;
     while ((p = parent[i]) != i) i = p;
     return i;
 }
 
-__device__ __forceinline__ void sm_unite(unsigned* parent, unsigned a, unsigned b) {
+// returns the surviving (smaller) root
+__device__ __forceinline__ unsigned sm_unite(unsigned* parent, unsigned a, unsigned b) {
     while (true) {
         a = sm_find(parent, a);
         b = sm_find(parent, b);
-        if (a == b) return;
+        if (a == b) return a;
         const unsigned hi = max(a, b), lo = min(a, b);
         const unsigned old = atomicMin(&parent[hi], lo);
-        if (old == hi) return;
+        if (old == hi) return lo;
         a = old;
         b = lo;
     }
 }
 
-// Link row `m` (base index bm) with an already-seen neighbour row `u` (base bu).  `full` also links the two
-// x-diagonals.  Per pair of touching runs exactly one lane issues the union.
-__device__ __forceinline__ void link_rows(unsigned* parent, unsigned long long m, unsigned long long u, unsigned bm,
-                                          unsigned bu, bool full, int lane) {
+// Which lanes must issue a union between row m and an already-seen neighbour row u.  One lane per pair of touching
+// runs: the straight link is dropped when the left neighbours are linked too, a diagonal link is dropped when the
+// straight neighbour or the run's own continuation makes it redundant.
+struct LinkMasks {
+    u64 c, l, r;
+};
+__device__ __forceinline__ LinkMasks link_masks(u64 m, u64 u, bool diag) {
+    LinkMasks k;
+    k.c = m & u & ~((m << 1) & (u << 1));
+    k.l = diag ? (m & ~u & (u << 1) & ~(m << 1)) : 0ull;
+    k.r = diag ? (m & ~u & (u >> 1) & ~(m >> 1)) : 0ull;
+    return k;
+}
+
+// pairwise linking of two rows whose runs already carry labels (lab[] indexed by run id)
+__device__ __forceinline__ void link_rows(unsigned* parent, const unsigned short* lab, u64 m, u64 sm_, u64 u, u64 su,
+                                          unsigned bm, unsigned bu, bool diag, int lane) {
     if (!u) return;
-    const unsigned long long both_left = (m << 1) & (u << 1);
-    const unsigned long long need_c = m & u & ~both_left;
-    const unsigned long long need_l = full ? (m & ~u & (u << 1) & ~(m << 1)) : 0ull;
-    const unsigned long long need_r = full ? (m & ~u & (u >> 1) & ~(m >> 1)) : 0ull;
-    if (!(need_c | need_l | need_r)) return;
+    const LinkMasks k = link_masks(m, u, diag);
+    if (!(k.c | k.l | k.r)) return;
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
         const int x = lane + 32 * h;
-        const unsigned long long bit = 1ull << x;
-        if (need_c & bit) sm_unite(parent, bm + run_start(m, x), bu + run_start(u, x));
-        if (need_l & bit) sm_unite(parent, bm + run_start(m, x), bu + run_start(u, x - 1));
-        if (need_r & bit) sm_unite(parent, bm + run_start(m, x), bu + run_start(u, x + 1));
+        const u64 bit = 1ull << x;
+        if ((k.c | k.l | k.r) & bit) {
+            const unsigned a = lab[bm + run_index(sm_, x)];
+            if (k.c & bit) sm_unite(parent, a, lab[bu + run_index(su, x)]);
+            if (k.l & bit) sm_unite(parent, a, lab[bu + run_index(su, x - 1)]);
+            if (k.r & bit) sm_unite(parent, a, lab[bu + run_index(su, x + 1)]);
+        }
     }
 }
 
+// Two-pass style labelling of one row against the row above it, inside a strip that one warp walks top to bottom.
+// Lanes sitting on a run start first publish the start position under the run's index, then lane k takes run k (a
+// row of 64 pixels has at most 32 runs): it looks at the runs of the previous row that touch its run; the first one
+// hands down its label (no union-find traffic at all — the common case), further ones are bridged with unions.
+__device__ __forceinline__ void label_row(unsigned* parent, unsigned short* lab, unsigned char* xstart, u64 m, u64 s,
+                                          u64 u, u64 su, unsigned bm, unsigned bu, bool diag, int lane, u64 le0, u64 le1) {
+    if ((s >> lane) & 1ull) xstart[bm + __popcll(s & le0) - 1] = (unsigned char)lane;
+    if ((s >> (lane + 32)) & 1ull) xstart[bm + __popcll(s & le1) - 1] = (unsigned char)(lane + 32);
+    __syncwarp();
+    if (lane >= __popcll(s)) return;
+    const unsigned id = bm + lane;
+    unsigned label = id;
+    if (u) {
+        const int x = xstart[id];
+        const u64 rest = ~(m >> x);  // first zero above the run start ends the run
+        const int len = rest ? __ffsll((long long)rest) - 1 : 64;
+        int lo = x, hi = x + len - 1;
+        if (diag) {
+            lo = max(lo - 1, 0);
+            hi = min(hi + 1, 63);
+        }
+        const u64 window = ((2ull << hi) - 1ull) & ~((1ull << lo) - 1ull);
+        const u64 t = u & window;
+        if (t) {
+            const int f = __ffsll((long long)t) - 1;
+            label = lab[bu + run_index(su, f)];
+            // further touched runs start strictly after f inside the window
+            u64 more = su & window & ~((2ull << f) - 1ull);
+            while (more) {
+                const int p = __ffsll((long long)more) - 1;
+                more &= more - 1;
+                label = sm_unite(parent, label, lab[bu + run_index(su, p)]);
+            }
+        }
+    }
+    lab[id] = (unsigned short)label;
+}
+
+__device__ __forceinline__ unsigned nibble_of(unsigned w) {
+    // one bit per non-zero byte, lowest address -> lowest bit
+    return (((__vcmpne4(w, 0u) & 0x01010101u) * 0x01020408u) >> 24) & 0xfu;
+}
+
 __global__ void __launch_bounds__(kThreads) ccl_tile_kernel(const uint8_t* __restrict__ mask, int32_t* __restrict__ L,
+                                                            u64* __restrict__ rootbits, TileEdges* __restrict__ edges,
                                                             Geom g) {
-    __shared__ unsigned long long rmask[kRows];
-    __shared__ unsigned parent[kRows * kTX];
+    __shared__ u64 rmask[kRows];
+    __shared__ u64 rstart[kRows];
+    __shared__ __align__(16) unsigned parent[kMaxRuns];   // union-find over labels (= id of the run that made them)
+    __shared__ unsigned short lab[kMaxRuns];              // label of every run
+    __shared__ int32_t glab[kMaxRuns];                    // root label -> global index of its first pixel
+    __shared__ unsigned char xstart[kMaxRuns];            // first pixel (x within the tile) of every run
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int ty_mask = (1 << g.ty_log2) - 1;
     const int bid = blockIdx.x;
@@ -85,60 +169,145 @@ __global__ void __launch_bounds__(kThreads) ccl_tile_kernel(const uint8_t* __res
     const uint8_t* im = mask + (int64_t)blockIdx.y * vol;
     int32_t* Li = L + (int64_t)blockIdx.y * vol;
 
-    for (int r = warp; r < kRows; r += kThreads / 32) {
+    // ---- A: rows -> bit masks ----
+    if ((g.X & 15) == 0 && x0 + kTX <= g.X && (((uintptr_t)im) & 15) == 0) {
+        // 4 lanes x 16 bytes per row, 8 rows per warp: one load instruction per warp
+        const int r = warp * 8 + (lane >> 2), part = lane & 3;
         const int64_t z = z0 + (r >> g.ty_log2), y = y0 + (r & ty_mask);
-        const bool row_ok = (z < g.Z) && (y < g.Y);
-        const uint8_t* p = im + (z * g.Y + y) * g.X + x0;
-        const bool b0 = row_ok && (x0 + lane < g.X) && p[lane] != 0;
-        const bool b1 = row_ok && (x0 + 32 + lane < g.X) && p[32 + lane] != 0;
-        const unsigned lo = __ballot_sync(0xffffffffu, b0), hi = __ballot_sync(0xffffffffu, b1);
-        if (lane == 0) rmask[r] = ((unsigned long long)hi << 32) | lo;
+        u64 v = 0;
+        if (z < g.Z && y < g.Y) {
+            const uint4 q = __ldg(reinterpret_cast<const uint4*>(im + (z * g.Y + y) * g.X + x0) + part);
+            const unsigned bits = nibble_of(q.x) | (nibble_of(q.y) << 4) | (nibble_of(q.z) << 8) | (nibble_of(q.w) << 12);
+            v = (u64)bits << (16 * part);
+        }
+        v |= __shfl_xor_sync(0xffffffffu, v, 1);
+        v |= __shfl_xor_sync(0xffffffffu, v, 2);
+        if (part == 0) {
+            rmask[r] = v;
+            rstart[r] = v & ~(v << 1);
+        }
+    } else {
+        for (int r = warp; r < kRows; r += kThreads / 32) {
+            const int64_t z = z0 + (r >> g.ty_log2), y = y0 + (r & ty_mask);
+            const bool row_ok = (z < g.Z) && (y < g.Y);
+            const uint8_t* p = im + (z * g.Y + y) * g.X + x0;
+            const bool b0 = row_ok && (x0 + lane < g.X) && p[lane] != 0;
+            const bool b1 = row_ok && (x0 + 32 + lane < g.X) && p[32 + lane] != 0;
+            const unsigned lo = __ballot_sync(0xffffffffu, b0), hi = __ballot_sync(0xffffffffu, b1);
+            if (lane == 0) {
+                const u64 v = ((u64)hi << 32) | lo;
+                rmask[r] = v;
+                rstart[r] = v & ~(v << 1);
+                }
+        }
     }
-    for (int i = threadIdx.x; i < kRows * kTX; i += kThreads) parent[i] = i;
+    for (int i = threadIdx.x; i < kMaxRuns; i += kThreads) parent[i] = i;
     __syncthreads();
 
+    // ---- B1: each warp walks its strip of 8 rows top to bottom (2-D: 8 image rows, 3-D: the 8 y-rows of one z) ----
     const int TY = 1 << g.ty_log2;
-    for (int r = warp; r < kRows; r += kThreads / 32) {
-        const unsigned long long m = rmask[r];
-        if (!m) continue;
-        const int lz = r >> g.ty_log2, ly = r & ty_mask;
-        const unsigned bm = r * kTX;
-        if (ly > 0) link_rows(parent, m, rmask[r - 1], bm, (r - 1) * kTX, g.conn >= 2, lane);
-        if (lz > 0) {
-            link_rows(parent, m, rmask[r - TY], bm, (r - TY) * kTX, g.conn >= 2, lane);
+    const bool diag1 = g.conn >= 2;
+    const u64 le0 = (2ull << lane) - 1ull, le1 = (2ull << (lane + 32)) - 1ull;  // bits <= this lane's two pixels
+    {
+        const int r0 = warp * 8;
+        for (int r = r0; r < r0 + 8; ++r) {
+            const u64 m = rmask[r];
+            if (m) {
+                const bool first = (r == r0);
+                label_row(parent, lab, xstart, m, rstart[r], first ? 0ull : rmask[r - 1], first ? 0ull : rstart[r - 1],
+                          r * 32, (r - 1) * 32, diag1, lane, le0, le1);
+            }
+            __syncwarp();
+        }
+    }
+    __syncthreads();
+
+    // ---- B2: pairwise links across strip boundaries (2-D) / between z-planes (3-D) ----
+    if (g.ty_log2 == 6) {
+        const int r = warp * 8;
+        if (warp > 0 && rmask[r])
+            link_rows(parent, lab, rmask[r], rstart[r], rmask[r - 1], rstart[r - 1], r * 32, (r - 1) * 32, diag1, lane);
+    } else {
+        for (int r = warp; r < kRows; r += kThreads / 32) {
+            const u64 m = rmask[r];
+            const int lz = r >> g.ty_log2, ly = r & ty_mask;
+            if (!m || lz == 0) continue;
+            const u64 s = rstart[r];
+            link_rows(parent, lab, m, s, rmask[r - TY], rstart[r - TY], r * 32, (r - TY) * 32, diag1, lane);
             if (g.conn >= 2) {
-                if (ly > 0) link_rows(parent, m, rmask[r - TY - 1], bm, (r - TY - 1) * kTX, g.conn >= 3, lane);
-                if (ly < TY - 1) link_rows(parent, m, rmask[r - TY + 1], bm, (r - TY + 1) * kTX, g.conn >= 3, lane);
+                if (ly > 0)
+                    link_rows(parent, lab, m, s, rmask[r - TY - 1], rstart[r - TY - 1], r * 32, (r - TY - 1) * 32,
+                              g.conn >= 3, lane);
+                if (ly < TY - 1)
+                    link_rows(parent, lab, m, s, rmask[r - TY + 1], rstart[r - TY + 1], r * 32, (r - TY + 1) * 32,
+                              g.conn >= 3, lane);
             }
         }
     }
     __syncthreads();
 
+    // ---- C: flatten per run; a root label is the id of the component's first run in the tile and gets the global
+    //         index of that run's first pixel ----
+    for (int id = threadIdx.x; id < kMaxRuns; id += kThreads) {
+        const int r = id >> 5, k = id & 31;
+        if (k >= __popcll(rstart[r])) continue;
+        const unsigned root = sm_find_ro(parent, lab[id]);
+        lab[id] = (unsigned short)root;
+        if (root == (unsigned)id)
+            glab[id] = (int32_t)(((z0 + (r >> g.ty_log2)) * g.Y + (y0 + (r & ty_mask))) * g.X + x0 + xstart[id]);
+    }
+    __syncthreads();
+
+    // ---- D: per-pixel parents; the tile's roots (run starts whose run kept its own label) go to the root bitmap ----
+    const int64_t wpr = g.tiles_x;
     for (int r = warp; r < kRows; r += kThreads / 32) {
         const int64_t z = z0 + (r >> g.ty_log2), y = y0 + (r & ty_mask);
         if (z >= g.Z || y >= g.Y) continue;
-        const unsigned long long m = rmask[r];
+        const u64 m = rmask[r], s = rstart[r];
         int32_t* row = Li + (z * g.Y + y) * g.X + x0;
+        unsigned rootmask[2];
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
             const int x = lane + 32 * h;
-            if (x0 + x >= g.X) continue;
             int32_t v = -1;
+            bool is_root = false;
             if ((m >> x) & 1ull) {
-                const unsigned start = r * kTX + run_start(m, x);
-                const unsigned root = sm_find(parent, start);
-                const int rr = root >> 6, rx = root & 63;
-                v = (int32_t)(((z0 + (rr >> g.ty_log2)) * g.Y + (y0 + (rr & ty_mask))) * g.X + x0 + rx);
+                const unsigned id = r * 32 + __popcll(s & (h ? le1 : le0)) - 1;
+                const unsigned root = lab[id];
+                v = glab[root];
+                is_root = ((s >> x) & 1ull) && root == id;
             }
-            row[x] = v;
+            rootmask[h] = __ballot_sync(0xffffffffu, is_root);
+            if (x0 + x < g.X) row[x] = v;
+        }
+        if (lane == 0)
+            rootbits[((int64_t)blockIdx.y * g.Z * g.Y + z * g.Y + y) * wpr + tx] = ((u64)rootmask[1] << 32) | rootmask[0];
+    }
+    if (warp == 0 && edges) {
+        const u64 a = rmask[lane], b = rmask[lane + 32];
+        const unsigned l_lo = __ballot_sync(0xffffffffu, a & 1ull), l_hi = __ballot_sync(0xffffffffu, b & 1ull);
+        const unsigned r_lo = __ballot_sync(0xffffffffu, (a >> 63) & 1ull), r_hi = __ballot_sync(0xffffffffu, (b >> 63) & 1ull);
+        if (lane == 0) {
+            TileEdges e;
+            e.top = rmask[0];
+            e.bottom = rmask[kRows - 1];
+            e.left = ((u64)l_hi << 32) | l_lo;
+            e.right = ((u64)r_hi << 32) | r_lo;
+            edges[(int64_t)blockIdx.y * gridDim.x + bid] = e;
         }
     }
 }
 
+// ---- global union-find on the parent array ----
+
 __device__ __forceinline__ int32_t gl_find(volatile int32_t* L, int32_t i) {
-    int32_t p;
-    while ((p = L[i]) != i) i = p;
-    return i;
+    while (true) {
+        const int32_t p = L[i];
+        if (p == i) return i;
+        const int32_t gp = L[p];
+        if (gp != p) L[i] = gp;
+        i = gp;
+    }
 }
 
 __device__ __forceinline__ void gl_unite(int32_t* L, int32_t a, int32_t b) {
@@ -154,9 +323,47 @@ __device__ __forceinline__ void gl_unite(int32_t* L, int32_t a, int32_t b) {
     }
 }
 
-// One thread per voxel; only voxels on a tile face do any memory access.
-__global__ void __launch_bounds__(kThreads) ccl_border_kernel(const uint8_t* __restrict__ mask, int32_t* __restrict__ L,
-                                                              Geom g) {
+// 2-D: one warp per tile; top edge against the tile above, left edge against the tile to the left, two corners.
+// pm / pu give the pixel index of bit i on the two sides of an edge: base + i * step.
+__device__ __forceinline__ void link_edge(int32_t* Li, u64 m, u64 u, int64_t base_m, int64_t base_u, int64_t step,
+                                          bool diag, int lane) {
+    if (!m || !u) return;
+    const LinkMasks k = link_masks(m, u, diag);
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const int i = lane + 32 * h;
+        const u64 bit = 1ull << i;
+        const int32_t a = (int32_t)(base_m + i * step);
+        if (k.c & bit) gl_unite(Li, a, (int32_t)(base_u + i * step));
+        if (k.l & bit) gl_unite(Li, a, (int32_t)(base_u + (i - 1) * step));
+        if (k.r & bit) gl_unite(Li, a, (int32_t)(base_u + (i + 1) * step));
+    }
+}
+
+__global__ void __launch_bounds__(kThreads) ccl_edge_kernel(int32_t* __restrict__ L, const TileEdges* __restrict__ edges,
+                                                            Geom g, int tiles_per_image) {
+    const int t = blockIdx.x * (kThreads / 32) + (threadIdx.x >> 5);
+    if (t >= tiles_per_image) return;
+    const int lane = threadIdx.x & 31;
+    const int tx = t % g.tiles_x, ty = t / g.tiles_x;
+    const TileEdges* E = edges + (int64_t)blockIdx.y * tiles_per_image;
+    int32_t* Li = L + (int64_t)blockIdx.y * g.Y * g.X;
+    const TileEdges me = E[t];
+    const int64_t x0 = (int64_t)tx * kTX, y0 = (int64_t)ty * kRows;
+    const bool diag = g.conn >= 2;
+    if (ty > 0) link_edge(Li, me.top, E[t - g.tiles_x].bottom, y0 * g.X + x0, (y0 - 1) * g.X + x0, 1, diag, lane);
+    if (tx > 0) link_edge(Li, me.left, E[t - 1].right, y0 * g.X + x0, y0 * g.X + x0 - 1, g.X, diag, lane);
+    if (diag && ty > 0 && lane == 0) {
+        if (tx > 0 && (me.top & 1ull) && (E[t - g.tiles_x - 1].bottom >> 63))
+            gl_unite(Li, (int32_t)(y0 * g.X + x0), (int32_t)((y0 - 1) * g.X + x0 - 1));
+        if (tx + 1 < g.tiles_x && (me.top >> 63) && (E[t - g.tiles_x + 1].bottom & 1ull))
+            gl_unite(Li, (int32_t)(y0 * g.X + x0 + 63), (int32_t)((y0 - 1) * g.X + x0 + 64));
+    }
+}
+
+// 3-D: one thread per voxel; only voxels on a tile face do any memory access.
+__global__ void __launch_bounds__(kThreads) ccl_face_kernel(const uint8_t* __restrict__ mask, int32_t* __restrict__ L,
+                                                            Geom g) {
     const int64_t vol = g.Z * g.Y * g.X;
     const int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x;
     if (i >= vol) return;
@@ -195,17 +402,26 @@ __global__ void __launch_bounds__(kThreads) ccl_border_kernel(const uint8_t* __r
     }
 }
 
-// ---- raster-order numbering of the roots ----
+// ---- raster-order numbering of the surviving roots, driven by the root bitmap ----
 
-__global__ void __launch_bounds__(kThreads) ccl_count_kernel(const int32_t* __restrict__ L, int64_t vol,
+__global__ void __launch_bounds__(kThreads) ccl_count_kernel(const int32_t* __restrict__ L, u64* __restrict__ rootbits,
+                                                             int64_t vol, int64_t X, int wpr, int64_t words_per_image,
                                                              int blocks_per_image, int32_t* __restrict__ block_count) {
-    const int64_t base = (int64_t)blockIdx.x * kChunk;
+    const int64_t w = (int64_t)blockIdx.x * kWordsPerBlock + threadIdx.x;
     const int32_t* Li = L + (int64_t)blockIdx.y * vol;
     int c = 0;
-#pragma unroll
-    for (int k = 0; k < kChunk / kThreads; ++k) {
-        const int64_t i = base + k * kThreads + threadIdx.x;
-        if (i < vol) c += (Li[i] == (int32_t)i);
+    if (w < words_per_image) {
+        u64* word = rootbits + (int64_t)blockIdx.y * words_per_image + w;
+        u64 bits = *word, keep = 0;
+        const int64_t base = (w / wpr) * X + (w % wpr) * kTX;
+        while (bits) {
+            const int b = __ffsll((long long)bits) - 1;
+            bits &= bits - 1;
+            const int32_t p = (int32_t)(base + b);
+            if (Li[p] == p) keep |= 1ull << b;  // still a root after the border unions
+        }
+        *word = keep;
+        c = __popcll(keep);
     }
     c = __reduce_add_sync(0xffffffffu, c);
     __shared__ int s[kThreads / 32];
@@ -213,7 +429,7 @@ __global__ void __launch_bounds__(kThreads) ccl_count_kernel(const int32_t* __re
     __syncthreads();
     if (threadIdx.x == 0) {
         int t = 0;
-        for (int w = 0; w < kThreads / 32; ++w) t += s[w];
+        for (int i = 0; i < kThreads / 32; ++i) t += s[i];
         block_count[(int64_t)blockIdx.y * blocks_per_image + blockIdx.x] = t;
     }
 }
@@ -248,19 +464,14 @@ __global__ void __launch_bounds__(1024) ccl_scan_kernel(int32_t* __restrict__ bl
     if (threadIdx.x == 0) n_labels[blockIdx.x] = s_carry;
 }
 
-__global__ void __launch_bounds__(kThreads) ccl_assign_kernel(int32_t* __restrict__ L, int64_t vol, int blocks_per_image,
+__global__ void __launch_bounds__(kThreads) ccl_assign_kernel(int32_t* __restrict__ L, const u64* __restrict__ rootbits,
+                                                              int64_t vol, int64_t X, int wpr, int64_t words_per_image,
+                                                              int blocks_per_image,
                                                               const int32_t* __restrict__ block_offset) {
-    constexpr int per = kChunk / kThreads;
-    const int64_t base = (int64_t)blockIdx.x * kChunk + (int64_t)threadIdx.x * per;
+    const int64_t w = (int64_t)blockIdx.x * kWordsPerBlock + threadIdx.x;
     int32_t* Li = L + (int64_t)blockIdx.y * vol;
-    bool is_root[per];
-    int c = 0;
-#pragma unroll
-    for (int k = 0; k < per; ++k) {
-        const int64_t i = base + k;
-        is_root[k] = (i < vol) && (Li[i] == (int32_t)i);
-        c += is_root[k];
-    }
+    u64 bits = (w < words_per_image) ? rootbits[(int64_t)blockIdx.y * words_per_image + w] : 0ull;
+    const int c = __popcll(bits);
     int incl = c;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -271,10 +482,13 @@ __global__ void __launch_bounds__(kThreads) ccl_assign_kernel(int32_t* __restric
     if ((threadIdx.x & 31) == 31) s_warp[threadIdx.x >> 5] = incl;
     __syncthreads();
     int id = block_offset[(int64_t)blockIdx.y * blocks_per_image + blockIdx.x] + incl - c;
-    for (int w = 0; w < (int)(threadIdx.x >> 5); ++w) id += s_warp[w];
-#pragma unroll
-    for (int k = 0; k < per; ++k)
-        if (is_root[k]) Li[base + k] = -(++id) - 1;
+    for (int i = 0; i < (int)(threadIdx.x >> 5); ++i) id += s_warp[i];
+    const int64_t base = (w / wpr) * X + (w % wpr) * kTX;
+    while (bits) {
+        const int b = __ffsll((long long)bits) - 1;
+        bits &= bits - 1;
+        Li[base + b] = -(++id) - 1;
+    }
 }
 
 __device__ __forceinline__ int32_t resolve_one(const int32_t* __restrict__ Li, int32_t v) {
@@ -300,14 +514,43 @@ __global__ void __launch_bounds__(kThreads) ccl_resolve_kernel(const int32_t* __
     }
 }
 
-inline int blocks_per_image(int64_t vol) { return (int)((vol + kChunk - 1) / kChunk); }
+struct CclWorkspace {
+    int32_t* L;
+    u64* rootbits;
+    TileEdges* edges;
+    int32_t* block_count;
+    int64_t words_per_image;
+    int blocks_per_image;
+    size_t total_bytes;
+};
+
+CclWorkspace carve_ccl_ws(void* ws, int64_t N, int64_t Z, int64_t Y, int64_t X) {
+    CclWorkspace w;
+    const int64_t vol = Z * Y * X;
+    const int ndim = Z > 1 ? 3 : 2;
+    const int TY = ndim == 2 ? 64 : 8, TZ = kRows / TY;
+    const int64_t tiles_x = (X + kTX - 1) / kTX, tiles_y = (Y + TY - 1) / TY, tiles_z = (Z + TZ - 1) / TZ;
+    w.words_per_image = Z * Y * tiles_x;
+    w.blocks_per_image = (int)((w.words_per_image + kWordsPerBlock - 1) / kWordsPerBlock);
+    char* p = (char*)ws;
+    size_t off = 0;
+    w.L = (int32_t*)(p + off);
+    off += be_align_up(sizeof(int32_t) * N * vol, 256);
+    w.rootbits = (u64*)(p + off);
+    off += be_align_up(sizeof(u64) * N * w.words_per_image, 256);
+    w.edges = (TileEdges*)(p + off);
+    off += be_align_up(sizeof(TileEdges) * N * tiles_x * tiles_y * tiles_z, 256);
+    w.block_count = (int32_t*)(p + off);
+    off += be_align_up(sizeof(int32_t) * N * w.blocks_per_image, 256);
+    w.total_bytes = off;
+    return w;
+}
 
 }  // namespace
 
 extern "C" size_t be_ccl_workspace_bytes(int64_t N, int64_t Z, int64_t Y, int64_t X) {
     if (N <= 0 || Z <= 0 || Y <= 0 || X <= 0) return 256;
-    const int64_t vol = Z * Y * X;
-    return be_align_up(sizeof(int32_t) * N * vol, 256) + be_align_up(sizeof(int32_t) * N * blocks_per_image(vol), 256);
+    return carve_ccl_ws(nullptr, N, Z, Y, X).total_bytes;
 }
 
 extern "C" int be_ccl_u8_i32(const uint8_t* mask, int32_t* labels, int64_t N, int64_t Z, int64_t Y, int64_t X,
@@ -334,22 +577,33 @@ extern "C" int be_ccl_u8_i32(const uint8_t* mask, int32_t* labels, int64_t N, in
     const int64_t n_tiles = (int64_t)g.tiles_x * g.tiles_y * g.tiles_z;
     BE_REQUIRE(n_tiles < ((int64_t)1 << 31) - 1, BE_ERR_TOO_LARGE, "be_ccl_u8_i32: too many tiles");
     cudaStream_t s = (cudaStream_t)stream;
-    int32_t* L = (int32_t*)ws;
-    int32_t* block_count = (int32_t*)((char*)ws + be_align_up(sizeof(int32_t) * N * vol, 256));
-    const int bpi = blocks_per_image(vol);
+    const CclWorkspace w = carve_ccl_ws(ws, N, Z, Y, X);
 
-    ccl_tile_kernel<<<dim3((unsigned)n_tiles, (unsigned)N), kThreads, 0, s>>>(mask, L, g);
+    ccl_tile_kernel<<<dim3((unsigned)n_tiles, (unsigned)N), kThreads, 0, s>>>(mask, w.L, w.rootbits,
+                                                                              ndim == 2 ? w.edges : nullptr, g);
     BE_LAUNCH_CHECK();
-    ccl_border_kernel<<<dim3((unsigned)((vol + kThreads - 1) / kThreads), (unsigned)N), kThreads, 0, s>>>(mask, L, g);
+    if (ndim == 2) {
+        if (n_tiles > 1) {
+            const unsigned gx = (unsigned)((n_tiles + kThreads / 32 - 1) / (kThreads / 32));
+            ccl_edge_kernel<<<dim3(gx, (unsigned)N), kThreads, 0, s>>>(w.L, w.edges, g, (int)n_tiles);
+            BE_LAUNCH_CHECK();
+        }
+    } else {
+        ccl_face_kernel<<<dim3((unsigned)((vol + kThreads - 1) / kThreads), (unsigned)N), kThreads, 0, s>>>(mask, w.L, g);
+        BE_LAUNCH_CHECK();
+    }
+    ccl_count_kernel<<<dim3(w.blocks_per_image, (unsigned)N), kThreads, 0, s>>>(w.L, w.rootbits, vol, X, g.tiles_x,
+                                                                               w.words_per_image, w.blocks_per_image,
+                                                                               w.block_count);
     BE_LAUNCH_CHECK();
-    ccl_count_kernel<<<dim3(bpi, (unsigned)N), kThreads, 0, s>>>(L, vol, bpi, block_count);
+    ccl_scan_kernel<<<(unsigned)N, 1024, 0, s>>>(w.block_count, w.blocks_per_image, n_labels);
     BE_LAUNCH_CHECK();
-    ccl_scan_kernel<<<(unsigned)N, 1024, 0, s>>>(block_count, bpi, n_labels);
-    BE_LAUNCH_CHECK();
-    ccl_assign_kernel<<<dim3(bpi, (unsigned)N), kThreads, 0, s>>>(L, vol, bpi, block_count);
+    ccl_assign_kernel<<<dim3(w.blocks_per_image, (unsigned)N), kThreads, 0, s>>>(w.L, w.rootbits, vol, X, g.tiles_x,
+                                                                                w.words_per_image, w.blocks_per_image,
+                                                                                w.block_count);
     BE_LAUNCH_CHECK();
     ccl_resolve_kernel<<<dim3((unsigned)((vol + kThreads * 4 - 1) / (kThreads * 4)), (unsigned)N), kThreads, 0, s>>>(
-        L, labels, vol);
+        w.L, labels, vol);
     BE_LAUNCH_CHECK();
     return BE_OK;
 }

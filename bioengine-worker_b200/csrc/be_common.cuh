@@ -40,8 +40,8 @@ static inline size_t be_align_up(size_t v, size_t a) { return (v + a - 1) / a * 
 
 // Streaming loads/stores: data touched once goes around L1 so it does not evict the small tables.
 __device__ __forceinline__ float4 ld_stream_f4(const float4* p) {
-    float4 r;
-    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+    float4 r;  // not volatile: the compiler may (and should) hoist several of these ahead of their uses
+    asm("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
                  : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
                  : "l"(p));
     return r;
@@ -79,6 +79,30 @@ __device__ __forceinline__ float be_numpy_expf(float x) {
 // bioimageio `sigmoid` on an fp32 tensor: 1 / (1 + np.exp(-x)), every step rounded to fp32 as numpy does.
 __device__ __forceinline__ float be_sigmoid_f32(float x) {
     return __fdiv_rn(1.0f, __fadd_rn(1.0f, be_numpy_expf(-x)));
+}
+
+// (float)(n / d) with the fp64 quotient correctly rounded first — what numpy does when an fp64 expression is cast to
+// fp32 — without paying for an IEEE fp64 division per element.  q = n * r, r ~ 1/d to a few ulp, is within 2^-50 of
+// the exact quotient; it rounds to the same fp32 value as the correctly rounded quotient unless it lies within 2^-48
+// of an fp32 rounding boundary (the midpoint between two neighbouring fp32 values: low 29 mantissa bits = 2^28).
+// Those ~1 in 10^7 elements, and anything outside the normal fp32 range, take the exact division.
+__device__ __forceinline__ double be_fast_rcp(double d) {
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d));
+    r = fma(fma(-d, r, 1.0), r, r);
+    r = fma(fma(-d, r, 1.0), r, r);
+    return r;
+}
+__device__ __forceinline__ float be_div_to_f32(double n, double d, double r) {
+    const double q = n * r;
+    if (n == 0.0) return (float)q;  // +-0 / d (and 0/0 -> NaN through r = inf), very common at the lower quantile
+    const unsigned long long b = (unsigned long long)__double_as_longlong(q);
+    const unsigned low = (unsigned)(b & 0x1fffffffull);   // bits below fp32 precision
+    const unsigned ex = (unsigned)(b >> 52) & 0x7ffu;
+    const bool near_mid = (low - (0x10000000u - 64u)) <= 128u;
+    const bool normal = ex > (1023u - 126u) && ex < (1023u + 127u);
+    if (!near_mid && normal) return (float)q;
+    return (float)__ddiv_rn(n, d);
 }
 
 __device__ __forceinline__ double warp_sum(double v) {

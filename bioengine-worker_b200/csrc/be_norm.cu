@@ -19,11 +19,15 @@ struct SegSplit {
     int bps;
     int64_t chunk;
 };
-inline SegSplit split_segment(int64_t seg_len) {
-    const int64_t per_block = (int64_t)kThreads * 4 * 8;
-    int64_t bps = (seg_len + per_block - 1) / per_block;
+inline SegSplit split_segment(int64_t n_seg, int64_t seg_len) {
+    // Few fat blocks: a block's fixed cost (zeroing and flushing a shared histogram, the block reduction) is paid
+    // once per ~10^4 elements, and the whole grid is about 8 CTAs per SM across all segments.
+    const int64_t min_per_block = (int64_t)kThreads * 16;
+    int64_t bps = kMaxBlocksPerSeg / (n_seg < 1 ? 1 : n_seg);
     if (bps < 1) bps = 1;
-    if (bps > kMaxBlocksPerSeg) bps = kMaxBlocksPerSeg;
+    const int64_t most = (seg_len + min_per_block - 1) / min_per_block;
+    if (bps > most) bps = most;
+    if (bps < 1) bps = 1;
     int64_t chunk = (seg_len + bps - 1) / bps;
     chunk = (chunk + 3) / 4 * 4;
     bps = (seg_len + chunk - 1) / chunk;
@@ -31,7 +35,8 @@ inline SegSplit split_segment(int64_t seg_len) {
     return {(int)bps, chunk};
 }
 
-// Apply f to every element of p[0..n) with the whole block; float4 body, scalar head/tail.
+// Apply f to every element of p[0..n) with the whole block; float4 body, scalar head/tail.  Four independent 16-byte
+// loads are issued before any of them is consumed: 64 B in flight per thread is what keeps HBM busy at ~2k threads/SM.
 template <class F>
 __device__ __forceinline__ void block_foreach(const float* __restrict__ p, int64_t n, F f) {
     int64_t head = ((16 - ((uintptr_t)p & 15)) & 15) >> 2;
@@ -39,13 +44,20 @@ __device__ __forceinline__ void block_foreach(const float* __restrict__ p, int64
     if ((int64_t)threadIdx.x < head) f(p[threadIdx.x]);
     const float4* p4 = reinterpret_cast<const float4*>(p + head);
     const int64_t n4 = (n - head) >> 2;
-#pragma unroll 4
-    for (int64_t i = threadIdx.x; i < n4; i += kThreads) {
-        float4 v = ld_stream_f4(p4 + i);
-        f(v.x);
-        f(v.y);
-        f(v.z);
-        f(v.w);
+    int64_t i = threadIdx.x;
+    for (; i + 3 * kThreads < n4; i += 4 * kThreads) {
+        const float4 a = ld_stream_f4(p4 + i);
+        const float4 b = ld_stream_f4(p4 + i + kThreads);
+        const float4 c = ld_stream_f4(p4 + i + 2 * kThreads);
+        const float4 d = ld_stream_f4(p4 + i + 3 * kThreads);
+        f(a.x); f(a.y); f(a.z); f(a.w);
+        f(b.x); f(b.y); f(b.z); f(b.w);
+        f(c.x); f(c.y); f(c.z); f(c.w);
+        f(d.x); f(d.y); f(d.z); f(d.w);
+    }
+    for (; i < n4; i += kThreads) {
+        const float4 v = ld_stream_f4(p4 + i);
+        f(v.x); f(v.y); f(v.z); f(v.w);
     }
     const int64_t done = head + (n4 << 2);
     if (done + (int64_t)threadIdx.x < n) f(p[done + threadIdx.x]);
@@ -367,9 +379,20 @@ __global__ void __launch_bounds__(kThreads) qsel_level12_kernel(const float* __r
     const int64_t begin = (int64_t)blockIdx.x * chunk;
     const int64_t end = min(begin + chunk, seg_len);
     RunCounter rc[kMaxRanks];
+    // A bucket of keys is an interval of floats, so almost every element is rejected by two float compares against the
+    // hull of the (<= 4, usually 1-2) wanted buckets; NaNs fail both.  The inclusive float test lets both zeros through
+    // at a bucket edge; the exact key test below sorts them out.
+    float fmin = __int_as_float(0x7f800000), fmax = __int_as_float(0xff800000);
+#pragma unroll
+    for (int g = 0; g < kMaxRanks; ++g) {
+        if (g < n_groups) {
+            fmin = fminf(fmin, key_to_f32(gp[g] << kHiShift));
+            fmax = fmaxf(fmax, key_to_f32((gp[g] << kHiShift) | ((1u << kHiShift) - 1u)));
+        }
+    }
     if (n_valid > 0) {
         block_foreach(xs + begin, end - begin, [&](float v) {
-            if (v == v) {
+            if (v >= fmin && v <= fmax) {
                 const uint32_t key = f32_to_key(v);
                 const uint32_t hi = key >> kHiShift;
                 const uint32_t digit = (key >> kShift) & kMask;
@@ -435,10 +458,11 @@ __global__ void __launch_bounds__(kThreads) qsel_level12_kernel(const float* __r
 // elementwise
 // ---------------------------------------------------------------------------------------------------
 
-__device__ __forceinline__ float normalize_one(float v, double sub, double div, int clip, float lo, float hi) {
-    double r = __ddiv_rn(__dsub_rn((double)v, sub), div);
-    if (clip && r == r) r = fmin(fmax(r, (double)lo), (double)hi);  // NaN passes through, as in np.clip
-    return (float)r;
+__device__ __forceinline__ float normalize_one(float v, double sub, double div, double rdiv, int clip, float lo,
+                                               float hi) {
+    float r = be_div_to_f32(__dsub_rn((double)v, sub), div, rdiv);
+    if (clip && r == r) r = fminf(fmaxf(r, lo), hi);  // NaN passes through, as in np.clip
+    return r;
 }
 
 __global__ void __launch_bounds__(kThreads) normalize_kernel(const float* __restrict__ x, float* __restrict__ y,
@@ -446,6 +470,7 @@ __global__ void __launch_bounds__(kThreads) normalize_kernel(const float* __rest
                                                              float lo, float hi) {
     const int64_t seg = blockIdx.y;
     const double sub = norm[seg * 2], div = norm[seg * 2 + 1];
+    const double rdiv = be_fast_rcp(div);
     const float* xs = x + seg * seg_len;
     float* ys = y + seg * seg_len;
     const bool vec = ((((uintptr_t)xs | (uintptr_t)ys) & 15) == 0);
@@ -454,17 +479,17 @@ __global__ void __launch_bounds__(kThreads) normalize_kernel(const float* __rest
         const int64_t n4 = seg_len >> 2;
         for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n4; i += stride) {
             float4 v = ld_stream_f4(reinterpret_cast<const float4*>(xs) + i);
-            v.x = normalize_one(v.x, sub, div, clip, lo, hi);
-            v.y = normalize_one(v.y, sub, div, clip, lo, hi);
-            v.z = normalize_one(v.z, sub, div, clip, lo, hi);
-            v.w = normalize_one(v.w, sub, div, clip, lo, hi);
+            v.x = normalize_one(v.x, sub, div, rdiv, clip, lo, hi);
+            v.y = normalize_one(v.y, sub, div, rdiv, clip, lo, hi);
+            v.z = normalize_one(v.z, sub, div, rdiv, clip, lo, hi);
+            v.w = normalize_one(v.w, sub, div, rdiv, clip, lo, hi);
             st_stream_f4(reinterpret_cast<float4*>(ys) + i, v);
         }
         for (int64_t i = (n4 << 2) + (int64_t)blockIdx.x * kThreads + threadIdx.x; i < seg_len; i += stride)
-            ys[i] = normalize_one(xs[i], sub, div, clip, lo, hi);
+            ys[i] = normalize_one(xs[i], sub, div, rdiv, clip, lo, hi);
     } else {
         for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < seg_len; i += stride)
-            ys[i] = normalize_one(xs[i], sub, div, clip, lo, hi);
+            ys[i] = normalize_one(xs[i], sub, div, rdiv, clip, lo, hi);
     }
 }
 
@@ -533,7 +558,7 @@ inline int stream_grid(int64_t n_items_per_thread_units) {
 
 extern "C" size_t be_meanvar_workspace_bytes(int64_t n_seg, int64_t seg_len) {
     if (n_seg <= 0 || seg_len <= 0) return 256;
-    const SegSplit sp = split_segment(seg_len);
+    const SegSplit sp = split_segment(n_seg, seg_len);
     return be_align_up(sizeof(unsigned) * n_seg, 256) + be_align_up(sizeof(double) * 2 * sp.bps * n_seg, 256);
 }
 
@@ -544,7 +569,7 @@ extern "C" int be_meanvar_f32(const float* x, int64_t n_seg, int64_t seg_len, do
                (long long)n_seg, (long long)seg_len);
     BE_REQUIRE(n_seg <= 65535, BE_ERR_TOO_LARGE, "be_meanvar_f32: n_seg %lld > 65535", (long long)n_seg);
     cudaStream_t s = (cudaStream_t)stream;
-    const SegSplit sp = split_segment(seg_len);
+    const SegSplit sp = split_segment(n_seg, seg_len);
     unsigned* counters = (unsigned*)ws;
     double* partials = (double*)((char*)ws + be_align_up(sizeof(unsigned) * n_seg, 256));
     BE_CUDA(cudaMemsetAsync(counters, 0, sizeof(unsigned) * n_seg, s));
@@ -570,7 +595,7 @@ extern "C" int be_quantile_f32(const float* x, int64_t n_seg, int64_t seg_len, c
     BE_REQUIRE(seg_len < (int64_t)1 << 31, BE_ERR_TOO_LARGE, "be_quantile_f32: seg_len %lld >= 2^31", (long long)seg_len);
     BE_REQUIRE(n_seg <= 65535, BE_ERR_TOO_LARGE, "be_quantile_f32: n_seg %lld > 65535", (long long)n_seg);
     cudaStream_t s = (cudaStream_t)stream;
-    const SegSplit sp = split_segment(seg_len);
+    const SegSplit sp = split_segment(n_seg, seg_len);
     QWorkspace w = carve_quantile_ws(ws, n_seg);
     BE_CUDA(cudaMemsetAsync(ws, 0, w.zero_bytes, s));
     const dim3 grid(sp.bps, (unsigned)n_seg);

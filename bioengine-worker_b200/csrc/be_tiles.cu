@@ -15,16 +15,20 @@ struct Dims {
     int Tz, Ty, Tx, Bz, By, Bx;
 };
 
-__device__ __forceinline__ float norm_apply(float v, double sub, double div, int clip, float lo, float hi) {
-    double r = __ddiv_rn(__dsub_rn((double)v, sub), div);
-    if (clip && r == r) r = fmin(fmax(r, (double)lo), (double)hi);
-    return (float)r;
+__device__ __forceinline__ float norm_apply(float v, double sub, double div, double rdiv, int clip, float lo, float hi) {
+    // np.clip on the fp64 quotient then a cast equals a clip of the cast value: the bounds are fp32 numbers
+    float r = be_div_to_f32(__dsub_rn((double)v, sub), div, rdiv);
+    if (clip && r == r) r = fminf(fmaxf(r, lo), hi);
+    return r;
 }
 
 // ---------------------------------------------------------------------------------------------------
 // gather
 // ---------------------------------------------------------------------------------------------------
 
+// grid: x = tile (n, kz, ky, kx), y = (c, iz), z = a band of tile rows.  A thread owns one 4-px column unit and walks
+// the rows of its band, so the tile / plane decomposition (integer divides) is paid once per thread, not once per
+// 16 bytes, and several independent row loads are in flight per thread.
 template <bool NORM>
 __global__ void __launch_bounds__(kThreads) tile_gather_kernel(const float* __restrict__ img, float* __restrict__ tiles,
                                                                Dims d, const int32_t* __restrict__ zsrc,
@@ -32,63 +36,73 @@ __global__ void __launch_bounds__(kThreads) tile_gather_kernel(const float* __re
                                                                const int32_t* __restrict__ xsrc,
                                                                const double* __restrict__ norm, int norm_mode, int clip,
                                                                float clip_lo, float clip_hi, int units_per_row,
-                                                               int64_t n_units) {
-    const int64_t gid = (int64_t)blockIdx.x * kThreads + threadIdx.x;
-    if (gid >= n_units) return;
-    const int u = (int)(gid % units_per_row);
-    int64_t r = gid / units_per_row;  // row index over (n, kz, ky, kx, c, iz, iy)
-    const int iy = (int)(r % d.By);
-    r /= d.By;
-    const int iz = (int)(r % d.Bz);
-    r /= d.Bz;
-    const int c = (int)(r % d.C);
-    r /= d.C;
-    const int kx = (int)(r % d.Tx);
-    r /= d.Tx;
-    const int ky = (int)(r % d.Ty);
-    r /= d.Ty;
-    const int kz = (int)(r % d.Tz);
-    const int64_t n = r / d.Tz;
+                                                               int rows_per_band) {
+    const int ucols = min(units_per_row, kThreads);     // column units the block covers per sweep
+    const int u_in = threadIdx.x % ucols;
+    const int r_in = threadIdx.x / ucols;               // first row offset inside the band
+    const int r_step = kThreads / ucols;                // rows the block covers per sweep
+    if (r_in >= r_step) return;
+    unsigned t = blockIdx.x;
+    const int kx = t % d.Tx;
+    t /= d.Tx;
+    const int ky = t % d.Ty;
+    t /= d.Ty;
+    const int kz = t % d.Tz;
+    const int64_t n = t / d.Tz;
+    const int c = blockIdx.y / d.Bz, iz = blockIdx.y - c * d.Bz;
+    const int iy0 = blockIdx.z * rows_per_band, iy1 = min(iy0 + rows_per_band, d.By);
 
     const int64_t sz = zsrc[kz * d.Bz + iz];
-    const int64_t sy = ysrc[ky * d.By + iy];
-    const float* src = img + (((n * d.C + c) * d.Z + sz) * d.Y + sy) * d.X;
-    const int32_t* xs = xsrc + kx * d.Bx + u * 4;
-    float* dst = tiles + (gid / units_per_row) * d.Bx + u * 4;
+    const float* plane = img + ((n * d.C + c) * d.Z + sz) * d.Y * d.X;
+    const int32_t* ys = ysrc + ky * d.By;
+    float* dst_tile = tiles + (((int64_t)blockIdx.x * d.C + c) * d.Bz + iz) * (int64_t)d.By * d.Bx;
 
-    double sub = 0.0, div = 1.0;
+    double sub = 0.0, div = 1.0, rdiv = 1.0;
     if (NORM) {
         const int64_t s = (norm_mode == 1) ? (n * d.C + c) : n;
         sub = norm[2 * s];
         div = norm[2 * s + 1];
+        rdiv = be_fast_rcp(div);
     }
 
+    for (int u = u_in; u < units_per_row; u += ucols) {
+    float* dst_plane = dst_tile + u * 4;
     const int rem = d.Bx - u * 4;
+    const int32_t* xs = xsrc + kx * d.Bx + u * 4;
     if (rem >= 4 && (d.Bx & 3) == 0) {
         const int4 xi = *reinterpret_cast<const int4*>(xs);
-        float4 v;
-        const float* p0 = src + xi.x;
-        if (xi.y == xi.x + 1 && xi.z == xi.x + 2 && xi.w == xi.x + 3 && (((uintptr_t)p0) & 15) == 0) {
-            v = __ldg(reinterpret_cast<const float4*>(p0));
-        } else {
-            v.x = __ldg(src + xi.x);
-            v.y = __ldg(src + xi.y);
-            v.z = __ldg(src + xi.z);
-            v.w = __ldg(src + xi.w);
+        const bool contiguous = xi.y == xi.x + 1 && xi.z == xi.x + 2 && xi.w == xi.x + 3 && ((d.X & 3) == 0) &&
+                                ((xi.x & 3) == 0) && ((((uintptr_t)img) & 15) == 0);
+#pragma unroll 4
+        for (int iy = iy0 + r_in; iy < iy1; iy += r_step) {
+            const float* src = plane + (int64_t)ys[iy] * d.X;
+            float4 v;
+            if (contiguous) {
+                v = __ldg(reinterpret_cast<const float4*>(src + xi.x));
+            } else {
+                v.x = __ldg(src + xi.x);
+                v.y = __ldg(src + xi.y);
+                v.z = __ldg(src + xi.z);
+                v.w = __ldg(src + xi.w);
+            }
+            if (NORM) {
+                v.x = norm_apply(v.x, sub, div, rdiv, clip, clip_lo, clip_hi);
+                v.y = norm_apply(v.y, sub, div, rdiv, clip, clip_lo, clip_hi);
+                v.z = norm_apply(v.z, sub, div, rdiv, clip, clip_lo, clip_hi);
+                v.w = norm_apply(v.w, sub, div, rdiv, clip, clip_lo, clip_hi);
+            }
+            st_stream_f4(reinterpret_cast<float4*>(dst_plane + (int64_t)iy * d.Bx), v);
         }
-        if (NORM) {
-            v.x = norm_apply(v.x, sub, div, clip, clip_lo, clip_hi);
-            v.y = norm_apply(v.y, sub, div, clip, clip_lo, clip_hi);
-            v.z = norm_apply(v.z, sub, div, clip, clip_lo, clip_hi);
-            v.w = norm_apply(v.w, sub, div, clip, clip_lo, clip_hi);
-        }
-        st_stream_f4(reinterpret_cast<float4*>(dst), v);
     } else {
-        for (int j = 0; j < rem && j < 4; ++j) {
-            float v = __ldg(src + xs[j]);
-            if (NORM) v = norm_apply(v, sub, div, clip, clip_lo, clip_hi);
-            dst[j] = v;
+        for (int iy = iy0 + r_in; iy < iy1; iy += r_step) {
+            const float* src = plane + (int64_t)ys[iy] * d.X;
+            for (int j = 0; j < rem && j < 4; ++j) {
+                float v = __ldg(src + xs[j]);
+                if (NORM) v = norm_apply(v, sub, div, rdiv, clip, clip_lo, clip_hi);
+                dst_plane[(int64_t)iy * d.Bx + j] = v;
+            }
         }
+    }
     }
 }
 
@@ -96,24 +110,54 @@ __global__ void __launch_bounds__(kThreads) tile_gather_kernel(const float* __re
 // stitch: shared epilogue
 // ---------------------------------------------------------------------------------------------------
 
-__device__ __forceinline__ void store4(float* __restrict__ out, uint8_t* __restrict__ mask, int64_t o, int cnt,
-                                       const float v[4], float thr, bool aligned) {
+// Post-processing fused into the stitchers.  `fast` (mask-only sigmoid): the decision sigmoid(v) > thr is v > logit(thr)
+// for every v farther than a safety margin from logit(thr) — [lo, hi] is that margin band, computed by the host; only
+// values inside the band (a vanishing fraction) take the exact numpy-fp32 sigmoid.
+struct Epilogue {
+    int mode;   // BE_EPI_*
+    int fast;   // 1: mask only, sigmoid decided by the band test
+    float thr, lo, hi;
+};
+
+__device__ __forceinline__ void finish4(float* __restrict__ out, uint8_t* __restrict__ mask, int64_t o, int cnt,
+                                        float v[4], const Epilogue& e, bool aligned) {
+    bool m[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        if (e.fast) {
+            m[j] = (v[j] > e.hi) || (!(v[j] < e.lo) && be_sigmoid_f32(v[j]) > e.thr);
+        } else {
+            if (e.mode == BE_EPI_SIGMOID) v[j] = be_sigmoid_f32(v[j]);
+            m[j] = v[j] > e.thr;
+        }
+    }
     if (cnt == 4 && aligned) {
         if (out) st_stream_f4(reinterpret_cast<float4*>(out + o), make_float4(v[0], v[1], v[2], v[3]));
-        if (mask) {
-            uchar4 m;
-            m.x = v[0] > thr;
-            m.y = v[1] > thr;
-            m.z = v[2] > thr;
-            m.w = v[3] > thr;
-            *reinterpret_cast<uchar4*>(mask + o) = m;
-        }
+        if (mask) *reinterpret_cast<uchar4*>(mask + o) = make_uchar4(m[0], m[1], m[2], m[3]);
     } else {
         for (int j = 0; j < cnt; ++j) {
             if (out) out[o + j] = v[j];
-            if (mask) mask[o + j] = v[j] > thr;
+            if (mask) mask[o + j] = m[j];
         }
     }
+}
+
+// grid: x = 4-px units along the row, y = output row y, z = (n, c, z) planes (grid-strided)
+struct RowIndex {
+    int u, y, z, c;
+    int64_t n, row;
+};
+
+__device__ __forceinline__ bool row_index(const Dims& d, int units_per_row, unsigned plane, RowIndex* r) {
+    r->u = blockIdx.x * kThreads + threadIdx.x;
+    if (r->u >= units_per_row) return false;
+    r->y = blockIdx.y;
+    r->z = plane % (unsigned)d.Z;
+    const unsigned nc = plane / (unsigned)d.Z;
+    r->c = nc % (unsigned)d.C;
+    r->n = nc / (unsigned)d.C;
+    r->row = (int64_t)plane * d.Y + r->y;
+    return true;
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -124,41 +168,31 @@ __global__ void __launch_bounds__(kThreads) stitch_crop_kernel(const float* __re
                                                                uint8_t* __restrict__ mask, Dims d,
                                                                const int32_t* __restrict__ zsel,
                                                                const int32_t* __restrict__ ysel,
-                                                               const int32_t* __restrict__ xsel, int epilogue, float thr,
-                                                               int units_per_row, int64_t n_units) {
-    const int64_t gid = (int64_t)blockIdx.x * kThreads + threadIdx.x;
-    if (gid >= n_units) return;
-    const int u = (int)(gid % units_per_row);
-    int64_t r = gid / units_per_row;  // (n, c, z, y)
-    const int64_t row = r;
-    const int y = (int)(r % d.Y);
-    r /= d.Y;
-    const int z = (int)(r % d.Z);
-    r /= d.Z;
-    const int c = (int)(r % d.C);
-    const int64_t n = r / d.C;
+                                                               const int32_t* __restrict__ xsel, Epilogue e,
+                                                               int units_per_row, unsigned n_planes) {
+    for (unsigned plane = blockIdx.z; plane < n_planes; plane += gridDim.z) {
+        RowIndex r;
+        if (!row_index(d, units_per_row, plane, &r)) return;
+        const int vz = zsel[r.z], vy = ysel[r.y];
+        const int kz = vz / d.Bz, iz = vz - kz * d.Bz;
+        const int ky = vy / d.By, iy = vy - ky * d.By;
+        const int64_t tvol = (int64_t)d.Bz * d.By * d.Bx;
+        const int64_t trow = ((r.n * d.Tz + kz) * d.Ty + ky) * d.Tx;  // + kx
+        const int64_t in_tile = ((int64_t)r.c * d.Bz + iz) * d.By * d.Bx + (int64_t)iy * d.Bx;
 
-    const int vz = zsel[z], vy = ysel[y];
-    const int kz = vz / d.Bz, iz = vz - kz * d.Bz;
-    const int ky = vy / d.By, iy = vy - ky * d.By;
-    const int64_t tvol = (int64_t)d.Bz * d.By * d.Bx;
-    const int64_t trow = ((n * d.Tz + kz) * d.Ty + ky) * d.Tx;  // + kx
-    const int64_t in_tile = ((int64_t)c * d.Bz + iz) * d.By * d.Bx + (int64_t)iy * d.Bx;
-
-    const int x0 = u * 4;
-    const int cnt = min(4, (int)d.X - x0);
-    float v[4];
+        const int x0 = r.u * 4;
+        const int cnt = min(4, (int)d.X - x0);
+        float v[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-        if (j < cnt) {
-            const int vx = xsel[x0 + j];
-            const int kx = vx / d.Bx, ix = vx - kx * d.Bx;
-            float t = __ldg(tiles + (trow + kx) * d.C * tvol + in_tile + ix);
-            if (epilogue == BE_EPI_SIGMOID) t = be_sigmoid_f32(t);
-            v[j] = t;
+        for (int j = 0; j < 4; ++j) {
+            if (j < cnt) {
+                const int vx = xsel[x0 + j];
+                const int kx = vx / d.Bx, ix = vx - kx * d.Bx;
+                v[j] = __ldg(tiles + (trow + kx) * d.C * tvol + in_tile + ix);
+            }
         }
+        finish4(out, mask, r.row * d.X + x0, cnt, v, e, (d.X & 3) == 0);
     }
-    store4(out, mask, row * d.X + x0, cnt, v, thr, (d.X & 3) == 0);
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -169,6 +203,7 @@ struct Strides {
     int Sz, Sy, Sx;
 };
 
+// tiles k covering output coordinate p: k*S <= p < k*S + B, 0 <= k < T
 __device__ __forceinline__ void cover(int p, int B, int S, int T, int* lo, int* hi) {
     *hi = min(p / S, T - 1);
     const int t = p - B + 1;
@@ -179,62 +214,77 @@ __global__ void __launch_bounds__(kThreads) stitch_blend_kernel(const float* __r
                                                                 uint8_t* __restrict__ mask, Dims d, Strides s,
                                                                 const double* __restrict__ wz,
                                                                 const double* __restrict__ wy,
-                                                                const double* __restrict__ wx, int epilogue, float thr,
-                                                                int units_per_row, int64_t n_units) {
-    const int64_t gid = (int64_t)blockIdx.x * kThreads + threadIdx.x;
-    if (gid >= n_units) return;
-    const int u = (int)(gid % units_per_row);
-    int64_t r = gid / units_per_row;
-    const int64_t row = r;
-    const int y = (int)(r % d.Y);
-    r /= d.Y;
-    const int z = (int)(r % d.Z);
-    r /= d.Z;
-    const int c = (int)(r % d.C);
-    const int64_t n = r / d.C;
-
+                                                                const double* __restrict__ wx, Epilogue e,
+                                                                int units_per_row, unsigned n_planes) {
+    const int u = blockIdx.x * kThreads + threadIdx.x;
+    if (u >= units_per_row) return;
+    const int y = blockIdx.y;
     const int64_t tvol = (int64_t)d.Bz * d.By * d.Bx;
+    const int64_t tile_stride = d.C * tvol;  // elements between consecutive tiles
     const int x0 = u * 4;
     const int cnt = min(4, (int)d.X - x0);
-    int kz_lo, kz_hi, ky_lo, ky_hi;
-    cover(z, d.Bz, s.Sz, d.Tz, &kz_lo, &kz_hi);
-    cover(y, d.By, s.Sy, d.Ty, &ky_lo, &ky_hi);
+    // x cover: one division pair for the first pixel, the other three follow by comparison
     int kx_lo[4], kx_hi[4];
+    cover(x0, d.Bx, s.Sx, d.Tx, &kx_lo[0], &kx_hi[0]);
 #pragma unroll
-    for (int j = 0; j < 4; ++j) cover(min(x0 + j, (int)d.X - 1), d.Bx, s.Sx, d.Tx, &kx_lo[j], &kx_hi[j]);
+    for (int j = 1; j < 4; ++j) {
+        const int x = x0 + j;
+        kx_hi[j] = kx_hi[j - 1] + ((kx_hi[j - 1] + 1 < d.Tx && (kx_hi[j - 1] + 1) * s.Sx <= x) ? 1 : 0);
+        kx_lo[j] = kx_lo[j - 1] + ((kx_lo[j - 1] * s.Sx + d.Bx <= x) ? 1 : 0);
+    }
+    int ky_lo, ky_hi;
+    cover(y, d.By, s.Sy, d.Ty, &ky_lo, &ky_hi);  // block-uniform
 
-    double acc[4] = {0.0, 0.0, 0.0, 0.0}, wacc[4] = {0.0, 0.0, 0.0, 0.0};
-    // ascending (kz, ky, kx): the order a sequential walk over the reference's tile_coords list adds them
-    for (int kz = kz_lo; kz <= kz_hi; ++kz) {
-        const int iz = z - kz * s.Sz;
-        const double wzv = wz[iz];
-        for (int ky = ky_lo; ky <= ky_hi; ++ky) {
-            const int iy = y - ky * s.Sy;
-            const double wzy = __dmul_rn(wzv, wy[iy]);
-            const int64_t trow = ((n * d.Tz + kz) * d.Ty + ky) * d.Tx;
-            const int64_t in_tile = (((int64_t)c * d.Bz + iz) * d.By + iy) * d.Bx;
+    for (unsigned plane = blockIdx.z; plane < n_planes; plane += gridDim.z) {
+        const int z = plane % (unsigned)d.Z;
+        const unsigned nc = plane / (unsigned)d.Z;
+        const int c = nc % (unsigned)d.C;
+        const int64_t n = nc / (unsigned)d.C;
+        int kz_lo, kz_hi;
+        cover(z, d.Bz, s.Sz, d.Tz, &kz_lo, &kz_hi);
+
+        double acc[4] = {0.0, 0.0, 0.0, 0.0}, wacc[4] = {0.0, 0.0, 0.0, 0.0};
+        // ascending (kz, ky, kx): the order a sequential walk over the reference's tile_coords list adds them
+        for (int kz = kz_lo; kz <= kz_hi; ++kz) {
+            const int iz = z - kz * s.Sz;
+            const double wzv = wz[iz];
+            for (int ky = ky_lo; ky <= ky_hi; ++ky) {
+                const int iy = y - ky * s.Sy;
+                const double wzy = __dmul_rn(wzv, wy[iy]);
+                const float* rowbase = tiles + (((n * d.Tz + kz) * d.Ty + ky) * d.Tx) * tile_stride +
+                                       (((int64_t)c * d.Bz + iz) * d.By + iy) * d.Bx;
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                if (j < cnt) {
-                    for (int kx = kx_lo[j]; kx <= kx_hi[j]; ++kx) {
-                        const int ix = x0 + j - kx * s.Sx;
-                        const float w = (float)__dmul_rn(wzy, wx[ix]);
-                        const float p = __ldg(tiles + (trow + kx) * d.C * tvol + in_tile + ix);
-                        acc[j] = __dadd_rn(acc[j], (double)__fmul_rn(p, w));
-                        wacc[j] = __dadd_rn(wacc[j], (double)w);
+                for (int j = 0; j < 4; ++j) {
+                    if (j < cnt) {
+                        for (int kx = kx_lo[j]; kx <= kx_hi[j]; ++kx) {
+                            const int ix = x0 + j - kx * s.Sx;
+                            const float w = (float)__dmul_rn(wzy, wx[ix]);
+                            const float p = __ldg(rowbase + kx * tile_stride + ix);
+                            acc[j] = __dadd_rn(acc[j], (double)__fmul_rn(p, w));
+                            wacc[j] = __dadd_rn(wacc[j], (double)w);
+                        }
                     }
                 }
             }
         }
-    }
-    float v[4];
+        float v[4];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-        float t = (float)__ddiv_rn(acc[j], wacc[j]);
-        if (epilogue == BE_EPI_SIGMOID) t = be_sigmoid_f32(t);
-        v[j] = t;
+        for (int j = 0; j < 4; ++j) v[j] = be_div_to_f32(acc[j], wacc[j], be_fast_rcp(wacc[j]));
+        finish4(out, mask, ((int64_t)plane * d.Y + y) * d.X + x0, cnt, v, e, (d.X & 3) == 0);
     }
-    store4(out, mask, row * d.X + x0, cnt, v, thr, (d.X & 3) == 0);
+}
+
+// Host side of the band test: sigmoid'(x) = s(1-s) >= 0.0099 for thr in [0.01, 0.99], so 1e-4 away from logit(thr) the
+// true sigmoid is >= 9.9e-7 away from thr, while the fp32 evaluation is good to a few ulp (<= 2.4e-7 near 1).
+Epilogue make_epilogue(int mode, float thr, bool mask_only) {
+    Epilogue e{mode, 0, thr, 0.f, 0.f};
+    if (mode == BE_EPI_SIGMOID && mask_only && thr >= 0.01f && thr <= 0.99f) {
+        const double L = log((double)thr / (1.0 - (double)thr));
+        e.fast = 1;
+        e.lo = (float)(L - 1e-4);
+        e.hi = (float)(L + 1e-4);
+    }
+    return e;
 }
 
 int check_dims(const char* who, int64_t N, int64_t C, int64_t Z, int64_t Y, int64_t X, int Tz, int Ty, int Tx, int Bz,
@@ -247,7 +297,13 @@ int check_dims(const char* who, int64_t N, int64_t C, int64_t Z, int64_t Y, int6
     return BE_OK;
 }
 
-inline unsigned grid_for(int64_t n_units) { return (unsigned)((n_units + kThreads - 1) / kThreads); }
+int stitch_grid(const char* who, const Dims& d, int upr, dim3* grid) {
+    BE_REQUIRE(d.Y <= 65535, BE_ERR_TOO_LARGE, "%s: Y %lld > 65535", who, (long long)d.Y);
+    const int64_t planes = d.N * d.C * d.Z;
+    BE_REQUIRE(planes < ((int64_t)1 << 31), BE_ERR_TOO_LARGE, "%s: too many planes", who);
+    *grid = dim3((unsigned)((upr + kThreads - 1) / kThreads), (unsigned)d.Y, (unsigned)(planes > 65535 ? 65535 : planes));
+    return BE_OK;
+}
 
 }  // namespace
 
@@ -262,16 +318,26 @@ extern "C" int be_tile_gather_f32(const float* img, float* tiles, int64_t N, int
     BE_REQUIRE(norm_mode == 0 || norm, BE_ERR_INVALID_ARG, "be_tile_gather_f32: norm_mode %d needs norm", norm_mode);
     const Dims d{N, C, Z, Y, X, Tz, Ty, Tx, Bz, By, Bx};
     const int upr = (Bx + 3) / 4;
-    const int64_t rows = N * Tz * Ty * Tx * C * Bz * By;
-    const int64_t n_units = rows * upr;
-    BE_REQUIRE(n_units / kThreads < ((int64_t)1 << 31) - 1, BE_ERR_TOO_LARGE, "be_tile_gather_f32: too many tiles");
+    const int64_t n_tiles = N * Tz * Ty * Tx;
+    BE_REQUIRE(n_tiles < ((int64_t)1 << 31) - 1, BE_ERR_TOO_LARGE, "be_tile_gather_f32: too many tiles");
+    BE_REQUIRE(C * Bz <= 65535, BE_ERR_TOO_LARGE, "be_tile_gather_f32: C*Bz %lld > 65535", (long long)(C * Bz));
+    // bands of tile rows: enough blocks for ~8 CTAs per SM, at least 4 sweeps of work per thread where possible
+    const int r_step = kThreads / (upr < kThreads ? upr : kThreads);
+    const int64_t planes = n_tiles * C * Bz;
+    int bands = (int)((int64_t)BE_SM_COUNT * 8 / (planes < 1 ? 1 : planes)) + 1;
+    const int max_bands = (By + 4 * r_step - 1) / (4 * r_step);
+    if (bands > max_bands) bands = max_bands;
+    if (bands < 1) bands = 1;
+    const int rows_per_band = (By + bands - 1) / bands;
+    bands = (By + rows_per_band - 1) / rows_per_band;
+    const dim3 grid((unsigned)n_tiles, (unsigned)(C * Bz), (unsigned)bands);
     cudaStream_t s = (cudaStream_t)stream;
     if (norm_mode)
-        tile_gather_kernel<true><<<grid_for(n_units), kThreads, 0, s>>>(img, tiles, d, zsrc, ysrc, xsrc, norm, norm_mode,
-                                                                        clip, clip_lo, clip_hi, upr, n_units);
+        tile_gather_kernel<true><<<grid, kThreads, 0, s>>>(img, tiles, d, zsrc, ysrc, xsrc, norm, norm_mode, clip, clip_lo,
+                                                           clip_hi, upr, rows_per_band);
     else
-        tile_gather_kernel<false><<<grid_for(n_units), kThreads, 0, s>>>(img, tiles, d, zsrc, ysrc, xsrc, norm, 0, 0, 0.f,
-                                                                         0.f, upr, n_units);
+        tile_gather_kernel<false><<<grid, kThreads, 0, s>>>(img, tiles, d, zsrc, ysrc, xsrc, norm, 0, 0, 0.f, 0.f, upr,
+                                                            rows_per_band);
     BE_LAUNCH_CHECK();
     return BE_OK;
 }
@@ -287,10 +353,12 @@ extern "C" int be_stitch_crop_f32(const float* tiles, float* out, uint8_t* mask,
                "be_stitch_crop_f32: epilogue %d", epilogue);
     const Dims d{N, C, Z, Y, X, Tz, Ty, Tx, Bz, By, Bx};
     const int upr = (int)((X + 3) / 4);
-    const int64_t n_units = N * C * Z * Y * upr;
-    BE_REQUIRE(n_units / kThreads < ((int64_t)1 << 31) - 1, BE_ERR_TOO_LARGE, "be_stitch_crop_f32: output too large");
-    stitch_crop_kernel<<<grid_for(n_units), kThreads, 0, (cudaStream_t)stream>>>(tiles, out, mask, d, zsel, ysel, xsel,
-                                                                                 epilogue, thr, upr, n_units);
+    dim3 grid;
+    rc = stitch_grid("be_stitch_crop_f32", d, upr, &grid);
+    if (rc) return rc;
+    stitch_crop_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(tiles, out, mask, d, zsel, ysel, xsel,
+                                                                    make_epilogue(epilogue, thr, out == nullptr), upr,
+                                                                    (unsigned)(N * C * Z));
     BE_LAUNCH_CHECK();
     return BE_OK;
 }
@@ -312,10 +380,12 @@ extern "C" int be_stitch_blend_f32(const float* tiles, float* out, uint8_t* mask
     const Dims d{N, C, Z, Y, X, Tz, Ty, Tx, Bz, By, Bx};
     const Strides st{Sz, Sy, Sx};
     const int upr = (int)((X + 3) / 4);
-    const int64_t n_units = N * C * Z * Y * upr;
-    BE_REQUIRE(n_units / kThreads < ((int64_t)1 << 31) - 1, BE_ERR_TOO_LARGE, "be_stitch_blend_f32: output too large");
-    stitch_blend_kernel<<<grid_for(n_units), kThreads, 0, (cudaStream_t)stream>>>(tiles, out, mask, d, st, wz, wy, wx,
-                                                                                  epilogue, thr, upr, n_units);
+    dim3 grid;
+    rc = stitch_grid("be_stitch_blend_f32", d, upr, &grid);
+    if (rc) return rc;
+    stitch_blend_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(tiles, out, mask, d, st, wz, wy, wx,
+                                                                     make_epilogue(epilogue, thr, out == nullptr), upr,
+                                                                     (unsigned)(N * C * Z));
     BE_LAUNCH_CHECK();
     return BE_OK;
 }

@@ -34,7 +34,8 @@ class _UNet(nn.Module):
         self.head = conv(feats[0], out_channels, 1)
         self.final_sigmoid = final_sigmoid
 
-    def forward(self, x: torch.Tensor) -> torch.Tensor:
+    def features(self, x: torch.Tensor) -> torch.Tensor:
+        """Everything up to (not including) the 1x1 head."""
         pool = F.max_pool2d if self.nd == 2 else F.max_pool3d
         mode = "bilinear" if self.nd == 2 else "trilinear"
         skips = []
@@ -46,7 +47,10 @@ class _UNet(nn.Module):
         for red, dec in zip(self.reducers, self.decoders):
             x = red(F.interpolate(x, scale_factor=2, mode=mode, align_corners=False))
             x = dec(torch.cat([skips.pop(), x], dim=1))
-        x = self.head(x)
+        return x
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        x = self.head(self.features(x))
         return torch.sigmoid(x) if self.final_sigmoid else x
 
 
@@ -59,6 +63,22 @@ class UNet3d(_UNet):
 
 
 ARCHITECTURES = {"UNet2d": UNet2d, "UNet3d": UNet3d}
+
+
+def calibrate_head(model: nn.Module, probe: torch.Tensor) -> nn.Module:
+    """Re-centre and re-scale the 1x1 head so the logits of `probe` have median 0 and unit spread.
+
+    A random-init UNet's output is its head bias plus a few hundredths of variation, so every pixel lands on the same
+    side of the threshold and the mask is all-0 or all-1 — the stitch/label stages would have nothing to do.  This keeps
+    the random weights and only applies an affine map to the output channel(s).
+    """
+    with torch.no_grad():
+        y = model(probe.to(next(model.parameters()).device))
+        med = y.median()
+        spread = (y - med).abs().mean().clamp_min(1e-12)
+        model.head.weight.div_(spread)
+        model.head.bias.sub_(med).div_(spread)
+    return model
 
 
 def build_model(name: str, seed: int = 0, **kwargs) -> nn.Module:

@@ -415,14 +415,18 @@ def gaussian_blobs(shape: Sequence[int], n: int, sigma=(4.0, 10.0), seed: int = 
     return out
 
 
-def synthetic_image(shape: Sequence[int], n_blobs: int, seed: int, microscope: bool = True) -> np.ndarray:
-    """C2-style frame: blobs*1000 + 100 + shot-like noise + 0.1 % hot pixels at 65535 (exercises the percentiles)."""
+def synthetic_image(shape: Sequence[int], n_blobs: int, seed: int, microscope: bool = True,
+                    with_truth: bool = False):
+    """C2-style frame: blobs*1000 + 100 + shot-like noise + 0.1 % hot pixels at 65535 (exercises the percentiles).
+    with_truth=True also returns the noise-free blob field (ground truth for fitting a read-out / making GT labels)."""
     rng = np.random.default_rng(seed + 7919)
-    img = gaussian_blobs(shape, n_blobs, seed=seed)
+    clean = gaussian_blobs(shape, n_blobs, seed=seed)
     if not microscope:
-        return (img + 0.1 * rng.standard_normal(img.shape).astype(np.float32)).astype(np.float32)
-    img = img * 1000.0 + 100.0
-    img = img + np.sqrt(img) * rng.standard_normal(img.shape).astype(np.float32)
-    hot = rng.random(img.shape) < 0.001
-    img[hot] = 65535.0
-    return img.astype(np.float32)
+        img = (clean + 0.1 * rng.standard_normal(clean.shape).astype(np.float32)).astype(np.float32)
+    else:
+        img = clean * 1000.0 + 100.0
+        img = img + np.sqrt(img) * rng.standard_normal(img.shape).astype(np.float32)
+        hot = rng.random(img.shape) < 0.001
+        img[hot] = 65535.0
+        img = img.astype(np.float32)
+    return (img, clean) if with_truth else img

@@ -28,6 +28,9 @@ def test_c2_shape_path_fibsem_blend(dev):
     x = torch.from_numpy(img).to(dev)
     tiles = pipe.preprocess_and_tile(x)
     assert np.array_equal(tiles.cpu().numpy(), P.c2_pre(img, B, ov))
+    from bioengine_worker_b200 import models
+
+    models.calibrate_head(model, tiles[::3].contiguous())
     logits = pipe.forward(model, tiles)
     res = pipe.stitch_and_label(logits)
     prob, mask, labels = P.c2_post(logits.cpu().numpy(), (H, W), B, ov, 2)
@@ -48,8 +51,12 @@ def test_bioimageio_crop_path_batch(dev):
     x = torch.from_numpy(img).to(dev)
     tiles = pipe.preprocess_and_tile(x)
     assert np.array_equal(tiles.cpu().numpy(), P.crop_pre(img, (B, B), (halo, halo)))
+    from bioengine_worker_b200 import models
+
+    models.calibrate_head(model, tiles[::5].contiguous())
     logits = pipe.forward(model, tiles)
     res = pipe.stitch_and_label(logits)
+    assert res["n_labels"].min().item() > 0
     prob, mask, labels = P.crop_post(logits.cpu().numpy(), shape, (B, B), (halo, halo))
     assert np.array_equal(res["prob"].cpu().numpy(), prob)
     assert np.array_equal(res["mask"].cpu().numpy(), mask)
@@ -84,8 +91,12 @@ def test_c3_shape_path_3d(dev):
     tiles = pipe.preprocess_and_tile(x)
     want_tiles = O.fibsem_tiles(O.fibsem_normalize(vol[0, 0]), B, ov)
     assert np.array_equal(tiles.cpu().numpy()[:, 0], want_tiles)
+    from bioengine_worker_b200 import models
+
+    models.calibrate_head(model, tiles[::7].contiguous())
     logits = pipe.forward(model, tiles)
     res = pipe.stitch_and_label(logits)
+    assert res["n_labels"].item() > 0
     prob, mask, labels = P.c2_post(logits.cpu().numpy(), D, B, ov, 3)
     assert np.array_equal(res["mask"].cpu().numpy()[0, 0], mask)
     assert np.array_equal(res["labels"].cpu().numpy()[0, 0], labels)
