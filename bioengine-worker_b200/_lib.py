@@ -33,6 +33,7 @@ SIGNATURES = {
     "be_meanvar_f32": (_i32, [_ptr, _i64, _i64, _f64, _ptr, _ptr, _ptr, _ptr]),
     "be_quantile_workspace_bytes": (_sz, [_i64, _i64]),
     "be_quantile_f32": (_i32, [_ptr, _i64, _i64, _ptr, _i32, _f64, _ptr, _ptr, _ptr, _ptr]),
+    "be_quantile_f32_noalloc": (_i32, [_ptr, _i64, _i64, _ptr, _i32, _f64, _ptr, _ptr, _ptr]),
     "be_normalize_f32": (_i32, [_ptr, _ptr, _i64, _i64, _ptr, _i32, _f32, _f32, _ptr]),
     "be_elementwise_f32": (_i32, [_ptr, _ptr, _i64, _i32, _f32, _f32, _ptr]),
     "be_binarize_f32_u8": (_i32, [_ptr, _ptr, _i64, _f32, _ptr]),

@@ -608,6 +608,49 @@ extern "C" int be_quantile_f32(const float* x, int64_t n_seg, int64_t seg_len, c
     return BE_OK;
 }
 
+// ---- quantiles for callers that must not allocate -------------------------------------------------------------------
+//
+// Some hosts of this library cannot give it a workspace: a microscope acquisition loop that is not allowed to touch
+// the CUDA allocator between frames (cudaMalloc / cudaFree serialise the whole device and can stall a live stream), or
+// an embedding runtime that has handed every byte of device memory to its own pool and passes plugins nothing but the
+// input and output pointers.  For them the scratch of the quantile kernels lives in the library image itself: one
+// fixed array per GPU, present from the moment the library is loaded on that GPU until the process exits.
+//
+// `g_quantile_scratch` below is that array.  On the host the name is only a handle for the symbol — it is not a
+// device address and must never be handed to a kernel; the address is looked up once per device with
+// cudaGetSymbolAddress while that device is current, and cached.
+constexpr int kNoAllocMaxSegments = 8;
+constexpr size_t kNoAllocScratchBytes = 344064;  // >= carve_quantile_ws(., 8).total_bytes (checked at run time)
+static __device__ __align__(256) unsigned char g_quantile_scratch[kNoAllocScratchBytes];
+
+constexpr int kMaxDevices = 64;
+static void* g_quantile_scratch_addr[kMaxDevices];  // per-device address of g_quantile_scratch, filled on first use
+
+extern "C" int be_quantile_f32_noalloc(const float* x, int64_t n_seg, int64_t seg_len, const double* q, int n_q,
+                                       double eps, double* quant, double* norm, be_stream_t stream) {
+    BE_REQUIRE(n_seg >= 1 && n_seg <= kNoAllocMaxSegments, BE_ERR_TOO_LARGE,
+               "be_quantile_f32_noalloc: n_seg %lld outside 1..%d (the built-in scratch is sized for %d segments; use "
+               "be_quantile_f32 with a caller workspace for more)",
+               (long long)n_seg, kNoAllocMaxSegments, kNoAllocMaxSegments);
+    BE_REQUIRE(carve_quantile_ws(nullptr, n_seg).total_bytes <= kNoAllocScratchBytes, BE_ERR_TOO_LARGE,
+               "be_quantile_f32_noalloc: built-in scratch too small (library bug)");
+    int dev = -1;
+    BE_CUDA(cudaGetDevice(&dev));
+    BE_REQUIRE(dev >= 0 && dev < kMaxDevices, BE_ERR_TOO_LARGE, "be_quantile_f32_noalloc: device ordinal %d >= %d", dev,
+               kMaxDevices);
+    void* scratch = g_quantile_scratch_addr[dev];
+    if (!scratch) {
+        // first call on this device: resolve the symbol's device address (no allocation; the array is part of the
+        // loaded module).  Two threads racing here both store the same value.
+        BE_CUDA(cudaGetSymbolAddress(&scratch, g_quantile_scratch));
+        BE_REQUIRE(scratch != nullptr, BE_ERR_CUDA, "be_quantile_f32_noalloc: cudaGetSymbolAddress returned null");
+        g_quantile_scratch_addr[dev] = scratch;
+    }
+    // be_quantile_f32 zeroes the counters and histograms it needs at the start of every call, so whatever the previous
+    // call left in the shared array is harmless.
+    return be_quantile_f32(x, n_seg, seg_len, q, n_q, eps, quant, norm, scratch, stream);
+}
+
 extern "C" int be_normalize_f32(const float* x, float* y, int64_t n_seg, int64_t seg_len, const double* norm, int clip,
                                 float clip_lo, float clip_hi, be_stream_t stream) {
     BE_REQUIRE(x && y && norm, BE_ERR_INVALID_ARG, "be_normalize_f32: null pointer");

@@ -64,6 +64,21 @@ size_t be_quantile_workspace_bytes(int64_t n_seg, int64_t seg_len);
 int be_quantile_f32(const float* x, int64_t n_seg, int64_t seg_len, const double* q, int n_q, double eps,
                     double* quant, double* norm, void* ws, be_stream_t stream);
 
+/* be_quantile_f32 for callers that cannot provide a workspace because they cannot allocate device memory at all:
+ * e.g. a live acquisition loop that must keep clear of cudaMalloc/cudaFree (both stall every stream on the device),
+ * or a host runtime that owns all device memory through its own pool and gives a plugin only the input and output
+ * pointers.  Same arguments and results as be_quantile_f32 minus `ws`: the scratch is a fixed 336 KiB array inside
+ * the library, one copy per GPU for as long as the library stays loaded there.  No counterpart in the reference
+ * (it never manages device memory itself); this entry point exists only for such embedders.
+ *   - at most 8 segments per call (n_seg > 8 → BE_ERR_TOO_LARGE); seg_len as for be_quantile_f32;
+ *   - never calls cudaMalloc, cudaFree or any allocating routine;
+ *   - the first call on each device looks up the array's device address (cudaGetSymbolAddress): make that first
+ *     call with the device current and before starting any stream capture on it;
+ *   - all calls on one GPU share the array: calls whose GPU work can overlap (different streams, different host
+ *     threads) race on it — issue them on one stream or order them with events. */
+int be_quantile_f32_noalloc(const float* x, int64_t n_seg, int64_t seg_len, const double* q, int n_q, double eps,
+                            double* quant, double* norm, be_stream_t stream);
+
 /* ---- elementwise -------------------------------------------------------------------------------- */
 
 /* y = (float)(((double)x - norm[2s]) / norm[2s+1]), optionally clipped to [clip_lo, clip_hi].
