@@ -1,0 +1,273 @@
+"""`RuntimeDeployment` — B200 replacement for ref: apps/model-runner/runtime_deployment.py.
+
+Same class name, same `predict(...)` / `test(...)` signatures, same `{output_id: ndarray}` result, same error
+conventions (FileNotFoundError for a missing RDF, ValueError for bad inputs, CUDA OOM re-raised as a plain RuntimeError
+after `torch.cuda.empty_cache()`, ref: runtime_deployment.py:253-254,296-310).  What changed is underneath: instead of
+bioimageio.core running numpy pre-/post-processing on the CPU and shipping every block to the GPU and back, the sample
+is uploaded once and `TiledPipeline` runs statistics, normalise + halo-block gather, the torch forward, inner-region
+stitching and post-processing on the device.
+
+`ray` is optional: with Ray Serve installed the class is a deployment with the reference's options; without it the
+decorators are no-ops and `RuntimeDeployment.func_or_class()` still constructs the plain object (the reference's own
+local-dev pattern, ref: runtime_deployment.py:328).
+"""
+from __future__ import annotations
+
+import hashlib
+import json
+import logging
+import os
+from collections import OrderedDict
+from pathlib import Path
+from typing import Dict, List, Literal, Optional, Union
+
+import numpy as np
+import torch
+
+from . import _lib, kernels as K, models
+from .pipeline import PipelineSpec, TiledPipeline
+from .rdf import ModelSpec, Op, load_model_spec
+
+logger = logging.getLogger("ray.serve")
+
+try:  # pragma: no cover - ray is not installed in the build image
+    from ray import serve
+
+    _deployment = serve.deployment(
+        ray_actor_options={"num_cpus": 1, "num_gpus": 1, "memory": 12 * 1024 * 1024 * 1024},
+        max_ongoing_requests=1,
+        autoscaling_config={"min_replicas": 1, "initial_replicas": 1, "max_replicas": 2,
+                            "target_num_ongoing_requests_per_replica": 0.8, "metrics_interval_s": 2.0,
+                            "look_back_period_s": 10.0, "downscale_delay_s": 300, "upscale_delay_s": 0.0},
+        health_check_period_s=30.0, health_check_timeout_s=30.0, graceful_shutdown_timeout_s=120.0,
+        graceful_shutdown_wait_loop_s=2.0,
+    )
+except Exception:  # ray absent: plain class
+    def _deployment(cls):
+        cls.func_or_class = cls
+        return cls
+
+
+_NORMALISERS = ("scale_range", "zero_mean_unit_variance", "fixed_zero_mean_unit_variance")
+
+
+class _LoadedModel:
+    """A model description with its weights on the device (what bioimageio calls a loaded prediction pipeline)."""
+
+    def __init__(self, spec: ModelSpec, device: torch.device, blocksize_parameter: Optional[int]):
+        self.spec, self.device, self.n = spec, device, blocksize_parameter
+        self.net = models.build_model(spec.architecture, seed=spec.seed, **spec.arch_kwargs)
+        if spec.weights_source:
+            src = spec.root / spec.weights_source
+            if not src.exists():
+                raise FileNotFoundError(f"weights not found: {src}")
+            self.net.load_state_dict(torch.load(src, map_location="cpu"))
+        self.net = self.net.to(device).eval()
+        self.pipelines: Dict[tuple, TiledPipeline] = {}
+
+
+@_deployment
+class RuntimeDeployment:
+    """Internal deployment for running model inference on the B200 tiled path."""
+
+    def __init__(self):
+        self._kwargs_cache = {}
+        self._pipelines: "OrderedDict[str, _LoadedModel]" = OrderedDict()
+        self._cache_size = int(os.environ.get("PIPELINE_CACHE_SIZE", 10))
+        models.strict_fp32()
+
+    # === model test ===
+
+    async def test(self, rdf_path: str, additional_requirements: Optional[List[str]] = None) -> dict:
+        """Load the model and run it once on a zero sample of its minimum shape (the zoo's test tensors are not
+        available offline, ref: runtime_deployment.py:86-99)."""
+        spec = load_model_spec(rdf_path)
+        inp = spec.inputs[0]
+        spatial = [max(inp.size_min.get(a, 64), 16) for a in inp.axes if a in "zyx"]
+        x = np.zeros([1, spec.arch_kwargs.get("in_channels", 1)] + spatial, np.float32)
+        out = await self.predict(rdf_path, x)
+        return {"status": "passed", "name": spec.name,
+                "details": [{"name": k, "shape": list(v.shape), "dtype": str(v.dtype)} for k, v in out.items()]}
+
+    # === prediction ===
+
+    def _set_prediction_kwargs(self, rdf_path, weights_format, device, default_blocksize_parameter,
+                               latest_remote_modified=None) -> str:
+        """Cache key of a loaded pipeline — same recipe as ref: runtime_deployment.py:160-185."""
+        pipeline_kwargs = {
+            "rdf_path": rdf_path,
+            "latest_remote_modified": latest_remote_modified,
+            "create_kwargs": {"weights_format": weights_format, "device": device,
+                              "default_blocksize_parameter": default_blocksize_parameter},
+        }
+        cache_key = hashlib.md5(json.dumps(pipeline_kwargs, sort_keys=True).encode()).hexdigest()
+        self._kwargs_cache[cache_key] = pipeline_kwargs
+        return cache_key
+
+    async def _create_prediction_pipeline(self, cache_key: str) -> _LoadedModel:
+        if cache_key in self._pipelines:
+            self._pipelines.move_to_end(cache_key)
+            self._kwargs_cache.pop(cache_key, None)
+            return self._pipelines[cache_key]
+        pipeline_kwargs = self._kwargs_cache.get(cache_key)
+        if not pipeline_kwargs:
+            raise ValueError(f"No pipeline kwargs found for cache key: {cache_key}")
+        try:
+            ck = pipeline_kwargs["create_kwargs"]
+            if ck["weights_format"] not in (None, "pytorch_state_dict"):
+                raise ValueError(f"weights_format {ck['weights_format']!r} is not supported (pytorch_state_dict only)")
+            if ck["device"] == "cpu":
+                raise ValueError("device='cpu' is not available in the B200 runtime (no CPU fallback)")
+            spec = load_model_spec(pipeline_kwargs["rdf_path"])
+            loaded = _LoadedModel(spec, torch.device("cuda", torch.cuda.current_device()),
+                                  ck["default_blocksize_parameter"])
+            self._pipelines[cache_key] = loaded
+            while len(self._pipelines) > self._cache_size:  # LRU like serve.multiplexed
+                self._pipelines.popitem(last=False)
+            return loaded
+        finally:
+            self._kwargs_cache.pop(cache_key, None)
+
+    @staticmethod
+    def _to_ncsp(x: np.ndarray, axes: str) -> np.ndarray:
+        """Bring an input array to (N, C, *spatial), guessing the axes the way `create_sample_for_model` does when the
+        array has fewer dimensions than the model declares (missing leading batch / channel axes are added)."""
+        want = len(axes)
+        if x.ndim > want:
+            raise ValueError(f"input has {x.ndim} dimensions, model expects at most {want} ({axes})")
+        while x.ndim < want:
+            x = x[None]
+        order = [axes.index(a) for a in "bc" if a in axes] + [axes.index(a) for a in "zyx" if a in axes]
+        return np.ascontiguousarray(np.transpose(x, order), dtype=np.float32)
+
+    def _run_ops_unfused(self, x: torch.Tensor, ops: List[Op], n: int, c: int) -> torch.Tensor:
+        for op in ops:
+            k = op.kwargs
+            if op.name == "ensure_dtype":
+                continue
+            if op.name in _NORMALISERS:
+                x = K.normalize(x, self._norm_params(x, op, n, c)[0], out=x)
+            elif op.name == "clip":
+                x = K.clip(x, float(k["min"]), float(k["max"]), out=x)
+            elif op.name == "scale_linear":
+                x = K.scale_linear(x, float(k.get("gain", 1.0)), float(k.get("offset", 0.0)), out=x)
+            elif op.name == "sigmoid":
+                x = K.sigmoid(x, out=x)
+            elif op.name == "binarize":
+                x = K.binarize(x, float(k["threshold"])).to(torch.float32)
+            else:
+                raise ValueError(f"unsupported processing op {op.name!r}")
+        return x
+
+    @staticmethod
+    def _norm_params(x: torch.Tensor, op: Op, n: int, c: int):
+        """→ (norm [n_seg, 2] fp64 on device, norm_mode for the gather).  `axes` lists the REDUCED axes (Appendix A.2)."""
+        k = op.kwargs
+        axes = k.get("axes")
+        joint_c = axes is None or any(a in ("c", "channel") for a in axes)
+        if axes is not None and any(a in ("b", "batch") for a in axes):
+            raise ValueError("statistics over the batch axis are not supported")
+        n_seg, mode = (n, 2) if joint_c else (n * c, 1)
+        eps = float(k.get("eps", 1e-6))
+        if op.name == "scale_range":
+            q = torch.tensor([float(k.get("min_percentile", 0.0)) / 100.0, float(k.get("max_percentile", 100.0)) / 100.0],
+                             dtype=torch.float64, device=x.device)
+            return K.quantile(x, n_seg, q, eps)[1], mode
+        if op.name == "zero_mean_unit_variance":
+            return K.meanvar(x, n_seg, eps)[1], mode
+        mean, std = k["mean"], k["std"]
+        if isinstance(mean, (list, tuple)):
+            vals = [[float(m), float(s) + eps] for m, s in zip(mean, std)] * n
+            return torch.tensor(vals, dtype=torch.float64, device=x.device), 1
+        return torch.tensor([[float(mean), float(std) + eps]] * n, dtype=torch.float64, device=x.device), 2
+
+    def _predict_one(self, loaded: _LoadedModel, x_np: np.ndarray, blocking: bool) -> Dict[str, np.ndarray]:
+        spec = loaded.spec
+        inp, outp = spec.inputs[0], spec.outputs[0]
+        x = torch.from_numpy(self._to_ncsp(x_np, inp.axes)).to(loaded.device, non_blocking=True)
+        N, C = x.shape[:2]
+        spatial = tuple(x.shape[2:])
+        sp_axes = [a for a in inp.axes if a in "zyx"]
+        if blocking:
+            block = tuple(inp.size_min.get(a, s) + loaded.n * inp.size_step.get(a, 0) for a, s in zip(sp_axes, spatial))
+            halo = tuple(outp.halo.get(a, 0) for a in sp_axes)
+            if any(s < b - 2 * h for s, b, h in zip(spatial, block, halo)):
+                raise ValueError(f"sample {spatial} is smaller than the block {block} minus halo")
+        else:
+            block, halo = spatial, (0,) * len(spatial)
+
+        pre = [o for o in inp.ops if o.name != "ensure_dtype"]
+        post = [o for o in outp.ops if o.name != "ensure_dtype"]
+        fused_norm = len(pre) == 1 and pre[0].name in _NORMALISERS
+        key = (tuple(x.shape), block, halo)
+        pipe = loaded.pipelines.get(key)
+        if pipe is None:
+            pipe = TiledPipeline(tuple(x.shape), PipelineSpec(block=block, halo=halo, convention="bioimageio",
+                                                              preprocess="none", label=False), device=loaded.device)
+            loaded.pipelines[key] = pipe
+        # whole-sample pre-processing first (statistics are per sample, never per block), fused into the gather
+        if fused_norm:
+            norm, mode = self._norm_params(x, pre[0], N, C)
+            tiles = K.tile_gather(x, pipe.axes, norm=norm, norm_mode=mode, out=pipe.tiles)
+        else:
+            tiles = K.tile_gather(self._run_ops_unfused(x, pre, N, C), pipe.axes, out=pipe.tiles)
+        logits = pipe.forward(loaded.net, tiles)
+        out_shape = (N, logits.shape[1]) + spatial
+        names = [o.name for o in post]
+        if names in (["sigmoid"], ["binarize"], ["sigmoid", "binarize"], []):
+            epi = _lib.BE_EPI_SIGMOID if "sigmoid" in names else _lib.BE_EPI_NONE
+            if "binarize" in names:
+                thr = float(post[-1].kwargs["threshold"])
+                _, mask = K.stitch_crop(logits, out_shape, pipe.axes, epi, thr, want_out=False, want_mask=True)
+                result = mask
+            else:
+                result, _ = K.stitch_crop(logits, out_shape, pipe.axes, epi)
+        else:
+            stitched, _ = K.stitch_crop(logits, out_shape, pipe.axes)
+            result = self._run_ops_unfused(stitched, post, N, logits.shape[1])
+        out = result.to(getattr(torch, outp.dtype, torch.float32)) if result.dtype != getattr(torch, outp.dtype, None) else result
+        arr = out.cpu().numpy()
+        # back to the model's declared output axis order
+        have = [a for a in "bc" if a in outp.axes] + [a for a in "zyx" if a in outp.axes]
+        if "".join(have) != outp.axes and len(have) == arr.ndim:
+            arr = np.transpose(arr, [have.index(a) for a in outp.axes])
+        return {str(outp.id): arr}
+
+    async def predict(
+        self,
+        rdf_path: str,
+        inputs: Union[np.ndarray, Dict[str, np.ndarray]],
+        weights_format: Optional[str] = None,
+        device: Literal["cuda", "cpu"] = None,
+        default_blocksize_parameter: Optional[int] = None,
+        sample_id: str = "sample",
+        latest_remote_modified: Optional[float] = None,
+    ) -> Dict[str, np.ndarray]:
+        """Run inference on model using the B200 tiled pipeline (signature of ref: runtime_deployment.py:234-243)."""
+        try:
+            if not Path(rdf_path).exists():
+                raise FileNotFoundError(f"RDF not found: {rdf_path}")
+            cache_key = self._set_prediction_kwargs(rdf_path=rdf_path, weights_format=weights_format, device=device,
+                                                    default_blocksize_parameter=default_blocksize_parameter,
+                                                    latest_remote_modified=latest_remote_modified)
+            loaded = await self._create_prediction_pipeline(cache_key)
+            if isinstance(inputs, dict):
+                want = loaded.spec.inputs[0].id
+                if want not in inputs and len(inputs) != 1:
+                    raise ValueError(f"inputs must contain tensor {want!r}")
+                x = inputs[want] if want in inputs else next(iter(inputs.values()))
+            else:
+                x = inputs
+            x = np.asarray(x)
+            if x.size == 0:
+                raise ValueError("empty input")
+            return self._predict_one(loaded, x, blocking=bool(default_blocksize_parameter))
+        except Exception as e:
+            torch.cuda.empty_cache()
+            err_type = type(e).__name__
+            if err_type in ("OutOfMemoryError", "CUDAOutOfMemoryError") or ("out of memory" in str(e).lower()):
+                oom_msg = f"CUDA out of memory during inference: {str(e)}"
+                logger.error(oom_msg)
+                raise RuntimeError(oom_msg) from None
+            logger.error(f"Prediction failed: {str(e)}")
+            raise

@@ -11,7 +11,8 @@ reference test holds a numeric known answer for this path.  Wha
   * the in-tree numpy code of apps/fibsem-mito-analysis/analysis_deployment.py is followed statement by
     statement (citations below) and calls the *same* numpy/scipy routines the reference calls;
   * bioimageio.core / cellpose semantics are restated from their published behaviour (SURVEY.md App. A/B);
-  * hand-checkable micro cases live in tests/golden/ (6x6 masks, IoU = 0.5 ties, reflect-pad tables).
+  * hand-derived known answers in tests/test_oracle_golden.py (6x6 masks, quantile lerp, shifted last block, reflect
+    padding, IoU = 0.5 ties, rectangle moments) and seeded vectors in tests/golden/ (made by make_golden.py).
 
 Paths cited as `ref:` are relative to the reference tree root.
 """

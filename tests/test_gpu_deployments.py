@@ -1,0 +1,138 @@
+"""The reference-facing classes: RuntimeDeployment.predict (RDF-driven) and MitoAnalysisDeployment.analyze, driven the
+way the reference's own local-dev mains drive them (`RuntimeDeployment.func_or_class()`, asyncio.run), against the
+whole-path oracle on identical logits."""
+import asyncio
+
+import numpy as np
+import pytest
+import torch
+import yaml
+
+from oracle import oracle as O
+from oracle import paths as P
+
+pytestmark = pytest.mark.gpu
+
+
+def write_model(tmp_path, pre, post, halo=16, out_dtype="float32", seed=3, arch="UNet2d", arch_kwargs=None, calibrate_on=None):
+    from bioengine_worker_b200 import models
+
+    arch_kwargs = arch_kwargs or {"depth": 2, "initial_features": 8}
+    net = models.build_model(arch, seed=seed, **arch_kwargs)
+    if calibrate_on is not None:
+        models.calibrate_head(net, torch.from_numpy(calibrate_on))
+    torch.save(net.state_dict(), tmp_path / "weights.pt")
+    rdf = {
+        "format_version": "0.5.3", "type": "model", "name": "test-unet",
+        "inputs": [{"id": "raw", "axes": [{"type": "batch"}, {"type": "channel", "channel_names": ["c0"]},
+                                           {"type": "space", "id": "y", "size": {"min": 64, "step": 32}},
+                                           {"type": "space", "id": "x", "size": {"min": 64, "step": 32}}],
+                    "preprocessing": pre}],
+        "outputs": [{"id": "mask", "data": {"type": out_dtype},
+                     "axes": [{"type": "batch"}, {"type": "channel", "channel_names": ["p"]},
+                              {"type": "space", "id": "y", "halo": halo}, {"type": "space", "id": "x", "halo": halo}],
+                     "postprocessing": post}],
+        "weights": {"pytorch_state_dict": {"source": "weights.pt",
+                                           "architecture": {"callable": arch, "kwargs": arch_kwargs}}},
+    }
+    (tmp_path / "rdf.yaml").write_text(yaml.safe_dump(rdf))
+    return str(tmp_path / "rdf.yaml"), net
+
+
+def test_predict_with_blocking_scale_range_sigmoid_binarize(tmp_path, dev):
+    from bioengine_worker_b200.runtime_deployment import RuntimeDeployment
+
+    img = O.synthetic_image((300, 420), 60, seed=9)
+    norm = O.scale_range(img[None, None], 1.0, 99.8, axes=(1, 2, 3))
+    pre = [{"id": "ensure_dtype", "kwargs": {"dtype": "float32"}},
+           {"id": "scale_range", "kwargs": {"min_percentile": 1.0, "max_percentile": 99.8, "axes": ["y", "x"]}}]
+    post = [{"id": "sigmoid"}, {"id": "binarize", "kwargs": {"threshold": 0.5}}]
+    rdf_path, net = write_model(tmp_path, pre, post, halo=16, out_dtype="uint8", calibrate_on=norm[:, :, :128, :128])
+    rt = RuntimeDeployment.func_or_class()
+    # default_blocksize_parameter n=2 → block = 64 + 2*32 = 128 (halo 16 inside)
+    out = asyncio.run(rt.predict(rdf_path, img, default_blocksize_parameter=2))
+    assert list(out) == ["mask"] and out["mask"].shape == (1, 1, 300, 420) and out["mask"].dtype == np.uint8
+    tiles = P.crop_pre(img[None, None], (128, 128), (16, 16))
+    with torch.no_grad():
+        logits = net.to(dev)(torch.from_numpy(tiles).to(dev)).cpu().numpy()
+    _, mask, _ = P.crop_post(logits, (1, 1, 300, 420), (128, 128), (16, 16))
+    assert 0.02 < mask.mean() < 0.98
+    assert np.array_equal(out["mask"], mask)
+    # second call hits the pipeline cache and agrees
+    assert np.array_equal(asyncio.run(rt.predict(rdf_path, {"raw": img[None, None]}, default_blocksize_parameter=2))["mask"], mask)
+
+
+def test_predict_without_blocking_zmuv_float_output(tmp_path, dev):
+    from bioengine_worker_b200.runtime_deployment import RuntimeDeployment
+
+    img = O.synthetic_image((128, 160), 12, seed=4, microscope=False)
+    pre = [{"id": "zero_mean_unit_variance", "kwargs": {"axes": ["y", "x"]}}]
+    post = [{"id": "sigmoid"}]
+    rdf_path, net = write_model(tmp_path, pre, post)
+    rt = RuntimeDeployment.func_or_class()
+    out = asyncio.run(rt.predict(rdf_path, img))
+    xn = O.zero_mean_unit_variance(img[None, None], axes=(1, 2, 3))
+    with torch.no_grad():
+        want = O.sigmoid(net.to(dev)(torch.from_numpy(xn).to(dev)).cpu().numpy())
+    assert out["mask"].dtype == np.float32 and out["mask"].shape == want.shape
+    np.testing.assert_allclose(out["mask"], want, rtol=1e-4, atol=1e-6)  # forward sees inputs that differ by <= 1e-5 rel
+
+
+def test_predict_errors_follow_the_reference(tmp_path):
+    from bioengine_worker_b200.runtime_deployment import RuntimeDeployment
+
+    rt = RuntimeDeployment.func_or_class()
+    with pytest.raises(FileNotFoundError):
+        asyncio.run(rt.predict(str(tmp_path / "missing.yaml"), np.zeros((64, 64), np.float32)))
+    rdf_path, _ = write_model(tmp_path, [], [])
+    with pytest.raises(ValueError):
+        asyncio.run(rt.predict(rdf_path, np.zeros((64, 64), np.float32), device="cpu"))
+    with pytest.raises(ValueError):
+        asyncio.run(rt.predict(rdf_path, np.zeros((1, 1, 1, 64, 64), np.float32)))
+    report = asyncio.run(rt.test(rdf_path))
+    assert report["status"] == "passed" and report["details"][0]["name"] == "mask"
+
+
+def test_analyze_matches_fibsem_oracle(dev):
+    from bioengine_worker_b200 import models
+    from bioengine_worker_b200.analysis_deployment import MitoAnalysisDeployment
+
+    models.strict_fp32()
+    H, W, tile, ov = 300, 410, 128, 32
+    rng = np.random.default_rng(0)
+    img = (O.gaussian_blobs((H, W), 40, seed=6) * 200 + 20 + 5 * rng.standard_normal((H, W))).clip(0, 255).astype(np.float32)
+    net = models.build_model("UNet2d", seed=2, depth=2, initial_features=8, final_sigmoid=True).to(dev)
+    norm = O.fibsem_normalize(img)
+    tiles = O.fibsem_tiles(norm, tile, ov)[:, None]
+    # centre the pre-sigmoid head output so the probabilities straddle 0.5
+    net.final_sigmoid = False
+    models.calibrate_head(net, torch.from_numpy(tiles[::3]).to(dev))
+    net.final_sigmoid = True
+    dep = MitoAnalysisDeployment(model=net, device=dev)
+    res = asyncio.run(dep.analyze(img.tolist(), pixel_size_nm=5.0, tile_size=tile, overlap=ov))
+    with torch.no_grad():
+        probs = net(torch.from_numpy(tiles).to(dev)).cpu().numpy()[:, 0]
+    prob = O.fibsem_blend(probs, (H, W), tile, ov)
+    labels = O.label(prob > 0.5)
+    assert res["n_mitochondria"] == labels.max() > 0
+    assert np.array_equal(np.asarray(res["labels"], dtype=np.int32), labels)
+    want = O.regionprops_table(labels, 5.0)
+    assert res["properties"]["label"] == want["label"]
+    for k in ("area_um2", "centroid_y", "centroid_x"):
+        np.testing.assert_allclose(res["properties"][k], want[k], rtol=1e-12)
+    # aspect_ratio = major / (minor + 1e-6) is ill-conditioned for one-pixel-thin objects (minor is cancellation noise in
+    # any floating-point evaluation); compare tightly where the minor axis is resolved, loosely elsewhere
+    ar_got, ar_want = np.asarray(res["properties"]["aspect_ratio"]), np.asarray(want["aspect_ratio"])
+    thin = ar_want > 1e3
+    np.testing.assert_allclose(ar_got[~thin], ar_want[~thin], rtol=1e-6)
+    assert (ar_got[thin] > 1e3).all()
+    np.testing.assert_allclose(res["properties"]["eccentricity"], want["eccentricity"], rtol=1e-6, atol=1e-6)
+    assert res["image_shape"] == [H, W] and set(res) >= {"labels", "properties", "n_mitochondria", "pixel_size_nm", "model"}
+    # small image → single untiled call (ref: analysis_deployment.py:247-248)
+    small = img[:100, :120]
+    res2 = asyncio.run(dep.analyze(small.tolist(), tile_size=128, overlap=32, as_numpy=True))
+    with torch.no_grad():
+        p2 = net(torch.from_numpy(O.fibsem_normalize(small)[None, None]).to(dev)).cpu().numpy()[0, 0]
+    assert np.array_equal(res2["labels"], O.label(p2 > 0.5))
+    with pytest.raises(ValueError):
+        asyncio.run(dep.analyze(np.zeros((2, 3, 4)).tolist()))
