@@ -87,66 +87,31 @@ __device__ __forceinline__ LinkMasks link_masks(u64 m, u64 u, bool diag) {
     return k;
 }
 
-// pairwise linking of two rows whose runs already carry labels (lab[] indexed by run id)
-__device__ __forceinline__ void link_rows(unsigned* parent, const unsigned short* lab, u64 m, u64 sm_, u64 u, u64 su,
-                                          unsigned bm, unsigned bu, bool diag, int lane) {
-    if (!u) return;
-    const LinkMasks k = link_masks(m, u, diag);
-    if (!(k.c | k.l | k.r)) return;
-#pragma unroll
-    for (int h = 0; h < 2; ++h) {
-        const int x = lane + 32 * h;
-        const u64 bit = 1ull << x;
-        if ((k.c | k.l | k.r) & bit) {
-            const unsigned a = lab[bm + run_index(sm_, x)];
-            if (k.c & bit) sm_unite(parent, a, lab[bu + run_index(su, x)]);
-            if (k.l & bit) sm_unite(parent, a, lab[bu + run_index(su, x - 1)]);
-            if (k.r & bit) sm_unite(parent, a, lab[bu + run_index(su, x + 1)]);
-        }
-    }
-}
-
-// Two-pass style labelling of one row against the row above it, inside a strip that one warp walks top to bottom.
-// Lanes sitting on a run start first publish the start position under the run's index, then lane k takes run k (a
-// row of 64 pixels has at most 32 runs): it looks at the runs of the previous row that touch its run; the first one
-// hands down its label (no union-find traffic at all — the common case), further ones are bridged with unions.
-__device__ __forceinline__ void label_row(unsigned* parent, unsigned short* lab, unsigned char* xstart, u64 m, u64 s,
-                                          u64 u, u64 su, unsigned bm, unsigned bu, bool diag, int lane, u64 le0, u64 le1) {
-    if ((s >> lane) & 1ull) xstart[bm + __popcll(s & le0) - 1] = (unsigned char)lane;
-    if ((s >> (lane + 32)) & 1ull) xstart[bm + __popcll(s & le1) - 1] = (unsigned char)(lane + 32);
-    __syncwarp();
-    if (lane >= __popcll(s)) return;
-    const unsigned id = bm + lane;
-    unsigned label = id;
-    if (u) {
-        const int x = xstart[id];
-        const u64 rest = ~(m >> x);  // first zero above the run start ends the run
-        const int len = rest ? __ffsll((long long)rest) - 1 : 64;
-        int lo = x, hi = x + len - 1;
-        if (diag) {
-            lo = max(lo - 1, 0);
-            hi = min(hi + 1, 63);
-        }
-        const u64 window = ((2ull << hi) - 1ull) & ~((1ull << lo) - 1ull);
-        const u64 t = u & window;
-        if (t) {
-            const int f = __ffsll((long long)t) - 1;
-            label = lab[bu + run_index(su, f)];
-            // further touched runs start strictly after f inside the window
-            u64 more = su & window & ~((2ull << f) - 1ull);
-            while (more) {
-                const int p = __ffsll((long long)more) - 1;
-                more &= more - 1;
-                label = sm_unite(parent, label, lab[bu + run_index(su, p)]);
-            }
-        }
-    }
-    lab[id] = (unsigned short)label;
-}
-
 __device__ __forceinline__ unsigned nibble_of(unsigned w) {
     // one bit per non-zero byte, lowest address -> lowest bit
     return (((__vcmpne4(w, 0u) & 0x01010101u) * 0x01020408u) >> 24) & 0xfu;
+}
+
+// Link run `id` = [x, x+len) of one row with every run of neighbour row (mask u, starts su, id base bu) it touches.
+// Touched runs are consecutive in index, so only the first needs a popcount.
+__device__ __forceinline__ void link_run(unsigned* parent, unsigned id, int x, int len, u64 u, u64 su, unsigned bu,
+                                         bool diag) {
+    int lo = x, hi = x + len - 1;
+    if (diag) {
+        lo = max(lo - 1, 0);
+        hi = min(hi + 1, 63);
+    }
+    const u64 window = ((2ull << hi) - 1ull) & ~((1ull << lo) - 1ull);
+    const u64 t = u & window;
+    if (!t) return;
+    const int f = __ffsll((long long)t) - 1;
+    unsigned j = bu + run_index(su, f);
+    sm_unite(parent, id, j);
+    u64 more = su & window & ~((2ull << f) - 1ull);  // further touched runs start strictly after f inside the window
+    while (more) {
+        more &= more - 1;
+        sm_unite(parent, id, ++j);
+    }
 }
 
 __global__ void __launch_bounds__(kThreads) ccl_tile_kernel(const uint8_t* __restrict__ mask, int32_t* __restrict__ L,
@@ -154,20 +119,21 @@ __global__ void __launch_bounds__(kThreads) ccl_tile_kernel(const uint8_t* __res
                                                             Geom g) {
     __shared__ u64 rmask[kRows];
     __shared__ u64 rstart[kRows];
-    __shared__ __align__(16) unsigned parent[kMaxRuns];   // union-find over labels (= id of the run that made them)
-    __shared__ unsigned short lab[kMaxRuns];              // label of every run
-    __shared__ int32_t glab[kMaxRuns];                    // root label -> global index of its first pixel
+    __shared__ __align__(16) unsigned parent[kMaxRuns];   // union-find over run ids (row * 32 + index in row)
+    __shared__ int32_t glab[kMaxRuns];                    // root run -> global index of its first pixel
     __shared__ unsigned char xstart[kMaxRuns];            // first pixel (x within the tile) of every run
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int ty_mask = (1 << g.ty_log2) - 1;
-    const int bid = blockIdx.x;
-    const int tx = bid % g.tiles_x;
-    const int ty = (bid / g.tiles_x) % g.tiles_y;
-    const int tz = bid / (g.tiles_x * g.tiles_y);
+    // grid: x = tile column, y = tile row, z = image * tiles_z + tile plane
+    const int tx = blockIdx.x, ty = blockIdx.y;
+    const int img = blockIdx.z / g.tiles_z, tz = blockIdx.z - img * g.tiles_z;
+    const int bid = (tz * g.tiles_y + ty) * g.tiles_x + tx;
     const int64_t x0 = (int64_t)tx * kTX, y0 = (int64_t)ty << g.ty_log2, z0 = (int64_t)tz * (kRows >> g.ty_log2);
     const int64_t vol = g.Z * g.Y * g.X;
-    const uint8_t* im = mask + (int64_t)blockIdx.y * vol;
-    int32_t* Li = L + (int64_t)blockIdx.y * vol;
+    const uint8_t* im = mask + (int64_t)img * vol;
+    int32_t* Li = L + (int64_t)img * vol;
+    __shared__ u64 rroot[kRows];
+    if (threadIdx.x < kRows) rroot[threadIdx.x] = 0;
 
     // ---- A: rows -> bit masks ----
     if ((g.X & 15) == 0 && x0 + kTX <= g.X && (((uintptr_t)im) & 15) == 0) {
@@ -198,90 +164,114 @@ __global__ void __launch_bounds__(kThreads) ccl_tile_kernel(const uint8_t* __res
                 const u64 v = ((u64)hi << 32) | lo;
                 rmask[r] = v;
                 rstart[r] = v & ~(v << 1);
-                }
+            }
         }
     }
     for (int i = threadIdx.x; i < kMaxRuns; i += kThreads) parent[i] = i;
     __syncthreads();
 
-    // ---- B1: each warp walks its strip of 8 rows top to bottom (2-D: 8 image rows, 3-D: the 8 y-rows of one z) ----
-    const int TY = 1 << g.ty_log2;
-    const bool diag1 = g.conn >= 2;
-    const u64 le0 = (2ull << lane) - 1ull, le1 = (2ull << (lane + 32)) - 1ull;  // bits <= this lane's two pixels
+    // ---- B: every run is linked to the runs it touches in the rows before it.  Four threads share a row and take
+    //         every fourth run: the loop over a row's runs is sequential per thread, but all 256 threads (64 rows)
+    //         run it side by side, so the instruction stream is spent on runs, not on idle lanes. ----
     {
-        const int r0 = warp * 8;
-        for (int r = r0; r < r0 + 8; ++r) {
-            const u64 m = rmask[r];
-            if (m) {
-                const bool first = (r == r0);
-                label_row(parent, lab, xstart, m, rstart[r], first ? 0ull : rmask[r - 1], first ? 0ull : rstart[r - 1],
-                          r * 32, (r - 1) * 32, diag1, lane, le0, le1);
+        const int TY = 1 << g.ty_log2;
+        const int r = threadIdx.x >> 2, part = threadIdx.x & 3;
+        const u64 m = rmask[r];
+        u64 s = rstart[r];
+        const int lz = r >> g.ty_log2, ly = r & ty_mask;
+        const bool d1 = g.conn >= 2, d2 = g.conn >= 3;
+        int k = part;
+        for (int i = 0; i < part && s; ++i) s &= s - 1;  // skip to this thread's first run
+        while (s) {
+            const int x = __ffsll((long long)s) - 1;
+            const unsigned id = r * 32 + k;
+            xstart[id] = (unsigned char)x;
+            const u64 rest = ~(m >> x);  // first zero above the run start ends the run
+            const int len = rest ? __ffsll((long long)rest) - 1 : 64;
+            if (ly > 0) link_run(parent, id, x, len, rmask[r - 1], rstart[r - 1], (r - 1) * 32, d1);
+            if (lz > 0) {
+                link_run(parent, id, x, len, rmask[r - TY], rstart[r - TY], (r - TY) * 32, d1);
+                if (g.conn >= 2) {
+                    if (ly > 0) link_run(parent, id, x, len, rmask[r - TY - 1], rstart[r - TY - 1], (r - TY - 1) * 32, d2);
+                    if (ly < TY - 1)
+                        link_run(parent, id, x, len, rmask[r - TY + 1], rstart[r - TY + 1], (r - TY + 1) * 32, d2);
+                }
             }
-            __syncwarp();
+            // on to run k + 4 of this row
+            s &= s - 1;
+            s &= s - 1;
+            s &= s - 1;
+            s &= s - 1;
+            k += 4;
         }
     }
     __syncthreads();
 
-    // ---- B2: pairwise links across strip boundaries (2-D) / between z-planes (3-D) ----
-    if (g.ty_log2 == 6) {
-        const int r = warp * 8;
-        if (warp > 0 && rmask[r])
-            link_rows(parent, lab, rmask[r], rstart[r], rmask[r - 1], rstart[r - 1], r * 32, (r - 1) * 32, diag1, lane);
-    } else {
-        for (int r = warp; r < kRows; r += kThreads / 32) {
-            const u64 m = rmask[r];
-            const int lz = r >> g.ty_log2, ly = r & ty_mask;
-            if (!m || lz == 0) continue;
-            const u64 s = rstart[r];
-            link_rows(parent, lab, m, s, rmask[r - TY], rstart[r - TY], r * 32, (r - TY) * 32, diag1, lane);
-            if (g.conn >= 2) {
-                if (ly > 0)
-                    link_rows(parent, lab, m, s, rmask[r - TY - 1], rstart[r - TY - 1], r * 32, (r - TY - 1) * 32,
-                              g.conn >= 3, lane);
-                if (ly < TY - 1)
-                    link_rows(parent, lab, m, s, rmask[r - TY + 1], rstart[r - TY + 1], r * 32, (r - TY + 1) * 32,
-                              g.conn >= 3, lane);
-            }
+    // ---- C: flatten per run (same walk: 4 threads per row); a root is the component's first run in the tile and gets
+    //         the global index of its first pixel ----
+    {
+        const int r = threadIdx.x >> 2, part = threadIdx.x & 3;
+        const int n_runs = __popcll(rstart[r]);
+        const int64_t row_base = ((z0 + (r >> g.ty_log2)) * g.Y + (y0 + (r & ty_mask))) * g.X + x0;
+        for (int k = part; k < n_runs; k += 4) {
+            const unsigned id = r * 32 + k;
+            const unsigned root = sm_find_ro(parent, id);
+            parent[id] = root;
+            if (root == id) glab[id] = (int32_t)(row_base + xstart[id]);
         }
     }
     __syncthreads();
 
-    // ---- C: flatten per run; a root label is the id of the component's first run in the tile and gets the global
-    //         index of that run's first pixel ----
-    for (int id = threadIdx.x; id < kMaxRuns; id += kThreads) {
-        const int r = id >> 5, k = id & 31;
-        if (k >= __popcll(rstart[r])) continue;
-        const unsigned root = sm_find_ro(parent, lab[id]);
-        lab[id] = (unsigned short)root;
-        if (root == (unsigned)id)
-            glab[id] = (int32_t)(((z0 + (r >> g.ty_log2)) * g.Y + (y0 + (r & ty_mask))) * g.X + x0 + xstart[id]);
-    }
-    __syncthreads();
-
-    // ---- D: per-pixel parents; the tile's roots (run starts whose run kept its own label) go to the root bitmap ----
-    const int64_t wpr = g.tiles_x;
-    for (int r = warp; r < kRows; r += kThreads / 32) {
-        const int64_t z = z0 + (r >> g.ty_log2), y = y0 + (r & ty_mask);
-        if (z >= g.Z || y >= g.Y) continue;
-        const u64 m = rmask[r], s = rstart[r];
-        int32_t* row = Li + (z * g.Y + y) * g.X + x0;
-        unsigned rootmask[2];
+    // ---- D: per-pixel parents, 4 pixels per lane (one 16-byte store), two rows per warp instruction; tile roots
+    //         (first pixel of a run that is its own root) go to the root bitmap ----
+    {
+        const int64_t wpr = g.tiles_x;
+        const int lane16 = lane & 15, sub = lane >> 4;
+        const int x4 = lane16 * 4;
+        const bool vec_ok = ((g.X & 3) == 0) && ((((uintptr_t)Li) & 15) == 0);
+#pragma unroll 1
+        for (int it = 0; it < 4; ++it) {
+            const int r = warp * 8 + it * 2 + sub;
+            const int64_t z = z0 + (r >> g.ty_log2), y = y0 + (r & ty_mask);
+            const bool row_ok = z < g.Z && y < g.Y;
+            const u64 m = rmask[r], s = rstart[r];
+            const unsigned m4 = (unsigned)(m >> x4) & 0xfu, s4 = (unsigned)(s >> x4) & 0xfu;
+            int idx = r * 32 + __popcll(s & ((1ull << x4) - 1ull)) - 1;  // run open before this unit (if any)
+            int32_t v[4] = {-1, -1, -1, -1};
+            int32_t cur = -1;
+            bool have = false;
+            unsigned rootnib = 0;
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {
-            const int x = lane + 32 * h;
-            int32_t v = -1;
-            bool is_root = false;
-            if ((m >> x) & 1ull) {
-                const unsigned id = r * 32 + __popcll(s & (h ? le1 : le0)) - 1;
-                const unsigned root = lab[id];
-                v = glab[root];
-                is_root = ((s >> x) & 1ull) && root == id;
+            for (int j = 0; j < 4; ++j) {
+                if ((s4 >> j) & 1u) {
+                    ++idx;
+                    const unsigned root = parent[idx];
+                    cur = glab[root];
+                    have = true;
+                    if (root == (unsigned)idx) rootnib |= 1u << j;
+                } else if (((m4 >> j) & 1u) && !have) {
+                    cur = glab[parent[idx]];
+                    have = true;
+                }
+                if ((m4 >> j) & 1u) v[j] = cur;
             }
-            rootmask[h] = __ballot_sync(0xffffffffu, is_root);
-            if (x0 + x < g.X) row[x] = v;
+            if (rootnib) atomicOr(&rroot[r], (u64)rootnib << x4);
+            if (!row_ok) continue;
+            int32_t* row = Li + (z * g.Y + y) * g.X + x0 + x4;
+            if (vec_ok && x0 + x4 + 4 <= g.X) {
+                *reinterpret_cast<int4*>(row) = make_int4(v[0], v[1], v[2], v[3]);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    if (x0 + x4 + j < g.X) row[j] = v[j];
+            }
         }
-        if (lane == 0)
-            rootbits[((int64_t)blockIdx.y * g.Z * g.Y + z * g.Y + y) * wpr + tx] = ((u64)rootmask[1] << 32) | rootmask[0];
+        __syncwarp();  // the 8 rows of this warp's band were written by this warp only
+        if (lane < 8) {
+            const int r = warp * 8 + lane;
+            const int64_t z = z0 + (r >> g.ty_log2), y = y0 + (r & ty_mask);
+            if (z < g.Z && y < g.Y) rootbits[((int64_t)img * g.Z * g.Y + z * g.Y + y) * wpr + tx] = rroot[r];
+        }
     }
     if (warp == 0 && edges) {
         const u64 a = rmask[lane], b = rmask[lane + 32];
@@ -293,7 +283,7 @@ __global__ void __launch_bounds__(kThreads) ccl_tile_kernel(const uint8_t* __res
             e.bottom = rmask[kRows - 1];
             e.left = ((u64)l_hi << 32) | l_lo;
             e.right = ((u64)r_hi << 32) | r_lo;
-            edges[(int64_t)blockIdx.y * gridDim.x + bid] = e;
+            edges[(int64_t)img * (g.tiles_x * g.tiles_y * g.tiles_z) + bid] = e;
         }
     }
 }
@@ -579,8 +569,11 @@ extern "C" int be_ccl_u8_i32(const uint8_t* mask, int32_t* labels, int64_t N, in
     cudaStream_t s = (cudaStream_t)stream;
     const CclWorkspace w = carve_ccl_ws(ws, N, Z, Y, X);
 
-    ccl_tile_kernel<<<dim3((unsigned)n_tiles, (unsigned)N), kThreads, 0, s>>>(mask, w.L, w.rootbits,
-                                                                              ndim == 2 ? w.edges : nullptr, g);
+    BE_REQUIRE(g.tiles_y <= 65535 && (int64_t)g.tiles_z * N <= 65535, BE_ERR_TOO_LARGE,
+               "be_ccl_u8_i32: tile grid (%d, %d, %lld) exceeds the launch limits", g.tiles_x, g.tiles_y,
+               (long long)g.tiles_z * N);
+    ccl_tile_kernel<<<dim3((unsigned)g.tiles_x, (unsigned)g.tiles_y, (unsigned)(g.tiles_z * N)), kThreads, 0, s>>>(
+        mask, w.L, w.rootbits, ndim == 2 ? w.edges : nullptr, g);
     BE_LAUNCH_CHECK();
     if (ndim == 2) {
         if (n_tiles > 1) {

@@ -223,15 +223,10 @@ __global__ void __launch_bounds__(kThreads) stitch_blend_kernel(const float* __r
     const int64_t tile_stride = d.C * tvol;  // elements between consecutive tiles
     const int x0 = u * 4;
     const int cnt = min(4, (int)d.X - x0);
-    // x cover: one division pair for the first pixel, the other three follow by comparison
-    int kx_lo[4], kx_hi[4];
-    cover(x0, d.Bx, s.Sx, d.Tx, &kx_lo[0], &kx_hi[0]);
-#pragma unroll
-    for (int j = 1; j < 4; ++j) {
-        const int x = x0 + j;
-        kx_hi[j] = kx_hi[j - 1] + ((kx_hi[j - 1] + 1 < d.Tx && (kx_hi[j - 1] + 1) * s.Sx <= x) ? 1 : 0);
-        kx_lo[j] = kx_lo[j - 1] + ((kx_lo[j - 1] * s.Sx + d.Bx <= x) ? 1 : 0);
-    }
+    // tiles touching this 4-px unit: from the first tile covering x0 to the last one covering its last pixel
+    int kx_first, kx_last, tmp;
+    cover(x0, d.Bx, s.Sx, d.Tx, &kx_first, &tmp);
+    cover(x0 + cnt - 1, d.Bx, s.Sx, d.Tx, &tmp, &kx_last);
     int ky_lo, ky_hi;
     cover(y, d.By, s.Sy, d.Ty, &ky_lo, &ky_hi);  // block-uniform
 
@@ -253,15 +248,33 @@ __global__ void __launch_bounds__(kThreads) stitch_blend_kernel(const float* __r
                 const double wzy = __dmul_rn(wzv, wy[iy]);
                 const float* rowbase = tiles + (((n * d.Tz + kz) * d.Ty + ky) * d.Tx) * tile_stride +
                                        (((int64_t)c * d.Bz + iz) * d.By + iy) * d.Bx;
+                for (int kx = kx_first; kx <= kx_last; ++kx) {
+                    const int ix0 = x0 - kx * s.Sx;  // in-tile offset of the unit's first pixel
+                    const float* src = rowbase + kx * tile_stride + ix0;
+                    if (cnt == 4 && ix0 >= 0 && ix0 + 4 <= d.Bx && ((((uintptr_t)src) & 15) == 0) && ((ix0 & 1) == 0)) {
+                        // the whole unit lies inside this tile: one 16-byte tile load, two 16-byte window loads
+                        const float4 p = __ldg(reinterpret_cast<const float4*>(src));
+                        const double2 wa = __ldg(reinterpret_cast<const double2*>(wx + ix0));
+                        const double2 wb = __ldg(reinterpret_cast<const double2*>(wx + ix0 + 2));
+                        const float w0 = (float)__dmul_rn(wzy, wa.x), w1 = (float)__dmul_rn(wzy, wa.y);
+                        const float w2 = (float)__dmul_rn(wzy, wb.x), w3 = (float)__dmul_rn(wzy, wb.y);
+                        acc[0] = __dadd_rn(acc[0], (double)__fmul_rn(p.x, w0));
+                        acc[1] = __dadd_rn(acc[1], (double)__fmul_rn(p.y, w1));
+                        acc[2] = __dadd_rn(acc[2], (double)__fmul_rn(p.z, w2));
+                        acc[3] = __dadd_rn(acc[3], (double)__fmul_rn(p.w, w3));
+                        wacc[0] = __dadd_rn(wacc[0], (double)w0);
+                        wacc[1] = __dadd_rn(wacc[1], (double)w1);
+                        wacc[2] = __dadd_rn(wacc[2], (double)w2);
+                        wacc[3] = __dadd_rn(wacc[3], (double)w3);
+                    } else {
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    if (j < cnt) {
-                        for (int kx = kx_lo[j]; kx <= kx_hi[j]; ++kx) {
-                            const int ix = x0 + j - kx * s.Sx;
-                            const float w = (float)__dmul_rn(wzy, wx[ix]);
-                            const float p = __ldg(rowbase + kx * tile_stride + ix);
-                            acc[j] = __dadd_rn(acc[j], (double)__fmul_rn(p, w));
-                            wacc[j] = __dadd_rn(wacc[j], (double)w);
+                        for (int j = 0; j < 4; ++j) {
+                            const int ix = ix0 + j;
+                            if (j < cnt && ix >= 0 && ix < d.Bx) {
+                                const float w = (float)__dmul_rn(wzy, wx[ix]);
+                                acc[j] = __dadd_rn(acc[j], (double)__fmul_rn(__ldg(src + j), w));
+                                wacc[j] = __dadd_rn(wacc[j], (double)w);
+                            }
                         }
                     }
                 }
