@@ -93,6 +93,17 @@ __device__ __forceinline__ double be_fast_rcp(double d) {
     r = fma(fma(-d, r, 1.0), r, r);
     return r;
 }
+// kept out of line on purpose: inlined, the compiler computes the full division speculatively next to the fast path
+static __device__ __noinline__ float be_div_to_f32_exact(double n, double d) { return (float)__ddiv_rn(n, d); }
+
+// exact floor(p / S) for 0 <= p < 2^24, 0 < S < 2^24, with rS = 1.0f / S: float estimate + one-step correction
+__device__ __forceinline__ int be_fast_div(int p, int S, float rS) {
+    int q = __float2int_rz(__int2float_rz(p) * rS);
+    q -= (q * S > p);
+    q += ((q + 1) * S <= p);
+    return q;
+}
+
 __device__ __forceinline__ float be_div_to_f32(double n, double d, double r) {
     const double q = n * r;
     if (n == 0.0) return (float)q;  // +-0 / d (and 0/0 -> NaN through r = inf), very common at the lower quantile
@@ -102,7 +113,7 @@ __device__ __forceinline__ float be_div_to_f32(double n, double d, double r) {
     const bool near_mid = (low - (0x10000000u - 64u)) <= 128u;
     const bool normal = ex > (1023u - 126u) && ex < (1023u + 127u);
     if (!near_mid && normal) return (float)q;
-    return (float)__ddiv_rn(n, d);
+    return be_div_to_f32_exact(n, d);
 }
 
 __device__ __forceinline__ double warp_sum(double v) {

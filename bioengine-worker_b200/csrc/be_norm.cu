@@ -5,7 +5,11 @@
 //   be_normalize_f32   (x - sub) / div in fp64, optional clip
 //   be_elementwise_f32 clip / scale_linear / sigmoid
 //   be_binarize_f32_u8 x > thr
+#include <cooperative_groups.h>
+
 #include "be_common.cuh"
+
+namespace cg = cooperative_groups;
 
 namespace {
 
@@ -542,6 +546,496 @@ __global__ void __launch_bounds__(kThreads) binarize_kernel(const float* __restr
     }
 }
 
+// ---------------------------------------------------------------------------------------------------
+// sampled-pivot select: one streaming pass over a large segment instead of three
+// ---------------------------------------------------------------------------------------------------
+//
+// For every (segment, quantile) TASK a 2048-element sample is sorted and two pivots flo <= fhi are taken 5 sigma
+// (of the sample-rank binomial) either side of the wanted rank.  One pass over the segment then counts the elements
+// below flo, equal to flo, equal to fhi, and appends the (about 2-3 %) strictly in between to a candidate list.  The
+// exact order statistics are found by the same 11/11/10-bit radix select, run over the candidate list only, with the
+// tie counts entering the histograms as "virtual" elements at key(flo) / key(fhi).  If the wanted rank falls outside
+// the bracket or the list overflows (both essentially impossible, but data-dependent), the task's source is switched
+// to the whole segment and the very same radix kernels do the full three passes: the result is exact either way.
+
+constexpr int kSample = 2048;  // one compare-exchange pair per thread and stage
+constexpr int kSampleThreads = 1024;
+constexpr int64_t kSampleMinLen = (int64_t)1 << 18;  // below this the plain radix select is used
+constexpr int kStage = 1024;                         // per-block staging of candidates in shared memory
+
+struct QTask {
+    const float* src;     // candidate list, or the segment itself after a fallback
+    uint32_t len;
+    uint32_t rank[2];     // ranks (lo, hi) inside the multiset {virtual ties} + src
+    uint32_t vkey[2];     // key(flo), key(fhi)
+    uint32_t vcnt[2];     // how many elements equal flo / fhi
+    uint32_t total;       // multiset size (0 => all-NaN segment => NaN result)
+    double gamma;
+    // partition phase
+    float flo, fhi;
+    uint32_t below, eq_lo, eq_hi, n_mid;
+};
+
+struct SWorkspace {
+    unsigned* counters;   // [4][n_tasks] (partition uses slot 3, by segment)
+    unsigned* nan_count;  // [n_seg]
+    unsigned* seg_done;   // [n_seg]
+    unsigned* hist0;      // [n_tasks][kBins]
+    unsigned* hist12;     // [n_tasks][2][kBins]
+    QTask* tasks;         // [n_tasks]   (zeroed: counters inside)
+    size_t zero_bytes;
+    QState* state;        // [n_tasks]
+    float* cand;          // [n_tasks][cap]
+    int64_t cap;
+    size_t total_bytes;
+};
+
+inline int64_t sample_cap(int64_t seg_len) {
+    int64_t c = seg_len / 16;
+    if (c < 16384) c = 16384;
+    return (c + 63) / 64 * 64;
+}
+
+inline int64_t sample_segments_per_pass(int64_t n_seg, int64_t seg_len) {
+    const int64_t per_seg = sample_cap(seg_len) * 2 * (int64_t)sizeof(float);
+    int64_t s = ((int64_t)256 << 20) / per_seg;
+    if (s < 1) s = 1;
+    if (s > 4096) s = 4096;
+    return n_seg < s ? n_seg : s;
+}
+
+inline SWorkspace carve_sample_ws(void* ws, int64_t n_seg, int n_q, int64_t seg_len) {
+    SWorkspace w;
+    const int64_t nt = n_seg * n_q;
+    char* p = (char*)ws;
+    size_t off = 0;
+    w.counters = (unsigned*)(p + off);
+    off += be_align_up(sizeof(unsigned) * 4 * nt, 256);
+    w.nan_count = (unsigned*)(p + off);
+    off += be_align_up(sizeof(unsigned) * n_seg, 256);
+    w.seg_done = (unsigned*)(p + off);
+    off += be_align_up(sizeof(unsigned) * n_seg, 256);
+    w.hist0 = (unsigned*)(p + off);
+    off += be_align_up(sizeof(unsigned) * kBins * nt, 256);
+    w.hist12 = (unsigned*)(p + off);
+    off += be_align_up(sizeof(unsigned) * kBins * 2 * nt, 256);
+    w.tasks = (QTask*)(p + off);
+    off += be_align_up(sizeof(QTask) * nt, 256);
+    w.zero_bytes = off;
+    w.state = (QState*)(p + off);
+    off += be_align_up(sizeof(QState) * nt, 256);
+    w.cap = sample_cap(seg_len);
+    w.cand = (float*)(p + off);
+    off += be_align_up(sizeof(float) * w.cap * nt, 256);
+    w.total_bytes = off;
+    return w;
+}
+
+__device__ __forceinline__ uint32_t hash32(uint32_t x) {
+    x ^= x >> 16;
+    x *= 0x7feb352du;
+    x ^= x >> 15;
+    x *= 0x846ca68bu;
+    x ^= x >> 16;
+    return x;
+}
+
+// one block per segment: sample, bitonic sort in shared memory, pivots for each quantile
+__global__ void __launch_bounds__(kSampleThreads) qsel_sample_kernel(const float* __restrict__ x, int64_t seg_len,
+                                                                     const double* __restrict__ q, int n_q,
+                                                                     SWorkspace w) {
+    __shared__ uint32_t key[kSample];
+    __shared__ unsigned s_valid;
+    const int64_t seg = blockIdx.x;
+    const float* xs = x + seg * seg_len;
+    const uint32_t stride = (uint32_t)(seg_len / kSample);  // >= 64
+    if (threadIdx.x == 0) s_valid = 0;
+    __syncthreads();
+    unsigned valid = 0;
+    for (int i = threadIdx.x; i < kSample; i += kSampleThreads) {
+        const int64_t pos = (int64_t)i * stride + hash32((uint32_t)i * 0x9e3779b9u + (uint32_t)seg) % stride;
+        const float v = __ldg(xs + pos);
+        const bool ok = (v == v);
+        key[i] = ok ? f32_to_key(v) : 0xffffffffu;  // NaNs sort last
+        valid += ok;
+    }
+    valid = __reduce_add_sync(0xffffffffu, valid);
+    if ((threadIdx.x & 31) == 0) atomicAdd(&s_valid, valid);
+    __syncthreads();
+    for (int k = 2; k <= kSample; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int p = threadIdx.x; p < kSample / 2; p += kSampleThreads) {
+                const int i = ((p & ~(j - 1)) << 1) | (p & (j - 1));  // lower element of the p-th pair at distance j
+                const int l = i | j;
+                const uint32_t a = key[i], b = key[l];
+                if ((a > b) == ((i & k) == 0)) {
+                    key[i] = b;
+                    key[l] = a;
+                }
+            }
+            __syncthreads();
+        }
+    }
+    if ((int)threadIdx.x < n_q) {
+        const int i = threadIdx.x;
+        const int mv = (int)s_valid;
+        QTask* t = &w.tasks[seg * n_q + i];
+        float flo = __int_as_float(0xff800000), fhi = __int_as_float(0x7f800000);
+        if (mv > 0) {
+            const double qi = fmin(fmax(q[i], 0.0), 1.0);
+            const double sp = qi * (double)(mv - 1);
+            const int d = (int)(5.0 * sqrt((double)mv * qi * (1.0 - qi))) + 12;
+            const int lo = (int)floor(sp) - d, hi = (int)ceil(sp) + 1 + d;
+            if (lo >= 0) flo = key_to_f32(key[lo]);
+            if (hi < mv) fhi = key_to_f32(key[hi]);
+        }
+        t->flo = flo;
+        t->fhi = fhi;
+    }
+}
+
+// the single streaming pass: classify every element against the (<= 2) brackets of its segment
+template <int NQ>
+__global__ void __launch_bounds__(kThreads) qsel_partition_kernel(const float* __restrict__ x, int64_t seg_len, int bps,
+                                                                  int64_t chunk, const double* __restrict__ q,
+                                                                  SWorkspace w, int64_t n_seg) {
+    __shared__ float s_buf[NQ][kStage];
+    __shared__ unsigned s_n[NQ], s_cnt[NQ][3], s_nan, s_base[NQ];
+    const int64_t seg = blockIdx.y;
+    const float* xs = x + seg * seg_len;
+    QTask* tasks = w.tasks + seg * NQ;
+    float flo[NQ], fhi[NQ];
+#pragma unroll
+    for (int i = 0; i < NQ; ++i) {
+        flo[i] = tasks[i].flo;
+        fhi[i] = tasks[i].fhi;
+    }
+    if (threadIdx.x < NQ) {
+        s_n[threadIdx.x] = 0;
+        s_cnt[threadIdx.x][0] = s_cnt[threadIdx.x][1] = s_cnt[threadIdx.x][2] = 0;
+    }
+    if (threadIdx.x == 0) s_nan = 0;
+    __syncthreads();
+
+    const int64_t begin = (int64_t)blockIdx.x * chunk;
+    const int64_t end = min(begin + chunk, seg_len);
+    unsigned below[NQ], eqlo[NQ], eqhi[NQ], nans = 0;
+#pragma unroll
+    for (int i = 0; i < NQ; ++i) below[i] = eqlo[i] = eqhi[i] = 0;
+
+    // rare path, one element: ties with the pivots are counted, the rest of the bracket is appended
+    auto take_inside = [&](float v) {
+#pragma unroll
+        for (int i = 0; i < NQ; ++i) {
+            if (v >= flo[i] && v <= fhi[i]) {
+                if (v == flo[i]) {
+                    ++eqlo[i];
+                } else if (v == fhi[i]) {
+                    ++eqhi[i];
+                } else {
+                    const unsigned pos = atomicAdd(&s_n[i], 1u);
+                    if (pos < kStage) {
+                        s_buf[i][pos] = v;
+                    } else {  // staging full: straight to the global list (still counted if that is full too)
+                        const unsigned g = atomicAdd(&tasks[i].n_mid, 1u);
+                        if (g < w.cap) w.cand[(seg * NQ + i) * w.cap + g] = v;
+                    }
+                }
+            }
+        }
+    };
+    // common path, one element: a compare-and-count per bracket; returns whether the element needs the rare path
+    auto classify = [&](float v) -> bool {
+        nans += (v != v);
+        bool inside = false;
+#pragma unroll
+        for (int i = 0; i < NQ; ++i) {
+            below[i] += (v < flo[i]);
+            inside |= (v >= flo[i]) & (v <= fhi[i]);  // NaN is never inside
+        }
+        return inside;
+    };
+
+    const float* p = xs + begin;
+    const int64_t n = end - begin;
+    if ((((uintptr_t)p) & 15) == 0) {
+        // 16 elements per thread and iteration: all of them take the cheap path first, and the 2-3 % that fall inside a
+        // bracket are handled afterwards from a 16-bit flag word, so the divergent code runs once per 16 elements
+        const float4* p4 = reinterpret_cast<const float4*>(p);
+        const int64_t n4 = n >> 2;
+        for (int64_t base = threadIdx.x; base < n4; base += 4 * kThreads) {
+            float4 v[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                if (base + k * kThreads < n4) v[k] = ld_stream_f4(p4 + base + k * kThreads);
+            unsigned flags = 0;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                if (base + k * kThreads < n4) {
+                    flags |= (unsigned)classify(v[k].x) << (4 * k + 0);
+                    flags |= (unsigned)classify(v[k].y) << (4 * k + 1);
+                    flags |= (unsigned)classify(v[k].z) << (4 * k + 2);
+                    flags |= (unsigned)classify(v[k].w) << (4 * k + 3);
+                }
+            }
+            while (flags) {
+                const int b = __ffs(flags) - 1;
+                flags &= flags - 1;
+                const float4 q4 = v[b >> 2];
+                const int c = b & 3;
+                take_inside(c == 0 ? q4.x : (c == 1 ? q4.y : (c == 2 ? q4.z : q4.w)));
+            }
+        }
+        for (int64_t i = (n4 << 2) + threadIdx.x; i < n; i += kThreads)
+            if (classify(p[i])) take_inside(p[i]);
+    } else {
+        for (int64_t i = threadIdx.x; i < n; i += kThreads)
+            if (classify(p[i])) take_inside(p[i]);
+    }
+#pragma unroll
+    for (int i = 0; i < NQ; ++i) {
+        const unsigned b = __reduce_add_sync(0xffffffffu, below[i]);
+        const unsigned l = __reduce_add_sync(0xffffffffu, eqlo[i]);
+        const unsigned h = __reduce_add_sync(0xffffffffu, eqhi[i]);
+        if ((threadIdx.x & 31) == 0) {
+            if (b) atomicAdd(&s_cnt[i][0], b);
+            if (l) atomicAdd(&s_cnt[i][1], l);
+            if (h) atomicAdd(&s_cnt[i][2], h);
+        }
+    }
+    nans = __reduce_add_sync(0xffffffffu, nans);
+    if ((threadIdx.x & 31) == 0 && nans) atomicAdd(&s_nan, nans);
+    __syncthreads();
+    if (threadIdx.x < NQ) {
+        const int i = threadIdx.x;
+        const unsigned n = min(s_n[i], (unsigned)kStage);
+        s_base[i] = n ? atomicAdd(&tasks[i].n_mid, n) : 0u;
+        if (s_cnt[i][0]) atomicAdd(&tasks[i].below, s_cnt[i][0]);
+        if (s_cnt[i][1]) atomicAdd(&tasks[i].eq_lo, s_cnt[i][1]);
+        if (s_cnt[i][2]) atomicAdd(&tasks[i].eq_hi, s_cnt[i][2]);
+    }
+    if (threadIdx.x == 0 && s_nan) atomicAdd(&w.nan_count[seg], s_nan);
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < NQ; ++i) {
+        const unsigned n = min(s_n[i], (unsigned)kStage), base = s_base[i];
+        float* dst = w.cand + (seg * NQ + i) * w.cap;
+        for (unsigned k = threadIdx.x; k < n; k += kThreads)
+            if (base + k < w.cap) dst[base + k] = s_buf[i][k];
+    }
+
+    if (!last_block_of_segment(&w.counters[3 * n_seg * NQ + seg], bps)) return;
+
+    // all counts of this segment are final: turn each bracket into a selection task (fields are read into registers
+    // up front and the task is written back once, so the serial tail is a handful of memory round trips)
+    if (threadIdx.x < NQ) {
+        const int i = threadIdx.x;
+        QTask* t = &tasks[i];
+        const uint32_t n_nan = __ldcg(&w.nan_count[seg]);
+        const uint32_t below_c = __ldcg(&t->below), eq_lo = __ldcg(&t->eq_lo), eq_hi = __ldcg(&t->eq_hi);
+        const uint32_t n_mid = __ldcg(&t->n_mid);
+        const float tflo = flo[i], tfhi = fhi[i];
+        const double qi = q[i];
+        const uint32_t n_valid = (uint32_t)seg_len - n_nan;
+        // numpy: virtual index q*(n-1) in fp64, neighbours floor / floor+1 clipped to n-1
+        double h = (n_valid > 0) ? qi * (double)(n_valid - 1) : 0.0;
+        if (h < 0.0) h = 0.0;
+        const double lo = floor(h);
+        uint32_t ilo = (uint32_t)lo;
+        if (n_valid > 0 && ilo > n_valid - 1) ilo = n_valid - 1;
+        const uint32_t ihi = (n_valid > 0 && ilo + 1 < n_valid) ? ilo + 1 : ilo;
+        const uint32_t inside = eq_lo + n_mid + eq_hi;
+        const bool ok = n_mid <= (uint32_t)w.cap && ilo >= below_c && ihi < below_c + inside;
+        QTask r;
+        r.gamma = h - lo;
+        r.flo = tflo;
+        r.fhi = tfhi;
+        r.below = below_c;
+        r.eq_lo = eq_lo;
+        r.eq_hi = eq_hi;
+        r.n_mid = n_mid;
+        if (ok || n_valid == 0) {
+            r.src = w.cand + (seg * NQ + i) * w.cap;
+            r.len = n_valid ? n_mid : 0;
+            r.rank[0] = ilo - below_c;
+            r.rank[1] = ihi - below_c;
+            r.vkey[0] = f32_to_key(tflo);
+            r.vkey[1] = f32_to_key(tfhi);
+            r.vcnt[0] = eq_lo;
+            r.vcnt[1] = eq_hi;
+            r.total = n_valid ? inside : 0;
+        } else {  // bracket missed or list overflowed: select on the whole segment instead
+            r.src = xs;
+            r.len = (uint32_t)seg_len;
+            r.rank[0] = ilo;
+            r.rank[1] = ihi;
+            r.vkey[0] = r.vkey[1] = 0;
+            r.vcnt[0] = r.vcnt[1] = 0;
+            r.total = n_valid;
+        }
+        *t = r;
+        __threadfence();
+    }
+}
+
+// ties with the pivots take part in the selection as `vcnt` virtual elements at `vkey`
+template <int LEVEL>
+__device__ __forceinline__ void add_virtual(const QTask* t, const QState* st, unsigned* gh) {
+    constexpr int kBits = (LEVEL == 0) ? 11 : (LEVEL == 1 ? 11 : 10);
+    constexpr int kShift = (LEVEL == 0) ? 21 : (LEVEL == 1 ? 10 : 0);
+    constexpr int kHiShift = kShift + kBits;
+    constexpr uint32_t kMask = (1u << kBits) - 1u;
+    for (int v = 0; v < 2; ++v) {
+        if (!t->vcnt[v]) continue;
+        const uint32_t digit = (t->vkey[v] >> kShift) & kMask;
+        if (LEVEL == 0) {
+            atomicAdd(&gh[digit], t->vcnt[v]);
+        } else {
+            for (int g = 0; g < st->n_groups; ++g)
+                if ((t->vkey[v] >> kHiShift) == st->gprefix[g]) atomicAdd(&gh[g * kBins + digit], t->vcnt[v]);
+        }
+    }
+}
+
+// radix select over the task sources; same structure as the segment kernels, but source, length and ranks come from
+// the task table and blocks past the end of a (short) candidate list only take part in the completion count
+template <int LEVEL>
+__global__ void __launch_bounds__(kThreads) qsel_task_kernel(int bps, int64_t chunk, int n_q, double eps, SWorkspace w,
+                                                             int64_t n_tasks, double* __restrict__ quant,
+                                                             double* __restrict__ norm) {
+    constexpr int kBits = (LEVEL == 0) ? 11 : (LEVEL == 1 ? 11 : 10);
+    constexpr int kShift = (LEVEL == 0) ? 21 : (LEVEL == 1 ? 10 : 0);
+    constexpr int kHiShift = kShift + kBits;
+    constexpr uint32_t kMask = (1u << kBits) - 1u;
+    constexpr int kGroups = (LEVEL == 0) ? 1 : 2;
+    __shared__ unsigned sh[kGroups][kBins];
+    const int64_t task = blockIdx.y;
+    const QTask* t = &w.tasks[task];
+    QState* st = &w.state[task];
+    const float* xs = t->src;
+    const int64_t len = t->len;
+    const int n_groups = (LEVEL == 0) ? 1 : st->n_groups;
+    uint32_t gp[kGroups];
+#pragma unroll
+    for (int g = 0; g < kGroups; ++g) gp[g] = (LEVEL == 0) ? 0u : ((g < n_groups) ? st->gprefix[g] : 0xffffffffu);
+
+    unsigned* gh = (LEVEL == 0) ? (w.hist0 + task * kBins) : (w.hist12 + task * 2 * kBins);
+    if ((int64_t)blockIdx.x * chunk < len) {
+        for (int i = threadIdx.x; i < n_groups * kBins; i += kThreads) (&sh[0][0])[i] = 0;
+        __syncthreads();
+        RunCounter rc[kGroups];
+        float fmin = __int_as_float(0xff800000), fmax = __int_as_float(0x7f800000);
+        if (LEVEL > 0) {
+            fmin = __int_as_float(0x7f800000);
+            fmax = __int_as_float(0xff800000);
+#pragma unroll
+            for (int g = 0; g < kGroups; ++g) {
+                if (g < n_groups) {
+                    fmin = fminf(fmin, key_to_f32(gp[g] << kHiShift));
+                    fmax = fmaxf(fmax, key_to_f32((gp[g] << kHiShift) | ((1u << kHiShift) - 1u)));
+                }
+            }
+        }
+        // the block takes chunks blockIdx.x, blockIdx.x + gridDim.x, ...: a short candidate list is spread over all
+        // blocks, a full segment (fallback) is simply more iterations
+        for (int64_t begin = (int64_t)blockIdx.x * chunk; begin < len; begin += (int64_t)gridDim.x * chunk) {
+            const int64_t end = min(begin + chunk, len);
+            block_foreach(xs + begin, end - begin, [&](float v) {
+                if (v >= fmin && v <= fmax) {  // also drops NaN
+                    const uint32_t key = f32_to_key(v);
+                    const uint32_t digit = (key >> kShift) & kMask;
+                    if (LEVEL == 0) {
+                        rc[0].add(sh[0], digit);
+                    } else {
+                        const uint32_t hi = key >> kHiShift;
+#pragma unroll
+                        for (int g = 0; g < kGroups; ++g)
+                            if (hi == gp[g]) rc[g].add(sh[g], digit);
+                    }
+                }
+            });
+        }
+#pragma unroll
+        for (int g = 0; g < kGroups; ++g) rc[g].flush(sh[g]);
+        __syncthreads();
+        for (int i = threadIdx.x; i < n_groups * kBins; i += kThreads) {
+            const unsigned c = (&sh[0][0])[i];
+            if (c) atomicAdd(&gh[i], c);
+        }
+    }
+    if (!last_block_of_segment(&w.counters[LEVEL * n_tasks + task], bps)) return;
+
+    // the serial tail works on shared-memory copies: global round trips only to fetch and to publish
+    __shared__ QState s_st;
+    __shared__ QTask s_t;
+    if (threadIdx.x == 0) {
+        s_t = *t;
+        if (LEVEL == 0) {
+            s_st.n_ranks = 2;
+            s_st.n_valid = s_t.total;
+            s_st.gamma[0] = s_t.gamma;
+            s_st.n_groups = 1;
+            s_st.gprefix[0] = 0;
+            s_st.group[0] = s_st.group[1] = 0;
+            s_st.prefix[0] = s_st.prefix[1] = 0;
+            s_st.krem[0] = s_t.rank[0];
+            s_st.krem[1] = s_t.rank[1];
+        } else {
+            s_st = *st;
+        }
+        add_virtual<LEVEL>(&s_t, &s_st, gh);
+        __threadfence();
+    }
+    __syncthreads();
+    const uint32_t total = s_t.total;
+    if (total > 0) {
+        for (int j = 0; j < 2; ++j) {
+            uint32_t bin, krem;
+            find_bin(gh + s_st.group[j] * kBins, s_st.krem[j], &bin, &krem);
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                s_st.prefix[j] = (s_st.prefix[j] << kBits) | bin;
+                s_st.krem[j] = krem;
+            }
+        }
+    }
+    __syncthreads();
+    if (LEVEL == 1) {
+        for (int i = threadIdx.x; i < 2 * kBins; i += kThreads) gh[i] = 0;  // the same storage serves level 2
+    }
+    if (LEVEL < 2) {
+        if (threadIdx.x == 0) {
+            regroup(&s_st);
+            *st = s_st;
+        }
+        return;
+    }
+    if (threadIdx.x == 0) {
+        double r;
+        if (total == 0) {
+            r = __longlong_as_double(0x7ff8000000000000LL);
+        } else {
+            // numpy _lerp: fp32 difference, fp64 product and sum, switch of anchor at gamma >= 0.5
+            const float a = key_to_f32(s_st.prefix[0]);
+            const float b = key_to_f32(s_st.prefix[1]);
+            const double d = (double)__fsub_rn(b, a);
+            const double g = s_st.gamma[0];
+            r = (g >= 0.5) ? __dsub_rn((double)b, __dmul_rn(d, __dsub_rn(1.0, g))) : __dadd_rn((double)a, __dmul_rn(d, g));
+        }
+        quant[task] = r;
+        if (norm) {  // the task of a segment that finishes second writes {q0, q1 - q0 + eps}
+            __threadfence();
+            const int64_t seg = task / n_q;
+            if (atomicAdd(&w.seg_done[seg], 1u) == (unsigned)(n_q - 1)) {
+                __threadfence();
+                const double lo = __ldcg(&quant[seg * n_q + 0]), hi = __ldcg(&quant[seg * n_q + 1]);
+                norm[seg * 2 + 0] = lo;
+                norm[seg * 2 + 1] = __dadd_rn(__dsub_rn(hi, lo), eps);
+            }
+        }
+    }
+}
+
 inline int stream_grid(int64_t n_items_per_thread_units) {
     int64_t blocks = (n_items_per_thread_units + kThreads - 1) / kThreads;
     const int64_t cap = (int64_t)BE_SM_COUNT * 16;
@@ -579,22 +1073,9 @@ extern "C" int be_meanvar_f32(const float* x, int64_t n_seg, int64_t seg_len, do
     return BE_OK;
 }
 
-extern "C" size_t be_quantile_workspace_bytes(int64_t n_seg, int64_t seg_len) {
-    (void)seg_len;
-    if (n_seg <= 0) return 256;
-    return carve_quantile_ws(nullptr, n_seg).total_bytes;
-}
-
-extern "C" int be_quantile_f32(const float* x, int64_t n_seg, int64_t seg_len, const double* q, int n_q, double eps,
-                               double* quant, double* norm, void* ws, be_stream_t stream) {
-    BE_REQUIRE(x && q && quant && ws, BE_ERR_INVALID_ARG, "be_quantile_f32: null pointer");
-    BE_REQUIRE(n_seg > 0 && seg_len > 0, BE_ERR_INVALID_ARG, "be_quantile_f32: empty input (n_seg=%lld seg_len=%lld)",
-               (long long)n_seg, (long long)seg_len);
-    BE_REQUIRE(n_q >= 1 && 2 * n_q <= kMaxRanks, BE_ERR_INVALID_ARG, "be_quantile_f32: n_q must be 1 or 2, got %d", n_q);
-    BE_REQUIRE(!norm || n_q == 2, BE_ERR_INVALID_ARG, "be_quantile_f32: norm output needs n_q == 2");
-    BE_REQUIRE(seg_len < (int64_t)1 << 31, BE_ERR_TOO_LARGE, "be_quantile_f32: seg_len %lld >= 2^31", (long long)seg_len);
-    BE_REQUIRE(n_seg <= 65535, BE_ERR_TOO_LARGE, "be_quantile_f32: n_seg %lld > 65535", (long long)n_seg);
-    cudaStream_t s = (cudaStream_t)stream;
+// plain three-pass radix select on whole segments (small segments, and the library-resident-scratch entry point)
+static int quantile_radix(const float* x, int64_t n_seg, int64_t seg_len, const double* q, int n_q, double eps,
+                          double* quant, double* norm, void* ws, cudaStream_t s) {
     const SegSplit sp = split_segment(n_seg, seg_len);
     QWorkspace w = carve_quantile_ws(ws, n_seg);
     BE_CUDA(cudaMemsetAsync(ws, 0, w.zero_bytes, s));
@@ -606,6 +1087,72 @@ extern "C" int be_quantile_f32(const float* x, int64_t n_seg, int64_t seg_len, c
     qsel_level12_kernel<2><<<grid, kThreads, 0, s>>>(x, seg_len, sp.bps, sp.chunk, n_q, eps, w, n_seg, quant, norm);
     BE_LAUNCH_CHECK();
     return BE_OK;
+}
+
+// sampled-pivot select: one pass over the data + radix select on ~2 % of it, `per_pass` segments at a time
+static int quantile_sampled(const float* x, int64_t n_seg, int64_t seg_len, const double* q, int n_q, double eps,
+                            double* quant, double* norm, void* ws, cudaStream_t s) {
+    const int64_t per_pass = sample_segments_per_pass(n_seg, seg_len);
+    for (int64_t s0 = 0; s0 < n_seg; s0 += per_pass) {
+        const int64_t ns = (n_seg - s0 < per_pass) ? (n_seg - s0) : per_pass;
+        const int64_t nt = ns * n_q;
+        const SegSplit sp = split_segment(ns, seg_len);
+        const SWorkspace w = carve_sample_ws(ws, ns, n_q, seg_len);
+        const float* xs = x + s0 * seg_len;
+        double* qs = quant + s0 * n_q;
+        double* nr = norm ? norm + s0 * 2 : nullptr;
+        BE_CUDA(cudaMemsetAsync(ws, 0, w.zero_bytes, s));
+        qsel_sample_kernel<<<(unsigned)ns, kSampleThreads, 0, s>>>(xs, seg_len, q, n_q, w);
+        BE_LAUNCH_CHECK();
+        const dim3 grid(sp.bps, (unsigned)ns);
+        if (n_q == 1)
+            qsel_partition_kernel<1><<<grid, kThreads, 0, s>>>(xs, seg_len, sp.bps, sp.chunk, q, w, ns);
+        else
+            qsel_partition_kernel<2><<<grid, kThreads, 0, s>>>(xs, seg_len, sp.bps, sp.chunk, q, w, ns);
+        BE_LAUNCH_CHECK();
+        // selection stage: 2048-element chunks dealt round-robin to a grid of about two CTAs per SM over all tasks
+        const int64_t tchunk = 2048;
+        int tb = (int)((int64_t)BE_SM_COUNT * 2 / nt);
+        if (tb < 1) tb = 1;
+        const int64_t most = (seg_len + tchunk - 1) / tchunk;
+        if (tb > most) tb = (int)most;
+        const dim3 tgrid(tb, (unsigned)nt);
+        qsel_task_kernel<0><<<tgrid, kThreads, 0, s>>>(tb, tchunk, n_q, eps, w, nt, qs, nr);
+        BE_LAUNCH_CHECK();
+        qsel_task_kernel<1><<<tgrid, kThreads, 0, s>>>(tb, tchunk, n_q, eps, w, nt, qs, nr);
+        BE_LAUNCH_CHECK();
+        qsel_task_kernel<2><<<tgrid, kThreads, 0, s>>>(tb, tchunk, n_q, eps, w, nt, qs, nr);
+        BE_LAUNCH_CHECK();
+    }
+    return BE_OK;
+}
+
+extern "C" size_t be_quantile_workspace_bytes(int64_t n_seg, int64_t seg_len) {
+    if (n_seg <= 0) return 256;
+    if (seg_len >= kSampleMinLen)
+        return carve_sample_ws(nullptr, sample_segments_per_pass(n_seg, seg_len), 2, seg_len).total_bytes;
+    return carve_quantile_ws(nullptr, n_seg).total_bytes;
+}
+
+static int quantile_check(const char* who, const float* x, int64_t n_seg, int64_t seg_len, const double* q, int n_q,
+                          const double* quant, const double* norm, const void* ws) {
+    BE_REQUIRE(x && q && quant && ws, BE_ERR_INVALID_ARG, "%s: null pointer", who);
+    BE_REQUIRE(n_seg > 0 && seg_len > 0, BE_ERR_INVALID_ARG, "%s: empty input (n_seg=%lld seg_len=%lld)", who,
+               (long long)n_seg, (long long)seg_len);
+    BE_REQUIRE(n_q >= 1 && 2 * n_q <= kMaxRanks, BE_ERR_INVALID_ARG, "%s: n_q must be 1 or 2, got %d", who, n_q);
+    BE_REQUIRE(!norm || n_q == 2, BE_ERR_INVALID_ARG, "%s: norm output needs n_q == 2", who);
+    BE_REQUIRE(seg_len < (int64_t)1 << 31, BE_ERR_TOO_LARGE, "%s: seg_len %lld >= 2^31", who, (long long)seg_len);
+    BE_REQUIRE(n_seg <= 65535, BE_ERR_TOO_LARGE, "%s: n_seg %lld > 65535", who, (long long)n_seg);
+    return BE_OK;
+}
+
+extern "C" int be_quantile_f32(const float* x, int64_t n_seg, int64_t seg_len, const double* q, int n_q, double eps,
+                               double* quant, double* norm, void* ws, be_stream_t stream) {
+    const int rc = quantile_check("be_quantile_f32", x, n_seg, seg_len, q, n_q, quant, norm, ws);
+    if (rc) return rc;
+    if (seg_len >= kSampleMinLen)
+        return quantile_sampled(x, n_seg, seg_len, q, n_q, eps, quant, norm, ws, (cudaStream_t)stream);
+    return quantile_radix(x, n_seg, seg_len, q, n_q, eps, quant, norm, ws, (cudaStream_t)stream);
 }
 
 // ---- quantiles for callers that must not allocate -------------------------------------------------------------------
@@ -646,9 +1193,12 @@ extern "C" int be_quantile_f32_noalloc(const float* x, int64_t n_seg, int64_t se
         BE_REQUIRE(scratch != nullptr, BE_ERR_CUDA, "be_quantile_f32_noalloc: cudaGetSymbolAddress returned null");
         g_quantile_scratch_addr[dev] = scratch;
     }
-    // be_quantile_f32 zeroes the counters and histograms it needs at the start of every call, so whatever the previous
-    // call left in the shared array is harmless.
-    return be_quantile_f32(x, n_seg, seg_len, q, n_q, eps, quant, norm, scratch, stream);
+    const int rc = quantile_check("be_quantile_f32_noalloc", x, n_seg, seg_len, q, n_q, quant, norm, scratch);
+    if (rc) return rc;
+    // the radix select zeroes the counters and histograms it needs at the start of every call, so whatever the
+    // previous call left in the shared array is harmless (the sampled path of be_quantile_f32 would need candidate
+    // lists proportional to the input and is not used here)
+    return quantile_radix(x, n_seg, seg_len, q, n_q, eps, quant, norm, scratch, (cudaStream_t)stream);
 }
 
 extern "C" int be_normalize_f32(const float* x, float* y, int64_t n_seg, int64_t seg_len, const double* norm, int clip,

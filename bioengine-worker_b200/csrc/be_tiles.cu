@@ -201,13 +201,14 @@ __global__ void __launch_bounds__(kThreads) stitch_crop_kernel(const float* __re
 
 struct Strides {
     int Sz, Sy, Sx;
+    float rSz, rSy, rSx;  // 1.0f / stride, for be_fast_div
 };
 
 // tiles k covering output coordinate p: k*S <= p < k*S + B, 0 <= k < T
-__device__ __forceinline__ void cover(int p, int B, int S, int T, int* lo, int* hi) {
-    *hi = min(p / S, T - 1);
+__device__ __forceinline__ void cover(int p, int B, int S, float rS, int T, int* lo, int* hi) {
+    *hi = min(be_fast_div(p, S, rS), T - 1);
     const int t = p - B + 1;
-    *lo = (t <= 0) ? 0 : (t + S - 1) / S;
+    *lo = (t <= 0) ? 0 : be_fast_div(t + S - 1, S, rS);
 }
 
 __global__ void __launch_bounds__(kThreads) stitch_blend_kernel(const float* __restrict__ tiles, float* __restrict__ out,
@@ -225,18 +226,22 @@ __global__ void __launch_bounds__(kThreads) stitch_blend_kernel(const float* __r
     const int cnt = min(4, (int)d.X - x0);
     // tiles touching this 4-px unit: from the first tile covering x0 to the last one covering its last pixel
     int kx_first, kx_last, tmp;
-    cover(x0, d.Bx, s.Sx, d.Tx, &kx_first, &tmp);
-    cover(x0 + cnt - 1, d.Bx, s.Sx, d.Tx, &tmp, &kx_last);
+    cover(x0, d.Bx, s.Sx, s.rSx, d.Tx, &kx_first, &tmp);
+    cover(x0 + cnt - 1, d.Bx, s.Sx, s.rSx, d.Tx, &tmp, &kx_last);
     int ky_lo, ky_hi;
-    cover(y, d.By, s.Sy, d.Ty, &ky_lo, &ky_hi);  // block-uniform
+    cover(y, d.By, s.Sy, s.rSy, d.Ty, &ky_lo, &ky_hi);  // block-uniform
 
     for (unsigned plane = blockIdx.z; plane < n_planes; plane += gridDim.z) {
-        const int z = plane % (unsigned)d.Z;
-        const unsigned nc = plane / (unsigned)d.Z;
-        const int c = nc % (unsigned)d.C;
-        const int64_t n = nc / (unsigned)d.C;
+        int z = 0, c = 0;
+        int64_t n = 0;
+        if (n_planes > 1) {  // single 2-D image: nothing to decompose
+            z = plane % (unsigned)d.Z;
+            const unsigned nc = plane / (unsigned)d.Z;
+            c = nc % (unsigned)d.C;
+            n = nc / (unsigned)d.C;
+        }
         int kz_lo, kz_hi;
-        cover(z, d.Bz, s.Sz, d.Tz, &kz_lo, &kz_hi);
+        cover(z, d.Bz, s.Sz, s.rSz, d.Tz, &kz_lo, &kz_hi);
 
         double acc[4] = {0.0, 0.0, 0.0, 0.0}, wacc[4] = {0.0, 0.0, 0.0, 0.0};
         // ascending (kz, ky, kx): the order a sequential walk over the reference's tile_coords list adds them
@@ -391,7 +396,8 @@ extern "C" int be_stitch_blend_f32(const float* tiles, float* out, uint8_t* mask
                    (int64_t)(Tx - 1) * Sx < X && (int64_t)Tx * Sx >= X,
                BE_ERR_INVALID_ARG, "be_stitch_blend_f32: tile grid must be ceil(dim/stride) per axis");
     const Dims d{N, C, Z, Y, X, Tz, Ty, Tx, Bz, By, Bx};
-    const Strides st{Sz, Sy, Sx};
+    BE_REQUIRE(Z < (1 << 24) && Y < (1 << 24) && X < (1 << 24), BE_ERR_TOO_LARGE, "be_stitch_blend_f32: axis longer than 2^24");
+    const Strides st{Sz, Sy, Sx, 1.0f / (float)Sz, 1.0f / (float)Sy, 1.0f / (float)Sx};
     const int upr = (int)((X + 3) / 4);
     dim3 grid;
     rc = stitch_grid("be_stitch_blend_f32", d, upr, &grid);

@@ -52,8 +52,10 @@ int be_meanvar_f32(const float* x, int64_t n_seg, int64_t seg_len, double eps, d
                    void* ws, be_stream_t stream);
 
 /* Exact per-segment quantiles, numpy `nanquantile(..., method="linear")` semantics (NaNs dropped, fp64
- * virtual index q*(n-1), numpy's two-sided lerp), by 3-level radix select on the order-preserving uint32
- * key of fp32.  Replaces bioimageio.core SamplePercentilesCalculator / `scale_range`
+ * virtual index q*(n-1), numpy's two-sided lerp).  Segments of >= 2^18 elements: one streaming pass that brackets
+ * each wanted rank between two pivots taken from a sorted 2048-element sample, then an 11/11/10-bit radix select on
+ * the ~2 % of elements inside the bracket (on the whole segment if the bracket missed — the result is exact either
+ * way); smaller segments: the radix select directly, on the order-preserving uint32 key of fp32.  Replaces bioimageio.core SamplePercentilesCalculator / `scale_range`
  * (runtime_deployment.py:17,:278; Appendix A.2/A.3) and `np.percentile(image_np, [1, 99])`
  * (apps/fibsem-mito-analysis/analysis_deployment.py:241).
  *   q        [n_q] fp64 in [0,1], DEVICE pointer, 1 <= n_q <= 2

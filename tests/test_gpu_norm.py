@@ -147,3 +147,76 @@ def test_errors_are_loud(dev):
         K().quantile(x, 1, torch.tensor([0.1, 0.2, 0.3], dtype=torch.float64, device=dev))
     with pytest.raises(ValueError):
         K().quantile(x.cpu(), 1, torch.tensor([0.1], dtype=torch.float64, device=dev))
+
+
+# ---- sampled-pivot path (segments >= 2^18 elements) ----
+
+def _sample_positions(seg_len, seg=0, m=2048):
+    """The positions qsel_sample_kernel reads (csrc/be_norm.cu: hash32 / qsel_sample_kernel), restated in numpy so a test
+    can plant an unrepresentative sample and force the full-segment fallback."""
+    i = np.arange(m, dtype=np.uint64)  # m = kSample
+    x = (i * np.uint64(0x9E3779B9) + np.uint64(seg)) & np.uint64(0xFFFFFFFF)
+    x ^= x >> np.uint64(16)
+    x = (x * np.uint64(0x7FEB352D)) & np.uint64(0xFFFFFFFF)
+    x ^= x >> np.uint64(15)
+    x = (x * np.uint64(0x846CA68B)) & np.uint64(0xFFFFFFFF)
+    x ^= x >> np.uint64(16)
+    stride = np.uint64(seg_len // m)
+    return (i * stride + x % stride).astype(np.int64)
+
+
+@pytest.mark.parametrize("q", [(0.01, 0.998), (0.0, 1.0), (0.5,), (0.25, 0.75), (1e-7, 0.9999999)])
+def test_sampled_quantile_distributions(q, dev, rng):
+    n = (1 << 20) + 12345
+    cases = {
+        "normal": (rng.standard_normal(n) * 100 + 50).astype(np.float32),
+        "uint8 image": rng.integers(0, 256, n).astype(np.float32),                 # 256 distinct values: all ties
+        "half zeros": np.where(rng.random(n) < 0.5, 0.0, rng.random(n)).astype(np.float32),
+        "constant": np.full(n, 3.25, np.float32),
+        "two values": np.where(rng.random(n) < 0.3, -1.0, 2.0).astype(np.float32),
+        "signed zeros": np.where(rng.random(n) < 0.5, -0.0, 0.0).astype(np.float32),
+        "heavy tail": (rng.standard_cauchy(n) * 1e3).astype(np.float32),
+        "sorted": np.sort(rng.standard_normal(n)).astype(np.float32),
+    }
+    for name, x in cases.items():
+        got, _ = _quant(x, q, 1, dev)
+        want = np.nanquantile(x, np.asarray(q, np.float64), method="linear")
+        assert np.array_equal(got[0], want), name
+
+
+def test_sampled_quantile_nans_infs_and_segments(dev, rng):
+    n_seg, seg_len = 5, (1 << 18) + 77
+    x = (rng.standard_normal((n_seg, seg_len)) * 10).astype(np.float32)
+    x[0, ::2] = np.nan                     # half NaN
+    x[1, :] = np.nan                       # all NaN → NaN
+    x[2, :1000] = np.inf
+    x[2, 1000:3000] = -np.inf
+    x[3] = np.round(x[3])                  # ties
+    q = (0.01, 0.99)
+    got, norm = _quant(x, q, n_seg, dev)
+    with warnings.catch_warnings(), np.errstate(all="ignore"):
+        warnings.simplefilter("ignore")
+        want = np.nanquantile(x, np.asarray(q, np.float64), axis=1, method="linear").T
+    assert np.array_equal(got, want, equal_nan=True)
+    ok = ~np.isnan(want[:, 0])
+    assert np.array_equal(norm[ok, 0], want[ok, 0])
+    assert np.array_equal(norm[ok, 1], want[ok, 1] - want[ok, 0] + 1e-6)
+
+
+def test_sampled_quantile_falls_back_when_the_sample_lies(dev, rng):
+    """Plant tiny values exactly where the sampler looks: its brackets then miss the true quantiles completely and the
+    selection must fall back to the whole segment — still exact."""
+    n = 1 << 19
+    x = (rng.random(n) * 1000 + 5000).astype(np.float32)
+    x[_sample_positions(n)] = np.linspace(0.0, 1.0, 2048, dtype=np.float32)
+    for q in ((0.5, 0.9), (0.01, 0.998)):
+        got, _ = _quant(x, q, 1, dev)
+        assert np.array_equal(got[0], np.nanquantile(x, np.asarray(q, np.float64), method="linear"))
+
+
+def test_sampled_quantile_many_segments_one_call(dev, rng):
+    n_seg, seg_len = 24, 1 << 18
+    x = rng.gamma(2.0, 50.0, size=(n_seg, seg_len)).astype(np.float32)
+    got, _ = _quant(x, (0.01, 0.998), n_seg, dev)
+    want = np.nanquantile(x, np.array([0.01, 0.998]), axis=1, method="linear").T
+    assert np.array_equal(got, want)
