@@ -190,7 +190,8 @@ def stitch_blend(tiles: torch.Tensor, sample_shape: Sequence[int], axes: Sequenc
     return out, mask
 
 
-def ccl(mask: torch.Tensor, connectivity: Optional[int] = None, ws: Workspace = _default_ws):
+def ccl(mask: torch.Tensor, connectivity: Optional[int] = None, ws: Workspace = _default_ws,
+        out: Optional[torch.Tensor] = None, n_out: Optional[torch.Tensor] = None):
     """mask (N,[Z,]Y,X) uint8 → (labels int32 same shape, n_labels int32 [N] on device)."""
     _check(mask, torch.uint8, "mask")
     if mask.dim() == 3:
@@ -202,8 +203,10 @@ def ccl(mask: torch.Tensor, connectivity: Optional[int] = None, ws: Workspace = 
         raise ValueError(f"expected (N,Y,X) or (N,Z,Y,X), got {tuple(mask.shape)}")
     ndim = 3 if Z > 1 else 2
     conn = ndim if connectivity is None else int(connectivity)
-    labels = torch.empty(mask.shape, dtype=torch.int32, device=mask.device)
-    n_labels = torch.empty((N,), dtype=torch.int32, device=mask.device)
+    labels = torch.empty(mask.shape, dtype=torch.int32, device=mask.device) if out is None else _check(out, torch.int32, "out")
+    n_labels = torch.empty((N,), dtype=torch.int32, device=mask.device) if n_out is None else _check(n_out, torch.int32, "n_out")
+    if labels.numel() != mask.numel() or n_labels.numel() != N:
+        raise ValueError("output buffers do not match the mask")
     w = ws.get(_lib.query("be_ccl_workspace_bytes", N, Z, Y, X), mask.device)
     _lib.call("be_ccl_u8_i32", mask.data_ptr(), labels.data_ptr(), N, Z, Y, X, conn, n_labels.data_ptr(),
               w.data_ptr(), _stream())

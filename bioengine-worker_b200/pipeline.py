@@ -98,6 +98,8 @@ class TiledPipeline:
                 out: Optional[torch.Tensor] = None) -> torch.Tensor:
         fb = max(1, int(self.spec.forward_batch))
         first = model(tiles[:fb])
+        if first.shape[0] == tiles.shape[0] and out is None:
+            return first  # one chunk covered everything
         if out is None:
             out = torch.empty((tiles.shape[0],) + tuple(first.shape[1:]), dtype=torch.float32, device=tiles.device)
         out[:fb] = first
@@ -106,7 +108,8 @@ class TiledPipeline:
         return out
 
     # ---- stage 2: stitch (+ sigmoid + binarize) + labels ----
-    def stitch_and_label(self, logits: torch.Tensor) -> Dict[str, torch.Tensor]:
+    def stitch_and_label(self, logits: torch.Tensor, labels_out: Optional[torch.Tensor] = None,
+                         n_out: Optional[torch.Tensor] = None) -> Dict[str, torch.Tensor]:
         sp = self.spec
         out_shape = (self.shape[0], logits.shape[1]) + self.shape[2:]
         epi = _lib.BE_EPI_SIGMOID if sp.sigmoid else _lib.BE_EPI_NONE
@@ -121,7 +124,7 @@ class TiledPipeline:
             res["prob"] = prob
         if sp.label:
             m = mask.reshape((out_shape[0] * out_shape[1],) + out_shape[2:])
-            labels, n = K.ccl(m, sp.connectivity, ws=self.ws)
+            labels, n = K.ccl(m, sp.connectivity, ws=self.ws, out=labels_out, n_out=n_out)
             res["labels"] = labels.reshape(out_shape)
             res["n_labels"] = n
         return res
@@ -135,3 +138,54 @@ class TiledPipeline:
         tiles = self.preprocess_and_tile(x)
         logits = self.forward(model, tiles)
         return self.stitch_and_label(logits)
+
+    def run_stream(self, host_images: Sequence[torch.Tensor], model: Callable[[torch.Tensor], torch.Tensor],
+                   host_labels: Sequence[torch.Tensor], host_counts: Sequence[torch.Tensor]):
+        """Throughput mode for a stream of same-shaped images (microscope frames, a screening shard).
+
+        host_images[i] (pinned CPU fp32, sample shape) → host_labels[i] (pinned int32, sample shape), host_counts[i]
+        (pinned int32 [N]).  Three streams: the upload of image i+1 and the download of labels i-1 overlap the kernels
+        of image i; device buffers are double-buffered, so the only requirement on the caller is that host_labels[i]
+        and host_labels[i+2] may alias but host_labels[i] and host_labels[i+1] may not.  Returns after everything has
+        been enqueued; synchronise (or wait on the returned event) before reading the host buffers.
+        """
+        dev = self.device
+        if not hasattr(self, "_streams"):
+            self._streams = (torch.cuda.Stream(dev), torch.cuda.Stream(dev), torch.cuda.Stream(dev))
+            self._xbuf = [torch.empty(self.shape, dtype=torch.float32, device=dev) for _ in range(2)]
+            lshape = (self.shape[0], 1) + self.shape[2:]
+            self._lbuf = [torch.empty(lshape, dtype=torch.int32, device=dev) for _ in range(2)]
+            self._nbuf = [torch.empty((self.shape[0],), dtype=torch.int32, device=dev) for _ in range(2)]
+        s_in, s_run, s_out = self._streams
+        start = torch.cuda.current_stream(dev)
+        for s in (s_in, s_run, s_out):
+            s.wait_stream(start)
+        ev_in = [torch.cuda.Event() for _ in range(2)]
+        ev_run = [torch.cuda.Event() for _ in range(2)]
+        ev_out = [torch.cuda.Event() for _ in range(2)]
+        for i, img in enumerate(host_images):
+            b = i & 1
+            with torch.cuda.stream(s_in):
+                if i >= 2:
+                    s_in.wait_event(ev_run[b])      # the kernels that read this input buffer two images ago
+                self._xbuf[b].copy_(img, non_blocking=True)
+                ev_in[b].record(s_in)
+            with torch.cuda.stream(s_run):
+                s_run.wait_event(ev_in[b])
+                if i >= 2:
+                    s_run.wait_event(ev_out[b])     # the download that read this label buffer two images ago
+                tiles = self.preprocess_and_tile(self._xbuf[b])
+                logits = self.forward(model, tiles)
+                self.stitch_and_label(logits, labels_out=self._lbuf[b], n_out=self._nbuf[b])
+                ev_run[b].record(s_run)
+            with torch.cuda.stream(s_out):
+                s_out.wait_event(ev_run[b])
+                host_labels[i].copy_(self._lbuf[b], non_blocking=True)
+                host_counts[i].copy_(self._nbuf[b], non_blocking=True)
+                ev_out[b].record(s_out)
+        done = torch.cuda.Event(enable_timing=True)
+        start.wait_stream(s_out)
+        start.wait_stream(s_run)
+        start.wait_stream(s_in)
+        done.record(start)
+        return done

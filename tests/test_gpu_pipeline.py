@@ -100,3 +100,24 @@ def test_c3_shape_path_3d(dev):
     prob, mask, labels = P.c2_post(logits.cpu().numpy(), D, B, ov, 3)
     assert np.array_equal(res["mask"].cpu().numpy()[0, 0], mask)
     assert np.array_equal(res["labels"].cpu().numpy()[0, 0], labels)
+
+
+def test_run_stream_equals_run(dev):
+    """Throughput mode (three streams, double buffering) returns exactly what the one-image call returns."""
+    shape = (1, 1, 200, 260)
+    imgs = [O.synthetic_image(shape, 40, seed=20 + i) for i in range(5)]
+    pipe, model = make(shape, dict(block=(64, 64), halo=(8, 8), convention="fibsem", overlap=(16, 16),
+                                   preprocess="scale_range", connectivity=2), dev)
+    from bioengine_worker_b200 import models
+
+    models.calibrate_head(model, pipe.preprocess_and_tile(torch.from_numpy(imgs[0]).to(dev))[::3].contiguous())
+    want = [pipe.run(im, model) for im in imgs]
+    want = [(w["labels"].cpu().numpy().copy(), int(w["n_labels"].item())) for w in want]
+    host_in = [torch.from_numpy(im).pin_memory() for im in imgs]
+    host_l = [torch.empty((1, 1) + shape[2:], dtype=torch.int32).pin_memory() for _ in imgs]
+    host_n = [torch.empty((1,), dtype=torch.int32).pin_memory() for _ in imgs]
+    pipe.run_stream(host_in, model, host_l, host_n).synchronize()
+    torch.cuda.synchronize()
+    for (wl, wn), gl, gn in zip(want, host_l, host_n):
+        assert wn == int(gn.item()) > 0
+        assert np.array_equal(wl, gl.numpy())
