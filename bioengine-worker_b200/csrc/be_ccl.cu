@@ -12,8 +12,9 @@
 //   2. ccl_edge_kernel      (2-D) one warp per tile links its top and left edge to the neighbouring tiles from the edge
 //                           masks alone, again one union per touching run pair;  ccl_face_kernel (3-D) does it per face
 //                           voxel.  Unions are atomicMin on the global parent array with path halving.
-//   3. ccl_count / scan / assign   surviving roots are numbered in raster order from the root bitmap (2 MB instead of
-//                           a second pass over all parents); a root's entry becomes -(id) - 1.
+//   3. ccl_number_kernel    surviving roots are numbered in raster order from the root bitmap (2 MB instead of a
+//                           second pass over all parents) with a single-pass decoupled look-back scan; a root's entry
+//                           becomes -(id) - 1.
 //   4. ccl_resolve_kernel   every pixel walks to its root (<= 2-3 hops) and writes id; background decodes to 0.
 #include "be_common.cuh"
 
@@ -392,92 +393,89 @@ __global__ void __launch_bounds__(kThreads) ccl_face_kernel(const uint8_t* __res
     }
 }
 
-// ---- raster-order numbering of the surviving roots, driven by the root bitmap ----
+// ---- raster-order numbering of the surviving roots, driven by the root bitmap: one pass ----
+//
+// Every thread takes one 64-pixel bitmap word.  Tile roots that are still their own parent after the border unions
+// are the components.  The running count across blocks is a decoupled look-back scan: blocks take tickets in launch order,
+// publish their aggregate, and add up the predecessors' values until they meet a published inclusive prefix.  A
+// numbered root's entry becomes -(id) - 1.
+constexpr unsigned long long kFlagAggregate = 1ull << 62, kFlagPrefix = 2ull << 62, kFlagMask = 3ull << 62;
 
-__global__ void __launch_bounds__(kThreads) ccl_count_kernel(const int32_t* __restrict__ L, u64* __restrict__ rootbits,
-                                                             int64_t vol, int64_t X, int wpr, int64_t words_per_image,
-                                                             int blocks_per_image, int32_t* __restrict__ block_count) {
-    const int64_t w = (int64_t)blockIdx.x * kWordsPerBlock + threadIdx.x;
-    const int32_t* Li = L + (int64_t)blockIdx.y * vol;
-    int c = 0;
+__global__ void __launch_bounds__(kThreads) ccl_number_kernel(int32_t* __restrict__ L, const u64* __restrict__ rootbits,
+                                                              int64_t vol, int64_t X, int wpr, int64_t words_per_image,
+                                                              int blocks_per_image, unsigned* __restrict__ tickets,
+                                                              unsigned long long* __restrict__ block_state,
+                                                              int32_t* __restrict__ n_labels) {
+    __shared__ int s_warp[kThreads / 32];
+    __shared__ unsigned s_ticket;
+    __shared__ long long s_excl;
+    const int img = blockIdx.y;
+    if (threadIdx.x == 0) s_ticket = atomicAdd(&tickets[img], 1u);
+    __syncthreads();
+    const int blk = (int)s_ticket;
+    int32_t* Li = L + (int64_t)img * vol;
+    volatile int32_t* Lv = Li;
+    const int64_t w = (int64_t)blk * kWordsPerBlock + threadIdx.x;
+    u64 keep = 0;
+    int64_t base = 0;
     if (w < words_per_image) {
-        u64* word = rootbits + (int64_t)blockIdx.y * words_per_image + w;
-        u64 bits = *word, keep = 0;
-        const int64_t base = (w / wpr) * X + (w % wpr) * kTX;
+        u64 bits = rootbits[(int64_t)img * words_per_image + w];
+        base = (w / wpr) * X + (w % wpr) * kTX;
         while (bits) {
             const int b = __ffsll((long long)bits) - 1;
             bits &= bits - 1;
             const int32_t p = (int32_t)(base + b);
-            if (Li[p] == p) keep |= 1ull << b;  // still a root after the border unions
+            if (Lv[p] == p) keep |= 1ull << b;  // still a root after the border unions
         }
-        *word = keep;
-        c = __popcll(keep);
     }
-    c = __reduce_add_sync(0xffffffffu, c);
-    __shared__ int s[kThreads / 32];
-    if ((threadIdx.x & 31) == 0) s[threadIdx.x >> 5] = c;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        int t = 0;
-        for (int i = 0; i < kThreads / 32; ++i) t += s[i];
-        block_count[(int64_t)blockIdx.y * blocks_per_image + blockIdx.x] = t;
-    }
-}
-
-// one block per image: in-place exclusive scan of its block counts, total -> n_labels
-__global__ void __launch_bounds__(1024) ccl_scan_kernel(int32_t* __restrict__ block_count, int blocks_per_image,
-                                                        int32_t* __restrict__ n_labels) {
-    __shared__ int s_warp[32];
-    __shared__ int s_carry;
-    int32_t* bc = block_count + (int64_t)blockIdx.x * blocks_per_image;
-    if (threadIdx.x == 0) s_carry = 0;
-    __syncthreads();
-    for (int base = 0; base < blocks_per_image; base += 1024) {
-        const int i = base + threadIdx.x;
-        const int v = (i < blocks_per_image) ? bc[i] : 0;
-        int incl = v;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const int t = __shfl_up_sync(0xffffffffu, incl, o);
-            if ((threadIdx.x & 31) >= o) incl += t;
-        }
-        if ((threadIdx.x & 31) == 31) s_warp[threadIdx.x >> 5] = incl;
-        __syncthreads();
-        int wbase = 0;
-        for (int w = 0; w < (int)(threadIdx.x >> 5); ++w) wbase += s_warp[w];
-        const int carry = s_carry;
-        if (i < blocks_per_image) bc[i] = carry + wbase + incl - v;
-        __syncthreads();
-        if (threadIdx.x == 1023) s_carry = carry + wbase + incl;
-        __syncthreads();
-    }
-    if (threadIdx.x == 0) n_labels[blockIdx.x] = s_carry;
-}
-
-__global__ void __launch_bounds__(kThreads) ccl_assign_kernel(int32_t* __restrict__ L, const u64* __restrict__ rootbits,
-                                                              int64_t vol, int64_t X, int wpr, int64_t words_per_image,
-                                                              int blocks_per_image,
-                                                              const int32_t* __restrict__ block_offset) {
-    const int64_t w = (int64_t)blockIdx.x * kWordsPerBlock + threadIdx.x;
-    int32_t* Li = L + (int64_t)blockIdx.y * vol;
-    u64 bits = (w < words_per_image) ? rootbits[(int64_t)blockIdx.y * words_per_image + w] : 0ull;
-    const int c = __popcll(bits);
+    const int c = __popcll(keep);
     int incl = c;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
         const int t = __shfl_up_sync(0xffffffffu, incl, o);
         if ((threadIdx.x & 31) >= o) incl += t;
     }
-    __shared__ int s_warp[kThreads / 32];
     if ((threadIdx.x & 31) == 31) s_warp[threadIdx.x >> 5] = incl;
     __syncthreads();
-    int id = block_offset[(int64_t)blockIdx.y * blocks_per_image + blockIdx.x] + incl - c;
-    for (int i = 0; i < (int)(threadIdx.x >> 5); ++i) id += s_warp[i];
-    const int64_t base = (w / wpr) * X + (w % wpr) * kTX;
-    while (bits) {
-        const int b = __ffsll((long long)bits) - 1;
-        bits &= bits - 1;
-        Li[base + b] = -(++id) - 1;
+    int before = incl - c, total = 0;
+    for (int i = 0; i < kThreads / 32; ++i) {
+        if (i < (int)(threadIdx.x >> 5)) before += s_warp[i];
+        total += s_warp[i];
+    }
+    unsigned long long* state = block_state + (int64_t)img * blocks_per_image;
+    if (threadIdx.x < 32) {
+        // warp-wide look-back: 32 predecessors per step, nearest first (lane 0 = block blk-1)
+        const int lane = threadIdx.x;
+        if (lane == 0 && blk > 0) atomicExch(&state[blk], kFlagAggregate | (unsigned long long)total);
+        long long excl = 0;
+        for (int end = blk - 1; end >= 0; end -= 32) {
+            const int j = end - lane;
+            unsigned long long sj = kFlagPrefix;  // lanes before block 0 contribute a zero prefix
+            if (j >= 0) {
+                do {
+                    sj = atomicAdd(&state[j], 0ull);
+                } while ((sj & kFlagMask) == 0);
+            }
+            const unsigned has_prefix = __ballot_sync(0xffffffffu, (sj & kFlagMask) == kFlagPrefix);
+            const int stop = __ffs(has_prefix) - 1;  // nearest predecessor with an inclusive prefix (always >= 0 at block 0)
+            long long v = (stop < 0 || lane <= stop) ? (long long)(sj & ~kFlagMask) : 0;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            excl += v;
+            if (stop >= 0) break;
+        }
+        if (lane == 0) {
+            atomicExch(&state[blk], kFlagPrefix | (unsigned long long)(excl + total));
+            s_excl = excl;
+            if (blk == blocks_per_image - 1) n_labels[img] = (int32_t)(excl + total);
+        }
+    }
+    __syncthreads();
+    int id = (int)s_excl + before;
+    while (keep) {
+        const int b = __ffsll((long long)keep) - 1;
+        keep &= keep - 1;
+        Lv[base + b] = -(++id) - 1;
     }
 }
 
@@ -493,11 +491,12 @@ __global__ void __launch_bounds__(kThreads) ccl_resolve_kernel(const int32_t* __
     const int64_t i4 = ((int64_t)blockIdx.x * kThreads + threadIdx.x) * 4;
     if (i4 >= vol) return;
     if (i4 + 4 <= vol && (((uintptr_t)(Li + i4) | (uintptr_t)(oi + i4)) & 15) == 0) {
-        int4 v = *reinterpret_cast<const int4*>(Li + i4);
-        v.x = resolve_one(Li, v.x);
-        v.y = resolve_one(Li, v.y);
-        v.z = resolve_one(Li, v.z);
-        v.w = resolve_one(Li, v.w);
+        const int4 p = *reinterpret_cast<const int4*>(Li + i4);
+        int4 v;  // neighbouring pixels usually share their parent: look it up once
+        v.x = resolve_one(Li, p.x);
+        v.y = (p.y == p.x) ? v.x : resolve_one(Li, p.y);
+        v.z = (p.z == p.y) ? v.y : resolve_one(Li, p.z);
+        v.w = (p.w == p.z) ? v.z : resolve_one(Li, p.w);
         *reinterpret_cast<int4*>(oi + i4) = v;
     } else {
         for (int64_t i = i4; i < min(i4 + 4, vol); ++i) oi[i] = resolve_one(Li, Li[i]);
@@ -508,7 +507,9 @@ struct CclWorkspace {
     int32_t* L;
     u64* rootbits;
     TileEdges* edges;
-    int32_t* block_count;
+    unsigned* tickets;                 // [N]
+    unsigned long long* block_state;   // [N][blocks_per_image]
+    size_t scan_bytes;                 // tickets + block_state: zeroed by every call
     int64_t words_per_image;
     int blocks_per_image;
     size_t total_bytes;
@@ -530,8 +531,12 @@ CclWorkspace carve_ccl_ws(void* ws, int64_t N, int64_t Z, int64_t Y, int64_t X) 
     off += be_align_up(sizeof(u64) * N * w.words_per_image, 256);
     w.edges = (TileEdges*)(p + off);
     off += be_align_up(sizeof(TileEdges) * N * tiles_x * tiles_y * tiles_z, 256);
-    w.block_count = (int32_t*)(p + off);
-    off += be_align_up(sizeof(int32_t) * N * w.blocks_per_image, 256);
+    w.tickets = (unsigned*)(p + off);
+    const size_t scan_begin = off;
+    off += be_align_up(sizeof(unsigned) * N, 256);
+    w.block_state = (unsigned long long*)(p + off);
+    off += be_align_up(sizeof(unsigned long long) * N * w.blocks_per_image, 256);
+    w.scan_bytes = off - scan_begin;
     w.total_bytes = off;
     return w;
 }
@@ -585,15 +590,9 @@ extern "C" int be_ccl_u8_i32(const uint8_t* mask, int32_t* labels, int64_t N, in
         ccl_face_kernel<<<dim3((unsigned)((vol + kThreads - 1) / kThreads), (unsigned)N), kThreads, 0, s>>>(mask, w.L, g);
         BE_LAUNCH_CHECK();
     }
-    ccl_count_kernel<<<dim3(w.blocks_per_image, (unsigned)N), kThreads, 0, s>>>(w.L, w.rootbits, vol, X, g.tiles_x,
-                                                                               w.words_per_image, w.blocks_per_image,
-                                                                               w.block_count);
-    BE_LAUNCH_CHECK();
-    ccl_scan_kernel<<<(unsigned)N, 1024, 0, s>>>(w.block_count, w.blocks_per_image, n_labels);
-    BE_LAUNCH_CHECK();
-    ccl_assign_kernel<<<dim3(w.blocks_per_image, (unsigned)N), kThreads, 0, s>>>(w.L, w.rootbits, vol, X, g.tiles_x,
-                                                                                w.words_per_image, w.blocks_per_image,
-                                                                                w.block_count);
+    BE_CUDA(cudaMemsetAsync(w.tickets, 0, w.scan_bytes, s));
+    ccl_number_kernel<<<dim3(w.blocks_per_image, (unsigned)N), kThreads, 0, s>>>(
+        w.L, w.rootbits, vol, X, g.tiles_x, w.words_per_image, w.blocks_per_image, w.tickets, w.block_state, n_labels);
     BE_LAUNCH_CHECK();
     ccl_resolve_kernel<<<dim3((unsigned)((vol + kThreads * 4 - 1) / (kThreads * 4)), (unsigned)N), kThreads, 0, s>>>(
         w.L, labels, vol);
