@@ -10,8 +10,8 @@
 //                           background; tile roots are also flagged in a 1-bit-per-pixel bitmap and the tile's four
 //                           edge masks are kept for step 2.
 //   2. ccl_edge_kernel      (2-D) one warp per tile links its top and left edge to the neighbouring tiles from the edge
-//                           masks alone, again one union per touching run pair;  ccl_face_kernel (3-D) does it per face
-//                           voxel.  Unions are atomicMin on the global parent array with path halving.
+//                           masks alone, again one union per touching run pair;  ccl_face3d_kernel (3-D) does the same
+//                           per 64-voxel row word of the bit-packed mask.  Unions are atomicMin on the global parent array with path halving.
 //   3. ccl_number_kernel    surviving roots are numbered in raster order from the root bitmap (2 MB instead of a
 //                           second pass over all parents) with a single-pass decoupled look-back scan; a root's entry
 //                           becomes -(id) - 1.
@@ -116,8 +116,8 @@ __device__ __forceinline__ void link_run(unsigned* parent, unsigned id, int x, i
 }
 
 __global__ void __launch_bounds__(kThreads) ccl_tile_kernel(const uint8_t* __restrict__ mask, int32_t* __restrict__ L,
-                                                            u64* __restrict__ rootbits, TileEdges* __restrict__ edges,
-                                                            Geom g) {
+                                                            u64* __restrict__ rootbits, u64* __restrict__ bitvol,
+                                                            TileEdges* __restrict__ edges, Geom g) {
     __shared__ u64 rmask[kRows];
     __shared__ u64 rstart[kRows];
     __shared__ __align__(16) unsigned parent[kMaxRuns];   // union-find over run ids (row * 32 + index in row)
@@ -271,7 +271,11 @@ __global__ void __launch_bounds__(kThreads) ccl_tile_kernel(const uint8_t* __res
         if (lane < 8) {
             const int r = warp * 8 + lane;
             const int64_t z = z0 + (r >> g.ty_log2), y = y0 + (r & ty_mask);
-            if (z < g.Z && y < g.Y) rootbits[((int64_t)img * g.Z * g.Y + z * g.Y + y) * wpr + tx] = rroot[r];
+            if (z < g.Z && y < g.Y) {
+                const int64_t wi = ((int64_t)img * g.Z * g.Y + z * g.Y + y) * wpr + tx;
+                rootbits[wi] = rroot[r];
+                if (bitvol) bitvol[wi] = rmask[r];  // the mask, 1 bit per voxel, for the 3-D face links
+            }
         }
     }
     if (warp == 0 && edges) {
@@ -352,43 +356,63 @@ __global__ void __launch_bounds__(kThreads) ccl_edge_kernel(int32_t* __restrict_
     }
 }
 
-// 3-D: one thread per voxel; only voxels on a tile face do any memory access.
-__global__ void __launch_bounds__(kThreads) ccl_face_kernel(const uint8_t* __restrict__ mask, int32_t* __restrict__ L,
-                                                            Geom g) {
-    const int64_t vol = g.Z * g.Y * g.X;
-    const int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x;
-    if (i >= vol) return;
-    const int x = (int)(i % g.X);
-    const int64_t t = i / g.X;
-    const int y = (int)(t % g.Y);
-    const int z = (int)(t / g.Y);
+// 3-D: links across tile faces from the packed mask (1 bit per voxel, one 64-bit word per row segment).  One thread
+// per word: for each raster-order predecessor row it applies the same one-union-per-touching-run-pair bit rules as the
+// tile kernel, but only where the two rows sit in different tiles; links through the x faces are the single bit pairs
+// 63|0 between neighbouring words.
+__device__ __forceinline__ void link_words(int32_t* Li, u64 m, u64 u, int64_t pm, int64_t pu, bool diag) {
+    if (!u) return;
+    const LinkMasks k = link_masks(m, u, diag);
+    u64 any = k.c | k.l | k.r;
+    while (any) {
+        const int i = __ffsll((long long)any) - 1;
+        const u64 bit = 1ull << i;
+        any &= any - 1;
+        if (k.c & bit) gl_unite(Li, (int32_t)(pm + i), (int32_t)(pu + i));
+        if (k.l & bit) gl_unite(Li, (int32_t)(pm + i), (int32_t)(pu + i - 1));
+        if (k.r & bit) gl_unite(Li, (int32_t)(pm + i), (int32_t)(pu + i + 1));
+    }
+}
+
+__global__ void __launch_bounds__(kThreads) ccl_face3d_kernel(int32_t* __restrict__ L, const u64* __restrict__ bitvol,
+                                                              Geom g, int64_t words_per_image) {
+    const int64_t w = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+    if (w >= words_per_image) return;
+    const int wpr = g.tiles_x;
+    const u64* B = bitvol + (int64_t)blockIdx.y * words_per_image;
+    const u64 m = B[w];
+    if (!m) return;
+    int32_t* Li = L + (int64_t)blockIdx.y * g.Z * g.Y * g.X;
+    const int tx = (int)(w % wpr);
+    const int64_t row = w / wpr;
+    const int y = (int)(row % g.Y), z = (int)(row / g.Y);
     const int TY = 1 << g.ty_log2, TZ = kRows >> g.ty_log2;
-    const int lx = x & (kTX - 1), ly = y & (TY - 1), lz = z & (TZ - 1);
-    const bool f_xlo = lx == 0 && x > 0, f_xhi = lx == kTX - 1 && x + 1 < g.X;
-    const bool f_ylo = ly == 0 && y > 0, f_yhi = ly == TY - 1 && y + 1 < g.Y;
-    const bool f_zlo = lz == 0 && z > 0;
-    if (!(f_xlo | f_xhi | f_ylo | f_yhi | f_zlo)) return;
-    const uint8_t* im = mask + (int64_t)blockIdx.y * vol;
-    int32_t* Li = L + (int64_t)blockIdx.y * vol;
-    if (!im[i]) return;
-    // the 13 raster-order predecessors
-    for (int dz = -1; dz <= 0; ++dz) {
-        if (dz < 0 && z == 0) continue;
-        for (int dy = -1; dy <= 1; ++dy) {
-            if (dz == 0 && dy > 0) break;
-            const int qy = y + dy;
-            if (qy < 0 || qy >= g.Y) continue;
-            for (int dx = -1; dx <= 1; ++dx) {
-                if (dz == 0 && dy == 0 && dx >= 0) break;
-                const int qx = x + dx;
-                if (qx < 0 || qx >= g.X) continue;
-                if ((dz != 0) + (dy != 0) + (dx != 0) > g.conn) continue;
-                const bool crosses = (dx < 0 && lx == 0) || (dx > 0 && lx == kTX - 1) || (dy < 0 && ly == 0) ||
-                                     (dy > 0 && ly == TY - 1) || (dz < 0 && lz == 0);
-                if (!crosses) continue;
-                const int64_t q = ((int64_t)(z + dz) * g.Y + qy) * g.X + qx;
-                if (im[q]) gl_unite(Li, (int32_t)i, (int32_t)q);
-            }
+    const int ly = y & (TY - 1), lz = z & (TZ - 1);
+    const int64_t x0 = (int64_t)tx * kTX;
+    const int64_t pm = ((int64_t)z * g.Y + y) * g.X + x0;
+    // same row, x face
+    if (tx > 0 && (m & 1ull) && (B[w - 1] >> 63)) gl_unite(Li, (int32_t)pm, (int32_t)(pm - 1));
+    // predecessor rows (dz, dy): (0,-1) (-1,-1) (-1,0) (-1,+1)
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int dz = (k == 0) ? 0 : -1, dy = (k == 0 || k == 1) ? -1 : (k == 2 ? 0 : 1);
+        const int steps = (dz != 0) + (dy != 0);
+        if (steps > g.conn) continue;
+        const int zz = z + dz, yy = y + dy;
+        if (zz < 0 || yy < 0 || yy >= g.Y) continue;
+        const bool diag = steps + 1 <= g.conn;
+        const bool other_tile = (dz < 0 && lz == 0) || (dy < 0 && ly == 0) || (dy > 0 && ly == TY - 1);
+        if (!other_tile && !diag) continue;
+        const int64_t wu = ((int64_t)zz * g.Y + yy) * wpr + tx;
+        const int64_t pu = ((int64_t)zz * g.Y + yy) * g.X + x0;
+        const u64 u = B[wu];
+        if (other_tile) link_words(Li, m, u, pm, pu, diag);
+        if (diag) {
+            // corner bits through the x faces; redundant when the straight neighbour in row u is set (it is linked to
+            // this row by the straight rule and to its x neighbour by the same-row rule)
+            if (tx > 0 && (m & 1ull) && !(u & 1ull) && (B[wu - 1] >> 63)) gl_unite(Li, (int32_t)pm, (int32_t)(pu - 1));
+            if (tx + 1 < wpr && (m >> 63) && !(u >> 63) && (B[wu + 1] & 1ull))
+                gl_unite(Li, (int32_t)(pm + 63), (int32_t)(pu + 64));
         }
     }
 }
@@ -506,6 +530,7 @@ __global__ void __launch_bounds__(kThreads) ccl_resolve_kernel(const int32_t* __
 struct CclWorkspace {
     int32_t* L;
     u64* rootbits;
+    u64* bitvol;        // 3-D only (aliases nothing; 2-D leaves it unused)
     TileEdges* edges;
     unsigned* tickets;                 // [N]
     unsigned long long* block_state;   // [N][blocks_per_image]
@@ -529,6 +554,8 @@ CclWorkspace carve_ccl_ws(void* ws, int64_t N, int64_t Z, int64_t Y, int64_t X) 
     off += be_align_up(sizeof(int32_t) * N * vol, 256);
     w.rootbits = (u64*)(p + off);
     off += be_align_up(sizeof(u64) * N * w.words_per_image, 256);
+    w.bitvol = (u64*)(p + off);
+    if (ndim == 3) off += be_align_up(sizeof(u64) * N * w.words_per_image, 256);
     w.edges = (TileEdges*)(p + off);
     off += be_align_up(sizeof(TileEdges) * N * tiles_x * tiles_y * tiles_z, 256);
     w.tickets = (unsigned*)(p + off);
@@ -578,7 +605,7 @@ extern "C" int be_ccl_u8_i32(const uint8_t* mask, int32_t* labels, int64_t N, in
                "be_ccl_u8_i32: tile grid (%d, %d, %lld) exceeds the launch limits", g.tiles_x, g.tiles_y,
                (long long)g.tiles_z * N);
     ccl_tile_kernel<<<dim3((unsigned)g.tiles_x, (unsigned)g.tiles_y, (unsigned)(g.tiles_z * N)), kThreads, 0, s>>>(
-        mask, w.L, w.rootbits, ndim == 2 ? w.edges : nullptr, g);
+        mask, w.L, w.rootbits, ndim == 3 ? w.bitvol : nullptr, ndim == 2 ? w.edges : nullptr, g);
     BE_LAUNCH_CHECK();
     if (ndim == 2) {
         if (n_tiles > 1) {
@@ -587,7 +614,8 @@ extern "C" int be_ccl_u8_i32(const uint8_t* mask, int32_t* labels, int64_t N, in
             BE_LAUNCH_CHECK();
         }
     } else {
-        ccl_face_kernel<<<dim3((unsigned)((vol + kThreads - 1) / kThreads), (unsigned)N), kThreads, 0, s>>>(mask, w.L, g);
+        ccl_face3d_kernel<<<dim3((unsigned)((w.words_per_image + kThreads - 1) / kThreads), (unsigned)N), kThreads, 0, s>>>(
+            w.L, w.bitvol, g, w.words_per_image);
         BE_LAUNCH_CHECK();
     }
     BE_CUDA(cudaMemsetAsync(w.tickets, 0, w.scan_bytes, s));

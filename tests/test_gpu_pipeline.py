@@ -121,3 +121,35 @@ def test_run_stream_equals_run(dev):
     for (wl, wn), gl, gn in zip(want, host_l, host_n):
         assert wn == int(gn.item()) > 0
         assert np.array_equal(wl, gl.numpy())
+
+
+def test_c3_full_size_properties(dev):
+    """BASELINE config 3 at full size (512^3, 128^3 tiles, 16-voxel halo → overlap 32, 216 tiles): size-independent
+    properties instead of an oracle run — blending tiles cut from one volume returns that volume, the crop stitch of the
+    bioimageio blocks is the identity, and 26-connected labelling is idempotent and agrees with the oracle on a slab."""
+    from bioengine_worker_b200 import geometry as G
+    from bioengine_worker_b200 import kernels as K
+
+    S, B, halo = 512, 128, 16
+    g = torch.Generator(device=dev).manual_seed(3)
+    x = torch.rand((1, 1, S, S, S), device=dev, generator=g)
+    fax = [K.DeviceAxis(G.fibsem_axis(S, B, 2 * halo), dev) for _ in range(3)]
+    tiles = K.tile_gather(x, fax)
+    assert tuple(tiles.shape) == (216, 1, B, B, B)
+    w = torch.from_numpy(G.gauss_window_1d(B)).to(dev)
+    out, mask = K.stitch_blend(tiles, (1, 1, S, S, S), fax, (w, w, w), want_mask=True, thr=0.7)
+    torch.testing.assert_close(out, x, rtol=1e-5, atol=1e-6)
+    del tiles
+    bax = [K.DeviceAxis(G.bioimageio_axis(S, B, halo), dev) for _ in range(3)]
+    btiles = K.tile_gather(x, bax)
+    back, _ = K.stitch_crop(btiles, (1, 1, S, S, S), bax)
+    assert torch.equal(back, x)
+    del btiles, back, out
+    labels, n = K.ccl(mask[0], 3)
+    assert int(n.item()) > 0 and int(labels.max().item()) == int(n.item())
+    again, n2 = K.ccl((labels > 0).to(torch.uint8), 3)
+    assert torch.equal(labels, again) and int(n2.item()) == int(n.item())
+    # the oracle on a slab: labels restricted to z < 40 must induce the same partition as labelling the slab alone
+    slab = mask[0, 0, :40].cpu().numpy()
+    got = K.ccl(mask[0, :, :40].contiguous(), 3)[0].cpu().numpy()[0]
+    assert np.array_equal(got, O.label(slab, 3))
