@@ -239,6 +239,77 @@ __global__ void bbox_init_kernel(int32_t* bbox, int64_t n_labels_total) {
     B[3] = B[4] = B[5] = -1;
 }
 
+// ---- pixel-level binary metrics ----
+
+__device__ __forceinline__ float atomic_min_f32(float* addr, float v) {
+    // ordered-int trick: valid for any non-NaN floats
+    return (v >= 0.f) ? __int_as_float(atomicMin((int*)addr, __float_as_int(v)))
+                      : __uint_as_float(atomicMax((unsigned*)addr, __float_as_uint(v)));
+}
+__device__ __forceinline__ float atomic_max_f32(float* addr, float v) {
+    return (v >= 0.f) ? __int_as_float(atomicMax((int*)addr, __float_as_int(v)))
+                      : __uint_as_float(atomicMin((unsigned*)addr, __float_as_uint(v)));
+}
+
+__global__ void __launch_bounds__(kThreads) minmax_kernel(const float* __restrict__ a, const float* __restrict__ b,
+                                                          int64_t n, float* __restrict__ out /* amin amax bmin bmax */) {
+    float lo_a = __int_as_float(0x7f800000), hi_a = __int_as_float(0xff800000), lo_b = lo_a, hi_b = hi_a;
+    for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kThreads) {
+        const float x = a[i], y = b[i];
+        lo_a = fminf(lo_a, x);
+        hi_a = fmaxf(hi_a, x);
+        lo_b = fminf(lo_b, y);
+        hi_b = fmaxf(hi_b, y);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        lo_a = fminf(lo_a, __shfl_xor_sync(0xffffffffu, lo_a, o));
+        hi_a = fmaxf(hi_a, __shfl_xor_sync(0xffffffffu, hi_a, o));
+        lo_b = fminf(lo_b, __shfl_xor_sync(0xffffffffu, lo_b, o));
+        hi_b = fmaxf(hi_b, __shfl_xor_sync(0xffffffffu, hi_b, o));
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomic_min_f32(&out[0], lo_a);
+        atomic_max_f32(&out[1], hi_a);
+        atomic_min_f32(&out[2], lo_b);
+        atomic_max_f32(&out[3], hi_b);
+    }
+}
+
+__global__ void minmax_init_kernel(float* out) {
+    out[0] = out[2] = __int_as_float(0x7f800000);
+    out[1] = out[3] = __int_as_float(0xff800000);
+}
+
+// thresholds chosen on the device exactly like the reference: 0.5 if the value range lies inside [0, 1], else 0.0
+__global__ void __launch_bounds__(kThreads) confusion_kernel(const float* __restrict__ pred, const float* __restrict__ target,
+                                                             int64_t n, const float* __restrict__ mm, int adaptive,
+                                                             float thr_pred, float thr_target,
+                                                             unsigned long long* __restrict__ counts /* tp fp fn tn */) {
+    if (adaptive) {
+        thr_pred = (mm[0] >= 0.f && mm[1] <= 1.f) ? 0.5f : 0.0f;
+        thr_target = (mm[2] >= 0.f && mm[3] <= 1.f) ? 0.5f : 0.0f;
+    }
+    unsigned tp = 0, fp = 0, fn = 0, tn = 0;
+    for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kThreads) {
+        const bool p = pred[i] > thr_pred, t = target[i] > thr_target;
+        tp += p & t;
+        fp += p & !t;
+        fn += !p & t;
+        tn += !p & !t;
+    }
+    tp = __reduce_add_sync(0xffffffffu, tp);
+    fp = __reduce_add_sync(0xffffffffu, fp);
+    fn = __reduce_add_sync(0xffffffffu, fn);
+    tn = __reduce_add_sync(0xffffffffu, tn);
+    if ((threadIdx.x & 31) == 0) {
+        if (tp) atomicAdd(&counts[0], (unsigned long long)tp);
+        if (fp) atomicAdd(&counts[1], (unsigned long long)fp);
+        if (fn) atomicAdd(&counts[2], (unsigned long long)fn);
+        if (tn) atomicAdd(&counts[3], (unsigned long long)tn);
+    }
+}
+
 inline bool is_pow2(int64_t v) { return v > 0 && (v & (v - 1)) == 0; }
 
 }  // namespace
@@ -315,6 +386,24 @@ extern "C" int be_label_stats_i32(const int32_t* labels, int64_t N, int64_t Z, i
     BE_LAUNCH_CHECK();
     label_stats_kernel<<<dim3((unsigned)((vol + kThreads - 1) / kThreads), (unsigned)N), kThreads, 0, s>>>(
         labels, Z, Y, X, cap, (unsigned long long*)sums, bbox, status);
+    BE_LAUNCH_CHECK();
+    return BE_OK;
+}
+
+extern "C" int be_binary_confusion_f32(const float* pred, const float* target, int64_t n, int adaptive, float thr_pred,
+                                       float thr_target, float* minmax, int64_t* counts, be_stream_t stream) {
+    BE_REQUIRE(pred && target && minmax && counts, BE_ERR_INVALID_ARG, "be_binary_confusion_f32: null pointer");
+    BE_REQUIRE(n > 0, BE_ERR_INVALID_ARG, "be_binary_confusion_f32: empty input");
+    cudaStream_t s = (cudaStream_t)stream;
+    int64_t blocks = (n + kThreads * 8 - 1) / (kThreads * 8);
+    if (blocks > BE_SM_COUNT * 16) blocks = BE_SM_COUNT * 16;
+    minmax_init_kernel<<<1, 1, 0, s>>>(minmax);
+    BE_LAUNCH_CHECK();
+    minmax_kernel<<<(unsigned)blocks, kThreads, 0, s>>>(pred, target, n, minmax);
+    BE_LAUNCH_CHECK();
+    BE_CUDA(cudaMemsetAsync(counts, 0, sizeof(int64_t) * 4, s));
+    confusion_kernel<<<(unsigned)blocks, kThreads, 0, s>>>(pred, target, n, minmax, adaptive, thr_pred, thr_target,
+                                                          (unsigned long long*)counts);
     BE_LAUNCH_CHECK();
     return BE_OK;
 }

@@ -217,19 +217,23 @@ __global__ void __launch_bounds__(kThreads) stitch_blend_kernel(const float* __r
                                                                 const double* __restrict__ wy,
                                                                 const double* __restrict__ wx, Epilogue e,
                                                                 int units_per_row, unsigned n_planes) {
-    const int u = blockIdx.x * kThreads + threadIdx.x;
-    if (u >= units_per_row) return;
+    const int u = min((int)(blockIdx.x * kThreads + threadIdx.x), units_per_row - 1);
+    const bool live = blockIdx.x * kThreads + threadIdx.x < (unsigned)units_per_row;  // spare threads shadow the last unit
     const int y = blockIdx.y;
     const int64_t tvol = (int64_t)d.Bz * d.By * d.Bx;
     const int64_t tile_stride = d.C * tvol;  // elements between consecutive tiles
     const int x0 = u * 4;
     const int cnt = min(4, (int)d.X - x0);
-    // tiles touching this 4-px unit: from the first tile covering x0 to the last one covering its last pixel
-    int kx_first, kx_last, tmp;
-    cover(x0, d.Bx, s.Sx, s.rSx, d.Tx, &kx_first, &tmp);
-    cover(x0 + cnt - 1, d.Bx, s.Sx, s.rSx, d.Tx, &tmp, &kx_last);
-    int ky_lo, ky_hi;
-    cover(y, d.By, s.Sy, s.rSy, d.Ty, &ky_lo, &ky_hi);  // block-uniform
+    // tiles touching this 4-px unit: from the first tile covering x0 to the last one covering its last pixel (one
+    // division pair; a unit is 4 px wide, so the last pixel can at most reach the next tile)
+    int kx_first, kx_last;
+    cover(x0, d.Bx, s.Sx, s.rSx, d.Tx, &kx_first, &kx_last);
+    kx_last += (kx_last + 1 < d.Tx && (kx_last + 1) * s.Sx <= x0 + cnt - 1) ? 1 : 0;
+    // the row's tile range is the same for the whole block: one thread works it out
+    __shared__ int s_ky[2];
+    if (threadIdx.x == 0) cover(y, d.By, s.Sy, s.rSy, d.Ty, &s_ky[0], &s_ky[1]);
+    __syncthreads();
+    const int ky_lo = s_ky[0], ky_hi = s_ky[1];
 
     for (unsigned plane = blockIdx.z; plane < n_planes; plane += gridDim.z) {
         int z = 0, c = 0;
@@ -253,9 +257,9 @@ __global__ void __launch_bounds__(kThreads) stitch_blend_kernel(const float* __r
                 const double wzy = __dmul_rn(wzv, wy[iy]);
                 const float* rowbase = tiles + (((n * d.Tz + kz) * d.Ty + ky) * d.Tx) * tile_stride +
                                        (((int64_t)c * d.Bz + iz) * d.By + iy) * d.Bx;
-                for (int kx = kx_first; kx <= kx_last; ++kx) {
+                const float* src = rowbase + kx_first * tile_stride + (x0 - kx_first * s.Sx);
+                for (int kx = kx_first; kx <= kx_last; ++kx, src += tile_stride - s.Sx) {
                     const int ix0 = x0 - kx * s.Sx;  // in-tile offset of the unit's first pixel
-                    const float* src = rowbase + kx * tile_stride + ix0;
                     if (cnt == 4 && ix0 >= 0 && ix0 + 4 <= d.Bx && ((((uintptr_t)src) & 15) == 0) && ((ix0 & 1) == 0)) {
                         // the whole unit lies inside this tile: one 16-byte tile load, two 16-byte window loads
                         const float4 p = __ldg(reinterpret_cast<const float4*>(src));
@@ -288,7 +292,7 @@ __global__ void __launch_bounds__(kThreads) stitch_blend_kernel(const float* __r
         float v[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j) v[j] = be_div_to_f32(acc[j], wacc[j], be_fast_rcp(wacc[j]));
-        finish4(out, mask, ((int64_t)plane * d.Y + y) * d.X + x0, cnt, v, e, (d.X & 3) == 0);
+        if (live) finish4(out, mask, ((int64_t)plane * d.Y + y) * d.X + x0, cnt, v, e, (d.X & 3) == 0);
     }
 }
 

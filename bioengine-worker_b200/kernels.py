@@ -265,3 +265,17 @@ def label_stats(labels: torch.Tensor, cap: int):
     _lib.call("be_label_stats_i32", labels.data_ptr(), N, Z, Y, X, cap, sums.data_ptr(), bbox.data_ptr(),
               status.data_ptr(), _stream())
     return sums, bbox, status
+
+
+def binary_confusion(pred: torch.Tensor, target: torch.Tensor, thresholds: Optional[Tuple[float, float]] = None):
+    """→ (counts int64 [4] {tp, fp, fn, tn}, minmax fp32 [4]) on the device.  thresholds=None: the reference's adaptive rule."""
+    _check(pred, torch.float32, "pred")
+    _check(target, torch.float32, "target")
+    if pred.numel() != target.numel():
+        raise ValueError("pred and target differ in size")
+    counts = torch.empty((4,), dtype=torch.int64, device=pred.device)
+    minmax = torch.empty((4,), dtype=torch.float32, device=pred.device)
+    tp, tt = thresholds if thresholds is not None else (0.0, 0.0)
+    _lib.call("be_binary_confusion_f32", pred.data_ptr(), target.data_ptr(), pred.numel(), int(thresholds is None),
+              float(tp), float(tt), minmax.data_ptr(), counts.data_ptr(), _stream())
+    return counts, minmax

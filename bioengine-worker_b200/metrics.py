@@ -130,3 +130,31 @@ def average_precision(masks_true, masks_pred, threshold=(0.5, 0.75, 0.9), device
     if not_list:
         return ap[0], tpf[0], fp[0], fn[0]
     return ap, tpf, fp, fn
+
+
+def _safe_div(n: float, d: float) -> float:
+    """Return n / d, or 0.0 when d is zero (ref: apps/cellpose-finetuning/main.py:1218-1220)."""
+    return float(n / d) if d != 0 else 0.0
+
+
+def binary_metrics(pred: ArrayLike, target: ArrayLike, device="cuda:0") -> dict:
+    """Pixel-level foreground metrics of ref: apps/cellpose-finetuning/main.py:1225-1270 (`_compute_binary_metrics`): adaptive
+    thresholds (0.5 if the values lie in [0, 1], else 0.0), TP / FP / FN / TN counted on the device, then the same ratios."""
+    dev = torch.device(device)
+
+    def dev_f32(a):
+        t = a if isinstance(a, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(a))
+        return t.to(device=dev, dtype=torch.float32).contiguous()
+
+    counts, _ = K.binary_confusion(dev_f32(pred), dev_f32(target))
+    tp, fp, fn, tn = (int(v) for v in counts.cpu().tolist())
+    precision = _safe_div(tp, tp + fp)
+    recall = _safe_div(tp, tp + fn)
+    return {
+        "tp": tp, "fp": fp, "fn": fn, "tn": tn,
+        "pixel_accuracy": _safe_div(tp + tn, tp + tn + fp + fn),
+        "precision": precision,
+        "recall": recall,
+        "f1": _safe_div(2 * precision * recall, precision + recall),
+        "iou": _safe_div(tp, tp + fp + fn),
+    }

@@ -175,6 +175,14 @@ int be_match_counts(const uint64_t* keys, const uint32_t* counts, int64_t N, int
                     const int32_t* area_true, int64_t cap_true, const int32_t* area_pred, int64_t cap_pred,
                     const double* thr, int n_thr, int64_t* counts_out, void* ws, be_stream_t stream);
 
+/* Pixel-level binary confusion counts of a prediction against a target — `_binary_threshold` +
+ * `_compute_binary_metrics` of apps/cellpose-finetuning/main.py:1225-1270.  adaptive != 0 picks each threshold on the
+ * device the way the reference does (0.5 if that tensor's values lie within [0, 1], else 0.0); otherwise thr_pred /
+ * thr_target are used.  foreground = value > threshold.
+ *   minmax [4] fp32 out {pred min, pred max, target min, target max}     counts [4] int64 out {tp, fp, fn, tn} */
+int be_binary_confusion_f32(const float* pred, const float* target, int64_t n, int adaptive, float thr_pred,
+                            float thr_target, float* minmax, int64_t* counts, be_stream_t stream);
+
 /* Per-label integer raw moments of N label maps (Z,Y,X): for label l in 1..cap-1,
  * sums[((n*cap + l)*10 + j)] = {area, Σz, Σy, Σx, Σzz, Σyy, Σxx, Σzy, Σzx, Σyx} (int64, exact) and
  * bbox[((n*cap + l)*6 + j)] = {zmin, ymin, xmin, zmax, ymax, xmax} (int32, inclusive).  The integer core of

@@ -89,3 +89,25 @@ def test_screening_single_rank_matches_oracle(dev):
         ap, _, _, _ = O.average_precision(gts, preds)
         assert np.array_equal(res["ap"][m], ap, equal_nan=True)
     assert sorted(res["ranking"].tolist()) == [0, 1, 2]
+
+
+@pytest.mark.parametrize("case", ["probabilities", "logits", "mixed"])
+def test_binary_metrics_match_reference_rule(case):
+    from bioengine_worker_b200.metrics import binary_metrics
+
+    rng = np.random.default_rng(3)
+    shape = (3, 257, 300)
+    target = (O.gaussian_blobs(shape[1:], 20, seed=1)[None] > 0.5).astype(np.float32).repeat(3, 0)
+    if case == "probabilities":          # both in [0, 1] → thresholds 0.5 / 0.5
+        pred = rng.random(shape).astype(np.float32)
+    elif case == "logits":               # prediction range leaves [0, 1] → threshold 0.0
+        pred = rng.standard_normal(shape).astype(np.float32) * 3
+    else:                                # target as +-1 labels → its threshold drops to 0.0 too
+        pred = rng.random(shape).astype(np.float32)
+        target = target * 2 - 1
+    got = binary_metrics(pred, target)
+    want = O.binary_metrics(pred, target)
+    for k in ("tp", "fp", "fn", "tn"):
+        assert got[k] == want[k], k
+    for k in ("precision", "recall", "f1", "pixel_accuracy", "iou"):
+        assert got[k] == want[k], k

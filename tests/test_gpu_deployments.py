@@ -136,3 +136,24 @@ def test_analyze_matches_fibsem_oracle(dev):
     assert np.array_equal(res2["labels"], O.label(p2 > 0.5))
     with pytest.raises(ValueError):
         asyncio.run(dep.analyze(np.zeros((2, 3, 4)).tolist()))
+
+
+def test_entry_deployment_infer_mirrors_the_reference_call(tmp_path, dev):
+    from bioengine_worker_b200.entry_deployment import EntryDeployment
+    from bioengine_worker_b200.runtime_deployment import RuntimeDeployment
+
+    pkg = tmp_path / "models" / "tiny-unet"
+    pkg.mkdir(parents=True)
+    rdf_path, _ = write_model(pkg, [{"id": "zero_mean_unit_variance", "kwargs": {"axes": ["y", "x"]}}], [{"id": "sigmoid"}])
+    entry = EntryDeployment(RuntimeDeployment.func_or_class(), models_dir=str(tmp_path / "models"))
+    img = O.synthetic_image((96, 128), 8, seed=1, microscope=False)
+    direct = asyncio.run(entry.infer("tiny-unet", img))
+    assert list(direct) == ["mask"] and direct["mask"].shape == (1, 1, 96, 128)
+    np.save(tmp_path / "in.npy", img)
+    via_file = asyncio.run(entry.infer("tiny-unet", str(tmp_path / "in.npy"), return_download_url=True))
+    assert via_file["mask"].startswith("file://")
+    assert np.array_equal(np.load(via_file["mask"][7:]), direct["mask"])
+    with pytest.raises(FileNotFoundError):
+        asyncio.run(entry.infer("no-such-model", img))
+    with pytest.raises(ValueError):
+        asyncio.run(entry.infer("tiny-unet", "https://example.org/x.npy"))
