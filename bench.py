@@ -331,6 +331,14 @@ def run_b200(args):
             stages[name] = {"ms": round(float(ms), 4), "alg_bytes": alg_bytes[name], "alg_GBps": round(gbs, 1),
                             "frac_of_peak": round(gbs / peak, 4)}
         dom = max(stage_names, key=lambda n: stages[n]["ms"])
+        traffic, traffic_src = None, None
+        tp = os.path.join(ROOT, "profiles", "r1_traffic.json")
+        if os.path.exists(tp):  # dram__bytes_read.sum + dram__bytes_write.sum of the stage's kernels, one ncu --set full capture
+            tj = json.load(open(tp))
+            if dom in tj.get("stages", {}):
+                traffic, traffic_src = tj["stages"][dom]["dram_bytes_per_launch"], tj["source"]
+                kernels_in_stage = tj["stages"][dom]["kernels"]
+        kernels_in_stage = locals().get("kernels_in_stage")
         path_bytes = sum(alg_bytes.values())
         path_gbs = path_bytes / (ms_per_step * 1e-3) / 1e9
 
@@ -345,14 +353,17 @@ def run_b200(args):
             best = dt if best is None else min(best, dt)
         cpu_value = px / best / 1e6
 
-        launches_per_step = 3 + 1 + 1 + 6  # quantile levels, gather, blend, ccl (tile/border/count/scan/assign/resolve)
+        launches_per_step = 5 + 1 + 1 + 4  # quantile (sample/partition/select x3), gather, blend, ccl (tile/edge/number/resolve)
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": workload_config({"tiles": n_tiles, "tile_expansion": round(E, 4)}),
             "roofline": {"bound": "hbm", "kernel": dom, "achieved": stages[dom]["alg_GBps"], "peak": peak,
-                         "unit": "GB/s", "frac": stages[dom]["frac_of_peak"], "traffic": None, "peak_source": peak_src},
+                         "unit": "GB/s", "frac": stages[dom]["frac_of_peak"], "traffic": traffic, "peak_source": peak_src,
+                         "traffic_source": traffic_src, "alg_bytes": alg_bytes[dom],
+                         "note": "one C-ABI call = the listed kernels; achieved = algorithmic bytes / CUDA-event time of the call",
+                         "kernels": kernels_in_stage if traffic is not None else None},
             "path_roofline": {"alg_bytes_per_px": round(path_bytes / px, 3), "achieved": round(path_gbs, 1), "peak": peak,
                               "unit": "GB/s", "frac": round(path_gbs / peak, 4)},
             "stages": stages,
