@@ -504,7 +504,14 @@ __global__ void __launch_bounds__(kThreads) ccl_number_kernel(int32_t* __restric
 }
 
 __device__ __forceinline__ int32_t resolve_one(const int32_t* __restrict__ Li, int32_t v) {
-    while (v >= 0) v = Li[v];
+    // background (-1) and roots are already terminal; a pixel is normally one or two hops from its root
+    if (v >= 0) {
+        v = __ldg(Li + v);
+        if (v >= 0) {
+            v = __ldg(Li + v);
+            while (v >= 0) v = __ldg(Li + v);
+        }
+    }
     return -v - 1;
 }
 

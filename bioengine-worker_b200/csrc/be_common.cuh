@@ -82,10 +82,7 @@ __device__ __forceinline__ float be_sigmoid_f32(float x) {
 }
 
 // (float)(n / d) with the fp64 quotient correctly rounded first — what numpy does when an fp64 expression is cast to
-// fp32 — without paying for an IEEE fp64 division per element.  q = n * r, r ~ 1/d to a few ulp, is within 2^-50 of
-// the exact quotient; it rounds to the same fp32 value as the correctly rounded quotient unless it lies within 2^-48
-// of an fp32 rounding boundary (the midpoint between two neighbouring fp32 values: low 29 mantissa bits = 2^28).
-// Those ~1 in 10^7 elements, and anything outside the normal fp32 range, take the exact division.
+// fp32 — without paying for an IEEE fp64 division per element: r ~ 1/d to a few ulp (be_fast_rcp), then be_div_to_f32.
 __device__ __forceinline__ double be_fast_rcp(double d) {
     double r;
     asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d));
@@ -105,14 +102,14 @@ __device__ __forceinline__ int be_fast_div(int p, int S, float rS) {
 }
 
 __device__ __forceinline__ float be_div_to_f32(double n, double d, double r) {
+    // q = n * r is within 2^-50 of the exact quotient.  Round q(1 + 2^-44) and q(1 - 2^-44) to fp32: rounding is monotone,
+    // so if both give the same value the correctly rounded fp64 quotient — which lies between them — rounds to it too
+    // (zeros, infinities and fp32 subnormals included).  They differ only next to an fp32 rounding boundary (~2e-6 of
+    // inputs) or for NaN, and those take the real division.
     const double q = n * r;
-    if (n == 0.0) return (float)q;  // +-0 / d (and 0/0 -> NaN through r = inf), very common at the lower quantile
-    const unsigned long long b = (unsigned long long)__double_as_longlong(q);
-    const unsigned low = (unsigned)(b & 0x1fffffffull);   // bits below fp32 precision
-    const unsigned ex = (unsigned)(b >> 52) & 0x7ffu;
-    const bool near_mid = (low - (0x10000000u - 64u)) <= 128u;
-    const bool normal = ex > (1023u - 126u) && ex < (1023u + 127u);
-    if (!near_mid && normal) return (float)q;
+    const float a = (float)fma(q, 0x1p-44, q);
+    const float b = (float)fma(q, -0x1p-44, q);
+    if (a == b) return a;
     return be_div_to_f32_exact(n, d);
 }
 

@@ -65,8 +65,9 @@ class UNet3d(_UNet):
 ARCHITECTURES = {"UNet2d": UNet2d, "UNet3d": UNet3d}
 
 
-def calibrate_head(model: nn.Module, probe: torch.Tensor) -> nn.Module:
-    """Re-centre and re-scale the 1x1 head so the logits of `probe` have median 0 and unit spread.
+def calibrate_head(model: nn.Module, probe: torch.Tensor, foreground: float = 0.5) -> nn.Module:
+    """Re-centre and re-scale the 1x1 head so that a fraction `foreground` of the logits of `probe` is positive (0.5: the
+    median lands on 0) and their spread is of order one.
 
     A random-init UNet's output is its head bias plus a few hundredths of variation, so every pixel lands on the same
     side of the threshold and the mask is all-0 or all-1 — the stitch/label stages would have nothing to do.  This keeps
@@ -74,7 +75,7 @@ def calibrate_head(model: nn.Module, probe: torch.Tensor) -> nn.Module:
     """
     with torch.no_grad():
         y = model(probe.to(next(model.parameters()).device))
-        med = y.median()
+        med = torch.quantile(y.flatten()[:: max(1, y.numel() // (1 << 22))].float(), 1.0 - float(foreground))
         spread = (y - med).abs().mean().clamp_min(1e-12)
         model.head.weight.div_(spread)
         model.head.bias.sub_(med).div_(spread)
