@@ -15,10 +15,11 @@ struct Dims {
     int Tz, Ty, Tx, Bz, By, Bx;
 };
 
-__device__ __forceinline__ float norm_apply(float v, double sub, double div, double rdiv, int clip, float lo, float hi) {
+template <bool CLIP>
+__device__ __forceinline__ float norm_apply(float v, double sub, double div, double rdiv, float lo, float hi) {
     // np.clip on the fp64 quotient then a cast equals a clip of the cast value: the bounds are fp32 numbers
     float r = be_div_to_f32(__dsub_rn((double)v, sub), div, rdiv);
-    if (clip && r == r) r = fminf(fmaxf(r, lo), hi);
+    if (CLIP && r == r) r = fminf(fmaxf(r, lo), hi);
     return r;
 }
 
@@ -29,12 +30,12 @@ __device__ __forceinline__ float norm_apply(float v, double sub, double div, dou
 // grid: x = tile (n, kz, ky, kx), y = (c, iz), z = a band of tile rows.  A thread owns one 4-px column unit and walks
 // the rows of its band, so the tile / plane decomposition (integer divides) is paid once per thread, not once per
 // 16 bytes, and several independent row loads are in flight per thread.
-template <bool NORM>
+template <bool NORM, bool CLIP>
 __global__ void __launch_bounds__(kThreads) tile_gather_kernel(const float* __restrict__ img, float* __restrict__ tiles,
                                                                Dims d, const int32_t* __restrict__ zsrc,
                                                                const int32_t* __restrict__ ysrc,
                                                                const int32_t* __restrict__ xsrc,
-                                                               const double* __restrict__ norm, int norm_mode, int clip,
+                                                               const double* __restrict__ norm, int norm_mode,
                                                                float clip_lo, float clip_hi, int units_per_row,
                                                                int rows_per_band) {
     const int ucols = min(units_per_row, kThreads);     // column units the block covers per sweep
@@ -86,10 +87,10 @@ __global__ void __launch_bounds__(kThreads) tile_gather_kernel(const float* __re
                 v.w = __ldg(src + xi.w);
             }
             if (NORM) {
-                v.x = norm_apply(v.x, sub, div, rdiv, clip, clip_lo, clip_hi);
-                v.y = norm_apply(v.y, sub, div, rdiv, clip, clip_lo, clip_hi);
-                v.z = norm_apply(v.z, sub, div, rdiv, clip, clip_lo, clip_hi);
-                v.w = norm_apply(v.w, sub, div, rdiv, clip, clip_lo, clip_hi);
+                v.x = norm_apply<CLIP>(v.x, sub, div, rdiv, clip_lo, clip_hi);
+                v.y = norm_apply<CLIP>(v.y, sub, div, rdiv, clip_lo, clip_hi);
+                v.z = norm_apply<CLIP>(v.z, sub, div, rdiv, clip_lo, clip_hi);
+                v.w = norm_apply<CLIP>(v.w, sub, div, rdiv, clip_lo, clip_hi);
             }
             st_stream_f4(reinterpret_cast<float4*>(dst_plane + (int64_t)iy * d.Bx), v);
         }
@@ -98,7 +99,7 @@ __global__ void __launch_bounds__(kThreads) tile_gather_kernel(const float* __re
             const float* src = plane + (int64_t)ys[iy] * d.X;
             for (int j = 0; j < rem && j < 4; ++j) {
                 float v = __ldg(src + xs[j]);
-                if (NORM) v = norm_apply(v, sub, div, rdiv, clip, clip_lo, clip_hi);
+                if (NORM) v = norm_apply<CLIP>(v, sub, div, rdiv, clip_lo, clip_hi);
                 dst_plane[(int64_t)iy * d.Bx + j] = v;
             }
         }
@@ -201,7 +202,8 @@ __global__ void __launch_bounds__(kThreads) stitch_crop_kernel(const float* __re
 
 struct Strides {
     int Sz, Sy, Sx;
-    float rSz, rSy, rSx;  // 1.0f / stride, for be_fast_div
+    float rSz, rSy, rSx;   // 1.0f / stride, for be_fast_div
+    int64_t tile_stride;   // elements between consecutive tiles = C * Bz * By * Bx
 };
 
 // tiles k covering output coordinate p: k*S <= p < k*S + B, 0 <= k < T
@@ -220,8 +222,7 @@ __global__ void __launch_bounds__(kThreads) stitch_blend_kernel(const float* __r
     const int u = min((int)(blockIdx.x * kThreads + threadIdx.x), units_per_row - 1);
     const bool live = blockIdx.x * kThreads + threadIdx.x < (unsigned)units_per_row;  // spare threads shadow the last unit
     const int y = blockIdx.y;
-    const int64_t tvol = (int64_t)d.Bz * d.By * d.Bx;
-    const int64_t tile_stride = d.C * tvol;  // elements between consecutive tiles
+    const int64_t tile_stride = s.tile_stride;
     const int x0 = u * 4;
     const int cnt = min(4, (int)d.X - x0);
     // tiles touching this 4-px unit: from the first tile covering x0 to the last one covering its last pixel (one
@@ -354,12 +355,15 @@ extern "C" int be_tile_gather_f32(const float* img, float* tiles, int64_t N, int
     bands = (By + rows_per_band - 1) / rows_per_band;
     const dim3 grid((unsigned)n_tiles, (unsigned)(C * Bz), (unsigned)bands);
     cudaStream_t s = (cudaStream_t)stream;
-    if (norm_mode)
-        tile_gather_kernel<true><<<grid, kThreads, 0, s>>>(img, tiles, d, zsrc, ysrc, xsrc, norm, norm_mode, clip, clip_lo,
-                                                           clip_hi, upr, rows_per_band);
+    if (norm_mode && clip)
+        tile_gather_kernel<true, true><<<grid, kThreads, 0, s>>>(img, tiles, d, zsrc, ysrc, xsrc, norm, norm_mode, clip_lo,
+                                                                 clip_hi, upr, rows_per_band);
+    else if (norm_mode)
+        tile_gather_kernel<true, false><<<grid, kThreads, 0, s>>>(img, tiles, d, zsrc, ysrc, xsrc, norm, norm_mode, 0.f, 0.f,
+                                                                  upr, rows_per_band);
     else
-        tile_gather_kernel<false><<<grid, kThreads, 0, s>>>(img, tiles, d, zsrc, ysrc, xsrc, norm, 0, 0, 0.f, 0.f, upr,
-                                                            rows_per_band);
+        tile_gather_kernel<false, false><<<grid, kThreads, 0, s>>>(img, tiles, d, zsrc, ysrc, xsrc, norm, 0, 0.f, 0.f, upr,
+                                                                   rows_per_band);
     BE_LAUNCH_CHECK();
     return BE_OK;
 }
@@ -401,7 +405,7 @@ extern "C" int be_stitch_blend_f32(const float* tiles, float* out, uint8_t* mask
                BE_ERR_INVALID_ARG, "be_stitch_blend_f32: tile grid must be ceil(dim/stride) per axis");
     const Dims d{N, C, Z, Y, X, Tz, Ty, Tx, Bz, By, Bx};
     BE_REQUIRE(Z < (1 << 24) && Y < (1 << 24) && X < (1 << 24), BE_ERR_TOO_LARGE, "be_stitch_blend_f32: axis longer than 2^24");
-    const Strides st{Sz, Sy, Sx, 1.0f / (float)Sz, 1.0f / (float)Sy, 1.0f / (float)Sx};
+    const Strides st{Sz, Sy, Sx, 1.0f / (float)Sz, 1.0f / (float)Sy, 1.0f / (float)Sx, (int64_t)C * Bz * By * Bx};
     const int upr = (int)((X + 3) / 4);
     dim3 grid;
     rc = stitch_grid("be_stitch_blend_f32", d, upr, &grid);
