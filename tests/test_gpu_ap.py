@@ -72,6 +72,9 @@ def test_screening_single_rank_matches_oracle(dev):
         net = models.build_model("UNet2d", seed=40 + m, depth=2, initial_features=8).to(dev)
         probe = torch.from_numpy(O.zero_mean_unit_variance(np.stack(imgs)[:, None], axes=(1, 2, 3))).to(dev)
         nets.append(models.calibrate_head(net, probe))
+    # a candidate that actually segments (threshold on the normalised intensity): it must win the ranking
+    level = float((0.5 - np.mean(imgs[0])) / np.std(imgs[0]))  # the GT level (0.5) in normalised units
+    nets.append(lambda t: (torch.nn.functional.avg_pool2d(t, 5, 1, 2) - level) * 8.0)
     res = screen_models(nets, imgs, gts, device=dev, batch=4)
     # oracle: CPU post-processing + cellpose restatement on the logits of the same forward (device-normalised input:
     # downstream integer results are compared on identical logits)
@@ -88,7 +91,8 @@ def test_screening_single_rank_matches_oracle(dev):
         preds = [O.label(O.binarize(O.sigmoid(l), 0.5)[0], 2) for l in logits]
         ap, _, _, _ = O.average_precision(gts, preds)
         assert np.array_equal(res["ap"][m], ap, equal_nan=True)
-    assert sorted(res["ranking"].tolist()) == [0, 1, 2]
+    assert sorted(res["ranking"].tolist()) == [0, 1, 2, 3]
+    assert res["ranking"][0] == 3 and res["mean_ap"][3, 0] > 0.5 > res["mean_ap"][:3, 0].max()
 
 
 @pytest.mark.parametrize("case", ["probabilities", "logits", "mixed"])
