@@ -46,6 +46,12 @@ SIGNATURES = {
     "be_match_workspace_bytes": (_sz, [_i64, _i64, _i64, _i32]),
     "be_match_counts": (_i32, [_ptr, _ptr, _i64, _i64, _ptr, _i64, _ptr, _i64, _ptr, _i32, _ptr, _ptr, _ptr]),
     "be_binary_confusion_f32": (_i32, [_ptr, _ptr, _i64, _i32, _f32, _f32, _ptr, _ptr, _ptr]),
+    "be_label_area_i32": (_i32, [_ptr, _i64, _i64, _i64, _ptr, _ptr, _ptr]),
+    "be_keep_large_u8": (_i32, [_ptr, _ptr, _i64, _i64, _i64, _i32, _ptr, _ptr]),
+    "be_binary_closing_workspace_bytes": (_sz, [_i64, _i64, _i64]),
+    "be_binary_closing_u8": (_i32, [_ptr, _ptr, _i64, _i64, _i64, _ptr, _i32, _ptr, _ptr]),
+    "be_edt_workspace_bytes": (_sz, [_i64, _i64, _i64]),
+    "be_edt_u8_f64": (_i32, [_ptr, _ptr, _i64, _i64, _i64, _ptr, _ptr]),
     "be_label_stats_i32": (_i32, [_ptr] + [_i64] * 5 + [_ptr] * 4),
 }
 

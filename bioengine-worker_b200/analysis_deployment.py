@@ -5,9 +5,12 @@ Same `analyze(image, pixel_size_nm, tile_size, overlap)` arguments and the same 
 scipy and skimage on one CPU core; here the image goes to the GPU once and p1/p99 normalisation, reflect-padded tiling,
 the forward, the Gaussian blend, the 0.5 threshold, connected components and the per-label moments all run there.
 
-Not yet on the device: the clean-up between threshold and labelling in `_prob_to_instances`
-(remove_small_objects, binary_closing, distance transform, peak_local_max, watershed; ref: analysis_deployment.py:166-175).
-`analyze` therefore labels the thresholded probability map directly (`measure.label(prob > 0.5)` semantics).
+Of `_prob_to_instances` (ref: analysis_deployment.py:160-176) the deterministic front half runs on the device and matches
+scipy / skimage bit for bit: threshold, `remove_small_objects(min_size=300)`, `binary_closing(disk(4))`, and the exact
+Euclidean distance transform (`prob_to_closed_and_distance`).  The seeded watershed that follows (`peak_local_max`,
+`watershed`) is not ported yet: with `cleanup=False` `analyze` labels the thresholded map
+directly (`measure.label(prob > 0.5)`), with `cleanup=True` it labels the cleaned mask — identical to the reference
+whenever the watershed would not split a connected component.
 """
 from __future__ import annotations
 
@@ -84,9 +87,20 @@ class MitoAnalysisDeployment:
             self._pipes[key] = TiledPipeline((1, 1, H, W), spec, device=self.device)
         return self._pipes[key]
 
+    @staticmethod
+    def prob_to_closed_and_distance(mask: torch.Tensor, min_size: int = 300, radius: int = 4):
+        """Front half of `_prob_to_instances` on a thresholded (N, Y, X) uint8 mask: remove_small_objects → (empty?) →
+        binary_closing(disk(radius)) → distance_transform_edt.  Returns (closed uint8, dist fp64 or None if nothing is left)."""
+        kept = K.remove_small_objects(mask, min_size)
+        if not bool(kept.any().item()):
+            return kept, None
+        closed = K.binary_closing(kept, K.disk_half_widths(radius))
+        return closed, K.distance_transform_edt(closed)
+
     async def analyze(self, image, pixel_size_nm: float = 5.0, tile_size: int = 512, overlap: int = 64,
-                      as_numpy: bool = False) -> dict:
-        """Same contract as ref: analysis_deployment.py:192-286 (`as_numpy=True` skips the nested-list conversion)."""
+                      as_numpy: bool = False, cleanup: bool = False) -> dict:
+        """Same contract as ref: analysis_deployment.py:192-286 (`as_numpy=True` skips the nested-list conversion;
+        `cleanup=True` applies remove_small_objects(300) and binary_closing(disk(4)) before labelling)."""
         t0 = time.time()
         image_np = np.array(image, dtype=np.float32)
         if image_np.ndim != 2:
@@ -94,8 +108,13 @@ class MitoAnalysisDeployment:
         H, W = image_np.shape
         pipe = self._pipeline(H, W, tile_size, overlap)
         res = pipe.run(image_np[None, None], self._model)
-        labels_d = res["labels"][0, 0]
-        n_mito = int(res["n_labels"].item())
+        if cleanup:
+            closed, _ = self.prob_to_closed_and_distance(res["mask"][0])
+            labels3, n_lab = K.ccl(closed, 2)
+            labels_d, n_mito = labels3[0], int(n_lab.item())
+        else:
+            labels_d = res["labels"][0, 0]
+            n_mito = int(res["n_labels"].item())
         if n_mito > 0:
             sums, _, status = K.label_stats(labels_d[None], n_mito + 1)
             if int(status.item()) != 0:

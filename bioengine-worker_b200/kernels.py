@@ -279,3 +279,49 @@ def binary_confusion(pred: torch.Tensor, target: torch.Tensor, thresholds: Optio
     _lib.call("be_binary_confusion_f32", pred.data_ptr(), target.data_ptr(), pred.numel(), int(thresholds is None),
               float(tp), float(tt), minmax.data_ptr(), counts.data_ptr(), _stream())
     return counts, minmax
+
+
+def remove_small_objects(mask: torch.Tensor, min_size: int, ws: Workspace = _default_ws) -> torch.Tensor:
+    """skimage `remove_small_objects(mask, min_size)` (connectivity 1) for (N, Y, X) uint8 masks → uint8 mask."""
+    _check(mask, torch.uint8, "mask")
+    labels, n = ccl(mask, 1, ws=ws)
+    N = mask.shape[0]
+    n_px = mask.numel() // N
+    cap = int(n.max().item()) + 1
+    area = torch.empty((N, cap), dtype=torch.int32, device=mask.device)
+    status = torch.empty((N,), dtype=torch.int32, device=mask.device)
+    out = torch.empty_like(mask)
+    _lib.call("be_label_area_i32", labels.data_ptr(), N, n_px, cap, area.data_ptr(), status.data_ptr(), _stream())
+    _lib.call("be_keep_large_u8", labels.data_ptr(), area.data_ptr(), N, n_px, cap, int(min_size), out.data_ptr(), _stream())
+    return out
+
+
+def disk_half_widths(radius: int) -> np.ndarray:
+    """Rows of skimage `morphology.disk(radius)`: half width of row dy = largest dx with dx^2 + dy^2 <= radius^2."""
+    r = int(radius)
+    return np.array([int(np.floor(np.sqrt(r * r - dy * dy))) for dy in range(-r, r + 1)], dtype=np.int32)
+
+
+def binary_closing(mask: torch.Tensor, half_widths: np.ndarray, ws: Workspace = _default_ws) -> torch.Tensor:
+    """scipy `binary_closing(mask, structure)` for (N, Y, X) uint8 masks; structure given by its row half widths."""
+    import ctypes
+
+    _check(mask, torch.uint8, "mask")
+    N, Y, X = mask.shape
+    hw = np.ascontiguousarray(half_widths, dtype=np.int32)
+    radius = (hw.size - 1) // 2
+    out = torch.empty_like(mask)
+    w = ws.get(_lib.query("be_binary_closing_workspace_bytes", N, Y, X), mask.device)
+    _lib.call("be_binary_closing_u8", mask.data_ptr(), out.data_ptr(), N, Y, X, hw.ctypes.data_as(ctypes.c_void_p), radius,
+              w.data_ptr(), _stream())
+    return out
+
+
+def distance_transform_edt(mask: torch.Tensor, ws: Workspace = _default_ws) -> torch.Tensor:
+    """scipy `distance_transform_edt(mask)` for (N, Y, X) uint8 masks → fp64 distances."""
+    _check(mask, torch.uint8, "mask")
+    N, Y, X = mask.shape
+    dist = torch.empty(mask.shape, dtype=torch.float64, device=mask.device)
+    w = ws.get(_lib.query("be_edt_workspace_bytes", N, Y, X), mask.device)
+    _lib.call("be_edt_u8_f64", mask.data_ptr(), dist.data_ptr(), N, Y, X, w.data_ptr(), _stream())
+    return dist

@@ -191,6 +191,33 @@ int be_binary_confusion_f32(const float* pred, const float* target, int64_t n, i
 int be_label_stats_i32(const int32_t* labels, int64_t N, int64_t Z, int64_t Y, int64_t X, int64_t cap,
                        int64_t* sums, int32_t* bbox, int32_t* status, be_stream_t stream);
 
+/* ---- mask clean-up and distance transform (first part) ------------------------ */
+
+/* Pixel count of every label: area[n*cap + l] for l in 0..cap-1 (area[.., 0] stays 0).  With be_ccl_u8_i32 at
+ * connectivity 1 and be_keep_large_u8 this is `skimage.morphology.remove_small_objects(mask, min_size)`
+ * (apps/fibsem-mito-analysis/analysis_deployment.py:166): components with fewer than min_size pixels are dropped.
+ *   status [N] int32 out: 0 ok, 2 a label >= cap was met */
+int be_label_area_i32(const int32_t* labels, int64_t N, int64_t n_px, int64_t cap, int32_t* area, int32_t* status,
+                      be_stream_t stream);
+int be_keep_large_u8(const int32_t* labels, const int32_t* area, int64_t N, int64_t n_px, int64_t cap, int32_t min_size,
+                     uint8_t* out, be_stream_t stream);
+
+/* `scipy.ndimage.binary_closing(mask, structure)` for N independent (Y, X) masks and a structuring element given by
+ * its rows: half_widths[dy + radius] = half width of row dy (-1: empty row), symmetric in dy, HOST pointer —
+ * e.g. skimage `disk(4)` = {0, 2, 3, 3, 4, 3, 3, 2, 0} (analysis_deployment.py:169).  Dilation then erosion, both with
+ * scipy's border_value = 0.  mask and out may alias.
+ *   ws   be_binary_closing_workspace_bytes(N, Y, X) bytes */
+size_t be_binary_closing_workspace_bytes(int64_t N, int64_t Y, int64_t X);
+int be_binary_closing_u8(const uint8_t* mask, uint8_t* out, int64_t N, int64_t Y, int64_t X, const int32_t* half_widths,
+                         int radius, void* ws, be_stream_t stream);
+
+/* Exact Euclidean distance of every pixel to the nearest zero pixel, fp64 — `scipy.ndimage.distance_transform_edt`
+ * (analysis_deployment.py:170) for N independent (Y, X) masks.  X <= 16384.  A mask without any zero pixel has no
+ * defined answer (scipy's is implementation-specific); very large values are returned.
+ *   ws   be_edt_workspace_bytes(N, Y, X) bytes */
+size_t be_edt_workspace_bytes(int64_t N, int64_t Y, int64_t X);
+int be_edt_u8_f64(const uint8_t* mask, double* dist, int64_t N, int64_t Y, int64_t X, void* ws, be_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -263,6 +263,35 @@ def label(mask: np.ndarray, connectivity: Optional[int] = None) -> np.ndarray:
     return lab.astype(np.int32)
 
 
+def remove_small_objects(mask: np.ndarray, min_size: int) -> np.ndarray:
+    """`skimage.morphology.remove_small_objects(mask, min_size)` (ref: analysis_deployment.py:166), restated: components
+    under connectivity 1, sizes by bincount, those with fewer than min_size pixels removed."""
+    mask = np.asarray(mask) != 0
+    lab, _ = ndi.label(mask, structure=ndi.generate_binary_structure(mask.ndim, 1))
+    sizes = np.bincount(lab.ravel())
+    too_small = sizes < min_size
+    out = mask.copy()
+    out[too_small[lab]] = False
+    return out
+
+
+def disk(radius: int) -> np.ndarray:
+    """`skimage.morphology.disk(radius)`: (X^2 + Y^2) <= radius^2 on a (2r+1)^2 grid."""
+    L = np.arange(-radius, radius + 1)
+    X, Y = np.meshgrid(L, L)
+    return (X**2 + Y**2) <= radius**2
+
+
+def binary_closing_disk(mask: np.ndarray, radius: int = 4) -> np.ndarray:
+    """ref: analysis_deployment.py:169 — ndi.binary_closing(binary, structure=morphology.disk(4))."""
+    return ndi.binary_closing(np.asarray(mask) != 0, structure=disk(radius))
+
+
+def distance_transform_edt(mask: np.ndarray) -> np.ndarray:
+    """ref: analysis_deployment.py:170 — ndi.distance_transform_edt(closed), fp64."""
+    return ndi.distance_transform_edt(np.asarray(mask) != 0)
+
+
 def regionprops_table(labels: np.ndarray, pixel_size_nm: float = 5.0) -> Dict[str, list]:
     """The property loop of ref: analysis_deployment.py:256-271, with skimage's definitions (Appendix C):
 
