@@ -1,7 +1,8 @@
 // Pre-/post-processing statistics and elementwise kernels (HBM-bound; no tensor cores by design).
 //
 //   be_meanvar_f32     one pass, shifted fp64 sums, deterministic two-stage reduction
-//   be_quantile_f32    exact order statistics by 3-level (11/11/10 bit) radix select + numpy's linear lerp
+//   be_quantile_f32    exact order statistics + numpy's linear lerp: sampled-pivot single pass for large segments
+//                      (qsel_sample / partition / task kernels), 3-level (11/11/10 bit) radix select otherwise
 //   be_normalize_f32   (x - sub) / div in fp64, optional clip
 //   be_elementwise_f32 clip / scale_linear / sigmoid
 //   be_binarize_f32_u8 x > thr

@@ -1,0 +1,56 @@
+"""Wire formats of the model-runner data path: `.npy` in, `.npy` out (minimal).
+
+The reference moves arrays as `.npy` files over presigned-S3 HTTP (`np.load(BytesIO(...))` / `np.save`, ref:
+apps/model-runner/entry_deployment.py:1196-1300, bioengine/cli/utils.py:93-212) and `analyze` even takes nested Python
+lists.  Here a `.npy` file is memory-mapped, copied once into a reusable pinned staging buffer and uploaded
+asynchronously, and results are written from a pinned download buffer — no intermediate pageable copies.
+PNG / TIFF decoding is not implemented (imageio / tifffile are not available offline).
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import numpy as np
+import torch
+
+
+class PinnedStaging:
+    """Grow-only pinned host buffer reused across requests (one per replica)."""
+
+    def __init__(self):
+        self._buf: Optional[torch.Tensor] = None
+
+    def view(self, shape, dtype: torch.dtype) -> torch.Tensor:
+        n = int(np.prod(shape)) * torch.empty((), dtype=dtype).element_size()
+        if self._buf is None or self._buf.numel() < n:
+            self._buf = torch.empty(max(n, 1 << 20), dtype=torch.uint8).pin_memory()
+        return self._buf[:n].view(dtype).view(*shape)
+
+
+_NP2TORCH = {np.dtype(k): v for k, v in {
+    "float32": torch.float32, "float64": torch.float64, "uint8": torch.uint8, "int16": torch.int16,
+    "int32": torch.int32, "int64": torch.int64, "float16": torch.float16, "bool": torch.bool}.items()}
+
+
+def load_npy_to_device(path: str, device="cuda:0", staging: Optional[PinnedStaging] = None,
+                       dtype: torch.dtype = torch.float32) -> torch.Tensor:
+    """`.npy` file → device tensor of `dtype` (uint16 microscope frames are widened on the way; torch has no uint16
+    arithmetic, so they are staged as int32)."""
+    arr = np.load(path, mmap_mode="r", allow_pickle=False)
+    if arr.dtype == np.uint16:
+        arr = arr.astype(np.int32)
+    if arr.dtype not in _NP2TORCH:
+        raise ValueError(f"unsupported .npy dtype {arr.dtype}")
+    staging = staging or PinnedStaging()
+    host = staging.view(arr.shape, _NP2TORCH[arr.dtype])
+    np.copyto(host.numpy(), arr)  # the only host-side copy: file pages → pinned memory
+    return host.to(device, non_blocking=True).to(dtype)
+
+
+def save_npy_from_device(path: str, t: torch.Tensor, staging: Optional[PinnedStaging] = None) -> None:
+    """device tensor → `.npy` file through a pinned download buffer."""
+    staging = staging or PinnedStaging()
+    host = staging.view(tuple(t.shape), t.dtype)
+    host.copy_(t, non_blocking=True)
+    torch.cuda.current_stream(t.device).synchronize()
+    np.save(path, host.numpy())

@@ -162,3 +162,19 @@ def test_entry_deployment_infer_mirrors_the_reference_call(tmp_path, dev):
         asyncio.run(entry.infer("no-such-model", img))
     with pytest.raises(ValueError):
         asyncio.run(entry.infer("tiny-unet", "https://example.org/x.npy"))
+
+
+def test_npy_wire_path_round_trip(tmp_path, dev):
+    from bioengine_worker_b200 import io as bio
+
+    rng = np.random.default_rng(0)
+    staging = bio.PinnedStaging()
+    for arr in (rng.random((3, 40, 50)).astype(np.float32), rng.integers(0, 65535, (64, 64)).astype(np.uint16),
+                rng.integers(0, 255, (5, 7)).astype(np.uint8)):
+        p = tmp_path / "a.npy"
+        np.save(p, arr)
+        t = bio.load_npy_to_device(str(p), dev, staging)
+        assert t.dtype == torch.float32 and np.array_equal(t.cpu().numpy(), arr.astype(np.float32))
+    lab = torch.arange(24, dtype=torch.int32, device=dev).reshape(4, 6)
+    bio.save_npy_from_device(str(tmp_path / "out.npy"), lab, staging)
+    assert np.array_equal(np.load(tmp_path / "out.npy"), lab.cpu().numpy())
