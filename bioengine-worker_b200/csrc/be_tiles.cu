@@ -118,6 +118,7 @@ struct Epilogue {
     int mode;   // BE_EPI_*
     int fast;   // 1: mask only, sigmoid decided by the band test
     float thr, lo, hi;
+    double lo2, hi2;  // the same band, a little wider, for the division-free test acc <> wacc * bound (row-walking blend)
 };
 
 __device__ __forceinline__ void finish4(float* __restrict__ out, uint8_t* __restrict__ mask, int64_t o, int cnt,
@@ -297,15 +298,245 @@ __global__ void __launch_bounds__(kThreads) stitch_blend_kernel(const float* __r
     }
 }
 
+// In-band pixels of the division-free test: the exact quotient and numpy's fp32 sigmoid.  Out of line on purpose: a
+// vanishing fraction of pixels gets here and the inlined code would cost every thread registers.
+static __device__ __noinline__ bool blend_decide_exact(double acc, double wacc, float lo, float hi, float thr) {
+    const float v = be_div_to_f32(acc, wacc, be_fast_rcp(wacc));
+    return (v > hi) || (!(v < lo) && be_sigmoid_f32(v) > thr);
+}
+
+// Row-walking variant for the usual geometry (Bx <= 2*Sx, By <= 2*Sy; Sx, Bx, X multiples of 4; 16-byte aligned
+// buffers): every 4-px unit is covered by the same one or two tiles along x and every tile access is one aligned
+// 16-byte load.  A thread owns one unit and walks the rows of its band, so the x cover, its eight window values and the
+// tile offsets live in registers for the whole band and a row costs only the y cover plus the arithmetic.
+//
+// Latency: the 16-byte tile loads of the step two ahead are issued with cp.async into the thread's own shared-memory
+// slots (kStages x 4 slots x 16 B per thread), so every thread keeps 2..8 loads in flight without holding them in
+// registers.  A thread only ever reads the slots it filled itself: cp.async.wait_group is the only synchronisation.
+// A step is one (row, kz) pair — the kz tiles of a row are consecutive steps adding into the same accumulators, in the
+// reference's ascending (kz, ky, kx) order.
+//
+// FAST (mask-only sigmoid): a pixel is decided by acc <> wacc * bound (one DMUL instead of the exact division) unless it
+// falls in the safety band around logit(thr); only those pixels take the division and numpy's fp32 sigmoid.
+// Block: bx = 1 << log2_bx threads along x, kThreads / bx rows in flight; grid (x blocks, row bands, planes).
+constexpr int kStages = 3;
+
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(gmem)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+template <int OFF>
+__device__ __forceinline__ void cp_async16_at(unsigned smem, const char* gmem) {
+    asm volatile("cp.async.cg.shared.global [%0+%2], [%1], 16;" ::"r"(smem), "l"(gmem), "n"(OFF) : "memory");
+}
+
+constexpr int kSlotBytes = kThreads * 16;     // one slot of every thread
+constexpr int kStageBytes = 4 * kSlotBytes;   // (ky_lo | ky_lo+1) x (kxa | kxb)
+
+// Position of one thread's walk over its steps (row, kz), in order.  Everything a step needs is kept incrementally:
+// `k` = kz - kz_lo, `iy` = in-tile row of the first covering tile (the second one, if any, is at iy - Sy), `nky` = tiles
+// covering this row along y (1 or 2), `change` = first row at which the y cover differs.
+struct StepCursor {
+    int y, k, iy, nky, ky_lo, change;
+    __device__ __forceinline__ void set_row(int y_, const Dims& d, const Strides& s) {
+        int hi;
+        y = y_;
+        cover(y, d.By, s.Sy, s.rSy, d.Ty, &ky_lo, &hi);
+        nky = hi - ky_lo + 1;
+        iy = y - ky_lo * s.Sy;
+        const int up = (hi + 1 < d.Ty) ? (hi + 1) * s.Sy : 0x7fffffff;
+        change = min(up, ky_lo * s.Sy + d.By);
+    }
+};
+
+template <bool FAST>
+__global__ void __launch_bounds__(kThreads, 3) stitch_blend_rows_kernel(const float* __restrict__ tiles, float* __restrict__ out,
+                                                                        uint8_t* __restrict__ mask, Dims d, Strides s,
+                                                                        const double* __restrict__ wz,
+                                                                        const double* __restrict__ wy,
+                                                                        const double* __restrict__ wx, Epilogue e,
+                                                                        int units_per_row, unsigned n_planes, int log2_bx,
+                                                                        int rows_per_band) {
+    __shared__ __align__(16) unsigned char s_buf[kStages * kStageBytes];
+    const int tid = threadIdx.x;
+    const int tx = tid & ((1 << log2_bx) - 1), ty = tid >> log2_bx;
+    const int u = (blockIdx.x << log2_bx) + tx;
+    if (u >= units_per_row) return;
+    const int r_step = kThreads >> log2_bx;
+    const int x0 = u * 4;
+    int kxa, kxb;
+    cover(x0, d.Bx, s.Sx, s.rSx, d.Tx, &kxa, &kxb);
+    const bool two = kxb > kxa;
+    const int ixa = x0 - kxa * s.Sx, ixb = x0 - kxb * s.Sx;
+    double wxa[4], wxb[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        wxa[j] = wx[ixa + j];
+        wxb[j] = wx[ixb + j];
+    }
+    // byte offsets between the tiles of one step, and between consecutive rows of this thread
+    const int64_t offa = (kxa * s.tile_stride + ixa) * 4;
+    const int64_t dkx = ((kxb - kxa) * s.tile_stride + (ixb - ixa)) * 4;
+    const int64_t dky = ((int64_t)d.Tx * s.tile_stride - (int64_t)s.Sy * d.Bx) * 4;
+    const int64_t dkz = ((int64_t)d.Ty * d.Tx * s.tile_stride - (int64_t)s.Sz * d.By * d.Bx) * 4;
+    const int64_t drow = (int64_t)r_step * d.Bx * 4;
+    const int y_begin = blockIdx.y * rows_per_band + ty, y_end = min((int)d.Y, (int)(blockIdx.y + 1) * rows_per_band);
+    if (y_begin >= y_end) return;
+    const int n_rows = (y_end - y_begin + r_step - 1) / r_step;
+    const unsigned smem0 = (unsigned)__cvta_generic_to_shared(s_buf) + tid * 16;
+    const float4* lds0 = reinterpret_cast<const float4*>(s_buf) + tid;
+    // division-free band test: |acc - wacc*mid| > wacc*half  <=>  acc/wacc outside [lo2, hi2]
+    const double mid = 0.5 * (e.hi2 + e.lo2), half = 0.5 * (e.hi2 - e.lo2) * (1.0 + 0x1p-30);
+
+    for (unsigned plane = blockIdx.z; plane < n_planes; plane += gridDim.z) {
+        int z = 0, c = 0;
+        int64_t n = 0;
+        if (n_planes > 1) {
+            z = plane % (unsigned)d.Z;
+            const unsigned nc = plane / (unsigned)d.Z;
+            c = nc % (unsigned)d.C;
+            n = nc / (unsigned)d.C;
+        }
+        int kz_lo = 0, kz_hi = 0;
+        if (d.Z > 1) cover(z, d.Bz, s.Sz, s.rSz, d.Tz, &kz_lo, &kz_hi);
+        const int nkz = kz_hi - kz_lo + 1;
+        const int iz0 = z - kz_lo * s.Sz;
+        const int total = n_rows * nkz;
+        // tile (n, kz_lo, ky = 0, kx = 0), channel c, plane iz0, row 0 -- plus this thread's x offset
+        const char* plane_base = reinterpret_cast<const char*>(
+                                     tiles + ((n * d.Tz + kz_lo) * d.Ty * d.Tx) * s.tile_stride +
+                                     ((int64_t)c * d.Bz + iz0) * d.By * d.Bx) + offa;
+        auto row_ptr = [&](const StepCursor& q) {
+            return plane_base + ((int64_t)q.ky_lo * d.Tx * s.tile_stride + (int64_t)q.iy * d.Bx) * 4;
+        };
+
+        StepCursor qi, qc;
+        qi.set_row(y_begin, d, s);
+        qi.k = 0;
+        qc = qi;
+        const char* pi = row_ptr(qi);   // issue pointer: slot (kz_lo, ky_lo, kxa) of the issue row
+        uint8_t* mrow = mask ? mask + ((int64_t)plane * d.Y + y_begin) * d.X + x0 : nullptr;
+        float* orow = out ? out + ((int64_t)plane * d.Y + y_begin) * d.X + x0 : nullptr;
+        const int64_t dout = (int64_t)r_step * d.X;
+
+        auto issue = [&](unsigned sm) {
+            const char* p = pi + qi.k * dkz;
+            cp_async16_at<0>(sm, p);
+            if (two) cp_async16_at<kSlotBytes>(sm, p + dkx);
+            if (qi.nky > 1) {
+                cp_async16_at<2 * kSlotBytes>(sm, p + dky);
+                if (two) cp_async16_at<3 * kSlotBytes>(sm, p + dky + dkx);
+            }
+            if (++qi.k == nkz) {
+                qi.k = 0;
+                pi += drow;
+                qi.y += r_step;
+                qi.iy += r_step;
+                if (qi.y >= qi.change && qi.y < y_end) {
+                    qi.set_row(qi.y, d, s);
+                    pi = row_ptr(qi);
+                }
+            }
+        };
+
+        int ti = 0;
+#pragma unroll
+        for (int k = 0; k < kStages - 1; ++k) {
+            if (ti < total) issue(smem0 + k * kStageBytes);
+            cp_async_commit();
+            ++ti;
+        }
+        double acc[4] = {0.0, 0.0, 0.0, 0.0}, wacc[4] = {0.0, 0.0, 0.0, 0.0};
+        int st_c = 0, st_i = kStages - 1;
+        for (int t = 0; t < total; ++t, ++ti) {
+            if (ti < total) issue(smem0 + st_i * kStageBytes);
+            cp_async_commit();
+            cp_async_wait<kStages - 1>();
+
+            const double wzv = wz[iz0 - qc.k * s.Sz];
+            const float4* sc = lds0 + st_c * (kStageBytes / 16);
+#pragma unroll
+            for (int jy = 0; jy < 2; ++jy) {
+                if (jy < qc.nky) {
+                    const double wzy = __dmul_rn(wzv, wy[qc.iy - jy * s.Sy]);
+                    {
+                        const float4 p = sc[(2 * jy) * kThreads];
+                        const float pv[4] = {p.x, p.y, p.z, p.w};
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            const float w = (float)__dmul_rn(wzy, wxa[j]);
+                            acc[j] = __dadd_rn(acc[j], (double)__fmul_rn(pv[j], w));
+                            wacc[j] = __dadd_rn(wacc[j], (double)w);
+                        }
+                    }
+                    if (two) {
+                        const float4 p = sc[(2 * jy + 1) * kThreads];
+                        const float pv[4] = {p.x, p.y, p.z, p.w};
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            const float w = (float)__dmul_rn(wzy, wxb[j]);
+                            acc[j] = __dadd_rn(acc[j], (double)__fmul_rn(pv[j], w));
+                            wacc[j] = __dadd_rn(wacc[j], (double)w);
+                        }
+                    }
+                }
+            }
+            if (++qc.k == nkz) {  // last kz of this row: finish the four pixels
+                qc.k = 0;
+                if (FAST) {
+                    unsigned bits = 0;
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const double dlt = fma(wacc[j], -mid, acc[j]);
+                        // wacc is a positive normal number (high word > 0; a NaN also passes and lands in the exact
+                        // path through the comparison below) and the quotient is clear of the band
+                        bool m = dlt > 0.0;
+                        if (!(__double2hiint(wacc[j]) > 0 && fabs(dlt) > __dmul_rn(wacc[j], half)))
+                            m = blend_decide_exact(acc[j], wacc[j], e.lo, e.hi, e.thr);
+                        bits |= (m ? 1u : 0u) << (8 * j);
+                    }
+                    *reinterpret_cast<unsigned*>(mrow) = bits;
+                    mrow += dout;
+                } else {
+                    float v[4];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) v[j] = be_div_to_f32(acc[j], wacc[j], be_fast_rcp(wacc[j]));
+                    finish4(orow, mrow, 0, 4, v, e, true);
+                    if (orow) orow += dout;
+                    if (mrow) mrow += dout;
+                }
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[j] = wacc[j] = 0.0;
+                qc.y += r_step;
+                qc.iy += r_step;
+                if (qc.y >= qc.change && qc.y < y_end) qc.set_row(qc.y, d, s);
+            }
+            st_c = (st_c + 1 == kStages) ? 0 : st_c + 1;
+            st_i = (st_i + 1 == kStages) ? 0 : st_i + 1;
+        }
+        cp_async_wait<0>();
+    }
+}
+
 // Host side of the band test: sigmoid'(x) = s(1-s) >= 0.0099 for thr in [0.01, 0.99], so 1e-4 away from logit(thr) the
 // true sigmoid is >= 9.9e-7 away from thr, while the fp32 evaluation is good to a few ulp (<= 2.4e-7 near 1).
 Epilogue make_epilogue(int mode, float thr, bool mask_only) {
-    Epilogue e{mode, 0, thr, 0.f, 0.f};
+    Epilogue e{mode, 0, thr, 0.f, 0.f, 0.0, 0.0};
     if (mode == BE_EPI_SIGMOID && mask_only && thr >= 0.01f && thr <= 0.99f) {
         const double L = log((double)thr / (1.0 - (double)thr));
         e.fast = 1;
         e.lo = (float)(L - 1e-4);
         e.hi = (float)(L + 1e-4);
+        // acc > wacc * hi2 (wacc > 0) puts the exact quotient above hi * (1 + 2^-21) >= the next float after hi, and
+        // rounding is monotone, so float(acc / wacc) > hi; the absolute 2^-100 covers hi == 0.  Same for lo2.
+        e.hi2 = (double)e.hi + fabs((double)e.hi) * 0x1p-20 + 0x1p-100;
+        e.lo2 = (double)e.lo - fabs((double)e.lo) * 0x1p-20 - 0x1p-100;
     }
     return e;
 }
@@ -410,9 +641,32 @@ extern "C" int be_stitch_blend_f32(const float* tiles, float* out, uint8_t* mask
     dim3 grid;
     rc = stitch_grid("be_stitch_blend_f32", d, upr, &grid);
     if (rc) return rc;
-    stitch_blend_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(tiles, out, mask, d, st, wz, wy, wx,
-                                                                     make_epilogue(epilogue, thr, out == nullptr), upr,
-                                                                     (unsigned)(N * C * Z));
+    const Epilogue e = make_epilogue(epilogue, thr, out == nullptr);
+    const bool aligned16 = ((((uintptr_t)tiles) | ((uintptr_t)out)) & 15) == 0 && (((uintptr_t)mask) & 3) == 0 &&
+                           (((uintptr_t)wx) & 7) == 0;
+    if (Bx <= 2 * Sx && By <= 2 * Sy && (Sx & 3) == 0 && (Bx & 3) == 0 && (X & 3) == 0 && aligned16) {
+        int log2_bx = 5;
+        while ((1 << log2_bx) < upr && (1 << log2_bx) < kThreads) ++log2_bx;
+        const int r_step = kThreads >> log2_bx;
+        const unsigned xblocks = (unsigned)((upr + (1 << log2_bx) - 1) >> log2_bx);
+        // row bands: ~16 blocks per SM in total, at least 4 rows per thread where the image allows
+        const int64_t want = (int64_t)BE_SM_COUNT * 16;
+        int64_t bands = want / ((int64_t)xblocks * grid.z) + 1;
+        const int64_t max_bands = (Y + 4 * r_step - 1) / (4 * r_step);
+        if (bands > max_bands) bands = max_bands;
+        if (bands > 65535) bands = 65535;
+        const int rows_per_band = (int)((Y + bands - 1) / bands);
+        const dim3 g2(xblocks, (unsigned)((Y + rows_per_band - 1) / rows_per_band), grid.z);
+        if (e.fast)
+            stitch_blend_rows_kernel<true><<<g2, kThreads, 0, (cudaStream_t)stream>>>(
+                tiles, out, mask, d, st, wz, wy, wx, e, upr, (unsigned)(N * C * Z), log2_bx, rows_per_band);
+        else
+            stitch_blend_rows_kernel<false><<<g2, kThreads, 0, (cudaStream_t)stream>>>(
+                tiles, out, mask, d, st, wz, wy, wx, e, upr, (unsigned)(N * C * Z), log2_bx, rows_per_band);
+    } else {
+        stitch_blend_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(tiles, out, mask, d, st, wz, wy, wx, e, upr,
+                                                                         (unsigned)(N * C * Z));
+    }
     BE_LAUNCH_CHECK();
     return BE_OK;
 }
