@@ -307,97 +307,184 @@ static __device__ __noinline__ bool blend_decide_exact(double acc, double wacc, 
 
 // Row-walking variant for the usual geometry (Bx <= 2*Sx, By <= 2*Sy; Sx, Bx, X multiples of 4; 16-byte aligned
 // buffers): every 4-px unit is covered by the same one or two tiles along x and every tile access is one aligned
-// 16-byte load.  A thread owns one unit and walks the rows of its band, so the x cover, its eight window values and the
-// tile offsets live in registers for the whole band and a row costs only the y cover plus the arithmetic.
+// 16-byte read.  A block owns an x range of bx*4 pixels and a band of rows; a thread owns one 4-px unit and walks the
+// rows, so its x cover, eight window values and shared-memory offsets live in registers for the whole band.
 //
-// Latency: the 16-byte tile loads of the step two ahead are issued with cp.async into the thread's own shared-memory
-// slots (kStages x 4 slots x 16 B per thread), so every thread keeps 2..8 loads in flight without holding them in
-// registers.  A thread only ever reads the slots it filled itself: cp.async.wait_group is the only synchronisation.
-// A step is one (row, kz) pair — the kz tiles of a row are consecutive steps adding into the same accumulators, in the
-// reference's ascending (kz, ky, kx) order.
+// Data movement: the tile rows a step needs are contiguous runs of the tile buffer, so warp 0 fetches them with TMA bulk
+// copies (cp.async.bulk, one per tile row segment, clipped to the block's x range) into a kStages-deep ring of
+// shared-memory stages, two steps ahead of the arithmetic; an mbarrier per stage counts the bytes in.  The other
+// warps issue no loads at all.  A step is one (row group, kz) pair — the kz tiles of a row are consecutive steps
+// adding into the same accumulators, in the reference's ascending (kz, ky, kx) order.
 //
-// FAST (mask-only sigmoid): a pixel is decided by acc <> wacc * bound (one DMUL instead of the exact division) unless it
-// falls in the safety band around logit(thr); only those pixels take the division and numpy's fp32 sigmoid.
-// Block: bx = 1 << log2_bx threads along x, kThreads / bx rows in flight; grid (x blocks, row bands, planes).
-constexpr int kStages = 3;
+// FAST (mask-only sigmoid): a pixel is decided by |acc - wacc*mid| > wacc*half (one DFMA + DMUL instead of the exact
+// division) unless it falls in the safety band around logit(thr); only those take the division and numpy's sigmoid.
+// Block: bx = 1 << log2_bx threads along x, r_step = kThreads / bx rows per step; grid (x blocks, row bands, planes).
+// measured on the 4096^2 / 256-px-tile workload: 3..5 stages within 2 %; 3 blocks of 72 registers per SM beat both
+// 2 x 96 (too few warps to hide the fp64 / conversion latencies) and 4 x 56 (spills)
+constexpr int kStages = 4;
 
-__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(gmem)
+__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(unsigned dst, const void* src, unsigned bytes, unsigned bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                 "l"(src), "r"(bytes), "r"(bar)
                  : "memory");
 }
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() {
-    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
+    unsigned ok = 0;
+    for (int spin = 0; !ok; ++spin) {
+        asm volatile(
+            "{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+            : "=r"(ok)
+            : "r"(bar), "r"(parity)
+            : "memory");
+        if (spin > (1 << 22)) __trap();  // a byte count that never arrives is a bug, not something to wait out
+    }
 }
 
-template <int OFF>
-__device__ __forceinline__ void cp_async16_at(unsigned smem, const char* gmem) {
-    asm volatile("cp.async.cg.shared.global [%0+%2], [%1], 16;" ::"r"(smem), "l"(gmem), "n"(OFF) : "memory");
+__device__ __forceinline__ bool mbar_try_wait(unsigned bar, unsigned parity) {
+    unsigned ok;
+    asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                 : "=r"(ok)
+                 : "r"(bar), "r"(parity)
+                 : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ float4 lds128(unsigned addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+    return v;
+}
+// four pixels of one tile row into the accumulators: w = fp32(wzy * wx), acc += fp64(fp32(p * w)), wacc += fp64(w)
+__device__ __forceinline__ double2 lds_d2(unsigned addr) {
+    double2 v;
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ void blend_add4(const float4 p, const double wzy, unsigned w_addr, unsigned w_half,
+                                           double (&acc)[4], double (&wacc)[4]) {
+    const float pv[4] = {p.x, p.y, p.z, p.w};
+    const double2 w01 = lds_d2(w_addr), w23 = lds_d2(w_addr + w_half);
+    const double wx4[4] = {w01.x, w01.y, w23.x, w23.y};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const float w = (float)__dmul_rn(wzy, wx4[j]);
+        acc[j] = __dadd_rn(acc[j], (double)__fmul_rn(pv[j], w));
+        wacc[j] = __dadd_rn(wacc[j], (double)w);
+    }
 }
 
-constexpr int kSlotBytes = kThreads * 16;     // one slot of every thread
-constexpr int kStageBytes = 4 * kSlotBytes;   // (ky_lo | ky_lo+1) x (kxa | kxb)
+// launch-invariant numbers of the row-walking kernel, worked out by the host so that they are constant-bank operands
+struct RowsConst {
+    int64_t dky, dkz;        // element steps in the tile buffer: next tile along y / z (same in-tile position + stride)
+    int64_t dout;            // element step in the output: next row of this thread
+    double mid, half;        // division-free band test: |acc - wacc*mid| > wacc*half  <=>  acc/wacc outside [lo2, hi2]
+    int log2_bx, rows_per_band, units_per_row;
+    int slot_bytes, stage_bytes;   // shared memory: one (row, ky slot) = nseg tile rows; one stage = r_step rows x 2 slots
+    unsigned n_planes;
+};
 
-// Position of one thread's walk over its steps (row, kz), in order.  Everything a step needs is kept incrementally:
-// `k` = kz - kz_lo, `iy` = in-tile row of the first covering tile (the second one, if any, is at iy - Sy), `nky` = tiles
-// covering this row along y (1 or 2), `change` = first row at which the y cover differs.
-struct StepCursor {
-    int y, k, iy, nky, ky_lo, change;
-    __device__ __forceinline__ void set_row(int y_, const Dims& d, const Strides& s) {
+// tiles covering row y along y: first tile, how many (1 or 2), first row at which this changes
+struct RowCover {
+    int ky_lo, nky, change;
+    __device__ __forceinline__ void set(int y, const Dims& d, const Strides& s) {
         int hi;
-        y = y_;
         cover(y, d.By, s.Sy, s.rSy, d.Ty, &ky_lo, &hi);
         nky = hi - ky_lo + 1;
-        iy = y - ky_lo * s.Sy;
         const int up = (hi + 1 < d.Ty) ? (hi + 1) * s.Sy : 0x7fffffff;
         change = min(up, ky_lo * s.Sy + d.By);
     }
 };
 
+constexpr int kRowsThreads = kThreads + 32;   // eight arithmetic warps + the copy warp
+
 template <bool FAST>
-__global__ void __launch_bounds__(kThreads, 3) stitch_blend_rows_kernel(const float* __restrict__ tiles, float* __restrict__ out,
-                                                                        uint8_t* __restrict__ mask, Dims d, Strides s,
-                                                                        const double* __restrict__ wz,
+__global__ void __launch_bounds__(kRowsThreads, 3) stitch_blend_rows_kernel(const float* __restrict__ tiles, float* __restrict__ out,
+                                                                        uint8_t* __restrict__ mask, const Dims d,
+                                                                        const Strides s, const double* __restrict__ wz,
                                                                         const double* __restrict__ wy,
-                                                                        const double* __restrict__ wx, Epilogue e,
-                                                                        int units_per_row, unsigned n_planes, int log2_bx,
-                                                                        int rows_per_band) {
-    __shared__ __align__(16) unsigned char s_buf[kStages * kStageBytes];
+                                                                        const double* __restrict__ wx, const Epilogue e,
+                                                                        const RowsConst k) {
+    extern __shared__ __align__(128) unsigned char s_dyn[];
+    __shared__ __align__(8) unsigned long long s_bar[2 * kStages];   // full[kStages], empty[kStages]
     const int tid = threadIdx.x;
+    const int log2_bx = k.log2_bx;
     const int tx = tid & ((1 << log2_bx) - 1), ty = tid >> log2_bx;
-    const int u = (blockIdx.x << log2_bx) + tx;
-    if (u >= units_per_row) return;
     const int r_step = kThreads >> log2_bx;
-    const int x0 = u * 4;
+    const int u = (blockIdx.x << log2_bx) + tx;
+    const bool x_live = u < k.units_per_row;
+    const int x0 = min(u, k.units_per_row - 1) * 4;
+    const int X0 = (blockIdx.x << log2_bx) * 4, X1 = min((int)d.X, X0 + (4 << log2_bx));   // the block's x range
+    // tiles overlapping the block's x range: the segments of a stage
+    int seg_first, seg_last;
+    cover(X0, d.Bx, s.Sx, s.rSx, d.Tx, &seg_first, &seg_last);
+    seg_last = min(d.Tx - 1, be_fast_div(X1 - 1, s.Sx, s.rSx));
+    const int seg_bytes = d.Bx * 4;                      // a segment slot holds a whole tile row
+    const int slot_bytes = k.slot_bytes;                 // one (row, ky slot): nseg segments
+    const int stage_bytes = k.stage_bytes;               // r_step rows x 2 ky slots
+    const unsigned smem0 = (unsigned)__cvta_generic_to_shared(s_dyn);
+    const unsigned bar0 = (unsigned)__cvta_generic_to_shared(s_bar);
+
     int kxa, kxb;
     cover(x0, d.Bx, s.Sx, s.rSx, d.Tx, &kxa, &kxb);
     const bool two = kxb > kxa;
     const int ixa = x0 - kxa * s.Sx, ixb = x0 - kxb * s.Sx;
-    double wxa[4], wxb[4];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-        wxa[j] = wx[ixa + j];
-        wxb[j] = wx[ixb + j];
+    // the x window lives in shared memory behind the stages, split so that a warp's reads are contiguous:
+    // A[u] = (wx[4u], wx[4u+1]), B[u] = (wx[4u+2], wx[4u+3]); a thread reads entries ixa/4 and ixb/4
+    const unsigned wxs = smem0 + kStages * stage_bytes;
+    for (int i = tid; i < d.Bx / 4; i += kRowsThreads) {
+        double2* A = reinterpret_cast<double2*>(s_dyn + kStages * stage_bytes);
+        double2* B = A + d.Bx / 4;
+        A[i] = make_double2(wx[4 * i], wx[4 * i + 1]);
+        B[i] = make_double2(wx[4 * i + 2], wx[4 * i + 3]);
     }
-    // byte offsets between the tiles of one step, and between consecutive rows of this thread
-    const int64_t offa = (kxa * s.tile_stride + ixa) * 4;
-    const int64_t dkx = ((kxb - kxa) * s.tile_stride + (ixb - ixa)) * 4;
-    const int64_t dky = ((int64_t)d.Tx * s.tile_stride - (int64_t)s.Sy * d.Bx) * 4;
-    const int64_t dkz = ((int64_t)d.Ty * d.Tx * s.tile_stride - (int64_t)s.Sz * d.By * d.Bx) * 4;
-    const int64_t drow = (int64_t)r_step * d.Bx * 4;
-    const int y_begin = blockIdx.y * rows_per_band + ty, y_end = min((int)d.Y, (int)(blockIdx.y + 1) * rows_per_band);
-    if (y_begin >= y_end) return;
-    const int n_rows = (y_end - y_begin + r_step - 1) / r_step;
-    const unsigned smem0 = (unsigned)__cvta_generic_to_shared(s_buf) + tid * 16;
-    const float4* lds0 = reinterpret_cast<const float4*>(s_buf) + tid;
-    // division-free band test: |acc - wacc*mid| > wacc*half  <=>  acc/wacc outside [lo2, hi2]
-    const double mid = 0.5 * (e.hi2 + e.lo2), half = 0.5 * (e.hi2 - e.lo2) * (1.0 + 0x1p-30);
+    const unsigned wa = wxs + ixa * 4, wb = wxs + ixb * 4, wB = d.Bx * 4;   // byte addresses of A[ix/4]; B is wB further
+    // this thread's two 16-byte reads inside a (row, ky slot): byte offsets from the start of a stage
+    const int lda = (ty * 2) * slot_bytes + (kxa - seg_first) * seg_bytes + ixa * 4;
+    const int ab = (kxb - kxa) * seg_bytes + (ixb - ixa) * 4;   // from the read of the first x tile to the second
 
-    for (unsigned plane = blockIdx.z; plane < n_planes; plane += gridDim.z) {
+    const int band_begin = blockIdx.y * k.rows_per_band, y_end = min((int)d.Y, band_begin + k.rows_per_band);
+    const int n_groups = (y_end - band_begin + r_step - 1) / r_step;
+
+    // producer lane i of warp 0 owns segment i: the part of tile row (kx = seg_first + i) inside [X0, X1)
+    const bool producer = tid >= kThreads;
+    const int lane = tid & 31;
+    int seg_src = 0, seg_dst = 0, seg_len = 0;   // element offset in the tile row, byte offset in the slot, bytes
+    if (producer) {
+        const int kx = seg_first + lane;
+        if (kx <= seg_last) {
+            const int xs = max(kx * s.Sx, X0), xe = min(kx * s.Sx + d.Bx, X1);
+            seg_src = xs - kx * s.Sx;
+            seg_dst = lane * seg_bytes + seg_src * 4;
+            seg_len = (xe - xs) * 4;
+        }
+    }
+    int row_bytes = seg_len;   // bytes one (row, ky slot) brings in
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) row_bytes += __shfl_xor_sync(0xffffffffu, row_bytes, o);
+
+    if (tid == 0) {
+#pragma unroll
+        for (int i = 0; i < kStages; ++i) {
+            mbar_init(bar0 + 8 * i, 1);                           // full: the copy warp's expect_tx arrival + the bytes
+            mbar_init(bar0 + 8 * (kStages + i), kThreads / 32);   // empty: one arrival per arithmetic warp
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    unsigned use = 0;   // steps this warp has been through (stage = use % kStages, parity = (use / kStages) & 1)
+
+    for (unsigned plane = blockIdx.z; plane < k.n_planes; plane += gridDim.z) {
         int z = 0, c = 0;
         int64_t n = 0;
-        if (n_planes > 1) {
+        if (k.n_planes > 1) {
             z = plane % (unsigned)d.Z;
             const unsigned nc = plane / (unsigned)d.Z;
             c = nc % (unsigned)d.C;
@@ -407,120 +494,144 @@ __global__ void __launch_bounds__(kThreads, 3) stitch_blend_rows_kernel(const fl
         if (d.Z > 1) cover(z, d.Bz, s.Sz, s.rSz, d.Tz, &kz_lo, &kz_hi);
         const int nkz = kz_hi - kz_lo + 1;
         const int iz0 = z - kz_lo * s.Sz;
-        const int total = n_rows * nkz;
-        // tile (n, kz_lo, ky = 0, kx = 0), channel c, plane iz0, row 0 -- plus this thread's x offset
-        const char* plane_base = reinterpret_cast<const char*>(
-                                     tiles + ((n * d.Tz + kz_lo) * d.Ty * d.Tx) * s.tile_stride +
-                                     ((int64_t)c * d.Bz + iz0) * d.By * d.Bx) + offa;
-        auto row_ptr = [&](const StepCursor& q) {
-            return plane_base + ((int64_t)q.ky_lo * d.Tx * s.tile_stride + (int64_t)q.iy * d.Bx) * 4;
-        };
+        const int total = n_groups * nkz;
+        // tile (n, kz_lo, ky = 0, kx = seg_first + lane), channel c, plane iz0, row 0, first element this lane copies
+        const float* lane_base = tiles + ((n * d.Tz + kz_lo) * d.Ty * d.Tx + seg_first + lane) * s.tile_stride +
+                                 ((int64_t)c * d.Bz + iz0) * d.By * d.Bx + seg_src;
 
-        StepCursor qi, qc;
-        qi.set_row(y_begin, d, s);
-        qi.k = 0;
-        qc = qi;
-        const char* pi = row_ptr(qi);   // issue pointer: slot (kz_lo, ky_lo, kxa) of the issue row
-        uint8_t* mrow = mask ? mask + ((int64_t)plane * d.Y + y_begin) * d.X + x0 : nullptr;
-        float* orow = out ? out + ((int64_t)plane * d.Y + y_begin) * d.X + x0 : nullptr;
-        const int64_t dout = (int64_t)r_step * d.X;
-
-        auto issue = [&](unsigned sm) {
-            const char* p = pi + qi.k * dkz;
-            cp_async16_at<0>(sm, p);
-            if (two) cp_async16_at<kSlotBytes>(sm, p + dkx);
-            if (qi.nky > 1) {
-                cp_async16_at<2 * kSlotBytes>(sm, p + dky);
-                if (two) cp_async16_at<3 * kSlotBytes>(sm, p + dky + dkx);
-            }
-            if (++qi.k == nkz) {
-                qi.k = 0;
-                pi += drow;
-                qi.y += r_step;
-                qi.iy += r_step;
-                if (qi.y >= qi.change && qi.y < y_end) {
-                    qi.set_row(qi.y, d, s);
-                    pi = row_ptr(qi);
+        if (producer) {
+            // the copy warp: fetch step after step into the ring, as far ahead as free stages allow
+            for (int ts = 0; ts < total; ++ts, ++use) {
+                const int g = ts / nkz, kk = ts - g * nkz;
+                const unsigned st = use % kStages;
+                const unsigned full = bar0 + 8 * st, empty = bar0 + 8 * (kStages + st);
+                int slots = 0;
+                for (int r = 0; r < r_step; ++r) {
+                    const int y = band_begin + g * r_step + r;
+                    if (y < y_end) {
+                        RowCover rc;
+                        rc.set(y, d, s);
+                        slots += rc.nky;
+                    }
+                }
+                mbar_wait(empty, ((use / kStages) & 1) ^ 1);   // all arithmetic warps are done with this stage
+                if (lane == 0) {
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic reads before async writes
+                    mbar_expect_tx(full, (unsigned)(slots * row_bytes));
+                }
+                __syncwarp();
+                if (seg_len > 0) {
+                    for (int r = 0; r < r_step; ++r) {
+                        const int y = band_begin + g * r_step + r;
+                        if (y >= y_end) break;
+                        RowCover rc;
+                        rc.set(y, d, s);
+                        const float* src = lane_base + kk * k.dkz + (int64_t)rc.ky_lo * d.Tx * s.tile_stride +
+                                           (int64_t)(y - rc.ky_lo * s.Sy) * d.Bx;
+                        const unsigned dst = smem0 + st * stage_bytes + (r * 2) * slot_bytes + seg_dst;
+                        bulk_g2s(dst, src, (unsigned)seg_len, full);
+                        if (rc.nky > 1) bulk_g2s(dst + slot_bytes, src + k.dky, (unsigned)seg_len, full);
+                    }
                 }
             }
-        };
-
-        int ti = 0;
-#pragma unroll
-        for (int k = 0; k < kStages - 1; ++k) {
-            if (ti < total) issue(smem0 + k * kStageBytes);
-            cp_async_commit();
-            ++ti;
+            continue;
         }
+        // arithmetic warps.  Loop-carried state is kept as plain registers that only ever get an add: the stage cursor
+        // (index, parity, shared-memory address of this thread's first read), the row cursor (y, in-tile row, window
+        // pointer, output pointer), the kz cursor.
+        int y = band_begin + ty;
+        RowCover rc;
+        rc.set(min(y, y_end - 1), d, s);
+        int iy = y - rc.ky_lo * s.Sy, kk = 0;
+        bool live = x_live && y < y_end;
+        uint8_t* mrow = mask ? mask + ((int64_t)plane * d.Y + y) * d.X + x0 : nullptr;
+        float* orow = out ? out + ((int64_t)plane * d.Y + y) * d.X + x0 : nullptr;
         double acc[4] = {0.0, 0.0, 0.0, 0.0}, wacc[4] = {0.0, 0.0, 0.0, 0.0};
-        int st_c = 0, st_i = kStages - 1;
-        for (int t = 0; t < total; ++t, ++ti) {
-            if (ti < total) issue(smem0 + st_i * kStageBytes);
-            cp_async_commit();
-            cp_async_wait<kStages - 1>();
+        double wzv = wz[iz0];
+        // y window values of the current row, fetched a step ahead of their use
+        double wy0 = wy[max(iy, 0)], wy1 = (rc.nky > 1) ? wy[iy - s.Sy] : 0.0;
+        unsigned st = use % kStages, par = (use / kStages) & 1;
+        unsigned sa = smem0 + st * stage_bytes + lda;   // this thread's read of the first x tile, ky slot 0
 
-            const double wzv = wz[iz0 - qc.k * s.Sz];
-            const float4* sc = lds0 + st_c * (kStageBytes / 16);
-#pragma unroll
-            for (int jy = 0; jy < 2; ++jy) {
-                if (jy < qc.nky) {
-                    const double wzy = __dmul_rn(wzv, wy[qc.iy - jy * s.Sy]);
-                    {
-                        const float4 p = sc[(2 * jy) * kThreads];
-                        const float pv[4] = {p.x, p.y, p.z, p.w};
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) {
-                            const float w = (float)__dmul_rn(wzy, wxa[j]);
-                            acc[j] = __dadd_rn(acc[j], (double)__fmul_rn(pv[j], w));
-                            wacc[j] = __dadd_rn(wacc[j], (double)w);
-                        }
-                    }
-                    if (two) {
-                        const float4 p = sc[(2 * jy + 1) * kThreads];
-                        const float pv[4] = {p.x, p.y, p.z, p.w};
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) {
-                            const float w = (float)__dmul_rn(wzy, wxb[j]);
-                            acc[j] = __dadd_rn(acc[j], (double)__fmul_rn(pv[j], w));
-                            wacc[j] = __dadd_rn(wacc[j], (double)w);
-                        }
-                    }
+        for (int t = 0; t < total; ++t) {
+            if (!mbar_try_wait(bar0 + 8 * st, par)) mbar_wait(bar0 + 8 * st, par);
+            if (live) {
+                const double wzy0 = __dmul_rn(wzv, wy0);
+                blend_add4(lds128(sa), wzy0, wa, wB, acc, wacc);
+                if (two) blend_add4(lds128(sa + ab), wzy0, wb, wB, acc, wacc);
+                if (rc.nky > 1) {
+                    const double wzy1 = __dmul_rn(wzv, wy1);
+                    blend_add4(lds128(sa + slot_bytes), wzy1, wa, wB, acc, wacc);
+                    if (two) blend_add4(lds128(sa + slot_bytes + ab), wzy1, wb, wB, acc, wacc);
                 }
             }
-            if (++qc.k == nkz) {  // last kz of this row: finish the four pixels
-                qc.k = 0;
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar0 + 8 * (kStages + st));   // this warp has read its part of the stage
+            ++use;
+            sa += stage_bytes;
+            if (++st == kStages) {
+                st = 0;
+                par ^= 1;
+                sa -= kStages * stage_bytes;
+            }
+            if (++kk < nkz) {
+                wzv = wz[iz0 - kk * s.Sz];
+                continue;
+            }
+            // last kz of this row group: finish the four pixels, move to the next group
+            if (live) {
                 if (FAST) {
-                    unsigned bits = 0;
+                    // m = acc/wacc above the band <=> dlt > 0 (sign bit clear; dlt == 0 is inside the band).  The test
+                    // trusts wacc only when it is a positive normal number (high word > 0; a NaN passes that but
+                    // fails the comparison), everything else takes the exact path
+                    unsigned bits = 0, slow = 0;
 #pragma unroll
                     for (int j = 0; j < 4; ++j) {
-                        const double dlt = fma(wacc[j], -mid, acc[j]);
-                        // wacc is a positive normal number (high word > 0; a NaN also passes and lands in the exact
-                        // path through the comparison below) and the quotient is clear of the band
-                        bool m = dlt > 0.0;
-                        if (!(__double2hiint(wacc[j]) > 0 && fabs(dlt) > __dmul_rn(wacc[j], half)))
-                            m = blend_decide_exact(acc[j], wacc[j], e.lo, e.hi, e.thr);
-                        bits |= (m ? 1u : 0u) << (8 * j);
+                        const double dlt = fma(wacc[j], -k.mid, acc[j]);
+                        const bool clear = (fabs(dlt) > __dmul_rn(wacc[j], k.half)) & (__double2hiint(wacc[j]) > 0);
+                        bits |= ((unsigned)(~__double2hiint(dlt)) >> 31) << (8 * j);
+                        slow |= clear ? 0u : (1u << j);
+                    }
+                    if (slow) {
+#pragma unroll
+                        for (int j = 0; j < 4; ++j)
+                            if (slow & (1u << j)) {
+                                const bool m = blend_decide_exact(acc[j], wacc[j], e.lo, e.hi, e.thr);
+                                bits = (bits & ~(0xffu << (8 * j))) | ((m ? 1u : 0u) << (8 * j));
+                            }
                     }
                     *reinterpret_cast<unsigned*>(mrow) = bits;
-                    mrow += dout;
                 } else {
                     float v[4];
 #pragma unroll
                     for (int j = 0; j < 4; ++j) v[j] = be_div_to_f32(acc[j], wacc[j], be_fast_rcp(wacc[j]));
                     finish4(orow, mrow, 0, 4, v, e, true);
-                    if (orow) orow += dout;
-                    if (mrow) mrow += dout;
                 }
-#pragma unroll
-                for (int j = 0; j < 4; ++j) acc[j] = wacc[j] = 0.0;
-                qc.y += r_step;
-                qc.iy += r_step;
-                if (qc.y >= qc.change && qc.y < y_end) qc.set_row(qc.y, d, s);
             }
-            st_c = (st_c + 1 == kStages) ? 0 : st_c + 1;
-            st_i = (st_i + 1 == kStages) ? 0 : st_i + 1;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc[j] = wacc[j] = 0.0;
+            kk = 0;
+            if (nkz > 1) wzv = wz[iz0];
+            y += r_step;
+            iy += r_step;
+            if (FAST) {
+                mrow += k.dout;
+            } else {
+                if (mrow) mrow += k.dout;
+                if (orow) orow += k.dout;
+            }
+            if (y >= rc.change) {
+                live = x_live && y < y_end;
+                if (y < y_end) {
+                    rc.set(y, d, s);
+                    iy = y - rc.ky_lo * s.Sy;
+                }
+            }
+            if (y < y_end) {
+                wy0 = wy[iy];
+                if (rc.nky > 1) wy1 = wy[iy - s.Sy];
+            }
         }
-        cp_async_wait<0>();
     }
 }
 
@@ -644,25 +755,50 @@ extern "C" int be_stitch_blend_f32(const float* tiles, float* out, uint8_t* mask
     const Epilogue e = make_epilogue(epilogue, thr, out == nullptr);
     const bool aligned16 = ((((uintptr_t)tiles) | ((uintptr_t)out)) & 15) == 0 && (((uintptr_t)mask) & 3) == 0 &&
                            (((uintptr_t)wx) & 7) == 0;
-    if (Bx <= 2 * Sx && By <= 2 * Sy && (Sx & 3) == 0 && (Bx & 3) == 0 && (X & 3) == 0 && aligned16) {
-        int log2_bx = 5;
-        while ((1 << log2_bx) < upr && (1 << log2_bx) < kThreads) ++log2_bx;
-        const int r_step = kThreads >> log2_bx;
-        const unsigned xblocks = (unsigned)((upr + (1 << log2_bx) - 1) >> log2_bx);
-        // row bands: ~16 blocks per SM in total, at least 4 rows per thread where the image allows
-        const int64_t want = (int64_t)BE_SM_COUNT * 16;
+    // geometry of the row-walking kernel: bx threads along x, r_step rows per step, nseg tile rows per (row, ky slot)
+    int log2_bx = 5;
+    while ((1 << log2_bx) < upr && (1 << log2_bx) < kThreads) ++log2_bx;
+    const int r_step = kThreads >> log2_bx;
+    const unsigned xblocks = (unsigned)((upr + (1 << log2_bx) - 1) >> log2_bx);
+    int nseg = 0;
+    for (unsigned b = 0; b < xblocks; ++b) {
+        const int64_t X0 = (int64_t)b * (4 << log2_bx), X1 = (X0 + (4 << log2_bx) < X) ? X0 + (4 << log2_bx) : X;
+        const int64_t first = (X0 - Bx + 1 <= 0) ? 0 : (X0 - Bx + 1 + Sx - 1) / Sx;
+        const int64_t last = ((X1 - 1) / Sx < Tx - 1) ? (X1 - 1) / Sx : Tx - 1;
+        if ((int)(last - first + 1) > nseg) nseg = (int)(last - first + 1);
+    }
+    const size_t smem = (size_t)kStages * r_step * 2 * nseg * Bx * 4 + (size_t)Bx * 8;
+    if (Bx <= 2 * Sx && By <= 2 * Sy && (Sx & 3) == 0 && (Bx & 3) == 0 && (X & 3) == 0 && aligned16 && nseg <= 32 &&
+        smem <= 72 * 1024) {
+        // row bands: ~6 blocks per SM in total, at least 4 steps per block where the image allows
+        const int64_t want = (int64_t)BE_SM_COUNT * 6;   // measured: 3 (one wave) .. 16 per SM within 5 %, 6 best
         int64_t bands = want / ((int64_t)xblocks * grid.z) + 1;
         const int64_t max_bands = (Y + 4 * r_step - 1) / (4 * r_step);
         if (bands > max_bands) bands = max_bands;
         if (bands > 65535) bands = 65535;
-        const int rows_per_band = (int)((Y + bands - 1) / bands);
+        int rows_per_band = (int)((Y + bands - 1) / bands);
+        rows_per_band = (rows_per_band + r_step - 1) / r_step * r_step;
         const dim3 g2(xblocks, (unsigned)((Y + rows_per_band - 1) / rows_per_band), grid.z);
+        RowsConst k;
+        k.dky = (int64_t)Tx * st.tile_stride - (int64_t)Sy * Bx;
+        k.dkz = (int64_t)Ty * Tx * st.tile_stride - (int64_t)Sz * By * Bx;
+        k.dout = (int64_t)r_step * X;
+        k.mid = 0.5 * (e.hi2 + e.lo2);
+        k.half = 0.5 * (e.hi2 - e.lo2) * (1.0 + 0x1p-30);
+        k.log2_bx = log2_bx;
+        k.rows_per_band = rows_per_band;
+        k.units_per_row = upr;
+        k.slot_bytes = nseg * Bx * 4;
+        k.stage_bytes = r_step * 2 * k.slot_bytes;
+        k.n_planes = (unsigned)(N * C * Z);
         if (e.fast)
-            stitch_blend_rows_kernel<true><<<g2, kThreads, 0, (cudaStream_t)stream>>>(
-                tiles, out, mask, d, st, wz, wy, wx, e, upr, (unsigned)(N * C * Z), log2_bx, rows_per_band);
+            BE_CUDA(cudaFuncSetAttribute(stitch_blend_rows_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 72 * 1024));
         else
-            stitch_blend_rows_kernel<false><<<g2, kThreads, 0, (cudaStream_t)stream>>>(
-                tiles, out, mask, d, st, wz, wy, wx, e, upr, (unsigned)(N * C * Z), log2_bx, rows_per_band);
+            BE_CUDA(cudaFuncSetAttribute(stitch_blend_rows_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 72 * 1024));
+        if (e.fast)
+            stitch_blend_rows_kernel<true><<<g2, kRowsThreads, smem, (cudaStream_t)stream>>>(tiles, out, mask, d, st, wz, wy, wx, e, k);
+        else
+            stitch_blend_rows_kernel<false><<<g2, kRowsThreads, smem, (cudaStream_t)stream>>>(tiles, out, mask, d, st, wz, wy, wx, e, k);
     } else {
         stitch_blend_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(tiles, out, mask, d, st, wz, wy, wx, e, upr,
                                                                          (unsigned)(N * C * Z));
