@@ -237,6 +237,7 @@ __global__ void __launch_bounds__(kThreads) ccl_tile_kernel(const uint8_t* __res
             const bool row_ok = z < g.Z && y < g.Y;
             const u64 m = rmask[r], s = rstart[r];
             const unsigned m4 = (unsigned)(m >> x4) & 0xfu, s4 = (unsigned)(s >> x4) & 0xfu;
+            if (m4 == 0) continue;   // parents exist only where the mask has pixels: nobody reads the rest
             int idx = r * 32 + __popcll(s & ((1ull << x4) - 1ull)) - 1;  // run open before this unit (if any)
             int32_t v[4] = {-1, -1, -1, -1};
             int32_t cur = -1;
@@ -274,7 +275,7 @@ __global__ void __launch_bounds__(kThreads) ccl_tile_kernel(const uint8_t* __res
             if (z < g.Z && y < g.Y) {
                 const int64_t wi = ((int64_t)img * g.Z * g.Y + z * g.Y + y) * wpr + tx;
                 rootbits[wi] = rroot[r];
-                if (bitvol) bitvol[wi] = rmask[r];  // the mask, 1 bit per voxel, for the 3-D face links
+                bitvol[wi] = rmask[r];  // the mask, 1 bit per voxel: 3-D face links, and the resolve pass
             }
         }
     }
@@ -319,19 +320,78 @@ __device__ __forceinline__ void gl_unite(int32_t* L, int32_t a, int32_t b) {
 }
 
 // 2-D: one warp per tile; top edge against the tile above, left edge against the tile to the left, two corners.
-// pm / pu give the pixel index of bit i on the two sides of an edge: base + i * step.
-__device__ __forceinline__ void link_edge(int32_t* Li, u64 m, u64 u, int64_t base_m, int64_t base_u, int64_t step,
-                                          bool diag, int lane) {
+// A lane owns bits lane and lane + 32 of both edges: at most 12 unions.  They are independent, so they are run as a
+// batch — all parent loads of a level issued before any is used, then all atomics — and a lane pays about three memory
+// round trips in total instead of five per union.  pm / pu give the pixel index of bit i on the two sides of an edge:
+// base + i * step.
+constexpr int kEdgePairs = 12;
+
+struct EdgeBatch {
+    int32_t a[kEdgePairs], b[kEdgePairs];
+    unsigned valid;
+};
+
+__device__ __forceinline__ void edge_pairs(EdgeBatch& q, int slot0, u64 m, u64 u, int64_t base_m, int64_t base_u,
+                                           int64_t step, bool diag, int lane) {
     if (!m || !u) return;
     const LinkMasks k = link_masks(m, u, diag);
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
         const int i = lane + 32 * h;
         const u64 bit = 1ull << i;
-        const int32_t a = (int32_t)(base_m + i * step);
-        if (k.c & bit) gl_unite(Li, a, (int32_t)(base_u + i * step));
-        if (k.l & bit) gl_unite(Li, a, (int32_t)(base_u + (i - 1) * step));
-        if (k.r & bit) gl_unite(Li, a, (int32_t)(base_u + (i + 1) * step));
+        const int32_t am = (int32_t)(base_m + i * step);
+        const int s = slot0 + 3 * h;
+        q.a[s] = q.a[s + 1] = q.a[s + 2] = am;
+        q.b[s] = (int32_t)(base_u + i * step);
+        q.b[s + 1] = (int32_t)(base_u + (i - 1) * step);
+        q.b[s + 2] = (int32_t)(base_u + (i + 1) * step);
+        q.valid |= ((k.c & bit) ? 1u : 0u) << s;
+        q.valid |= ((k.l & bit) ? 1u : 0u) << (s + 1);
+        q.valid |= ((k.r & bit) ? 1u : 0u) << (s + 2);
+    }
+}
+
+__device__ __forceinline__ void unite_batch(int32_t* Li, EdgeBatch& q) {
+    if (!q.valid) return;
+    // level 1: an edge pixel's parent is its tile root (or something even closer to the final root)
+#pragma unroll
+    for (int k = 0; k < kEdgePairs; ++k)
+        if ((q.valid >> k) & 1u) {
+            q.a[k] = __ldcg(Li + q.a[k]);
+            q.b[k] = __ldcg(Li + q.b[k]);
+        }
+    // level 2: is it still a root?
+    int32_t ga[kEdgePairs], gb[kEdgePairs];
+#pragma unroll
+    for (int k = 0; k < kEdgePairs; ++k)
+        if ((q.valid >> k) & 1u) {
+            ga[k] = __ldcg(Li + q.a[k]);
+            gb[k] = __ldcg(Li + q.b[k]);
+        }
+    // both roots in hand: one atomicMin; anything else goes through the general walk
+    unsigned fast = 0;
+    int32_t old[kEdgePairs];
+#pragma unroll
+    for (int k = 0; k < kEdgePairs; ++k)
+        if ((q.valid >> k) & 1u) {
+            if (ga[k] == q.a[k] && gb[k] == q.b[k]) {
+                if (q.a[k] != q.b[k]) {
+                    const int32_t hi = max(q.a[k], q.b[k]), lo = min(q.a[k], q.b[k]);
+                    old[k] = atomicMin(&Li[hi], lo);
+                    q.a[k] = hi;
+                    q.b[k] = lo;
+                    fast |= 1u << k;
+                }
+                q.valid &= ~(1u << k);
+            }
+        }
+#pragma unroll
+    for (int k = 0; k < kEdgePairs; ++k) {
+        if ((fast >> k) & 1u) {
+            if (old[k] != q.a[k]) gl_unite(Li, old[k], q.b[k]);   // hi was no longer a root: keep its old link alive
+        } else if ((q.valid >> k) & 1u) {
+            gl_unite(Li, q.a[k], q.b[k]);
+        }
     }
 }
 
@@ -346,8 +406,13 @@ __global__ void __launch_bounds__(kThreads) ccl_edge_kernel(int32_t* __restrict_
     const TileEdges me = E[t];
     const int64_t x0 = (int64_t)tx * kTX, y0 = (int64_t)ty * kRows;
     const bool diag = g.conn >= 2;
-    if (ty > 0) link_edge(Li, me.top, E[t - g.tiles_x].bottom, y0 * g.X + x0, (y0 - 1) * g.X + x0, 1, diag, lane);
-    if (tx > 0) link_edge(Li, me.left, E[t - 1].right, y0 * g.X + x0, y0 * g.X + x0 - 1, g.X, diag, lane);
+    EdgeBatch q;
+    q.valid = 0;
+#pragma unroll
+    for (int k = 0; k < kEdgePairs; ++k) q.a[k] = q.b[k] = 0;
+    if (ty > 0) edge_pairs(q, 0, me.top, E[t - g.tiles_x].bottom, y0 * g.X + x0, (y0 - 1) * g.X + x0, 1, diag, lane);
+    if (tx > 0) edge_pairs(q, 6, me.left, E[t - 1].right, y0 * g.X + x0, y0 * g.X + x0 - 1, g.X, diag, lane);
+    unite_batch(Li, q);
     if (diag && ty > 0 && lane == 0) {
         if (tx > 0 && (me.top & 1ull) && (E[t - g.tiles_x - 1].bottom >> 63))
             gl_unite(Li, (int32_t)(y0 * g.X + x0), (int32_t)((y0 - 1) * g.X + x0 - 1));
@@ -515,29 +580,59 @@ __device__ __forceinline__ int32_t resolve_one(const int32_t* __restrict__ Li, i
     return -v - 1;
 }
 
-__global__ void __launch_bounds__(kThreads) ccl_resolve_kernel(const int32_t* __restrict__ L, int32_t* __restrict__ out,
-                                                               int64_t vol) {
-    const int32_t* Li = L + (int64_t)blockIdx.y * vol;
-    int32_t* oi = out + (int64_t)blockIdx.y * vol;
-    const int64_t i4 = ((int64_t)blockIdx.x * kThreads + threadIdx.x) * 4;
-    if (i4 >= vol) return;
-    if (i4 + 4 <= vol && (((uintptr_t)(Li + i4) | (uintptr_t)(oi + i4)) & 15) == 0) {
-        const int4 p = *reinterpret_cast<const int4*>(Li + i4);
-        int4 v;  // neighbouring pixels usually share their parent: look it up once
-        v.x = resolve_one(Li, p.x);
-        v.y = (p.y == p.x) ? v.x : resolve_one(Li, p.y);
-        v.z = (p.z == p.y) ? v.y : resolve_one(Li, p.z);
-        v.w = (p.w == p.z) ? v.z : resolve_one(Li, p.w);
-        *reinterpret_cast<int4*>(oi + i4) = v;
+// grid: x = row (z * Y + y), y = blocks of 8-px units along the row, z = image.  The packed mask says which pixels have a
+// parent entry at all: all-background units (most of a typical mask) are written without touching the parent array,
+// and a unit's two 16-byte parent loads are issued together.
+__global__ void __launch_bounds__(kThreads) ccl_resolve_kernel(const int32_t* __restrict__ L, const u64* __restrict__ bitvol,
+                                                               int32_t* __restrict__ out, int64_t vol, int X, int wpr,
+                                                               int64_t words_per_image, int units_per_row) {
+    const int u = blockIdx.y * kThreads + threadIdx.x;
+    if (u >= units_per_row) return;
+    const int64_t row = blockIdx.x;
+    const int x = u * 8;
+    const u64 word = __ldg(bitvol + (int64_t)blockIdx.z * words_per_image + row * wpr + (x >> 6));
+    const unsigned bits = (unsigned)(word >> (x & 63)) & 0xffu;
+    const int32_t* Li = L + (int64_t)blockIdx.z * vol;
+    const int64_t base = row * X + x;
+    int32_t* o = out + (int64_t)blockIdx.z * vol + base;
+    const bool vec = x + 8 <= X && (((uintptr_t)o | (uintptr_t)(Li + base)) & 15) == 0;
+    int32_t p[8], v[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (bits) {
+        if (vec) {
+            int4 a = make_int4(-1, -1, -1, -1), b = a;
+            if (bits & 0x0fu) a = __ldg(reinterpret_cast<const int4*>(Li + base));
+            if (bits & 0xf0u) b = __ldg(reinterpret_cast<const int4*>(Li + base) + 1);
+            p[0] = a.x, p[1] = a.y, p[2] = a.z, p[3] = a.w, p[4] = b.x, p[5] = b.y, p[6] = b.z, p[7] = b.w;
+        } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) p[j] = ((bits >> j) & 1u) ? __ldg(Li + base + j) : -1;
+        }
+        int32_t prev_p = -1, prev_v = 0;   // neighbouring pixels usually share their parent: look it up once
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            if ((bits >> j) & 1u) {
+                if (p[j] != prev_p) {
+                    prev_p = p[j];
+                    prev_v = resolve_one(Li, p[j]);
+                }
+                v[j] = prev_v;
+            }
+        }
+    }
+    if (vec) {
+        reinterpret_cast<int4*>(o)[0] = make_int4(v[0], v[1], v[2], v[3]);
+        reinterpret_cast<int4*>(o)[1] = make_int4(v[4], v[5], v[6], v[7]);
     } else {
-        for (int64_t i = i4; i < min(i4 + 4, vol); ++i) oi[i] = resolve_one(Li, Li[i]);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+            if (x + j < X) o[j] = v[j];
     }
 }
 
 struct CclWorkspace {
     int32_t* L;
     u64* rootbits;
-    u64* bitvol;        // 3-D only (aliases nothing; 2-D leaves it unused)
+    u64* bitvol;        // the mask, 1 bit per voxel
     TileEdges* edges;
     unsigned* tickets;                 // [N]
     unsigned long long* block_state;   // [N][blocks_per_image]
@@ -562,7 +657,7 @@ CclWorkspace carve_ccl_ws(void* ws, int64_t N, int64_t Z, int64_t Y, int64_t X) 
     w.rootbits = (u64*)(p + off);
     off += be_align_up(sizeof(u64) * N * w.words_per_image, 256);
     w.bitvol = (u64*)(p + off);
-    if (ndim == 3) off += be_align_up(sizeof(u64) * N * w.words_per_image, 256);
+    off += be_align_up(sizeof(u64) * N * w.words_per_image, 256);
     w.edges = (TileEdges*)(p + off);
     off += be_align_up(sizeof(TileEdges) * N * tiles_x * tiles_y * tiles_z, 256);
     w.tickets = (unsigned*)(p + off);
@@ -612,7 +707,7 @@ extern "C" int be_ccl_u8_i32(const uint8_t* mask, int32_t* labels, int64_t N, in
                "be_ccl_u8_i32: tile grid (%d, %d, %lld) exceeds the launch limits", g.tiles_x, g.tiles_y,
                (long long)g.tiles_z * N);
     ccl_tile_kernel<<<dim3((unsigned)g.tiles_x, (unsigned)g.tiles_y, (unsigned)(g.tiles_z * N)), kThreads, 0, s>>>(
-        mask, w.L, w.rootbits, ndim == 3 ? w.bitvol : nullptr, ndim == 2 ? w.edges : nullptr, g);
+        mask, w.L, w.rootbits, w.bitvol, ndim == 2 ? w.edges : nullptr, g);
     BE_LAUNCH_CHECK();
     if (ndim == 2) {
         if (n_tiles > 1) {
@@ -629,8 +724,10 @@ extern "C" int be_ccl_u8_i32(const uint8_t* mask, int32_t* labels, int64_t N, in
     ccl_number_kernel<<<dim3(w.blocks_per_image, (unsigned)N), kThreads, 0, s>>>(
         w.L, w.rootbits, vol, X, g.tiles_x, w.words_per_image, w.blocks_per_image, w.tickets, w.block_state, n_labels);
     BE_LAUNCH_CHECK();
-    ccl_resolve_kernel<<<dim3((unsigned)((vol + kThreads * 4 - 1) / (kThreads * 4)), (unsigned)N), kThreads, 0, s>>>(
-        w.L, labels, vol);
+    const int upr = (int)((X + 7) / 8);
+    BE_REQUIRE((upr + kThreads - 1) / kThreads <= 65535, BE_ERR_TOO_LARGE, "be_ccl_u8_i32: X %lld too long", (long long)X);
+    ccl_resolve_kernel<<<dim3((unsigned)(Z * Y), (unsigned)((upr + kThreads - 1) / kThreads), (unsigned)N), kThreads, 0, s>>>(
+        w.L, w.bitvol, labels, vol, (int)X, g.tiles_x, w.words_per_image, upr);
     BE_LAUNCH_CHECK();
     return BE_OK;
 }
