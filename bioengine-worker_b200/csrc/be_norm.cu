@@ -7,6 +7,7 @@
 //   be_elementwise_f32 clip / scale_linear / sigmoid
 //   be_binarize_f32_u8 x > thr
 #include <cooperative_groups.h>
+#include <stdlib.h>
 
 #include "be_common.cuh"
 
@@ -575,6 +576,8 @@ struct QTask {
     // partition phase
     float flo, fhi;
     uint32_t below, eq_lo, eq_hi, n_mid;
+    uint32_t kmax, nkmin;  // max key and max ~key over the candidate list (zero-initialised, raised with atomicMax)
+    uint32_t klo, range;   // selection: digits are cut from (key - klo), which lies in [0, range]
 };
 
 struct SWorkspace {
@@ -701,7 +704,7 @@ __global__ void __launch_bounds__(kThreads) qsel_partition_kernel(const float* _
                                                                   int64_t chunk, const double* __restrict__ q,
                                                                   SWorkspace w, int64_t n_seg) {
     __shared__ float s_buf[NQ][kStage];
-    __shared__ unsigned s_n[NQ], s_cnt[NQ][3], s_nan, s_base[NQ];
+    __shared__ unsigned s_n[NQ], s_cnt[NQ][3], s_nan, s_base[NQ], s_kmax[NQ], s_nkmin[NQ];
     const int64_t seg = blockIdx.y;
     const float* xs = x + seg * seg_len;
     QTask* tasks = w.tasks + seg * NQ;
@@ -714,6 +717,7 @@ __global__ void __launch_bounds__(kThreads) qsel_partition_kernel(const float* _
     if (threadIdx.x < NQ) {
         s_n[threadIdx.x] = 0;
         s_cnt[threadIdx.x][0] = s_cnt[threadIdx.x][1] = s_cnt[threadIdx.x][2] = 0;
+        s_kmax[threadIdx.x] = s_nkmin[threadIdx.x] = 0;
     }
     if (threadIdx.x == 0) s_nan = 0;
     __syncthreads();
@@ -740,6 +744,8 @@ __global__ void __launch_bounds__(kThreads) qsel_partition_kernel(const float* _
                     } else {  // staging full: straight to the global list (still counted if that is full too)
                         const unsigned g = atomicAdd(&tasks[i].n_mid, 1u);
                         if (g < w.cap) w.cand[(seg * NQ + i) * w.cap + g] = v;
+                        atomicMax(&s_kmax[i], f32_to_key(v));
+                        atomicMax(&s_nkmin[i], ~f32_to_key(v));
                     }
                 }
             }
@@ -817,12 +823,31 @@ __global__ void __launch_bounds__(kThreads) qsel_partition_kernel(const float* _
     }
     if (threadIdx.x == 0 && s_nan) atomicAdd(&w.nan_count[seg], s_nan);
     __syncthreads();
+    // staged candidates go to the global list; their key range (what the selection cuts its digits from) rides along
 #pragma unroll
     for (int i = 0; i < NQ; ++i) {
         const unsigned n = min(s_n[i], (unsigned)kStage), base = s_base[i];
         float* dst = w.cand + (seg * NQ + i) * w.cap;
-        for (unsigned k = threadIdx.x; k < n; k += kThreads)
-            if (base + k < w.cap) dst[base + k] = s_buf[i][k];
+        unsigned kx = 0, nk = 0;
+        for (unsigned k = threadIdx.x; k < n; k += kThreads) {
+            const float v = s_buf[i][k];
+            if (base + k < w.cap) dst[base + k] = v;
+            kx = max(kx, f32_to_key(v));
+            nk = max(nk, ~f32_to_key(v));
+        }
+        if (__any_sync(0xffffffffu, kx | nk)) {
+            kx = __reduce_max_sync(0xffffffffu, kx);
+            nk = __reduce_max_sync(0xffffffffu, nk);
+            if ((threadIdx.x & 31) == 0) {
+                atomicMax(&s_kmax[i], kx);
+                atomicMax(&s_nkmin[i], nk);
+            }
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x < NQ && (s_kmax[threadIdx.x] | s_nkmin[threadIdx.x])) {
+        atomicMax(&tasks[threadIdx.x].kmax, s_kmax[threadIdx.x]);
+        atomicMax(&tasks[threadIdx.x].nkmin, s_nkmin[threadIdx.x]);
     }
 
     if (!last_block_of_segment(&w.counters[3 * n_seg * NQ + seg], bps)) return;
@@ -835,6 +860,7 @@ __global__ void __launch_bounds__(kThreads) qsel_partition_kernel(const float* _
         const uint32_t n_nan = __ldcg(&w.nan_count[seg]);
         const uint32_t below_c = __ldcg(&t->below), eq_lo = __ldcg(&t->eq_lo), eq_hi = __ldcg(&t->eq_hi);
         const uint32_t n_mid = __ldcg(&t->n_mid);
+        const uint32_t kmax = __ldcg(&t->kmax), kmin = ~__ldcg(&t->nkmin);
         const float tflo = flo[i], tfhi = fhi[i];
         const double qi = q[i];
         const uint32_t n_valid = (uint32_t)seg_len - n_nan;
@@ -855,6 +881,7 @@ __global__ void __launch_bounds__(kThreads) qsel_partition_kernel(const float* _
         r.eq_lo = eq_lo;
         r.eq_hi = eq_hi;
         r.n_mid = n_mid;
+        r.kmax = r.nkmin = 0;
         if (ok || n_valid == 0) {
             r.src = w.cand + (seg * NQ + i) * w.cap;
             r.len = n_valid ? n_mid : 0;
@@ -865,7 +892,11 @@ __global__ void __launch_bounds__(kThreads) qsel_partition_kernel(const float* _
             r.vcnt[0] = eq_lo;
             r.vcnt[1] = eq_hi;
             r.total = n_valid ? inside : 0;
+            r.klo = (n_mid && kmax >= kmin) ? kmin : 0u;
+            r.range = (n_mid && kmax >= kmin) ? kmax - kmin : 0u;
         } else {  // bracket missed or list overflowed: select on the whole segment instead
+            r.klo = 0;
+            r.range = 0xffffffffu;
             r.src = xs;
             r.len = (uint32_t)seg_len;
             r.rank[0] = ilo;
@@ -1037,6 +1068,278 @@ __global__ void __launch_bounds__(kThreads) qsel_task_kernel(int bps, int64_t ch
     }
 }
 
+// ---- the selection stage as ONE launch: a thread-block cluster per task ----
+//
+// The radix levels only ever look at the ~1-2 % of a segment the partition pass kept, so relaunching a grid per level
+// costs more in launch and completion-ticket latency than the passes themselves.  Here a cluster of kClusterCtas CTAs
+// owns a task and the levels are separated by cluster barriers:
+//   * digits are taken from (key - key(flo)), top bits of the bracket's actual width first, so the first level already
+//     spreads the candidates over all 2048 bins (plain key digits would put a narrow bracket into one or two bins);
+//   * every CTA histograms its slice of the list in shared memory; the eight histograms are summed through distributed
+//     shared memory (each CTA sums 1/8 of the bins and stores the sums into the leader's table), the leader adds the
+//     virtual ties, finds the bins of the two ranks and publishes the new prefixes;
+//   * after the first level each CTA keeps only the elements of the selected bins (~1/2048 of its slice) in a small
+//     shared-memory list, so the remaining levels cost next to nothing.  A CTA whose selected elements do not fit the
+//     list (heavy ties, or a fallback to a whole segment) streams its slice again instead.
+constexpr int kClusterMax = 16;   // CTAs per cluster: 16 where the device grants it (non-portable size), else 8
+constexpr int kSelThreads = 1024;
+constexpr int kSmallCap = 3072;
+
+struct ClusterShared {
+    unsigned sh[2][kBins];    // this CTA's histograms (one per group)
+    unsigned tot[2][kBins];   // leader: the cluster's histograms
+    float small[kSmallCap];   // elements of the bins selected at level 0
+    unsigned n_small;
+    QState st;
+    QTask t;
+    uint32_t fixed_key[2];    // ranks that fall on a tie with a pivot need no selection: their key is known
+    int fixed[2];
+    uint32_t s_warp[kSelThreads / 32];
+    uint32_t s_res[2];
+};
+
+// block-cooperative (kSelThreads): the bin holding the k-th (0-based) element of a shared-memory histogram
+__device__ void find_bin_sm(ClusterShared& S, const unsigned* hist, uint32_t k, uint32_t* bin_out, uint32_t* krem_out) {
+    constexpr int per = kBins / kSelThreads;
+    uint32_t c[per];
+    uint32_t local = 0;
+#pragma unroll
+    for (int i = 0; i < per; ++i) {
+        c[i] = hist[threadIdx.x * per + i];
+        local += c[i];
+    }
+    uint32_t incl = local;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+        if ((threadIdx.x & 31) >= o) incl += t;
+    }
+    __syncthreads();  // protects s_warp / s_res from the previous call
+    if ((threadIdx.x & 31) == 31) S.s_warp[threadIdx.x >> 5] = incl;
+    if (threadIdx.x == 0) S.s_res[0] = S.s_res[1] = 0;   // k beyond the histogram (an empty list): bin 0
+    __syncthreads();
+    uint32_t base = 0;
+    for (int w = 0; w < (int)(threadIdx.x >> 5); ++w) base += S.s_warp[w];
+    const uint32_t excl = base + incl - local;
+    if (k >= excl && k < excl + local) {
+        uint32_t r = k - excl;
+#pragma unroll
+        for (int i = 0; i < per; ++i) {
+            if (r < c[i]) {
+                S.s_res[0] = threadIdx.x * per + i;
+                S.s_res[1] = r;
+                break;
+            }
+            r -= c[i];
+        }
+    }
+    __syncthreads();
+    *bin_out = S.s_res[0];
+    *krem_out = S.s_res[1];
+}
+
+// how the bracket's key range is cut into digits: level l takes `bits[l]` bits at `shift[l]` of (key - klo)
+struct DigitPlan {
+    uint32_t klo;
+    int shift[3], bits[3];
+};
+
+__device__ __forceinline__ DigitPlan make_plan(const QTask& t) {
+    DigitPlan p;
+    p.klo = t.klo;
+    int left = 32 - __clz(t.range);
+    const int want[3] = {11, 11, 10};
+#pragma unroll
+    for (int l = 0; l < 3; ++l) {
+        p.bits[l] = min(want[l], left);
+        left -= p.bits[l];
+        p.shift[l] = left;
+    }
+    return p;   // 32 bits are always used up by 11 + 11 + 10
+}
+
+// apply f to the elements of this CTA's slice: the small list if it is valid, the source otherwise
+template <class F>
+__device__ __forceinline__ void slice_foreach(const float* xs, int64_t n, F f) {
+    int64_t head = ((16 - ((uintptr_t)xs & 15)) & 15) >> 2;
+    if (head > n) head = n;
+    if ((int64_t)threadIdx.x < head) f(xs[threadIdx.x]);
+    const float4* p4 = reinterpret_cast<const float4*>(xs + head);
+    const int64_t n4 = (n - head) >> 2;
+    int64_t i = threadIdx.x;
+    for (; i + kSelThreads < n4; i += 2 * kSelThreads) {
+        const float4 a = ld_stream_f4(p4 + i);
+        const float4 b = ld_stream_f4(p4 + i + kSelThreads);
+        f(a.x); f(a.y); f(a.z); f(a.w);
+        f(b.x); f(b.y); f(b.z); f(b.w);
+    }
+    for (; i < n4; i += kSelThreads) {
+        const float4 v = ld_stream_f4(p4 + i);
+        f(v.x); f(v.y); f(v.z); f(v.w);
+    }
+    const int64_t done = head + (n4 << 2);
+    if (done + (int64_t)threadIdx.x < n) f(xs[done + threadIdx.x]);
+}
+
+template <int LEVEL>
+__device__ __forceinline__ void cluster_level(cg::cluster_group& cluster, ClusterShared& S, const DigitPlan& plan,
+                                              const float* xs, int64_t n, bool use_small) {
+    constexpr int kGroups = (LEVEL == 0) ? 1 : 2;
+    const unsigned rank = cluster.block_rank();
+    const int shift = plan.shift[LEVEL], hi_shift = (LEVEL == 0) ? 0 : plan.shift[LEVEL - 1];
+    const uint32_t mask = (1u << plan.bits[LEVEL]) - 1u;
+    const uint32_t klo = plan.klo;
+    const int n_groups = (LEVEL == 0) ? 1 : S.st.n_groups;
+    uint32_t gp[kGroups];
+#pragma unroll
+    for (int g = 0; g < kGroups; ++g) gp[g] = (LEVEL == 0) ? 0u : ((g < n_groups) ? S.st.gprefix[g] : 0xffffffffu);
+    for (int i = threadIdx.x; i < n_groups * kBins; i += kSelThreads) (&S.sh[0][0])[i] = 0;
+    __syncthreads();
+    RunCounter rc[kGroups];
+    auto count = [&](float v) {
+        if (v == v) {  // a fallback source may hold NaN
+            const uint32_t d = f32_to_key(v) - klo;
+            const uint32_t digit = (d >> shift) & mask;
+            if (LEVEL == 0) {
+                rc[0].add(S.sh[0], digit);
+            } else {
+                const uint32_t hi = (hi_shift >= 32) ? 0u : (d >> hi_shift);
+#pragma unroll
+                for (int g = 0; g < kGroups; ++g)
+                    if (hi == gp[g]) rc[g].add(S.sh[g], digit);
+            }
+        }
+    };
+    if (use_small) {
+        for (unsigned i = threadIdx.x; i < S.n_small; i += kSelThreads) count(S.small[i]);
+    } else {
+        slice_foreach(xs, n, count);
+    }
+#pragma unroll
+    for (int g = 0; g < kGroups; ++g) rc[g].flush(S.sh[g]);
+    cluster.sync();   // every CTA's histogram is complete
+    {
+        // this CTA sums its share of the bins over the cluster and stores the sums into the leader's table
+        const int n_cta = (int)cluster.num_blocks(), part = kBins / n_cta;
+        unsigned* lead_tot = cluster.map_shared_rank(&S.tot[0][0], 0);
+        for (int i = threadIdx.x; i < n_groups * part; i += kSelThreads) {
+            const int g = i / part, bin = rank * part + (i - g * part);
+            unsigned sum = 0;
+            for (int c = 0; c < n_cta; ++c) sum += *(cluster.map_shared_rank(&S.sh[0][0], c) + g * kBins + bin);
+            lead_tot[g * kBins + bin] = sum;
+        }
+    }
+    cluster.sync();   // the leader's table is complete; nobody reads this CTA's histogram any more
+    if (rank == 0) {
+        {
+            for (int j = 0; j < 2; ++j) {
+                uint32_t bin, krem;
+                find_bin_sm(S, &S.tot[0][0] + S.st.group[j] * kBins, S.st.krem[j], &bin, &krem);
+                __syncthreads();
+                if (threadIdx.x == 0) {
+                    S.st.prefix[j] = (S.st.prefix[j] << plan.bits[LEVEL]) | bin;
+                    S.st.krem[j] = krem;
+                }
+            }
+        }
+        __syncthreads();
+        if (LEVEL < 2 && threadIdx.x == 0) regroup(&S.st);
+    }
+    cluster.sync();   // the leader's state is final
+    if (LEVEL < 2 && rank != 0) {
+        if (threadIdx.x == 0) S.st = *cluster.map_shared_rank(&S.st, 0);
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(kSelThreads)
+    qsel_cluster_kernel(int n_q, double eps, SWorkspace w, double* __restrict__ quant, double* __restrict__ norm) {
+    __shared__ ClusterShared S;
+    cg::cluster_group cluster = cg::this_cluster();
+    const unsigned r = cluster.block_rank();
+    const int64_t task = blockIdx.y;
+    if (threadIdx.x == 0) {
+        S.t = w.tasks[task];
+        S.st.n_ranks = 2;
+        S.st.n_valid = S.t.total;
+        S.st.gamma[0] = S.t.gamma;
+        S.st.n_groups = 1;
+        S.st.gprefix[0] = 0;
+        S.st.group[0] = S.st.group[1] = 0;
+        S.st.prefix[0] = S.st.prefix[1] = 0;
+        // the multiset is {vcnt[0] x flo} + list + {vcnt[1] x fhi}: a rank inside a run of ties is settled right away
+        for (int j = 0; j < 2; ++j) {
+            const uint32_t k = S.t.rank[j];
+            S.fixed[j] = 1;
+            if (k < S.t.vcnt[0]) {
+                S.fixed_key[j] = S.t.vkey[0];
+            } else if (k - S.t.vcnt[0] < S.t.len) {
+                S.fixed[j] = 0;
+                S.st.krem[j] = k - S.t.vcnt[0];
+            } else {
+                S.fixed_key[j] = S.t.vkey[1];
+            }
+        }
+        // a settled rank shadows the other one through the levels (same histogram, result ignored)
+        if (S.fixed[0] && !S.fixed[1]) S.st.krem[0] = S.st.krem[1];
+        if (S.fixed[1] && !S.fixed[0]) S.st.krem[1] = S.st.krem[0];
+        S.n_small = 0;
+    }
+    __syncthreads();
+    const DigitPlan plan = make_plan(S.t);
+    // this CTA's slice of the source
+    const int64_t len = S.t.len;
+    const int64_t n_cta = cluster.num_blocks();
+    int64_t per = (len + n_cta - 1) / n_cta;
+    per = (per + 3) & ~(int64_t)3;
+    const int64_t begin = min(len, (int64_t)r * per), n = min(len, begin + per) - begin;
+    const float* xs = S.t.src + begin;
+
+    cluster_level<0>(cluster, S, plan, xs, n, false);
+
+    // keep the elements of the selected level-0 bins (at most two distinct ones) if this CTA's share of them fits
+    const uint32_t b0 = S.st.gprefix[0], b1 = (S.st.n_groups > 1) ? S.st.gprefix[1] : b0;
+    const unsigned mine = S.sh[0][b0] + ((b1 != b0) ? S.sh[0][b1] : 0u);   // S.sh still holds this CTA's level-0 counts
+    const bool use_small = mine <= (unsigned)kSmallCap;
+    if (use_small && mine > 0) {
+        const int shift = plan.shift[0];
+        const uint32_t klo = plan.klo, mask = (1u << plan.bits[0]) - 1u;
+        slice_foreach(xs, n, [&](float v) {
+            if (v == v) {
+                const uint32_t digit = ((f32_to_key(v) - klo) >> shift) & mask;
+                if (digit == b0 || digit == b1) S.small[atomicAdd(&S.n_small, 1u)] = v;
+            }
+        });
+    }
+    __syncthreads();
+
+    cluster_level<1>(cluster, S, plan, xs, n, use_small);
+    cluster_level<2>(cluster, S, plan, xs, n, use_small);
+    if (r != 0 || threadIdx.x != 0) return;
+    double res;
+    if (S.t.total == 0) {
+        res = __longlong_as_double(0x7ff8000000000000LL);
+    } else {
+        // numpy _lerp: fp32 difference, fp64 product and sum, switch of anchor at gamma >= 0.5
+        const float a = key_to_f32(S.fixed[0] ? S.fixed_key[0] : plan.klo + S.st.prefix[0]);
+        const float b = key_to_f32(S.fixed[1] ? S.fixed_key[1] : plan.klo + S.st.prefix[1]);
+        const double d = (double)__fsub_rn(b, a);
+        const double g = S.st.gamma[0];
+        res = (g >= 0.5) ? __dsub_rn((double)b, __dmul_rn(d, __dsub_rn(1.0, g))) : __dadd_rn((double)a, __dmul_rn(d, g));
+    }
+    quant[task] = res;
+    if (norm) {  // the task of a segment that finishes second writes {q0, q1 - q0 + eps}
+        __threadfence();
+        const int64_t seg = task / n_q;
+        if (atomicAdd(&w.seg_done[seg], 1u) == (unsigned)(n_q - 1)) {
+            __threadfence();
+            const double lo = __ldcg(&quant[seg * n_q + 0]), hi = __ldcg(&quant[seg * n_q + 1]);
+            norm[seg * 2 + 0] = lo;
+            norm[seg * 2 + 1] = __dadd_rn(__dsub_rn(hi, lo), eps);
+        }
+    }
+}
+
 inline int stream_grid(int64_t n_items_per_thread_units) {
     int64_t blocks = (n_items_per_thread_units + kThreads - 1) / kThreads;
     const int64_t cap = (int64_t)BE_SM_COUNT * 16;
@@ -1090,6 +1393,40 @@ static int quantile_radix(const float* x, int64_t n_seg, int64_t seg_len, const 
     return BE_OK;
 }
 
+// Largest cluster the selection kernel can be launched with on the current device: 16 CTAs if the device grants the
+// non-portable size and can keep at least two such clusters resident, else 8; 0 if neither works.  Asked once per device.
+static int select_cluster_size() {
+    static int cached[64];   // 0 = not asked yet, -1 = no cluster possible
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 0;
+    if (cached[dev]) return cached[dev] > 0 ? cached[dev] : 0;
+    int best = -1;
+    for (int size = kClusterMax; size >= 8 && best < 0; size >>= 1) {
+        if (size > 8 &&
+            cudaFuncSetAttribute(qsel_cluster_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) {
+            cudaGetLastError();
+            continue;
+        }
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)size, 2);
+        cfg.blockDim = dim3(kSelThreads);
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = (unsigned)size;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        int n = 0;
+        if (cudaOccupancyMaxActiveClusters(&n, qsel_cluster_kernel, &cfg) == cudaSuccess && n >= (size > 8 ? 2 : 1))
+            best = size;
+        else
+            cudaGetLastError();
+    }
+    cached[dev] = best;
+    return best > 0 ? best : 0;
+}
+
 // sampled-pivot select: one pass over the data + radix select on ~2 % of it, `per_pass` segments at a time
 static int quantile_sampled(const float* x, int64_t n_seg, int64_t seg_len, const double* q, int n_q, double eps,
                             double* quant, double* norm, void* ws, cudaStream_t s) {
@@ -1118,6 +1455,24 @@ static int quantile_sampled(const float* x, int64_t n_seg, int64_t seg_len, cons
         const int64_t most = (seg_len + tchunk - 1) / tchunk;
         if (tb > most) tb = (int)most;
         const dim3 tgrid(tb, (unsigned)nt);
+        if (!getenv("BE_QSEL_OLD")) {   // A/B ONLY
+            const int n_cta = select_cluster_size();
+            BE_REQUIRE(n_cta > 0, BE_ERR_CUDA, "be_quantile_f32: the device cannot run a thread-block cluster of 8");
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = dim3((unsigned)n_cta, (unsigned)nt);
+            cfg.blockDim = dim3(kSelThreads);
+            cfg.dynamicSmemBytes = 0;
+            cfg.stream = s;
+            cudaLaunchAttribute attr[1];
+            attr[0].id = cudaLaunchAttributeClusterDimension;
+            attr[0].val.clusterDim.x = (unsigned)n_cta;
+            attr[0].val.clusterDim.y = 1;
+            attr[0].val.clusterDim.z = 1;
+            cfg.attrs = attr;
+            cfg.numAttrs = 1;
+            BE_CUDA(cudaLaunchKernelEx(&cfg, qsel_cluster_kernel, n_q, eps, w, qs, nr));
+            continue;
+        }
         qsel_task_kernel<0><<<tgrid, kThreads, 0, s>>>(tb, tchunk, n_q, eps, w, nt, qs, nr);
         BE_LAUNCH_CHECK();
         qsel_task_kernel<1><<<tgrid, kThreads, 0, s>>>(tb, tchunk, n_q, eps, w, nt, qs, nr);
