@@ -1118,8 +1118,14 @@ __device__ void find_bin_sm(ClusterShared& S, const unsigned* hist, uint32_t k, 
     if ((threadIdx.x & 31) == 31) S.s_warp[threadIdx.x >> 5] = incl;
     if (threadIdx.x == 0) S.s_res[0] = S.s_res[1] = 0;   // k beyond the histogram (an empty list): bin 0
     __syncthreads();
-    uint32_t base = 0;
-    for (int w = 0; w < (int)(threadIdx.x >> 5); ++w) base += S.s_warp[w];
+    // exclusive prefix of the warp totals: every warp scans the 32 totals itself (one shuffle scan, no serial loop)
+    uint32_t wt = S.s_warp[threadIdx.x & 31], winc = wt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        uint32_t t = __shfl_up_sync(0xffffffffu, winc, o);
+        if ((threadIdx.x & 31) >= o) winc += t;
+    }
+    const uint32_t base = __shfl_sync(0xffffffffu, winc - wt, threadIdx.x >> 5);
     const uint32_t excl = base + incl - local;
     if (k >= excl && k < excl + local) {
         uint32_t r = k - excl;
@@ -1193,7 +1199,10 @@ __device__ __forceinline__ void cluster_level(cg::cluster_group& cluster, Cluste
     uint32_t gp[kGroups];
 #pragma unroll
     for (int g = 0; g < kGroups; ++g) gp[g] = (LEVEL == 0) ? 0u : ((g < n_groups) ? S.st.gprefix[g] : 0xffffffffu);
-    for (int i = threadIdx.x; i < n_groups * kBins; i += kSelThreads) (&S.sh[0][0])[i] = 0;
+    for (int i = threadIdx.x; i < n_groups * kBins; i += kSelThreads) {
+        (&S.sh[0][0])[i] = 0;
+        if (rank == 0) (&S.tot[0][0])[i] = 0;
+    }
     __syncthreads();
     RunCounter rc[kGroups];
     auto count = [&](float v) {
@@ -1217,19 +1226,16 @@ __device__ __forceinline__ void cluster_level(cg::cluster_group& cluster, Cluste
     }
 #pragma unroll
     for (int g = 0; g < kGroups; ++g) rc[g].flush(S.sh[g]);
-    cluster.sync();   // every CTA's histogram is complete
+    cluster.sync();   // every CTA's histogram is complete, the leader's table is zeroed
     {
-        // this CTA sums its share of the bins over the cluster and stores the sums into the leader's table
-        const int n_cta = (int)cluster.num_blocks(), part = kBins / n_cta;
+        // push this CTA's non-empty bins into the leader's table: remote shared-memory atomics, nothing waits on them
         unsigned* lead_tot = cluster.map_shared_rank(&S.tot[0][0], 0);
-        for (int i = threadIdx.x; i < n_groups * part; i += kSelThreads) {
-            const int g = i / part, bin = rank * part + (i - g * part);
-            unsigned sum = 0;
-            for (int c = 0; c < n_cta; ++c) sum += *(cluster.map_shared_rank(&S.sh[0][0], c) + g * kBins + bin);
-            lead_tot[g * kBins + bin] = sum;
+        for (int i = threadIdx.x; i < n_groups * kBins; i += kSelThreads) {
+            const unsigned c = (&S.sh[0][0])[i];
+            if (c) atomicAdd(lead_tot + i, c);
         }
     }
-    cluster.sync();   // the leader's table is complete; nobody reads this CTA's histogram any more
+    cluster.sync();   // the leader's table is complete
     if (rank == 0) {
         {
             for (int j = 0; j < 2; ++j) {
@@ -1243,13 +1249,51 @@ __device__ __forceinline__ void cluster_level(cg::cluster_group& cluster, Cluste
             }
         }
         __syncthreads();
-        if (LEVEL < 2 && threadIdx.x == 0) regroup(&S.st);
+        if (LEVEL < 2 && threadIdx.x == 0) {
+            regroup(&S.st);
+            if (LEVEL == 0) {
+                // few enough elements left in the selected bins: they are gathered into the leader's list and the leader
+                // finishes alone, without cluster barriers
+                const uint32_t b0 = S.st.gprefix[0], b1 = (S.st.n_groups > 1) ? S.st.gprefix[1] : b0;
+                const unsigned left = S.tot[0][b0] + ((b1 != b0) ? S.tot[0][b1] : 0u);
+                S.st.pad = left <= (unsigned)kSmallCap;
+            }
+        }
     }
     cluster.sync();   // the leader's state is final
     if (LEVEL < 2 && rank != 0) {
         if (threadIdx.x == 0) S.st = *cluster.map_shared_rank(&S.st, 0);
         __syncthreads();
     }
+}
+
+// a level on the leader's gathered list: block-local, no cluster barrier
+template <int LEVEL>
+__device__ __forceinline__ void leader_level(ClusterShared& S, const DigitPlan& plan) {
+    const int shift = plan.shift[LEVEL], hi_shift = plan.shift[LEVEL - 1];
+    const uint32_t mask = (1u << plan.bits[LEVEL]) - 1u, klo = plan.klo;
+    const int n_groups = S.st.n_groups;
+    for (int i = threadIdx.x; i < n_groups * kBins; i += kSelThreads) (&S.tot[0][0])[i] = 0;
+    __syncthreads();
+    for (unsigned i = threadIdx.x; i < S.n_small; i += kSelThreads) {
+        const uint32_t d = f32_to_key(S.small[i]) - klo;
+        const uint32_t hi = d >> hi_shift;
+        for (int g = 0; g < n_groups; ++g)
+            if (hi == S.st.gprefix[g]) atomicAdd(&S.tot[g][(d >> shift) & mask], 1u);
+    }
+    __syncthreads();
+    for (int j = 0; j < 2; ++j) {
+        uint32_t bin, krem;
+        find_bin_sm(S, &S.tot[0][0] + S.st.group[j] * kBins, S.st.krem[j], &bin, &krem);
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            S.st.prefix[j] = (S.st.prefix[j] << plan.bits[LEVEL]) | bin;
+            S.st.krem[j] = krem;
+        }
+    }
+    __syncthreads();
+    if (LEVEL < 2 && threadIdx.x == 0) regroup(&S.st);
+    __syncthreads();
 }
 
 __global__ void __launch_bounds__(kSelThreads)
@@ -1297,24 +1341,43 @@ __global__ void __launch_bounds__(kSelThreads)
 
     cluster_level<0>(cluster, S, plan, xs, n, false);
 
-    // keep the elements of the selected level-0 bins (at most two distinct ones) if this CTA's share of them fits
     const uint32_t b0 = S.st.gprefix[0], b1 = (S.st.n_groups > 1) ? S.st.gprefix[1] : b0;
-    const unsigned mine = S.sh[0][b0] + ((b1 != b0) ? S.sh[0][b1] : 0u);   // S.sh still holds this CTA's level-0 counts
-    const bool use_small = mine <= (unsigned)kSmallCap;
-    if (use_small && mine > 0) {
-        const int shift = plan.shift[0];
-        const uint32_t klo = plan.klo, mask = (1u << plan.bits[0]) - 1u;
-        slice_foreach(xs, n, [&](float v) {
-            if (v == v) {
-                const uint32_t digit = ((f32_to_key(v) - klo) >> shift) & mask;
-                if (digit == b0 || digit == b1) S.small[atomicAdd(&S.n_small, 1u)] = v;
-            }
-        });
+    const int shift0 = plan.shift[0];
+    const uint32_t klo0 = plan.klo, mask0 = (1u << plan.bits[0]) - 1u;
+    if (S.st.pad) {
+        // the usual case: the elements of the selected level-0 bins (~1/2048 of the list) go to the leader's list
+        // through distributed shared memory, and the leader runs the remaining levels on its own
+        const unsigned mine = S.sh[0][b0] + ((b1 != b0) ? S.sh[0][b1] : 0u);   // this CTA's level-0 counts
+        if (mine > 0) {
+            float* lead_small = cluster.map_shared_rank(&S.small[0], 0);
+            unsigned* lead_n = cluster.map_shared_rank(&S.n_small, 0);
+            slice_foreach(xs, n, [&](float v) {
+                if (v == v) {
+                    const uint32_t digit = ((f32_to_key(v) - klo0) >> shift0) & mask0;
+                    if (digit == b0 || digit == b1) lead_small[atomicAdd(lead_n, 1u)] = v;
+                }
+            });
+        }
+        cluster.sync();   // the leader's list is complete
+        if (r != 0) return;
+        leader_level<1>(S, plan);
+        leader_level<2>(S, plan);
+    } else {
+        // heavy ties or a fallback to a whole segment: every CTA keeps its share if that fits, else streams again
+        const unsigned mine = S.sh[0][b0] + ((b1 != b0) ? S.sh[0][b1] : 0u);
+        const bool use_small = mine <= (unsigned)kSmallCap;
+        if (use_small && mine > 0) {
+            slice_foreach(xs, n, [&](float v) {
+                if (v == v) {
+                    const uint32_t digit = ((f32_to_key(v) - klo0) >> shift0) & mask0;
+                    if (digit == b0 || digit == b1) S.small[atomicAdd(&S.n_small, 1u)] = v;
+                }
+            });
+        }
+        __syncthreads();
+        cluster_level<1>(cluster, S, plan, xs, n, use_small);
+        cluster_level<2>(cluster, S, plan, xs, n, use_small);
     }
-    __syncthreads();
-
-    cluster_level<1>(cluster, S, plan, xs, n, use_small);
-    cluster_level<2>(cluster, S, plan, xs, n, use_small);
     if (r != 0 || threadIdx.x != 0) return;
     double res;
     if (S.t.total == 0) {
