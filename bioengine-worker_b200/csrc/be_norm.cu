@@ -2,12 +2,11 @@
 //
 //   be_meanvar_f32     one pass, shifted fp64 sums, deterministic two-stage reduction
 //   be_quantile_f32    exact order statistics + numpy's linear lerp: sampled-pivot single pass for large segments
-//                      (qsel_sample / partition / task kernels), 3-level (11/11/10 bit) radix select otherwise
+//                      (qsel_sample / partition kernels, then one thread-block-cluster launch for the selection), 3-level (11/11/10 bit) radix select otherwise
 //   be_normalize_f32   (x - sub) / div in fp64, optional clip
 //   be_elementwise_f32 clip / scale_linear / sigmoid
 //   be_binarize_f32_u8 x > thr
 #include <cooperative_groups.h>
-#include <stdlib.h>
 
 #include "be_common.cuh"
 
@@ -581,14 +580,11 @@ struct QTask {
 };
 
 struct SWorkspace {
-    unsigned* counters;   // [4][n_tasks] (partition uses slot 3, by segment)
+    unsigned* counters;   // [n_seg] completion tickets of the partition pass
     unsigned* nan_count;  // [n_seg]
     unsigned* seg_done;   // [n_seg]
-    unsigned* hist0;      // [n_tasks][kBins]
-    unsigned* hist12;     // [n_tasks][2][kBins]
     QTask* tasks;         // [n_tasks]   (zeroed: counters inside)
-    size_t zero_bytes;
-    QState* state;        // [n_tasks]
+    size_t zero_bytes;    // everything up to here is zeroed at the start of a call
     float* cand;          // [n_tasks][cap]
     int64_t cap;
     size_t total_bytes;
@@ -614,20 +610,14 @@ inline SWorkspace carve_sample_ws(void* ws, int64_t n_seg, int n_q, int64_t seg_
     char* p = (char*)ws;
     size_t off = 0;
     w.counters = (unsigned*)(p + off);
-    off += be_align_up(sizeof(unsigned) * 4 * nt, 256);
+    off += be_align_up(sizeof(unsigned) * n_seg, 256);
     w.nan_count = (unsigned*)(p + off);
     off += be_align_up(sizeof(unsigned) * n_seg, 256);
     w.seg_done = (unsigned*)(p + off);
     off += be_align_up(sizeof(unsigned) * n_seg, 256);
-    w.hist0 = (unsigned*)(p + off);
-    off += be_align_up(sizeof(unsigned) * kBins * nt, 256);
-    w.hist12 = (unsigned*)(p + off);
-    off += be_align_up(sizeof(unsigned) * kBins * 2 * nt, 256);
     w.tasks = (QTask*)(p + off);
     off += be_align_up(sizeof(QTask) * nt, 256);
     w.zero_bytes = off;
-    w.state = (QState*)(p + off);
-    off += be_align_up(sizeof(QState) * nt, 256);
     w.cap = sample_cap(seg_len);
     w.cand = (float*)(p + off);
     off += be_align_up(sizeof(float) * w.cap * nt, 256);
@@ -850,7 +840,7 @@ __global__ void __launch_bounds__(kThreads) qsel_partition_kernel(const float* _
         atomicMax(&tasks[threadIdx.x].nkmin, s_nkmin[threadIdx.x]);
     }
 
-    if (!last_block_of_segment(&w.counters[3 * n_seg * NQ + seg], bps)) return;
+    if (!last_block_of_segment(&w.counters[seg], bps)) return;
 
     // all counts of this segment are final: turn each bracket into a selection task (fields are read into registers
     // up front and the task is written back once, so the serial tail is a handful of memory round trips)
@@ -907,164 +897,6 @@ __global__ void __launch_bounds__(kThreads) qsel_partition_kernel(const float* _
         }
         *t = r;
         __threadfence();
-    }
-}
-
-// ties with the pivots take part in the selection as `vcnt` virtual elements at `vkey`
-template <int LEVEL>
-__device__ __forceinline__ void add_virtual(const QTask* t, const QState* st, unsigned* gh) {
-    constexpr int kBits = (LEVEL == 0) ? 11 : (LEVEL == 1 ? 11 : 10);
-    constexpr int kShift = (LEVEL == 0) ? 21 : (LEVEL == 1 ? 10 : 0);
-    constexpr int kHiShift = kShift + kBits;
-    constexpr uint32_t kMask = (1u << kBits) - 1u;
-    for (int v = 0; v < 2; ++v) {
-        if (!t->vcnt[v]) continue;
-        const uint32_t digit = (t->vkey[v] >> kShift) & kMask;
-        if (LEVEL == 0) {
-            atomicAdd(&gh[digit], t->vcnt[v]);
-        } else {
-            for (int g = 0; g < st->n_groups; ++g)
-                if ((t->vkey[v] >> kHiShift) == st->gprefix[g]) atomicAdd(&gh[g * kBins + digit], t->vcnt[v]);
-        }
-    }
-}
-
-// radix select over the task sources; same structure as the segment kernels, but source, length and ranks come from
-// the task table and blocks past the end of a (short) candidate list only take part in the completion count
-template <int LEVEL>
-__global__ void __launch_bounds__(kThreads) qsel_task_kernel(int bps, int64_t chunk, int n_q, double eps, SWorkspace w,
-                                                             int64_t n_tasks, double* __restrict__ quant,
-                                                             double* __restrict__ norm) {
-    constexpr int kBits = (LEVEL == 0) ? 11 : (LEVEL == 1 ? 11 : 10);
-    constexpr int kShift = (LEVEL == 0) ? 21 : (LEVEL == 1 ? 10 : 0);
-    constexpr int kHiShift = kShift + kBits;
-    constexpr uint32_t kMask = (1u << kBits) - 1u;
-    constexpr int kGroups = (LEVEL == 0) ? 1 : 2;
-    __shared__ unsigned sh[kGroups][kBins];
-    const int64_t task = blockIdx.y;
-    const QTask* t = &w.tasks[task];
-    QState* st = &w.state[task];
-    const float* xs = t->src;
-    const int64_t len = t->len;
-    const int n_groups = (LEVEL == 0) ? 1 : st->n_groups;
-    uint32_t gp[kGroups];
-#pragma unroll
-    for (int g = 0; g < kGroups; ++g) gp[g] = (LEVEL == 0) ? 0u : ((g < n_groups) ? st->gprefix[g] : 0xffffffffu);
-
-    unsigned* gh = (LEVEL == 0) ? (w.hist0 + task * kBins) : (w.hist12 + task * 2 * kBins);
-    if ((int64_t)blockIdx.x * chunk < len) {
-        for (int i = threadIdx.x; i < n_groups * kBins; i += kThreads) (&sh[0][0])[i] = 0;
-        __syncthreads();
-        RunCounter rc[kGroups];
-        float fmin = __int_as_float(0xff800000), fmax = __int_as_float(0x7f800000);
-        if (LEVEL > 0) {
-            fmin = __int_as_float(0x7f800000);
-            fmax = __int_as_float(0xff800000);
-#pragma unroll
-            for (int g = 0; g < kGroups; ++g) {
-                if (g < n_groups) {
-                    fmin = fminf(fmin, key_to_f32(gp[g] << kHiShift));
-                    fmax = fmaxf(fmax, key_to_f32((gp[g] << kHiShift) | ((1u << kHiShift) - 1u)));
-                }
-            }
-        }
-        // the block takes chunks blockIdx.x, blockIdx.x + gridDim.x, ...: a short candidate list is spread over all
-        // blocks, a full segment (fallback) is simply more iterations
-        for (int64_t begin = (int64_t)blockIdx.x * chunk; begin < len; begin += (int64_t)gridDim.x * chunk) {
-            const int64_t end = min(begin + chunk, len);
-            block_foreach(xs + begin, end - begin, [&](float v) {
-                if (v >= fmin && v <= fmax) {  // also drops NaN
-                    const uint32_t key = f32_to_key(v);
-                    const uint32_t digit = (key >> kShift) & kMask;
-                    if (LEVEL == 0) {
-                        rc[0].add(sh[0], digit);
-                    } else {
-                        const uint32_t hi = key >> kHiShift;
-#pragma unroll
-                        for (int g = 0; g < kGroups; ++g)
-                            if (hi == gp[g]) rc[g].add(sh[g], digit);
-                    }
-                }
-            });
-        }
-#pragma unroll
-        for (int g = 0; g < kGroups; ++g) rc[g].flush(sh[g]);
-        __syncthreads();
-        for (int i = threadIdx.x; i < n_groups * kBins; i += kThreads) {
-            const unsigned c = (&sh[0][0])[i];
-            if (c) atomicAdd(&gh[i], c);
-        }
-    }
-    if (!last_block_of_segment(&w.counters[LEVEL * n_tasks + task], bps)) return;
-
-    // the serial tail works on shared-memory copies: global round trips only to fetch and to publish
-    __shared__ QState s_st;
-    __shared__ QTask s_t;
-    if (threadIdx.x == 0) {
-        s_t = *t;
-        if (LEVEL == 0) {
-            s_st.n_ranks = 2;
-            s_st.n_valid = s_t.total;
-            s_st.gamma[0] = s_t.gamma;
-            s_st.n_groups = 1;
-            s_st.gprefix[0] = 0;
-            s_st.group[0] = s_st.group[1] = 0;
-            s_st.prefix[0] = s_st.prefix[1] = 0;
-            s_st.krem[0] = s_t.rank[0];
-            s_st.krem[1] = s_t.rank[1];
-        } else {
-            s_st = *st;
-        }
-        add_virtual<LEVEL>(&s_t, &s_st, gh);
-        __threadfence();
-    }
-    __syncthreads();
-    const uint32_t total = s_t.total;
-    if (total > 0) {
-        for (int j = 0; j < 2; ++j) {
-            uint32_t bin, krem;
-            find_bin(gh + s_st.group[j] * kBins, s_st.krem[j], &bin, &krem);
-            __syncthreads();
-            if (threadIdx.x == 0) {
-                s_st.prefix[j] = (s_st.prefix[j] << kBits) | bin;
-                s_st.krem[j] = krem;
-            }
-        }
-    }
-    __syncthreads();
-    if (LEVEL == 1) {
-        for (int i = threadIdx.x; i < 2 * kBins; i += kThreads) gh[i] = 0;  // the same storage serves level 2
-    }
-    if (LEVEL < 2) {
-        if (threadIdx.x == 0) {
-            regroup(&s_st);
-            *st = s_st;
-        }
-        return;
-    }
-    if (threadIdx.x == 0) {
-        double r;
-        if (total == 0) {
-            r = __longlong_as_double(0x7ff8000000000000LL);
-        } else {
-            // numpy _lerp: fp32 difference, fp64 product and sum, switch of anchor at gamma >= 0.5
-            const float a = key_to_f32(s_st.prefix[0]);
-            const float b = key_to_f32(s_st.prefix[1]);
-            const double d = (double)__fsub_rn(b, a);
-            const double g = s_st.gamma[0];
-            r = (g >= 0.5) ? __dsub_rn((double)b, __dmul_rn(d, __dsub_rn(1.0, g))) : __dadd_rn((double)a, __dmul_rn(d, g));
-        }
-        quant[task] = r;
-        if (norm) {  // the task of a segment that finishes second writes {q0, q1 - q0 + eps}
-            __threadfence();
-            const int64_t seg = task / n_q;
-            if (atomicAdd(&w.seg_done[seg], 1u) == (unsigned)(n_q - 1)) {
-                __threadfence();
-                const double lo = __ldcg(&quant[seg * n_q + 0]), hi = __ldcg(&quant[seg * n_q + 1]);
-                norm[seg * 2 + 0] = lo;
-                norm[seg * 2 + 1] = __dadd_rn(__dsub_rn(hi, lo), eps);
-            }
-        }
     }
 }
 
@@ -1511,14 +1343,7 @@ static int quantile_sampled(const float* x, int64_t n_seg, int64_t seg_len, cons
         else
             qsel_partition_kernel<2><<<grid, kThreads, 0, s>>>(xs, seg_len, sp.bps, sp.chunk, q, w, ns);
         BE_LAUNCH_CHECK();
-        // selection stage: 2048-element chunks dealt round-robin to a grid of about two CTAs per SM over all tasks
-        const int64_t tchunk = 2048;
-        int tb = (int)((int64_t)BE_SM_COUNT * 2 / nt);
-        if (tb < 1) tb = 1;
-        const int64_t most = (seg_len + tchunk - 1) / tchunk;
-        if (tb > most) tb = (int)most;
-        const dim3 tgrid(tb, (unsigned)nt);
-        if (!getenv("BE_QSEL_OLD")) {   // A/B ONLY
+        {
             const int n_cta = select_cluster_size();
             BE_REQUIRE(n_cta > 0, BE_ERR_CUDA, "be_quantile_f32: the device cannot run a thread-block cluster of 8");
             cudaLaunchConfig_t cfg = {};
@@ -1534,14 +1359,7 @@ static int quantile_sampled(const float* x, int64_t n_seg, int64_t seg_len, cons
             cfg.attrs = attr;
             cfg.numAttrs = 1;
             BE_CUDA(cudaLaunchKernelEx(&cfg, qsel_cluster_kernel, n_q, eps, w, qs, nr));
-            continue;
         }
-        qsel_task_kernel<0><<<tgrid, kThreads, 0, s>>>(tb, tchunk, n_q, eps, w, nt, qs, nr);
-        BE_LAUNCH_CHECK();
-        qsel_task_kernel<1><<<tgrid, kThreads, 0, s>>>(tb, tchunk, n_q, eps, w, nt, qs, nr);
-        BE_LAUNCH_CHECK();
-        qsel_task_kernel<2><<<tgrid, kThreads, 0, s>>>(tb, tchunk, n_q, eps, w, nt, qs, nr);
-        BE_LAUNCH_CHECK();
     }
     return BE_OK;
 }
