@@ -102,15 +102,18 @@ __device__ __forceinline__ int be_fast_div(int p, int S, float rS) {
 }
 
 __device__ __forceinline__ float be_div_to_f32(double n, double d, double r) {
-    // q = n * r is within 2^-50 of the exact quotient.  Round q(1 + 2^-44) and q(1 - 2^-44) to fp32: rounding is monotone,
-    // so if both give the same value the correctly rounded fp64 quotient — which lies between them — rounds to it too
-    // (zeros, infinities and fp32 subnormals included).  They differ only next to an fp32 rounding boundary (~2e-6 of
-    // inputs) or for NaN, and those take the real division.
+    // q = n * r is within 2^-50 of the exact quotient Q, i.e. within 8 units of q's last mantissa bit.  fp32 keeps 24 of
+    // the 53 mantissa bits: fp32(q) can differ from fp32(fp64(Q)) only if the 29 dropped bits of q sit next to the
+    // rounding boundary 0x10000000.  Anything within 512 units of it (~4e-6 of inputs) takes the real division, and so
+    // does every result outside the fp32 normal range except an exact zero (q == 0 means Q rounds to the same zero),
+    // which covers subnormals, overflow, infinities and NaN.  One conversion and integer tests, where converting
+    // q(1 + 2^-44) and q(1 - 2^-44) and comparing would cost two conversions and two fp64 FMAs.
     const double q = n * r;
-    const float a = (float)fma(q, 0x1p-44, q);
-    const float b = (float)fma(q, -0x1p-44, q);
-    if (a == b) return a;
-    return be_div_to_f32_exact(n, d);
+    const float f = (float)q;
+    const unsigned dist = ((unsigned)__double2loint(q) & 0x1fffffffu) - 0x0ffffe00u;
+    const unsigned e = __float_as_uint(f) & 0x7f800000u;
+    if (dist <= 0x400u || e == 0x7f800000u || (e == 0u && q != 0.0)) return be_div_to_f32_exact(n, d);
+    return f;
 }
 
 __device__ __forceinline__ double warp_sum(double v) {

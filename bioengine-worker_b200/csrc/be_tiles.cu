@@ -15,6 +15,50 @@ struct Dims {
     int Tz, Ty, Tx, Bz, By, Bx;
 };
 
+// ---- TMA bulk copies + mbarriers (shared by the gather and the blend): one warp fetches contiguous runs of global
+//      memory into a ring of shared-memory stages; `full` barriers count the bytes in, `empty` barriers the readers out ----
+constexpr int kCopyThreads = kThreads + 32;   // eight arithmetic warps + the copy warp
+
+__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(unsigned dst, const void* src, unsigned bytes, unsigned bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                 "l"(src), "r"(bytes), "r"(bar)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
+    unsigned ok = 0;
+    for (int spin = 0; !ok; ++spin) {
+        asm volatile(
+            "{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+            : "=r"(ok)
+            : "r"(bar), "r"(parity)
+            : "memory");
+        if (spin > (1 << 22)) __trap();  // a byte count that never arrives is a bug, not something to wait out
+    }
+}
+
+__device__ __forceinline__ bool mbar_try_wait(unsigned bar, unsigned parity) {
+    unsigned ok;
+    asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                 : "=r"(ok)
+                 : "r"(bar), "r"(parity)
+                 : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ float4 lds128(unsigned addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+    return v;
+}
+
 template <bool CLIP>
 __device__ __forceinline__ float norm_apply(float v, double sub, double div, double rdiv, float lo, float hi) {
     // np.clip on the fp64 quotient then a cast equals a clip of the cast value: the bounds are fp32 numbers
@@ -31,32 +75,30 @@ __device__ __forceinline__ float norm_apply(float v, double sub, double div, dou
 // the rows of its band, so the tile / plane decomposition (integer divides) is paid once per thread, not once per
 // 16 bytes, and several independent row loads are in flight per thread.
 template <bool NORM, bool CLIP>
-__global__ void __launch_bounds__(kThreads) tile_gather_kernel(const float* __restrict__ img, float* __restrict__ tiles,
-                                                               Dims d, const int32_t* __restrict__ zsrc,
-                                                               const int32_t* __restrict__ ysrc,
-                                                               const int32_t* __restrict__ xsrc,
-                                                               const double* __restrict__ norm, int norm_mode,
-                                                               float clip_lo, float clip_hi, int units_per_row,
-                                                               int rows_per_band) {
+__device__ __forceinline__ void gather_direct(const float* __restrict__ img, float* __restrict__ tiles, const Dims& d,
+                                              const int32_t* __restrict__ zsrc, const int32_t* __restrict__ ysrc,
+                                              const int32_t* __restrict__ xsrc, const double* __restrict__ norm,
+                                              int norm_mode, float clip_lo, float clip_hi, int units_per_row,
+                                              int rows_per_band, unsigned tile, unsigned cz, unsigned band) {
     const int ucols = min(units_per_row, kThreads);     // column units the block covers per sweep
     const int u_in = threadIdx.x % ucols;
     const int r_in = threadIdx.x / ucols;               // first row offset inside the band
     const int r_step = kThreads / ucols;                // rows the block covers per sweep
     if (r_in >= r_step) return;
-    unsigned t = blockIdx.x;
+    unsigned t = tile;
     const int kx = t % d.Tx;
     t /= d.Tx;
     const int ky = t % d.Ty;
     t /= d.Ty;
     const int kz = t % d.Tz;
     const int64_t n = t / d.Tz;
-    const int c = blockIdx.y / d.Bz, iz = blockIdx.y - c * d.Bz;
-    const int iy0 = blockIdx.z * rows_per_band, iy1 = min(iy0 + rows_per_band, d.By);
+    const int c = cz / d.Bz, iz = cz - c * d.Bz;
+    const int iy0 = band * rows_per_band, iy1 = min(iy0 + rows_per_band, d.By);
 
     const int64_t sz = zsrc[kz * d.Bz + iz];
     const float* plane = img + ((n * d.C + c) * d.Z + sz) * d.Y * d.X;
     const int32_t* ys = ysrc + ky * d.By;
-    float* dst_tile = tiles + (((int64_t)blockIdx.x * d.C + c) * d.Bz + iz) * (int64_t)d.By * d.Bx;
+    float* dst_tile = tiles + (((int64_t)tile * d.C + c) * d.Bz + iz) * (int64_t)d.By * d.Bx;
 
     double sub = 0.0, div = 1.0, rdiv = 1.0;
     if (NORM) {
@@ -104,6 +146,190 @@ __global__ void __launch_bounds__(kThreads) tile_gather_kernel(const float* __re
             }
         }
     }
+    }
+}
+
+template <bool NORM, bool CLIP>
+__global__ void __launch_bounds__(kThreads) tile_gather_kernel(const float* __restrict__ img, float* __restrict__ tiles,
+                                                               Dims d, const int32_t* __restrict__ zsrc,
+                                                               const int32_t* __restrict__ ysrc,
+                                                               const int32_t* __restrict__ xsrc,
+                                                               const double* __restrict__ norm, int norm_mode,
+                                                               float clip_lo, float clip_hi, int units_per_row,
+                                                               int rows_per_band) {
+    gather_direct<NORM, CLIP>(img, tiles, d, zsrc, ysrc, xsrc, norm, norm_mode, clip_lo, clip_hi, units_per_row,
+                              rows_per_band, blockIdx.x, blockIdx.y, blockIdx.z);
+}
+
+// The same gather fed by TMA bulk copies, for the usual geometry (Bx a multiple of 4 whose unit count divides 256, X a
+// multiple of 4, 16-byte aligned buffers).  A tile row whose x sources are one contiguous, aligned run of the image row
+// (every tile that does not touch the left / right border) is a single cp.async.bulk.
+//
+// Persistent blocks: the grid is one wave (3 blocks per SM) and every block walks work items (tile, plane, band of
+// rows) with a grid stride.  The copy warp runs ahead of the arithmetic warps across item boundaries, so the ring of
+// kGatherStages x 16 KB stages never drains: with one block per item (the direct kernel) every block pays table
+// look-ups and a first round of loads before it moves a byte, and at ~90 rows per block that start-up was a third of
+// the kernel.  Border tiles (reflected sources) take the direct path inside the same launch.
+constexpr int kGatherStages = 4;
+constexpr int kGatherSweeps = 4;                                   // sweeps of the 256 threads per stage
+constexpr int kGatherStageBytes = kGatherSweeps * kThreads * 16;   // 16 KB: 16 rows of a 256-px tile
+constexpr int kGatherMaxTx = 2048;
+
+struct GatherItem {
+    unsigned tile, cz, band;
+    int kx, ky, kz, c, iz, iy0, iy1;
+    int64_t n;
+};
+
+__device__ __forceinline__ GatherItem gather_item(unsigned item, const Dims& d, int cz_count, int bands, int rows_per_band) {
+    GatherItem it;
+    it.band = item % bands;
+    const unsigned rest = item / bands;
+    it.cz = rest % cz_count;
+    it.tile = rest / cz_count;
+    unsigned t = it.tile;
+    it.kx = t % d.Tx;
+    t /= d.Tx;
+    it.ky = t % d.Ty;
+    t /= d.Ty;
+    it.kz = t % d.Tz;
+    it.n = t / d.Tz;
+    it.c = it.cz / d.Bz;
+    it.iz = it.cz - it.c * d.Bz;
+    it.iy0 = it.band * rows_per_band;
+    it.iy1 = min(it.iy0 + rows_per_band, d.By);
+    return it;
+}
+
+template <bool NORM, bool CLIP>
+__global__ void __launch_bounds__(kCopyThreads, 3) tile_gather_tma_kernel(const float* __restrict__ img, float* __restrict__ tiles,
+                                                                       Dims d, const int32_t* __restrict__ zsrc,
+                                                                       const int32_t* __restrict__ ysrc,
+                                                                       const int32_t* __restrict__ xsrc,
+                                                                       const double* __restrict__ norm, int norm_mode,
+                                                                       float clip_lo, float clip_hi, int units_per_row,
+                                                                       int rows_per_band, int bands, unsigned n_items) {
+    extern __shared__ __align__(128) unsigned char s_stage[];   // kGatherStages * kGatherStageBytes
+    __shared__ __align__(8) unsigned long long s_bar[2 * kGatherStages];
+    __shared__ unsigned s_ok[kGatherMaxTx / 32];   // bit kx: the x sources of tile column kx are one aligned run
+    const int tid = threadIdx.x;
+    for (int i = tid; i < kGatherMaxTx / 32; i += kCopyThreads) s_ok[i] = 0xffffffffu;
+    const unsigned smem0 = (unsigned)__cvta_generic_to_shared(s_stage);
+    const unsigned bar0 = (unsigned)__cvta_generic_to_shared(s_bar);
+    if (tid == 0) {
+#pragma unroll
+        for (int i = 0; i < kGatherStages; ++i) {
+            mbar_init(bar0 + 8 * i, 1);
+            mbar_init(bar0 + 8 * (kGatherStages + i), kThreads / 32);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    for (int i = tid; i < d.Tx * units_per_row; i += kCopyThreads) {
+        const int kx = i / units_per_row, u = i - kx * units_per_row;
+        const int x_first = xsrc[kx * d.Bx];
+        const int4 xi = *reinterpret_cast<const int4*>(xsrc + kx * d.Bx + 4 * u);
+        const bool ok = (x_first & 3) == 0 && xi.x == x_first + 4 * u && xi.y == xi.x + 1 && xi.z == xi.x + 2 && xi.w == xi.x + 3;
+        if (!ok) atomicAnd(&s_ok[kx >> 5], ~(1u << (kx & 31)));
+    }
+    __syncthreads();
+
+    const int r_sweep = kThreads / units_per_row;       // rows per sweep; units_per_row divides kThreads here
+    const int r_stage = r_sweep * kGatherSweeps;        // rows per stage
+    const int cz_count = (int)d.C * d.Bz;
+    const unsigned row_bytes = (unsigned)d.Bx * 4;
+
+    if (tid >= kThreads) {   // the copy warp: lane r fetches rows r, r + 32, ... of every step
+        const int lane = tid & 31;
+        unsigned st = 0, par = 0;
+        for (unsigned item = blockIdx.x; item < n_items; item += gridDim.x) {
+            const GatherItem it = gather_item(item, d, cz_count, bands, rows_per_band);
+            if (!((s_ok[it.kx >> 5] >> (it.kx & 31)) & 1u)) continue;
+            const int64_t sz = zsrc[it.kz * d.Bz + it.iz];
+            const float* plane = img + ((it.n * d.C + it.c) * d.Z + sz) * d.Y * d.X + xsrc[it.kx * d.Bx];
+            const int32_t* ys = ysrc + it.ky * d.By;
+            const int n_steps = (it.iy1 - it.iy0 + r_stage - 1) / r_stage;
+            for (int g = 0; g < n_steps; ++g) {
+                const int row0 = it.iy0 + g * r_stage;
+                const int rows = min(r_stage, it.iy1 - row0);
+                // the source rows first: these loads do not depend on the stage being free
+                int64_t off[2];
+#pragma unroll
+                for (int k = 0; k < 2; ++k) off[k] = (lane + 32 * k < rows) ? (int64_t)ys[row0 + lane + 32 * k] * d.X : 0;
+                mbar_wait(bar0 + 8 * (kGatherStages + st), par ^ 1);
+                if (lane == 0) {
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic reads before async writes
+                    mbar_expect_tx(bar0 + 8 * st, rows * row_bytes);
+                }
+                __syncwarp();
+#pragma unroll
+                for (int k = 0; k < 2; ++k)
+                    if (lane + 32 * k < rows)
+                        bulk_g2s(smem0 + st * kGatherStageBytes + (lane + 32 * k) * row_bytes, plane + off[k], row_bytes,
+                                 bar0 + 8 * st);
+                for (int r = lane + 64; r < rows; r += 32)   // tiles narrower than 64 px: more than 64 rows per stage
+                    bulk_g2s(smem0 + st * kGatherStageBytes + r * row_bytes, plane + (int64_t)ys[row0 + r] * d.X,
+                             row_bytes, bar0 + 8 * st);
+                if (++st == kGatherStages) {
+                    st = 0;
+                    par ^= 1;
+                }
+            }
+        }
+        return;
+    }
+
+    // thread -> (row of the sweep, 4-px unit): its 16 bytes sit at (sweep * kThreads + tid) * 16 of the stage
+    const int r_in = tid / units_per_row, u_in = tid - r_in * units_per_row;
+    const int64_t dsweep = (int64_t)r_sweep * d.Bx;
+    unsigned st = 0, par = 0, sa = smem0 + tid * 16;
+    double sub = 0.0, div = 1.0, rdiv = 1.0;
+    int64_t have = -1;   // segment whose normalisation constants are loaded
+    for (unsigned item = blockIdx.x; item < n_items; item += gridDim.x) {
+        const GatherItem it = gather_item(item, d, cz_count, bands, rows_per_band);
+        if (!((s_ok[it.kx >> 5] >> (it.kx & 31)) & 1u)) {
+            gather_direct<NORM, CLIP>(img, tiles, d, zsrc, ysrc, xsrc, norm, norm_mode, clip_lo, clip_hi, units_per_row,
+                                      rows_per_band, it.tile, it.cz, it.band);
+            continue;
+        }
+        if (NORM) {
+            const int64_t s = (norm_mode == 1) ? (it.n * d.C + it.c) : it.n;
+            if (s != have) {
+                sub = norm[2 * s];
+                div = norm[2 * s + 1];
+                rdiv = be_fast_rcp(div);
+                have = s;
+            }
+        }
+        float* dst = tiles + ((((int64_t)it.tile * d.C + it.c) * d.Bz + it.iz) * (int64_t)d.By + it.iy0 + r_in) * d.Bx + u_in * 4;
+        int row = it.iy0 + r_in;
+        const int n_steps = (it.iy1 - it.iy0 + r_stage - 1) / r_stage;
+        for (int g = 0; g < n_steps; ++g) {
+            if (!mbar_try_wait(bar0 + 8 * st, par)) mbar_wait(bar0 + 8 * st, par);
+            float4 v[kGatherSweeps];
+#pragma unroll
+            for (int k = 0; k < kGatherSweeps; ++k) v[k] = lds128(sa + k * kThreads * 16);
+            __syncwarp();
+            if ((tid & 31) == 0) mbar_arrive(bar0 + 8 * (kGatherStages + st));   // this warp has read its part of the stage
+#pragma unroll
+            for (int k = 0; k < kGatherSweeps; ++k, row += r_sweep, dst += dsweep) {
+                if (row < it.iy1) {
+                    if (NORM) {
+                        v[k].x = norm_apply<CLIP>(v[k].x, sub, div, rdiv, clip_lo, clip_hi);
+                        v[k].y = norm_apply<CLIP>(v[k].y, sub, div, rdiv, clip_lo, clip_hi);
+                        v[k].z = norm_apply<CLIP>(v[k].z, sub, div, rdiv, clip_lo, clip_hi);
+                        v[k].w = norm_apply<CLIP>(v[k].w, sub, div, rdiv, clip_lo, clip_hi);
+                    }
+                    st_stream_f4(reinterpret_cast<float4*>(dst), v[k]);
+                }
+            }
+            sa += kGatherStageBytes;
+            if (++st == kGatherStages) {
+                st = 0;
+                par ^= 1;
+                sa -= kGatherStages * kGatherStageBytes;
+            }
+        }
     }
 }
 
@@ -323,45 +549,6 @@ static __device__ __noinline__ bool blend_decide_exact(double acc, double wacc, 
 // 2 x 96 (too few warps to hide the fp64 / conversion latencies) and 4 x 56 (spills)
 constexpr int kStages = 4;
 
-__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(unsigned bar, unsigned bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(unsigned bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void bulk_g2s(unsigned dst, const void* src, unsigned bytes, unsigned bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
-                 "l"(src), "r"(bytes), "r"(bar)
-                 : "memory");
-}
-__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
-    unsigned ok = 0;
-    for (int spin = 0; !ok; ++spin) {
-        asm volatile(
-            "{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
-            : "=r"(ok)
-            : "r"(bar), "r"(parity)
-            : "memory");
-        if (spin > (1 << 22)) __trap();  // a byte count that never arrives is a bug, not something to wait out
-    }
-}
-
-__device__ __forceinline__ bool mbar_try_wait(unsigned bar, unsigned parity) {
-    unsigned ok;
-    asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
-                 : "=r"(ok)
-                 : "r"(bar), "r"(parity)
-                 : "memory");
-    return ok != 0;
-}
-__device__ __forceinline__ float4 lds128(unsigned addr) {
-    float4 v;
-    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
-    return v;
-}
 // four pixels of one tile row into the accumulators: w = fp32(wzy * wx), acc += fp64(fp32(p * w)), wacc += fp64(w)
 __device__ __forceinline__ double2 lds_d2(unsigned addr) {
     double2 v;
@@ -403,7 +590,7 @@ struct RowCover {
     }
 };
 
-constexpr int kRowsThreads = kThreads + 32;   // eight arithmetic warps + the copy warp
+constexpr int kRowsThreads = kCopyThreads;
 
 template <bool FAST>
 __global__ void __launch_bounds__(kRowsThreads, 3) stitch_blend_rows_kernel(const float* __restrict__ tiles, float* __restrict__ out,
@@ -697,7 +884,31 @@ extern "C" int be_tile_gather_f32(const float* img, float* tiles, int64_t N, int
     bands = (By + rows_per_band - 1) / rows_per_band;
     const dim3 grid((unsigned)n_tiles, (unsigned)(C * Bz), (unsigned)bands);
     cudaStream_t s = (cudaStream_t)stream;
-    if (norm_mode && clip)
+    const bool tma = (Bx & 3) == 0 && (X & 3) == 0 && upr <= kThreads && kThreads % upr == 0 && Tx <= kGatherMaxTx &&
+                     ((((uintptr_t)img) | ((uintptr_t)tiles)) & 15) == 0;
+    if (tma) {
+        // work items of two stages of rows each; one wave of persistent blocks walks them
+        const int r_stage = kThreads / upr * kGatherSweeps;
+        const int rpb = 2 * r_stage;
+        const int nb = (By + rpb - 1) / rpb;
+        const int64_t n_items = n_tiles * C * Bz * nb;
+        BE_REQUIRE(n_items < ((int64_t)1 << 31), BE_ERR_TOO_LARGE, "be_tile_gather_f32: too many work items");
+        const size_t smem = (size_t)kGatherStages * kGatherStageBytes;
+        const unsigned blocks = (unsigned)(n_items < (int64_t)BE_SM_COUNT * 3 ? n_items : (int64_t)BE_SM_COUNT * 3);
+        if (norm_mode && clip) {
+            BE_CUDA(cudaFuncSetAttribute(tile_gather_tma_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            tile_gather_tma_kernel<true, true><<<blocks, kCopyThreads, smem, s>>>(img, tiles, d, zsrc, ysrc, xsrc, norm, norm_mode,
+                                                                                 clip_lo, clip_hi, upr, rpb, nb, (unsigned)n_items);
+        } else if (norm_mode) {
+            BE_CUDA(cudaFuncSetAttribute(tile_gather_tma_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            tile_gather_tma_kernel<true, false><<<blocks, kCopyThreads, smem, s>>>(img, tiles, d, zsrc, ysrc, xsrc, norm, norm_mode,
+                                                                                  0.f, 0.f, upr, rpb, nb, (unsigned)n_items);
+        } else {
+            BE_CUDA(cudaFuncSetAttribute(tile_gather_tma_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            tile_gather_tma_kernel<false, false><<<blocks, kCopyThreads, smem, s>>>(img, tiles, d, zsrc, ysrc, xsrc, norm, 0, 0.f,
+                                                                                   0.f, upr, rpb, nb, (unsigned)n_items);
+        }
+    } else if (norm_mode && clip)
         tile_gather_kernel<true, true><<<grid, kThreads, 0, s>>>(img, tiles, d, zsrc, ysrc, xsrc, norm, norm_mode, clip_lo,
                                                                  clip_hi, upr, rows_per_band);
     else if (norm_mode)
