@@ -222,9 +222,25 @@ __global__ void __launch_bounds__(kThreads) ccl_tile_kernel(const uint8_t* __res
         }
     }
     __syncthreads();
+    // ---- C2: every run takes its root's label (a non-root slot is read by nobody else, so this is done in place);
+    //          a root run flags its first pixel in the root bitmap ----
+    {
+        const int r = threadIdx.x >> 2, part = threadIdx.x & 3;
+        const int n_runs = __popcll(rstart[r]);
+        u64 roots = 0;
+        for (int k = part; k < n_runs; k += 4) {
+            const unsigned id = r * 32 + k;
+            const unsigned root = parent[id];
+            if (root == id)
+                roots |= 1ull << xstart[id];
+            else
+                glab[id] = glab[root];
+        }
+        if (roots) atomicOr(&rroot[r], roots);
+    }
+    __syncthreads();
 
-    // ---- D: per-pixel parents, 4 pixels per lane (one 16-byte store), two rows per warp instruction; tile roots
-    //         (first pixel of a run that is its own root) go to the root bitmap ----
+    // ---- D: per-pixel parents, 4 pixels per lane (one 16-byte store), two rows per warp instruction ----
     {
         const int64_t wpr = g.tiles_x;
         const int lane16 = lane & 15, sub = lane >> 4;
@@ -238,26 +254,15 @@ __global__ void __launch_bounds__(kThreads) ccl_tile_kernel(const uint8_t* __res
             const u64 m = rmask[r], s = rstart[r];
             const unsigned m4 = (unsigned)(m >> x4) & 0xfu, s4 = (unsigned)(s >> x4) & 0xfu;
             if (m4 == 0) continue;   // parents exist only where the mask has pixels: nobody reads the rest
-            int idx = r * 32 + __popcll(s & ((1ull << x4) - 1ull)) - 1;  // run open before this unit (if any)
-            int32_t v[4] = {-1, -1, -1, -1};
-            int32_t cur = -1;
-            bool have = false;
-            unsigned rootnib = 0;
+            // four pixels hold at most two runs: A = the one containing the first set pixel, B = a second one starting
+            // inside the unit (its index is A's + 1)
+            const int f = __ffs(m4) - 1;
+            const int idxA = r * 32 + __popcll(s & ((1ull << x4) - 1ull)) - 1 + (int)((s4 >> f) & 1u);
+            const unsigned runA = m4 & ~(m4 + (1u << f)), runB = m4 & ~runA;
+            const int32_t labA = glab[idxA], labB = runB ? glab[idxA + 1] : -1;
+            int32_t v[4];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                if ((s4 >> j) & 1u) {
-                    ++idx;
-                    const unsigned root = parent[idx];
-                    cur = glab[root];
-                    have = true;
-                    if (root == (unsigned)idx) rootnib |= 1u << j;
-                } else if (((m4 >> j) & 1u) && !have) {
-                    cur = glab[parent[idx]];
-                    have = true;
-                }
-                if ((m4 >> j) & 1u) v[j] = cur;
-            }
-            if (rootnib) atomicOr(&rroot[r], (u64)rootnib << x4);
+            for (int j = 0; j < 4; ++j) v[j] = ((runA >> j) & 1u) ? labA : (((runB >> j) & 1u) ? labB : -1);
             if (!row_ok) continue;
             int32_t* row = Li + (z * g.Y + y) * g.X + x0 + x4;
             if (vec_ok && x0 + x4 + 4 <= g.X) {
