@@ -168,7 +168,12 @@ __global__ void __launch_bounds__(kThreads) ccl_tile_kernel(const uint8_t* __res
             }
         }
     }
-    for (int i = threadIdx.x; i < kMaxRuns; i += kThreads) parent[i] = i;
+    __syncthreads();
+    // union-find nodes: only the runs that exist (a row's share of the 2048 slots is mostly unused)
+    {
+        const int r = threadIdx.x >> 2, n_runs = __popcll(rstart[r]);
+        for (int k = threadIdx.x & 3; k < n_runs; k += 4) parent[r * 32 + k] = r * 32 + k;
+    }
     __syncthreads();
 
     // ---- B: every run is linked to the runs it touches in the rows before it.  Four threads share a row and take
@@ -246,11 +251,14 @@ __global__ void __launch_bounds__(kThreads) ccl_tile_kernel(const uint8_t* __res
         const int lane16 = lane & 15, sub = lane >> 4;
         const int x4 = lane16 * 4;
         const bool vec_ok = ((g.X & 3) == 0) && ((((uintptr_t)Li) & 15) == 0);
+        // the warp's eight rows are consecutive in y (2-D: 64 rows of one plane; 3-D: one 8-row plane of the tile)
+        const int r0 = warp * 8 + sub;
+        const int64_t zw = z0 + (r0 >> g.ty_log2), yw = y0 + (r0 & ty_mask);
+        int32_t* row = Li + (zw * g.Y + yw) * g.X + x0 + x4;
 #pragma unroll 1
-        for (int it = 0; it < 4; ++it) {
-            const int r = warp * 8 + it * 2 + sub;
-            const int64_t z = z0 + (r >> g.ty_log2), y = y0 + (r & ty_mask);
-            const bool row_ok = z < g.Z && y < g.Y;
+        for (int it = 0; it < 4; ++it, row += 2 * g.X) {
+            const int r = r0 + it * 2;
+            const bool row_ok = zw < g.Z && yw + it * 2 < g.Y;
             const u64 m = rmask[r], s = rstart[r];
             const unsigned m4 = (unsigned)(m >> x4) & 0xfu, s4 = (unsigned)(s >> x4) & 0xfu;
             if (m4 == 0) continue;   // parents exist only where the mask has pixels: nobody reads the rest
@@ -264,7 +272,6 @@ __global__ void __launch_bounds__(kThreads) ccl_tile_kernel(const uint8_t* __res
 #pragma unroll
             for (int j = 0; j < 4; ++j) v[j] = ((runA >> j) & 1u) ? labA : (((runB >> j) & 1u) ? labB : -1);
             if (!row_ok) continue;
-            int32_t* row = Li + (z * g.Y + y) * g.X + x0 + x4;
             if (vec_ok && x0 + x4 + 4 <= g.X) {
                 *reinterpret_cast<int4*>(row) = make_int4(v[0], v[1], v[2], v[3]);
             } else {
