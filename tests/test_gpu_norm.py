@@ -177,6 +177,9 @@ def test_sampled_quantile_distributions(q, dev, rng):
         "signed zeros": np.where(rng.random(n) < 0.5, -0.0, 0.0).astype(np.float32),
         "heavy tail": (rng.standard_cauchy(n) * 1e3).astype(np.float32),
         "sorted": np.sort(rng.standard_normal(n)).astype(np.float32),
+        # ~160 distinct values: the list between the pivots is thousands of copies of one or two values, so the level-0
+        # bins cannot be gathered into the leader CTA and the cluster-wide levels run
+        "rounded normal": np.round(rng.standard_normal(n) * 20).astype(np.float32),
     }
     for name, x in cases.items():
         got, _ = _quant(x, q, 1, dev)
@@ -220,3 +223,28 @@ def test_sampled_quantile_many_segments_one_call(dev, rng):
     got, _ = _quant(x, (0.01, 0.998), n_seg, dev)
     want = np.nanquantile(x, np.array([0.01, 0.998]), axis=1, method="linear").T
     assert np.array_equal(got, want)
+
+
+def test_sampled_quantile_long_tied_lists_stream_every_level(dev, rng):
+    """8 M elements rounded to ~300 values: a bracket holds ~10^5 equal elements, more than a CTA's shared-memory list, so
+    the selection streams its slice on every level (the path a fallback to a whole segment takes as well)."""
+    n = 1 << 23
+    x = np.round(rng.standard_normal(n) * 40).astype(np.float32)
+    for q in ((0.01, 0.998), (0.3, 0.7)):
+        got, _ = _quant(x, q, 1, dev)
+        assert np.array_equal(got[0], np.nanquantile(x, np.asarray(q, np.float64), method="linear"))
+
+
+def test_sampled_quantile_ranks_on_and_next_to_pivot_ties(dev, rng):
+    """Ranks that fall inside the run of elements equal to a pivot, and one element either side of it."""
+    n = 1 << 19
+    base = rng.random(n).astype(np.float32)
+    for frac in (0.2, 0.5, 0.8):
+        x = base.copy()
+        x[rng.random(n) < 0.3] = np.float32(frac)      # 30 % of the data is one value sitting at quantile ~frac
+        xs = np.sort(x)
+        lo, hi = np.searchsorted(xs, np.float32(frac), "left"), np.searchsorted(xs, np.float32(frac), "right")
+        for k in (lo - 1, lo, lo + 1, (lo + hi) // 2, hi - 2, hi - 1, hi):
+            q = (k / (n - 1), min(1.0, (k + 0.5) / (n - 1)))
+            got, _ = _quant(x, q, 1, dev)
+            assert np.array_equal(got[0], np.nanquantile(x, np.asarray(q, np.float64), method="linear")), (frac, k)

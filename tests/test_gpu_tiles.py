@@ -123,3 +123,76 @@ def test_c2_geometry_full_size_round_trip(dev):
     one = torch.ones(1, dtype=torch.float64, device=dev)
     bl, _ = K().stitch_blend(ft, (1, 1, 4096, 4096), faxes, (one, w1, w1))
     torch.testing.assert_close(bl, x, rtol=1e-5, atol=1e-6)
+
+
+# ---- the TMA-fed kernels (aligned geometry) next to the general ones: every path of both ----
+
+@pytest.mark.parametrize("shape,block,halo", [
+    ((2, 3, 96, 128), (64, 64), (8, 8)),        # batch + channels, interior and border tiles in one launch
+    ((1, 1, 300, 64), (200, 16), (4, 2)),       # 16-px-wide tiles: more than 64 rows per shared-memory stage
+    ((1, 2, 24, 40, 64), (8, 16, 32), (1, 2, 4)),  # 3-D, different block per axis
+    ((1, 1, 64, 1024), (32, 512), (4, 16)),     # 512-px-wide tiles (two 4-px-unit sweeps per row group)
+])
+def test_gather_tma_paths_bit_exact(shape, block, halo, dev, rng):
+    x = rng.standard_normal(shape).astype(np.float32)
+    nd = len(block)
+    axes = [G.bioimageio_axis(s, b, h) for s, b, h in zip(shape[2:], block, halo)]
+    if nd == 2:
+        axes = [G.identity_axis(1)] + axes
+    tiles = K().tile_gather(torch.from_numpy(x).to(dev), dev_axes(axes, dev)).cpu().numpy()
+    assert np.array_equal(tiles, O.blocks_tensor(x, block, halo))
+    # the fused normalisation through the same kernel: per-sample constants, clip
+    norm = torch.tensor([[0.1, 1.7]] * shape[0], dtype=torch.float64, device=dev)
+    fused = K().tile_gather(torch.from_numpy(x).to(dev), dev_axes(axes, dev), norm=norm, norm_mode=2, clip=(0.0, 1.0))
+    want = np.clip((x.astype(np.float64) - 0.1) / 1.7, 0.0, 1.0).astype(np.float32)
+    assert np.array_equal(fused.cpu().numpy(), O.blocks_tensor(want, block, halo))
+
+
+@pytest.mark.parametrize("spatial,B,ov,N,C", [
+    ((128, 256), 64, 16, 2, 2),      # rows kernel, several (n, c) planes
+    ((40, 52, 96), 32, 8, 1, 1),     # rows kernel, 3-D: a row's kz tiles are consecutive steps
+    ((40, 52, 96), 32, 8, 1, 2),
+    ((70, 81, 90), 32, 8, 1, 1),     # X not a multiple of 4: the general kernel
+])
+@pytest.mark.parametrize("thr", [0.5, 0.3])
+def test_blend_kernels_all_epilogues(spatial, B, ov, N, C, thr, dev, rng):
+    nd = len(spatial)
+    axes = [G.fibsem_axis(s, B, ov) for s in spatial]
+    if nd == 2:
+        axes = [G.identity_axis(1)] + axes
+    T = int(np.prod([a.T for a in axes]))
+    logits = (rng.standard_normal((N * T, C) + (B,) * nd) * 2).astype(np.float32)
+    w1 = torch.from_numpy(G.gauss_window_1d(B)).to(dev)
+    wins = (w1,) * 3 if nd == 3 else (torch.ones(1, dtype=torch.float64, device=dev), w1, w1)
+    ld = torch.from_numpy(logits).to(dev)
+    daxes = dev_axes(axes, dev)
+    shape = (N, C) + tuple(spatial)
+    want = np.stack([np.stack([O.fibsem_blend(logits[n * T:(n + 1) * T, c], spatial, B, ov) for c in range(C)])
+                     for n in range(N)])
+    out, mask = K().stitch_blend(ld, shape, daxes, wins, want_mask=True, thr=thr)             # raw blend + threshold
+    assert np.array_equal(out.cpu().numpy(), want)
+    assert np.array_equal(mask.cpu().numpy(), O.binarize(want, thr))
+    prob, pmask = K().stitch_blend(ld, shape, daxes, wins, epilogue=1, want_mask=True, thr=thr)   # sigmoid, both outputs
+    assert np.array_equal(prob.cpu().numpy(), O.sigmoid(want))
+    assert np.array_equal(pmask.cpu().numpy(), O.binarize(O.sigmoid(want), thr))
+    _, only = K().stitch_blend(ld, shape, daxes, wins, epilogue=1, want_out=False, want_mask=True, thr=thr)  # band test
+    assert np.array_equal(only.cpu().numpy(), O.binarize(O.sigmoid(want), thr))
+
+
+def test_blend_band_test_on_values_at_the_threshold(dev):
+    """Logits planted exactly at, one ulp below and one ulp above logit(thr) — where the division-free band test must
+    hand over to the exact quotient and numpy's fp32 sigmoid."""
+    B, ov, H, W = 64, 16, 96, 128
+    axes = [G.identity_axis(1), G.fibsem_axis(H, B, ov), G.fibsem_axis(W, B, ov)]
+    T = axes[1].T * axes[2].T
+    for thr in (0.5, 0.3, 0.9):
+        L = np.float32(np.log(thr / (1 - thr)))
+        vals = np.array([L, np.nextafter(L, np.float32(-9)), np.nextafter(L, np.float32(9)), L + np.float32(5e-5),
+                         L - np.float32(5e-5), 0.0, -0.0], np.float32)
+        logits = np.tile(vals, (T * B * B + len(vals) - 1) // len(vals))[:T * B * B].reshape(T, 1, B, B).copy()
+        w1 = torch.from_numpy(G.gauss_window_1d(B)).to(dev)
+        wins = (torch.ones(1, dtype=torch.float64, device=dev), w1, w1)
+        want = O.fibsem_blend(logits[:, 0], (H, W), B, ov)
+        _, only = K().stitch_blend(torch.from_numpy(logits).to(dev), (1, 1, H, W), dev_axes(axes, dev), wins, epilogue=1,
+                                   want_out=False, want_mask=True, thr=thr)
+        assert np.array_equal(only.cpu().numpy()[0, 0], O.binarize(O.sigmoid(want), thr)), thr
