@@ -24,11 +24,11 @@ struct SegSplit {
     int bps;
     int64_t chunk;
 };
-inline SegSplit split_segment(int64_t n_seg, int64_t seg_len) {
+inline SegSplit split_segment(int64_t n_seg, int64_t seg_len, int64_t max_blocks = kMaxBlocksPerSeg) {
     // Few fat blocks: a block's fixed cost (zeroing and flushing a shared histogram, the block reduction) is paid
     // once per ~10^4 elements, and the whole grid is about 8 CTAs per SM across all segments.
     const int64_t min_per_block = (int64_t)kThreads * 16;
-    int64_t bps = kMaxBlocksPerSeg / (n_seg < 1 ? 1 : n_seg);
+    int64_t bps = max_blocks / (n_seg < 1 ? 1 : n_seg);
     if (bps < 1) bps = 1;
     const int64_t most = (seg_len + min_per_block - 1) / min_per_block;
     if (bps > most) bps = most;
@@ -720,6 +720,10 @@ __global__ void __launch_bounds__(kThreads) qsel_partition_kernel(const float* _
 
     // rare path, one element: ties with the pivots are counted, the rest of the bracket is appended
     auto take_inside = [&](float v) {
+        if (v != v) {   // NaNs are flagged by the common path (they fail both of its comparisons) and counted here
+            ++nans;
+            return;
+        }
 #pragma unroll
         for (int i = 0; i < NQ; ++i) {
             if (v >= flo[i] && v <= fhi[i]) {
@@ -743,14 +747,14 @@ __global__ void __launch_bounds__(kThreads) qsel_partition_kernel(const float* _
     };
     // common path, one element: a compare-and-count per bracket; returns whether the element needs the rare path
     auto classify = [&](float v) -> bool {
-        nans += (v != v);
-        bool inside = false;
+        bool flagged = false;
 #pragma unroll
         for (int i = 0; i < NQ; ++i) {
-            below[i] += (v < flo[i]);
-            inside |= (v >= flo[i]) & (v <= fhi[i]);  // NaN is never inside
+            const bool lt = v < flo[i];
+            below[i] += lt;
+            flagged |= !(lt | (v > fhi[i]));   // inside the bracket — or NaN, which the rare path sorts out
         }
-        return inside;
+        return flagged;
     };
 
     const float* p = xs + begin;
@@ -764,7 +768,7 @@ __global__ void __launch_bounds__(kThreads) qsel_partition_kernel(const float* _
             float4 v[4];
 #pragma unroll
             for (int k = 0; k < 4; ++k)
-                if (base + k * kThreads < n4) v[k] = ld_stream_f4(p4 + base + k * kThreads);
+                if (base + k * kThreads < n4) v[k] = __ldg(p4 + base + k * kThreads);   // allocating: the rare path re-reads from L1
             unsigned flags = 0;
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
@@ -778,9 +782,9 @@ __global__ void __launch_bounds__(kThreads) qsel_partition_kernel(const float* _
             while (flags) {  // (measured: faster than 16 statically indexed copies of the rare path)
                 const int b = __ffs(flags) - 1;
                 flags &= flags - 1;
-                const float4 q4 = v[b >> 2];
-                const int c = b & 3;
-                take_inside(c == 0 ? q4.x : (c == 1 ? q4.y : (c == 2 ? q4.z : q4.w)));
+                // the element is read again (an L1 hit) rather than picked out of v[]: indexing the register array
+                // dynamically would put all of v[] in local memory, with four 16-byte stores on the common path
+                take_inside(__ldg(p + ((base + (int64_t)(b >> 2) * kThreads) << 2) + (b & 3)));
             }
         }
         for (int64_t i = (n4 << 2) + threadIdx.x; i < n; i += kThreads)
@@ -1329,7 +1333,9 @@ static int quantile_sampled(const float* x, int64_t n_seg, int64_t seg_len, cons
     for (int64_t s0 = 0; s0 < n_seg; s0 += per_pass) {
         const int64_t ns = (n_seg - s0 < per_pass) ? (n_seg - s0) : per_pass;
         const int64_t nt = ns * n_q;
-        const SegSplit sp = split_segment(ns, seg_len);
+        // the partition kernel keeps 5 blocks of 48 registers per SM resident and a block runs for most of the kernel:
+        // exactly one wave (measured: 8 blocks per SM = 1.6 waves 80 us for the stage, 5 = 74.6, 4 = 76.7, 10 = 76.8)
+        const SegSplit sp = split_segment(ns, seg_len, (int64_t)BE_SM_COUNT * 5);
         const SWorkspace w = carve_sample_ws(ws, ns, n_q, seg_len);
         const float* xs = x + s0 * seg_len;
         double* qs = quant + s0 * n_q;
