@@ -573,7 +573,8 @@ struct RowsConst {
     int64_t dky, dkz;        // element steps in the tile buffer: next tile along y / z (same in-tile position + stride)
     int64_t dout;            // element step in the output: next row of this thread
     double mid, half;        // division-free band test: |acc - wacc*mid| > wacc*half  <=>  acc/wacc outside [lo2, hi2]
-    int log2_bx, rows_per_band, units_per_row;
+    int log2_bx, units_per_row;
+    unsigned n_bands, n_items;     // work items = (plane, band); band b covers rows [b*Y/n_bands, (b+1)*Y/n_bands)
     int slot_bytes, stage_bytes;   // shared memory: one (row, ky slot) = nseg tile rows; one stage = r_step rows x 2 slots
     unsigned n_planes;
 };
@@ -637,9 +638,6 @@ __global__ void __launch_bounds__(kRowsThreads, 3) stitch_blend_rows_kernel(cons
     const int lda = (ty * 2) * slot_bytes + (kxa - seg_first) * seg_bytes + ixa * 4;
     const int ab = (kxb - kxa) * seg_bytes + (ixb - ixa) * 4;   // from the read of the first x tile to the second
 
-    const int band_begin = blockIdx.y * k.rows_per_band, y_end = min((int)d.Y, band_begin + k.rows_per_band);
-    const int n_groups = (y_end - band_begin + r_step - 1) / r_step;
-
     // producer lane i of warp 0 owns segment i: the part of tile row (kx = seg_first + i) inside [X0, X1)
     const bool producer = tid >= kThreads;
     const int lane = tid & 31;
@@ -668,7 +666,13 @@ __global__ void __launch_bounds__(kRowsThreads, 3) stitch_blend_rows_kernel(cons
     __syncthreads();
     unsigned use = 0;   // steps this warp has been through (stage = use % kStages, parity = (use / kStages) & 1)
 
-    for (unsigned plane = blockIdx.z; plane < k.n_planes; plane += gridDim.z) {
+    // persistent blocks: the grid is one wave and a block walks work items (plane, band of rows) with a grid stride, so
+    // the window table, the barriers and the x cover are set up once and the ring of stages never drains between bands
+    for (unsigned item = blockIdx.y; item < k.n_items; item += gridDim.y) {
+        const unsigned plane = item / k.n_bands, band = item - plane * k.n_bands;
+        const int band_begin = (int)(((int64_t)band * d.Y) / k.n_bands);
+        const int y_end = (int)(((int64_t)(band + 1) * d.Y) / k.n_bands);
+        const int n_groups = (y_end - band_begin + r_step - 1) / r_step;
         int z = 0, c = 0;
         int64_t n = 0;
         if (k.n_planes > 1) {
@@ -807,12 +811,10 @@ __global__ void __launch_bounds__(kRowsThreads, 3) stitch_blend_rows_kernel(cons
                 if (mrow) mrow += k.dout;
                 if (orow) orow += k.dout;
             }
-            if (y >= rc.change) {
-                live = x_live && y < y_end;
-                if (y < y_end) {
-                    rc.set(y, d, s);
-                    iy = y - rc.ky_lo * s.Sy;
-                }
+            live = x_live && y < y_end;   // a band need not be a whole number of row groups
+            if (y >= rc.change && y < y_end) {
+                rc.set(y, d, s);
+                iy = y - rc.ky_lo * s.Sy;
             }
             if (y < y_end) {
                 wy0 = wy[iy];
@@ -981,15 +983,26 @@ extern "C" int be_stitch_blend_f32(const float* tiles, float* out, uint8_t* mask
     const size_t smem = (size_t)kStages * r_step * 2 * nseg * Bx * 4 + (size_t)Bx * 8;
     if (Bx <= 2 * Sx && By <= 2 * Sy && (Sx & 3) == 0 && (Bx & 3) == 0 && (X & 3) == 0 && aligned16 && nseg <= 32 &&
         smem <= 72 * 1024) {
-        // row bands: ~6 blocks per SM in total, at least 4 steps per block where the image allows
-        const int64_t want = (int64_t)BE_SM_COUNT * 6;   // measured: 3 (one wave) .. 16 per SM within 5 %, 6 best
-        int64_t bands = want / ((int64_t)xblocks * grid.z) + 1;
-        const int64_t max_bands = (Y + 4 * r_step - 1) / (4 * r_step);
-        if (bands > max_bands) bands = max_bands;
-        if (bands > 65535) bands = 65535;
-        int rows_per_band = (int)((Y + bands - 1) / bands);
-        rows_per_band = (rows_per_band + r_step - 1) / r_step * r_step;
-        const dim3 g2(xblocks, (unsigned)((Y + rows_per_band - 1) / rows_per_band), grid.z);
+        // one wave of persistent blocks (3 per SM) walks (plane, band) items; bands of about 8 steps, their number
+        // rounded so that every block gets the same count when there are only a few items per block
+        const int64_t planes = N * C * Z;
+        BE_REQUIRE(planes < ((int64_t)1 << 31), BE_ERR_TOO_LARGE, "be_stitch_blend_f32: too many planes");
+        int64_t G = (int64_t)BE_SM_COUNT * 3 / xblocks;
+        if (G < 1) G = 1;
+        int64_t n_bands = (Y + 8 * r_step - 1) / (8 * r_step);
+        const int64_t per_block = n_bands * planes / G;
+        if (per_block < 16) {
+            const int64_t kk = per_block < 1 ? 1 : per_block + 1;
+            n_bands = (kk * G + planes - 1) / planes;
+        }
+        const int64_t max_bands = (Y + r_step - 1) / r_step;
+        if (n_bands > max_bands) n_bands = max_bands;
+        if (n_bands < 1) n_bands = 1;
+        const int64_t n_items = n_bands * planes;
+        BE_REQUIRE(n_items < ((int64_t)1 << 31), BE_ERR_TOO_LARGE, "be_stitch_blend_f32: too many work items");
+        if (G > n_items) G = n_items;
+        if (G > 65535) G = 65535;
+        const dim3 g2(xblocks, (unsigned)G, 1);
         RowsConst k;
         k.dky = (int64_t)Tx * st.tile_stride - (int64_t)Sy * Bx;
         k.dkz = (int64_t)Ty * Tx * st.tile_stride - (int64_t)Sz * By * Bx;
@@ -997,8 +1010,9 @@ extern "C" int be_stitch_blend_f32(const float* tiles, float* out, uint8_t* mask
         k.mid = 0.5 * (e.hi2 + e.lo2);
         k.half = 0.5 * (e.hi2 - e.lo2) * (1.0 + 0x1p-30);
         k.log2_bx = log2_bx;
-        k.rows_per_band = rows_per_band;
         k.units_per_row = upr;
+        k.n_bands = (unsigned)n_bands;
+        k.n_items = (unsigned)n_items;
         k.slot_bytes = nseg * Bx * 4;
         k.stage_bytes = r_step * 2 * k.slot_bytes;
         k.n_planes = (unsigned)(N * C * Z);
