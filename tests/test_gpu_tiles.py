@@ -196,3 +196,44 @@ def test_blend_band_test_on_values_at_the_threshold(dev):
         _, only = K().stitch_blend(torch.from_numpy(logits).to(dev), (1, 1, H, W), dev_axes(axes, dev), wins, epilogue=1,
                                    want_out=False, want_mask=True, thr=thr)
         assert np.array_equal(only.cpu().numpy()[0, 0], O.binarize(O.sigmoid(want), thr)), thr
+
+
+def test_kernels_write_nothing_outside_their_outputs(dev, rng):
+    """Guard bands around the output buffers (compute-sanitizer is not available on the GPU pool): shapes whose rows are
+    not a whole number of row groups / stages, several planes, both blend kernels and both gather kernels."""
+    from bioengine_worker_b200 import _lib
+    kern = K()
+    guard = 4096
+    stream = kern._stream()
+    for spatial, B, ov, C in (((52, 96), 32, 8, 2), ((40, 52, 96), 32, 8, 2), ((50, 90), 32, 8, 1), ((77, 1024 + 64), 256, 64, 1)):
+        nd = len(spatial)
+        axes = [G.fibsem_axis(s, B, ov) for s in spatial]
+        if nd == 2:
+            axes = [G.identity_axis(1)] + axes
+        az, ay, ax = dev_axes(axes, dev)
+        T = az.ax.T * ay.ax.T * ax.ax.T
+        Z, Y, X = az.ax.S, ay.ax.S, ax.ax.S
+        n_px = C * Z * Y * X
+        img = torch.from_numpy(rng.standard_normal((1, C, Z, Y, X)).astype(np.float32)).to(dev)
+        # gather into a guarded tile buffer
+        n_t = T * C * az.ax.B * ay.ax.B * ax.ax.B
+        tbuf = torch.full((n_t + 2 * guard,), 7.5, dtype=torch.float32, device=dev)
+        _lib.call("be_tile_gather_f32", img.data_ptr(), tbuf[guard:].data_ptr(), 1, C, Z, Y, X, az.ax.T, ay.ax.T, ax.ax.T,
+                  az.ax.B, ay.ax.B, ax.ax.B, az.src.data_ptr(), ay.src.data_ptr(), ax.src.data_ptr(), 0, 0, 0, 0.0, 0.0, stream)
+        assert bool((tbuf[:guard] == 7.5).all()) and bool((tbuf[guard + n_t:] == 7.5).all()), (spatial, "gather")
+        assert not bool((tbuf[guard:guard + n_t] == 7.5).any())
+        # blend into guarded outputs, every epilogue combination
+        w1 = torch.from_numpy(G.gauss_window_1d(B)).to(dev)
+        one = torch.ones(1, dtype=torch.float64, device=dev)
+        wz = w1 if nd == 3 else one
+        for want_out, epi in ((True, 0), (True, 1), (False, 1)):
+            obuf = torch.full((n_px + 2 * guard,), -3.25, dtype=torch.float32, device=dev)
+            mbuf = torch.full((n_px + 2 * guard,), 9, dtype=torch.uint8, device=dev)
+            _lib.call("be_stitch_blend_f32", tbuf[guard:].data_ptr(), obuf[guard:].data_ptr() if want_out else 0,
+                      mbuf[guard:].data_ptr(), 1, C, Z, Y, X, az.ax.T, ay.ax.T, ax.ax.T, az.ax.B, ay.ax.B, ax.ax.B,
+                      az.ax.stride, ay.ax.stride, ax.ax.stride, wz.data_ptr(), w1.data_ptr(), w1.data_ptr(), epi, 0.5, stream)
+            assert bool((mbuf[:guard] == 9).all()) and bool((mbuf[guard + n_px:] == 9).all()), (spatial, epi, "mask")
+            assert bool((mbuf[guard:guard + n_px] <= 1).all())
+            assert bool((obuf[:guard] == -3.25).all()) and bool((obuf[guard + n_px:] == -3.25).all()), (spatial, epi, "out")
+            if want_out:
+                assert not bool((obuf[guard:guard + n_px] == -3.25).any())
