@@ -522,11 +522,22 @@ __global__ void __launch_bounds__(kThreads) ccl_number_kernel(int32_t* __restric
     if (w < words_per_image) {
         u64 bits = rootbits[(int64_t)img * words_per_image + w];
         base = (w / wpr) * X + (w % wpr) * kTX;
+        // still a root after the border unions?  Four candidates per round, their loads issued together: a block
+        // publishes its count only when its slowest thread is through, and one dependent load per root bit made that
+        // several round trips for the words with many tile roots
         while (bits) {
-            const int b = __ffsll((long long)bits) - 1;
-            bits &= bits - 1;
-            const int32_t p = (int32_t)(base + b);
-            if (Lv[p] == p) keep |= 1ull << b;  // still a root after the border unions
+            int b[4];
+            int32_t pv[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                b[i] = bits ? __ffsll((long long)bits) - 1 : -1;
+                bits &= bits - 1;   // (0 & anything stays 0)
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) pv[i] = (b[i] >= 0) ? __ldcg(Li + base + b[i]) : -1;
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                if (b[i] >= 0 && pv[i] == (int32_t)(base + b[i])) keep |= 1ull << b[i];
         }
     }
     const int c = __popcll(keep);
@@ -543,27 +554,40 @@ __global__ void __launch_bounds__(kThreads) ccl_number_kernel(int32_t* __restric
         if (i < (int)(threadIdx.x >> 5)) before += s_warp[i];
         total += s_warp[i];
     }
+    // Exclusive prefix over the blocks before this one: decoupled look-back by warp 0, 128 predecessors per step (four
+    // per lane, nearest first), polled with plain loads — thousands of pollers spinning with atomics on the same few KB
+    // is slow, and with all blocks resident at once nobody finds a published prefix early, so the step count matters.
     unsigned long long* state = block_state + (int64_t)img * blocks_per_image;
+    volatile unsigned long long* vstate = state;
     if (threadIdx.x < 32) {
-        // warp-wide look-back: 32 predecessors per step, nearest first (lane 0 = block blk-1)
         const int lane = threadIdx.x;
         if (lane == 0 && blk > 0) atomicExch(&state[blk], kFlagAggregate | (unsigned long long)total);
         long long excl = 0;
-        for (int end = blk - 1; end >= 0; end -= 32) {
-            const int j = end - lane;
-            unsigned long long sj = kFlagPrefix;  // lanes before block 0 contribute a zero prefix
-            if (j >= 0) {
-                do {
-                    sj = atomicAdd(&state[j], 0ull);
-                } while ((sj & kFlagMask) == 0);
+        for (int end = blk; end > 0; end -= 128) {
+            long long v = 0;
+            int best = -1;   // nearest entry of this lane that carries an inclusive prefix
+            unsigned long long sj[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int j = end - 1 - lane - 32 * i;
+                sj[i] = kFlagAggregate;   // entries before block 0 contribute nothing
+                if (j >= 0) {
+                    do {
+                        sj[i] = vstate[j];
+                    } while ((sj[i] & kFlagMask) == 0);
+                    if ((sj[i] & kFlagMask) == kFlagPrefix) best = max(best, j);
+                }
             }
-            const unsigned has_prefix = __ballot_sync(0xffffffffu, (sj & kFlagMask) == kFlagPrefix);
-            const int stop = __ffs(has_prefix) - 1;  // nearest predecessor with an inclusive prefix (always >= 0 at block 0)
-            long long v = (stop < 0 || lane <= stop) ? (long long)(sj & ~kFlagMask) : 0;
+            const int nearest = __reduce_max_sync(0xffffffffu, best);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int j = end - 1 - lane - 32 * i;
+                if (j >= 0 && j >= nearest) v += (long long)(sj[i] & ~kFlagMask);
+            }
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
             excl += v;
-            if (stop >= 0) break;
+            if (nearest >= 0) break;
         }
         if (lane == 0) {
             atomicExch(&state[blk], kFlagPrefix | (unsigned long long)(excl + total));
