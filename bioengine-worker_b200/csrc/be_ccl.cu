@@ -372,37 +372,26 @@ __device__ __forceinline__ void unite_batch(int32_t* Li, EdgeBatch& q) {
             q.a[k] = __ldcg(Li + q.a[k]);
             q.b[k] = __ldcg(Li + q.b[k]);
         }
-    // level 2: is it still a root?
-    int32_t ga[kEdgePairs], gb[kEdgePairs];
-#pragma unroll
-    for (int k = 0; k < kEdgePairs; ++k)
-        if ((q.valid >> k) & 1u) {
-            ga[k] = __ldcg(Li + q.a[k]);
-            gb[k] = __ldcg(Li + q.b[k]);
-        }
-    // both roots in hand: one atomicMin; anything else goes through the general walk
+    // both are roots as far as this lane knows: one atomicMin per pair, all issued before any result is looked at.  If
+    // the larger one had been linked elsewhere in the meantime the atomic says so (old != hi) and the pair goes through
+    // the general walk with that link preserved — so there is no need to re-read the roots first
     unsigned fast = 0;
     int32_t old[kEdgePairs];
 #pragma unroll
     for (int k = 0; k < kEdgePairs; ++k)
         if ((q.valid >> k) & 1u) {
-            if (ga[k] == q.a[k] && gb[k] == q.b[k]) {
-                if (q.a[k] != q.b[k]) {
-                    const int32_t hi = max(q.a[k], q.b[k]), lo = min(q.a[k], q.b[k]);
-                    old[k] = atomicMin(&Li[hi], lo);
-                    q.a[k] = hi;
-                    q.b[k] = lo;
-                    fast |= 1u << k;
-                }
-                q.valid &= ~(1u << k);
+            if (q.a[k] != q.b[k]) {
+                const int32_t hi = max(q.a[k], q.b[k]), lo = min(q.a[k], q.b[k]);
+                old[k] = atomicMin(&Li[hi], lo);
+                q.a[k] = hi;
+                q.b[k] = lo;
+                fast |= 1u << k;
             }
         }
 #pragma unroll
     for (int k = 0; k < kEdgePairs; ++k) {
         if ((fast >> k) & 1u) {
             if (old[k] != q.a[k]) gl_unite(Li, old[k], q.b[k]);   // hi was no longer a root: keep its old link alive
-        } else if ((q.valid >> k) & 1u) {
-            gl_unite(Li, q.a[k], q.b[k]);
         }
     }
 }
