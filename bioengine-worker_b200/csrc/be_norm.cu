@@ -1009,6 +1009,16 @@ __device__ __forceinline__ void slice_foreach(const float* xs, int64_t n, F f) {
     const float4* p4 = reinterpret_cast<const float4*>(xs + head);
     const int64_t n4 = (n - head) >> 2;
     int64_t i = threadIdx.x;
+    for (; i + 3 * kSelThreads < n4; i += 4 * kSelThreads) {   // four loads in flight: a slice is only a few rounds long
+        const float4 a = ld_stream_f4(p4 + i);
+        const float4 b = ld_stream_f4(p4 + i + kSelThreads);
+        const float4 c = ld_stream_f4(p4 + i + 2 * kSelThreads);
+        const float4 e = ld_stream_f4(p4 + i + 3 * kSelThreads);
+        f(a.x); f(a.y); f(a.z); f(a.w);
+        f(b.x); f(b.y); f(b.z); f(b.w);
+        f(c.x); f(c.y); f(c.z); f(c.w);
+        f(e.x); f(e.y); f(e.z); f(e.w);
+    }
     for (; i + kSelThreads < n4; i += 2 * kSelThreads) {
         const float4 a = ld_stream_f4(p4 + i);
         const float4 b = ld_stream_f4(p4 + i + kSelThreads);
