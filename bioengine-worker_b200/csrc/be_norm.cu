@@ -757,41 +757,71 @@ __global__ void __launch_bounds__(kThreads) qsel_partition_kernel(const float* _
         return flagged;
     };
 
-    const float* p = xs + begin;
-    const int64_t n = end - begin;
-    if ((((uintptr_t)p) & 15) == 0) {
-        // 16 elements per thread and iteration: all of them take the cheap path first, and the 2-3 % that fall inside a
-        // bracket are handled afterwards from a 16-bit flag word, so the divergent code runs once per 16 elements
-        const float4* p4 = reinterpret_cast<const float4*>(p);
-        const int64_t n4 = n >> 2;
-        for (int64_t base = threadIdx.x; base < n4; base += 4 * kThreads) {
-            float4 v[4];
+    // The chunk is streamed in rounds of 32 K elements; after each round the staged candidates move to the global lists
+    // (one reservation per block and bracket).  A round brings ~1 % of 32 K elements per bracket, well inside the 1024
+    // staging slots — without rounds a long chunk (a 512^3 volume gives every block 180 K elements) overflows the
+    // staging area and every further candidate costs a global atomic on one address (partition 1.24 ms -> see profiles).
+    constexpr int64_t kRound = (int64_t)kThreads * 16 * 8;
+    unsigned kx[NQ], nk[NQ];   // key range of the candidates this thread moved
 #pragma unroll
-            for (int k = 0; k < 4; ++k)
-                if (base + k * kThreads < n4) v[k] = __ldg(p4 + base + k * kThreads);   // allocating: the rare path re-reads from L1
-            unsigned flags = 0;
+    for (int i = 0; i < NQ; ++i) kx[i] = nk[i] = 0;
+    for (int64_t r0 = begin; r0 < end; r0 += kRound) {
+        const float* p = xs + r0;
+        const int64_t n = min(end, r0 + kRound) - r0;
+        if ((((uintptr_t)p) & 15) == 0) {
+            // 16 elements per thread and iteration: all of them take the cheap path first, and the 2-3 % that fall inside a
+            // bracket are handled afterwards from a 16-bit flag word, so the divergent code runs once per 16 elements
+            const float4* p4 = reinterpret_cast<const float4*>(p);
+            const int64_t n4 = n >> 2;
+            for (int64_t base = threadIdx.x; base < n4; base += 4 * kThreads) {
+                float4 v[4];
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                if (base + k * kThreads < n4) {
-                    flags |= (unsigned)classify(v[k].x) << (4 * k + 0);
-                    flags |= (unsigned)classify(v[k].y) << (4 * k + 1);
-                    flags |= (unsigned)classify(v[k].z) << (4 * k + 2);
-                    flags |= (unsigned)classify(v[k].w) << (4 * k + 3);
+                for (int k = 0; k < 4; ++k)
+                    if (base + k * kThreads < n4) v[k] = __ldg(p4 + base + k * kThreads);   // allocating: the rare path re-reads from L1
+                unsigned flags = 0;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    if (base + k * kThreads < n4) {
+                        flags |= (unsigned)classify(v[k].x) << (4 * k + 0);
+                        flags |= (unsigned)classify(v[k].y) << (4 * k + 1);
+                        flags |= (unsigned)classify(v[k].z) << (4 * k + 2);
+                        flags |= (unsigned)classify(v[k].w) << (4 * k + 3);
+                    }
+                }
+                while (flags) {  // (measured: faster than 16 statically indexed copies of the rare path)
+                    const int b = __ffs(flags) - 1;
+                    flags &= flags - 1;
+                    // the element is read again (an L1 hit) rather than picked out of v[]: indexing the register array
+                    // dynamically would put all of v[] in local memory, with four 16-byte stores on the common path
+                    take_inside(__ldg(p + ((base + (int64_t)(b >> 2) * kThreads) << 2) + (b & 3)));
                 }
             }
-            while (flags) {  // (measured: faster than 16 statically indexed copies of the rare path)
-                const int b = __ffs(flags) - 1;
-                flags &= flags - 1;
-                // the element is read again (an L1 hit) rather than picked out of v[]: indexing the register array
-                // dynamically would put all of v[] in local memory, with four 16-byte stores on the common path
-                take_inside(__ldg(p + ((base + (int64_t)(b >> 2) * kThreads) << 2) + (b & 3)));
+            for (int64_t i = (n4 << 2) + threadIdx.x; i < n; i += kThreads)
+                if (classify(p[i])) take_inside(p[i]);
+        } else {
+            for (int64_t i = threadIdx.x; i < n; i += kThreads)
+                if (classify(p[i])) take_inside(p[i]);
+        }
+        __syncthreads();   // this round's staging is complete
+        if (threadIdx.x < NQ) {
+            const unsigned n_st = min(s_n[threadIdx.x], (unsigned)kStage);
+            s_base[threadIdx.x] = n_st ? atomicAdd(&tasks[threadIdx.x].n_mid, n_st) : 0u;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < NQ; ++i) {
+            const unsigned n_st = min(s_n[i], (unsigned)kStage), base = s_base[i];
+            float* dst = w.cand + (seg * NQ + i) * w.cap;
+            for (unsigned k = threadIdx.x; k < n_st; k += kThreads) {
+                const float v = s_buf[i][k];
+                if (base + k < w.cap) dst[base + k] = v;
+                kx[i] = max(kx[i], f32_to_key(v));
+                nk[i] = max(nk[i], ~f32_to_key(v));
             }
         }
-        for (int64_t i = (n4 << 2) + threadIdx.x; i < n; i += kThreads)
-            if (classify(p[i])) take_inside(p[i]);
-    } else {
-        for (int64_t i = threadIdx.x; i < n; i += kThreads)
-            if (classify(p[i])) take_inside(p[i]);
+        __syncthreads();   // staging read out: free for the next round
+        if (threadIdx.x < NQ) s_n[threadIdx.x] = 0;
+        __syncthreads();
     }
 #pragma unroll
     for (int i = 0; i < NQ; ++i) {
@@ -809,32 +839,19 @@ __global__ void __launch_bounds__(kThreads) qsel_partition_kernel(const float* _
     __syncthreads();
     if (threadIdx.x < NQ) {
         const int i = threadIdx.x;
-        const unsigned n = min(s_n[i], (unsigned)kStage);
-        s_base[i] = n ? atomicAdd(&tasks[i].n_mid, n) : 0u;
         if (s_cnt[i][0]) atomicAdd(&tasks[i].below, s_cnt[i][0]);
         if (s_cnt[i][1]) atomicAdd(&tasks[i].eq_lo, s_cnt[i][1]);
         if (s_cnt[i][2]) atomicAdd(&tasks[i].eq_hi, s_cnt[i][2]);
     }
     if (threadIdx.x == 0 && s_nan) atomicAdd(&w.nan_count[seg], s_nan);
-    __syncthreads();
-    // staged candidates go to the global list; their key range (what the selection cuts its digits from) rides along
+    // the key range of the candidates (what the selection cuts its digits from)
 #pragma unroll
     for (int i = 0; i < NQ; ++i) {
-        const unsigned n = min(s_n[i], (unsigned)kStage), base = s_base[i];
-        float* dst = w.cand + (seg * NQ + i) * w.cap;
-        unsigned kx = 0, nk = 0;
-        for (unsigned k = threadIdx.x; k < n; k += kThreads) {
-            const float v = s_buf[i][k];
-            if (base + k < w.cap) dst[base + k] = v;
-            kx = max(kx, f32_to_key(v));
-            nk = max(nk, ~f32_to_key(v));
-        }
-        if (__any_sync(0xffffffffu, kx | nk)) {
-            kx = __reduce_max_sync(0xffffffffu, kx);
-            nk = __reduce_max_sync(0xffffffffu, nk);
+        if (__any_sync(0xffffffffu, kx[i] | nk[i])) {
+            const unsigned a = __reduce_max_sync(0xffffffffu, kx[i]), b = __reduce_max_sync(0xffffffffu, nk[i]);
             if ((threadIdx.x & 31) == 0) {
-                atomicMax(&s_kmax[i], kx);
-                atomicMax(&s_nkmin[i], nk);
+                atomicMax(&s_kmax[i], a);
+                atomicMax(&s_nkmin[i], b);
             }
         }
     }
