@@ -132,15 +132,18 @@ static __device__ __forceinline__ void bulk_g2s(unsigned dst, const void* src, u
                  "l"(src), "r"(bytes), "r"(bar)
                  : "memory");
 }
+// Waits with a suspend-time hint: the warp sleeps in hardware until the phase completes (or the hint runs out), so a copy
+// warp that is a whole ring ahead does not burn issue slots polling — with plain try_wait the polling loop was a fifth
+// of all instructions the blend kernel issued.
 static __device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
     unsigned ok = 0;
     for (int spin = 0; !ok; ++spin) {
         asm volatile(
-            "{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+            "{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3; selp.u32 %0, 1, 0, p; }"
             : "=r"(ok)
-            : "r"(bar), "r"(parity)
+            : "r"(bar), "r"(parity), "r"(100000u)
             : "memory");
-        if (spin > (1 << 22)) __trap();  // a byte count that never arrives is a bug, not something to wait out
+        if (spin > (1 << 18)) __trap();  // a byte count that never arrives is a bug, not something to wait out
     }
 }
 
