@@ -356,7 +356,7 @@ def run_b200(args):
             best = dt if best is None else min(best, dt)
         cpu_value = px / best / 1e6
 
-        launches_per_step = 5 + 1 + 1 + 4  # quantile (sample/partition/select x3), gather, blend, ccl (tile/edge/number/resolve)
+        launches_per_step = 3 + 1 + 1 + 4  # quantile (sample/partition/cluster select), gather, blend, ccl (tile/edge/number/resolve)
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
