@@ -255,7 +255,7 @@ __global__ void __launch_bounds__(kThreads) ccl_tile_kernel(const uint8_t* __res
         const int r0 = warp * 8 + sub;
         const int64_t zw = z0 + (r0 >> g.ty_log2), yw = y0 + (r0 & ty_mask);
         int32_t* row = Li + (zw * g.Y + yw) * g.X + x0 + x4;
-#pragma unroll 1
+#pragma unroll
         for (int it = 0; it < 4; ++it, row += 2 * g.X) {
             const int r = r0 + it * 2;
             const bool row_ok = zw < g.Z && yw + it * 2 < g.Y;
