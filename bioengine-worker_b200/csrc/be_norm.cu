@@ -7,6 +7,7 @@
 //   be_elementwise_f32 clip / scale_linear / sigmoid
 //   be_binarize_f32_u8 x > thr
 #include <cooperative_groups.h>
+#include <stdlib.h>
 
 #include "be_common.cuh"
 
@@ -1327,7 +1328,10 @@ static int select_cluster_size() {
     if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 0;
     if (cached[dev]) return cached[dev] > 0 ? cached[dev] : 0;
     int best = -1;
-    for (int size = kClusterMax; size >= 8 && best < 0; size >>= 1) {
+    // BE_B200_CLUSTER_MAX=8 (test hook): take the portable cluster size even where 16 is available
+    const char* cap = getenv("BE_B200_CLUSTER_MAX");
+    const int first = (cap && atoi(cap) == 8) ? 8 : kClusterMax;
+    for (int size = first; size >= 8 && best < 0; size >>= 1) {
         if (size > 8 &&
             cudaFuncSetAttribute(qsel_cluster_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) {
             cudaGetLastError();

@@ -248,3 +248,27 @@ def test_sampled_quantile_ranks_on_and_next_to_pivot_ties(dev, rng):
             q = (k / (n - 1), min(1.0, (k + 0.5) / (n - 1)))
             got, _ = _quant(x, q, 1, dev)
             assert np.array_equal(got[0], np.nanquantile(x, np.asarray(q, np.float64), method="linear")), (frac, k)
+
+
+def test_selection_with_the_portable_cluster_size(dev):
+    """The selection kernel takes clusters of 16 CTAs where the device grants them; BE_B200_CLUSTER_MAX=8 (read once per
+    process, hence the subprocess) forces the portable size a smaller part would fall back to."""
+    import os, subprocess, sys, textwrap
+
+    code = textwrap.dedent('''
+        import numpy as np, torch
+        from bioengine_worker_b200 import kernels as K
+        rng = np.random.default_rng(7)
+        dev = torch.device("cuda:0")
+        for x in ((rng.standard_normal((2, (1 << 19) + 5)) * 50).astype(np.float32),
+                  np.round(rng.standard_normal((1, 1 << 20)) * 20).astype(np.float32)):
+            q = np.array([0.01, 0.998])
+            got, _ = K.quantile(torch.from_numpy(x).to(dev), x.shape[0], torch.from_numpy(q).to(dev), 1e-6)
+            want = np.nanquantile(x, q, axis=1, method="linear").T
+            assert np.array_equal(got.cpu().numpy(), want)
+        print("ok")
+    ''')
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, BE_B200_CLUSTER_MAX="8", PYTHONPATH=root + os.pathsep + os.environ.get("PYTHONPATH", ""))
+    out = subprocess.run([sys.executable, "-c", code], env=env, cwd=root, capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0 and "ok" in out.stdout, out.stderr[-2000:]
