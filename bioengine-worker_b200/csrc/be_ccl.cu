@@ -3,19 +3,23 @@
 // Pipeline (all int/bit work, HBM-bound):
 //   1. ccl_tile_kernel      one CTA per 64x64 (2-D) / 64x8x8 (3-D) tile.  Rows become 64-bit masks (16-byte loads +
 //                           byte->bit multiply trick, or warp ballots at ragged edges).  The union-find nodes are the
-//                           RUNS of a row (<= 32 per row, 2048 per tile, uint16 parents in shared memory): x-links cost
+//                           RUNS of a row (<= 32 per row, 2048 per tile, parents in shared memory): x-links cost
 //                           nothing, and rows are linked with bit arithmetic that leaves exactly one lane per touching
-//                           run pair to issue the union (atomicMin, path halving).  After a per-run flatten every pixel
-//                           gets parent = global index of its tile-local root pixel (minimum raster index), -1 for
-//                           background; tile roots are also flagged in a 1-bit-per-pixel bitmap and the tile's four
-//                           edge masks are kept for step 2.
+//                           run pair to issue the union (atomicMin, path halving).  After a per-run flatten every run
+//                           takes the label of its root (global index of the component's first pixel in the tile) and
+//                           every foreground pixel gets that as its parent, branch-free, 16 bytes per lane; units
+//                           without a foreground pixel are not written at all.  Tile roots are flagged in a
+//                           1-bit-per-pixel bitmap, the mask itself is kept bit-packed, and the tile's four edge
+//                           masks are kept for step 2.
 //   2. ccl_edge_kernel      (2-D) one warp per tile links its top and left edge to the neighbouring tiles from the edge
-//                           masks alone, again one union per touching run pair;  ccl_face3d_kernel (3-D) does the same
-//                           per 64-voxel row word of the bit-packed mask.  Unions are atomicMin on the global parent array with path halving.
+//                           masks alone, one union per touching run pair, a lane's (up to 12) unions issued as a batch;
+//                           ccl_face3d_kernel (3-D) does the same per 64-voxel row word of the bit-packed mask, one
+//                           union after the other.  Unions are atomicMin on the global parent array with path halving.
 //   3. ccl_number_kernel    surviving roots are numbered in raster order from the root bitmap (2 MB instead of a
-//                           second pass over all parents) with a single-pass decoupled look-back scan; a root's entry
-//                           becomes -(id) - 1.
-//   4. ccl_resolve_kernel   every pixel walks to its root (<= 2-3 hops) and writes id; background decodes to 0.
+//                           second pass over all parents) with a single-pass decoupled look-back scan (128 predecessors
+//                           per step); a root's entry becomes -(id) - 1.
+//   4. ccl_resolve_kernel   driven by the packed mask: a foreground pixel walks to its root (<= 2-3 hops) and writes
+//                           the id, background is written as 0 without touching the parent array.
 #include "be_common.cuh"
 
 namespace {

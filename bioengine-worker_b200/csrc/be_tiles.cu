@@ -1,9 +1,14 @@
-// Halo-tile gather and the two stitchers.  All three are pure data movement (HBM-bound): one thread makes
-// four consecutive x outputs and stores them as one 16-byte (fp32) / 4-byte (uint8) transaction.
+// Halo-tile gather and the two stitchers.  All three move data (HBM-bound by design): one thread makes four consecutive
+// x outputs and stores them as one 16-byte (fp32) / 4-byte (uint8) transaction.
 //
 //   be_tile_gather_f32   image (+ fused normalise) -> (N*T, C, Bz, By, Bx) tiles, table-driven padding
 //   be_stitch_crop_f32   bioimageio inner-region reassembly, table-driven, optional sigmoid / mask epilogue
 //   be_stitch_blend_f32  fibsem Gaussian-weighted overlap blend as a gather, fp64 accumulation
+//
+// The gather and the blend each have two kernels: a general one (any geometry, per-thread loads) and, for geometries
+// whose tile rows are aligned 16-byte runs, one wave of persistent blocks in which a copy warp streams the rows into a
+// ring of shared-memory stages with TMA bulk copies (cp.async.bulk + mbarrier) while eight arithmetic warps work from
+// shared memory.
 #include "be_common.cuh"
 
 namespace {
