@@ -39,13 +39,14 @@ class EntryDeployment:
 
     @staticmethod
     def _load_image_from_source(source: str) -> np.ndarray:
-        """ref: entry_deployment.py:1196-1263 restricted to local files (`.npy`; `file://` prefix accepted)."""
-        path = source[7:] if source.startswith("file://") else source
+        """ref: entry_deployment.py:1196-1263 restricted to local files (`file://` prefix accepted): `.npy`, `.png`,
+        `.tif(f)`, `.jp(e)g`, decoded as `imageio.v3.imread` would; same exceptions (ValueError for an unsupported
+        extension or unreadable content, FileNotFoundError for a missing file)."""
+        from .io import load_image
+
         if source.startswith(("http://", "https://")):
-            raise ValueError("remote inputs are resolved by the reference EntryDeployment; pass an array or a local .npy path")
-        if not path.endswith(".npy") or not os.path.exists(path):
-            raise ValueError(f"cannot load input from {source!r} (expected an existing .npy file)")
-        return np.load(path)
+            raise ValueError("remote inputs are resolved by the reference EntryDeployment; pass an array or a local file path")
+        return load_image(source[7:] if source.startswith("file://") else source)
 
     async def get_model_rdf(self, model_id: str) -> dict:
         import yaml
