@@ -110,6 +110,20 @@ def scale_linear(x, gain, offset, out=None):
     return elementwise(x, _lib.BE_OP_SCALE_LINEAR, gain, offset, out)
 
 
+def scale_mean_variance(x: torch.Tensor, ref_norm: torch.Tensor, n_seg: int, eps: float = 1e-6,
+                        out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """bioimageio `scale_mean_variance`: (x - mean) / (std + eps) * (ref_std + eps) + ref_mean per segment.
+    ref_norm = `meanvar(reference, n_seg, eps)[1]` ({ref_mean, ref_std + eps}, fp64 on the device).  Composed from the
+    existing entry points: statistics, normalise, then one scale_linear per segment (N*C of them at most)."""
+    own = meanvar(x, n_seg, eps)[1]
+    y = normalize(x, own, out=out)
+    r = ref_norm.cpu().numpy()
+    seg = y.view(n_seg, -1)
+    for i in range(n_seg):
+        scale_linear(seg[i], float(r[i, 1]), float(r[i, 0]), out=seg[i])
+    return y
+
+
 def sigmoid(x, out=None):
     return elementwise(x, _lib.BE_OP_SIGMOID, 0.0, 0.0, out)
 

@@ -140,10 +140,20 @@ class RuntimeDeployment:
         order = [axes.index(a) for a in "bc" if a in axes] + [axes.index(a) for a in "zyx" if a in axes]
         return np.ascontiguousarray(np.transpose(x, order), dtype=np.float32)
 
-    def _run_ops_unfused(self, x: torch.Tensor, ops: List[Op], n: int, c: int) -> torch.Tensor:
+    def _run_ops_unfused(self, x: torch.Tensor, ops: List[Op], n: int, c: int,
+                         ref_norms: Optional[Dict[int, torch.Tensor]] = None) -> torch.Tensor:
         for op in ops:
             k = op.kwargs
             if op.name == "ensure_dtype":
+                continue
+            if op.name == "scale_mean_variance":
+                # statistics of the reference tensor were taken before anything touched it (see _reference_norms)
+                if ref_norms is None or id(op) not in ref_norms:
+                    raise ValueError(f"scale_mean_variance: reference tensor {k.get('reference_tensor')!r} is not an input")
+                n_seg = self._segments_of(op, n, c)
+                if ref_norms[id(op)].shape[0] != n_seg:
+                    raise ValueError("scale_mean_variance: the reference tensor has a different number of channels")
+                x = K.scale_mean_variance(x, ref_norms[id(op)], n_seg, float(k.get("eps", 1e-6)), out=x)
                 continue
             if op.name in _NORMALISERS:
                 x = K.normalize(x, self._norm_params(x, op, n, c)[0], out=x)
@@ -158,6 +168,29 @@ class RuntimeDeployment:
             else:
                 raise ValueError(f"unsupported processing op {op.name!r}")
         return x
+
+    @staticmethod
+    def _segments_of(op: Op, n: int, c: int) -> int:
+        """How many independent segments the statistics of `op` have: `axes` lists the REDUCED axes (Appendix A.2)."""
+        axes = op.kwargs.get("axes")
+        if axes is not None and any(a in ("b", "batch") for a in axes):
+            raise ValueError("statistics over the batch axis are not supported")
+        joint_c = axes is None or any(a in ("c", "channel") for a in axes)
+        return n if joint_c else n * c
+
+    def _reference_norms(self, ops: List[Op], tensors: Dict[str, torch.Tensor]) -> Dict[int, torch.Tensor]:
+        """{id(op): {ref_mean, ref_std + eps}} for every scale_mean_variance op whose reference tensor is in `tensors`
+        (bioimageio computes input-tensor measures on the sample as given, before any pre-processing)."""
+        out = {}
+        for op in ops:
+            if op.name != "scale_mean_variance":
+                continue
+            ref = tensors.get(str(op.kwargs.get("reference_tensor")))
+            if ref is None:
+                continue
+            n_seg = self._segments_of(op, ref.shape[0], ref.shape[1])
+            out[id(op)] = K.meanvar(ref, n_seg, float(op.kwargs.get("eps", 1e-6)))[1]
+        return out
 
     @staticmethod
     def _norm_params(x: torch.Tensor, op: Op, n: int, c: int):
@@ -198,6 +231,7 @@ class RuntimeDeployment:
 
         pre = [o for o in inp.ops if o.name != "ensure_dtype"]
         post = [o for o in outp.ops if o.name != "ensure_dtype"]
+        ref_norms = self._reference_norms(pre + post, {str(inp.id): x})   # before x is normalised in place
         fused_norm = len(pre) == 1 and pre[0].name in _NORMALISERS
         key = (tuple(x.shape), block, halo)
         pipe = loaded.pipelines.get(key)
@@ -210,7 +244,7 @@ class RuntimeDeployment:
             norm, mode = self._norm_params(x, pre[0], N, C)
             tiles = K.tile_gather(x, pipe.axes, norm=norm, norm_mode=mode, out=pipe.tiles)
         else:
-            tiles = K.tile_gather(self._run_ops_unfused(x, pre, N, C), pipe.axes, out=pipe.tiles)
+            tiles = K.tile_gather(self._run_ops_unfused(x, pre, N, C, ref_norms), pipe.axes, out=pipe.tiles)
         logits = pipe.forward(loaded.net, tiles)
         out_shape = (N, logits.shape[1]) + spatial
         names = [o.name for o in post]
@@ -224,7 +258,7 @@ class RuntimeDeployment:
                 result, _ = K.stitch_crop(logits, out_shape, pipe.axes, epi)
         else:
             stitched, _ = K.stitch_crop(logits, out_shape, pipe.axes)
-            result = self._run_ops_unfused(stitched, post, N, logits.shape[1])
+            result = self._run_ops_unfused(stitched, post, N, logits.shape[1], ref_norms)
         out = result.to(getattr(torch, outp.dtype, torch.float32)) if result.dtype != getattr(torch, outp.dtype, None) else result
         arr = out.cpu().numpy()
         # back to the model's declared output axis order

@@ -93,6 +93,17 @@ def fixed_zero_mean_unit_variance(x: np.ndarray, mean: float, std: float, eps: f
     return ((x - np.float32(mean)) / (np.float32(std) + np.float32(eps))).astype(np.float32)
 
 
+def scale_mean_variance(x: np.ndarray, ref: np.ndarray, axes: Optional[Sequence[int]] = None, eps: float = 1e-6) -> np.ndarray:
+    """bioimageio `scale_mean_variance` (Appendix A.2): (x - mean) / (std + eps) * (ref_std + eps) + ref_mean, the
+    statistics of x and of the reference tensor taken over `axes` (population variance, like zero_mean_unit_variance)."""
+    x = np.asarray(x, dtype=np.float32)
+    ref = np.asarray(ref, dtype=np.float32)
+    mean, var = mean_var(x, axes)
+    rmean, rvar = mean_var(ref, axes)
+    std, rstd = np.sqrt(var) + np.float32(eps), np.sqrt(rvar) + np.float32(eps)
+    return ((x - mean) / std * rstd + rmean).astype(np.float32)
+
+
 def clip(x: np.ndarray, lo: float, hi: float) -> np.ndarray:
     """bioimageio `clip` → np.clip."""
     return np.clip(np.asarray(x, dtype=np.float32), np.float32(lo), np.float32(hi))

@@ -178,3 +178,32 @@ def test_npy_wire_path_round_trip(tmp_path, dev):
     lab = torch.arange(24, dtype=torch.int32, device=dev).reshape(4, 6)
     bio.save_npy_from_device(str(tmp_path / "out.npy"), lab, staging)
     assert np.array_equal(np.load(tmp_path / "out.npy"), lab.cpu().numpy())
+
+
+def test_scale_mean_variance_op_and_in_predict(tmp_path, dev):
+    """bioimageio `scale_mean_variance`: the output is brought to the mean / std of a reference tensor
+    — in zoo models the raw input, whose statistics are taken before pre-processing touches it."""
+    from bioengine_worker_b200 import kernels as K
+    from bioengine_worker_b200.runtime_deployment import RuntimeDeployment
+
+    rng = np.random.default_rng(11)
+    x = (rng.standard_normal((2, 3, 40, 50)) * 3 + 1).astype(np.float32)
+    ref = (rng.standard_normal((2, 3, 40, 50)) * 7 - 4).astype(np.float32)
+    for axes, n_seg in (((1, 2, 3), 2), ((2, 3), 6)):
+        ref_norm = K.meanvar(torch.from_numpy(ref).to(dev), n_seg, 1e-6)[1]
+        got = K.scale_mean_variance(torch.from_numpy(x).to(dev), ref_norm, n_seg, 1e-6).cpu().numpy()
+        np.testing.assert_allclose(got, O.scale_mean_variance(x, ref, axes=axes), rtol=1e-5, atol=2e-5)
+
+    img = O.synthetic_image((128, 160), 12, seed=6, microscope=False) * 50 + 200   # a raw image far from unit scale
+    pre = [{"id": "zero_mean_unit_variance", "kwargs": {"axes": ["y", "x"]}}]
+    post = [{"id": "scale_mean_variance", "kwargs": {"reference_tensor": "raw", "axes": ["y", "x"]}}]
+    rdf_path, net = write_model(tmp_path, pre, post)
+    out = asyncio.run(RuntimeDeployment.func_or_class().predict(rdf_path, img))["mask"]
+    xn = O.zero_mean_unit_variance(img[None, None], axes=(1, 2, 3))
+    with torch.no_grad():
+        y = net.to(dev)(torch.from_numpy(xn).to(dev)).cpu().numpy()
+    want = O.scale_mean_variance(y, img[None, None], axes=(1, 2, 3))
+    assert out.shape == want.shape and out.dtype == np.float32
+    np.testing.assert_allclose(out, want, rtol=1e-4, atol=1e-3)   # forward sees inputs that differ by <= 1e-5 rel
+    assert abs(float(out.mean()) - float(img.mean())) < 1e-2 * abs(float(img.mean()))
+    assert abs(float(out.std()) - float(img.std())) < 1e-2 * float(img.std())
