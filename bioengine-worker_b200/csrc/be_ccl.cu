@@ -446,7 +446,11 @@ __device__ __forceinline__ void link_words(int32_t* Li, u64 m, u64 u, int64_t pm
 
 __global__ void __launch_bounds__(kThreads) ccl_face3d_kernel(int32_t* __restrict__ L, const u64* __restrict__ bitvol,
                                                               Geom g, int64_t words_per_image) {
-    const int64_t w = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+    // four threads per word, one per predecessor row: a thread's unions are a chain of dependent memory round trips, and
+    // the kernel ends when the longest chain does
+    const int64_t gt = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+    const int64_t w = gt >> 2;
+    const int kk = (int)(gt & 3);
     if (w >= words_per_image) return;
     const int wpr = g.tiles_x;
     const u64* B = bitvol + (int64_t)blockIdx.y * words_per_image;
@@ -461,18 +465,18 @@ __global__ void __launch_bounds__(kThreads) ccl_face3d_kernel(int32_t* __restric
     const int64_t x0 = (int64_t)tx * kTX;
     const int64_t pm = ((int64_t)z * g.Y + y) * g.X + x0;
     // same row, x face
-    if (tx > 0 && (m & 1ull) && (B[w - 1] >> 63)) gl_unite(Li, (int32_t)pm, (int32_t)(pm - 1));
+    if (kk == 0 && tx > 0 && (m & 1ull) && (B[w - 1] >> 63)) gl_unite(Li, (int32_t)pm, (int32_t)(pm - 1));
     // predecessor rows (dz, dy): (0,-1) (-1,-1) (-1,0) (-1,+1)
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
+    {
+        const int k = kk;
         const int dz = (k == 0) ? 0 : -1, dy = (k == 0 || k == 1) ? -1 : (k == 2 ? 0 : 1);
         const int steps = (dz != 0) + (dy != 0);
-        if (steps > g.conn) continue;
+        if (steps > g.conn) return;
         const int zz = z + dz, yy = y + dy;
-        if (zz < 0 || yy < 0 || yy >= g.Y) continue;
+        if (zz < 0 || yy < 0 || yy >= g.Y) return;
         const bool diag = steps + 1 <= g.conn;
         const bool other_tile = (dz < 0 && lz == 0) || (dy < 0 && ly == 0) || (dy > 0 && ly == TY - 1);
-        if (!other_tile && !diag) continue;
+        if (!other_tile && !diag) return;
         const int64_t wu = ((int64_t)zz * g.Y + yy) * wpr + tx;
         const int64_t pu = ((int64_t)zz * g.Y + yy) * g.X + x0;
         const u64 u = B[wu];
@@ -745,7 +749,7 @@ extern "C" int be_ccl_u8_i32(const uint8_t* mask, int32_t* labels, int64_t N, in
             BE_LAUNCH_CHECK();
         }
     } else {
-        ccl_face3d_kernel<<<dim3((unsigned)((w.words_per_image + kThreads - 1) / kThreads), (unsigned)N), kThreads, 0, s>>>(
+        ccl_face3d_kernel<<<dim3((unsigned)((4 * w.words_per_image + kThreads - 1) / kThreads), (unsigned)N), kThreads, 0, s>>>(
             w.L, w.bitvol, g, w.words_per_image);
         BE_LAUNCH_CHECK();
     }
