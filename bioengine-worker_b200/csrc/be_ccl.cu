@@ -13,8 +13,8 @@
 //                           masks are kept for step 2.
 //   2. ccl_edge_kernel      (2-D) one warp per tile links its top and left edge to the neighbouring tiles from the edge
 //                           masks alone, one union per touching run pair, a lane's (up to 12) unions issued as a batch;
-//                           ccl_face3d_kernel (3-D) does the same per 64-voxel row word of the bit-packed mask, one
-//                           union after the other.  Unions are atomicMin on the global parent array with path halving.
+//                           ccl_face3d_kernel (3-D) does the same per 64-voxel row word of the bit-packed mask, four
+//                           threads per word (one per predecessor row), each issuing its unions one after the other.  Unions are atomicMin on the global parent array with path halving.
 //   3. ccl_number_kernel    surviving roots are numbered in raster order from the root bitmap (2 MB instead of a
 //                           second pass over all parents) with a single-pass decoupled look-back scan (128 predecessors
 //                           per step); a root's entry becomes -(id) - 1.
