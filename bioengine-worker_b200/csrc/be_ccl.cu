@@ -335,36 +335,28 @@ __device__ __forceinline__ void gl_unite(int32_t* L, int32_t a, int32_t b) {
     }
 }
 
-// 2-D: one warp per tile; top edge against the tile above, left edge against the tile to the left, two corners.
-// A lane owns bits lane and lane + 32 of both edges: at most 12 unions.  They are independent, so they are run as a
-// batch — all parent loads of a level issued before any is used, then all atomics — and a lane pays about three memory
-// round trips in total instead of five per union.  pm / pu give the pixel index of bit i on the two sides of an edge:
-// base + i * step.
-constexpr int kEdgePairs = 12;
+// 2-D: top edge against the tile above, left edge against the tile to the left, two corners.  A lane's unions are
+// independent, so they run as a batch — all parent loads issued before any is used, then all atomics — and cost about
+// three memory round trips in total instead of five per union.  pm / pu give the pixel index of bit i on the two sides
+// of an edge: base + i * step.
+constexpr int kEdgePairs = 3;
 
 struct EdgeBatch {
     int32_t a[kEdgePairs], b[kEdgePairs];
     unsigned valid;
 };
 
-__device__ __forceinline__ void edge_pairs(EdgeBatch& q, int slot0, u64 m, u64 u, int64_t base_m, int64_t base_u,
-                                           int64_t step, bool diag, int lane) {
+// the (up to three) unions of bit i of edge mask m against the neighbour's edge mask u
+__device__ __forceinline__ void edge_pairs(EdgeBatch& q, u64 m, u64 u, int64_t base_m, int64_t base_u, int64_t step,
+                                           bool diag, int i) {
     if (!m || !u) return;
     const LinkMasks k = link_masks(m, u, diag);
-#pragma unroll
-    for (int h = 0; h < 2; ++h) {
-        const int i = lane + 32 * h;
-        const u64 bit = 1ull << i;
-        const int32_t am = (int32_t)(base_m + i * step);
-        const int s = slot0 + 3 * h;
-        q.a[s] = q.a[s + 1] = q.a[s + 2] = am;
-        q.b[s] = (int32_t)(base_u + i * step);
-        q.b[s + 1] = (int32_t)(base_u + (i - 1) * step);
-        q.b[s + 2] = (int32_t)(base_u + (i + 1) * step);
-        q.valid |= ((k.c & bit) ? 1u : 0u) << s;
-        q.valid |= ((k.l & bit) ? 1u : 0u) << (s + 1);
-        q.valid |= ((k.r & bit) ? 1u : 0u) << (s + 2);
-    }
+    const u64 bit = 1ull << i;
+    q.a[0] = q.a[1] = q.a[2] = (int32_t)(base_m + i * step);
+    q.b[0] = (int32_t)(base_u + i * step);
+    q.b[1] = (int32_t)(base_u + (i - 1) * step);
+    q.b[2] = (int32_t)(base_u + (i + 1) * step);
+    q.valid = ((k.c & bit) ? 1u : 0u) | ((k.l & bit) ? 2u : 0u) | ((k.r & bit) ? 4u : 0u);
 }
 
 __device__ __forceinline__ void unite_batch(int32_t* Li, EdgeBatch& q) {
@@ -400,11 +392,17 @@ __device__ __forceinline__ void unite_batch(int32_t* Li, EdgeBatch& q) {
     }
 }
 
+// Four warps per tile: (top | left edge) x (bits 0..31 | 32..63); a lane owns one edge pixel and its at most three unions.
+// A lane's unions are a chain of dependent memory round trips and the kernel ends when the longest chain does, so the
+// work is spread over as many lanes as there are edge pixels.
 __global__ void __launch_bounds__(kThreads) ccl_edge_kernel(int32_t* __restrict__ L, const TileEdges* __restrict__ edges,
                                                             Geom g, int tiles_per_image) {
-    const int t = blockIdx.x * (kThreads / 32) + (threadIdx.x >> 5);
+    const int wg = blockIdx.x * (kThreads / 32) + (threadIdx.x >> 5);
+    const int t = wg >> 2, part = wg & 3;
     if (t >= tiles_per_image) return;
     const int lane = threadIdx.x & 31;
+    const int i = lane + 32 * (part & 1);
+    const bool left = part >> 1;
     const int tx = t % g.tiles_x, ty = t / g.tiles_x;
     const TileEdges* E = edges + (int64_t)blockIdx.y * tiles_per_image;
     int32_t* Li = L + (int64_t)blockIdx.y * g.Y * g.X;
@@ -415,10 +413,10 @@ __global__ void __launch_bounds__(kThreads) ccl_edge_kernel(int32_t* __restrict_
     q.valid = 0;
 #pragma unroll
     for (int k = 0; k < kEdgePairs; ++k) q.a[k] = q.b[k] = 0;
-    if (ty > 0) edge_pairs(q, 0, me.top, E[t - g.tiles_x].bottom, y0 * g.X + x0, (y0 - 1) * g.X + x0, 1, diag, lane);
-    if (tx > 0) edge_pairs(q, 6, me.left, E[t - 1].right, y0 * g.X + x0, y0 * g.X + x0 - 1, g.X, diag, lane);
+    if (!left && ty > 0) edge_pairs(q, me.top, E[t - g.tiles_x].bottom, y0 * g.X + x0, (y0 - 1) * g.X + x0, 1, diag, i);
+    if (left && tx > 0) edge_pairs(q, me.left, E[t - 1].right, y0 * g.X + x0, y0 * g.X + x0 - 1, g.X, diag, i);
     unite_batch(Li, q);
-    if (diag && ty > 0 && lane == 0) {
+    if (diag && ty > 0 && part == 0 && lane == 0) {
         if (tx > 0 && (me.top & 1ull) && (E[t - g.tiles_x - 1].bottom >> 63))
             gl_unite(Li, (int32_t)(y0 * g.X + x0), (int32_t)((y0 - 1) * g.X + x0 - 1));
         if (tx + 1 < g.tiles_x && (me.top >> 63) && (E[t - g.tiles_x + 1].bottom & 1ull))
@@ -744,7 +742,7 @@ extern "C" int be_ccl_u8_i32(const uint8_t* mask, int32_t* labels, int64_t N, in
     BE_LAUNCH_CHECK();
     if (ndim == 2) {
         if (n_tiles > 1) {
-            const unsigned gx = (unsigned)((n_tiles + kThreads / 32 - 1) / (kThreads / 32));
+            const unsigned gx = (unsigned)((4 * n_tiles + kThreads / 32 - 1) / (kThreads / 32));   // four warps per tile
             ccl_edge_kernel<<<dim3(gx, (unsigned)N), kThreads, 0, s>>>(w.L, w.edges, g, (int)n_tiles);
             BE_LAUNCH_CHECK();
         }
