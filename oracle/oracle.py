@@ -4,15 +4,21 @@ This file restates, in numpy/scipy, what the reference (aicell-lab/bioengine-wor
 path.  Only `tests/`, `__graft_entry__.smoke()` and the CPU-baseline / `--impl reference` legs of `bench.py`
 may import it; nothing under `bioengine-worker_b200/` does.
 
-PARITY UNPINNED: the reference is pure Python whose arithmetic lives in third-party packages that are not
-vendored and not installable here (bioimageio.core==0.10.0, xarray==2025.1.2, scikit-image, cellpose==4.0.7;
-pins at apps/model-runner/runtime_deployment.py:16-28 and apps/cellpose-finetuning/main.py:3608), and no
-reference test holds a numeric known answer for this path.  What pins this oracle instead:
-  * the in-tree numpy code of apps/fibsem-mito-analysis/analysis_deployment.py is followed statement by
-    statement (citations below) and calls the *same* numpy/scipy routines the reference calls;
-  * bioimageio.core / cellpose semantics are restated from their published behaviour (SURVEY.md App. A/B);
-  * hand-derived known answers in tests/test_oracle_golden.py (6x6 masks, quantile lerp, shifted last block, reflect
-    padding, IoU = 0.5 ties, rectangle moments) and seeded vectors in tests/golden/ (made by make_golden.py).
+PARITY, row by row:
+  * PINNED to the reference's own code: fibsem normalise (a10), overlap tiling + Gaussian blend (a11), pixel-level
+    binary metrics (a16).  apps/fibsem-mito-analysis/analysis_deployment.py and apps/cellpose-finetuning/main.py import
+    unmodified once `ray.serve` and `hypha_rpc.utils.schema` are stubbed; tests/golden/make_reference_golden.py runs
+    `_infer_tiled`, `analyze` (up to `_prob_to_instances`) and `_binary_threshold`/`_compute_binary_metrics` themselves
+    and commits their outputs as tests/golden/ref_*.npz; tests/test_reference_golden.py holds this oracle to them bit for
+    bit, tests/test_gpu_reference_golden.py holds the CUDA path to the same files.
+  * PARITY UNPINNED for the rows whose arithmetic lives in third-party packages that are not vendored and not
+    installable here (bioimageio.core==0.10.0, xarray==2025.1.2, scikit-image, cellpose==4.0.7; pins at
+    apps/model-runner/runtime_deployment.py:16-28 and apps/cellpose-finetuning/main.py:3608): scale_range /
+    zero_mean_unit_variance / pointwise ops (a6-a9), halo blocking and reassembly (a5), labelling numbering (a13),
+    regionprops (a14), average_precision (a15).  No reference test holds a numeric known answer for them (§8c).  They
+    call the same numpy/scipy routines those packages call, follow their published behaviour, and
+    are held to hand-derived known answers in tests/test_oracle_golden.py (6x6 masks, quantile lerp, shifted last block,
+    reflect padding, IoU = 0.5 ties, rectangle moments) plus seeded vectors in tests/golden/ (make_golden.py).
 
 Paths cited as `ref:` are relative to the reference tree root.
 """

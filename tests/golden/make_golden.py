@@ -1,7 +1,9 @@
 """Regenerates tests/golden/*.npz from the oracle (seeded, small).  Run from the repo root:
     python tests/golden/make_golden.py
-The reference itself cannot be imported here, so these vectors pin the ORACLE's behaviour over time
-and give the GPU tests fixed inputs/outputs; the hand-derived known answers live in tests/test_oracle_golden.py."""
+These vectors come from the ORACLE (they keep its behaviour fixed over time and give the GPU tests fixed inputs and
+outputs for the rows whose reference arithmetic sits in absent third-party packages); the fixtures written by the
+reference's own code are ref_*.npz, made by make_reference_golden.py; hand-derived known answers live in
+tests/test_oracle_golden.py."""
 import os
 import sys
 
