@@ -8,9 +8,16 @@ the forward, the Gaussian blend, the 0.5 threshold, connected components and the
 Of `_prob_to_instances` (ref: analysis_deployment.py:160-176) the deterministic front half runs on the device and matches
 scipy / skimage bit for bit: threshold, `remove_small_objects(min_size=300)`, `binary_closing(disk(4))`, and the exact
 Euclidean distance transform (`prob_to_closed_and_distance`).  The seeded watershed that follows (`peak_local_max`,
-`watershed`) is not ported yet: with `cleanup=False` `analyze` labels the thresholded map
-directly (`measure.label(prob > 0.5)`), with `cleanup=True` it labels the cleaned mask — identical to the reference
-whenever the watershed would not split a connected component.
+`watershed`) is not ported yet.  `analyze` therefore labels the cleaned mask
+(`cleanup=True`, the default: the closest available to the reference); its instances differ from the reference's in
+three known ways until the watershed exists:
+  * numbering: the watershed's labels follow marker order (raster order of the distance peaks), these follow the raster
+    order of each component's first pixel;
+  * `peak_local_max` excludes peaks within `min_distance` of the border, so a component whose only peak lies within
+    8 px of the border gets no marker and stays 0 in the reference; here it is labelled;
+  * the watershed floods with connectivity 1 and splits touching objects at the distance saddle; the labelling here uses
+    connectivity 2 and never splits a connected component.
+`cleanup=False` labels the thresholded map directly (`measure.label(prob > 0.5)`).
 """
 from __future__ import annotations
 
@@ -98,9 +105,10 @@ class MitoAnalysisDeployment:
         return closed, K.distance_transform_edt(closed)
 
     async def analyze(self, image, pixel_size_nm: float = 5.0, tile_size: int = 512, overlap: int = 64,
-                      as_numpy: bool = False, cleanup: bool = False) -> dict:
+                      as_numpy: bool = False, cleanup: bool = True) -> dict:
         """Same contract as ref: analysis_deployment.py:192-286 (`as_numpy=True` skips the nested-list conversion;
-        `cleanup=True` applies remove_small_objects(300) and binary_closing(disk(4)) before labelling)."""
+        `cleanup=True`, the default, applies remove_small_objects(300) and binary_closing(disk(4)) before labelling; see the
+        module docstring for what still differs from the reference's watershed instances)."""
         t0 = time.time()
         image_np = np.array(image, dtype=np.float32)
         if image_np.ndim != 2:

@@ -231,6 +231,7 @@ __device__ void find_bin(const unsigned* __restrict__ hist, uint32_t k, uint32_t
     }
     __syncthreads();  // protects s_warp / s_res from the previous call
     if ((threadIdx.x & 31) == 31) s_warp[threadIdx.x >> 5] = incl;
+    if (threadIdx.x == 0) s_res[0] = s_res[1] = 0;  // k beyond the histogram: a defined answer (bin 0)
     __syncthreads();
     uint32_t base = 0;
     for (int w = 0; w < (int)(threadIdx.x >> 5); ++w) base += s_warp[w];
@@ -387,13 +388,18 @@ __global__ void __launch_bounds__(kThreads) qsel_level12_kernel(const float* __r
     RunCounter rc[kMaxRanks];
     // A bucket of keys is an interval of floats, so almost every element is rejected by two float compares against the
     // hull of the (<= 4, usually 1-2) wanted buckets; NaNs fail both.  The inclusive float test lets both zeros through
-    // at a bucket edge; the exact key test below sorts them out.
+    // at a bucket edge; the exact key test below sorts them out.  The buckets that hold -inf / +inf also span NaN
+    // encodings (keys below key(-inf), above key(+inf)); their bounds are clamped to the infinities' keys first, so the
+    // hull stays a float interval that contains the infinities (a NaN bound would be dropped by fminf / fmaxf and the
+    // hull would come out empty).
+    constexpr uint32_t kKeyNegInf = 0x007fffffu, kKeyPosInf = 0xff800000u;
     float fmin = __int_as_float(0x7f800000), fmax = __int_as_float(0xff800000);
 #pragma unroll
     for (int g = 0; g < kMaxRanks; ++g) {
         if (g < n_groups) {
-            fmin = fminf(fmin, key_to_f32(gp[g] << kHiShift));
-            fmax = fmaxf(fmax, key_to_f32((gp[g] << kHiShift) | ((1u << kHiShift) - 1u)));
+            const uint32_t klo = gp[g] << kHiShift, khi = klo | ((1u << kHiShift) - 1u);
+            fmin = fminf(fmin, key_to_f32(klo < kKeyNegInf ? kKeyNegInf : klo));
+            fmax = fmaxf(fmax, key_to_f32(khi > kKeyPosInf ? kKeyPosInf : khi));
         }
     }
     if (n_valid > 0) {

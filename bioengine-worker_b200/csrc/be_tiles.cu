@@ -831,6 +831,9 @@ extern "C" int be_tile_gather_f32(const float* img, float* tiles, int64_t N, int
                                   const int32_t* ysrc, const int32_t* xsrc, const double* norm, int norm_mode, int clip,
                                   float clip_lo, float clip_hi, be_stream_t stream) {
     BE_REQUIRE(img && tiles && zsrc && ysrc && xsrc, BE_ERR_INVALID_ARG, "be_tile_gather_f32: null pointer");
+    BE_REQUIRE(((((uintptr_t)xsrc) | ((uintptr_t)tiles)) & 15) == 0, BE_ERR_INVALID_ARG,
+               "be_tile_gather_f32: xsrc and tiles must be 16-byte aligned (the kernels read the x table and write the tiles "
+               "with 16-byte accesses)");
     int rc = check_dims("be_tile_gather_f32", N, C, Z, Y, X, Tz, Ty, Tx, Bz, By, Bx);
     if (rc) return rc;
     BE_REQUIRE(norm_mode >= 0 && norm_mode <= 2, BE_ERR_INVALID_ARG, "be_tile_gather_f32: norm_mode %d", norm_mode);
@@ -914,6 +917,8 @@ extern "C" int be_stitch_blend_f32(const float* tiles, float* out, uint8_t* mask
                                    int Sx, const double* wz, const double* wy, const double* wx, int epilogue, float thr,
                                    be_stream_t stream) {
     BE_REQUIRE(tiles && (out || mask) && wz && wy && wx, BE_ERR_INVALID_ARG, "be_stitch_blend_f32: null pointer");
+    BE_REQUIRE((((uintptr_t)wx) & 15) == 0, BE_ERR_INVALID_ARG,
+               "be_stitch_blend_f32: wx must be 16-byte aligned (the kernels read the x window two doubles at a time)");
     int rc = check_dims("be_stitch_blend_f32", N, C, Z, Y, X, Tz, Ty, Tx, Bz, By, Bx);
     if (rc) return rc;
     BE_REQUIRE(epilogue == BE_EPI_NONE || epilogue == BE_EPI_SIGMOID, BE_ERR_INVALID_ARG,

@@ -5,6 +5,7 @@ used for device memory and streams only; all arithmetic happens in libbe_b200.so
 """
 from __future__ import annotations
 
+import functools
 from typing import Optional, Sequence, Tuple
 
 import numpy as np
@@ -16,6 +17,42 @@ from .geometry import AxisBlocks
 
 def _stream() -> int:
     return torch.cuda.current_stream().cuda_stream
+
+
+def _tensor_devices(obj, found):
+    if isinstance(obj, torch.Tensor):
+        found.append(obj.device)
+    elif isinstance(obj, DeviceAxis):
+        found.append(obj.src.device)
+    elif isinstance(obj, (list, tuple)):
+        for o in obj:
+            _tensor_devices(o, found)
+    elif isinstance(obj, dict):
+        for o in obj.values():
+            _tensor_devices(o, found)
+
+
+def _on_tensor_device(fn):
+    """The library launches on the CUDA device that is current and on the stream handed to it.  Every front-end function
+    therefore makes the device of its tensors current for the duration of the call (so `_stream()` is that device's
+    current stream) and refuses tensors that sit on different devices."""
+
+    @functools.wraps(fn)
+    def wrapper(*args, **kwargs):
+        found = []
+        _tensor_devices(args, found)
+        _tensor_devices(list(kwargs.values()), found)
+        cuda = [d for d in found if d.type == "cuda"]
+        if not cuda:
+            return fn(*args, **kwargs)   # the function's own checks report the non-CUDA tensor
+        if any(d != cuda[0] for d in cuda):
+            raise ValueError(f"{fn.__name__}: tensors on different devices ({sorted({str(d) for d in cuda})})")
+        if cuda[0].index is None or cuda[0].index == torch.cuda.current_device():
+            return fn(*args, **kwargs)
+        with torch.cuda.device(cuda[0]):
+            return fn(*args, **kwargs)
+
+    return wrapper
 
 
 def _p(t: Optional[torch.Tensor]) -> Optional[int]:
@@ -55,6 +92,7 @@ def _segments(x: torch.Tensor, n_seg: int) -> Tuple[int, int]:
     return n_seg, n // n_seg
 
 
+@_on_tensor_device
 def meanvar(x: torch.Tensor, n_seg: int, eps: float = 1e-6, ws: Workspace = _default_ws):
     """→ (stats [n_seg,2] fp64 {mean,var}, norm [n_seg,2] fp64 {mean, std+eps})."""
     _check(x, torch.float32, "x")
@@ -67,6 +105,7 @@ def meanvar(x: torch.Tensor, n_seg: int, eps: float = 1e-6, ws: Workspace = _def
     return stats, norm
 
 
+@_on_tensor_device
 def quantile(x: torch.Tensor, n_seg: int, q: torch.Tensor, eps: float = 1e-6, want_norm: bool = True,
              ws: Workspace = _default_ws):
     """Exact nanquantile(method="linear") per segment.  q: fp64 CUDA tensor of 1 or 2 fractions.
@@ -83,6 +122,7 @@ def quantile(x: torch.Tensor, n_seg: int, q: torch.Tensor, eps: float = 1e-6, wa
     return quant, norm
 
 
+@_on_tensor_device
 def normalize(x: torch.Tensor, norm: torch.Tensor, clip: Optional[Tuple[float, float]] = None,
               out: Optional[torch.Tensor] = None) -> torch.Tensor:
     _check(x, torch.float32, "x")
@@ -95,6 +135,7 @@ def normalize(x: torch.Tensor, norm: torch.Tensor, clip: Optional[Tuple[float, f
     return out
 
 
+@_on_tensor_device
 def elementwise(x: torch.Tensor, op: int, a: float = 0.0, b: float = 0.0, out: Optional[torch.Tensor] = None):
     _check(x, torch.float32, "x")
     out = torch.empty_like(x) if out is None else _check(out, torch.float32, "out")
@@ -110,6 +151,7 @@ def scale_linear(x, gain, offset, out=None):
     return elementwise(x, _lib.BE_OP_SCALE_LINEAR, gain, offset, out)
 
 
+@_on_tensor_device
 def scale_mean_variance(x: torch.Tensor, ref_norm: torch.Tensor, n_seg: int, eps: float = 1e-6,
                         out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """bioimageio `scale_mean_variance`: (x - mean) / (std + eps) * (ref_std + eps) + ref_mean per segment.
@@ -128,6 +170,7 @@ def sigmoid(x, out=None):
     return elementwise(x, _lib.BE_OP_SIGMOID, 0.0, 0.0, out)
 
 
+@_on_tensor_device
 def binarize(x: torch.Tensor, thr: float) -> torch.Tensor:
     _check(x, torch.float32, "x")
     out = torch.empty(x.shape, dtype=torch.uint8, device=x.device)
@@ -153,6 +196,7 @@ def _as5d(img: torch.Tensor) -> Tuple[int, int, int, int, int]:
     raise ValueError(f"expected (N,C,Y,X) or (N,C,Z,Y,X), got {tuple(img.shape)}")
 
 
+@_on_tensor_device
 def tile_gather(img: torch.Tensor, axes: Sequence[DeviceAxis], norm: Optional[torch.Tensor] = None, norm_mode: int = 0,
                 clip: Optional[Tuple[float, float]] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """img (N,C,[Z,]Y,X) fp32 → tiles (N*T, C, [Bz,] By, Bx) fp32.  axes = (z, y, x) DeviceAxis (z = identity for 2-D)."""
@@ -177,6 +221,7 @@ def _stitch_outputs(shape, device, want_out, want_mask):
     return out, mask
 
 
+@_on_tensor_device
 def stitch_crop(tiles: torch.Tensor, sample_shape: Sequence[int], axes: Sequence[DeviceAxis], epilogue: int = 0,
                 thr: float = 0.5, want_out: bool = True, want_mask: bool = False):
     """bioimageio inner-region reassembly.  → (out fp32 or None, mask uint8 or None), each of sample_shape."""
@@ -190,6 +235,7 @@ def stitch_crop(tiles: torch.Tensor, sample_shape: Sequence[int], axes: Sequence
     return out, mask
 
 
+@_on_tensor_device
 def stitch_blend(tiles: torch.Tensor, sample_shape: Sequence[int], axes: Sequence[DeviceAxis],
                  windows: Sequence[torch.Tensor], epilogue: int = 0, thr: float = 0.5, want_out: bool = True,
                  want_mask: bool = False):
@@ -204,6 +250,7 @@ def stitch_blend(tiles: torch.Tensor, sample_shape: Sequence[int], axes: Sequenc
     return out, mask
 
 
+@_on_tensor_device
 def ccl(mask: torch.Tensor, connectivity: Optional[int] = None, ws: Workspace = _default_ws,
         out: Optional[torch.Tensor] = None, n_out: Optional[torch.Tensor] = None):
     """mask (N,[Z,]Y,X) uint8 → (labels int32 same shape, n_labels int32 [N] on device)."""
@@ -227,6 +274,7 @@ def ccl(mask: torch.Tensor, connectivity: Optional[int] = None, ws: Workspace = 
     return labels, n_labels
 
 
+@_on_tensor_device
 def label_overlap(lab_true: torch.Tensor, lab_pred: torch.Tensor, capacity: int, cap_true: int, cap_pred: int):
     """(N, ...) int32 label maps → dict of device tensors: keys, counts, area_true, area_pred, max_lbl, status."""
     _check(lab_true, torch.int32, "lab_true")
@@ -250,6 +298,7 @@ def label_overlap(lab_true: torch.Tensor, lab_pred: torch.Tensor, capacity: int,
     return r
 
 
+@_on_tensor_device
 def match_counts(table: dict, thr: torch.Tensor, ws: Workspace = _default_ws) -> torch.Tensor:
     """→ int64 [N, n_thr, 2] {pairs with IoU >= thr, extra partners}."""
     _check(thr, torch.float64, "thr")
@@ -264,6 +313,7 @@ def match_counts(table: dict, thr: torch.Tensor, ws: Workspace = _default_ws) ->
     return out
 
 
+@_on_tensor_device
 def label_stats(labels: torch.Tensor, cap: int):
     """labels (N,[Z,]Y,X) int32 → (sums int64 [N,cap,10], bbox int32 [N,cap,6], status int32 [N])."""
     _check(labels, torch.int32, "labels")
@@ -281,6 +331,7 @@ def label_stats(labels: torch.Tensor, cap: int):
     return sums, bbox, status
 
 
+@_on_tensor_device
 def binary_confusion(pred: torch.Tensor, target: torch.Tensor, thresholds: Optional[Tuple[float, float]] = None):
     """→ (counts int64 [4] {tp, fp, fn, tn}, minmax fp32 [4]) on the device.  thresholds=None: the reference's adaptive rule."""
     _check(pred, torch.float32, "pred")
@@ -295,6 +346,7 @@ def binary_confusion(pred: torch.Tensor, target: torch.Tensor, thresholds: Optio
     return counts, minmax
 
 
+@_on_tensor_device
 def remove_small_objects(mask: torch.Tensor, min_size: int, ws: Workspace = _default_ws) -> torch.Tensor:
     """skimage `remove_small_objects(mask, min_size)` (connectivity 1) for (N, Y, X) uint8 masks → uint8 mask."""
     _check(mask, torch.uint8, "mask")
@@ -316,6 +368,7 @@ def disk_half_widths(radius: int) -> np.ndarray:
     return np.array([int(np.floor(np.sqrt(r * r - dy * dy))) for dy in range(-r, r + 1)], dtype=np.int32)
 
 
+@_on_tensor_device
 def binary_closing(mask: torch.Tensor, half_widths: np.ndarray, ws: Workspace = _default_ws) -> torch.Tensor:
     """scipy `binary_closing(mask, structure)` for (N, Y, X) uint8 masks; structure given by its row half widths."""
     import ctypes
@@ -331,6 +384,7 @@ def binary_closing(mask: torch.Tensor, half_widths: np.ndarray, ws: Workspace = 
     return out
 
 
+@_on_tensor_device
 def distance_transform_edt(mask: torch.Tensor, ws: Workspace = _default_ws) -> torch.Tensor:
     """scipy `distance_transform_edt(mask)` for (N, Y, X) uint8 masks → fp64 distances."""
     _check(mask, torch.uint8, "mask")

@@ -107,7 +107,8 @@ int be_binarize_f32_u8(const float* x, uint8_t* y, int64_t n, float thr, be_stre
  * reflect pad; Appendix A.4, `predict_sample_with_blocking` at runtime_deployment.py:278) and the fibsem
  * convention (stride tiles, bottom/right reflect pad; analysis_deployment.py:132-138).
  *   norm_mode 0: copy only; 1: norm[2*(n*C+c)]; 2: norm[2*n] (statistics joint over channels)
- *   clip      as be_normalize_f32 */
+ *   clip      as be_normalize_f32
+ * `xsrc` and `tiles` must be 16-byte aligned (BE_ERR_INVALID_ARG otherwise); `img` may have any float alignment. */
 int be_tile_gather_f32(const float* img, float* tiles, int64_t N, int64_t C, int64_t Z, int64_t Y, int64_t X,
                        int Tz, int Ty, int Tx, int Bz, int By, int Bx, const int32_t* zsrc, const int32_t* ysrc,
                        const int32_t* xsrc, const double* norm, int norm_mode, int clip, float clip_lo,
@@ -128,7 +129,8 @@ int be_stitch_crop_f32(const float* tiles, float* out, uint8_t* mask, int64_t N,
 /* Gaussian-weighted overlap blend, gather form of analysis_deployment.py:125-156: tiles sit at
  * k*stride, window w = (float)(wz[iz]*wy[iy]*wx[ix]) from host-computed fp64 1-D tables
  * (exp(-2*linspace(-1,1,B)^2); wz = {1.0} for 2-D), acc += (double)(tile*w), wacc += (double)w in
- * ascending tile order, value = (float)(acc/wacc).  Epilogue / mask as be_stitch_crop_f32. */
+ * ascending tile order, value = (float)(acc/wacc).  Epilogue / mask as be_stitch_crop_f32.
+ * `wx` must be 16-byte aligned (BE_ERR_INVALID_ARG otherwise). */
 int be_stitch_blend_f32(const float* tiles, float* out, uint8_t* mask, int64_t N, int64_t C, int64_t Z, int64_t Y,
                         int64_t X, int Tz, int Ty, int Tx, int Bz, int By, int Bx, int Sz, int Sy, int Sx,
                         const double* wz, const double* wy, const double* wx, int epilogue, float thr,

@@ -109,7 +109,7 @@ def test_analyze_matches_fibsem_oracle(dev):
     models.calibrate_head(net, torch.from_numpy(tiles[::3]).to(dev))
     net.final_sigmoid = True
     dep = MitoAnalysisDeployment(model=net, device=dev)
-    res = asyncio.run(dep.analyze(img.tolist(), pixel_size_nm=5.0, tile_size=tile, overlap=ov))
+    res = asyncio.run(dep.analyze(img.tolist(), pixel_size_nm=5.0, tile_size=tile, overlap=ov, cleanup=False))
     with torch.no_grad():
         probs = net(torch.from_numpy(tiles).to(dev)).cpu().numpy()[:, 0]
     prob = O.fibsem_blend(probs, (H, W), tile, ov)
@@ -129,13 +129,13 @@ def test_analyze_matches_fibsem_oracle(dev):
     np.testing.assert_allclose(res["properties"]["eccentricity"], want["eccentricity"], rtol=1e-6, atol=1e-6)
     assert res["image_shape"] == [H, W] and set(res) >= {"labels", "properties", "n_mitochondria", "pixel_size_nm", "model"}
     # cleaned variant: remove_small_objects(300) + binary_closing(disk(4)) before labelling, as `_prob_to_instances` starts
-    res3 = asyncio.run(dep.analyze(img.tolist(), tile_size=tile, overlap=ov, as_numpy=True, cleanup=True))
+    res3 = asyncio.run(dep.analyze(img.tolist(), tile_size=tile, overlap=ov, as_numpy=True))   # cleanup=True is the default
     kept = O.remove_small_objects(prob > 0.5, 300)
     want3 = O.label(O.binary_closing_disk(kept, 4)) if kept.any() else np.zeros((H, W), np.int32)
     assert np.array_equal(res3["labels"], want3) and res3["n_mitochondria"] == want3.max()
     # small image → single untiled call (ref: analysis_deployment.py:247-248)
     small = img[:100, :120]
-    res2 = asyncio.run(dep.analyze(small.tolist(), tile_size=128, overlap=32, as_numpy=True))
+    res2 = asyncio.run(dep.analyze(small.tolist(), tile_size=128, overlap=32, as_numpy=True, cleanup=False))
     with torch.no_grad():
         p2 = net(torch.from_numpy(O.fibsem_normalize(small)[None, None]).to(dev)).cpu().numpy()[0, 0]
     assert np.array_equal(res2["labels"], O.label(p2 > 0.5))
@@ -207,3 +207,26 @@ def test_scale_mean_variance_op_and_in_predict(tmp_path, dev):
     np.testing.assert_allclose(out, want, rtol=1e-4, atol=1e-3)   # forward sees inputs that differ by <= 1e-5 rel
     assert abs(float(out.mean()) - float(img.mean())) < 1e-2 * abs(float(img.mean()))
     assert abs(float(out.std()) - float(img.std())) < 1e-2 * float(img.std())
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_pipeline_on_second_gpu_while_first_is_current():
+    """The library launches on the current device: the front end must make the tensors' device current (and use that
+    device's stream) even when the caller's current device is another one."""
+    from bioengine_worker_b200 import kernels as K
+    from bioengine_worker_b200.pipeline import PipelineSpec, TiledPipeline
+
+    torch.cuda.set_device(0)
+    d1 = torch.device("cuda:1")
+    img = O.synthetic_image((1, 1, 256, 320), 30, seed=1)
+    spec = PipelineSpec(block=(64, 64), halo=(8, 8), convention="bioimageio", preprocess="scale_range")
+    pipe = TiledPipeline(img.shape, spec, device=d1)
+    res = pipe.run(img, lambda t: (t * 6.0 - 2.0).contiguous())
+    torch.cuda.synchronize(d1)
+    assert torch.cuda.current_device() == 0
+    want_tiles = O.blocks_tensor(O.scale_range(img, 1.0, 99.8), (64, 64), (8, 8))
+    want_mask = O.binarize(O.sigmoid(O.from_blocks(want_tiles * np.float32(6.0) - np.float32(2.0), img.shape, (64, 64), (8, 8))), 0.5)
+    assert np.array_equal(res["mask"].cpu().numpy(), want_mask)
+    assert np.array_equal(res["labels"].cpu().numpy()[0, 0], O.label(want_mask[0, 0], 2))
+    with pytest.raises(ValueError):
+        K.normalize(torch.zeros(8, device="cuda:0"), torch.zeros((1, 2), dtype=torch.float64, device=d1))

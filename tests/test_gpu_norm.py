@@ -56,6 +56,26 @@ def test_quantile_segments_ties_negatives_and_nans(dev, rng):
     assert np.array_equal(norm[ok, 1], want[ok, 1] - want[ok, 0] + 1e-6)
 
 
+@pytest.mark.parametrize("seg_len", [50_001, (1 << 18) + 77])   # whole-segment radix select / sampled path
+@pytest.mark.parametrize("q", [(0.0, 1.0), (0.01, 0.99), (0.04, 0.97), (0.5,)])
+def test_quantile_ranks_that_land_on_infinities(seg_len, q, dev, rng):
+    """scale_range defaults to percentiles 0 / 100, so a single inf pixel puts a rank on it.  numpy's lerp then gives
+    inf - inf = NaN or inf * 0 = NaN (or inf when only one neighbour is infinite and gamma > 0); the device lerp performs
+    the same operations on the same two order statistics."""
+    x = (rng.standard_normal((4, seg_len)) * 10).astype(np.float32)
+    x[0, 7] = np.inf                               # one +inf: only q = 1 touches it
+    x[1, rng.random(seg_len) < 0.05] = np.inf      # 5 % +inf
+    x[1, rng.random(seg_len) < 0.03] = -np.inf     # 3 % -inf
+    x[2, rng.random(seg_len) < 0.6] = -np.inf      # median on -inf
+    x[3, :] = np.inf
+    x[3, ::3] = np.nan
+    got, _ = _quant(x, q, 4, dev)
+    with warnings.catch_warnings(), np.errstate(all="ignore"):
+        warnings.simplefilter("ignore")
+        want = np.nanquantile(x, np.asarray(q, np.float64), axis=1, method="linear").T
+    assert np.array_equal(got, want, equal_nan=True)
+
+
 def test_quantile_c2_image_full_size(dev):
     """BASELINE config 2 input: 4096^2, p1.0 / p99.8 with hot pixels; numpy on the same data is the checker."""
     img = O.synthetic_image((2048, 2048), 1000, seed=2)

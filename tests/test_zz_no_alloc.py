@@ -46,6 +46,25 @@ def test_noalloc_matches_workspace_entry_point_twice_in_a_row(dev):
         assert np.array_equal(q_na, want)
 
 
+def test_noalloc_ranks_on_infinities(dev):
+    """Ranks that land in the key buckets of -inf / +inf (those buckets also span NaN encodings)."""
+    import warnings
+
+    rng = np.random.default_rng(11)
+    x = (rng.standard_normal((3, 70_001)) * 10).astype(np.float32)
+    x[0, 3] = np.inf
+    x[1, rng.random(70_001) < 0.05] = np.inf
+    x[1, rng.random(70_001) < 0.05] = -np.inf
+    x[2, :] = -np.inf
+    for q in ((0.0, 1.0), (0.02, 0.97)):
+        (q_ws, _), (q_na, _) = _both(x, 3, q, dev)
+        with warnings.catch_warnings(), np.errstate(all="ignore"):
+            warnings.simplefilter("ignore")
+            want = np.nanquantile(x, np.array(q), axis=1).T
+        assert np.array_equal(q_na, want, equal_nan=True)
+        assert np.array_equal(q_ws, q_na, equal_nan=True)
+
+
 def test_noalloc_rejects_more_segments_than_its_scratch_holds(dev):
     from bioengine_worker_b200 import _lib
 
