@@ -45,6 +45,7 @@ SIGNATURES = {
     "be_label_overlap_i32": (_i32, [_ptr, _ptr, _i64, _i64, _ptr, _ptr, _i64, _ptr, _i64, _ptr, _i64, _ptr, _ptr, _ptr]),
     "be_match_workspace_bytes": (_sz, [_i64, _i64, _i64, _i32]),
     "be_match_counts": (_i32, [_ptr, _ptr, _i64, _i64, _ptr, _i64, _ptr, _i64, _ptr, _i32, _ptr, _ptr, _ptr]),
+    "be_screen_rows_i64": (_i32, [_ptr, _ptr, _ptr, _i64, _i32, _ptr, _ptr, _ptr, _ptr, _ptr]),
     "be_binary_confusion_f32": (_i32, [_ptr, _ptr, _i64, _i32, _f32, _f32, _ptr, _ptr, _ptr]),
     "be_label_area_i32": (_i32, [_ptr, _i64, _i64, _i64, _ptr, _ptr, _ptr]),
     "be_keep_large_u8": (_i32, [_ptr, _ptr, _i64, _i64, _i64, _i32, _ptr, _ptr]),

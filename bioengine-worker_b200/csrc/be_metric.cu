@@ -170,6 +170,32 @@ __global__ void __launch_bounds__(kThreads) match_kernel(const unsigned long lon
     }
 }
 
+// ---- screening table rows ----
+//
+// One thread per (image, column): turns a batch's {pairs, extra} counts and max labels into rows of the screening
+// table [n_images][n_thr + 2] = {tp per threshold, n_true, n_pred} at the batch's image indices, and folds the batch's
+// status words into two sticky flags, so a shard runs without the host looking at anything until the table is merged.
+__global__ void screen_rows_kernel(const unsigned long long* __restrict__ counts, const int32_t* __restrict__ max_lbl,
+                                   const int32_t* __restrict__ status, int64_t N, int n_thr,
+                                   const double* __restrict__ thr, const int64_t* __restrict__ rows,
+                                   long long* __restrict__ table, int32_t* __restrict__ flags) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int cols = n_thr + 2;
+    if (i >= N * cols) return;
+    const int64_t img = i / cols;
+    const int k = (int)(i - img * cols);
+    long long v;
+    if (k < n_thr) {
+        const unsigned long long pairs = counts[(img * n_thr + k) * 2], extra = counts[(img * n_thr + k) * 2 + 1];
+        v = (long long)(pairs - extra);
+        if (extra && thr[k] < 0.5) atomicOr(&flags[1], 1);   // below 0.5 the assignment is not implied by the counts
+    } else {
+        v = max_lbl[img * 2 + (k - n_thr)];
+        if (k == n_thr && status[img]) atomicMax(&flags[0], status[img]);
+    }
+    table[rows[img] * cols + k] = v;
+}
+
 // ---- label statistics ----
 
 __device__ __forceinline__ unsigned long long series_sum(unsigned long long a, unsigned long long b) {
@@ -368,6 +394,19 @@ extern "C" int be_match_counts(const uint64_t* keys, const uint32_t* counts, int
     match_kernel<<<dim3((unsigned)((capacity + kThreads - 1) / kThreads), (unsigned)N), kThreads, 0, s>>>(
         (const unsigned long long*)keys, counts, capacity, area_true, cap_true, area_pred, cap_pred, thr, n_thr,
         (unsigned long long*)counts_out, (unsigned*)ws, wt, wp);
+    BE_LAUNCH_CHECK();
+    return BE_OK;
+}
+
+extern "C" int be_screen_rows_i64(const int64_t* counts, const int32_t* max_lbl, const int32_t* status, int64_t N,
+                                  int n_thr, const double* thr, const int64_t* rows, int64_t* table, int32_t* flags,
+                                  be_stream_t stream) {
+    BE_REQUIRE(counts && max_lbl && status && thr && rows && table && flags, BE_ERR_INVALID_ARG,
+               "be_screen_rows_i64: null pointer");
+    BE_REQUIRE(N > 0 && n_thr >= 1 && n_thr <= 16, BE_ERR_INVALID_ARG, "be_screen_rows_i64: bad sizes");
+    const int64_t n = N * (n_thr + 2);
+    screen_rows_kernel<<<(unsigned)((n + 127) / 128), 128, 0, (cudaStream_t)stream>>>(
+        (const unsigned long long*)counts, max_lbl, status, N, n_thr, thr, rows, (long long*)table, flags);
     BE_LAUNCH_CHECK();
     return BE_OK;
 }

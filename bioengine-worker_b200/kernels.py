@@ -314,6 +314,22 @@ def match_counts(table: dict, thr: torch.Tensor, ws: Workspace = _default_ws) ->
 
 
 @_on_tensor_device
+def screen_rows(counts: torch.Tensor, table_: dict, thr: torch.Tensor, rows: torch.Tensor, table_model: torch.Tensor,
+                flags: torch.Tensor):
+    """Write the batch's rows {tp per threshold, n_true, n_pred} into one model's [n_images, n_thr + 2] int64 block of the
+    screening table at image indices `rows` (int64, device); sticky status flags go to `flags` (int32 [2])."""
+    _check(counts, torch.int64, "counts")
+    _check(rows, torch.int64, "rows")
+    _check(table_model, torch.int64, "table_model")
+    _check(flags, torch.int32, "flags")
+    N, n_thr = counts.shape[0], counts.shape[1]
+    if table_model.shape[-1] != n_thr + 2 or rows.numel() != N:
+        raise ValueError("table block / rows do not match the counts")
+    _lib.call("be_screen_rows_i64", counts.data_ptr(), table_["max_lbl"].data_ptr(), table_["status"].data_ptr(), N, n_thr,
+              thr.data_ptr(), rows.data_ptr(), table_model.data_ptr(), flags.data_ptr(), _stream())
+
+
+@_on_tensor_device
 def label_stats(labels: torch.Tensor, cap: int):
     """labels (N,[Z,]Y,X) int32 → (sums int64 [N,cap,10], bbox int32 [N,cap,6], status int32 [N])."""
     _check(labels, torch.int32, "labels")

@@ -5,6 +5,11 @@ followed by `average_precision` and `np.nanmean` (ref: apps/cellpose-finetuning/
 evaluates all models on its image shard (i % world == rank) entirely on its GPU and contributes integer TP / FP / FN
 rows to a zero-initialised table; one all-reduce (sum ≡ gather, integer-exact) merges the shards and every rank computes
 the same float32 AP, nanmean and ranking the single-process reference would.
+
+The shard runs as a device loop: between the upload of a batch and the all-reduce nothing comes back to the host.  Label
+capacities are sized once per shard from bounds (the ground truth's largest label, known on the host; a cap on predicted
+components), the rows of the table are written by a kernel, and overflow / tie conditions are kept in two sticky device
+flags that are read once, after the last batch.
 """
 from __future__ import annotations
 
@@ -14,8 +19,8 @@ import numpy as np
 import torch
 import torch.distributed as dist
 
-from . import _lib, kernels as K
-from .metrics import ap_from_counts, counts_to_tp, match_counts_device
+from . import _lib, geometry as G, kernels as K
+from .metrics import _next_pow2, ap_from_counts, average_precision
 
 
 def shard_indices(n_images: int, rank: int, world: int) -> List[int]:
@@ -41,11 +46,70 @@ def merge_and_rank(local_table: torch.Tensor, thresholds: Sequence[float]) -> Di
     return {"ap": ap, "mean_ap": mean_ap, "ranking": order, "table": t}
 
 
+def max_components(shape: Sequence[int], connectivity: Optional[int] = None) -> int:
+    """Most components a binary image of this shape can hold: with full connectivity two foreground pixels of different
+    components cannot share a 2x2(x2) cell; with connectivity 1 a checkerboard reaches half the pixels."""
+    nd = len(shape)
+    c = nd if connectivity is None else connectivity
+    if c >= nd:
+        return int(np.prod([(s + 1) // 2 for s in shape]))
+    return int((np.prod(shape) + 1) // 2)
+
+
+class ShardScreener:
+    """Buffers and tables for screening batches of (B, 1, H, W) images against (B, H, W) ground-truth labels on one GPU.
+
+    `cap_true` = largest ground-truth label + 1 over the shard (host knowledge); `cap_pred` = how many predicted
+    components per image the tables are sized for (default: min(the geometric bound, max(4096, pixels / 32)) + 1).  If an
+    image exceeds it the sticky flag reports 2 and the caller reruns with the geometric bound."""
+
+    def __init__(self, spatial: Sequence[int], n_thr: int, cap_true: int, cap_pred: Optional[int] = None,
+                 connectivity: Optional[int] = None, device="cuda:0", eps: float = 1e-6):
+        self.device = torch.device(device)
+        self.spatial = tuple(int(s) for s in spatial)
+        self.connectivity = connectivity
+        self.eps = eps
+        n_px = int(np.prod(self.spatial))
+        bound = max_components(self.spatial, connectivity) + 1
+        self.cap_true = int(cap_true)
+        self.cap_pred = int(cap_pred) if cap_pred else min(bound, max(4096, n_px // 32) + 1)
+        self.capacity = _next_pow2(4 * (self.cap_true + self.cap_pred) + 64)
+        axes = [G.identity_axis(s) for s in self.spatial]
+        if len(axes) == 2:
+            axes = [G.identity_axis(1)] + axes
+        self.axes = [K.DeviceAxis(a, self.device) for a in axes]   # one block = the image: the stitcher's fused epilogue
+        self.ws = K.Workspace()
+        self.flags = torch.zeros(2, dtype=torch.int32, device=self.device)
+
+    def normalise(self, x: torch.Tensor) -> torch.Tensor:
+        """zero_mean_unit_variance per image: statistics, then the fused apply (what the forward reads)."""
+        _, norm = K.meanvar(x, x.shape[0], self.eps, ws=self.ws)
+        return K.normalize(x, norm)
+
+    def score(self, logits: torch.Tensor, gt: torch.Tensor, thr: torch.Tensor, rows: torch.Tensor,
+              table_model: torch.Tensor) -> None:
+        """logits (B, 1, *spatial) fp32 of one model → sigmoid + binarize 0.5 (one pass, mask only) → labels → overlap
+        table vs gt → pair counts → rows of `table_model` at image indices `rows`.  Nothing returns to the host."""
+        B = logits.shape[0]
+        shape = (B, 1) + self.spatial
+        _, mask = K.stitch_crop(logits, shape, self.axes, _lib.BE_EPI_SIGMOID, 0.5, want_out=False, want_mask=True)
+        labels, _ = K.ccl(mask.reshape((B,) + self.spatial), self.connectivity, ws=self.ws)
+        tab = K.label_overlap(gt, labels, self.capacity, self.cap_true, self.cap_pred)
+        counts = K.match_counts(tab, thr, ws=self.ws)
+        K.screen_rows(counts, tab, thr, rows, table_model, self.flags)
+
+    def check(self) -> int:
+        """The one host read of a shard: 0 ok, 1 pair table overflow, 2 label beyond a capacity, +4 a threshold below 0.5
+        met several partners (host assignment needed)."""
+        f = self.flags.cpu().tolist()
+        return int(f[0]) | (4 if f[1] else 0)
+
+
 @torch.no_grad()
 def screen_models(models: Sequence[Callable[[torch.Tensor], torch.Tensor]], images: Sequence[np.ndarray],
                   gt_labels: Sequence[np.ndarray], thresholds=(0.5, 0.75, 0.9), device="cuda:0", batch: int = 32,
                   rank: Optional[int] = None, world: Optional[int] = None, eps: float = 1e-6,
-                  connectivity: Optional[int] = None) -> Dict[str, np.ndarray]:
+                  connectivity: Optional[int] = None, cap_pred: Optional[int] = None) -> Dict[str, np.ndarray]:
     """images: list of (H, W) float arrays of one shape; gt_labels: matching int label images.
     Per (model, image): zero_mean_unit_variance → forward (untiled) → sigmoid → binarize 0.5 → CC labels → AP vs GT."""
     if rank is None:
@@ -56,22 +120,34 @@ def screen_models(models: Sequence[Callable[[torch.Tensor], torch.Tensor]], imag
     thr = torch.tensor([float(t) for t in thresholds], dtype=torch.float64, device=dev)
     table = torch.zeros((len(models), n_images, n_thr + 2), dtype=torch.int64, device=dev)
     mine = shard_indices(n_images, rank, world)
-    ws = K.Workspace()
-    for s in range(0, len(mine), batch):
-        idx = mine[s:s + batch]
-        x = torch.from_numpy(np.stack([np.asarray(images[i], np.float32) for i in idx])[:, None]).to(dev)
-        gt = torch.from_numpy(np.stack([np.asarray(gt_labels[i], np.int32) for i in idx])).to(dev)
-        cap_true = int(gt.max().item()) + 1
-        _, norm = K.meanvar(x, len(idx), eps, ws=ws)
-        xn = K.normalize(x, norm)
-        for m, model in enumerate(models):
-            logits = model(xn).contiguous()
-            mask = K.binarize(K.sigmoid(logits), 0.5)
-            labels, n_lab = K.ccl(mask[:, 0], connectivity, ws=ws)
-            cap_pred = int(n_lab.max().item()) + 1
-            counts, max_lbl, tab = match_counts_device(gt, labels, thr, cap_true, cap_pred)
-            tp = counts_to_tp(counts.cpu().numpy(), thresholds, tab)
-            rows = torch.tensor(idx, device=dev)
-            table[m, rows, :n_thr] = torch.from_numpy(tp).to(dev)
-            table[m, rows, n_thr:] = max_lbl.to(torch.int64)
+    if mine:
+        spatial = tuple(np.asarray(images[mine[0]]).shape)
+        cap_true = max(int(np.asarray(gt_labels[i]).max()) for i in mine) + 1   # host arrays: no device round trip
+        scr = ShardScreener(spatial, n_thr, cap_true, cap_pred, connectivity, dev, eps)
+        for s in range(0, len(mine), batch):
+            idx = mine[s:s + batch]
+            x = torch.from_numpy(np.stack([np.asarray(images[i], np.float32) for i in idx])[:, None]).to(dev, non_blocking=True)
+            gt = torch.from_numpy(np.stack([np.asarray(gt_labels[i], np.int32) for i in idx])).to(dev, non_blocking=True)
+            rows = torch.tensor(idx, dtype=torch.int64).to(dev, non_blocking=True)
+            xn = scr.normalise(x)
+            for m, model in enumerate(models):
+                scr.score(model(xn).contiguous(), gt, thr, rows, table[m])
+        state = scr.check()   # the shard's only device → host read before the merge
+        if state & 3 == 2 and scr.cap_pred < max_components(spatial, connectivity) + 1:
+            # more predicted components than the tables were sized for: once more with the geometric bound
+            return screen_models(models, images, gt_labels, thresholds, device, batch, rank, world, eps, connectivity,
+                                 cap_pred=max_components(spatial, connectivity) + 1)
+        if state & 3:
+            raise RuntimeError(f"screening tables overflowed (status {state & 3})")
+        if state & 4:
+            # thresholds below 0.5 with tied partners: those rows come from the exact assignment (rare; host)
+            for m, model in enumerate(models):
+                for i in mine:
+                    x = torch.from_numpy(np.asarray(images[i], np.float32)[None, None]).to(dev)
+                    lab, _ = K.ccl(K.stitch_crop(model(scr.normalise(x)).contiguous(), (1, 1) + spatial, scr.axes,
+                                                 _lib.BE_EPI_SIGMOID, 0.5, want_out=False, want_mask=True)[1][0],
+                                   connectivity)
+                    _, tp, _, _ = average_precision([np.asarray(gt_labels[i], np.int32)], [lab[0].cpu().numpy()],
+                                                    list(thresholds), device=dev)
+                    table[m, i, :n_thr] = torch.from_numpy(tp[0].astype(np.int64)).to(dev)
     return merge_and_rank(table, thresholds)

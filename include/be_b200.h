@@ -177,6 +177,17 @@ int be_match_counts(const uint64_t* keys, const uint32_t* counts, int64_t N, int
                     const int32_t* area_true, int64_t cap_true, const int32_t* area_pred, int64_t cap_pred,
                     const double* thr, int n_thr, int64_t* counts_out, void* ws, be_stream_t stream);
 
+/* Rows of the screening table for one batch of images and one model, written on the device: for image i of the batch,
+ * table[rows[i]*(n_thr+2) + k] = tp at threshold k (= pairs - extra of be_match_counts), then n_true, n_pred
+ * (= max labels, what cellpose uses for fp = n_pred - tp, fn = n_true - tp) — the integers the ranks all-reduce before
+ * `ap = tp/(tp+fp+fn)` and `np.nanmean` (apps/cellpose-finetuning/main.py:2002-2008).  `flags` (2 int32, zeroed by the
+ * caller once per shard, sticky): flags[0] = largest status word seen (1 pair table full, 2 label out of range),
+ * flags[1] = 1 if a threshold below 0.5 met a label with several partners (that image needs the host assignment).
+ *   counts [N*n_thr*2] int64, max_lbl [N*2], status [N] as written by be_match_counts / be_label_overlap_i32
+ *   rows   [N] int64 image index of each batch entry      table: the model's [n_images][n_thr+2] int64 block */
+int be_screen_rows_i64(const int64_t* counts, const int32_t* max_lbl, const int32_t* status, int64_t N, int n_thr,
+                       const double* thr, const int64_t* rows, int64_t* table, int32_t* flags, be_stream_t stream);
+
 /* Pixel-level binary confusion counts of a prediction against a target — `_binary_threshold` +
  * `_compute_binary_metrics` of apps/cellpose-finetuning/main.py:1225-1270.  adaptive != 0 picks each threshold on the
  * device the way the reference does (0.5 if that tensor's values lie within [0, 1], else 0.0); otherwise thr_pred /

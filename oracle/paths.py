@@ -40,11 +40,15 @@ def crop_post(logits: np.ndarray, shape: Sequence[int], block: Sequence[int], ha
     return prob, mask, labels
 
 
-def timed_c2(img: np.ndarray, logits: np.ndarray, tile: int, overlap: int) -> Tuple[float, Dict[str, float]]:
-    """Seconds for pre + post on one image (forward excluded: the logits are given)."""
+def timed_c2(img: np.ndarray, logits: np.ndarray, tile: int, overlap: int,
+             keep: Optional[dict] = None) -> Tuple[float, Dict[str, float]]:
+    """Seconds for pre + post on one image (forward excluded: the logits are given).  `keep`, if given, receives the
+    tiles and labels the pass produced (so a caller can compare them with another implementation's)."""
     t0 = time.perf_counter()
-    c2_pre(img, tile, overlap)
+    tiles = c2_pre(img, tile, overlap)
     t1 = time.perf_counter()
-    c2_post(logits, img.shape[2:], tile, overlap)
+    _, mask, labels = c2_post(logits, img.shape[2:], tile, overlap)
     t2 = time.perf_counter()
+    if keep is not None:
+        keep.update(tiles=tiles, mask=mask, labels=labels)
     return t2 - t0, {"pre_s": t1 - t0, "post_s": t2 - t1}

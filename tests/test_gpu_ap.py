@@ -115,3 +115,32 @@ def test_binary_metrics_match_reference_rule(case):
         assert got[k] == want[k], k
     for k in ("precision", "recall", "f1", "pixel_accuracy", "iou"):
         assert got[k] == want[k], k
+
+
+def test_screening_device_loop_capacity_retry_and_low_thresholds(dev):
+    """The shard runs without host reads; two conditions are only known afterwards and both must end in the exact table:
+    more predicted components than the tables were sized for (rerun with the geometric bound), and a threshold below
+    0.5 where a label has several partners (those rows come from the exact assignment)."""
+    from bioengine_worker_b200.screening import screen_models
+
+    rng = np.random.default_rng(5)
+    n, shape = 5, (96, 128)
+    imgs, gts = [], []
+    for i in range(n):
+        clean = O.gaussian_blobs(shape, 14, seed=300 + i)
+        imgs.append((clean + 0.35 * rng.standard_normal(shape)).astype(np.float32))   # noisy: speckle components
+        gts.append(O.label(clean > 0.5, 2))
+    nets = [lambda t: t * 4.0, lambda t: (torch.nn.functional.avg_pool2d(t, 3, 1, 1)) * 6.0 - 1.0]
+    thr = (0.2, 0.5, 0.8)
+    res = screen_models(nets, imgs, gts, thresholds=thr, device=dev, batch=2, cap_pred=8)
+    x = torch.from_numpy(np.stack(imgs)[:, None]).to(dev)
+    from bioengine_worker_b200 import kernels as K
+
+    xn = K.normalize(x, K.meanvar(x, n, 1e-6)[1])
+    for m, net in enumerate(nets):
+        logits = net(xn).cpu().numpy()
+        preds = [O.label(O.binarize(O.sigmoid(l), 0.5)[0], 2) for l in logits]
+        assert max(int(p.max()) for p in preds) > 8
+        ap, tp, _, _ = O.average_precision(gts, preds, threshold=list(thr))
+        assert np.array_equal(res["table"][m, :, :3], tp.astype(np.int64))
+        assert np.array_equal(res["ap"][m], ap, equal_nan=True)
