@@ -42,9 +42,10 @@ SIGNATURES = {
     "be_stitch_blend_f32": (_i32, [_ptr] * 3 + [_i64] * 5 + [_i32] * 9 + [_ptr] * 3 + [_i32, _f32, _ptr]),
     "be_ccl_workspace_bytes": (_sz, [_i64] * 4),
     "be_ccl_u8_i32": (_i32, [_ptr, _ptr] + [_i64] * 4 + [_i32, _ptr, _ptr, _ptr]),
-    "be_label_overlap_i32": (_i32, [_ptr, _ptr, _i64, _i64, _ptr, _ptr, _i64, _ptr, _i64, _ptr, _i64, _ptr, _ptr, _ptr]),
+    "be_label_overlap_i32": (_i32, [_ptr, _ptr, _i64, _i64, _i64, _ptr, _ptr, _i64, _ptr, _i64, _ptr, _i64, _ptr, _ptr, _ptr,
+                                    _ptr]),
     "be_match_workspace_bytes": (_sz, [_i64, _i64, _i64, _i32]),
-    "be_match_counts": (_i32, [_ptr, _ptr, _i64, _i64, _ptr, _i64, _ptr, _i64, _ptr, _i32, _ptr, _ptr, _ptr]),
+    "be_match_counts": (_i32, [_ptr, _ptr, _i64, _i64, _ptr, _i64, _ptr, _i64, _ptr, _i32, _ptr, _ptr, _ptr, _ptr]),
     "be_screen_rows_i64": (_i32, [_ptr, _ptr, _ptr, _i64, _i32, _ptr, _ptr, _ptr, _ptr, _ptr]),
     "be_binary_confusion_f32": (_i32, [_ptr, _ptr, _i64, _i32, _f32, _f32, _ptr, _ptr, _ptr]),
     "be_label_area_i32": (_i32, [_ptr, _i64, _i64, _i64, _ptr, _ptr, _ptr]),

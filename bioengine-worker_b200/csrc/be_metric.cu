@@ -43,46 +43,164 @@ __device__ __forceinline__ void table_add(unsigned long long* keys, unsigned* co
     *status = 1;  // table full
 }
 
-// Each lane owns 4 consecutive pixels.  A lane whose 4 pairs are equal joins a warp-level run with its
-// neighbours (one table update per run); mixed lanes insert their own sub-runs.
+// ---- label-pair overlap ----
+//
+// One CTA owns a 128 x 128 px tile of the image pair.  Each lane owns 4 consecutive pixels of a row; a lane whose 4 pairs
+// are equal joins a warp-level run with its neighbours, mixed lanes split into sub-runs.  Runs are accumulated in a
+// shared-memory hash table first: a component is a compact blob, so a tile sees each (true, pred) pair many times (once
+// per row it crosses) but holds only a few hundred distinct pairs, and the global atomics shrink from one per run to one
+// per (tile, pair).  Background-on-background runs are only counted.  At the end of the tile every entry adds its count to
+// the two per-label areas, and entries with both labels > 0 also go to the image's global pair table (only those pairs
+// can match; the areas carry what the IoU needs from the background row and column).
+
+constexpr int kOvTile = 128;        // tile edge in pixels
+constexpr int kOvSlots = 2048;      // shared-memory table slots (24 KB)
+constexpr int kOvProbes = 48;       // give up on the shared table after this many probes: straight to global
+
+// How much of an image's tables a call uses: the host passes the allocated sizes; if per-image label bounds are known on
+// the device (e.g. the component counts the labelling kernel just wrote) the pair table is cut to a power of two that
+// fits them, so clearing and scanning cost what the image needs, not what the worst image would.
+struct OvSizes {
+    int64_t capacity;   // pair-table slots in use (power of two, <= allocated)
+    int64_t n_true, n_pred;   // area entries in use (<= cap_true / cap_pred)
+};
+__device__ __forceinline__ OvSizes ov_sizes(const int32_t* __restrict__ bounds, int64_t img, int64_t capacity,
+                                            int64_t cap_true, int64_t cap_pred) {
+    OvSizes z{capacity, cap_true, cap_pred};
+    if (bounds) {
+        const int64_t bt = min((int64_t)max(bounds[img * 2 + 0], 0) + 1, cap_true);
+        const int64_t bp = min((int64_t)max(bounds[img * 2 + 1], 0) + 1, cap_pred);
+        z.n_true = bt;
+        z.n_pred = bp;
+        const unsigned long long want = 4ull * (unsigned long long)(bt + bp) + 64ull;
+        int64_t c = 1ll << (64 - __clzll((long long)(want - 1)));
+        z.capacity = min(c, capacity);
+    }
+    return z;
+}
+
+__global__ void __launch_bounds__(kThreads) overlap_init_kernel(unsigned long long* __restrict__ keys,
+                                                                unsigned* __restrict__ counts, int64_t capacity,
+                                                                int32_t* __restrict__ area_true, int64_t cap_true,
+                                                                int32_t* __restrict__ area_pred, int64_t cap_pred,
+                                                                int32_t* __restrict__ max_lbl, int32_t* __restrict__ status,
+                                                                const int32_t* __restrict__ bounds) {
+    const int64_t img = blockIdx.y;
+    const OvSizes z = ov_sizes(bounds, img, capacity, cap_true, cap_pred);
+    const int64_t stride = (int64_t)gridDim.x * kThreads;
+    const int64_t i0 = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+    for (int64_t i = i0; i < z.capacity; i += stride) {
+        keys[img * capacity + i] = kEmpty;
+        counts[img * capacity + i] = 0;
+    }
+    for (int64_t i = i0; i < z.n_true; i += stride) area_true[img * cap_true + i] = 0;
+    for (int64_t i = i0; i < z.n_pred; i += stride) area_pred[img * cap_pred + i] = 0;
+    if (i0 == 0) {
+        max_lbl[img * 2] = max_lbl[img * 2 + 1] = 0;
+        status[img] = 0;
+    }
+}
+
+struct OvGlobal {
+    unsigned long long* K;
+    unsigned* Cn;
+    int64_t capacity;
+    int32_t *area_true, *area_pred;
+    int64_t n_true, n_pred;
+    int32_t* st;
+};
+
+// one (pair, count) into the global structures; (t, 0) / (0, p) only touch the areas (background areas come per CTA)
+__device__ __forceinline__ void ov_global_add(const OvGlobal& G, unsigned long long key, unsigned cnt, unsigned* bg_true,
+                                              unsigned* bg_pred) {
+    const int64_t t = (int64_t)(key >> 32), p = (int64_t)(key & 0xffffffffull);
+    if (t >= G.n_true || p >= G.n_pred) {
+        *G.st = 2;
+        return;
+    }
+    if (t) atomicAdd(&G.area_true[t], (int)cnt); else atomicAdd(bg_true, cnt);
+    if (p) atomicAdd(&G.area_pred[p], (int)cnt); else atomicAdd(bg_pred, cnt);
+    if (t && p) table_add(G.K, G.Cn, G.capacity, key, cnt, G.st);
+}
+
+__device__ __forceinline__ void ov_add(unsigned long long* sk, unsigned* sc, const OvGlobal& G, unsigned long long key,
+                                       unsigned cnt, unsigned* bg_true, unsigned* bg_pred) {
+    unsigned slot = (unsigned)mix64(key) & (kOvSlots - 1);
+    for (int probe = 0; probe < kOvProbes; ++probe) {
+        unsigned long long old = sk[slot];
+        if (old != key) {
+            if (old == kEmpty) old = atomicCAS(&sk[slot], kEmpty, key);
+            if (old != kEmpty && old != key) {
+                slot = (slot + 1) & (kOvSlots - 1);
+                continue;
+            }
+        }
+        atomicAdd(&sc[slot], cnt);
+        return;
+    }
+    ov_global_add(G, key, cnt, bg_true, bg_pred);   // crowded tile (far more than ~1500 distinct pairs): bypass
+}
+
 __global__ void __launch_bounds__(kThreads) overlap_kernel(const int32_t* __restrict__ lab_true,
-                                                           const int32_t* __restrict__ lab_pred, int64_t n_px,
-                                                           unsigned long long* __restrict__ keys,
+                                                           const int32_t* __restrict__ lab_pred, int64_t n_px, int64_t X,
+                                                           int tiles_x, unsigned long long* __restrict__ keys,
                                                            unsigned* __restrict__ counts, int64_t capacity,
-                                                           int32_t* __restrict__ status) {
+                                                           int32_t* __restrict__ area_true, int64_t cap_true,
+                                                           int32_t* __restrict__ area_pred, int64_t cap_pred,
+                                                           int32_t* __restrict__ max_lbl, int32_t* __restrict__ status,
+                                                           const int32_t* __restrict__ bounds) {
+    __shared__ unsigned long long sk[kOvSlots];
+    __shared__ unsigned sc[kOvSlots];
+    __shared__ unsigned s_bg[3];   // pixels of (0,0), of (t,0) [pred background], of (0,p) [true background]
+    __shared__ int s_max[2];
     const int64_t img = blockIdx.y;
     const int32_t* t = lab_true + img * n_px;
     const int32_t* p = lab_pred + img * n_px;
-    unsigned long long* K = keys + img * capacity;
-    unsigned* Cn = counts + img * capacity;
-    int32_t* st = status + img;
-    const int lane = threadIdx.x & 31;
-    const int64_t n4 = (n_px + 3) >> 2;
-    const int64_t stride = (int64_t)gridDim.x * kThreads;
-    const bool vec_ok = ((((uintptr_t)t | (uintptr_t)p) & 15) == 0);
-    // all lanes of a warp iterate together (the bound is rounded up to a warp multiple)
-    const int64_t n4_pad = (n4 + 31) & ~(int64_t)31;
-    for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n4_pad; i += stride) {
+    const OvSizes z = ov_sizes(bounds, img, capacity, cap_true, cap_pred);
+    OvGlobal G{keys + img * capacity, counts + img * capacity, z.capacity, area_true + img * cap_true,
+               area_pred + img * cap_pred, z.n_true, z.n_pred, status + img};
+    for (int i = threadIdx.x; i < kOvSlots; i += kThreads) {
+        sk[i] = kEmpty;
+        sc[i] = 0;
+    }
+    if (threadIdx.x < 3) s_bg[threadIdx.x] = 0;
+    if (threadIdx.x < 2) s_max[threadIdx.x] = 0;
+    __syncthreads();
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t Y = n_px / X;
+    const int tx = blockIdx.x % tiles_x, ty = blockIdx.x / tiles_x;
+    const int64_t x = (int64_t)tx * kOvTile + lane * 4;
+    const int64_t y_end = min((int64_t)(ty + 1) * kOvTile, Y);
+    const bool vec_ok = ((((uintptr_t)t | (uintptr_t)p) & 15) == 0) && ((X & 3) == 0);
+    unsigned bg00 = 0;
+    int mt = 0, mp = 0;
+    for (int64_t y = (int64_t)ty * kOvTile + warp; y < y_end; y += kThreads / 32) {
         unsigned long long k[4];
         int cnt = 0;
-        if (i < n4) {
-            const int64_t b = i << 2;
+        if (x < X) {
+            const int64_t b = y * X + x;
             int32_t tv[4], pv[4];
-            if (vec_ok && b + 4 <= n_px) {
+            if (vec_ok && x + 4 <= X) {
                 const int4 a = __ldg(reinterpret_cast<const int4*>(t + b));
                 const int4 c = __ldg(reinterpret_cast<const int4*>(p + b));
                 tv[0] = a.x; tv[1] = a.y; tv[2] = a.z; tv[3] = a.w;
                 pv[0] = c.x; pv[1] = c.y; pv[2] = c.z; pv[3] = c.w;
                 cnt = 4;
             } else {
-                for (int j = 0; j < 4 && b + j < n_px; ++j) {
+                for (int j = 0; j < 4 && x + j < X; ++j) {
                     tv[j] = t[b + j];
                     pv[j] = p[b + j];
                     cnt = j + 1;
                 }
             }
             for (int j = 0; j < cnt; ++j) {
-                if ((tv[j] | pv[j]) < 0) *st = 2;
+                if ((tv[j] | pv[j]) < 0) {
+                    *G.st = 2;
+                    tv[j] = pv[j] = 0;
+                }
+                mt = max(mt, tv[j]);
+                mp = max(mp, pv[j]);
                 k[j] = ((unsigned long long)(unsigned)tv[j] << 32) | (unsigned)pv[j];
             }
         }
@@ -96,7 +214,8 @@ __global__ void __launch_bounds__(kThreads) overlap_kernel(const int32_t* __rest
             // run = consecutive uniform lanes up to the next start or the first non-uniform lane
             const unsigned stop = (starts | ~unif) & (lane == 31 ? 0u : (0xffffffffu << (lane + 1)));
             const int end = stop ? (__ffs(stop) - 1) : 32;
-            table_add(K, Cn, capacity, k0, 4u * (unsigned)(end - lane), st);
+            const unsigned c = 4u * (unsigned)(end - lane);
+            if (k0 == 0ull) bg00 += c; else ov_add(sk, sc, G, k0, c, &s_bg[2], &s_bg[1]);
         } else if (!uniform && cnt > 0) {
             unsigned long long cur = k[0];
             unsigned c = 1;
@@ -104,36 +223,37 @@ __global__ void __launch_bounds__(kThreads) overlap_kernel(const int32_t* __rest
                 if (k[j] == cur) {
                     ++c;
                 } else {
-                    table_add(K, Cn, capacity, cur, c, st);
+                    if (cur == 0ull) bg00 += c; else ov_add(sk, sc, G, cur, c, &s_bg[2], &s_bg[1]);
                     cur = k[j];
                     c = 1;
                 }
             }
-            table_add(K, Cn, capacity, cur, c, st);
+            if (cur == 0ull) bg00 += c; else ov_add(sk, sc, G, cur, c, &s_bg[2], &s_bg[1]);
         }
     }
-}
-
-__global__ void __launch_bounds__(kThreads) areas_kernel(const unsigned long long* __restrict__ keys,
-                                                         const unsigned* __restrict__ counts, int64_t capacity,
-                                                         int32_t* __restrict__ area_true, int64_t cap_true,
-                                                         int32_t* __restrict__ area_pred, int64_t cap_pred,
-                                                         int32_t* __restrict__ max_lbl, int32_t* __restrict__ status) {
-    const int64_t img = blockIdx.y;
-    const int64_t s = (int64_t)blockIdx.x * kThreads + threadIdx.x;
-    if (s >= capacity) return;
-    const unsigned long long k = keys[img * capacity + s];
-    if (k == kEmpty) return;
-    const unsigned c = counts[img * capacity + s];
-    const int64_t t = (int64_t)(k >> 32), p = (int64_t)(k & 0xffffffffull);
-    if (t >= cap_true || p >= cap_pred) {
-        status[img] = 2;
-        return;
+    bg00 = __reduce_add_sync(0xffffffffu, bg00);
+    mt = __reduce_max_sync(0xffffffffu, mt);
+    mp = __reduce_max_sync(0xffffffffu, mp);
+    if (lane == 0) {
+        if (bg00) atomicAdd(&s_bg[0], bg00);
+        if (mt) atomicMax(&s_max[0], mt);
+        if (mp) atomicMax(&s_max[1], mp);
     }
-    atomicAdd(&area_true[img * cap_true + t], (int)c);
-    atomicAdd(&area_pred[img * cap_pred + p], (int)c);
-    atomicMax(&max_lbl[img * 2 + 0], (int)t);
-    atomicMax(&max_lbl[img * 2 + 1], (int)p);
+    __syncthreads();
+    // the tile's pairs leave for the global structures: one area update per label and pair, one table update per pair
+    for (int i = threadIdx.x; i < kOvSlots; i += kThreads) {
+        const unsigned long long key = sk[i];
+        if (key != kEmpty) ov_global_add(G, key, sc[i], &s_bg[2], &s_bg[1]);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        // background row / column of the overlap matrix: area_true[0] = (0,0) + (0,p), area_pred[0] = (0,0) + (t,0)
+        const unsigned a0 = s_bg[0] + s_bg[2], b0 = s_bg[0] + s_bg[1];
+        if (a0) atomicAdd(&G.area_true[0], (int)a0);
+        if (b0) atomicAdd(&G.area_pred[0], (int)b0);
+        if (s_max[0]) atomicMax(&max_lbl[img * 2 + 0], s_max[0]);
+        if (s_max[1]) atomicMax(&max_lbl[img * 2 + 1], s_max[1]);
+    }
 }
 
 __global__ void __launch_bounds__(kThreads) match_kernel(const unsigned long long* __restrict__ keys,
@@ -143,29 +263,30 @@ __global__ void __launch_bounds__(kThreads) match_kernel(const unsigned long lon
                                                          const double* __restrict__ thr, int n_thr,
                                                          unsigned long long* __restrict__ out,
                                                          unsigned* __restrict__ bits, int64_t words_true,
-                                                         int64_t words_pred) {
+                                                         int64_t words_pred, const int32_t* __restrict__ bounds) {
     const int64_t img = blockIdx.y;
-    const int64_t s = (int64_t)blockIdx.x * kThreads + threadIdx.x;
-    if (s >= capacity) return;
-    const unsigned long long k = keys[img * capacity + s];
-    if (k == kEmpty) return;
-    const int64_t t = (int64_t)(k >> 32), p = (int64_t)(k & 0xffffffffull);
-    if (t == 0 || p == 0 || t >= cap_true || p >= cap_pred) return;
-    const unsigned c = counts[img * capacity + s];
-    const long long uni = (long long)area_true[img * cap_true + t] + (long long)area_pred[img * cap_pred + p] - (long long)c;
-    // the reference's comparison: fp64 quotient against the fp64 threshold
-    const double iou = __ddiv_rn((double)c, (double)uni);
-    for (int j = 0; j < n_thr; ++j) {
-        if (iou >= thr[j]) {
-            unsigned long long* o = out + (img * n_thr + j) * 2;
-            atomicAdd(&o[0], 1ull);
-            unsigned* bt = bits + (img * n_thr + j) * (words_true + words_pred);
-            unsigned* bp = bt + words_true;
-            const unsigned mt = 1u << (t & 31), mp = 1u << (p & 31);
-            unsigned extra = 0;
-            if (atomicOr(&bt[t >> 5], mt) & mt) ++extra;
-            if (atomicOr(&bp[p >> 5], mp) & mp) ++extra;
-            if (extra) atomicAdd(&o[1], (unsigned long long)extra);
+    const int64_t used = ov_sizes(bounds, img, capacity, cap_true, cap_pred).capacity;
+    for (int64_t s = (int64_t)blockIdx.x * kThreads + threadIdx.x; s < used; s += (int64_t)gridDim.x * kThreads) {
+        const unsigned long long k = keys[img * capacity + s];
+        if (k == kEmpty) continue;
+        const int64_t t = (int64_t)(k >> 32), p = (int64_t)(k & 0xffffffffull);
+        if (t == 0 || p == 0 || t >= cap_true || p >= cap_pred) continue;
+        const unsigned c = counts[img * capacity + s];
+        const long long uni = (long long)area_true[img * cap_true + t] + (long long)area_pred[img * cap_pred + p] - (long long)c;
+        // the reference's comparison: fp64 quotient against the fp64 threshold
+        const double iou = __ddiv_rn((double)c, (double)uni);
+        for (int j = 0; j < n_thr; ++j) {
+            if (iou >= thr[j]) {
+                unsigned long long* o = out + (img * n_thr + j) * 2;
+                atomicAdd(&o[0], 1ull);
+                unsigned* bt = bits + (img * n_thr + j) * (words_true + words_pred);
+                unsigned* bp = bt + words_true;
+                const unsigned mt = 1u << (t & 31), mp = 1u << (p & 31);
+                unsigned extra = 0;
+                if (atomicOr(&bt[t >> 5], mt) & mt) ++extra;
+                if (atomicOr(&bp[p >> 5], mp) & mp) ++extra;
+                if (extra) atomicAdd(&o[1], (unsigned long long)extra);
+            }
         }
     }
 }
@@ -341,9 +462,9 @@ inline bool is_pow2(int64_t v) { return v > 0 && (v & (v - 1)) == 0; }
 }  // namespace
 
 extern "C" int be_label_overlap_i32(const int32_t* lab_true, const int32_t* lab_pred, int64_t N, int64_t n_px,
-                                    uint64_t* keys, uint32_t* counts, int64_t capacity, int32_t* area_true,
-                                    int64_t cap_true, int32_t* area_pred, int64_t cap_pred, int32_t* max_lbl,
-                                    int32_t* status, be_stream_t stream) {
+                                    int64_t row_len, uint64_t* keys, uint32_t* counts, int64_t capacity,
+                                    int32_t* area_true, int64_t cap_true, int32_t* area_pred, int64_t cap_pred,
+                                    int32_t* max_lbl, int32_t* status, const int32_t* label_bounds, be_stream_t stream) {
     BE_REQUIRE(lab_true && lab_pred && keys && counts && area_true && area_pred && max_lbl && status, BE_ERR_INVALID_ARG,
                "be_label_overlap_i32: null pointer");
     BE_REQUIRE(N > 0 && n_px > 0, BE_ERR_INVALID_ARG, "be_label_overlap_i32: empty input");
@@ -352,22 +473,32 @@ extern "C" int be_label_overlap_i32(const int32_t* lab_true, const int32_t* lab_
     BE_REQUIRE(cap_true > 0 && cap_pred > 0, BE_ERR_INVALID_ARG, "be_label_overlap_i32: label capacities must be positive");
     BE_REQUIRE(N <= 65535, BE_ERR_TOO_LARGE, "be_label_overlap_i32: N %lld > 65535", (long long)N);
     BE_REQUIRE(n_px < ((int64_t)1 << 31), BE_ERR_TOO_LARGE, "be_label_overlap_i32: n_px >= 2^31");
+    BE_REQUIRE(row_len >= 0 && (row_len == 0 || n_px % row_len == 0), BE_ERR_INVALID_ARG,
+               "be_label_overlap_i32: row_len %lld does not divide n_px %lld", (long long)row_len, (long long)n_px);
     cudaStream_t s = (cudaStream_t)stream;
-    BE_CUDA(cudaMemsetAsync(keys, 0xff, sizeof(uint64_t) * N * capacity, s));
-    BE_CUDA(cudaMemsetAsync(counts, 0, sizeof(uint32_t) * N * capacity, s));
-    BE_CUDA(cudaMemsetAsync(area_true, 0, sizeof(int32_t) * N * cap_true, s));
-    BE_CUDA(cudaMemsetAsync(area_pred, 0, sizeof(int32_t) * N * cap_pred, s));
-    BE_CUDA(cudaMemsetAsync(max_lbl, 0, sizeof(int32_t) * N * 2, s));
-    BE_CUDA(cudaMemsetAsync(status, 0, sizeof(int32_t) * N, s));
-    const int64_t n4 = (n_px + 3) / 4;
-    int64_t gx = (n4 + kThreads - 1) / kThreads;
-    const int64_t cap_blocks = max((int64_t)1, (int64_t)BE_SM_COUNT * 16 / N);
-    if (gx > cap_blocks) gx = cap_blocks;
-    overlap_kernel<<<dim3((unsigned)gx, (unsigned)N), kThreads, 0, s>>>(
-        lab_true, lab_pred, n_px, (unsigned long long*)keys, counts, capacity, status);
-    BE_LAUNCH_CHECK();
-    areas_kernel<<<dim3((unsigned)((capacity + kThreads - 1) / kThreads), (unsigned)N), kThreads, 0, s>>>(
-        (const unsigned long long*)keys, counts, capacity, area_true, cap_true, area_pred, cap_pred, max_lbl, status);
+    // row_len 0 = no row structure known: rows of 128 px (the last one ragged), i.e. flat chunks of 16 K pixels per CTA
+    int64_t X = row_len > 0 ? row_len : kOvTile;
+    int64_t Y = (n_px + X - 1) / X;
+    if (row_len == 0 && n_px % X) {   // ragged tail: fall back to one long row per image
+        X = n_px;
+        Y = 1;
+    }
+    const int64_t tiles_x = (X + kOvTile - 1) / kOvTile, tiles_y = (Y + kOvTile - 1) / kOvTile;
+    BE_REQUIRE(tiles_x * tiles_y < ((int64_t)1 << 31), BE_ERR_TOO_LARGE, "be_label_overlap_i32: too many tiles");
+    {
+        int64_t most = capacity > cap_pred ? capacity : cap_pred;
+        if (cap_true > most) most = cap_true;
+        int64_t gx = (most + kThreads * 8 - 1) / (kThreads * 8);
+        const int64_t cap_blocks = max((int64_t)1, (int64_t)BE_SM_COUNT * 8 / N);
+        if (gx > cap_blocks) gx = cap_blocks;
+        overlap_init_kernel<<<dim3((unsigned)gx, (unsigned)N), kThreads, 0, s>>>(
+            (unsigned long long*)keys, counts, capacity, area_true, cap_true, area_pred, cap_pred, max_lbl, status,
+            label_bounds);
+        BE_LAUNCH_CHECK();
+    }
+    overlap_kernel<<<dim3((unsigned)(tiles_x * tiles_y), (unsigned)N), kThreads, 0, s>>>(
+        lab_true, lab_pred, n_px, X, (int)tiles_x, (unsigned long long*)keys, counts, capacity, area_true, cap_true,
+        area_pred, cap_pred, max_lbl, status, label_bounds);
     BE_LAUNCH_CHECK();
     return BE_OK;
 }
@@ -380,7 +511,8 @@ extern "C" size_t be_match_workspace_bytes(int64_t N, int64_t cap_true, int64_t 
 
 extern "C" int be_match_counts(const uint64_t* keys, const uint32_t* counts, int64_t N, int64_t capacity,
                                const int32_t* area_true, int64_t cap_true, const int32_t* area_pred, int64_t cap_pred,
-                               const double* thr, int n_thr, int64_t* counts_out, void* ws, be_stream_t stream) {
+                               const double* thr, int n_thr, int64_t* counts_out, void* ws, const int32_t* label_bounds,
+                               be_stream_t stream) {
     BE_REQUIRE(keys && counts && area_true && area_pred && thr && counts_out && ws, BE_ERR_INVALID_ARG,
                "be_match_counts: null pointer");
     BE_REQUIRE(N > 0 && is_pow2(capacity) && cap_true > 0 && cap_pred > 0, BE_ERR_INVALID_ARG,
@@ -391,9 +523,12 @@ extern "C" int be_match_counts(const uint64_t* keys, const uint32_t* counts, int
     const int64_t wt = (cap_true + 31) / 32, wp = (cap_pred + 31) / 32;
     BE_CUDA(cudaMemsetAsync(ws, 0, sizeof(uint32_t) * N * n_thr * (wt + wp), s));
     BE_CUDA(cudaMemsetAsync(counts_out, 0, sizeof(int64_t) * N * n_thr * 2, s));
-    match_kernel<<<dim3((unsigned)((capacity + kThreads - 1) / kThreads), (unsigned)N), kThreads, 0, s>>>(
+    int64_t gx = (capacity + kThreads - 1) / kThreads;
+    const int64_t most = max((int64_t)1, (int64_t)BE_SM_COUNT * 16 / N);   // the used part of a table is usually far shorter
+    if (gx > most) gx = most;
+    match_kernel<<<dim3((unsigned)gx, (unsigned)N), kThreads, 0, s>>>(
         (const unsigned long long*)keys, counts, capacity, area_true, cap_true, area_pred, cap_pred, thr, n_thr,
-        (unsigned long long*)counts_out, (unsigned*)ws, wt, wp);
+        (unsigned long long*)counts_out, (unsigned*)ws, wt, wp, label_bounds);
     BE_LAUNCH_CHECK();
     return BE_OK;
 }

@@ -275,15 +275,23 @@ def ccl(mask: torch.Tensor, connectivity: Optional[int] = None, ws: Workspace = 
 
 
 @_on_tensor_device
-def label_overlap(lab_true: torch.Tensor, lab_pred: torch.Tensor, capacity: int, cap_true: int, cap_pred: int):
-    """(N, ...) int32 label maps → dict of device tensors: keys, counts, area_true, area_pred, max_lbl, status."""
+def label_overlap(lab_true: torch.Tensor, lab_pred: torch.Tensor, capacity: int, cap_true: int, cap_pred: int,
+                  bounds: Optional[torch.Tensor] = None):
+    """(N, ...) int32 label maps → dict of device tensors: keys, counts (pairs with both labels > 0), area_true,
+    area_pred (background overlaps included), max_lbl, status.  `bounds`: optional int32 [N, 2] device tensor of per-image
+    upper bounds of the true / pred labels — only the part of the tables they need is cleared and used."""
     _check(lab_true, torch.int32, "lab_true")
     _check(lab_pred, torch.int32, "lab_pred")
     if lab_true.shape != lab_pred.shape:
         raise ValueError("label maps differ in shape")
     N = lab_true.shape[0]
     n_px = lab_true.numel() // N
+    row_len = lab_true.shape[-1] if lab_true.dim() >= 3 else 0
     dev = lab_true.device
+    if bounds is not None:
+        _check(bounds, torch.int32, "bounds")
+        if bounds.numel() != 2 * N:
+            raise ValueError("bounds must be [N, 2]")
     r = dict(
         keys=torch.empty((N, capacity), dtype=torch.int64, device=dev),
         counts=torch.empty((N, capacity), dtype=torch.int32, device=dev),
@@ -291,10 +299,11 @@ def label_overlap(lab_true: torch.Tensor, lab_pred: torch.Tensor, capacity: int,
         area_pred=torch.empty((N, cap_pred), dtype=torch.int32, device=dev),
         max_lbl=torch.empty((N, 2), dtype=torch.int32, device=dev),
         status=torch.empty((N,), dtype=torch.int32, device=dev),
+        bounds=bounds,
     )
-    _lib.call("be_label_overlap_i32", lab_true.data_ptr(), lab_pred.data_ptr(), N, n_px, r["keys"].data_ptr(),
+    _lib.call("be_label_overlap_i32", lab_true.data_ptr(), lab_pred.data_ptr(), N, n_px, row_len, r["keys"].data_ptr(),
               r["counts"].data_ptr(), capacity, r["area_true"].data_ptr(), cap_true, r["area_pred"].data_ptr(),
-              cap_pred, r["max_lbl"].data_ptr(), r["status"].data_ptr(), _stream())
+              cap_pred, r["max_lbl"].data_ptr(), r["status"].data_ptr(), _p(bounds), _stream())
     return r
 
 
@@ -309,7 +318,7 @@ def match_counts(table: dict, thr: torch.Tensor, ws: Workspace = _default_ws) ->
     w = ws.get(_lib.query("be_match_workspace_bytes", N, cap_true, cap_pred, n_thr), thr.device)
     _lib.call("be_match_counts", table["keys"].data_ptr(), table["counts"].data_ptr(), N, capacity,
               table["area_true"].data_ptr(), cap_true, table["area_pred"].data_ptr(), cap_pred, thr.data_ptr(), n_thr,
-              out.data_ptr(), w.data_ptr(), _stream())
+              out.data_ptr(), w.data_ptr(), _p(table.get("bounds")), _stream())
     return out
 
 

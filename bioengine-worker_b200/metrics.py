@@ -54,11 +54,13 @@ def _assignment_tp(table: dict, i: int, th: float) -> int:
     used = keys != np.uint64(0xFFFFFFFFFFFFFFFF)
     t = (keys[used] >> np.uint64(32)).astype(np.int64)
     p = (keys[used] & np.uint64(0xFFFFFFFF)).astype(np.int64)
-    nt, npred = int(t.max()) + 1, int(p.max()) + 1
-    overlap = np.zeros((nt, npred), np.float64)
+    ml = table["max_lbl"][i].cpu().numpy()
+    nt, npred = int(ml[0]) + 1, int(ml[1]) + 1
+    overlap = np.zeros((nt, npred), np.float64)   # the table holds the pairs with both labels > 0 ...
     overlap[t, p] = cnt[used]
-    n_pred = overlap.sum(0, keepdims=True)
-    n_true = overlap.sum(1, keepdims=True)
+    # ... and the areas are the row / column sums of the full matrix (background overlaps included)
+    n_true = table["area_true"][i].cpu().numpy()[:nt].astype(np.float64)[:, None]
+    n_pred = table["area_pred"][i].cpu().numpy()[:npred].astype(np.float64)[None, :]
     with np.errstate(invalid="ignore", divide="ignore"):
         iou = overlap / (n_pred + n_true - overlap)
     iou[np.isnan(iou)] = 0.0

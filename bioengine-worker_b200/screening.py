@@ -61,7 +61,9 @@ class ShardScreener:
 
     `cap_true` = largest ground-truth label + 1 over the shard (host knowledge); `cap_pred` = how many predicted
     components per image the tables are sized for (default: min(the geometric bound, max(4096, pixels / 32)) + 1).  If an
-    image exceeds it the sticky flag reports 2 and the caller reruns with the geometric bound."""
+    image exceeds it the sticky flag reports 2 and the caller reruns with the geometric bound.  The tables are allocated
+    for these capacities but cleared and scanned only as far as each image's own label counts require (the kernels take
+    the counts from device memory)."""
 
     def __init__(self, spatial: Sequence[int], n_thr: int, cap_true: int, cap_pred: Optional[int] = None,
                  connectivity: Optional[int] = None, device="cuda:0", eps: float = 1e-6):
@@ -87,14 +89,19 @@ class ShardScreener:
         return K.normalize(x, norm)
 
     def score(self, logits: torch.Tensor, gt: torch.Tensor, thr: torch.Tensor, rows: torch.Tensor,
-              table_model: torch.Tensor) -> None:
+              table_model: torch.Tensor, gt_max: Optional[torch.Tensor] = None) -> None:
         """logits (B, 1, *spatial) fp32 of one model → sigmoid + binarize 0.5 (one pass, mask only) → labels → overlap
         table vs gt → pair counts → rows of `table_model` at image indices `rows`.  Nothing returns to the host."""
         B = logits.shape[0]
         shape = (B, 1) + self.spatial
         _, mask = K.stitch_crop(logits, shape, self.axes, _lib.BE_EPI_SIGMOID, 0.5, want_out=False, want_mask=True)
-        labels, _ = K.ccl(mask.reshape((B,) + self.spatial), self.connectivity, ws=self.ws)
-        tab = K.label_overlap(gt, labels, self.capacity, self.cap_true, self.cap_pred)
+        labels, n_lab = K.ccl(mask.reshape((B,) + self.spatial), self.connectivity, ws=self.ws)
+        if gt_max is not None:
+            # table sizes follow each image's label counts (known on the device only): bounds[i] = {max gt label, n_lab}
+            bounds = torch.stack((gt_max, n_lab), dim=1).contiguous()
+        else:
+            bounds = None
+        tab = K.label_overlap(gt, labels, self.capacity, self.cap_true, self.cap_pred, bounds=bounds)
         counts = K.match_counts(tab, thr, ws=self.ws)
         K.screen_rows(counts, tab, thr, rows, table_model, self.flags)
 
@@ -129,9 +136,10 @@ def screen_models(models: Sequence[Callable[[torch.Tensor], torch.Tensor]], imag
             x = torch.from_numpy(np.stack([np.asarray(images[i], np.float32) for i in idx])[:, None]).to(dev, non_blocking=True)
             gt = torch.from_numpy(np.stack([np.asarray(gt_labels[i], np.int32) for i in idx])).to(dev, non_blocking=True)
             rows = torch.tensor(idx, dtype=torch.int64).to(dev, non_blocking=True)
+            gt_max = torch.tensor([int(np.asarray(gt_labels[i]).max()) for i in idx], dtype=torch.int32).to(dev, non_blocking=True)
             xn = scr.normalise(x)
             for m, model in enumerate(models):
-                scr.score(model(xn).contiguous(), gt, thr, rows, table[m])
+                scr.score(model(xn).contiguous(), gt, thr, rows, table[m], gt_max)
         state = scr.check()   # the shard's only device → host read before the merge
         if state & 3 == 2 and scr.cap_pred < max_components(spatial, connectivity) + 1:
             # more predicted components than the tables were sized for: once more with the geometric bound

@@ -154,16 +154,23 @@ int be_ccl_u8_i32(const uint8_t* mask, int32_t* labels, int64_t N, int64_t Z, in
 /* Sparse label-pair overlap histogram of N (true, pred) label-map pairs of n_px pixels each — the
  * `_label_overlap` / `_intersection_over_union` step of cellpose.metrics.average_precision
  * (apps/cellpose-finetuning/main.py:2002; Appendix B.1).  Per image an open-addressing table of
- * `capacity` (power of two) slots: keys[slot] = (true << 32) | pred, or ~0 if empty; counts[slot] = #pixels.
- * Also fills the per-label pixel counts (row / column sums of the overlap matrix, background included) and
- * the max labels.  All outputs are (re)initialised by the call.
+ * `capacity` (power of two) slots holding the pairs with BOTH labels > 0 (the only ones that can match):
+ * keys[slot] = (true << 32) | pred, or ~0 if empty; counts[slot] = #pixels.  The per-label pixel counts (row / column
+ * sums of the overlap matrix, overlaps with the background included; index 0 = the background's own row / column sum)
+ * and the max labels are filled as well.  All outputs are (re)initialised by the call.
+ *   row_len   pixels per image row (n_px % row_len == 0): work is cut into 128 x 128 px tiles; 0 = unknown
  *   keys      [N * capacity] uint64 out     counts [N * capacity] uint32 out
  *   area_true [N * cap_true], area_pred [N * cap_pred] int32 out (index = label)
  *   max_lbl   [N * 2] int32 out {max true, max pred}
- *   status    [N] int32 out: 0 ok, 1 table full (retry with a larger capacity), 2 label negative or >= cap */
-int be_label_overlap_i32(const int32_t* lab_true, const int32_t* lab_pred, int64_t N, int64_t n_px, uint64_t* keys,
-                         uint32_t* counts, int64_t capacity, int32_t* area_true, int64_t cap_true, int32_t* area_pred,
-                         int64_t cap_pred, int32_t* max_lbl, int32_t* status, be_stream_t stream);
+ *   status    [N] int32 out: 0 ok, 1 table full (retry with a larger capacity), 2 label negative or >= cap
+ *   label_bounds  NULL, or [N * 2] int32 on the device: per image an upper bound of the true / pred labels (e.g. the
+ *                 n_labels be_ccl_u8_i32 wrote).  Then only the part of the tables those bounds need is cleared and used
+ *                 (pair table: the power of two >= 4 (bt + bp) + 64, at most `capacity`); a label above its bound gives
+ *                 status 2.  be_match_counts must be given the same bounds. */
+int be_label_overlap_i32(const int32_t* lab_true, const int32_t* lab_pred, int64_t N, int64_t n_px, int64_t row_len,
+                         uint64_t* keys, uint32_t* counts, int64_t capacity, int32_t* area_true, int64_t cap_true,
+                         int32_t* area_pred, int64_t cap_pred, int32_t* max_lbl, int32_t* status,
+                         const int32_t* label_bounds, be_stream_t stream);
 
 /* Threshold matching on the sparse table: for every image and threshold, the number of (true, pred) pairs
  * (both > 0) with (double)ov / (double)(a_t + a_p - ov) >= thr, and `extra` = the number of times a label
@@ -171,11 +178,13 @@ int be_label_overlap_i32(const int32_t* lab_true, const int32_t* lab_pred, int64
  * replaces the Hungarian assignment in cellpose `_true_positive`); for thr < 0.5 a non-zero `extra` means the
  * caller must solve the assignment for that image.
  *   thr        [n_thr] fp64, device          counts_out [N * n_thr * 2] int64 out {pairs, extra}
- *   ws         be_match_workspace_bytes(N, cap_true, cap_pred, n_thr) bytes */
+ *   ws         be_match_workspace_bytes(N, cap_true, cap_pred, n_thr) bytes
+ *   label_bounds  as given to be_label_overlap_i32 (NULL if none) */
 size_t be_match_workspace_bytes(int64_t N, int64_t cap_true, int64_t cap_pred, int n_thr);
 int be_match_counts(const uint64_t* keys, const uint32_t* counts, int64_t N, int64_t capacity,
                     const int32_t* area_true, int64_t cap_true, const int32_t* area_pred, int64_t cap_pred,
-                    const double* thr, int n_thr, int64_t* counts_out, void* ws, be_stream_t stream);
+                    const double* thr, int n_thr, int64_t* counts_out, void* ws, const int32_t* label_bounds,
+                    be_stream_t stream);
 
 /* Rows of the screening table for one batch of images and one model, written on the device: for image i of the batch,
  * table[rows[i]*(n_thr+2) + k] = tp at threshold k (= pairs - extra of be_match_counts), then n_true, n_pred

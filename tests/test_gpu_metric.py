@@ -40,10 +40,57 @@ def test_overlap_table_equals_dense_histogram(dev, rng):
     for i, (lt, lp) in enumerate(pairs):
         want = O.label_overlap(lt, lp)
         got = dense_overlap(tab, i, want.shape[0], want.shape[1])
-        assert np.array_equal(got, want)
+        assert np.array_equal(got[1:, 1:], want[1:, 1:])     # the table holds the pairs with both labels > 0 ...
+        assert not got[0].any() and not got[:, 0].any()      # ... the background row / column lives in the areas
         assert np.array_equal(tab["area_true"][i].cpu().numpy()[: want.shape[0]], want.sum(1).astype(np.int32))
         assert np.array_equal(tab["area_pred"][i].cpu().numpy()[: want.shape[1]], want.sum(0).astype(np.int32))
         assert tab["max_lbl"][i].cpu().tolist() == [lt.max(), lp.max()]
+
+
+@pytest.mark.parametrize("shape", [(256, 320), (131, 257), (7, 1000), (300, 5)])
+def test_overlap_with_device_bounds_ragged_shapes_and_flat_input(dev, rng, shape):
+    """Per-image label bounds on the device cut the tables to what each image needs (the rest stays uninitialised and
+    must never be read); rows that are not multiples of 4 / 128; the same pixels handed over without row structure."""
+    from bioengine_worker_b200.metrics import counts_to_tp
+
+    pairs = [make_pair(rng, shape=shape, n_blobs=12 + 9 * s, seed=10 + s) for s in range(3)]
+    t = torch.from_numpy(np.stack([p[0] for p in pairs])).to(dev)
+    p = torch.from_numpy(np.stack([p[1] for p in pairs])).to(dev)
+    bounds = torch.tensor([[int(a.max()), int(b.max())] for a, b in pairs], dtype=torch.int32, device=dev)
+    thr = torch.tensor([0.5, 0.75, 0.9], dtype=torch.float64, device=dev)
+    want_tp = O.average_precision([a for a, _ in pairs], [b for _, b in pairs])[1]
+    for tt, pp, bb in ((t, p, bounds), (t, p, None), (t.reshape(3, -1), p.reshape(3, -1), bounds)):
+        tab = K().label_overlap(tt, pp, capacity=1 << 15, cap_true=2048, cap_pred=8192, bounds=bb)
+        assert tab["status"].cpu().tolist() == [0, 0, 0]
+        c = K().match_counts(tab, thr).cpu().numpy()
+        assert np.array_equal(counts_to_tp(c, [0.5, 0.75, 0.9]), want_tp.astype(np.int64))
+        for i, (lt, lp) in enumerate(pairs):
+            want = O.label_overlap(lt, lp)
+            assert np.array_equal(tab["area_true"][i].cpu().numpy()[: want.shape[0]], want.sum(1).astype(np.int32))
+            assert np.array_equal(tab["area_pred"][i].cpu().numpy()[: want.shape[1]], want.sum(0).astype(np.int32))
+            assert tab["max_lbl"][i].cpu().tolist() == [lt.max(), lp.max()]
+    # a bound that is too small is reported, not overrun
+    low = bounds.clone()
+    low[1, 1] = 1
+    st = K().label_overlap(t, p, capacity=1 << 15, cap_true=2048, cap_pred=8192, bounds=low)["status"].cpu().tolist()
+    assert st[1] == 2 and st[0] == 0 and st[2] == 0
+
+
+def test_overlap_crowded_tiles_bypass_the_shared_table(dev, rng):
+    """Every pixel its own label on both sides: a 128 x 128 tile holds 16 K distinct pairs, far more than the CTA's
+    shared-memory table, so most pairs take the direct path to the global table."""
+    H, W = 200, 260
+    lt = (np.arange(H * W, dtype=np.int32).reshape(H, W) % 5000) + 1
+    lp = rng.permutation(H * W).astype(np.int32).reshape(H, W) % 7000 + 1
+    lp[::3] = 0
+    t, p = torch.from_numpy(lt[None]).to(dev), torch.from_numpy(lp[None]).to(dev)
+    tab = K().label_overlap(t, p, capacity=1 << 18, cap_true=5001, cap_pred=7001)
+    assert tab["status"].item() == 0
+    want = O.label_overlap(lt, lp)
+    got = dense_overlap(tab, 0, want.shape[0], want.shape[1])
+    assert np.array_equal(got[1:, 1:], want[1:, 1:])
+    assert np.array_equal(tab["area_true"][0].cpu().numpy(), want.sum(1).astype(np.int32))
+    assert np.array_equal(tab["area_pred"][0].cpu().numpy(), want.sum(0).astype(np.int32))
 
 
 def test_overlap_table_overflow_and_range_are_reported(dev, rng):
