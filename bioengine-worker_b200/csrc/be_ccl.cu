@@ -1,8 +1,10 @@
 // Connected-component labelling with raster-order numbering (scipy.ndimage.label / skimage.measure.label).
 //
-// Pipeline (all int/bit work, HBM-bound):
-//   1. ccl_tile_kernel      one CTA per 64x64 (2-D) / 64x8x8 (3-D) tile.  Rows become 64-bit masks (16-byte loads +
-//                           byte->bit multiply trick, or warp ballots at ragged edges).  The union-find nodes are the
+// Four launches, chained by programmatic dependent launch (all int/bit work, HBM-bound):
+//   1. ccl_tile_kernel<IN>  one CTA per 64x64 (2-D) / 64x8x8 (3-D) tile.  Rows become 64-bit masks — from a uint8 mask
+//                           (16-byte loads + byte->bit multiply trick, or warp ballots at ragged edges), from a
+//                           bit-packed mask (one word per row: what the blend stitcher can emit), or straight from fp32
+//                           logits with the sigmoid / threshold decided here.  The union-find nodes are the
 //                           RUNS of a row (<= 32 per row, 2048 per tile, parents in shared memory): x-links cost
 //                           nothing, and rows are linked with bit arithmetic that leaves exactly one lane per touching
 //                           run pair to issue the union (atomicMin, path halving).  After a per-run flatten every run
@@ -11,15 +13,22 @@
 //                           without a foreground pixel are not written at all.  Tile roots are flagged in a
 //                           1-bit-per-pixel bitmap, the mask itself is kept bit-packed, and the tile's four edge
 //                           masks are kept for step 2.
-//   2. ccl_edge_kernel      (2-D) one warp per tile links its top and left edge to the neighbouring tiles from the edge
-//                           masks alone, one union per touching run pair, a lane's (up to 12) unions issued as a batch;
+//   2. ccl_edge_kernel      (2-D) four warps per tile link its top and left edge to the neighbouring tiles from the edge
+//                           masks alone, one union per touching run pair, a lane's (up to 3) unions issued as a batch;
 //                           ccl_face3d_kernel (3-D) does the same per 64-voxel row word of the bit-packed mask, four
-//                           threads per word (one per predecessor row), each issuing its unions one after the other.  Unions are atomicMin on the global parent array with path halving.
+//                           threads per word (one per predecessor row).  Unions are atomicMin on the global parent array
+//                           with path halving.
 //   3. ccl_number_kernel    surviving roots are numbered in raster order from the root bitmap (2 MB instead of a
-//                           second pass over all parents) with a single-pass decoupled look-back scan (128 predecessors
-//                           per step); a root's entry becomes -(id) - 1.
+//                           second pass over all parents) with a single-pass decoupled look-back scan (blocks take their
+//                           256 words by ticket; 128 predecessors per step); a root's entry becomes -(id) - 1.
 //   4. ccl_resolve_kernel   driven by the packed mask: a foreground pixel walks to its root (<= 2-3 hops) and writes
 //                           the id, background is written as 0 without touching the parent array.
+// (Tried and dropped, with numbers in profiles/README.md: border unions inside the tile launch — by the last neighbour to
+// finish, or by ticketed edge blocks behind the tiles — numbering + resolving in one ticketed launch, and flattening the
+// merged tile roots while numbering so that the resolve needs no walk.  The fences and flags hold a CTA's slot for a
+// memory round trip per tile, blocks that spin for a number crowd out the blocks that produce it, and the flattening
+// costs the numbering more than it saves the resolve; four plain launches, chained so that launch latency is hidden,
+// are faster.)
 #include "be_common.cuh"
 
 namespace {
@@ -119,9 +128,20 @@ __device__ __forceinline__ void link_run(unsigned* parent, unsigned id, int x, i
     }
 }
 
-__global__ void __launch_bounds__(kThreads) ccl_tile_kernel(const uint8_t* __restrict__ mask, int32_t* __restrict__ L,
-                                                            u64* __restrict__ rootbits, u64* __restrict__ bitvol,
-                                                            TileEdges* __restrict__ edges, Geom g) {
+// what the tile kernel reads its rows from
+constexpr int kInU8 = 0, kInBits = 1, kInF32 = 2;
+
+// Programmatic dependent launch: the four kernels of a call are chained so that a kernel's blocks are placed as the
+// previous kernel drains and its launch latency is off the critical path.  pdl_wait() returns once the previous kernel
+// has completed and its writes are visible; everything before it may only touch what that kernel does not write.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+template <int IN>
+__global__ void __launch_bounds__(kThreads, 8) ccl_tile_kernel(const void* __restrict__ input, Epilogue epi,
+                                                            int32_t* __restrict__ L, u64* __restrict__ rootbits,
+                                                            u64* __restrict__ bitvol, TileEdges* __restrict__ edges,
+                                                            Geom g) {
     __shared__ u64 rmask[kRows];
     __shared__ u64 rstart[kRows];
     __shared__ __align__(16) unsigned parent[kMaxRuns];   // union-find over run ids (row * 32 + index in row)
@@ -135,13 +155,56 @@ __global__ void __launch_bounds__(kThreads) ccl_tile_kernel(const uint8_t* __res
     const int bid = (tz * g.tiles_y + ty) * g.tiles_x + tx;
     const int64_t x0 = (int64_t)tx * kTX, y0 = (int64_t)ty << g.ty_log2, z0 = (int64_t)tz * (kRows >> g.ty_log2);
     const int64_t vol = g.Z * g.Y * g.X;
-    const uint8_t* im = mask + (int64_t)img * vol;
     int32_t* Li = L + (int64_t)img * vol;
     __shared__ u64 rroot[kRows];
     if (threadIdx.x < kRows) rroot[threadIdx.x] = 0;
 
     // ---- A: rows -> bit masks ----
-    if ((g.X & 15) == 0 && x0 + kTX <= g.X && (((uintptr_t)im) & 15) == 0) {
+    if (IN == kInBits) {
+        // one word per row, laid out like bitvol: [image][z*Y + y][tile column]
+        if (threadIdx.x < kRows) {
+            const int r = threadIdx.x;
+            const int64_t z = z0 + (r >> g.ty_log2), y = y0 + (r & ty_mask);
+            u64 v = 0;
+            if (z < g.Z && y < g.Y) {
+                v = __ldg(reinterpret_cast<const u64*>(input) + ((int64_t)img * g.Z * g.Y + z * g.Y + y) * g.tiles_x + tx);
+                if (x0 + kTX > g.X) v &= (1ull << (g.X - x0)) - 1ull;   // bits past the row end do not count
+            }
+            rmask[r] = v;
+            rstart[r] = v & ~(v << 1);
+        }
+    } else if (IN == kInF32) {
+        // 16 lanes x 4 logits per row, two rows per warp instruction; the mask bit is decided here (sigmoid / threshold)
+        const float* im = reinterpret_cast<const float*>(input) + (int64_t)img * vol;
+        const int lane16 = lane & 15, sub = lane >> 4;
+        const bool vec_ok = ((g.X & 3) == 0) && ((((uintptr_t)im) & 15) == 0);
+#pragma unroll
+        for (int it = 0; it < 4; ++it) {
+            const int r = warp * 8 + it * 2 + sub;
+            const int64_t z = z0 + (r >> g.ty_log2), y = y0 + (r & ty_mask);
+            const int64_t x = x0 + lane16 * 4;
+            unsigned m4 = 0;
+            if (z < g.Z && y < g.Y && x < g.X) {
+                const float* src = im + (z * g.Y + y) * g.X + x;
+                if (vec_ok && x + 4 <= g.X) {
+                    const float4 q = ld_stream_f4(reinterpret_cast<const float4*>(src));
+                    m4 = (unsigned)be_epilogue_mask(q.x, epi) | ((unsigned)be_epilogue_mask(q.y, epi) << 1) |
+                         ((unsigned)be_epilogue_mask(q.z, epi) << 2) | ((unsigned)be_epilogue_mask(q.w, epi) << 3);
+                } else {
+                    for (int j = 0; j < 4 && x + j < g.X; ++j) m4 |= (unsigned)be_epilogue_mask(src[j], epi) << j;
+                }
+            }
+            u64 v = (u64)m4 << (4 * lane16);
+#pragma unroll
+            for (int o = 1; o < 16; o <<= 1) v |= __shfl_xor_sync(0xffffffffu, v, o);
+            if (lane16 == 0) {
+                rmask[r] = v;
+                rstart[r] = v & ~(v << 1);
+            }
+        }
+    } else if ((g.X & 15) == 0 && x0 + kTX <= g.X &&
+               (((uintptr_t)(reinterpret_cast<const uint8_t*>(input) + (int64_t)img * vol)) & 15) == 0) {
+        const uint8_t* im = reinterpret_cast<const uint8_t*>(input) + (int64_t)img * vol;
         // 4 lanes x 16 bytes per row, 8 rows per warp: one load instruction per warp
         const int r = warp * 8 + (lane >> 2), part = lane & 3;
         const int64_t z = z0 + (r >> g.ty_log2), y = y0 + (r & ty_mask);
@@ -158,6 +221,7 @@ __global__ void __launch_bounds__(kThreads) ccl_tile_kernel(const uint8_t* __res
             rstart[r] = v & ~(v << 1);
         }
     } else {
+        const uint8_t* im = reinterpret_cast<const uint8_t*>(input) + (int64_t)img * vol;
         for (int r = warp; r < kRows; r += kThreads / 32) {
             const int64_t z = z0 + (r >> g.ty_log2), y = y0 + (r & ty_mask);
             const bool row_ok = (z < g.Z) && (y < g.Y);
@@ -291,7 +355,7 @@ __global__ void __launch_bounds__(kThreads) ccl_tile_kernel(const uint8_t* __res
             if (z < g.Z && y < g.Y) {
                 const int64_t wi = ((int64_t)img * g.Z * g.Y + z * g.Y + y) * wpr + tx;
                 rootbits[wi] = rroot[r];
-                bitvol[wi] = rmask[r];  // the mask, 1 bit per voxel: 3-D face links, and the resolve pass
+                if (IN != kInBits || (g.X & (kTX - 1))) bitvol[wi] = rmask[r];  // the mask, 1 bit per voxel (3-D face links, the resolve pass); a bit-packed input with whole-word rows is used in place, one with ragged rows is copied with the tails cleaned
             }
         }
     }
@@ -308,6 +372,7 @@ __global__ void __launch_bounds__(kThreads) ccl_tile_kernel(const uint8_t* __res
             edges[(int64_t)img * (g.tiles_x * g.tiles_y * g.tiles_z) + bid] = e;
         }
     }
+    pdl_launch_dependents();
 }
 
 // ---- global union-find on the parent array ----
@@ -397,6 +462,7 @@ __device__ __forceinline__ void unite_batch(int32_t* Li, EdgeBatch& q) {
 // work is spread over as many lanes as there are edge pixels.
 __global__ void __launch_bounds__(kThreads) ccl_edge_kernel(int32_t* __restrict__ L, const TileEdges* __restrict__ edges,
                                                             Geom g, int tiles_per_image) {
+    pdl_wait();   // the tile kernel's parents and edge masks
     const int wg = blockIdx.x * (kThreads / 32) + (threadIdx.x >> 5);
     const int t = wg >> 2, part = wg & 3;
     if (t >= tiles_per_image) return;
@@ -452,6 +518,7 @@ __global__ void __launch_bounds__(kThreads) ccl_face3d_kernel(int32_t* __restric
     if (w >= words_per_image) return;
     const int wpr = g.tiles_x;
     const u64* B = bitvol + (int64_t)blockIdx.y * words_per_image;
+    pdl_wait();   // the tile kernel's parents and packed mask
     const u64 m = B[w];
     if (!m) return;
     int32_t* Li = L + (int64_t)blockIdx.y * g.Z * g.Y * g.X;
@@ -489,13 +556,20 @@ __global__ void __launch_bounds__(kThreads) ccl_face3d_kernel(int32_t* __restric
     }
 }
 
-// ---- raster-order numbering of the surviving roots, driven by the root bitmap: one pass ----
-//
-// Every thread takes one 64-pixel bitmap word.  Tile roots that are still their own parent after the border unions
-// are the components.  The running count across blocks is a decoupled look-back scan: blocks take tickets in launch order,
-// publish their aggregate, and add up the predecessors' values until they meet a published inclusive prefix.  A
-// numbered root's entry becomes -(id) - 1.
+// ---- raster-order numbering of the surviving roots + resolve, one launch (see the file header) ----
 constexpr unsigned long long kFlagAggregate = 1ull << 62, kFlagPrefix = 2ull << 62, kFlagMask = 3ull << 62;
+
+__device__ __forceinline__ int32_t resolve_one(const int32_t* __restrict__ Li, int32_t v) {
+    // roots hold -(id) - 1; a pixel is normally one or two hops from its root
+    if (v >= 0) {
+        v = __ldg(Li + v);
+        if (v >= 0) {
+            v = __ldg(Li + v);
+            while (v >= 0) v = __ldg(Li + v);
+        }
+    }
+    return -v - 1;
+}
 
 __global__ void __launch_bounds__(kThreads) ccl_number_kernel(int32_t* __restrict__ L, const u64* __restrict__ rootbits,
                                                               int64_t vol, int64_t X, int wpr, int64_t words_per_image,
@@ -506,20 +580,20 @@ __global__ void __launch_bounds__(kThreads) ccl_number_kernel(int32_t* __restric
     __shared__ unsigned s_ticket;
     __shared__ long long s_excl;
     const int img = blockIdx.y;
+    // blocks take their part of the bitmap by ticket, i.e. in starting order: a block only ever waits for blocks with
+    // smaller tickets, which are running already
     if (threadIdx.x == 0) s_ticket = atomicAdd(&tickets[img], 1u);
     __syncthreads();
     const int blk = (int)s_ticket;
     int32_t* Li = L + (int64_t)img * vol;
-    volatile int32_t* Lv = Li;
     const int64_t w = (int64_t)blk * kWordsPerBlock + threadIdx.x;
+    pdl_wait();   // the border unions
     u64 keep = 0;
     int64_t base = 0;
     if (w < words_per_image) {
         u64 bits = rootbits[(int64_t)img * words_per_image + w];
         base = (w / wpr) * X + (w % wpr) * kTX;
-        // still a root after the border unions?  Four candidates per round, their loads issued together: a block
-        // publishes its count only when its slowest thread is through, and one dependent load per root bit made that
-        // several round trips for the words with many tile roots
+        // still a root after the border unions?  Four candidates per round, their loads issued together
         while (bits) {
             int b[4];
             int32_t pv[4];
@@ -595,20 +669,9 @@ __global__ void __launch_bounds__(kThreads) ccl_number_kernel(int32_t* __restric
     while (keep) {
         const int b = __ffsll((long long)keep) - 1;
         keep &= keep - 1;
-        Lv[base + b] = -(++id) - 1;
+        __stcg(Li + base + b, -(++id) - 1);
     }
-}
-
-__device__ __forceinline__ int32_t resolve_one(const int32_t* __restrict__ Li, int32_t v) {
-    // background (-1) and roots are already terminal; a pixel is normally one or two hops from its root
-    if (v >= 0) {
-        v = __ldg(Li + v);
-        if (v >= 0) {
-            v = __ldg(Li + v);
-            while (v >= 0) v = __ldg(Li + v);
-        }
-    }
-    return -v - 1;
+    pdl_launch_dependents();
 }
 
 // grid: x = row (z * Y + y), y = blocks of 8-px units along the row, z = image.  The packed mask says which pixels have a
@@ -621,6 +684,7 @@ __global__ void __launch_bounds__(kThreads) ccl_resolve_kernel(const int32_t* __
     if (u >= units_per_row) return;
     const int64_t row = blockIdx.x;
     const int x = u * 8;
+    pdl_wait();   // the numbering (and, through it, everything before)
     const u64 word = __ldg(bitvol + (int64_t)blockIdx.z * words_per_image + row * wpr + (x >> 6));
     const unsigned bits = (unsigned)(word >> (x & 63)) & 0xffu;
     const int32_t* Li = L + (int64_t)blockIdx.z * vol;
@@ -631,14 +695,14 @@ __global__ void __launch_bounds__(kThreads) ccl_resolve_kernel(const int32_t* __
     if (bits) {
         if (vec) {
             int4 a = make_int4(-1, -1, -1, -1), b = a;
-            if (bits & 0x0fu) a = __ldg(reinterpret_cast<const int4*>(Li + base));
-            if (bits & 0xf0u) b = __ldg(reinterpret_cast<const int4*>(Li + base) + 1);
+            if (bits & 0x0fu) a = __ldcg(reinterpret_cast<const int4*>(Li + base));
+            if (bits & 0xf0u) b = __ldcg(reinterpret_cast<const int4*>(Li + base) + 1);
             p[0] = a.x, p[1] = a.y, p[2] = a.z, p[3] = a.w, p[4] = b.x, p[5] = b.y, p[6] = b.z, p[7] = b.w;
         } else {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) p[j] = ((bits >> j) & 1u) ? __ldg(Li + base + j) : -1;
+            for (int j = 0; j < 8; ++j) p[j] = ((bits >> j) & 1u) ? __ldcg(Li + base + j) : -1;
         }
-        int32_t prev_p = -1, prev_v = 0;   // neighbouring pixels usually share their parent: look it up once
+        int32_t prev_p = 0x7fffffff, prev_v = 0;   // neighbouring pixels usually share their parent: look it up once
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
             if ((bits >> j) & 1u) {
@@ -651,8 +715,8 @@ __global__ void __launch_bounds__(kThreads) ccl_resolve_kernel(const int32_t* __
         }
     }
     if (vec) {
-        reinterpret_cast<int4*>(o)[0] = make_int4(v[0], v[1], v[2], v[3]);
-        reinterpret_cast<int4*>(o)[1] = make_int4(v[4], v[5], v[6], v[7]);
+        __stcs(reinterpret_cast<int4*>(o), make_int4(v[0], v[1], v[2], v[3]));
+        __stcs(reinterpret_cast<int4*>(o) + 1, make_int4(v[4], v[5], v[6], v[7]));
     } else {
 #pragma unroll
         for (int j = 0; j < 8; ++j)
@@ -708,17 +772,17 @@ extern "C" size_t be_ccl_workspace_bytes(int64_t N, int64_t Z, int64_t Y, int64_
     return carve_ccl_ws(nullptr, N, Z, Y, X).total_bytes;
 }
 
-extern "C" int be_ccl_u8_i32(const uint8_t* mask, int32_t* labels, int64_t N, int64_t Z, int64_t Y, int64_t X,
-                             int connectivity, int32_t* n_labels, void* ws, be_stream_t stream) {
-    BE_REQUIRE(mask && labels && n_labels && ws, BE_ERR_INVALID_ARG, "be_ccl_u8_i32: null pointer");
-    BE_REQUIRE(N > 0 && Z > 0 && Y > 0 && X > 0, BE_ERR_INVALID_ARG, "be_ccl_u8_i32: empty input (%lld,%lld,%lld,%lld)",
+static int ccl_run(const char* who, int in_kind, const void* input, Epilogue epi, int32_t* labels, int64_t N, int64_t Z,
+                   int64_t Y, int64_t X, int connectivity, int32_t* n_labels, void* ws, be_stream_t stream) {
+    BE_REQUIRE(input && labels && n_labels && ws, BE_ERR_INVALID_ARG, "%s: null pointer", who);
+    BE_REQUIRE(N > 0 && Z > 0 && Y > 0 && X > 0, BE_ERR_INVALID_ARG, "%s: empty input (%lld,%lld,%lld,%lld)", who,
                (long long)N, (long long)Z, (long long)Y, (long long)X);
     const int ndim = (Z > 1) ? 3 : 2;
-    BE_REQUIRE(connectivity >= 1 && connectivity <= ndim, BE_ERR_INVALID_ARG,
-               "be_ccl_u8_i32: connectivity %d not in 1..%d", connectivity, ndim);
+    BE_REQUIRE(connectivity >= 1 && connectivity <= ndim, BE_ERR_INVALID_ARG, "%s: connectivity %d not in 1..%d", who,
+               connectivity, ndim);
     const int64_t vol = Z * Y * X;
-    BE_REQUIRE(vol < ((int64_t)1 << 31) - 2, BE_ERR_TOO_LARGE, "be_ccl_u8_i32: %lld voxels per image >= 2^31", (long long)vol);
-    BE_REQUIRE(N <= 65535, BE_ERR_TOO_LARGE, "be_ccl_u8_i32: N %lld > 65535", (long long)N);
+    BE_REQUIRE(vol < ((int64_t)1 << 31) - 2, BE_ERR_TOO_LARGE, "%s: %lld voxels per image >= 2^31", who, (long long)vol);
+    BE_REQUIRE(N <= 65535, BE_ERR_TOO_LARGE, "%s: N %lld > 65535", who, (long long)N);
     Geom g;
     g.Z = Z;
     g.Y = Y;
@@ -730,35 +794,71 @@ extern "C" int be_ccl_u8_i32(const uint8_t* mask, int32_t* labels, int64_t N, in
     g.tiles_z = (int)((Z + TZ - 1) / TZ);
     g.conn = connectivity;
     const int64_t n_tiles = (int64_t)g.tiles_x * g.tiles_y * g.tiles_z;
-    BE_REQUIRE(n_tiles < ((int64_t)1 << 31) - 1, BE_ERR_TOO_LARGE, "be_ccl_u8_i32: too many tiles");
+    BE_REQUIRE(n_tiles < ((int64_t)1 << 31) - 1, BE_ERR_TOO_LARGE, "%s: too many tiles", who);
     cudaStream_t s = (cudaStream_t)stream;
     const CclWorkspace w = carve_ccl_ws(ws, N, Z, Y, X);
 
+    BE_CUDA(cudaMemsetAsync(w.tickets, 0, w.scan_bytes, s));
     BE_REQUIRE(g.tiles_y <= 65535 && (int64_t)g.tiles_z * N <= 65535, BE_ERR_TOO_LARGE,
-               "be_ccl_u8_i32: tile grid (%d, %d, %lld) exceeds the launch limits", g.tiles_x, g.tiles_y,
-               (long long)g.tiles_z * N);
-    ccl_tile_kernel<<<dim3((unsigned)g.tiles_x, (unsigned)g.tiles_y, (unsigned)(g.tiles_z * N)), kThreads, 0, s>>>(
-        mask, w.L, w.rootbits, w.bitvol, ndim == 2 ? w.edges : nullptr, g);
+               "%s: tile grid (%d, %d, %lld) exceeds the launch limits", who, g.tiles_x, g.tiles_y, (long long)g.tiles_z * N);
+    const dim3 grid((unsigned)g.tiles_x, (unsigned)g.tiles_y, (unsigned)(g.tiles_z * N));
+    TileEdges* edges = ndim == 2 ? w.edges : nullptr;
+    // a bit-packed input whose rows are whole words is used in place of the workspace copy of the mask
+    const u64* bitvol = (in_kind == kInBits && (X % kTX) == 0) ? (const u64*)input : w.bitvol;
+    if (in_kind == kInBits)
+        ccl_tile_kernel<kInBits><<<grid, kThreads, 0, s>>>(input, epi, w.L, w.rootbits, w.bitvol, edges, g);
+    else if (in_kind == kInF32)
+        ccl_tile_kernel<kInF32><<<grid, kThreads, 0, s>>>(input, epi, w.L, w.rootbits, w.bitvol, edges, g);
+    else
+        ccl_tile_kernel<kInU8><<<grid, kThreads, 0, s>>>(input, epi, w.L, w.rootbits, w.bitvol, edges, g);
     BE_LAUNCH_CHECK();
+    // the following kernels are chained to their predecessor with programmatic stream serialization (see pdl_wait)
+    cudaLaunchAttribute pdl[1];
+    pdl[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    pdl[0].val.programmaticStreamSerializationAllowed = 1;
+    cudaLaunchConfig_t cfg = {};
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = s;
+    cfg.attrs = pdl;
+    cfg.numAttrs = 1;
     if (ndim == 2) {
         if (n_tiles > 1) {
-            const unsigned gx = (unsigned)((4 * n_tiles + kThreads / 32 - 1) / (kThreads / 32));   // four warps per tile
-            ccl_edge_kernel<<<dim3(gx, (unsigned)N), kThreads, 0, s>>>(w.L, w.edges, g, (int)n_tiles);
-            BE_LAUNCH_CHECK();
+            cfg.gridDim = dim3((unsigned)((4 * n_tiles + kThreads / 32 - 1) / (kThreads / 32)), (unsigned)N);   // four warps per tile
+            BE_CUDA(cudaLaunchKernelEx(&cfg, ccl_edge_kernel, w.L, (const TileEdges*)w.edges, g, (int)n_tiles));
         }
     } else {
-        ccl_face3d_kernel<<<dim3((unsigned)((4 * w.words_per_image + kThreads - 1) / kThreads), (unsigned)N), kThreads, 0, s>>>(
-            w.L, w.bitvol, g, w.words_per_image);
-        BE_LAUNCH_CHECK();
+        cfg.gridDim = dim3((unsigned)((4 * w.words_per_image + kThreads - 1) / kThreads), (unsigned)N);
+        BE_CUDA(cudaLaunchKernelEx(&cfg, ccl_face3d_kernel, w.L, bitvol, g, w.words_per_image));
     }
-    BE_CUDA(cudaMemsetAsync(w.tickets, 0, w.scan_bytes, s));
-    ccl_number_kernel<<<dim3(w.blocks_per_image, (unsigned)N), kThreads, 0, s>>>(
-        w.L, w.rootbits, vol, X, g.tiles_x, w.words_per_image, w.blocks_per_image, w.tickets, w.block_state, n_labels);
-    BE_LAUNCH_CHECK();
+    cfg.gridDim = dim3((unsigned)w.blocks_per_image, (unsigned)N);
+    BE_CUDA(cudaLaunchKernelEx(&cfg, ccl_number_kernel, w.L, (const u64*)w.rootbits, vol, X, g.tiles_x, w.words_per_image,
+                               w.blocks_per_image, w.tickets, w.block_state, n_labels));
     const int upr = (int)((X + 7) / 8);
-    BE_REQUIRE((upr + kThreads - 1) / kThreads <= 65535, BE_ERR_TOO_LARGE, "be_ccl_u8_i32: X %lld too long", (long long)X);
-    ccl_resolve_kernel<<<dim3((unsigned)(Z * Y), (unsigned)((upr + kThreads - 1) / kThreads), (unsigned)N), kThreads, 0, s>>>(
-        w.L, w.bitvol, labels, vol, (int)X, g.tiles_x, w.words_per_image, upr);
-    BE_LAUNCH_CHECK();
+    BE_REQUIRE((upr + kThreads - 1) / kThreads <= 65535 && N <= 65535, BE_ERR_TOO_LARGE, "%s: X %lld too long", who, (long long)X);
+    cfg.gridDim = dim3((unsigned)(Z * Y), (unsigned)((upr + kThreads - 1) / kThreads), (unsigned)N);
+    BE_CUDA(cudaLaunchKernelEx(&cfg, ccl_resolve_kernel, (const int32_t*)w.L, bitvol, labels, vol, (int)X, g.tiles_x,
+                               w.words_per_image, upr));
     return BE_OK;
+}
+
+extern "C" int be_ccl_u8_i32(const uint8_t* mask, int32_t* labels, int64_t N, int64_t Z, int64_t Y, int64_t X,
+                             int connectivity, int32_t* n_labels, void* ws, be_stream_t stream) {
+    return ccl_run("be_ccl_u8_i32", kInU8, mask, make_epilogue(BE_EPI_NONE, 0.5f, false), labels, N, Z, Y, X, connectivity,
+                   n_labels, ws, stream);
+}
+
+extern "C" int be_ccl_bits_i32(const uint64_t* bits, int32_t* labels, int64_t N, int64_t Z, int64_t Y, int64_t X,
+                               int connectivity, int32_t* n_labels, void* ws, be_stream_t stream) {
+    BE_REQUIRE((((uintptr_t)bits) & 7) == 0, BE_ERR_INVALID_ARG, "be_ccl_bits_i32: bits must be 8-byte aligned");
+    return ccl_run("be_ccl_bits_i32", kInBits, bits, make_epilogue(BE_EPI_NONE, 0.5f, false), labels, N, Z, Y, X,
+                   connectivity, n_labels, ws, stream);
+}
+
+extern "C" int be_ccl_f32_i32(const float* x, int epilogue, float thr, int32_t* labels, int64_t N, int64_t Z, int64_t Y,
+                              int64_t X, int connectivity, int32_t* n_labels, void* ws, be_stream_t stream) {
+    BE_REQUIRE(epilogue == BE_EPI_NONE || epilogue == BE_EPI_SIGMOID, BE_ERR_INVALID_ARG, "be_ccl_f32_i32: epilogue %d",
+               epilogue);
+    return ccl_run("be_ccl_f32_i32", kInF32, x, make_epilogue(epilogue, thr, true), labels, N, Z, Y, X, connectivity,
+                   n_labels, ws, stream);
 }

@@ -1,6 +1,7 @@
 // Shared helpers for the be_b200 kernels (sm_100a only).
 #pragma once
 #include <cuda_runtime.h>
+#include <math.h>
 #include <stdint.h>
 #include <stdio.h>
 
@@ -79,6 +80,47 @@ __device__ __forceinline__ float be_numpy_expf(float x) {
 // bioimageio `sigmoid` on an fp32 tensor: 1 / (1 + np.exp(-x)), every step rounded to fp32 as numpy does.
 __device__ __forceinline__ float be_sigmoid_f32(float x) {
     return __fdiv_rn(1.0f, __fadd_rn(1.0f, be_numpy_expf(-x)));
+}
+
+// Post-processing fused into the stitchers.  `fast` (mask-only sigmoid): the decision sigmoid(v) > thr is v > logit(thr)
+// for every v farther than a safety margin from logit(thr) — [lo, hi] is that margin band, computed by the host; only
+// values inside the band (a vanishing fraction) take the exact numpy-fp32 sigmoid.
+struct Epilogue {
+    int mode;   // BE_EPI_*
+    int fast;   // mask only: 1 = sigmoid decided by the band test around logit(thr), 2 = no sigmoid, band around thr itself
+    float thr, lo, hi;
+    double lo2, hi2;  // the same band, a little wider, for the division-free test acc <> wacc * bound (row-walking blend)
+};
+
+// Host side of the band test: sigmoid'(x) = s(1-s) >= 0.0099 for thr in [0.01, 0.99], so 1e-4 away from logit(thr) the
+// true sigmoid is >= 9.9e-7 away from thr, while the fp32 evaluation is good to a few ulp (<= 2.4e-7 near 1).
+static inline Epilogue make_epilogue(int mode, float thr, bool mask_only) {
+    Epilogue e{mode, 0, thr, 0.f, 0.f, 0.0, 0.0};
+    if (mode == BE_EPI_SIGMOID && mask_only && thr >= 0.01f && thr <= 0.99f) {
+        const double L = log((double)thr / (1.0 - (double)thr));
+        e.fast = 1;
+        e.lo = (float)(L - 1e-4);
+        e.hi = (float)(L + 1e-4);
+        // acc > wacc * hi2 (wacc > 0) puts the exact quotient above hi * (1 + 2^-21) >= the next float after hi, and
+        // rounding is monotone, so float(acc / wacc) > hi; the absolute 2^-100 covers hi == 0.  Same for lo2.
+        e.hi2 = (double)e.hi + fabs((double)e.hi) * 0x1p-20 + 0x1p-100;
+        e.lo2 = (double)e.lo - fabs((double)e.lo) * 0x1p-20 - 0x1p-100;
+    } else if (mode == BE_EPI_NONE && mask_only && thr == thr && fabs((double)thr) < 1e30) {
+        // float(q) > thr: a quotient above thr * (1 + 2^-22) rounds to at least the next float after thr, one below
+        // thr * (1 - 2^-22) to at most thr (rounding is monotone); the absolute term covers thr == 0 and subnormals
+        e.fast = 2;
+        e.lo = e.hi = thr;
+        e.hi2 = (double)thr + fabs((double)thr) * 0x1p-22 + 0x1p-140;
+        e.lo2 = (double)thr - fabs((double)thr) * 0x1p-22 - 0x1p-140;
+    }
+    return e;
+}
+
+// value > thr after the optional sigmoid: the mask the stitchers and the labelling kernel derive from a logit
+__device__ __forceinline__ bool be_epilogue_mask(float v, const Epilogue& e) {
+    if (e.fast == 1) return (v > e.hi) || (!(v < e.lo) && be_sigmoid_f32(v) > e.thr);
+    if (e.mode == BE_EPI_SIGMOID) v = be_sigmoid_f32(v);
+    return v > e.thr;
 }
 
 // (float)(n / d) with the fp64 quotient correctly rounded first — what numpy does when an fp64 expression is cast to

@@ -302,22 +302,24 @@ __global__ void __launch_bounds__(kCopyThreads, 3) tile_gather_tma_kernel(const 
 // stitch: shared epilogue
 // ---------------------------------------------------------------------------------------------------
 
-// Post-processing fused into the stitchers.  `fast` (mask-only sigmoid): the decision sigmoid(v) > thr is v > logit(thr)
-// for every v farther than a safety margin from logit(thr) — [lo, hi] is that margin band, computed by the host; only
-// values inside the band (a vanishing fraction) take the exact numpy-fp32 sigmoid.
-struct Epilogue {
-    int mode;   // BE_EPI_*
-    int fast;   // 1: mask only, sigmoid decided by the band test
-    float thr, lo, hi;
-    double lo2, hi2;  // the same band, a little wider, for the division-free test acc <> wacc * bound (row-walking blend)
-};
+// Packed mask: a row is ceil(X / 64) 64-bit words, lowest bit = first pixel; written as 32-bit pieces.  Called by every
+// lane of a warp whose lanes own consecutive 4-px units of one row starting at a multiple of 128 px (x0 = the lane's
+// first pixel, also for lanes past the end of the row, which pass m4 = 0 so that the last word's tail is clean).
+__device__ __forceinline__ void store_mask_bits(uint32_t* __restrict__ row32, int x0, unsigned m4, int pieces_per_row) {
+    unsigned c = m4 << (4 * (threadIdx.x & 7));
+    c |= __shfl_xor_sync(0xffffffffu, c, 1);
+    c |= __shfl_xor_sync(0xffffffffu, c, 2);
+    c |= __shfl_xor_sync(0xffffffffu, c, 4);
+    if ((threadIdx.x & 7) == 0 && (x0 >> 5) < pieces_per_row) row32[x0 >> 5] = c;
+}
 
-__device__ __forceinline__ void finish4(float* __restrict__ out, uint8_t* __restrict__ mask, int64_t o, int cnt,
-                                        float v[4], const Epilogue& e, bool aligned) {
+// returns the four mask bits
+__device__ __forceinline__ unsigned finish4(float* __restrict__ out, uint8_t* __restrict__ mask, int64_t o, int cnt,
+                                            float v[4], const Epilogue& e, bool aligned) {
     bool m[4];
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-        if (e.fast) {
+        if (e.fast == 1) {
             m[j] = (v[j] > e.hi) || (!(v[j] < e.lo) && be_sigmoid_f32(v[j]) > e.thr);
         } else {
             if (e.mode == BE_EPI_SIGMOID) v[j] = be_sigmoid_f32(v[j]);
@@ -333,6 +335,10 @@ __device__ __forceinline__ void finish4(float* __restrict__ out, uint8_t* __rest
             if (mask) mask[o + j] = m[j];
         }
     }
+    unsigned m4 = 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) m4 |= (j < cnt && m[j]) ? (1u << j) : 0u;
+    return m4;
 }
 
 // grid: x = 4-px units along the row, y = output row y, z = (n, c, z) planes (grid-strided)
@@ -343,14 +349,13 @@ struct RowIndex {
 
 __device__ __forceinline__ bool row_index(const Dims& d, int units_per_row, unsigned plane, RowIndex* r) {
     r->u = blockIdx.x * kThreads + threadIdx.x;
-    if (r->u >= units_per_row) return false;
     r->y = blockIdx.y;
     r->z = plane % (unsigned)d.Z;
     const unsigned nc = plane / (unsigned)d.Z;
     r->c = nc % (unsigned)d.C;
     r->n = nc / (unsigned)d.C;
     r->row = (int64_t)plane * d.Y + r->y;
-    return true;
+    return r->u < units_per_row;
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -358,14 +363,19 @@ __device__ __forceinline__ bool row_index(const Dims& d, int units_per_row, unsi
 // ---------------------------------------------------------------------------------------------------
 
 __global__ void __launch_bounds__(kThreads) stitch_crop_kernel(const float* __restrict__ tiles, float* __restrict__ out,
-                                                               uint8_t* __restrict__ mask, Dims d,
-                                                               const int32_t* __restrict__ zsel,
+                                                               uint8_t* __restrict__ mask, uint32_t* __restrict__ bits32,
+                                                               Dims d, const int32_t* __restrict__ zsel,
                                                                const int32_t* __restrict__ ysel,
                                                                const int32_t* __restrict__ xsel, Epilogue e,
                                                                int units_per_row, unsigned n_planes) {
+    const int pieces = 2 * (int)((d.X + 63) / 64);
     for (unsigned plane = blockIdx.z; plane < n_planes; plane += gridDim.z) {
         RowIndex r;
-        if (!row_index(d, units_per_row, plane, &r)) return;
+        const bool live = row_index(d, units_per_row, plane, &r);
+        if (!live) {   // past the end of the row: only the packed mask wants this lane (with a clean tail)
+            if (bits32) store_mask_bits(bits32 + r.row * pieces, r.u * 4, 0u, pieces);
+            continue;
+        }
         const int vz = zsel[r.z], vy = ysel[r.y];
         const int kz = vz / d.Bz, iz = vz - kz * d.Bz;
         const int ky = vy / d.By, iy = vy - ky * d.By;
@@ -384,7 +394,8 @@ __global__ void __launch_bounds__(kThreads) stitch_crop_kernel(const float* __re
                 v[j] = __ldg(tiles + (trow + kx) * d.C * tvol + in_tile + ix);
             }
         }
-        finish4(out, mask, r.row * d.X + x0, cnt, v, e, (d.X & 3) == 0);
+        const unsigned m4 = finish4(out, mask, r.row * d.X + x0, cnt, v, e, (d.X & 3) == 0);
+        if (bits32) store_mask_bits(bits32 + r.row * pieces, x0, m4, pieces);
     }
 }
 
@@ -406,7 +417,8 @@ __device__ __forceinline__ void cover(int p, int B, int S, float rS, int T, int*
 }
 
 __global__ void __launch_bounds__(kThreads) stitch_blend_kernel(const float* __restrict__ tiles, float* __restrict__ out,
-                                                                uint8_t* __restrict__ mask, Dims d, Strides s,
+                                                                uint8_t* __restrict__ mask, uint32_t* __restrict__ bits32,
+                                                                Dims d, Strides s,
                                                                 const double* __restrict__ wz,
                                                                 const double* __restrict__ wy,
                                                                 const double* __restrict__ wx, Epilogue e,
@@ -485,7 +497,13 @@ __global__ void __launch_bounds__(kThreads) stitch_blend_kernel(const float* __r
         float v[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j) v[j] = be_div_to_f32(acc[j], wacc[j], be_fast_rcp(wacc[j]));
-        if (live) finish4(out, mask, ((int64_t)plane * d.Y + y) * d.X + x0, cnt, v, e, (d.X & 3) == 0);
+        unsigned m4 = 0;
+        if (live) m4 = finish4(out, mask, ((int64_t)plane * d.Y + y) * d.X + x0, cnt, v, e, (d.X & 3) == 0);
+        if (bits32) {
+            const int pieces = 2 * (int)((d.X + 63) / 64);
+            store_mask_bits(bits32 + ((int64_t)plane * d.Y + y) * pieces, (int)(blockIdx.x * kThreads + threadIdx.x) * 4, m4,
+                            pieces);
+        }
     }
 }
 
@@ -494,6 +512,9 @@ __global__ void __launch_bounds__(kThreads) stitch_blend_kernel(const float* __r
 static __device__ __noinline__ bool blend_decide_exact(double acc, double wacc, float lo, float hi, float thr) {
     const float v = be_div_to_f32(acc, wacc, be_fast_rcp(wacc));
     return (v > hi) || (!(v < lo) && be_sigmoid_f32(v) > thr);
+}
+static __device__ __noinline__ bool blend_decide_exact_plain(double acc, double wacc, float thr) {
+    return be_div_to_f32(acc, wacc, be_fast_rcp(wacc)) > thr;
 }
 
 // Row-walking variant for the usual geometry (Bx <= 2*Sx, By <= 2*Sy; Sx, Bx, X multiples of 4; 16-byte aligned
@@ -560,7 +581,8 @@ constexpr int kRowsThreads = kCopyThreads;
 
 template <bool FAST>
 __global__ void __launch_bounds__(kRowsThreads, 3) stitch_blend_rows_kernel(const float* __restrict__ tiles, float* __restrict__ out,
-                                                                        uint8_t* __restrict__ mask, const Dims d,
+                                                                        uint8_t* __restrict__ mask, uint32_t* __restrict__ bits32,
+                                                                        const Dims d,
                                                                         const Strides s, const double* __restrict__ wz,
                                                                         const double* __restrict__ wy,
                                                                         const double* __restrict__ wx, const Epilogue e,
@@ -735,6 +757,7 @@ __global__ void __launch_bounds__(kRowsThreads, 3) stitch_blend_rows_kernel(cons
                 continue;
             }
             // last kz of this row group: finish the four pixels, move to the next group
+            unsigned m4 = 0;
             if (live) {
                 if (FAST) {
                     // m = acc/wacc above the band <=> dlt > 0 (sign bit clear; dlt == 0 is inside the band).  The test
@@ -752,18 +775,23 @@ __global__ void __launch_bounds__(kRowsThreads, 3) stitch_blend_rows_kernel(cons
 #pragma unroll
                         for (int j = 0; j < 4; ++j)
                             if (slow & (1u << j)) {
-                                const bool m = blend_decide_exact(acc[j], wacc[j], e.lo, e.hi, e.thr);
+                                const bool m = (e.fast == 2) ? blend_decide_exact_plain(acc[j], wacc[j], e.thr)
+                                                             : blend_decide_exact(acc[j], wacc[j], e.lo, e.hi, e.thr);
                                 bits = (bits & ~(0xffu << (8 * j))) | ((m ? 1u : 0u) << (8 * j));
                             }
                     }
-                    *reinterpret_cast<unsigned*>(mrow) = bits;
+                    if (mrow) *reinterpret_cast<unsigned*>(mrow) = bits;
+                    m4 = (bits & 1u) | ((bits >> 7) & 2u) | ((bits >> 14) & 4u) | ((bits >> 21) & 8u);
                 } else {
                     float v[4];
 #pragma unroll
                     for (int j = 0; j < 4; ++j) v[j] = be_div_to_f32(acc[j], wacc[j], be_fast_rcp(wacc[j]));
-                    finish4(orow, mrow, 0, 4, v, e, true);
+                    m4 = finish4(orow, mrow, 0, 4, v, e, true);
                 }
             }
+            if (bits32 && y < y_end)   // warp-uniform: a warp's lanes share their row
+                store_mask_bits(bits32 + ((int64_t)plane * d.Y + y) * (2 * (int)((d.X + 63) / 64)),
+                                ((blockIdx.x << log2_bx) + tx) * 4, m4, 2 * (int)((d.X + 63) / 64));
 #pragma unroll
             for (int j = 0; j < 4; ++j) acc[j] = wacc[j] = 0.0;
             kk = 0;
@@ -771,7 +799,7 @@ __global__ void __launch_bounds__(kRowsThreads, 3) stitch_blend_rows_kernel(cons
             y += r_step;
             iy += r_step;
             if (FAST) {
-                mrow += k.dout;
+                if (mrow) mrow += k.dout;
             } else {
                 if (mrow) mrow += k.dout;
                 if (orow) orow += k.dout;
@@ -789,21 +817,234 @@ __global__ void __launch_bounds__(kRowsThreads, 3) stitch_blend_rows_kernel(cons
     }
 }
 
-// Host side of the band test: sigmoid'(x) = s(1-s) >= 0.0099 for thr in [0.01, 0.99], so 1e-4 away from logit(thr) the
-// true sigmoid is >= 9.9e-7 away from thr, while the fp32 evaluation is good to a few ulp (<= 2.4e-7 near 1).
-Epilogue make_epilogue(int mode, float thr, bool mask_only) {
-    Epilogue e{mode, 0, thr, 0.f, 0.f, 0.0, 0.0};
-    if (mode == BE_EPI_SIGMOID && mask_only && thr >= 0.01f && thr <= 0.99f) {
-        const double L = log((double)thr / (1.0 - (double)thr));
-        e.fast = 1;
-        e.lo = (float)(L - 1e-4);
-        e.hi = (float)(L + 1e-4);
-        // acc > wacc * hi2 (wacc > 0) puts the exact quotient above hi * (1 + 2^-21) >= the next float after hi, and
-        // rounding is monotone, so float(acc / wacc) > hi; the absolute 2^-100 covers hi == 0.  Same for lo2.
-        e.hi2 = (double)e.hi + fabs((double)e.hi) * 0x1p-20 + 0x1p-100;
-        e.lo2 = (double)e.lo - fabs((double)e.lo) * 0x1p-20 - 0x1p-100;
+// ---------------------------------------------------------------------------------------------------
+// 2-D, mask only: fp32 interval filter
+// ---------------------------------------------------------------------------------------------------
+//
+// When only the mask of a 2-D blend is wanted (sigmoid -> binarize, or a plain threshold on the blended value) the exact
+// quotient matters for the few pixels next to the threshold only.  This kernel walks rows like the one above, but
+//   * the window is what the reference holds in memory, the fp32 table w[iy][ix] = fp32(wy[iy] * wx[ix]): the copy warp
+//     writes the row(s) of it that a step needs next to the tile rows it fetches (Bx products per row instead of eight
+//     per thread), so the arithmetic warps read pixel and weight with two 16-byte shared loads;
+//   * a pixel's sums are taken in fp32: A = sum fp32(p * w) (the products are the reference's own fp32 numbers),
+//     W = sum w, S = sum |p * w|.  With at most four terms |A - A_exact| <= 3u S and |W - W_exact| <= 3u W (u = 2^-24), so
+//     d = A - W * mid misses the exact A_exact - W_exact * mid by well under 2^-20 (S + W |mid| + |d|), and a pixel with
+//     |d| > W * half + 2^-20 (S + W |mid| + |d|) lies outside the band [mid - half, mid + half] on the side sign(d)
+//     shows — the same band the fp64 test of the kernel above uses.  No fp64 instruction and no conversion is issued;
+//   * the pixels that fail the test (about one in 10^4) are redone from the same shared-memory values in the
+//     reference's arithmetic (fp64 sums of the fp32 products in ascending tile order, exact quotient, numpy's sigmoid)
+//     before the stage is released.
+// The mask leaves bit-packed (one 32-bit piece per eight lanes) and / or as bytes.
+struct Mask2dConst {
+    int64_t dky;             // element step in the tile buffer: next tile along y (same in-tile column, row - Sy)
+    float mid, abs_mid, half_up;
+    int log2_bx, units_per_row;
+    unsigned n_bands, n_items;
+    int seg_slot_bytes;      // tile-row segments of one (row, ky slot): nseg * Bx * 4
+    int slot_bytes;          // seg_slot_bytes + Bx * 4 (the window row behind the segments)
+    int stage_bytes;         // r_step rows x 2 ky slots
+    int pieces;              // 32-bit pieces per row of the packed mask
+};
+
+constexpr int kMaskStages = 3;   // 3 x 16 KB stages at the 4096^2 / 256-px geometry: four blocks per SM
+
+__global__ void __launch_bounds__(kRowsThreads, 4) stitch_blend_mask2d_kernel(const float* __restrict__ tiles,
+                                                                              uint8_t* __restrict__ mask,
+                                                                              uint32_t* __restrict__ bits32, const Dims d,
+                                                                              const Strides s, const double* __restrict__ wz,
+                                                                              const double* __restrict__ wy,
+                                                                              const double* __restrict__ wx, const Epilogue e,
+                                                                              const Mask2dConst k) {
+    extern __shared__ __align__(128) unsigned char s_dyn[];
+    __shared__ __align__(8) unsigned long long s_bar[2 * kMaskStages];   // full[kMaskStages], empty[kMaskStages]
+    const int tid = threadIdx.x;
+    const int log2_bx = k.log2_bx;
+    const int tx = tid & ((1 << log2_bx) - 1), ty = tid >> log2_bx;
+    const int r_step = kThreads >> log2_bx;
+    const int u_raw = (blockIdx.x << log2_bx) + tx;
+    const bool x_live = u_raw < k.units_per_row;
+    const int x0 = min(u_raw, k.units_per_row - 1) * 4;
+    const int X0 = (blockIdx.x << log2_bx) * 4, X1 = min((int)d.X, X0 + (4 << log2_bx));   // the block's x range
+    int seg_first, seg_last;
+    cover(X0, d.Bx, s.Sx, s.rSx, d.Tx, &seg_first, &seg_last);
+    seg_last = min(d.Tx - 1, be_fast_div(X1 - 1, s.Sx, s.rSx));
+    const int seg_bytes = d.Bx * 4;
+    const unsigned smem0 = (unsigned)__cvta_generic_to_shared(s_dyn);
+    const unsigned bar0 = (unsigned)__cvta_generic_to_shared(s_bar);
+
+    int kxa, kxb;
+    cover(x0, d.Bx, s.Sx, s.rSx, d.Tx, &kxa, &kxb);
+    const bool two = kxb > kxa;
+    const int ixa = x0 - kxa * s.Sx, ixb = x0 - kxb * s.Sx;
+    // byte offsets inside a (row, ky slot): this thread's pixels in the first / second x tile, and their weights
+    const int pa = (ty * 2) * k.slot_bytes + (kxa - seg_first) * seg_bytes + ixa * 4;
+    const int pb = pa + (kxb - kxa) * seg_bytes + (ixb - ixa) * 4;
+    const int wa = (ty * 2) * k.slot_bytes + k.seg_slot_bytes + ixa * 4;
+    const int wb = wa + (ixb - ixa) * 4;
+
+    const bool producer = tid >= kThreads;
+    const int lane = tid & 31;
+    int seg_src = 0, seg_dst = 0, seg_len = 0;   // element offset in the tile row, byte offset in the slot, bytes
+    if (producer) {
+        const int kx = seg_first + lane;
+        if (kx <= seg_last) {
+            const int xs = max(kx * s.Sx, X0), xe = min(kx * s.Sx + d.Bx, X1);
+            seg_src = xs - kx * s.Sx;
+            seg_dst = lane * seg_bytes + seg_src * 4;
+            seg_len = (xe - xs) * 4;
+        }
     }
-    return e;
+    int row_bytes = seg_len;   // bytes one (row, ky slot) brings in by bulk copy
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) row_bytes += __shfl_xor_sync(0xffffffffu, row_bytes, o);
+    // the copy warp keeps the x window (fp64) in shared memory behind the stages
+    double* wx_s = reinterpret_cast<double*>(s_dyn + kMaskStages * k.stage_bytes);
+    for (int i = tid; i < d.Bx; i += kRowsThreads) wx_s[i] = wx[i];
+
+    if (tid == 0) {
+#pragma unroll
+        for (int i = 0; i < kMaskStages; ++i) {
+            mbar_init(bar0 + 8 * i, 1);                           // full: the copy warp's expect_tx arrival + the bytes
+            mbar_init(bar0 + 8 * (kMaskStages + i), kThreads / 32);   // empty: one arrival per arithmetic warp
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    unsigned use = 0;
+    const double wz0 = wz[0];
+
+    for (unsigned item = blockIdx.y; item < k.n_items; item += gridDim.y) {
+        const unsigned plane = item / k.n_bands, band = item - plane * k.n_bands;
+        const int band_begin = (int)(((int64_t)band * d.Y) / k.n_bands);
+        const int y_end = (int)(((int64_t)(band + 1) * d.Y) / k.n_bands);
+        const int total = (y_end - band_begin + r_step - 1) / r_step;
+        const unsigned c = plane % (unsigned)d.C;
+        const int64_t n = plane / (unsigned)d.C;
+        // tile (n, ky = 0, kx = seg_first + lane), channel c, row 0, first element this lane copies
+        const float* lane_base = tiles + (n * d.Ty * d.Tx + seg_first + lane) * s.tile_stride + (int64_t)c * d.By * d.Bx + seg_src;
+
+        if (producer) {
+            for (int g = 0; g < total; ++g, ++use) {
+                const unsigned st = use % kMaskStages;
+                const unsigned full = bar0 + 8 * st, empty = bar0 + 8 * (kMaskStages + st);
+                mbar_wait(empty, ((use / kMaskStages) & 1) ^ 1);   // all arithmetic warps are done with this stage
+                int slots = 0;
+                for (int r = 0; r < r_step; ++r) {
+                    const int y = band_begin + g * r_step + r;
+                    if (y >= y_end) break;
+                    RowCover rc;
+                    rc.set(y, d, s);
+                    slots += rc.nky;
+                    // window rows of this output row: fp32(fp64(wz0 * wy[iy]) * wx[ix]) for the one or two tiles along y
+                    for (int q = 0; q < rc.nky; ++q) {
+                        const double wzy = __dmul_rn(wz0, wy[y - (rc.ky_lo + q) * s.Sy]);
+                        float* wrow = reinterpret_cast<float*>(s_dyn + st * k.stage_bytes + (r * 2 + q) * k.slot_bytes +
+                                                               k.seg_slot_bytes);
+                        for (int i = lane; i < d.Bx; i += 32) wrow[i] = (float)__dmul_rn(wzy, wx_s[i]);
+                    }
+                }
+                __syncwarp();   // every lane's window values are written before lane 0's arrival publishes the stage
+                if (lane == 0) {
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic accesses before async writes
+                    mbar_expect_tx(full, (unsigned)(slots * row_bytes));
+                }
+                __syncwarp();
+                if (seg_len > 0) {
+                    for (int r = 0; r < r_step; ++r) {
+                        const int y = band_begin + g * r_step + r;
+                        if (y >= y_end) break;
+                        RowCover rc;
+                        rc.set(y, d, s);
+                        const float* src = lane_base + (int64_t)rc.ky_lo * d.Tx * s.tile_stride + (int64_t)(y - rc.ky_lo * s.Sy) * d.Bx;
+                        const unsigned dst = smem0 + st * k.stage_bytes + (r * 2) * k.slot_bytes + seg_dst;
+                        bulk_g2s(dst, src, (unsigned)seg_len, full);
+                        if (rc.nky > 1) bulk_g2s(dst + k.slot_bytes, src + k.dky, (unsigned)seg_len, full);
+                    }
+                }
+            }
+            continue;
+        }
+        // arithmetic warps
+        int y = band_begin + ty;
+        RowCover rc;
+        rc.set(min(y, y_end - 1), d, s);
+        unsigned st = use % kMaskStages, par = (use / kMaskStages) & 1;
+        unsigned sbase = smem0 + st * k.stage_bytes;
+        for (int t = 0; t < total; ++t) {
+            if (!mbar_try_wait(bar0 + 8 * st, par)) mbar_wait(bar0 + 8 * st, par);
+            const bool row_live = y < y_end;
+            const bool live = x_live && row_live;
+            unsigned m4 = 0;
+            if (live) {
+                float A[4] = {0.f, 0.f, 0.f, 0.f}, W[4] = {0.f, 0.f, 0.f, 0.f}, S[4] = {0.f, 0.f, 0.f, 0.f};
+                auto add4 = [&](unsigned p_addr, unsigned w_addr) {
+                    const float4 p = lds128(p_addr), w = lds128(w_addr);
+                    const float pv[4] = {p.x, p.y, p.z, p.w}, wv[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const float a = __fmul_rn(pv[j], wv[j]);
+                        A[j] = __fadd_rn(A[j], a);
+                        S[j] = __fadd_rn(S[j], fabsf(a));
+                        W[j] = __fadd_rn(W[j], wv[j]);
+                    }
+                };
+                add4(sbase + pa, sbase + wa);
+                if (two) add4(sbase + pb, sbase + wb);
+                if (rc.nky > 1) {
+                    add4(sbase + pa + k.slot_bytes, sbase + wa + k.slot_bytes);
+                    if (two) add4(sbase + pb + k.slot_bytes, sbase + wb + k.slot_bytes);
+                }
+                unsigned slow = 0;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const float dlt = __fmaf_rn(W[j], -k.mid, A[j]);
+                    const float e1 = __fadd_rn(__fmaf_rn(W[j], k.abs_mid, S[j]), fabsf(dlt));
+                    const float bound = __fmaf_rn(e1, 0x1p-20f, __fmul_rn(W[j], k.half_up));
+                    const bool clear = (fabsf(dlt) > bound) & (W[j] > 0x1p-60f);   // NaN / inf sums fail the comparison
+                    m4 |= (dlt > 0.f ? 1u : 0u) << j;
+                    slow |= clear ? 0u : (1u << j);
+                }
+                if (slow) {
+                    // the reference's arithmetic on the same shared-memory values, ascending (ky, kx)
+                    for (int j = 0; j < 4; ++j) {
+                        if (!(slow & (1u << j))) continue;
+                        double acc = 0.0, wacc = 0.0;
+                        for (int q = 0; q < rc.nky; ++q) {
+                            for (int h = 0; h < (two ? 2 : 1); ++h) {
+                                const unsigned po = sbase + (h ? pb : pa) + q * k.slot_bytes + 4 * j;
+                                const unsigned wo = sbase + (h ? wb : wa) + q * k.slot_bytes + 4 * j;
+                                float pv, wv;
+                                asm volatile("ld.shared.f32 %0, [%1];" : "=f"(pv) : "r"(po));
+                                asm volatile("ld.shared.f32 %0, [%1];" : "=f"(wv) : "r"(wo));
+                                acc = __dadd_rn(acc, (double)__fmul_rn(pv, wv));
+                                wacc = __dadd_rn(wacc, (double)wv);
+                            }
+                        }
+                        const bool m = (e.fast == 2) ? blend_decide_exact_plain(acc, wacc, e.thr)
+                                                     : blend_decide_exact(acc, wacc, e.lo, e.hi, e.thr);
+                        m4 = (m4 & ~(1u << j)) | ((m ? 1u : 0u) << j);
+                    }
+                }
+                if (mask) {
+                    const unsigned bytes = (m4 & 1u) | ((m4 & 2u) << 7) | ((m4 & 4u) << 14) | ((m4 & 8u) << 21);
+                    *reinterpret_cast<unsigned*>(mask + ((int64_t)plane * d.Y + y) * d.X + x0) = bytes;
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar0 + 8 * (kMaskStages + st));   // this warp has read its part of the stage
+            if (bits32 && row_live)   // warp-uniform: a warp's lanes share their row
+                store_mask_bits(bits32 + ((int64_t)plane * d.Y + y) * k.pieces, u_raw * 4, m4, k.pieces);
+            ++use;
+            sbase += k.stage_bytes;
+            if (++st == kMaskStages) {
+                st = 0;
+                par ^= 1;
+                sbase -= kMaskStages * k.stage_bytes;
+            }
+            y += r_step;
+            if (y >= rc.change && y < y_end) rc.set(y, d, s);
+        }
+    }
 }
 
 int check_dims(const char* who, int64_t N, int64_t C, int64_t Z, int64_t Y, int64_t X, int Tz, int Ty, int Tx, int Bz,
@@ -891,11 +1132,12 @@ extern "C" int be_tile_gather_f32(const float* img, float* tiles, int64_t N, int
     return BE_OK;
 }
 
-extern "C" int be_stitch_crop_f32(const float* tiles, float* out, uint8_t* mask, int64_t N, int64_t C, int64_t Z,
+extern "C" int be_stitch_crop_f32(const float* tiles, float* out, uint8_t* mask, uint64_t* bits, int64_t N, int64_t C, int64_t Z,
                                   int64_t Y, int64_t X, int Tz, int Ty, int Tx, int Bz, int By, int Bx,
                                   const int32_t* zsel, const int32_t* ysel, const int32_t* xsel, int epilogue, float thr,
                                   be_stream_t stream) {
-    BE_REQUIRE(tiles && (out || mask) && zsel && ysel && xsel, BE_ERR_INVALID_ARG, "be_stitch_crop_f32: null pointer");
+    BE_REQUIRE(tiles && (out || mask || bits) && zsel && ysel && xsel, BE_ERR_INVALID_ARG, "be_stitch_crop_f32: null pointer");
+    BE_REQUIRE((((uintptr_t)bits) & 7) == 0, BE_ERR_INVALID_ARG, "be_stitch_crop_f32: bits must be 8-byte aligned");
     int rc = check_dims("be_stitch_crop_f32", N, C, Z, Y, X, Tz, Ty, Tx, Bz, By, Bx);
     if (rc) return rc;
     BE_REQUIRE(epilogue == BE_EPI_NONE || epilogue == BE_EPI_SIGMOID, BE_ERR_INVALID_ARG,
@@ -905,18 +1147,20 @@ extern "C" int be_stitch_crop_f32(const float* tiles, float* out, uint8_t* mask,
     dim3 grid;
     rc = stitch_grid("be_stitch_crop_f32", d, upr, &grid);
     if (rc) return rc;
-    stitch_crop_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(tiles, out, mask, d, zsel, ysel, xsel,
+    if (bits) grid.x = (unsigned)(((X + 63) / 64 * 16 + kThreads - 1) / kThreads);   // lanes for the tail of the last word too
+    stitch_crop_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(tiles, out, mask, (uint32_t*)bits, d, zsel, ysel, xsel,
                                                                     make_epilogue(epilogue, thr, out == nullptr), upr,
                                                                     (unsigned)(N * C * Z));
     BE_LAUNCH_CHECK();
     return BE_OK;
 }
 
-extern "C" int be_stitch_blend_f32(const float* tiles, float* out, uint8_t* mask, int64_t N, int64_t C, int64_t Z,
-                                   int64_t Y, int64_t X, int Tz, int Ty, int Tx, int Bz, int By, int Bx, int Sz, int Sy,
+extern "C" int be_stitch_blend_f32(const float* tiles, float* out, uint8_t* mask, uint64_t* bits, int64_t N, int64_t C,
+                                   int64_t Z, int64_t Y, int64_t X, int Tz, int Ty, int Tx, int Bz, int By, int Bx, int Sz, int Sy,
                                    int Sx, const double* wz, const double* wy, const double* wx, int epilogue, float thr,
                                    be_stream_t stream) {
-    BE_REQUIRE(tiles && (out || mask) && wz && wy && wx, BE_ERR_INVALID_ARG, "be_stitch_blend_f32: null pointer");
+    BE_REQUIRE(tiles && (out || mask || bits) && wz && wy && wx, BE_ERR_INVALID_ARG, "be_stitch_blend_f32: null pointer");
+    BE_REQUIRE((((uintptr_t)bits) & 7) == 0, BE_ERR_INVALID_ARG, "be_stitch_blend_f32: bits must be 8-byte aligned");
     BE_REQUIRE((((uintptr_t)wx) & 15) == 0, BE_ERR_INVALID_ARG,
                "be_stitch_blend_f32: wx must be 16-byte aligned (the kernels read the x window two doubles at a time)");
     int rc = check_dims("be_stitch_blend_f32", N, C, Z, Y, X, Tz, Ty, Tx, Bz, By, Bx);
@@ -951,8 +1195,51 @@ extern "C" int be_stitch_blend_f32(const float* tiles, float* out, uint8_t* mask
         if ((int)(last - first + 1) > nseg) nseg = (int)(last - first + 1);
     }
     const size_t smem = (size_t)kStages * r_step * 2 * nseg * Bx * 4 + (size_t)Bx * 8;
-    if (Bx <= 2 * Sx && By <= 2 * Sy && (Sx & 3) == 0 && (Bx & 3) == 0 && (X & 3) == 0 && aligned16 && nseg <= 32 &&
-        smem <= 72 * 1024) {
+    const bool rows_geometry = Bx <= 2 * Sx && By <= 2 * Sy && (Sx & 3) == 0 && (Bx & 3) == 0 && (X & 3) == 0 && aligned16 &&
+                               nseg <= 32;
+    const size_t smem_mask2d = (size_t)kMaskStages * r_step * 2 * (nseg + 1) * Bx * 4 + (size_t)Bx * 8;
+    if (rows_geometry && e.fast && Z == 1 && Tz == 1 && Bz == 1 && smem_mask2d <= 100 * 1024) {
+        // 2-D, mask only: the fp32 interval filter (see stitch_blend_mask2d_kernel); one wave of persistent blocks
+        const int64_t planes = N * C;
+        BE_REQUIRE(planes < ((int64_t)1 << 31), BE_ERR_TOO_LARGE, "be_stitch_blend_f32: too many planes");
+        int64_t G = (int64_t)BE_SM_COUNT * 4 / xblocks;
+        if (G < 1) G = 1;
+        int64_t n_bands = (Y + 8 * r_step - 1) / (8 * r_step);
+        const int64_t per_block = n_bands * planes / G;
+        if (per_block < 16) {
+            const int64_t kk = per_block < 1 ? 1 : per_block + 1;
+            n_bands = (kk * G + planes - 1) / planes;
+        }
+        const int64_t max_bands = (Y + r_step - 1) / r_step;
+        if (n_bands > max_bands) n_bands = max_bands;
+        if (n_bands < 1) n_bands = 1;
+        const int64_t n_items = n_bands * planes;
+        BE_REQUIRE(n_items < ((int64_t)1 << 31), BE_ERR_TOO_LARGE, "be_stitch_blend_f32: too many work items");
+        if (G > n_items) G = n_items;
+        if (G > 65535) G = 65535;
+        Mask2dConst k;
+        k.dky = (int64_t)Tx * st.tile_stride - (int64_t)Sy * Bx;
+        const double mid = 0.5 * (e.hi2 + e.lo2), half = 0.5 * (e.hi2 - e.lo2);
+        k.mid = (float)mid;
+        k.abs_mid = fabsf(k.mid);
+        k.half_up = nextafterf((float)(half * (1.0 + 0x1p-19)), INFINITY);
+        k.log2_bx = log2_bx;
+        k.units_per_row = upr;
+        k.n_bands = (unsigned)n_bands;
+        k.n_items = (unsigned)n_items;
+        k.seg_slot_bytes = nseg * Bx * 4;
+        k.slot_bytes = k.seg_slot_bytes + Bx * 4;
+        k.stage_bytes = r_step * 2 * k.slot_bytes;
+        k.pieces = 2 * (int)((X + 63) / 64);
+        // with a packed mask the x blocks must also cover the tail of the row's last word
+        const unsigned xb = bits ? (unsigned)((((X + 63) / 64 * 16) + (1 << log2_bx) - 1) >> log2_bx) : xblocks;
+        BE_CUDA(cudaFuncSetAttribute(stitch_blend_mask2d_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_mask2d));
+        stitch_blend_mask2d_kernel<<<dim3(xb, (unsigned)G, 1), kRowsThreads, smem_mask2d, (cudaStream_t)stream>>>(
+            tiles, mask, (uint32_t*)bits, d, st, wz, wy, wx, e, k);
+        BE_LAUNCH_CHECK();
+        return BE_OK;
+    }
+    if (rows_geometry && smem <= 72 * 1024) {
         // one wave of persistent blocks (3 per SM) walks (plane, band) items; bands of about 8 steps, their number
         // rounded so that every block gets the same count when there are only a few items per block
         const int64_t planes = N * C * Z;
@@ -991,11 +1278,12 @@ extern "C" int be_stitch_blend_f32(const float* tiles, float* out, uint8_t* mask
         else
             BE_CUDA(cudaFuncSetAttribute(stitch_blend_rows_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 72 * 1024));
         if (e.fast)
-            stitch_blend_rows_kernel<true><<<g2, kRowsThreads, smem, (cudaStream_t)stream>>>(tiles, out, mask, d, st, wz, wy, wx, e, k);
+            stitch_blend_rows_kernel<true><<<g2, kRowsThreads, smem, (cudaStream_t)stream>>>(tiles, out, mask, (uint32_t*)bits, d, st, wz, wy, wx, e, k);
         else
-            stitch_blend_rows_kernel<false><<<g2, kRowsThreads, smem, (cudaStream_t)stream>>>(tiles, out, mask, d, st, wz, wy, wx, e, k);
+            stitch_blend_rows_kernel<false><<<g2, kRowsThreads, smem, (cudaStream_t)stream>>>(tiles, out, mask, (uint32_t*)bits, d, st, wz, wy, wx, e, k);
     } else {
-        stitch_blend_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(tiles, out, mask, d, st, wz, wy, wx, e, upr,
+        if (bits) grid.x = (unsigned)(((X + 63) / 64 * 16 + kThreads - 1) / kThreads);
+        stitch_blend_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(tiles, out, mask, (uint32_t*)bits, d, st, wz, wy, wx, e, upr,
                                                                          (unsigned)(N * C * Z));
     }
     BE_LAUNCH_CHECK();

@@ -215,39 +215,68 @@ def tile_gather(img: torch.Tensor, axes: Sequence[DeviceAxis], norm: Optional[to
     return out
 
 
-def _stitch_outputs(shape, device, want_out, want_mask):
+def packed_words(X: int) -> int:
+    """64-bit words per row of a bit-packed mask."""
+    return (int(X) + 63) // 64
+
+
+def _stitch_outputs(shape, device, want_out, want_mask, want_bits):
     out = torch.empty(shape, dtype=torch.float32, device=device) if want_out else None
     mask = torch.empty(shape, dtype=torch.uint8, device=device) if want_mask else None
-    return out, mask
+    bits = torch.empty(tuple(shape[:-1]) + (packed_words(shape[-1]),), dtype=torch.int64, device=device) if want_bits else None
+    return out, mask, bits
 
 
 @_on_tensor_device
 def stitch_crop(tiles: torch.Tensor, sample_shape: Sequence[int], axes: Sequence[DeviceAxis], epilogue: int = 0,
-                thr: float = 0.5, want_out: bool = True, want_mask: bool = False):
-    """bioimageio inner-region reassembly.  → (out fp32 or None, mask uint8 or None), each of sample_shape."""
+                thr: float = 0.5, want_out: bool = True, want_mask: bool = False, want_bits: bool = False):
+    """bioimageio inner-region reassembly.  → (out fp32 or None, mask uint8 or None), each of sample_shape; with
+    want_bits a third element: the mask bit-packed, int64 (*sample_shape[:-1], packed_words(X))."""
     _check(tiles, torch.float32, "tiles")
     N, C, Z, Y, X = (sample_shape[0], sample_shape[1], 1, *sample_shape[2:]) if len(sample_shape) == 4 else sample_shape
     az, ay, ax = axes
-    out, mask = _stitch_outputs(tuple(sample_shape), tiles.device, want_out, want_mask)
-    _lib.call("be_stitch_crop_f32", tiles.data_ptr(), _p(out), _p(mask), N, C, Z, Y, X, az.ax.T, ay.ax.T, ax.ax.T,
+    out, mask, bits = _stitch_outputs(tuple(sample_shape), tiles.device, want_out, want_mask, want_bits)
+    _lib.call("be_stitch_crop_f32", tiles.data_ptr(), _p(out), _p(mask), _p(bits), N, C, Z, Y, X, az.ax.T, ay.ax.T, ax.ax.T,
               az.ax.B, ay.ax.B, ax.ax.B, az.sel.data_ptr(), ay.sel.data_ptr(), ax.sel.data_ptr(), int(epilogue),
               float(thr), _stream())
-    return out, mask
+    return (out, mask, bits) if want_bits else (out, mask)
 
 
 @_on_tensor_device
 def stitch_blend(tiles: torch.Tensor, sample_shape: Sequence[int], axes: Sequence[DeviceAxis],
                  windows: Sequence[torch.Tensor], epilogue: int = 0, thr: float = 0.5, want_out: bool = True,
-                 want_mask: bool = False):
-    """fibsem Gaussian blend.  windows = (wz, wy, wx) fp64 CUDA tensors (wz = [1.0] for 2-D)."""
+                 want_mask: bool = False, want_bits: bool = False):
+    """fibsem Gaussian blend.  windows = (wz, wy, wx) fp64 CUDA tensors (wz = [1.0] for 2-D).  Returns as stitch_crop."""
     _check(tiles, torch.float32, "tiles")
     N, C, Z, Y, X = (sample_shape[0], sample_shape[1], 1, *sample_shape[2:]) if len(sample_shape) == 4 else sample_shape
     az, ay, ax = axes
-    out, mask = _stitch_outputs(tuple(sample_shape), tiles.device, want_out, want_mask)
-    _lib.call("be_stitch_blend_f32", tiles.data_ptr(), _p(out), _p(mask), N, C, Z, Y, X, az.ax.T, ay.ax.T, ax.ax.T,
+    out, mask, bits = _stitch_outputs(tuple(sample_shape), tiles.device, want_out, want_mask, want_bits)
+    _lib.call("be_stitch_blend_f32", tiles.data_ptr(), _p(out), _p(mask), _p(bits), N, C, Z, Y, X, az.ax.T, ay.ax.T, ax.ax.T,
               az.ax.B, ay.ax.B, ax.ax.B, az.ax.stride, ay.ax.stride, ax.ax.stride, windows[0].data_ptr(),
               windows[1].data_ptr(), windows[2].data_ptr(), int(epilogue), float(thr), _stream())
-    return out, mask
+    return (out, mask, bits) if want_bits else (out, mask)
+
+
+def _ccl_dims(shape):
+    if len(shape) == 3:
+        N, Y, X = shape
+        return N, 1, Y, X
+    if len(shape) == 4:
+        return tuple(shape)
+    raise ValueError(f"expected (N,Y,X) or (N,Z,Y,X), got {tuple(shape)}")
+
+
+def _ccl_call(fn: str, lead_args, shape, device, connectivity, ws, out, n_out):
+    N, Z, Y, X = _ccl_dims(shape)
+    ndim = 3 if Z > 1 else 2
+    conn = ndim if connectivity is None else int(connectivity)
+    labels = torch.empty(tuple(shape), dtype=torch.int32, device=device) if out is None else _check(out, torch.int32, "out")
+    n_labels = torch.empty((N,), dtype=torch.int32, device=device) if n_out is None else _check(n_out, torch.int32, "n_out")
+    if labels.numel() != N * Z * Y * X or n_labels.numel() != N:
+        raise ValueError("output buffers do not match the mask")
+    w = ws.get(_lib.query("be_ccl_workspace_bytes", N, Z, Y, X), device)
+    _lib.call(fn, *lead_args, labels.data_ptr(), N, Z, Y, X, conn, n_labels.data_ptr(), w.data_ptr(), _stream())
+    return labels, n_labels
 
 
 @_on_tensor_device
@@ -255,23 +284,28 @@ def ccl(mask: torch.Tensor, connectivity: Optional[int] = None, ws: Workspace = 
         out: Optional[torch.Tensor] = None, n_out: Optional[torch.Tensor] = None):
     """mask (N,[Z,]Y,X) uint8 → (labels int32 same shape, n_labels int32 [N] on device)."""
     _check(mask, torch.uint8, "mask")
-    if mask.dim() == 3:
-        N, Y, X = mask.shape
-        Z = 1
-    elif mask.dim() == 4:
-        N, Z, Y, X = mask.shape
-    else:
-        raise ValueError(f"expected (N,Y,X) or (N,Z,Y,X), got {tuple(mask.shape)}")
-    ndim = 3 if Z > 1 else 2
-    conn = ndim if connectivity is None else int(connectivity)
-    labels = torch.empty(mask.shape, dtype=torch.int32, device=mask.device) if out is None else _check(out, torch.int32, "out")
-    n_labels = torch.empty((N,), dtype=torch.int32, device=mask.device) if n_out is None else _check(n_out, torch.int32, "n_out")
-    if labels.numel() != mask.numel() or n_labels.numel() != N:
-        raise ValueError("output buffers do not match the mask")
-    w = ws.get(_lib.query("be_ccl_workspace_bytes", N, Z, Y, X), mask.device)
-    _lib.call("be_ccl_u8_i32", mask.data_ptr(), labels.data_ptr(), N, Z, Y, X, conn, n_labels.data_ptr(),
-              w.data_ptr(), _stream())
-    return labels, n_labels
+    return _ccl_call("be_ccl_u8_i32", [mask.data_ptr()], mask.shape, mask.device, connectivity, ws, out, n_out)
+
+
+@_on_tensor_device
+def ccl_bits(bits: torch.Tensor, shape: Sequence[int], connectivity: Optional[int] = None, ws: Workspace = _default_ws,
+             out: Optional[torch.Tensor] = None, n_out: Optional[torch.Tensor] = None):
+    """Bit-packed mask (int64 words, rows of `packed_words(X)`, lowest bit = first pixel) of an (N,[Z,]Y,X) image →
+    (labels int32 of `shape`, n_labels int32 [N])."""
+    _check(bits, torch.int64, "bits")
+    N, Z, Y, X = _ccl_dims(tuple(shape))
+    if bits.numel() != N * Z * Y * packed_words(X):
+        raise ValueError("bits do not match the shape")
+    return _ccl_call("be_ccl_bits_i32", [bits.data_ptr()], tuple(shape), bits.device, connectivity, ws, out, n_out)
+
+
+@_on_tensor_device
+def ccl_logits(x: torch.Tensor, epilogue: int = 0, thr: float = 0.5, connectivity: Optional[int] = None,
+               ws: Workspace = _default_ws, out: Optional[torch.Tensor] = None, n_out: Optional[torch.Tensor] = None):
+    """x (N,[Z,]Y,X) fp32 → labels of (sigmoid(x) if epilogue == BE_EPI_SIGMOID else x) > thr, no mask in between."""
+    _check(x, torch.float32, "x")
+    return _ccl_call("be_ccl_f32_i32", [x.data_ptr(), int(epilogue), float(thr)], x.shape, x.device, connectivity, ws,
+                     out, n_out)
 
 
 @_on_tensor_device

@@ -36,6 +36,7 @@ class PipelineSpec:
     connectivity: Optional[int] = None
     label: bool = True
     return_prob: bool = False
+    return_mask: bool = True                 # False: only the bit-packed mask moves between the stitcher and the labelling
     forward_batch: int = 64
 
 
@@ -113,18 +114,22 @@ class TiledPipeline:
         sp = self.spec
         out_shape = (self.shape[0], logits.shape[1]) + self.shape[2:]
         epi = _lib.BE_EPI_SIGMOID if sp.sigmoid else _lib.BE_EPI_NONE
+        want_mask = sp.return_mask or not sp.label
+        # the labelling reads the mask bit-packed (one bit per pixel leaves the stitcher instead of a byte)
         if sp.convention == "bioimageio":
-            prob, mask = K.stitch_crop(logits, out_shape, self.axes, epi, sp.threshold, want_out=sp.return_prob,
-                                       want_mask=True)
+            prob, mask, bits = K.stitch_crop(logits, out_shape, self.axes, epi, sp.threshold, want_out=sp.return_prob,
+                                             want_mask=want_mask, want_bits=sp.label)
         else:
-            prob, mask = K.stitch_blend(logits, out_shape, self.axes, self.windows, epi, sp.threshold,
-                                        want_out=sp.return_prob, want_mask=True)
-        res = {"mask": mask}
+            prob, mask, bits = K.stitch_blend(logits, out_shape, self.axes, self.windows, epi, sp.threshold,
+                                              want_out=sp.return_prob, want_mask=want_mask, want_bits=sp.label)
+        res = {}
+        if mask is not None:
+            res["mask"] = mask
         if prob is not None:
             res["prob"] = prob
         if sp.label:
-            m = mask.reshape((out_shape[0] * out_shape[1],) + out_shape[2:])
-            labels, n = K.ccl(m, sp.connectivity, ws=self.ws, out=labels_out, n_out=n_out)
+            lshape = (out_shape[0] * out_shape[1],) + out_shape[2:]
+            labels, n = K.ccl_bits(bits, lshape, sp.connectivity, ws=self.ws, out=labels_out, n_out=n_out)
             res["labels"] = labels.reshape(out_shape)
             res["n_labels"] = n
         return res

@@ -19,7 +19,7 @@ import numpy as np
 import torch
 import torch.distributed as dist
 
-from . import _lib, geometry as G, kernels as K
+from . import _lib, kernels as K
 from .metrics import _next_pow2, ap_from_counts, average_precision
 
 
@@ -76,10 +76,6 @@ class ShardScreener:
         self.cap_true = int(cap_true)
         self.cap_pred = int(cap_pred) if cap_pred else min(bound, max(4096, n_px // 32) + 1)
         self.capacity = _next_pow2(4 * (self.cap_true + self.cap_pred) + 64)
-        axes = [G.identity_axis(s) for s in self.spatial]
-        if len(axes) == 2:
-            axes = [G.identity_axis(1)] + axes
-        self.axes = [K.DeviceAxis(a, self.device) for a in axes]   # one block = the image: the stitcher's fused epilogue
         self.ws = K.Workspace()
         self.flags = torch.zeros(2, dtype=torch.int32, device=self.device)
 
@@ -90,12 +86,11 @@ class ShardScreener:
 
     def score(self, logits: torch.Tensor, gt: torch.Tensor, thr: torch.Tensor, rows: torch.Tensor,
               table_model: torch.Tensor, gt_max: Optional[torch.Tensor] = None) -> None:
-        """logits (B, 1, *spatial) fp32 of one model → sigmoid + binarize 0.5 (one pass, mask only) → labels → overlap
+        """logits (B, 1, *spatial) fp32 of one model → labels of sigmoid(x) > 0.5 (decided inside the labelling kernel) → overlap
         table vs gt → pair counts → rows of `table_model` at image indices `rows`.  Nothing returns to the host."""
         B = logits.shape[0]
-        shape = (B, 1) + self.spatial
-        _, mask = K.stitch_crop(logits, shape, self.axes, _lib.BE_EPI_SIGMOID, 0.5, want_out=False, want_mask=True)
-        labels, n_lab = K.ccl(mask.reshape((B,) + self.spatial), self.connectivity, ws=self.ws)
+        labels, n_lab = K.ccl_logits(logits.reshape((B,) + self.spatial), _lib.BE_EPI_SIGMOID, 0.5, self.connectivity,
+                                     ws=self.ws)
         if gt_max is not None:
             # table sizes follow each image's label counts (known on the device only): bounds[i] = {max gt label, n_lab}
             bounds = torch.stack((gt_max, n_lab), dim=1).contiguous()
@@ -152,9 +147,8 @@ def screen_models(models: Sequence[Callable[[torch.Tensor], torch.Tensor]], imag
             for m, model in enumerate(models):
                 for i in mine:
                     x = torch.from_numpy(np.asarray(images[i], np.float32)[None, None]).to(dev)
-                    lab, _ = K.ccl(K.stitch_crop(model(scr.normalise(x)).contiguous(), (1, 1) + spatial, scr.axes,
-                                                 _lib.BE_EPI_SIGMOID, 0.5, want_out=False, want_mask=True)[1][0],
-                                   connectivity)
+                    lab, _ = K.ccl_logits(model(scr.normalise(x)).contiguous().reshape((1,) + spatial),
+                                          _lib.BE_EPI_SIGMOID, 0.5, connectivity)
                     _, tp, _, _ = average_precision([np.asarray(gt_labels[i], np.int32)], [lab[0].cpu().numpy()],
                                                     list(thresholds), device=dev)
                     table[m, i, :n_thr] = torch.from_numpy(tp[0].astype(np.int64)).to(dev)

@@ -120,18 +120,19 @@ int be_tile_gather_f32(const float* img, float* tiles, int64_t N, int64_t C, int
 /* Inner-region reassembly (bioimageio `Sample.from_blocks`: out[inner_slice] = block[local_inner],
  * last writer wins; Appendix A.4, runtime_deployment.py:278).  Per-axis tables zsel[Z], ysel[Y], xsel[X]
  * hold k*B + i of the winning block for every output coordinate.  Optional fused epilogue: sigmoid on the
- * stitched value, and/or a uint8 mask = value > thr (the `sigmoid` / `binarize` post-processing ops).
- * Either of out / mask may be NULL. */
-int be_stitch_crop_f32(const float* tiles, float* out, uint8_t* mask, int64_t N, int64_t C, int64_t Z, int64_t Y,
-                       int64_t X, int Tz, int Ty, int Tx, int Bz, int By, int Bx, const int32_t* zsel,
+ * stitched value, and/or a mask = value > thr (the `sigmoid` / `binarize` post-processing ops) as uint8 (`mask`) and / or
+ * bit-packed (`bits`: per (n, c, z, y) row ceil(X / 64) 64-bit words, lowest bit = first pixel, tail bits zero — the
+ * input of be_ccl_bits_i32).  Any of out / mask / bits may be NULL (not all). */
+int be_stitch_crop_f32(const float* tiles, float* out, uint8_t* mask, uint64_t* bits, int64_t N, int64_t C, int64_t Z,
+                       int64_t Y, int64_t X, int Tz, int Ty, int Tx, int Bz, int By, int Bx, const int32_t* zsel,
                        const int32_t* ysel, const int32_t* xsel, int epilogue, float thr, be_stream_t stream);
 
 /* Gaussian-weighted overlap blend, gather form of analysis_deployment.py:125-156: tiles sit at
  * k*stride, window w = (float)(wz[iz]*wy[iy]*wx[ix]) from host-computed fp64 1-D tables
  * (exp(-2*linspace(-1,1,B)^2); wz = {1.0} for 2-D), acc += (double)(tile*w), wacc += (double)w in
- * ascending tile order, value = (float)(acc/wacc).  Epilogue / mask as be_stitch_crop_f32.
+ * ascending tile order, value = (float)(acc/wacc).  Epilogue / mask / bits as be_stitch_crop_f32.
  * `wx` must be 16-byte aligned (BE_ERR_INVALID_ARG otherwise). */
-int be_stitch_blend_f32(const float* tiles, float* out, uint8_t* mask, int64_t N, int64_t C, int64_t Z, int64_t Y,
+int be_stitch_blend_f32(const float* tiles, float* out, uint8_t* mask, uint64_t* bits, int64_t N, int64_t C, int64_t Z, int64_t Y,
                         int64_t X, int Tz, int Ty, int Tx, int Bz, int By, int Bx, int Sz, int Sy, int Sx,
                         const double* wz, const double* wy, const double* wx, int epilogue, float thr,
                         be_stream_t stream);
@@ -148,6 +149,19 @@ int be_stitch_blend_f32(const float* tiles, float* out, uint8_t* mask, int64_t N
 size_t be_ccl_workspace_bytes(int64_t N, int64_t Z, int64_t Y, int64_t X);
 int be_ccl_u8_i32(const uint8_t* mask, int32_t* labels, int64_t N, int64_t Z, int64_t Y, int64_t X,
                   int connectivity, int32_t* n_labels, void* ws, be_stream_t stream);
+
+/* The same labelling from a bit-packed mask: bits[((n*Z + z)*Y + y)*W + k] holds pixels 64k .. 64k+63 of row (n, z, y),
+ * lowest bit first, W = ceil(X / 64) words per row (bits past the end of a row are ignored) — the layout
+ * be_stitch_blend_f32 / be_stitch_crop_f32 write when asked for a packed mask, so `binarize` → `label`
+ * (analysis_deployment.py:166,175) moves one bit per pixel between the two kernels.  8-byte aligned. */
+int be_ccl_bits_i32(const uint64_t* bits, int32_t* labels, int64_t N, int64_t Z, int64_t Y, int64_t X,
+                    int connectivity, int32_t* n_labels, void* ws, be_stream_t stream);
+
+/* The same labelling straight from fp32 values: foreground = value > thr after the optional sigmoid (epilogue as in
+ * be_stitch_crop_f32) — bioimageio `sigmoid` → `binarize` → label of an untiled prediction
+ * (apps/model-runner/runtime_deployment.py:280 followed by the label call sites above) without writing a mask at all. */
+int be_ccl_f32_i32(const float* x, int epilogue, float thr, int32_t* labels, int64_t N, int64_t Z, int64_t Y, int64_t X,
+                   int connectivity, int32_t* n_labels, void* ws, be_stream_t stream);
 
 /* ---- screening metric --------------------------------------------------------------------------- */
 

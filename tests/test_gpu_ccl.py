@@ -95,3 +95,56 @@ def test_ccl_idempotent_on_own_output(dev, rng):
     got, _ = run(m, 2, dev)
     again, _ = run(got > 0, 2, dev)
     assert np.array_equal(got, again)
+
+
+def pack_bits(mask_np):
+    """(..., X) bool → (..., ceil(X/64)) int64 words, lowest bit = first pixel of the word (the kernels' layout)."""
+    X = mask_np.shape[-1]
+    W = (X + 63) // 64
+    padded = np.zeros(mask_np.shape[:-1] + (W * 64,), np.uint8)
+    padded[..., :X] = mask_np
+    by = np.packbits(padded.reshape(mask_np.shape[:-1] + (W, 64)), axis=-1, bitorder="little")
+    return np.ascontiguousarray(by).view(np.uint64).reshape(mask_np.shape[:-1] + (W,)).astype(np.int64)
+
+
+@pytest.mark.parametrize("shape,conn", [((2, 200, 333), 2), ((1, 64, 64), 1), ((3, 129, 640), 2), ((1, 700, 1), 2),
+                                        ((2, 9, 40, 130), 3), ((1, 16, 16, 256), 1)])
+def test_ccl_from_bit_packed_mask_and_from_logits(shape, conn, dev, rng):
+    """The three front ends of the labelling kernel (uint8 mask, bit-packed mask, fp32 values with the threshold fused)
+    must give the same labels: scipy's, numbering included."""
+    from bioengine_worker_b200 import _lib
+
+    x = (rng.standard_normal(shape) * 1.5 - 0.6).astype(np.float32)
+    x[..., ::7, :] += 1.0
+    for epi, mask in ((_lib.BE_EPI_SIGMOID, O.binarize(O.sigmoid(x), 0.5)), (_lib.BE_EPI_NONE, O.binarize(x, 0.25))):
+        thr = 0.5 if epi == _lib.BE_EPI_SIGMOID else 0.25
+        want = np.stack([O.label(m, conn) for m in mask])
+        got_u8, n_u8 = run(mask, conn, dev)
+        assert np.array_equal(got_u8, want)
+        bits = torch.from_numpy(pack_bits(mask.astype(bool))).to(dev)
+        # garbage past the end of ragged rows must be ignored
+        if shape[-1] % 64:
+            bits[..., -1] |= torch.tensor(-1, dtype=torch.int64, device=dev) << (shape[-1] % 64)
+        from bioengine_worker_b200.kernels import Workspace
+        fresh = Workspace()   # not the workspace the uint8 call above left its packed mask in
+        fresh.get(1 << 26, dev).fill_(0xA5)
+        got_b, n_b = K().ccl_bits(bits.contiguous(), shape, conn, ws=fresh)
+        assert np.array_equal(got_b.cpu().numpy(), want) and np.array_equal(n_b.cpu().numpy(), n_u8)
+        got_f, n_f = K().ccl_logits(torch.from_numpy(x).to(dev), epi, thr, conn)
+        assert np.array_equal(got_f.cpu().numpy(), want) and np.array_equal(n_f.cpu().numpy(), n_u8)
+
+
+def test_ccl_logits_values_planted_on_the_threshold(dev):
+    """sigmoid(x) > 0.5 decided inside the labelling kernel: values within a few ulp of logit(0.5) = 0 and exactly on it
+    must fall on the side numpy's float32 sigmoid puts them."""
+    from bioengine_worker_b200 import _lib
+
+    base = np.float32(0.0)
+    vals = [base]
+    for _ in range(40):
+        vals.append(np.nextafter(vals[-1], np.float32(1)))
+    vals = np.array(vals + [-v for v in vals] + [1e-4, -1e-4, 9.9e-5, -9.9e-5, 1.01e-4], np.float32)
+    x = np.tile(vals, 50)[: 64 * 64].reshape(1, 64, 64).copy()
+    mask = O.binarize(O.sigmoid(x), 0.5)
+    got, _ = K().ccl_logits(torch.from_numpy(x).to(dev), _lib.BE_EPI_SIGMOID, 0.5, 2)
+    assert np.array_equal(got.cpu().numpy()[0], O.label(mask[0], 2))

@@ -177,6 +177,16 @@ def test_blend_kernels_all_epilogues(spatial, B, ov, N, C, thr, dev, rng):
     assert np.array_equal(pmask.cpu().numpy(), O.binarize(O.sigmoid(want), thr))
     _, only = K().stitch_blend(ld, shape, daxes, wins, epilogue=1, want_out=False, want_mask=True, thr=thr)  # band test
     assert np.array_equal(only.cpu().numpy(), O.binarize(O.sigmoid(want), thr))
+    # the mask alone, bit-packed, for both epilogues (2-D: the fp32 interval filter decides most pixels)
+    from tests.test_gpu_ccl import pack_bits
+    for epi, m in ((1, O.binarize(O.sigmoid(want), thr)), (0, O.binarize(want, thr))):
+        _, none, bits = K().stitch_blend(ld, shape, daxes, wins, epilogue=epi, want_out=False, want_bits=True, thr=thr)
+        assert none is None and np.array_equal(bits.cpu().numpy(), pack_bits(m.astype(bool)))
+        _, both, bits2 = K().stitch_blend(ld, shape, daxes, wins, epilogue=epi, want_out=False, want_mask=True, want_bits=True,
+                                          thr=thr)
+        assert np.array_equal(both.cpu().numpy(), m) and torch.equal(bits, bits2)
+    _, m3, bits3 = K().stitch_blend(ld, shape, daxes, wins, epilogue=1, want_mask=True, want_bits=True, thr=thr)  # with the prob map
+    assert np.array_equal(bits3.cpu().numpy(), pack_bits(m3.cpu().numpy().astype(bool)))
 
 
 def test_blend_band_test_on_values_at_the_threshold(dev):
@@ -196,6 +206,17 @@ def test_blend_band_test_on_values_at_the_threshold(dev):
         _, only = K().stitch_blend(torch.from_numpy(logits).to(dev), (1, 1, H, W), dev_axes(axes, dev), wins, epilogue=1,
                                    want_out=False, want_mask=True, thr=thr)
         assert np.array_equal(only.cpu().numpy()[0, 0], O.binarize(O.sigmoid(want), thr)), thr
+        # no sigmoid: blended values planted on the threshold itself (every tile holds the same value, so the blend
+        # returns it up to rounding of the quotient)
+        t32 = np.float32(thr)
+        vals2 = np.array([t32, np.nextafter(t32, np.float32(-9)), np.nextafter(t32, np.float32(9)), t32 * np.float32(1.000001),
+                          t32 * np.float32(0.999999), 0.0, 1.0], np.float32)
+        img = np.tile(vals2, (H * W + len(vals2) - 1) // len(vals2))[:H * W].reshape(H, W)
+        plain = O.fibsem_tiles(img, B, ov)[:, None]
+        want2 = O.fibsem_blend(plain[:, 0], (H, W), B, ov)
+        _, only2 = K().stitch_blend(torch.from_numpy(plain).to(dev), (1, 1, H, W), dev_axes(axes, dev), wins, epilogue=0,
+                                    want_out=False, want_mask=True, thr=thr)
+        assert np.array_equal(only2.cpu().numpy()[0, 0], O.binarize(want2, thr)), thr
 
 
 def test_kernels_write_nothing_outside_their_outputs(dev, rng):
@@ -229,11 +250,41 @@ def test_kernels_write_nothing_outside_their_outputs(dev, rng):
         for want_out, epi in ((True, 0), (True, 1), (False, 1)):
             obuf = torch.full((n_px + 2 * guard,), -3.25, dtype=torch.float32, device=dev)
             mbuf = torch.full((n_px + 2 * guard,), 9, dtype=torch.uint8, device=dev)
+            n_words = C * Z * Y * ((X + 63) // 64)
+            bbuf = torch.full((n_words + 2 * guard,), 0x5555, dtype=torch.int64, device=dev)
             _lib.call("be_stitch_blend_f32", tbuf[guard:].data_ptr(), obuf[guard:].data_ptr() if want_out else 0,
-                      mbuf[guard:].data_ptr(), 1, C, Z, Y, X, az.ax.T, ay.ax.T, ax.ax.T, az.ax.B, ay.ax.B, ax.ax.B,
+                      mbuf[guard:].data_ptr(), bbuf[guard:].data_ptr(), 1, C, Z, Y, X, az.ax.T, ay.ax.T, ax.ax.T, az.ax.B, ay.ax.B, ax.ax.B,
                       az.ax.stride, ay.ax.stride, ax.ax.stride, wz.data_ptr(), w1.data_ptr(), w1.data_ptr(), epi, 0.5, stream)
             assert bool((mbuf[:guard] == 9).all()) and bool((mbuf[guard + n_px:] == 9).all()), (spatial, epi, "mask")
             assert bool((mbuf[guard:guard + n_px] <= 1).all())
+            assert bool((bbuf[:guard] == 0x5555).all()) and bool((bbuf[guard + n_words:] == 0x5555).all()), (spatial, epi, "bits")
+            from tests.test_gpu_ccl import pack_bits
+            want_bits = pack_bits(mbuf[guard:guard + n_px].cpu().numpy().reshape(C * Z * Y, X).astype(bool))
+            assert np.array_equal(bbuf[guard:guard + n_words].cpu().numpy().reshape(C * Z * Y, -1), want_bits), (spatial, epi)
             assert bool((obuf[:guard] == -3.25).all()) and bool((obuf[guard + n_px:] == -3.25).all()), (spatial, epi, "out")
             if want_out:
                 assert not bool((obuf[guard:guard + n_px] == -3.25).any())
+
+
+@pytest.mark.parametrize("shape,block,halo", [((2, 1, 100, 200), (48, 64), (8, 8)), ((1, 2, 70, 81), (32, 32), (4, 4)),
+                                              ((1, 1, 20, 33, 130), (8, 16, 64), (1, 2, 4))])
+def test_crop_stitch_packed_mask(shape, block, halo, dev, rng):
+    """The bit-packed mask of the crop stitcher (rows that end inside a word, several planes, 3-D) against the byte mask."""
+    from tests.test_gpu_ccl import pack_bits
+
+    nd = len(block)
+    axes = [G.bioimageio_axis(s, b, h) for s, b, h in zip(shape[2:], block, halo)]
+    if nd == 2:
+        axes = [G.identity_axis(1)] + axes
+    T = int(np.prod([a.T for a in axes]))
+    logits = (rng.standard_normal((shape[0] * T, shape[1]) + tuple(block)) * 2).astype(np.float32)
+    ld = torch.from_numpy(logits).to(dev)
+    want = O.binarize(O.sigmoid(O.from_blocks(logits, shape, block, halo)), 0.5)
+    out, mask, bits = K().stitch_crop(ld, shape, dev_axes(axes, dev), 1, 0.5, want_out=True, want_mask=True, want_bits=True)
+    assert np.array_equal(mask.cpu().numpy(), want)
+    assert np.array_equal(bits.cpu().numpy(), pack_bits(want.astype(bool)))
+    _, none, only = K().stitch_crop(ld, shape, dev_axes(axes, dev), 1, 0.5, want_out=False, want_bits=True)
+    assert none is None and torch.equal(only, bits)
+    labels, n = K().ccl_bits(only.reshape(-1), (shape[0] * shape[1],) + tuple(shape[2:]), None)
+    want_l = np.stack([O.label(m) for m in want.reshape((-1,) + tuple(shape[2:]))])
+    assert np.array_equal(labels.cpu().numpy(), want_l)
