@@ -388,7 +388,8 @@ def run_b200(args):
         events[1].record()
         K.tile_gather(x, pipe.axes, norm=norm, norm_mode=1, out=pipe.tiles)
         events[2].record()
-        _, _, bits = K.stitch_blend(logits, (1, 1, H, W), pipe.axes, pipe.windows, 1, 0.5, want_out=False, want_bits=True)
+        _, _, bits = K.stitch_blend(logits, (1, 1, H, W), pipe.axes, pipe.windows, 1, 0.5, want_out=False, want_bits=True,
+                                    window=pipe.window_table)
         events[3].record()
         K.ccl_bits(bits, (1, H, W), 2, ws=pipe.ws)
         events[4].record()

@@ -39,7 +39,8 @@ SIGNATURES = {
     "be_binarize_f32_u8": (_i32, [_ptr, _ptr, _i64, _f32, _ptr]),
     "be_tile_gather_f32": (_i32, [_ptr, _ptr] + [_i64] * 5 + [_i32] * 6 + [_ptr] * 4 + [_i32, _i32, _f32, _f32, _ptr]),
     "be_stitch_crop_f32": (_i32, [_ptr] * 4 + [_i64] * 5 + [_i32] * 6 + [_ptr] * 3 + [_i32, _f32, _ptr]),
-    "be_stitch_blend_f32": (_i32, [_ptr] * 4 + [_i64] * 5 + [_i32] * 9 + [_ptr] * 3 + [_i32, _f32, _ptr]),
+    "be_stitch_blend_f32": (_i32, [_ptr] * 4 + [_i64] * 5 + [_i32] * 9 + [_ptr] * 4 + [_i32, _f32, _ptr]),
+    "be_blend_window_f32": (_i32, [_ptr] * 3 + [_i32, _i32, _ptr, _ptr]),
     "be_ccl_workspace_bytes": (_sz, [_i64] * 4),
     "be_ccl_u8_i32": (_i32, [_ptr, _ptr] + [_i64] * 4 + [_i32, _ptr, _ptr, _ptr]),
     "be_ccl_bits_i32": (_i32, [_ptr, _ptr] + [_i64] * 4 + [_i32, _ptr, _ptr, _ptr]),

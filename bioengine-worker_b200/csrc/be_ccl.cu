@@ -131,12 +131,6 @@ __device__ __forceinline__ void link_run(unsigned* parent, unsigned id, int x, i
 // what the tile kernel reads its rows from
 constexpr int kInU8 = 0, kInBits = 1, kInF32 = 2;
 
-// Programmatic dependent launch: the four kernels of a call are chained so that a kernel's blocks are placed as the
-// previous kernel drains and its launch latency is off the critical path.  pdl_wait() returns once the previous kernel
-// has completed and its writes are visible; everything before it may only touch what that kernel does not write.
-__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
-__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
-
 template <int IN>
 __global__ void __launch_bounds__(kThreads, 8) ccl_tile_kernel(const void* __restrict__ input, Epilogue epi,
                                                             int32_t* __restrict__ L, u64* __restrict__ rootbits,
@@ -158,6 +152,7 @@ __global__ void __launch_bounds__(kThreads, 8) ccl_tile_kernel(const void* __res
     int32_t* Li = L + (int64_t)img * vol;
     __shared__ u64 rroot[kRows];
     if (threadIdx.x < kRows) rroot[threadIdx.x] = 0;
+    be_pdl_wait();   // the kernel that wrote the mask
 
     // ---- A: rows -> bit masks ----
     if (IN == kInBits) {
@@ -372,7 +367,7 @@ __global__ void __launch_bounds__(kThreads, 8) ccl_tile_kernel(const void* __res
             edges[(int64_t)img * (g.tiles_x * g.tiles_y * g.tiles_z) + bid] = e;
         }
     }
-    pdl_launch_dependents();
+    be_pdl_launch_dependents();
 }
 
 // ---- global union-find on the parent array ----
@@ -462,7 +457,7 @@ __device__ __forceinline__ void unite_batch(int32_t* Li, EdgeBatch& q) {
 // work is spread over as many lanes as there are edge pixels.
 __global__ void __launch_bounds__(kThreads) ccl_edge_kernel(int32_t* __restrict__ L, const TileEdges* __restrict__ edges,
                                                             Geom g, int tiles_per_image) {
-    pdl_wait();   // the tile kernel's parents and edge masks
+    be_pdl_wait();   // the tile kernel's parents and edge masks
     const int wg = blockIdx.x * (kThreads / 32) + (threadIdx.x >> 5);
     const int t = wg >> 2, part = wg & 3;
     if (t >= tiles_per_image) return;
@@ -518,7 +513,7 @@ __global__ void __launch_bounds__(kThreads) ccl_face3d_kernel(int32_t* __restric
     if (w >= words_per_image) return;
     const int wpr = g.tiles_x;
     const u64* B = bitvol + (int64_t)blockIdx.y * words_per_image;
-    pdl_wait();   // the tile kernel's parents and packed mask
+    be_pdl_wait();   // the tile kernel's parents and packed mask
     const u64 m = B[w];
     if (!m) return;
     int32_t* Li = L + (int64_t)blockIdx.y * g.Z * g.Y * g.X;
@@ -587,7 +582,7 @@ __global__ void __launch_bounds__(kThreads) ccl_number_kernel(int32_t* __restric
     const int blk = (int)s_ticket;
     int32_t* Li = L + (int64_t)img * vol;
     const int64_t w = (int64_t)blk * kWordsPerBlock + threadIdx.x;
-    pdl_wait();   // the border unions
+    be_pdl_wait();   // the border unions
     u64 keep = 0;
     int64_t base = 0;
     if (w < words_per_image) {
@@ -671,7 +666,7 @@ __global__ void __launch_bounds__(kThreads) ccl_number_kernel(int32_t* __restric
         keep &= keep - 1;
         __stcg(Li + base + b, -(++id) - 1);
     }
-    pdl_launch_dependents();
+    be_pdl_launch_dependents();
 }
 
 // grid: x = row (z * Y + y), y = blocks of 8-px units along the row, z = image.  The packed mask says which pixels have a
@@ -684,7 +679,7 @@ __global__ void __launch_bounds__(kThreads) ccl_resolve_kernel(const int32_t* __
     if (u >= units_per_row) return;
     const int64_t row = blockIdx.x;
     const int x = u * 8;
-    pdl_wait();   // the numbering (and, through it, everything before)
+    be_pdl_wait();   // the numbering (and, through it, everything before)
     const u64 word = __ldg(bitvol + (int64_t)blockIdx.z * words_per_image + row * wpr + (x >> 6));
     const unsigned bits = (unsigned)(word >> (x & 63)) & 0xffu;
     const int32_t* Li = L + (int64_t)blockIdx.z * vol;
@@ -805,6 +800,7 @@ static int ccl_run(const char* who, int in_kind, const void* input, Epilogue epi
     TileEdges* edges = ndim == 2 ? w.edges : nullptr;
     // a bit-packed input whose rows are whole words is used in place of the workspace copy of the mask
     const u64* bitvol = (in_kind == kInBits && (X % kTX) == 0) ? (const u64*)input : w.bitvol;
+    // (the memset above sits between this launch and the previous kernel, so this one starts a new chain)
     if (in_kind == kInBits)
         ccl_tile_kernel<kInBits><<<grid, kThreads, 0, s>>>(input, epi, w.L, w.rootbits, w.bitvol, edges, g);
     else if (in_kind == kInF32)
@@ -821,7 +817,7 @@ static int ccl_run(const char* who, int in_kind, const void* input, Epilogue epi
     cfg.dynamicSmemBytes = 0;
     cfg.stream = s;
     cfg.attrs = pdl;
-    cfg.numAttrs = 1;
+    cfg.numAttrs = be_pdl_enabled() ? 1 : 0;
     if (ndim == 2) {
         if (n_tiles > 1) {
             cfg.gridDim = dim3((unsigned)((4 * n_tiles + kThreads / 32 - 1) / (kThreads / 32)), (unsigned)N);   // four warps per tile

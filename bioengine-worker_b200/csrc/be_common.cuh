@@ -4,6 +4,7 @@
 #include <math.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 #include "be_b200.h"
 
@@ -38,6 +39,39 @@ void be_set_error(const char* fmt, ...);
     } while (0)
 
 static inline size_t be_align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// Programmatic dependent launch.  The kernels of the hot path are launched with programmatic stream serialization: the
+// next kernel's blocks are placed as the previous kernel drains, so launch latency and block start-up stay off the critical
+// path (nine launches per image).  be_pdl_wait() returns once the previous kernel in the stream has completed and its
+// writes are visible; a kernel calls it before it touches anything another kernel may have written.  Launched without the
+// attribute (or after a memset) it returns at once.
+__device__ __forceinline__ void be_pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void be_pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+// BE_B200_NO_PDL=1 (read once) launches everything with plain stream order: a debugging aid
+static inline bool be_pdl_enabled() {
+    static int on = -1;
+    if (on < 0) {
+        const char* e = getenv("BE_B200_NO_PDL");
+        on = (e && e[0] == '1') ? 0 : 1;
+    }
+    return on != 0;
+}
+
+template <typename Kernel, typename... Args>
+static inline cudaError_t be_launch_pdl(Kernel kernel, dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args... args) {
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cfg.attrs = attr;
+    cfg.numAttrs = be_pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, args...);
+}
 
 // Streaming loads/stores: data touched once goes around L1 so it does not evict the small tables.
 __device__ __forceinline__ float4 ld_stream_f4(const float4* p) {

@@ -86,6 +86,7 @@ __global__ void __launch_bounds__(kThreads) overlap_init_kernel(unsigned long lo
                                                                 int32_t* __restrict__ max_lbl, int32_t* __restrict__ status,
                                                                 const int32_t* __restrict__ bounds) {
     const int64_t img = blockIdx.y;
+    be_pdl_wait();   // the label counts in `bounds` may come from the kernel just before
     const OvSizes z = ov_sizes(bounds, img, capacity, cap_true, cap_pred);
     const int64_t stride = (int64_t)gridDim.x * kThreads;
     const int64_t i0 = (int64_t)blockIdx.x * kThreads + threadIdx.x;
@@ -156,6 +157,7 @@ __global__ void __launch_bounds__(kThreads) overlap_kernel(const int32_t* __rest
     const int64_t img = blockIdx.y;
     const int32_t* t = lab_true + img * n_px;
     const int32_t* p = lab_pred + img * n_px;
+    be_pdl_wait();   // the cleared tables
     const OvSizes z = ov_sizes(bounds, img, capacity, cap_true, cap_pred);
     OvGlobal G{keys + img * capacity, counts + img * capacity, z.capacity, area_true + img * cap_true,
                area_pred + img * cap_pred, z.n_true, z.n_pred, status + img};
@@ -491,15 +493,13 @@ extern "C" int be_label_overlap_i32(const int32_t* lab_true, const int32_t* lab_
         int64_t gx = (most + kThreads * 8 - 1) / (kThreads * 8);
         const int64_t cap_blocks = max((int64_t)1, (int64_t)BE_SM_COUNT * 8 / N);
         if (gx > cap_blocks) gx = cap_blocks;
-        overlap_init_kernel<<<dim3((unsigned)gx, (unsigned)N), kThreads, 0, s>>>(
-            (unsigned long long*)keys, counts, capacity, area_true, cap_true, area_pred, cap_pred, max_lbl, status,
-            label_bounds);
-        BE_LAUNCH_CHECK();
+        BE_CUDA(be_launch_pdl(overlap_init_kernel, dim3((unsigned)gx, (unsigned)N), dim3(kThreads), 0, s,
+                              (unsigned long long*)keys, counts, capacity, area_true, cap_true, area_pred, cap_pred, max_lbl,
+                              status, label_bounds));
     }
-    overlap_kernel<<<dim3((unsigned)(tiles_x * tiles_y), (unsigned)N), kThreads, 0, s>>>(
-        lab_true, lab_pred, n_px, X, (int)tiles_x, (unsigned long long*)keys, counts, capacity, area_true, cap_true,
-        area_pred, cap_pred, max_lbl, status, label_bounds);
-    BE_LAUNCH_CHECK();
+    BE_CUDA(be_launch_pdl(overlap_kernel, dim3((unsigned)(tiles_x * tiles_y), (unsigned)N), dim3(kThreads), 0, s, lab_true,
+                          lab_pred, n_px, X, (int)tiles_x, (unsigned long long*)keys, counts, capacity, area_true, cap_true,
+                          area_pred, cap_pred, max_lbl, status, label_bounds));
     return BE_OK;
 }
 

@@ -706,6 +706,7 @@ __global__ void __launch_bounds__(kThreads) qsel_partition_kernel(const float* _
     const float* xs = x + seg * seg_len;
     QTask* tasks = w.tasks + seg * NQ;
     float flo[NQ], fhi[NQ];
+    be_pdl_wait();   // the sample kernel's pivots
 #pragma unroll
     for (int i = 0; i < NQ; ++i) {
         flo[i] = tasks[i].flo;
@@ -1172,6 +1173,7 @@ __global__ void __launch_bounds__(kSelThreads)
     cg::cluster_group cluster = cg::this_cluster();
     const unsigned r = cluster.block_rank();
     const int64_t task = blockIdx.y;
+    be_pdl_wait();   // the partition pass
     if (threadIdx.x == 0) {
         S.t = w.tasks[task];
         S.st.n_ranks = 2;
@@ -1382,10 +1384,9 @@ static int quantile_sampled(const float* x, int64_t n_seg, int64_t seg_len, cons
         BE_LAUNCH_CHECK();
         const dim3 grid(sp.bps, (unsigned)ns);
         if (n_q == 1)
-            qsel_partition_kernel<1><<<grid, kThreads, 0, s>>>(xs, seg_len, sp.bps, sp.chunk, q, w, ns);
+            BE_CUDA(be_launch_pdl(qsel_partition_kernel<1>, grid, dim3(kThreads), 0, s, xs, seg_len, sp.bps, sp.chunk, q, w, ns));
         else
-            qsel_partition_kernel<2><<<grid, kThreads, 0, s>>>(xs, seg_len, sp.bps, sp.chunk, q, w, ns);
-        BE_LAUNCH_CHECK();
+            BE_CUDA(be_launch_pdl(qsel_partition_kernel<2>, grid, dim3(kThreads), 0, s, xs, seg_len, sp.bps, sp.chunk, q, w, ns));
         {
             const int n_cta = select_cluster_size();
             BE_REQUIRE(n_cta > 0, BE_ERR_CUDA, "be_quantile_f32: the device cannot run a thread-block cluster of 8");
@@ -1394,13 +1395,15 @@ static int quantile_sampled(const float* x, int64_t n_seg, int64_t seg_len, cons
             cfg.blockDim = dim3(kSelThreads);
             cfg.dynamicSmemBytes = 0;
             cfg.stream = s;
-            cudaLaunchAttribute attr[1];
+            cudaLaunchAttribute attr[2];
             attr[0].id = cudaLaunchAttributeClusterDimension;
             attr[0].val.clusterDim.x = (unsigned)n_cta;
             attr[0].val.clusterDim.y = 1;
             attr[0].val.clusterDim.z = 1;
+            attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            attr[1].val.programmaticStreamSerializationAllowed = 1;
             cfg.attrs = attr;
-            cfg.numAttrs = 1;
+            cfg.numAttrs = be_pdl_enabled() ? 2 : 1;
             BE_CUDA(cudaLaunchKernelEx(&cfg, qsel_cluster_kernel, n_q, eps, w, qs, nr));
         }
     }

@@ -9,6 +9,8 @@
 // whose tile rows are aligned 16-byte runs, one wave of persistent blocks in which a copy warp streams the rows into a
 // ring of shared-memory stages with TMA bulk copies (cp.async.bulk + mbarrier) while eight arithmetic warps work from
 // shared memory.
+#include <stdlib.h>
+
 #include "be_common.cuh"
 
 namespace {
@@ -174,6 +176,7 @@ __global__ void __launch_bounds__(kCopyThreads, 3) tile_gather_tma_kernel(const 
                                                                        const double* __restrict__ norm, int norm_mode,
                                                                        float clip_lo, float clip_hi, int units_per_row,
                                                                        int rows_per_band, int bands, unsigned n_items) {
+    be_pdl_wait();   // the statistics kernel that wrote `norm`
     extern __shared__ __align__(128) unsigned char s_stage[];   // kGatherStages * kGatherStageBytes
     __shared__ __align__(8) unsigned long long s_bar[2 * kGatherStages];
     __shared__ unsigned s_ok[kGatherMaxTx / 32];   // bit kx: the x sources of tile column kx are one aligned run
@@ -823,40 +826,64 @@ __global__ void __launch_bounds__(kRowsThreads, 3) stitch_blend_rows_kernel(cons
 //
 // When only the mask of a 2-D blend is wanted (sigmoid -> binarize, or a plain threshold on the blended value) the exact
 // quotient matters for the few pixels next to the threshold only.  This kernel walks rows like the one above, but
-//   * the window is what the reference holds in memory, the fp32 table w[iy][ix] = fp32(wy[iy] * wx[ix]): the copy warp
-//     writes the row(s) of it that a step needs next to the tile rows it fetches (Bx products per row instead of eight
-//     per thread), so the arithmetic warps read pixel and weight with two 16-byte shared loads;
+//   * the window is what the reference holds in memory, the fp32 table w[iy][ix] = fp32(wy[iy] * wx[ix])
+//     (be_blend_window_f32 writes it once per geometry; 256 KB for 256-px tiles, resident in L2 and mostly in L1);
 //   * a pixel's sums are taken in fp32: A = sum fp32(p * w) (the products are the reference's own fp32 numbers),
 //     W = sum w, S = sum |p * w|.  With at most four terms |A - A_exact| <= 3u S and |W - W_exact| <= 3u W (u = 2^-24), so
 //     d = A - W * mid misses the exact A_exact - W_exact * mid by well under 2^-20 (S + W |mid| + |d|), and a pixel with
 //     |d| > W * half + 2^-20 (S + W |mid| + |d|) lies outside the band [mid - half, mid + half] on the side sign(d)
 //     shows — the same band the fp64 test of the kernel above uses.  No fp64 instruction and no conversion is issued;
-//   * the pixels that fail the test (about one in 10^4) are redone from the same shared-memory values in the
-//     reference's arithmetic (fp64 sums of the fp32 products in ascending tile order, exact quotient, numpy's sigmoid)
-//     before the stage is released.
+//   * the pixels that fail the test (about one in 10^4) are redone in the reference's arithmetic (fp64 sums of the fp32
+//     products in ascending tile order, exact quotient, numpy's sigmoid) from the values the thread still holds;
+//   * every tile element is used by exactly one thread, so nothing is staged and no thread waits for another: a thread
+//     loads its (up to four) 16-byte pieces of a row and their weights straight into registers, and the warps of an SM
+//     cover each other's load latency.  (The ring of TMA bulk copies the kernel above feeds from is bound by the copy
+//     engine once the arithmetic is this light: ~0.8 KB per copy, about 6 B / cycle / SM = 1.8 TB/s; see profiles/README.md.)
 // The mask leaves bit-packed (one 32-bit piece per eight lanes) and / or as bytes.
 struct Mask2dConst {
     int64_t dky;             // element step in the tile buffer: next tile along y (same in-tile column, row - Sy)
     float mid, abs_mid, half_up;
     int log2_bx, units_per_row;
     unsigned n_bands, n_items;
-    int seg_slot_bytes;      // tile-row segments of one (row, ky slot): nseg * Bx * 4
-    int slot_bytes;          // seg_slot_bytes + Bx * 4 (the window row behind the segments)
-    int stage_bytes;         // r_step rows x 2 ky slots
     int pieces;              // 32-bit pieces per row of the packed mask
 };
 
-constexpr int kMaskStages = 3;   // 3 x 16 KB stages at the 4096^2 / 256-px geometry: four blocks per SM
+__global__ void __launch_bounds__(kThreads) blend_window_kernel(const double* __restrict__ wy, const double* __restrict__ wx,
+                                                                double wz0, int By, int Bx, float* __restrict__ table) {
+    const int i = blockIdx.x * kThreads + threadIdx.x;
+    if (i >= By * Bx) return;
+    const int iy = i / Bx, ix = i - iy * Bx;
+    table[i] = (float)__dmul_rn(__dmul_rn(wz0, wy[iy]), wx[ix]);
+}
 
-__global__ void __launch_bounds__(kRowsThreads, 4) stitch_blend_mask2d_kernel(const float* __restrict__ tiles,
-                                                                              uint8_t* __restrict__ mask,
-                                                                              uint32_t* __restrict__ bits32, const Dims d,
-                                                                              const Strides s, const double* __restrict__ wz,
-                                                                              const double* __restrict__ wy,
-                                                                              const double* __restrict__ wx, const Epilogue e,
-                                                                              const Mask2dConst k) {
-    extern __shared__ __align__(128) unsigned char s_dyn[];
-    __shared__ __align__(8) unsigned long long s_bar[2 * kMaskStages];   // full[kMaskStages], empty[kMaskStages]
+// one pixel again, in the reference's arithmetic: fp64 sums of the fp32 products in ascending (ky, kx) order, exact quotient,
+// numpy's sigmoid.  Out of line: about one pixel in 10^4 gets here, and it reloads its few operands itself so that the
+// caller keeps nothing alive for it.
+static __device__ __noinline__ bool mask2d_exact(const float* __restrict__ tiles, const float* __restrict__ wtab, unsigned pa,
+                                                 unsigned ab, unsigned dky, int wa, int wab, int dwy, int two, int nky,
+                                                 int fast, float thr, float lo, float hi) {
+    double acc = 0.0, wacc = 0.0;
+    for (int q = 0; q < nky; ++q) {
+        for (int h = 0; h <= two; ++h) {
+            const float pv = __ldg(tiles + (pa + (q ? dky : 0u) + (h ? ab : 0u)));
+            const float wv = __ldg(wtab + (wa - (q ? dwy : 0) + (h ? wab : 0)));
+            acc = __dadd_rn(acc, (double)__fmul_rn(pv, wv));
+            wacc = __dadd_rn(wacc, (double)wv);
+        }
+    }
+    const float v = be_div_to_f32(acc, wacc, be_fast_rcp(wacc));
+    if (fast == 2) return v > thr;
+    return (v > hi) || (!(v < lo) && be_sigmoid_f32(v) > thr);
+}
+
+template <int NB, bool ALL4>
+__global__ void __launch_bounds__(kThreads, NB) stitch_blend_mask2d_kernel(const float* __restrict__ tiles,
+                                                                          uint8_t* __restrict__ mask,
+                                                                          uint32_t* __restrict__ bits32,
+                                                                          const float* __restrict__ wtab, const Dims d,
+                                                                          const Strides s, const Epilogue e,
+                                                                          const Mask2dConst k) {
+    be_pdl_wait();   // whatever wrote the tiles
     const int tid = threadIdx.x;
     const int log2_bx = k.log2_bx;
     const int tx = tid & ((1 << log2_bx) - 1), ty = tid >> log2_bx;
@@ -864,122 +891,37 @@ __global__ void __launch_bounds__(kRowsThreads, 4) stitch_blend_mask2d_kernel(co
     const int u_raw = (blockIdx.x << log2_bx) + tx;
     const bool x_live = u_raw < k.units_per_row;
     const int x0 = min(u_raw, k.units_per_row - 1) * 4;
-    const int X0 = (blockIdx.x << log2_bx) * 4, X1 = min((int)d.X, X0 + (4 << log2_bx));   // the block's x range
-    int seg_first, seg_last;
-    cover(X0, d.Bx, s.Sx, s.rSx, d.Tx, &seg_first, &seg_last);
-    seg_last = min(d.Tx - 1, be_fast_div(X1 - 1, s.Sx, s.rSx));
-    const int seg_bytes = d.Bx * 4;
-    const unsigned smem0 = (unsigned)__cvta_generic_to_shared(s_dyn);
-    const unsigned bar0 = (unsigned)__cvta_generic_to_shared(s_bar);
-
     int kxa, kxb;
     cover(x0, d.Bx, s.Sx, s.rSx, d.Tx, &kxa, &kxb);
-    const bool two = kxb > kxa;
-    const int ixa = x0 - kxa * s.Sx, ixb = x0 - kxb * s.Sx;
-    // byte offsets inside a (row, ky slot): this thread's pixels in the first / second x tile, and their weights
-    const int pa = (ty * 2) * k.slot_bytes + (kxa - seg_first) * seg_bytes + ixa * 4;
-    const int pb = pa + (kxb - kxa) * seg_bytes + (ixb - ixa) * 4;
-    const int wa = (ty * 2) * k.slot_bytes + k.seg_slot_bytes + ixa * 4;
-    const int wb = wa + (ixb - ixa) * 4;
-
-    const bool producer = tid >= kThreads;
-    const int lane = tid & 31;
-    int seg_src = 0, seg_dst = 0, seg_len = 0;   // element offset in the tile row, byte offset in the slot, bytes
-    if (producer) {
-        const int kx = seg_first + lane;
-        if (kx <= seg_last) {
-            const int xs = max(kx * s.Sx, X0), xe = min(kx * s.Sx + d.Bx, X1);
-            seg_src = xs - kx * s.Sx;
-            seg_dst = lane * seg_bytes + seg_src * 4;
-            seg_len = (xe - xs) * 4;
-        }
-    }
-    int row_bytes = seg_len;   // bytes one (row, ky slot) brings in by bulk copy
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) row_bytes += __shfl_xor_sync(0xffffffffu, row_bytes, o);
-    // the copy warp keeps the x window (fp64) in shared memory behind the stages
-    double* wx_s = reinterpret_cast<double*>(s_dyn + kMaskStages * k.stage_bytes);
-    for (int i = tid; i < d.Bx; i += kRowsThreads) wx_s[i] = wx[i];
-
-    if (tid == 0) {
-#pragma unroll
-        for (int i = 0; i < kMaskStages; ++i) {
-            mbar_init(bar0 + 8 * i, 1);                           // full: the copy warp's expect_tx arrival + the bytes
-            mbar_init(bar0 + 8 * (kMaskStages + i), kThreads / 32);   // empty: one arrival per arithmetic warp
-        }
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    __syncthreads();
-    unsigned use = 0;
-    const double wz0 = wz[0];
+    const int two = kxb > kxa;
+    const int ixa = x0 - kxa * s.Sx;
+    // element offsets (the host checked that the tile buffer has fewer than 2^31 elements): second x tile, second y tile
+    const unsigned ab = (unsigned)((kxb - kxa) * s.tile_stride) - (unsigned)((kxb - kxa) * s.Sx);
+    const unsigned dky = (unsigned)k.dky;
+    const int wab = -(kxb - kxa) * s.Sx;   // in the window row: ixb - ixa
+    const int dwy = s.Sy * d.Bx;           // the window row of the second y tile lies Sy rows up
 
     for (unsigned item = blockIdx.y; item < k.n_items; item += gridDim.y) {
         const unsigned plane = item / k.n_bands, band = item - plane * k.n_bands;
         const int band_begin = (int)(((int64_t)band * d.Y) / k.n_bands);
         const int y_end = (int)(((int64_t)(band + 1) * d.Y) / k.n_bands);
-        const int total = (y_end - band_begin + r_step - 1) / r_step;
         const unsigned c = plane % (unsigned)d.C;
-        const int64_t n = plane / (unsigned)d.C;
-        // tile (n, ky = 0, kx = seg_first + lane), channel c, row 0, first element this lane copies
-        const float* lane_base = tiles + (n * d.Ty * d.Tx + seg_first + lane) * s.tile_stride + (int64_t)c * d.By * d.Bx + seg_src;
-
-        if (producer) {
-            for (int g = 0; g < total; ++g, ++use) {
-                const unsigned st = use % kMaskStages;
-                const unsigned full = bar0 + 8 * st, empty = bar0 + 8 * (kMaskStages + st);
-                mbar_wait(empty, ((use / kMaskStages) & 1) ^ 1);   // all arithmetic warps are done with this stage
-                int slots = 0;
-                for (int r = 0; r < r_step; ++r) {
-                    const int y = band_begin + g * r_step + r;
-                    if (y >= y_end) break;
-                    RowCover rc;
-                    rc.set(y, d, s);
-                    slots += rc.nky;
-                    // window rows of this output row: fp32(fp64(wz0 * wy[iy]) * wx[ix]) for the one or two tiles along y
-                    for (int q = 0; q < rc.nky; ++q) {
-                        const double wzy = __dmul_rn(wz0, wy[y - (rc.ky_lo + q) * s.Sy]);
-                        float* wrow = reinterpret_cast<float*>(s_dyn + st * k.stage_bytes + (r * 2 + q) * k.slot_bytes +
-                                                               k.seg_slot_bytes);
-                        for (int i = lane; i < d.Bx; i += 32) wrow[i] = (float)__dmul_rn(wzy, wx_s[i]);
-                    }
-                }
-                __syncwarp();   // every lane's window values are written before lane 0's arrival publishes the stage
-                if (lane == 0) {
-                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic accesses before async writes
-                    mbar_expect_tx(full, (unsigned)(slots * row_bytes));
-                }
-                __syncwarp();
-                if (seg_len > 0) {
-                    for (int r = 0; r < r_step; ++r) {
-                        const int y = band_begin + g * r_step + r;
-                        if (y >= y_end) break;
-                        RowCover rc;
-                        rc.set(y, d, s);
-                        const float* src = lane_base + (int64_t)rc.ky_lo * d.Tx * s.tile_stride + (int64_t)(y - rc.ky_lo * s.Sy) * d.Bx;
-                        const unsigned dst = smem0 + st * k.stage_bytes + (r * 2) * k.slot_bytes + seg_dst;
-                        bulk_g2s(dst, src, (unsigned)seg_len, full);
-                        if (rc.nky > 1) bulk_g2s(dst + k.slot_bytes, src + k.dky, (unsigned)seg_len, full);
-                    }
-                }
-            }
-            continue;
-        }
-        // arithmetic warps
-        int y = band_begin + ty;
+        const unsigned n = plane / (unsigned)d.C;
+        // tile (n, ky = 0, kx = kxa), channel c, row 0, this thread's first pixel
+        const unsigned base_a = (unsigned)((n * d.Ty * d.Tx + kxa) * s.tile_stride + (int64_t)c * d.By * d.Bx + ixa);
         RowCover rc;
-        rc.set(min(y, y_end - 1), d, s);
-        unsigned st = use % kMaskStages, par = (use / kMaskStages) & 1;
-        unsigned sbase = smem0 + st * k.stage_bytes;
-        for (int t = 0; t < total; ++t) {
-            if (!mbar_try_wait(bar0 + 8 * st, par)) mbar_wait(bar0 + 8 * st, par);
-            const bool row_live = y < y_end;
-            const bool live = x_live && row_live;
+        rc.change = -1;
+        for (int y = band_begin + ty; y < y_end; y += r_step) {   // warp-uniform: a warp's lanes share their row
+            if (y >= rc.change) rc.set(y, d, s);
+            const int nky = rc.nky;
+            const int iy = y - rc.ky_lo * s.Sy;
             unsigned m4 = 0;
-            if (live) {
+            if (x_live) {
+                const unsigned pa = base_a + (unsigned)(rc.ky_lo * d.Tx) * (unsigned)s.tile_stride + (unsigned)(iy * d.Bx);
+                const int wa = iy * d.Bx + ixa;
                 float A[4] = {0.f, 0.f, 0.f, 0.f}, W[4] = {0.f, 0.f, 0.f, 0.f}, S[4] = {0.f, 0.f, 0.f, 0.f};
-                auto add4 = [&](unsigned p_addr, unsigned w_addr) {
-                    const float4 p = lds128(p_addr), w = lds128(w_addr);
-                    const float pv[4] = {p.x, p.y, p.z, p.w}, wv[4] = {w.x, w.y, w.z, w.w};
+                auto add4 = [&](const float4& pp, const float4& ww) {
+                    const float pv[4] = {pp.x, pp.y, pp.z, pp.w}, wv[4] = {ww.x, ww.y, ww.z, ww.w};
 #pragma unroll
                     for (int j = 0; j < 4; ++j) {
                         const float a = __fmul_rn(pv[j], wv[j]);
@@ -988,11 +930,36 @@ __global__ void __launch_bounds__(kRowsThreads, 4) stitch_blend_mask2d_kernel(co
                         W[j] = __fadd_rn(W[j], wv[j]);
                     }
                 };
-                add4(sbase + pa, sbase + wa);
-                if (two) add4(sbase + pb, sbase + wb);
-                if (rc.nky > 1) {
-                    add4(sbase + pa + k.slot_bytes, sbase + wa + k.slot_bytes);
-                    if (two) add4(sbase + pb + k.slot_bytes, sbase + wb + k.slot_bytes);
+                // the pieces of the first y tile, then (one row in three) those of the second: two 16-byte loads in flight
+                // per thread at a time keeps the kernel at ~40 registers, i.e. six blocks per SM, and it is the number of
+                // loads in flight per SM that sets the pace
+                if (ALL4) {
+                    const float4 p0 = ld_stream_f4(reinterpret_cast<const float4*>(tiles + pa));
+                    float4 p1, p2, p3;
+                    if (two) p1 = ld_stream_f4(reinterpret_cast<const float4*>(tiles + (pa + ab)));
+                    if (nky > 1) {
+                        p2 = ld_stream_f4(reinterpret_cast<const float4*>(tiles + (pa + dky)));
+                        if (two) p3 = ld_stream_f4(reinterpret_cast<const float4*>(tiles + (pa + dky + ab)));
+                    }
+                    add4(p0, __ldg(reinterpret_cast<const float4*>(wtab + wa)));
+                    if (two) add4(p1, __ldg(reinterpret_cast<const float4*>(wtab + (wa + wab))));
+                    if (nky > 1) {
+                        add4(p2, __ldg(reinterpret_cast<const float4*>(wtab + (wa - dwy))));
+                        if (two) add4(p3, __ldg(reinterpret_cast<const float4*>(wtab + (wa - dwy + wab))));
+                    }
+                } else {
+                    const float4 p0 = ld_stream_f4(reinterpret_cast<const float4*>(tiles + pa));
+                    float4 p1;
+                    if (two) p1 = ld_stream_f4(reinterpret_cast<const float4*>(tiles + (pa + ab)));
+                    add4(p0, __ldg(reinterpret_cast<const float4*>(wtab + wa)));
+                    if (two) add4(p1, __ldg(reinterpret_cast<const float4*>(wtab + (wa + wab))));
+                }
+                if (!ALL4 && nky > 1) {
+                    const float4 p2 = ld_stream_f4(reinterpret_cast<const float4*>(tiles + (pa + dky)));
+                    float4 p3;
+                    if (two) p3 = ld_stream_f4(reinterpret_cast<const float4*>(tiles + (pa + dky + ab)));
+                    add4(p2, __ldg(reinterpret_cast<const float4*>(wtab + (wa - dwy))));
+                    if (two) add4(p3, __ldg(reinterpret_cast<const float4*>(wtab + (wa - dwy + wab))));
                 }
                 unsigned slow = 0;
 #pragma unroll
@@ -1004,45 +971,18 @@ __global__ void __launch_bounds__(kRowsThreads, 4) stitch_blend_mask2d_kernel(co
                     m4 |= (dlt > 0.f ? 1u : 0u) << j;
                     slow |= clear ? 0u : (1u << j);
                 }
-                if (slow) {
-                    // the reference's arithmetic on the same shared-memory values, ascending (ky, kx)
-                    for (int j = 0; j < 4; ++j) {
-                        if (!(slow & (1u << j))) continue;
-                        double acc = 0.0, wacc = 0.0;
-                        for (int q = 0; q < rc.nky; ++q) {
-                            for (int h = 0; h < (two ? 2 : 1); ++h) {
-                                const unsigned po = sbase + (h ? pb : pa) + q * k.slot_bytes + 4 * j;
-                                const unsigned wo = sbase + (h ? wb : wa) + q * k.slot_bytes + 4 * j;
-                                float pv, wv;
-                                asm volatile("ld.shared.f32 %0, [%1];" : "=f"(pv) : "r"(po));
-                                asm volatile("ld.shared.f32 %0, [%1];" : "=f"(wv) : "r"(wo));
-                                acc = __dadd_rn(acc, (double)__fmul_rn(pv, wv));
-                                wacc = __dadd_rn(wacc, (double)wv);
-                            }
-                        }
-                        const bool m = (e.fast == 2) ? blend_decide_exact_plain(acc, wacc, e.thr)
-                                                     : blend_decide_exact(acc, wacc, e.lo, e.hi, e.thr);
-                        m4 = (m4 & ~(1u << j)) | ((m ? 1u : 0u) << j);
-                    }
+                while (slow) {
+                    const int j = __ffs(slow) - 1;
+                    slow &= slow - 1;
+                    const bool m = mask2d_exact(tiles, wtab, pa + j, ab, dky, wa + j, wab, dwy, two, nky, e.fast, e.thr, e.lo, e.hi);
+                    m4 = (m4 & ~(1u << j)) | ((m ? 1u : 0u) << j);
                 }
                 if (mask) {
                     const unsigned bytes = (m4 & 1u) | ((m4 & 2u) << 7) | ((m4 & 4u) << 14) | ((m4 & 8u) << 21);
                     *reinterpret_cast<unsigned*>(mask + ((int64_t)plane * d.Y + y) * d.X + x0) = bytes;
                 }
             }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(bar0 + 8 * (kMaskStages + st));   // this warp has read its part of the stage
-            if (bits32 && row_live)   // warp-uniform: a warp's lanes share their row
-                store_mask_bits(bits32 + ((int64_t)plane * d.Y + y) * k.pieces, u_raw * 4, m4, k.pieces);
-            ++use;
-            sbase += k.stage_bytes;
-            if (++st == kMaskStages) {
-                st = 0;
-                par ^= 1;
-                sbase -= kMaskStages * k.stage_bytes;
-            }
-            y += r_step;
-            if (y >= rc.change && y < y_end) rc.set(y, d, s);
+            if (bits32) store_mask_bits(bits32 + ((int64_t)plane * d.Y + y) * k.pieces, u_raw * 4, m4, k.pieces);
         }
     }
 }
@@ -1108,16 +1048,16 @@ extern "C" int be_tile_gather_f32(const float* img, float* tiles, int64_t N, int
         const unsigned blocks = (unsigned)(n_items < (int64_t)BE_SM_COUNT * 3 ? n_items : (int64_t)BE_SM_COUNT * 3);
         if (norm_mode && clip) {
             BE_CUDA(cudaFuncSetAttribute(tile_gather_tma_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            tile_gather_tma_kernel<true, true><<<blocks, kCopyThreads, smem, s>>>(img, tiles, d, zsrc, ysrc, xsrc, norm, norm_mode,
-                                                                                 clip_lo, clip_hi, upr, rpb, nb, (unsigned)n_items);
+            BE_CUDA(be_launch_pdl(tile_gather_tma_kernel<true, true>, dim3(blocks), dim3(kCopyThreads), smem, s, img, tiles, d, zsrc, ysrc, xsrc, norm, norm_mode,
+                                                                                 clip_lo, clip_hi, upr, rpb, nb, (unsigned)n_items));
         } else if (norm_mode) {
             BE_CUDA(cudaFuncSetAttribute(tile_gather_tma_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            tile_gather_tma_kernel<true, false><<<blocks, kCopyThreads, smem, s>>>(img, tiles, d, zsrc, ysrc, xsrc, norm, norm_mode,
-                                                                                  0.f, 0.f, upr, rpb, nb, (unsigned)n_items);
+            BE_CUDA(be_launch_pdl(tile_gather_tma_kernel<true, false>, dim3(blocks), dim3(kCopyThreads), smem, s, img, tiles, d, zsrc, ysrc, xsrc, norm, norm_mode,
+                                                                                  0.f, 0.f, upr, rpb, nb, (unsigned)n_items));
         } else {
             BE_CUDA(cudaFuncSetAttribute(tile_gather_tma_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            tile_gather_tma_kernel<false, false><<<blocks, kCopyThreads, smem, s>>>(img, tiles, d, zsrc, ysrc, xsrc, norm, 0, 0.f,
-                                                                                   0.f, upr, rpb, nb, (unsigned)n_items);
+            BE_CUDA(be_launch_pdl(tile_gather_tma_kernel<false, false>, dim3(blocks), dim3(kCopyThreads), smem, s, img, tiles, d, zsrc, ysrc, xsrc, norm, 0, 0.f,
+                                                                                   0.f, upr, rpb, nb, (unsigned)n_items));
         }
     } else if (norm_mode && clip)
         tile_gather_kernel<true, true><<<grid, kThreads, 0, s>>>(img, tiles, d, zsrc, ysrc, xsrc, norm, norm_mode, clip_lo,
@@ -1155,11 +1095,25 @@ extern "C" int be_stitch_crop_f32(const float* tiles, float* out, uint8_t* mask,
     return BE_OK;
 }
 
+extern "C" int be_blend_window_f32(const double* wz, const double* wy, const double* wx, int By, int Bx, float* window,
+                                   be_stream_t stream) {
+    BE_REQUIRE(wy && wx && window, BE_ERR_INVALID_ARG, "be_blend_window_f32: null pointer");
+    BE_REQUIRE(By > 0 && Bx > 0 && (int64_t)By * Bx < ((int64_t)1 << 30), BE_ERR_INVALID_ARG, "be_blend_window_f32: bad block shape");
+    double wz0 = 1.0;
+    if (wz) BE_CUDA(cudaMemcpyAsync(&wz0, wz, sizeof(double), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    if (wz) BE_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    blend_window_kernel<<<(unsigned)(((int64_t)By * Bx + kThreads - 1) / kThreads), kThreads, 0, (cudaStream_t)stream>>>(
+        wy, wx, wz0, By, Bx, window);
+    BE_LAUNCH_CHECK();
+    return BE_OK;
+}
+
 extern "C" int be_stitch_blend_f32(const float* tiles, float* out, uint8_t* mask, uint64_t* bits, int64_t N, int64_t C,
                                    int64_t Z, int64_t Y, int64_t X, int Tz, int Ty, int Tx, int Bz, int By, int Bx, int Sz, int Sy,
-                                   int Sx, const double* wz, const double* wy, const double* wx, int epilogue, float thr,
-                                   be_stream_t stream) {
+                                   int Sx, const double* wz, const double* wy, const double* wx, const float* window,
+                                   int epilogue, float thr, be_stream_t stream) {
     BE_REQUIRE(tiles && (out || mask || bits) && wz && wy && wx, BE_ERR_INVALID_ARG, "be_stitch_blend_f32: null pointer");
+    BE_REQUIRE((((uintptr_t)window) & 15) == 0, BE_ERR_INVALID_ARG, "be_stitch_blend_f32: window must be 16-byte aligned");
     BE_REQUIRE((((uintptr_t)bits) & 7) == 0, BE_ERR_INVALID_ARG, "be_stitch_blend_f32: bits must be 8-byte aligned");
     BE_REQUIRE((((uintptr_t)wx) & 15) == 0, BE_ERR_INVALID_ARG,
                "be_stitch_blend_f32: wx must be 16-byte aligned (the kernels read the x window two doubles at a time)");
@@ -1197,12 +1151,12 @@ extern "C" int be_stitch_blend_f32(const float* tiles, float* out, uint8_t* mask
     const size_t smem = (size_t)kStages * r_step * 2 * nseg * Bx * 4 + (size_t)Bx * 8;
     const bool rows_geometry = Bx <= 2 * Sx && By <= 2 * Sy && (Sx & 3) == 0 && (Bx & 3) == 0 && (X & 3) == 0 && aligned16 &&
                                nseg <= 32;
-    const size_t smem_mask2d = (size_t)kMaskStages * r_step * 2 * (nseg + 1) * Bx * 4 + (size_t)Bx * 8;
-    if (rows_geometry && e.fast && Z == 1 && Tz == 1 && Bz == 1 && smem_mask2d <= 100 * 1024) {
-        // 2-D, mask only: the fp32 interval filter (see stitch_blend_mask2d_kernel); one wave of persistent blocks
+    if (rows_geometry && e.fast && window && Z == 1 && Tz == 1 && Bz == 1 &&
+        N * Ty * Tx * st.tile_stride < ((int64_t)1 << 31)) {
+        // 2-D, mask only: the fp32 interval filter (see stitch_blend_mask2d_kernel); one wave of blocks walking (plane, band) items
         const int64_t planes = N * C;
         BE_REQUIRE(planes < ((int64_t)1 << 31), BE_ERR_TOO_LARGE, "be_stitch_blend_f32: too many planes");
-        int64_t G = (int64_t)BE_SM_COUNT * 4 / xblocks;
+        int64_t G = (int64_t)BE_SM_COUNT * 8 / xblocks;
         if (G < 1) G = 1;
         int64_t n_bands = (Y + 8 * r_step - 1) / (8 * r_step);
         const int64_t per_block = n_bands * planes / G;
@@ -1227,15 +1181,19 @@ extern "C" int be_stitch_blend_f32(const float* tiles, float* out, uint8_t* mask
         k.units_per_row = upr;
         k.n_bands = (unsigned)n_bands;
         k.n_items = (unsigned)n_items;
-        k.seg_slot_bytes = nseg * Bx * 4;
-        k.slot_bytes = k.seg_slot_bytes + Bx * 4;
-        k.stage_bytes = r_step * 2 * k.slot_bytes;
         k.pieces = 2 * (int)((X + 63) / 64);
-        // with a packed mask the x blocks must also cover the tail of the row's last word
-        const unsigned xb = bits ? (unsigned)((((X + 63) / 64 * 16) + (1 << log2_bx) - 1) >> log2_bx) : xblocks;
-        BE_CUDA(cudaFuncSetAttribute(stitch_blend_mask2d_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_mask2d));
-        stitch_blend_mask2d_kernel<<<dim3(xb, (unsigned)G, 1), kRowsThreads, smem_mask2d, (cudaStream_t)stream>>>(
-            tiles, mask, (uint32_t*)bits, d, st, wz, wy, wx, e, k);
+        const char* nb_env = getenv("BE_MASK2D_BLOCKS");
+        const int nb = nb_env ? atoi(nb_env) : 4;
+        const dim3 g2(xblocks, (unsigned)G, 1);
+#define BE_MASK2D_LAUNCH(NB, ALL4) \
+    BE_CUDA(be_launch_pdl(stitch_blend_mask2d_kernel<NB, ALL4>, g2, dim3(kThreads), 0, (cudaStream_t)stream, tiles, mask, \
+                          (uint32_t*)bits, window, d, st, e, k))
+        if (nb == 3) BE_MASK2D_LAUNCH(3, false);
+        else if (nb == 13) BE_MASK2D_LAUNCH(3, true);
+        else if (nb == 14) BE_MASK2D_LAUNCH(4, true);
+        else if (nb == 5) BE_MASK2D_LAUNCH(5, false);
+        else BE_MASK2D_LAUNCH(4, false);
+#undef BE_MASK2D_LAUNCH
         BE_LAUNCH_CHECK();
         return BE_OK;
     }

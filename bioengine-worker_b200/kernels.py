@@ -243,17 +243,29 @@ def stitch_crop(tiles: torch.Tensor, sample_shape: Sequence[int], axes: Sequence
 
 
 @_on_tensor_device
+def blend_window(windows: Sequence[torch.Tensor]) -> torch.Tensor:
+    """The reference's fp32 window table for 2-D tiles, (By, Bx) float32 = fp32(wz[0] * wy[iy] * wx[ix]); computed once per
+    geometry and passed to `stitch_blend(..., window=...)`."""
+    wz, wy, wx = windows
+    table = torch.empty((wy.numel(), wx.numel()), dtype=torch.float32, device=wy.device)
+    _lib.call("be_blend_window_f32", wz.data_ptr(), wy.data_ptr(), wx.data_ptr(), wy.numel(), wx.numel(), table.data_ptr(),
+              _stream())
+    return table
+
+
+@_on_tensor_device
 def stitch_blend(tiles: torch.Tensor, sample_shape: Sequence[int], axes: Sequence[DeviceAxis],
                  windows: Sequence[torch.Tensor], epilogue: int = 0, thr: float = 0.5, want_out: bool = True,
-                 want_mask: bool = False, want_bits: bool = False):
-    """fibsem Gaussian blend.  windows = (wz, wy, wx) fp64 CUDA tensors (wz = [1.0] for 2-D).  Returns as stitch_crop."""
+                 want_mask: bool = False, want_bits: bool = False, window: Optional[torch.Tensor] = None):
+    """fibsem Gaussian blend.  windows = (wz, wy, wx) fp64 CUDA tensors (wz = [1.0] for 2-D); window = `blend_window(windows)`
+    (optional: lets a 2-D mask-only call take the fp32 filter kernel).  Returns as stitch_crop."""
     _check(tiles, torch.float32, "tiles")
     N, C, Z, Y, X = (sample_shape[0], sample_shape[1], 1, *sample_shape[2:]) if len(sample_shape) == 4 else sample_shape
     az, ay, ax = axes
     out, mask, bits = _stitch_outputs(tuple(sample_shape), tiles.device, want_out, want_mask, want_bits)
     _lib.call("be_stitch_blend_f32", tiles.data_ptr(), _p(out), _p(mask), _p(bits), N, C, Z, Y, X, az.ax.T, ay.ax.T, ax.ax.T,
               az.ax.B, ay.ax.B, ax.ax.B, az.ax.stride, ay.ax.stride, ax.ax.stride, windows[0].data_ptr(),
-              windows[1].data_ptr(), windows[2].data_ptr(), int(epilogue), float(thr), _stream())
+              windows[1].data_ptr(), windows[2].data_ptr(), _p(window), int(epilogue), float(thr), _stream())
     return (out, mask, bits) if want_bits else (out, mask)
 
 

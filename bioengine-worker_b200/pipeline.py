@@ -70,6 +70,7 @@ class TiledPipeline:
             if self.nd == 2:
                 wins = [torch.ones(1, dtype=torch.float64, device=self.device)] + wins
             self.windows = wins
+            self.window_table = K.blend_window(wins) if self.nd == 2 else None
         if spec.preprocess == "scale_range":
             self.q = torch.tensor([spec.min_percentile / 100.0, spec.max_percentile / 100.0], dtype=torch.float64,
                                   device=self.device)
@@ -121,7 +122,8 @@ class TiledPipeline:
                                              want_mask=want_mask, want_bits=sp.label)
         else:
             prob, mask, bits = K.stitch_blend(logits, out_shape, self.axes, self.windows, epi, sp.threshold,
-                                              want_out=sp.return_prob, want_mask=want_mask, want_bits=sp.label)
+                                              want_out=sp.return_prob, want_mask=want_mask, want_bits=sp.label,
+                                              window=self.window_table)
         res = {}
         if mask is not None:
             res["mask"] = mask

@@ -131,10 +131,20 @@ int be_stitch_crop_f32(const float* tiles, float* out, uint8_t* mask, uint64_t* 
  * k*stride, window w = (float)(wz[iz]*wy[iy]*wx[ix]) from host-computed fp64 1-D tables
  * (exp(-2*linspace(-1,1,B)^2); wz = {1.0} for 2-D), acc += (double)(tile*w), wacc += (double)w in
  * ascending tile order, value = (float)(acc/wacc).  Epilogue / mask / bits as be_stitch_crop_f32.
- * `wx` must be 16-byte aligned (BE_ERR_INVALID_ARG otherwise). */
+ * `wx` must be 16-byte aligned (BE_ERR_INVALID_ARG otherwise).
+ * `window` (optional, may be NULL): the reference's fp32 window table `weight_win` (analysis_deployment.py:125-127) as
+ * written by be_blend_window_f32 for the same wz / wy / wx.  With it a 2-D call that wants only the mask decides each
+ * pixel from fp32 sums and an error bound, and redoes the few pixels next to the threshold exactly; results are the
+ * same with and without it. */
 int be_stitch_blend_f32(const float* tiles, float* out, uint8_t* mask, uint64_t* bits, int64_t N, int64_t C, int64_t Z, int64_t Y,
                         int64_t X, int Tz, int Ty, int Tx, int Bz, int By, int Bx, int Sz, int Sy, int Sx,
-                        const double* wz, const double* wy, const double* wx, int epilogue, float thr,
+                        const double* wz, const double* wy, const double* wx, const float* window, int epilogue,
+                        float thr, be_stream_t stream);
+
+/* window[iy*Bx + ix] = (float)((wz ? wz[0] : 1.0) * wy[iy] * wx[ix]) — np.outer(...).astype(np.float32) of
+ * analysis_deployment.py:127, the table the reference multiplies every tile with.  Written once per tile geometry
+ * (By*Bx floats, 16-byte aligned) and handed to be_stitch_blend_f32.  Reads wz[0] back to the host (synchronises). */
+int be_blend_window_f32(const double* wz, const double* wy, const double* wx, int By, int Bx, float* window,
                         be_stream_t stream);
 
 /* ---- connected components ----------------------------------------------------------------------- */

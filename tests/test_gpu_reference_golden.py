@@ -8,6 +8,7 @@ import pytest
 import torch
 
 from bioengine_worker_b200 import geometry as G
+from oracle import oracle as O
 from tests.test_reference_golden import N_INFER_CASES, infer_case
 
 pytestmark = pytest.mark.gpu
@@ -40,6 +41,11 @@ def test_gather_and_blend_equal_reference_infer_tiled(dev, ci):
     # the mask-only call decides most pixels without the exact quotient; same mask
     _, mask2 = K().stitch_blend(p, (1, 1, H, W), fx, (one, w, w), 0, 0.5, want_out=False, want_mask=True)
     assert torch.equal(mask, mask2)
+    # with the reference's fp32 window table (itself bit-exact) the fp32 filter kernel decides; same mask
+    table = K().blend_window((one, w, w))
+    assert np.array_equal(table.cpu().numpy(), O.fibsem_window(tile))
+    _, mask3 = K().stitch_blend(p, (1, 1, H, W), fx, (one, w, w), 0, 0.5, want_out=False, want_mask=True, window=table)
+    assert torch.equal(mask, mask3)
 
 
 @pytest.mark.parametrize("name", ["u8", "f32", "flat", "hot"])

@@ -179,12 +179,15 @@ def test_blend_kernels_all_epilogues(spatial, B, ov, N, C, thr, dev, rng):
     assert np.array_equal(only.cpu().numpy(), O.binarize(O.sigmoid(want), thr))
     # the mask alone, bit-packed, for both epilogues (2-D: the fp32 interval filter decides most pixels)
     from tests.test_gpu_ccl import pack_bits
+    table = K().blend_window(wins) if nd == 2 else None   # 2-D + table: the fp32 interval filter kernel
     for epi, m in ((1, O.binarize(O.sigmoid(want), thr)), (0, O.binarize(want, thr))):
-        _, none, bits = K().stitch_blend(ld, shape, daxes, wins, epilogue=epi, want_out=False, want_bits=True, thr=thr)
-        assert none is None and np.array_equal(bits.cpu().numpy(), pack_bits(m.astype(bool)))
-        _, both, bits2 = K().stitch_blend(ld, shape, daxes, wins, epilogue=epi, want_out=False, want_mask=True, want_bits=True,
-                                          thr=thr)
-        assert np.array_equal(both.cpu().numpy(), m) and torch.equal(bits, bits2)
+        for tab in (None, table):
+            _, none, bits = K().stitch_blend(ld, shape, daxes, wins, epilogue=epi, want_out=False, want_bits=True, thr=thr,
+                                             window=tab)
+            assert none is None and np.array_equal(bits.cpu().numpy(), pack_bits(m.astype(bool)))
+            _, both, bits2 = K().stitch_blend(ld, shape, daxes, wins, epilogue=epi, want_out=False, want_mask=True,
+                                              want_bits=True, thr=thr, window=tab)
+            assert np.array_equal(both.cpu().numpy(), m) and torch.equal(bits, bits2)
     _, m3, bits3 = K().stitch_blend(ld, shape, daxes, wins, epilogue=1, want_mask=True, want_bits=True, thr=thr)  # with the prob map
     assert np.array_equal(bits3.cpu().numpy(), pack_bits(m3.cpu().numpy().astype(bool)))
 
@@ -203,9 +206,12 @@ def test_blend_band_test_on_values_at_the_threshold(dev):
         w1 = torch.from_numpy(G.gauss_window_1d(B)).to(dev)
         wins = (torch.ones(1, dtype=torch.float64, device=dev), w1, w1)
         want = O.fibsem_blend(logits[:, 0], (H, W), B, ov)
-        _, only = K().stitch_blend(torch.from_numpy(logits).to(dev), (1, 1, H, W), dev_axes(axes, dev), wins, epilogue=1,
-                                   want_out=False, want_mask=True, thr=thr)
-        assert np.array_equal(only.cpu().numpy()[0, 0], O.binarize(O.sigmoid(want), thr)), thr
+        table = K().blend_window(wins)
+        assert np.array_equal(table.cpu().numpy(), O.fibsem_window(B))   # the reference's weight_win, bit for bit
+        for tab in (None, table):
+            _, only = K().stitch_blend(torch.from_numpy(logits).to(dev), (1, 1, H, W), dev_axes(axes, dev), wins, epilogue=1,
+                                       want_out=False, want_mask=True, thr=thr, window=tab)
+            assert np.array_equal(only.cpu().numpy()[0, 0], O.binarize(O.sigmoid(want), thr)), thr
         # no sigmoid: blended values planted on the threshold itself (every tile holds the same value, so the blend
         # returns it up to rounding of the quotient)
         t32 = np.float32(thr)
@@ -214,9 +220,10 @@ def test_blend_band_test_on_values_at_the_threshold(dev):
         img = np.tile(vals2, (H * W + len(vals2) - 1) // len(vals2))[:H * W].reshape(H, W)
         plain = O.fibsem_tiles(img, B, ov)[:, None]
         want2 = O.fibsem_blend(plain[:, 0], (H, W), B, ov)
-        _, only2 = K().stitch_blend(torch.from_numpy(plain).to(dev), (1, 1, H, W), dev_axes(axes, dev), wins, epilogue=0,
-                                    want_out=False, want_mask=True, thr=thr)
-        assert np.array_equal(only2.cpu().numpy()[0, 0], O.binarize(want2, thr)), thr
+        for tab in (None, table):
+            _, only2 = K().stitch_blend(torch.from_numpy(plain).to(dev), (1, 1, H, W), dev_axes(axes, dev), wins, epilogue=0,
+                                        want_out=False, want_mask=True, thr=thr, window=tab)
+            assert np.array_equal(only2.cpu().numpy()[0, 0], O.binarize(want2, thr)), thr
 
 
 def test_kernels_write_nothing_outside_their_outputs(dev, rng):
@@ -247,14 +254,16 @@ def test_kernels_write_nothing_outside_their_outputs(dev, rng):
         w1 = torch.from_numpy(G.gauss_window_1d(B)).to(dev)
         one = torch.ones(1, dtype=torch.float64, device=dev)
         wz = w1 if nd == 3 else one
-        for want_out, epi in ((True, 0), (True, 1), (False, 1)):
+        wtab = kern.blend_window((wz, w1, w1)) if nd == 2 else None
+        for want_out, epi, use_table in ((True, 0, False), (True, 1, True), (False, 1, False), (False, 1, True), (False, 0, True)):
             obuf = torch.full((n_px + 2 * guard,), -3.25, dtype=torch.float32, device=dev)
             mbuf = torch.full((n_px + 2 * guard,), 9, dtype=torch.uint8, device=dev)
             n_words = C * Z * Y * ((X + 63) // 64)
             bbuf = torch.full((n_words + 2 * guard,), 0x5555, dtype=torch.int64, device=dev)
             _lib.call("be_stitch_blend_f32", tbuf[guard:].data_ptr(), obuf[guard:].data_ptr() if want_out else 0,
                       mbuf[guard:].data_ptr(), bbuf[guard:].data_ptr(), 1, C, Z, Y, X, az.ax.T, ay.ax.T, ax.ax.T, az.ax.B, ay.ax.B, ax.ax.B,
-                      az.ax.stride, ay.ax.stride, ax.ax.stride, wz.data_ptr(), w1.data_ptr(), w1.data_ptr(), epi, 0.5, stream)
+                      az.ax.stride, ay.ax.stride, ax.ax.stride, wz.data_ptr(), w1.data_ptr(), w1.data_ptr(),
+                      wtab.data_ptr() if (nd == 2 and use_table) else 0, epi, 0.5, stream)
             assert bool((mbuf[:guard] == 9).all()) and bool((mbuf[guard + n_px:] == 9).all()), (spatial, epi, "mask")
             assert bool((mbuf[guard:guard + n_px] <= 1).all())
             assert bool((bbuf[:guard] == 0x5555).all()) and bool((bbuf[guard + n_words:] == 0x5555).all()), (spatial, epi, "bits")
