@@ -876,8 +876,7 @@ static __device__ __noinline__ bool mask2d_exact(const float* __restrict__ tiles
     return (v > hi) || (!(v < lo) && be_sigmoid_f32(v) > thr);
 }
 
-template <int NB, bool ALL4>
-__global__ void __launch_bounds__(kThreads, NB) stitch_blend_mask2d_kernel(const float* __restrict__ tiles,
+__global__ void __launch_bounds__(kThreads, 4) stitch_blend_mask2d_kernel(const float* __restrict__ tiles,
                                                                           uint8_t* __restrict__ mask,
                                                                           uint32_t* __restrict__ bits32,
                                                                           const float* __restrict__ wtab, const Dims d,
@@ -930,10 +929,10 @@ __global__ void __launch_bounds__(kThreads, NB) stitch_blend_mask2d_kernel(const
                         W[j] = __fadd_rn(W[j], wv[j]);
                     }
                 };
-                // the pieces of the first y tile, then (one row in three) those of the second: two 16-byte loads in flight
-                // per thread at a time keeps the kernel at ~40 registers, i.e. six blocks per SM, and it is the number of
-                // loads in flight per SM that sets the pace
-                if (ALL4) {
+                // all pieces of the row are requested before the first is used: it is the number of loads in flight per SM
+                // that sets the pace (a pure-load kernel with this address pattern needs 30 us at eight blocks per SM and 43
+                // at three; benchmarks/readprobe.cu)
+                {
                     const float4 p0 = ld_stream_f4(reinterpret_cast<const float4*>(tiles + pa));
                     float4 p1, p2, p3;
                     if (two) p1 = ld_stream_f4(reinterpret_cast<const float4*>(tiles + (pa + ab)));
@@ -947,19 +946,6 @@ __global__ void __launch_bounds__(kThreads, NB) stitch_blend_mask2d_kernel(const
                         add4(p2, __ldg(reinterpret_cast<const float4*>(wtab + (wa - dwy))));
                         if (two) add4(p3, __ldg(reinterpret_cast<const float4*>(wtab + (wa - dwy + wab))));
                     }
-                } else {
-                    const float4 p0 = ld_stream_f4(reinterpret_cast<const float4*>(tiles + pa));
-                    float4 p1;
-                    if (two) p1 = ld_stream_f4(reinterpret_cast<const float4*>(tiles + (pa + ab)));
-                    add4(p0, __ldg(reinterpret_cast<const float4*>(wtab + wa)));
-                    if (two) add4(p1, __ldg(reinterpret_cast<const float4*>(wtab + (wa + wab))));
-                }
-                if (!ALL4 && nky > 1) {
-                    const float4 p2 = ld_stream_f4(reinterpret_cast<const float4*>(tiles + (pa + dky)));
-                    float4 p3;
-                    if (two) p3 = ld_stream_f4(reinterpret_cast<const float4*>(tiles + (pa + dky + ab)));
-                    add4(p2, __ldg(reinterpret_cast<const float4*>(wtab + (wa - dwy))));
-                    if (two) add4(p3, __ldg(reinterpret_cast<const float4*>(wtab + (wa - dwy + wab))));
                 }
                 unsigned slow = 0;
 #pragma unroll
@@ -1182,18 +1168,10 @@ extern "C" int be_stitch_blend_f32(const float* tiles, float* out, uint8_t* mask
         k.n_bands = (unsigned)n_bands;
         k.n_items = (unsigned)n_items;
         k.pieces = 2 * (int)((X + 63) / 64);
-        const char* nb_env = getenv("BE_MASK2D_BLOCKS");
-        const int nb = nb_env ? atoi(nb_env) : 4;
-        const dim3 g2(xblocks, (unsigned)G, 1);
-#define BE_MASK2D_LAUNCH(NB, ALL4) \
-    BE_CUDA(be_launch_pdl(stitch_blend_mask2d_kernel<NB, ALL4>, g2, dim3(kThreads), 0, (cudaStream_t)stream, tiles, mask, \
-                          (uint32_t*)bits, window, d, st, e, k))
-        if (nb == 3) BE_MASK2D_LAUNCH(3, false);
-        else if (nb == 13) BE_MASK2D_LAUNCH(3, true);
-        else if (nb == 14) BE_MASK2D_LAUNCH(4, true);
-        else if (nb == 5) BE_MASK2D_LAUNCH(5, false);
-        else BE_MASK2D_LAUNCH(4, false);
-#undef BE_MASK2D_LAUNCH
+        // four blocks of 63 registers per SM, all (up to four) loads of a row in flight at once: measured 42 us for the
+        // 4096^2 / 256-px workload against 44 (two loads at a time), 51 (three blocks) and 57 (six blocks, spilling)
+        BE_CUDA(be_launch_pdl(stitch_blend_mask2d_kernel, dim3(xblocks, (unsigned)G, 1), dim3(kThreads), 0, (cudaStream_t)stream,
+                              tiles, mask, (uint32_t*)bits, window, d, st, e, k));
         BE_LAUNCH_CHECK();
         return BE_OK;
     }
