@@ -9,6 +9,8 @@
 #include <cooperative_groups.h>
 #include <stdlib.h>
 
+#include <type_traits>
+
 #include "be_common.cuh"
 
 namespace cg = cooperative_groups;
@@ -697,7 +699,7 @@ __global__ void __launch_bounds__(kSampleThreads) qsel_sample_kernel(const float
 
 // the single streaming pass: classify every element against the (<= 2) brackets of its segment
 template <int NQ>
-__global__ void __launch_bounds__(kThreads) qsel_partition_kernel(const float* __restrict__ x, int64_t seg_len, int bps,
+__global__ void __launch_bounds__(kThreads, 4) qsel_partition_kernel(const float* __restrict__ x, int64_t seg_len, int bps,
                                                                   int64_t chunk, const double* __restrict__ q,
                                                                   SWorkspace w, int64_t n_seg) {
     __shared__ float s_buf[NQ][kStage];
@@ -720,117 +722,154 @@ __global__ void __launch_bounds__(kThreads) qsel_partition_kernel(const float* _
     if (threadIdx.x == 0) s_nan = 0;
     __syncthreads();
 
-    const int64_t begin = (int64_t)blockIdx.x * chunk;
-    const int64_t end = min(begin + chunk, seg_len);
     unsigned below[NQ], eqlo[NQ], eqhi[NQ], nans = 0;
 #pragma unroll
     for (int i = 0; i < NQ; ++i) below[i] = eqlo[i] = eqhi[i] = 0;
 
-    // rare path, one element: ties with the pivots are counted, the rest of the bracket is appended
-    auto take_inside = [&](float v) {
-        if (v != v) {   // NaNs are flagged by the common path (they fail both of its comparisons) and counted here
-            ++nans;
-            return;
-        }
-#pragma unroll
-        for (int i = 0; i < NQ; ++i) {
-            if (v >= flo[i] && v <= fhi[i]) {
-                if (v == flo[i]) {
-                    ++eqlo[i];
-                } else if (v == fhi[i]) {
-                    ++eqhi[i];
-                } else {
-                    const unsigned pos = atomicAdd(&s_n[i], 1u);
-                    if (pos < kStage) {
-                        s_buf[i][pos] = v;
-                    } else {  // staging full: straight to the global list (still counted if that is full too)
-                        const unsigned g = atomicAdd(&tasks[i].n_mid, 1u);
-                        if (g < w.cap) w.cand[(seg * NQ + i) * w.cap + g] = v;
-                        atomicMax(&s_kmax[i], f32_to_key(v));
-                        atomicMax(&s_nkmin[i], ~f32_to_key(v));
-                    }
-                }
-            }
-        }
-    };
-    // common path, one element: a compare-and-count per bracket; returns whether the element needs the rare path
-    auto classify = [&](float v) -> bool {
-        bool flagged = false;
-#pragma unroll
-        for (int i = 0; i < NQ; ++i) {
-            const bool lt = v < flo[i];
-            below[i] += lt;
-            flagged |= !(lt | (v > fhi[i]));   // inside the bracket — or NaN, which the rare path sorts out
-        }
-        return flagged;
-    };
+    // Two brackets that do not overlap (the usual case: a low and a high percentile) leave ~96 % of the elements strictly
+    // between them, and such an element only counts as "below the upper bracket": two compares and one add.  Everything
+    // else — below or inside the lower bracket, inside or above the upper one, NaN — goes through the rare path, which
+    // then does all the counting for it.
+    const bool fastmid = (NQ == 2) && (fhi[0] < flo[NQ - 1]);
 
-    // The chunk is streamed in rounds of 32 K elements; after each round the staged candidates move to the global lists
-    // (one reservation per block and bracket).  A round brings ~1 % of 32 K elements per bracket, well inside the 1024
-    // staging slots — without rounds a long chunk (a 512^3 volume gives every block 180 K elements) overflows the
-    // staging area and every further candidate costs a global atomic on one address (partition 1.24 ms -> see profiles).
-    constexpr int64_t kRound = (int64_t)kThreads * 16 * 8;
+    // Work is dealt out in spans of 4096 elements (16 per thread), span j going to block j mod bps: a block's spans are
+    // spread over the whole segment.  With one contiguous chunk per block the blocks that happened to hold a bright
+    // structure (most of an image's top percentile sits in a few places) had several times the rare-path work of the
+    // others, and a kernel that is one wave of blocks ends with its slowest block.
+    constexpr int64_t kSpan = (int64_t)kThreads * 16;
+    constexpr int kSpansPerRound = 8;   // staged candidates move to the global lists every 8 spans (32 K elements)
     unsigned kx[NQ], nk[NQ];   // key range of the candidates this thread moved
 #pragma unroll
     for (int i = 0; i < NQ; ++i) kx[i] = nk[i] = 0;
-    for (int64_t r0 = begin; r0 < end; r0 += kRound) {
-        const float* p = xs + r0;
-        const int64_t n = min(end, r0 + kRound) - r0;
-        if ((((uintptr_t)p) & 15) == 0) {
-            // 16 elements per thread and iteration: all of them take the cheap path first, and the 2-3 % that fall inside a
-            // bracket are handled afterwards from a 16-bit flag word, so the divergent code runs once per 16 elements
-            const float4* p4 = reinterpret_cast<const float4*>(p);
-            const int64_t n4 = n >> 2;
-            for (int64_t base = threadIdx.x; base < n4; base += 4 * kThreads) {
-                float4 v[4];
+    const int head = (int)(((16 - ((uintptr_t)xs & 15)) & 15) >> 2);   // elements before the first 16-byte boundary
+    const int64_t n_body = (seg_len > head) ? seg_len - head : 0;
+    const int64_t n_spans = (n_body + kSpan - 1) / kSpan;
+
+    auto stream = [&](auto fast_tag) {
+        constexpr bool FAST = decltype(fast_tag)::value;
+        // rare path, one element: ties with the pivots are counted, the rest of the bracket is appended
+        auto take_inside = [&](float v) {
+            if (v != v) {   // NaNs are flagged by the common path (they fail its comparisons) and counted here
+                ++nans;
+                return;
+            }
+            if (FAST) {
+                if (v <= fhi[0]) {
+                    ++below[NQ - 1];
+                    if (v < flo[0]) {
+                        ++below[0];
+                        return;
+                    }
+                } else if (v > fhi[NQ - 1]) {
+                    return;
+                }
+            }
 #pragma unroll
-                for (int k = 0; k < 4; ++k)
-                    if (base + k * kThreads < n4) v[k] = __ldg(p4 + base + k * kThreads);   // allocating: the rare path re-reads from L1
-                unsigned flags = 0;
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    if (base + k * kThreads < n4) {
-                        flags |= (unsigned)classify(v[k].x) << (4 * k + 0);
-                        flags |= (unsigned)classify(v[k].y) << (4 * k + 1);
-                        flags |= (unsigned)classify(v[k].z) << (4 * k + 2);
-                        flags |= (unsigned)classify(v[k].w) << (4 * k + 3);
+            for (int i = 0; i < NQ; ++i) {
+                if (v >= flo[i] && v <= fhi[i]) {
+                    if (v == flo[i]) {
+                        ++eqlo[i];
+                    } else if (v == fhi[i]) {
+                        ++eqhi[i];
+                    } else {
+                        const unsigned pos = atomicAdd(&s_n[i], 1u);
+                        if (pos < kStage) {
+                            s_buf[i][pos] = v;
+                        } else {  // staging full: straight to the global list (still counted if that is full too)
+                            const unsigned g = atomicAdd(&tasks[i].n_mid, 1u);
+                            if (g < w.cap) w.cand[(seg * NQ + i) * w.cap + g] = v;
+                            atomicMax(&s_kmax[i], f32_to_key(v));
+                            atomicMax(&s_nkmin[i], ~f32_to_key(v));
+                        }
                     }
                 }
-                while (flags) {  // (measured: faster than 16 statically indexed copies of the rare path)
-                    const int b = __ffs(flags) - 1;
-                    flags &= flags - 1;
-                    // the element is read again (an L1 hit) rather than picked out of v[]: indexing the register array
-                    // dynamically would put all of v[] in local memory, with four 16-byte stores on the common path
-                    take_inside(__ldg(p + ((base + (int64_t)(b >> 2) * kThreads) << 2) + (b & 3)));
+            }
+        };
+        // common path, one element; returns whether the element needs the rare path
+        auto classify = [&](float v) -> bool {
+            if (FAST) {
+                const bool mid = (v > fhi[0]) & (v < flo[NQ - 1]);
+                below[NQ - 1] += mid;
+                return !mid;
+            }
+            bool flagged = false;
+#pragma unroll
+            for (int i = 0; i < NQ; ++i) {
+                const bool lt = v < flo[i];
+                below[i] += lt;
+                flagged |= !(lt | (v > fhi[i]));   // inside the bracket — or NaN, which the rare path sorts out
+            }
+            return flagged;
+        };
+        // the staged candidates move to the global lists (one reservation per block and bracket)
+        auto flush = [&]() {
+            __syncthreads();   // staging is complete
+            if (threadIdx.x < NQ) {
+                const unsigned n_st = min(s_n[threadIdx.x], (unsigned)kStage);
+                s_base[threadIdx.x] = n_st ? atomicAdd(&tasks[threadIdx.x].n_mid, n_st) : 0u;
+            }
+            __syncthreads();
+#pragma unroll
+            for (int i = 0; i < NQ; ++i) {
+                const unsigned n_st = min(s_n[i], (unsigned)kStage), base = s_base[i];
+                float* dst = w.cand + (seg * NQ + i) * w.cap;
+                for (unsigned k = threadIdx.x; k < n_st; k += kThreads) {
+                    const float v = s_buf[i][k];
+                    if (base + k < w.cap) dst[base + k] = v;
+                    kx[i] = max(kx[i], f32_to_key(v));
+                    nk[i] = max(nk[i], ~f32_to_key(v));
                 }
             }
-            for (int64_t i = (n4 << 2) + threadIdx.x; i < n; i += kThreads)
-                if (classify(p[i])) take_inside(p[i]);
-        } else {
-            for (int64_t i = threadIdx.x; i < n; i += kThreads)
-                if (classify(p[i])) take_inside(p[i]);
-        }
-        __syncthreads();   // this round's staging is complete
-        if (threadIdx.x < NQ) {
-            const unsigned n_st = min(s_n[threadIdx.x], (unsigned)kStage);
-            s_base[threadIdx.x] = n_st ? atomicAdd(&tasks[threadIdx.x].n_mid, n_st) : 0u;
-        }
-        __syncthreads();
+            __syncthreads();   // staging read out: free again
+            if (threadIdx.x < NQ) s_n[threadIdx.x] = 0;
+            __syncthreads();
+        };
+
+        if (blockIdx.x == 0 && (int)threadIdx.x < head && (int64_t)threadIdx.x < seg_len)
+            if (classify(xs[threadIdx.x])) take_inside(xs[threadIdx.x]);
+        const float* body = xs + head;
+        int in_round = 0;
+        for (int64_t span = blockIdx.x; span < n_spans; span += bps) {
+            const float* p = body + span * kSpan;
+            const int64_t n = min(kSpan, n_body - span * kSpan);
+            // 16 elements per thread: all of them take the cheap path first, and the few per cent that need more are
+            // handled afterwards from a 16-bit flag word, so the divergent code runs once per 16 elements
+            const float4* p4 = reinterpret_cast<const float4*>(p);
+            const int n4 = (int)(n >> 2);
+            float4 v[4];
 #pragma unroll
-        for (int i = 0; i < NQ; ++i) {
-            const unsigned n_st = min(s_n[i], (unsigned)kStage), base = s_base[i];
-            float* dst = w.cand + (seg * NQ + i) * w.cap;
-            for (unsigned k = threadIdx.x; k < n_st; k += kThreads) {
-                const float v = s_buf[i][k];
-                if (base + k < w.cap) dst[base + k] = v;
-                kx[i] = max(kx[i], f32_to_key(v));
-                nk[i] = max(nk[i], ~f32_to_key(v));
+            for (int k = 0; k < 4; ++k)
+                if ((int)threadIdx.x + k * kThreads < n4) v[k] = __ldg(p4 + threadIdx.x + k * kThreads);   // allocating: the rare path re-reads from L1
+            unsigned flags = 0;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                if ((int)threadIdx.x + k * kThreads < n4) {
+                    flags |= (unsigned)classify(v[k].x) << (4 * k + 0);
+                    flags |= (unsigned)classify(v[k].y) << (4 * k + 1);
+                    flags |= (unsigned)classify(v[k].z) << (4 * k + 2);
+                    flags |= (unsigned)classify(v[k].w) << (4 * k + 3);
+                }
+            }
+            while (flags) {  // (measured: faster than 16 statically indexed copies of the rare path)
+                const int b = __ffs(flags) - 1;
+                flags &= flags - 1;
+                // the element is read again (an L1 hit) rather than picked out of v[]: indexing the register array
+                // dynamically would put all of v[] in local memory, with four 16-byte stores on the common path
+                take_inside(__ldg(p + (((int)threadIdx.x + (b >> 2) * kThreads) << 2) + (b & 3)));
+            }
+            for (int i = (n4 << 2) + threadIdx.x; i < n; i += kThreads)   // the segment's last, ragged span
+                if (classify(p[i])) take_inside(p[i]);
+            if (++in_round == kSpansPerRound) {
+                flush();
+                in_round = 0;
             }
         }
-        __syncthreads();   // staging read out: free for the next round
-        if (threadIdx.x < NQ) s_n[threadIdx.x] = 0;
-        __syncthreads();
-    }
+        flush();
+    };
+    if (fastmid)
+        stream(std::true_type{});
+    else
+        stream(std::false_type{});
 #pragma unroll
     for (int i = 0; i < NQ; ++i) {
         const unsigned b = __reduce_add_sync(0xffffffffu, below[i]);
@@ -1372,9 +1411,9 @@ static int quantile_sampled(const float* x, int64_t n_seg, int64_t seg_len, cons
     for (int64_t s0 = 0; s0 < n_seg; s0 += per_pass) {
         const int64_t ns = (n_seg - s0 < per_pass) ? (n_seg - s0) : per_pass;
         const int64_t nt = ns * n_q;
-        // the partition kernel keeps 5 blocks of 48 registers per SM resident and a block runs for most of the kernel:
-        // exactly one wave (measured: 8 blocks per SM = 1.6 waves 80 us for the stage, 5 = 74.6, 4 = 76.7, 10 = 76.8)
-        const SegSplit sp = split_segment(ns, seg_len, (int64_t)BE_SM_COUNT * 5);
+        // the partition kernel keeps 4 blocks of 60 registers per SM resident and a block runs for most of the kernel:
+        // exactly one wave; a block's spans are interleaved with the other blocks' (see the kernel)
+        const SegSplit sp = split_segment(ns, seg_len, (int64_t)BE_SM_COUNT * 4);
         const SWorkspace w = carve_sample_ws(ws, ns, n_q, seg_len);
         const float* xs = x + s0 * seg_len;
         double* qs = quant + s0 * n_q;
