@@ -512,7 +512,7 @@ def run_b200(args):
                             "frac_of_peak": round(gbs / peak, 4)}
         dom = max(path_stages, key=lambda n: stages[n]["ms"])
         traffic, traffic_src = None, None
-        tp = os.path.join(ROOT, "profiles", "r1_traffic.json")
+        tp = os.path.join(ROOT, "profiles", "r2_traffic.json")
         if os.path.exists(tp):  # dram__bytes_read.sum + dram__bytes_write.sum of the stage's kernels, one ncu --set full capture
             tj = json.load(open(tp))
             if dom in tj.get("stages", {}):

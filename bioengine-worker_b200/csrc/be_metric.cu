@@ -124,20 +124,20 @@ __device__ __forceinline__ void ov_global_add(const OvGlobal& G, unsigned long l
     if (t && p) table_add(G.K, G.Cn, G.capacity, key, cnt, G.st);
 }
 
+// the CTA's shared table: a cheap 32-bit hash of the two labels, the first probe is the claim itself (no look first)
 __device__ __forceinline__ void ov_add(unsigned long long* sk, unsigned* sc, const OvGlobal& G, unsigned long long key,
                                        unsigned cnt, unsigned* bg_true, unsigned* bg_pred) {
-    unsigned slot = (unsigned)mix64(key) & (kOvSlots - 1);
+    const unsigned h = ((unsigned)(key >> 32) * 0x9E3779B1u) ^ ((unsigned)key * 0x85EBCA6Bu);
+    unsigned slot = h >> (32 - 11);
+    static_assert(kOvSlots == (1 << 11), "slot bits");
+#pragma unroll 1
     for (int probe = 0; probe < kOvProbes; ++probe) {
-        unsigned long long old = sk[slot];
-        if (old != key) {
-            if (old == kEmpty) old = atomicCAS(&sk[slot], kEmpty, key);
-            if (old != kEmpty && old != key) {
-                slot = (slot + 1) & (kOvSlots - 1);
-                continue;
-            }
+        const unsigned long long old = atomicCAS(&sk[slot], kEmpty, key);
+        if (old == kEmpty || old == key) {
+            atomicAdd(&sc[slot], cnt);
+            return;
         }
-        atomicAdd(&sc[slot], cnt);
-        return;
+        slot = (slot + 1) & (kOvSlots - 1);
     }
     ov_global_add(G, key, cnt, bg_true, bg_pred);   // crowded tile (far more than ~1500 distinct pairs): bypass
 }

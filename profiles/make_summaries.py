@@ -8,8 +8,9 @@ import csv, json, re, sys
 STAGES = {
     "quantile_select": ["qsel_sample_kernel", "qsel_partition_kernel", "qsel_cluster_kernel"],
     "normalise+tile_gather": ["tile_gather_tma_kernel", "tile_gather_kernel"],
-    "blend_stitch+sigmoid+binarize": ["stitch_blend_rows_kernel", "stitch_blend_kernel"],
+    "blend_stitch+sigmoid+binarize": ["stitch_blend_mask2d_kernel", "stitch_blend_rows_kernel", "stitch_blend_kernel"],
     "ccl": ["ccl_tile_kernel", "ccl_edge_kernel", "ccl_number_kernel", "ccl_resolve_kernel"],
+    "map(label_overlap+match_counts)": ["overlap_init_kernel", "overlap_kernel", "match_kernel"],
 }
 COLS = {
     "us": ("gpu__time_duration.sum", 1e-3),  # ns -> us (unit checked below)
