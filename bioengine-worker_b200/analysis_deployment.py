@@ -110,7 +110,10 @@ class MitoAnalysisDeployment:
         `cleanup=True`, the default, applies remove_small_objects(300) and binary_closing(disk(4)) before labelling; see the
         module docstring for what still differs from the reference's watershed instances)."""
         t0 = time.time()
-        image_np = np.array(image, dtype=np.float32)
+        if isinstance(image, np.ndarray) and image.dtype.name in K.NUMPY_DEVICE_DTYPES:
+            image_np = image   # converted to float32 on the device (same values as the reference's host cast)
+        else:
+            image_np = np.array(image, dtype=np.float32)
         if image_np.ndim != 2:
             raise ValueError(f"Expected 2-D image, got shape {image_np.shape}.")
         H, W = image_np.shape

@@ -81,6 +81,11 @@ __device__ __forceinline__ float4 ld_stream_f4(const float4* p) {
                  : "l"(p));
     return r;
 }
+__device__ __forceinline__ int4 ld_stream_i4(const int4* p) {
+    int4 r;
+    asm("ld.global.nc.L1::no_allocate.v4.s32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
 __device__ __forceinline__ void st_stream_f4(float4* p, float4 v) {
     asm volatile("st.global.L1::no_allocate.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z),
                  "f"(v.w));

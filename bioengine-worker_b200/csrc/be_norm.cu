@@ -7,6 +7,7 @@
 //   be_elementwise_f32 clip / scale_linear / sigmoid
 //   be_binarize_f32_u8 x > thr
 #include <cooperative_groups.h>
+#include <cuda_fp16.h>
 #include <stdlib.h>
 
 #include <type_traits>
@@ -1314,6 +1315,46 @@ __global__ void __launch_bounds__(kSelThreads)
     }
 }
 
+// ---- ensure_dtype(float32) on the device ----
+template <typename T>
+__device__ __forceinline__ float to_f32(T v) { return (float)v; }
+template <>
+__device__ __forceinline__ float to_f32<int32_t>(int32_t v) { return __int2float_rn(v); }
+template <>
+__device__ __forceinline__ float to_f32<uint32_t>(uint32_t v) { return __uint2float_rn(v); }
+template <>
+__device__ __forceinline__ float to_f32<double>(double v) { return __double2float_rn(v); }
+template <>
+__device__ __forceinline__ float to_f32<__half>(__half v) { return __half2float(v); }
+
+// 16 input bytes per thread and iteration (one 16-byte load), 16-byte stores
+template <typename T>
+__global__ void __launch_bounds__(kThreads) cast_f32_kernel(const T* __restrict__ x, float* __restrict__ y, int64_t n) {
+    constexpr int kPer = 16 / (int)sizeof(T);
+    const int64_t stride = (int64_t)gridDim.x * kThreads;
+    const int64_t nv = n / kPer;
+    if (((((uintptr_t)x) | ((uintptr_t)y)) & 15) == 0) {
+        for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < nv; i += stride) {
+            const int4 raw = ld_stream_i4(reinterpret_cast<const int4*>(x) + i);
+            const T* e = reinterpret_cast<const T*>(&raw);
+            float out[kPer];
+#pragma unroll
+            for (int j = 0; j < kPer; ++j) out[j] = to_f32<T>(e[j]);
+            if (kPer >= 4) {
+#pragma unroll
+                for (int j = 0; j < kPer; j += 4)
+                    st_stream_f4(reinterpret_cast<float4*>(y + i * kPer + j), make_float4(out[j], out[j + 1], out[j + 2], out[j + 3]));
+            } else {
+#pragma unroll
+                for (int j = 0; j < kPer; ++j) y[i * kPer + j] = out[j];
+            }
+        }
+        for (int64_t i = nv * kPer + (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n; i += stride) y[i] = to_f32<T>(x[i]);
+    } else {
+        for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n; i += stride) y[i] = to_f32<T>(x[i]);
+    }
+}
+
 inline int stream_grid(int64_t n_items_per_thread_units) {
     int64_t blocks = (n_items_per_thread_units + kThreads - 1) / kThreads;
     const int64_t cap = (int64_t)BE_SM_COUNT * 16;
@@ -1546,6 +1587,26 @@ extern "C" int be_elementwise_f32(const float* x, float* y, int64_t n, int op, f
         case BE_OP_SCALE_LINEAR: elementwise_kernel<BE_OP_SCALE_LINEAR><<<g, kThreads, 0, s>>>(x, y, n, a, b); break;
         case BE_OP_SIGMOID: elementwise_kernel<BE_OP_SIGMOID><<<g, kThreads, 0, s>>>(x, y, n, a, b); break;
         default: BE_REQUIRE(false, BE_ERR_INVALID_ARG, "be_elementwise_f32: unknown op %d", op);
+    }
+    BE_LAUNCH_CHECK();
+    return BE_OK;
+}
+
+extern "C" int be_cast_f32(const void* x, int dtype, float* y, int64_t n, be_stream_t stream) {
+    BE_REQUIRE(x && y, BE_ERR_INVALID_ARG, "be_cast_f32: null pointer");
+    BE_REQUIRE(n > 0, BE_ERR_INVALID_ARG, "be_cast_f32: empty input");
+    cudaStream_t s = (cudaStream_t)stream;
+    const int g = stream_grid((n + 7) / 8);
+    switch (dtype) {
+        case BE_DTYPE_U8: cast_f32_kernel<uint8_t><<<g, kThreads, 0, s>>>((const uint8_t*)x, y, n); break;
+        case BE_DTYPE_I8: cast_f32_kernel<int8_t><<<g, kThreads, 0, s>>>((const int8_t*)x, y, n); break;
+        case BE_DTYPE_U16: cast_f32_kernel<uint16_t><<<g, kThreads, 0, s>>>((const uint16_t*)x, y, n); break;
+        case BE_DTYPE_I16: cast_f32_kernel<int16_t><<<g, kThreads, 0, s>>>((const int16_t*)x, y, n); break;
+        case BE_DTYPE_I32: cast_f32_kernel<int32_t><<<g, kThreads, 0, s>>>((const int32_t*)x, y, n); break;
+        case BE_DTYPE_U32: cast_f32_kernel<uint32_t><<<g, kThreads, 0, s>>>((const uint32_t*)x, y, n); break;
+        case BE_DTYPE_F16: cast_f32_kernel<__half><<<g, kThreads, 0, s>>>((const __half*)x, y, n); break;
+        case BE_DTYPE_F64: cast_f32_kernel<double><<<g, kThreads, 0, s>>>((const double*)x, y, n); break;
+        default: BE_REQUIRE(false, BE_ERR_INVALID_ARG, "be_cast_f32: unknown dtype code %d", dtype);
     }
     BE_LAUNCH_CHECK();
     return BE_OK;

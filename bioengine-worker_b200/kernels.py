@@ -166,6 +166,25 @@ def scale_mean_variance(x: torch.Tensor, ref_norm: torch.Tensor, n_seg: int, eps
     return y
 
 
+_CAST_CODES = {torch.uint8: 0, torch.int8: 1, torch.uint16: 2, torch.int16: 3, torch.int32: 4, torch.uint32: 5,
+               torch.float16: 6, torch.float64: 7}
+NUMPY_DEVICE_DTYPES = ("uint8", "int8", "uint16", "int16", "int32", "uint32", "float16", "float32", "float64")
+
+
+@_on_tensor_device
+def to_float32(x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """`ensure_dtype(float32)` on the device: an integer / half / double CUDA tensor → float32 (numpy astype rounding)."""
+    if not x.is_cuda or not x.is_contiguous():
+        raise ValueError("x must be a contiguous CUDA tensor")
+    if x.dtype == torch.float32:
+        return x
+    if x.dtype not in _CAST_CODES:
+        raise ValueError(f"unsupported input dtype {x.dtype}")
+    out = torch.empty(x.shape, dtype=torch.float32, device=x.device) if out is None else _check(out, torch.float32, "out")
+    _lib.call("be_cast_f32", x.data_ptr(), _CAST_CODES[x.dtype], out.data_ptr(), x.numel(), _stream())
+    return out
+
+
 def sigmoid(x, out=None):
     return elementwise(x, _lib.BE_OP_SIGMOID, 0.0, 0.0, out)
 

@@ -136,21 +136,43 @@ class TiledPipeline:
             res["n_labels"] = n
         return res
 
-    def run(self, image, model: Callable[[torch.Tensor], torch.Tensor]) -> Dict[str, torch.Tensor]:
-        """image: host ndarray / CPU tensor (uploaded here) or CUDA tensor of the sample shape."""
-        x = image if isinstance(image, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(image, dtype=np.float32))
+    def upload(self, image) -> torch.Tensor:
+        """Host ndarray / CPU tensor / CUDA tensor of the sample shape → float32 CUDA tensor.  Integer, half and double
+        inputs cross PCIe in their own element type and are converted on the device (`ensure_dtype(float32)`, the op
+        bioimageio.core puts in front of every pre-processing chain)."""
+        if isinstance(image, torch.Tensor):
+            x = image
+        else:
+            a = np.asarray(image)
+            if a.dtype.name not in K.NUMPY_DEVICE_DTYPES:
+                a = a.astype(np.float32)
+            x = torch.from_numpy(np.ascontiguousarray(a))
         if tuple(x.shape) != self.shape:
             raise ValueError(f"expected sample shape {self.shape}, got {tuple(x.shape)}")
-        x = x.to(self.device, dtype=torch.float32, non_blocking=True).contiguous()
+        x = x.to(self.device, non_blocking=True).contiguous()
+        return K.to_float32(x)
+
+    def run(self, image, model: Callable[[torch.Tensor], torch.Tensor]) -> Dict[str, torch.Tensor]:
+        """image: host ndarray / CPU tensor (uploaded here) or CUDA tensor of the sample shape, any of the element types
+        `upload` takes."""
+        x = self.upload(image)
         tiles = self.preprocess_and_tile(x)
         logits = self.forward(model, tiles)
         return self.stitch_and_label(logits)
+
+    def _rawbuf(self, b: int, dtype: torch.dtype) -> torch.Tensor:
+        if not hasattr(self, "_raw"):
+            self._raw = {}
+        if (b, dtype) not in self._raw:
+            self._raw[(b, dtype)] = torch.empty(self.shape, dtype=dtype, device=self.device)
+        return self._raw[(b, dtype)]
 
     def run_stream(self, host_images: Sequence[torch.Tensor], model: Callable[[torch.Tensor], torch.Tensor],
                    host_labels: Sequence[torch.Tensor], host_counts: Sequence[torch.Tensor]):
         """Throughput mode for a stream of same-shaped images (microscope frames, a screening shard).
 
-        host_images[i] (pinned CPU fp32, sample shape) → host_labels[i] (pinned int32, sample shape), host_counts[i]
+        host_images[i] (pinned CPU tensor of the sample shape; fp32, or uint8 / uint16 / ... frames that are converted on
+        the device after the upload) → host_labels[i] (pinned int32, sample shape), host_counts[i]
         (pinned int32 [N]).  Three streams: the upload of image i+1 and the download of labels i-1 overlap the kernels
         of image i; device buffers are double-buffered, so the only requirement on the caller is that host_labels[i]
         and host_labels[i+2] may alias but host_labels[i] and host_labels[i+1] may not.  Returns after everything has
@@ -175,7 +197,12 @@ class TiledPipeline:
             with torch.cuda.stream(s_in):
                 if i >= 2:
                     s_in.wait_event(ev_run[b])      # the kernels that read this input buffer two images ago
-                self._xbuf[b].copy_(img, non_blocking=True)
+                if img.dtype == torch.float32:
+                    self._xbuf[b].copy_(img, non_blocking=True)
+                else:   # raw frame up, converted on the device (same stream, so the event below covers both)
+                    raw = self._rawbuf(b, img.dtype)
+                    raw.copy_(img, non_blocking=True)
+                    K.to_float32(raw, out=self._xbuf[b])
                 ev_in[b].record(s_in)
             with torch.cuda.stream(s_run):
                 s_run.wait_event(ev_in[b])

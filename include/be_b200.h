@@ -98,6 +98,20 @@ int be_elementwise_f32(const float* x, float* y, int64_t n, int op, float a, flo
  * at analysis_deployment.py:166. */
 int be_binarize_f32_u8(const float* x, uint8_t* y, int64_t n, float thr, be_stream_t stream);
 
+/* y = (float)x for the integer / half / double element types a microscope or a caller hands over — the leading
+ * `EnsureDtype(float32)` bioimageio.core inserts before the pre-processing (Appendix A.2) and
+ * `np.array(image, dtype=np.float32)` of analysis_deployment.py:236, on the device, so that a uint8 / uint16 frame crosses
+ * PCIe at its own size.  Rounding as numpy's astype (to nearest even). */
+#define BE_DTYPE_U8 0
+#define BE_DTYPE_I8 1
+#define BE_DTYPE_U16 2
+#define BE_DTYPE_I16 3
+#define BE_DTYPE_I32 4
+#define BE_DTYPE_U32 5
+#define BE_DTYPE_F16 6
+#define BE_DTYPE_F64 7
+int be_cast_f32(const void* x, int dtype, float* y, int64_t n, be_stream_t stream);
+
 /* ---- halo tiles --------------------------------------------------------------------------------- */
 
 /* Gather halo tiles (any padding rule) into the batched tile tensor, fused with the normalise-apply so

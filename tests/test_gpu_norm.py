@@ -292,3 +292,46 @@ def test_selection_with_the_portable_cluster_size(dev):
     env = dict(os.environ, BE_B200_CLUSTER_MAX="8", PYTHONPATH=root + os.pathsep + os.environ.get("PYTHONPATH", ""))
     out = subprocess.run([sys.executable, "-c", code], env=env, cwd=root, capture_output=True, text=True, timeout=300)
     assert out.returncode == 0 and "ok" in out.stdout, out.stderr[-2000:]
+
+
+@pytest.mark.parametrize("dtype", ["uint8", "int8", "uint16", "int16", "int32", "uint32", "float16", "float64"])
+@pytest.mark.parametrize("n", [1, 7, 4096, 100_003])
+def test_cast_to_float32_is_numpy_astype(dtype, n, dev, rng):
+    """`ensure_dtype(float32)` on the device: every value of the small types, rounding of the wide ones."""
+    dt = np.dtype(dtype)
+    if dt.kind in "ui":
+        info = np.iinfo(dt)
+        x = rng.integers(info.min, info.max, size=n, endpoint=True, dtype=dt)
+        x[: min(n, 4)] = [info.min, info.max, info.max - 1, 0][: min(n, 4)]
+    elif dt == np.float16:
+        x = rng.standard_normal(n).astype(dt)
+        x[: min(n, 3)] = [np.inf, -0.0, 6.1e-5][: min(n, 3)]
+    else:
+        x = rng.standard_normal(n) * 10.0 ** rng.integers(-40, 40, n)     # beyond the float32 range too
+    for off in (0, 1):   # an unaligned start as well
+        t = torch.from_numpy(x).to(dev)[off:]
+        if t.numel() == 0:
+            continue
+        with np.errstate(over="ignore"):
+            want = x[off:].astype(np.float32)
+        got = K().to_float32(t.contiguous() if off == 0 else t.clone()).cpu().numpy()
+        assert np.array_equal(got, want, equal_nan=True), (dtype, n, off)
+
+
+def test_pipeline_takes_uint16_frames(dev):
+    """A uint16 frame uploaded as such gives exactly what its float32 copy gives (C5's frames are uint16)."""
+    from bioengine_worker_b200.pipeline import PipelineSpec, TiledPipeline
+
+    img16 = np.clip(O.synthetic_image((1, 1, 200, 264), 30, seed=9), 0, 65535).astype(np.uint16)
+    spec = PipelineSpec(block=(64, 64), halo=(8, 8), convention="bioimageio", preprocess="scale_range")
+    pipe = TiledPipeline(img16.shape, spec, device=dev)
+    fwd = lambda t: (t * 6.0 - 2.0).contiguous()
+    a = pipe.run(img16, fwd)
+    b = pipe.run(img16.astype(np.float32), fwd)
+    assert torch.equal(a["labels"], b["labels"]) and torch.equal(a["mask"], b["mask"])
+    host_l = [torch.empty((1, 1, 200, 264), dtype=torch.int32).pin_memory() for _ in range(3)]
+    host_n = [torch.empty((1,), dtype=torch.int32).pin_memory() for _ in range(3)]
+    frames = [torch.from_numpy(img16).pin_memory() for _ in range(3)]
+    pipe.run_stream(frames, fwd, host_l, host_n).synchronize()
+    for l in host_l:
+        assert np.array_equal(l.numpy(), a["labels"].cpu().numpy())

@@ -153,3 +153,31 @@ def test_c3_full_size_properties(dev):
     slab = mask[0, 0, :40].cpu().numpy()
     got = K.ccl(mask[0, :, :40].contiguous(), 3)[0].cpu().numpy()[0]
     assert np.array_equal(got, O.label(slab, 3))
+
+
+def test_c3_full_size_labels_equal_scipy(dev):
+    """BASELINE config 3 at full size: the 512^3 mask the device pipeline produces, labelled on the device (26- and
+    6-connected, from the packed mask) and by scipy on the identical mask: equal, numbering included."""
+    import scipy.ndimage as ndi
+
+    from bioengine_worker_b200 import kernels as K
+
+    S = 512
+    g = torch.Generator(device=dev).manual_seed(33)
+    coarse = torch.randn((1, 1, 20, 20, 20), device=dev, generator=g)
+    x = torch.nn.functional.interpolate(coarse, size=(S, S, S), mode="trilinear", align_corners=False)[0, 0]
+    x = x + 0.35 * torch.randn(x.shape, device=dev, generator=g)     # blobs with ragged, speckled borders
+    mask = (x > 0.9).to(torch.uint8).contiguous()
+    del x
+    m_np = mask.cpu().numpy()
+    from tests.test_gpu_ccl import pack_bits
+
+    bits = torch.from_numpy(pack_bits(m_np.astype(bool))).to(dev)
+    for conn in (3, 1):
+        want, n_want = ndi.label(m_np, structure=ndi.generate_binary_structure(3, conn))
+        got, n = K.ccl_bits(bits.reshape(-1), (1, S, S, S), conn)
+        assert int(n.item()) == n_want
+        assert np.array_equal(got.cpu().numpy()[0], want.astype(np.int32))
+        del want
+    got8, n8 = K.ccl(mask[None], 3)
+    assert torch.equal(got8, K.ccl_bits(bits.reshape(-1), (1, S, S, S), 3)[0])
