@@ -36,6 +36,7 @@ SIGNATURES = {
     "be_quantile_f32_noalloc": (_i32, [_ptr, _i64, _i64, _ptr, _i32, _f64, _ptr, _ptr, _ptr]),
     "be_normalize_f32": (_i32, [_ptr, _ptr, _i64, _i64, _ptr, _i32, _f32, _f32, _ptr]),
     "be_elementwise_f32": (_i32, [_ptr, _ptr, _i64, _i32, _f32, _f32, _ptr]),
+    "be_scale_linear_seg_f32": (_i32, [_ptr, _ptr, _i64, _i64, _ptr, _ptr]),
     "be_cast_f32": (_i32, [_ptr, _i32, _ptr, _i64, _ptr]),
     "be_binarize_f32_u8": (_i32, [_ptr, _ptr, _i64, _f32, _ptr]),
     "be_tile_gather_f32": (_i32, [_ptr, _ptr] + [_i64] * 5 + [_i32] * 6 + [_ptr] * 4 + [_i32, _i32, _f32, _f32, _ptr]),

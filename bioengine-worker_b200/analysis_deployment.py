@@ -29,6 +29,7 @@ import numpy as np
 import torch
 
 from . import kernels as K, models
+from ._serve_compat import deployment, schema_method
 from .pipeline import PipelineSpec, TiledPipeline
 
 _MODEL_ID = "b200/random-init-unet2d"
@@ -69,6 +70,7 @@ def region_properties(sums: np.ndarray, pixel_size_nm: float) -> Dict[str, list]
     }
 
 
+@deployment(ray_actor_options={"num_cpus": 2, "num_gpus": 1, "memory": 4 * 1024**3})
 class MitoAnalysisDeployment:
     """Mitochondria instance segmentation from a 2-D EM image, tiled inference on one B200."""
 
@@ -79,7 +81,22 @@ class MitoAnalysisDeployment:
         self._model = model if model is not None else models.build_model("UNet2d", seed=0, final_sigmoid=True).to(self.device)
         self._pipes: Dict[tuple, TiledPipeline] = {}
 
+    # ---- lifecycle hooks of the app builder (ref: analysis_deployment.py:53-80, bioengine/apps/builder.py:669-890) ----
+    async def async_init(self) -> None:
+        pass   # the reference connects to the model-runner service here; the model lives in this process
+
+    async def test_deployment(self) -> None:
+        """ref: analysis_deployment.py:72-77 — a 64x64 synthetic tile through the whole path."""
+        res = await self.analyze(np.random.rand(64, 64).astype(np.float32), as_numpy=True)
+        assert res["image_shape"] == [64, 64]
+
+    async def check_health(self) -> None:
+        if self._model is None:
+            raise RuntimeError("model not loaded.")
+
+    @schema_method
     async def ping(self) -> dict:
+        """Return service status."""
         return {"status": "ok", "model": _MODEL_ID, "model_runner": "in-process (B200)",
                 "uptime_s": round(time.time() - self.start_time, 1), "timestamp": datetime.now().isoformat()}
 
@@ -104,6 +121,7 @@ class MitoAnalysisDeployment:
         closed = K.binary_closing(kept, K.disk_half_widths(radius))
         return closed, K.distance_transform_edt(closed)
 
+    @schema_method
     async def analyze(self, image, pixel_size_nm: float = 5.0, tile_size: int = 512, overlap: int = 64,
                       as_numpy: bool = False, cleanup: bool = True) -> dict:
         """Same contract as ref: analysis_deployment.py:192-286 (`as_numpy=True` skips the nested-list conversion;

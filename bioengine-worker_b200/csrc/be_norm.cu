@@ -508,6 +508,18 @@ __global__ void __launch_bounds__(kThreads) normalize_kernel(const float* __rest
     }
 }
 
+// y = x * gain[seg] + offset[seg] in fp32, the per-segment constants read from device memory ({offset, gain} pairs, fp64,
+// as be_meanvar_f32 writes its `norm` output for a reference tensor: {ref_mean, ref_std + eps})
+__global__ void __launch_bounds__(kThreads) scale_linear_seg_kernel(const float* __restrict__ x, float* __restrict__ y,
+                                                                    int64_t seg_len, const double* __restrict__ params) {
+    const int64_t seg = blockIdx.y;
+    const float offset = (float)params[seg * 2], gain = (float)params[seg * 2 + 1];
+    const float* xs = x + seg * seg_len;
+    float* ys = y + seg * seg_len;
+    for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < seg_len; i += (int64_t)gridDim.x * kThreads)
+        ys[i] = __fadd_rn(__fmul_rn(xs[i], gain), offset);
+}
+
 template <int OP>
 __device__ __forceinline__ float ew_one(float v, float a, float b) {
     if (OP == BE_OP_CLIP) return (v != v) ? v : fminf(fmaxf(v, a), b);  // NaN passes through, as in np.clip
@@ -1588,6 +1600,18 @@ extern "C" int be_elementwise_f32(const float* x, float* y, int64_t n, int op, f
         case BE_OP_SIGMOID: elementwise_kernel<BE_OP_SIGMOID><<<g, kThreads, 0, s>>>(x, y, n, a, b); break;
         default: BE_REQUIRE(false, BE_ERR_INVALID_ARG, "be_elementwise_f32: unknown op %d", op);
     }
+    BE_LAUNCH_CHECK();
+    return BE_OK;
+}
+
+extern "C" int be_scale_linear_seg_f32(const float* x, float* y, int64_t n_seg, int64_t seg_len, const double* offset_gain,
+                                       be_stream_t stream) {
+    BE_REQUIRE(x && y && offset_gain, BE_ERR_INVALID_ARG, "be_scale_linear_seg_f32: null pointer");
+    BE_REQUIRE(n_seg > 0 && seg_len > 0, BE_ERR_INVALID_ARG, "be_scale_linear_seg_f32: empty input");
+    BE_REQUIRE(n_seg <= 65535, BE_ERR_TOO_LARGE, "be_scale_linear_seg_f32: n_seg %lld > 65535", (long long)n_seg);
+    int gx = stream_grid(seg_len);
+    if (n_seg > 1) gx = (int)min((int64_t)gx, max((int64_t)1, (int64_t)BE_SM_COUNT * 16 / n_seg));
+    scale_linear_seg_kernel<<<dim3(gx, (unsigned)n_seg), kThreads, 0, (cudaStream_t)stream>>>(x, y, seg_len, offset_gain);
     BE_LAUNCH_CHECK();
     return BE_OK;
 }

@@ -155,14 +155,13 @@ def scale_linear(x, gain, offset, out=None):
 def scale_mean_variance(x: torch.Tensor, ref_norm: torch.Tensor, n_seg: int, eps: float = 1e-6,
                         out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """bioimageio `scale_mean_variance`: (x - mean) / (std + eps) * (ref_std + eps) + ref_mean per segment.
-    ref_norm = `meanvar(reference, n_seg, eps)[1]` ({ref_mean, ref_std + eps}, fp64 on the device).  Composed from the
-    existing entry points: statistics, normalise, then one scale_linear per segment (N*C of them at most)."""
+    ref_norm = `meanvar(reference, n_seg, eps)[1]` ({ref_mean, ref_std + eps}, fp64 on the device).  Three launches
+    (statistics, normalise, per-segment scale_linear with the constants read from device memory), nothing on the host."""
+    _check(ref_norm, torch.float64, "ref_norm")
     own = meanvar(x, n_seg, eps)[1]
     y = normalize(x, own, out=out)
-    r = ref_norm.cpu().numpy()
-    seg = y.view(n_seg, -1)
-    for i in range(n_seg):
-        scale_linear(seg[i], float(r[i, 1]), float(r[i, 0]), out=seg[i])
+    n_seg, seg_len = _segments(y, n_seg)
+    _lib.call("be_scale_linear_seg_f32", y.data_ptr(), y.data_ptr(), n_seg, seg_len, ref_norm.data_ptr(), _stream())
     return y
 
 
@@ -443,7 +442,7 @@ def remove_small_objects(mask: torch.Tensor, min_size: int, ws: Workspace = _def
     labels, n = ccl(mask, 1, ws=ws)
     N = mask.shape[0]
     n_px = mask.numel() // N
-    cap = int(n.max().item()) + 1
+    cap = (n_px + 1) // 2 + 1   # most 4-connected components an image can hold (a checkerboard): no look at `n` on the host
     area = torch.empty((N, cap), dtype=torch.int32, device=mask.device)
     status = torch.empty((N,), dtype=torch.int32, device=mask.device)
     out = torch.empty_like(mask)

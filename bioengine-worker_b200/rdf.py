@@ -29,6 +29,7 @@ class TensorSpec:
     size_min: Dict[str, int] = field(default_factory=dict)   # spatial axis id -> min
     size_step: Dict[str, int] = field(default_factory=dict)  # spatial axis id -> step (0 = fixed)
     halo: Dict[str, int] = field(default_factory=dict)
+    n_channels: Optional[int] = None            # from `channel_names` / a fixed channel size, if declared
 
 
 @dataclass
@@ -86,6 +87,12 @@ def _tensor(entry: Dict[str, Any], is_output: bool) -> TensorSpec:
     for ax in axes or []:
         l = _axis_letter(ax)
         letters.append(l)
+        if l == "c":
+            names = ax.get("channel_names")
+            if isinstance(names, (list, tuple)) and names:
+                spec.n_channels = len(names)
+            elif isinstance(ax.get("size"), int):
+                spec.n_channels = int(ax["size"])
         if l in "zyx":
             size = ax.get("size")
             if isinstance(size, dict) and "min" in size:

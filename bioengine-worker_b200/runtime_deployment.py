@@ -30,22 +30,17 @@ from .rdf import ModelSpec, Op, load_model_spec
 
 logger = logging.getLogger("ray.serve")
 
-try:  # pragma: no cover - ray is not installed in the build image
-    from ray import serve
+from ._serve_compat import deployment
 
-    _deployment = serve.deployment(
-        ray_actor_options={"num_cpus": 1, "num_gpus": 1, "memory": 12 * 1024 * 1024 * 1024},
-        max_ongoing_requests=1,
-        autoscaling_config={"min_replicas": 1, "initial_replicas": 1, "max_replicas": 2,
-                            "target_num_ongoing_requests_per_replica": 0.8, "metrics_interval_s": 2.0,
-                            "look_back_period_s": 10.0, "downscale_delay_s": 300, "upscale_delay_s": 0.0},
-        health_check_period_s=30.0, health_check_timeout_s=30.0, graceful_shutdown_timeout_s=120.0,
-        graceful_shutdown_wait_loop_s=2.0,
-    )
-except Exception:  # ray absent: plain class
-    def _deployment(cls):
-        cls.func_or_class = cls
-        return cls
+_deployment = deployment(
+    ray_actor_options={"num_cpus": 1, "num_gpus": 1, "memory": 12 * 1024 * 1024 * 1024},
+    max_ongoing_requests=1,
+    autoscaling_config={"min_replicas": 1, "initial_replicas": 1, "max_replicas": 2,
+                        "target_num_ongoing_requests_per_replica": 0.8, "metrics_interval_s": 2.0,
+                        "look_back_period_s": 10.0, "downscale_delay_s": 300, "upscale_delay_s": 0.0},
+    health_check_period_s=30.0, health_check_timeout_s=30.0, graceful_shutdown_timeout_s=120.0,
+    graceful_shutdown_wait_loop_s=2.0,
+)
 
 
 _NORMALISERS = ("scale_range", "zero_mean_unit_variance", "fixed_zero_mean_unit_variance")
@@ -166,7 +161,7 @@ class RuntimeDeployment:
             elif op.name == "sigmoid":
                 x = K.sigmoid(x, out=x)
             elif op.name == "binarize":
-                x = K.binarize(x, float(k["threshold"])).to(torch.float32)
+                x = K.to_float32(K.binarize(x, float(k["threshold"])))
             else:
                 raise ValueError(f"unsupported processing op {op.name!r}")
         return x
@@ -216,10 +211,31 @@ class RuntimeDeployment:
             return torch.tensor(vals, dtype=torch.float64, device=x.device), 1
         return torch.tensor([[float(mean), float(std) + eps]] * n, dtype=torch.float64, device=x.device), 2
 
+    @staticmethod
+    def _validate_sample(x: np.ndarray, inp, blocking: bool) -> None:
+        """What `create_sample_for_model` checks against the model description (ref: runtime_deployment.py:270-274): the
+        channel count the RDF declares, and — without blocking — that every parameterised spatial axis has a size the
+        model accepts (min + k * step)."""
+        sp_axes = [a for a in inp.axes if a in "zyx"]
+        if inp.n_channels is not None and x.shape[1] != inp.n_channels:
+            raise ValueError(f"input {inp.id!r} has {x.shape[1]} channel(s), the model expects {inp.n_channels}")
+        for a, size in zip(sp_axes, x.shape[2:]):
+            lo, step = inp.size_min.get(a), inp.size_step.get(a, 0)
+            if lo is None:
+                continue
+            if size < lo and not blocking:
+                raise ValueError(f"input {inp.id!r}: axis {a} has size {size}, the model needs at least {lo}")
+            if not blocking and step > 0 and (size - lo) % step:
+                raise ValueError(f"input {inp.id!r}: axis {a} has size {size}, the model accepts {lo} + k*{step}")
+            if not blocking and step == 0 and size != lo:
+                raise ValueError(f"input {inp.id!r}: axis {a} has size {size}, the model needs exactly {lo}")
+
     def _predict_one(self, loaded: _LoadedModel, x_np: np.ndarray, blocking: bool) -> Dict[str, np.ndarray]:
         spec = loaded.spec
         inp, outp = spec.inputs[0], spec.outputs[0]
-        x = K.to_float32(torch.from_numpy(self._to_ncsp(x_np, inp.axes)).to(loaded.device, non_blocking=True))
+        x_host = self._to_ncsp(x_np, inp.axes)
+        self._validate_sample(x_host, inp, blocking)
+        x = K.to_float32(torch.from_numpy(x_host).to(loaded.device, non_blocking=True))
         N, C = x.shape[:2]
         spatial = tuple(x.shape[2:])
         sp_axes = [a for a in inp.axes if a in "zyx"]
@@ -261,7 +277,13 @@ class RuntimeDeployment:
         else:
             stitched, _ = K.stitch_crop(logits, out_shape, pipe.axes)
             result = self._run_ops_unfused(stitched, post, N, logits.shape[1], ref_norms)
-        out = result.to(getattr(torch, outp.dtype, torch.float32)) if result.dtype != getattr(torch, outp.dtype, None) else result
+        want_dtype = getattr(torch, outp.dtype, torch.float32)
+        if result.dtype == want_dtype:
+            out = result
+        elif want_dtype == torch.float32:
+            out = K.to_float32(result.contiguous())     # trailing ensure_dtype(float32), on the device
+        else:
+            out = result.to(want_dtype)
         arr = out.cpu().numpy()
         # back to the model's declared output axis order
         have = [a for a in "bc" if a in outp.axes] + [a for a in "zyx" if a in outp.axes]
@@ -287,16 +309,22 @@ class RuntimeDeployment:
                                                     default_blocksize_parameter=default_blocksize_parameter,
                                                     latest_remote_modified=latest_remote_modified)
             loaded = await self._create_prediction_pipeline(cache_key)
+            if len(loaded.spec.inputs) != 1:
+                raise ValueError(f"model declares {len(loaded.spec.inputs)} input tensors; the in-package architectures take one")
             if isinstance(inputs, dict):
                 want = loaded.spec.inputs[0].id
+                unknown = [k for k in inputs if k != want]
                 if want not in inputs and len(inputs) != 1:
                     raise ValueError(f"inputs must contain tensor {want!r}")
+                if want in inputs and unknown:
+                    raise ValueError(f"unknown input tensor(s) {unknown}; the model declares only {want!r}")
                 x = inputs[want] if want in inputs else next(iter(inputs.values()))
             else:
                 x = inputs
             x = np.asarray(x)
             if x.size == 0:
                 raise ValueError("empty input")
+            logger.info(f"Running inference for sample '{sample_id}'")
             return self._predict_one(loaded, x, blocking=bool(default_blocksize_parameter))
         except Exception as e:
             torch.cuda.empty_cache()

@@ -98,6 +98,13 @@ int be_elementwise_f32(const float* x, float* y, int64_t n, int op, float a, flo
  * at analysis_deployment.py:166. */
 int be_binarize_f32_u8(const float* x, uint8_t* y, int64_t n, float thr, be_stream_t stream);
 
+/* y = x * gain + offset in fp32 with per-segment constants on the device: offset_gain[2*seg] = offset, [2*seg + 1] = gain
+ * (fp64, converted to fp32) — the second half of bioimageio `scale_mean_variance`
+ * ((x - mean) / (std + eps) * (ref_std + eps) + ref_mean, Appendix A.2), fed with the `norm` output be_meanvar_f32 wrote
+ * for the reference tensor, so the op needs no host round trip. */
+int be_scale_linear_seg_f32(const float* x, float* y, int64_t n_seg, int64_t seg_len, const double* offset_gain,
+                            be_stream_t stream);
+
 /* y = (float)x for the integer / half / double element types a microscope or a caller hands over — the leading
  * `EnsureDtype(float32)` bioimageio.core inserts before the pre-processing (Appendix A.2) and
  * `np.array(image, dtype=np.float32)` of analysis_deployment.py:236, on the device, so that a uint8 / uint16 frame crosses

@@ -28,9 +28,58 @@ def test_manifest_deployments_resolve(app, methods):
         for m in methods[cls_name]:
             assert inspect.iscoroutinefunction(getattr(cls, m)), (cls_name, m)
     first = classes[0][1]
+    # ref: bioengine/apps/builder.py:1453-1465 — the entry class must carry schema methods
+    schema = [m for m in dir(first) if callable(getattr(first, m)) and hasattr(getattr(first, m), "__schema__")]
+    assert set(methods[first.__name__]) <= set(schema), schema
+    # ref: builder.py:892-975,1482-1508 — later deployments are injected through __init__ parameters named after the file
+    # stem and annotated DeploymentHandle (the annotation object itself is compared); every other parameter has a default
+    from bioengine_worker_b200._serve_compat import DeploymentHandle
+
     params = inspect.signature(first.__init__).parameters
     for stem, _ in classes[1:]:
         assert stem in params, f"{first.__name__}.__init__ must take the {stem} handle"
+        assert params[stem].annotation is DeploymentHandle
+    injected = {stem for stem, _ in classes[1:]}
+    for name, prm in params.items():
+        if name not in injected and name != "self":
+            assert prm.default is not inspect.Parameter.empty, f"{name} would have to be given in the manifest"
+    # lifecycle hooks the builder awaits when present (builder.py:669-890)
+    for hook in ("async_init", "test_deployment", "check_health"):
+        assert inspect.iscoroutinefunction(getattr(first, hook)), hook
+
+
+def test_entry_calls_the_runtime_through_a_deployment_handle(tmp_path, monkeypatch):
+    """ref: entry_deployment.py:1969-1977 — `await self.runtime_deployment.predict.remote(...)`: a Ray DeploymentHandle has
+    no awaitable `predict(...)`, only `predict.remote(...)`."""
+    import asyncio
+
+    import numpy as np
+
+    from bioengine_worker_b200.entry_deployment import EntryDeployment
+
+    calls = []
+
+    class _Method:
+        async def remote(self, **kw):
+            calls.append(kw)
+            return {"mask": np.ones((1, 1, 4, 4), np.uint8)}
+
+    class _Handle:
+        predict = _Method()
+
+    (tmp_path / "m1").mkdir()
+    (tmp_path / "m1" / "rdf.yaml").write_text("name: m1\n")
+    cls = getattr(EntryDeployment, "func_or_class", EntryDeployment)
+    entry = cls(runtime_deployment=_Handle(), models_dir=str(tmp_path))
+    monkeypatch.setattr(entry, "_check_runtime_available", lambda: None)
+    asyncio.run(entry.async_init())
+    out = asyncio.run(entry.infer("m1", np.zeros((4, 4), np.float32), default_blocksize_parameter=2))
+    assert out["mask"].shape == (1, 1, 4, 4)
+    assert calls[0]["rdf_path"].endswith("m1/rdf.yaml") and calls[0]["default_blocksize_parameter"] == 2
+    url = asyncio.run(entry.infer("m1", np.zeros((4, 4), np.float32), return_download_url=True))["mask"]
+    assert url.startswith("file://") and np.load(url[7:]).shape == (1, 1, 4, 4)
+    with pytest.raises(FileNotFoundError):
+        asyncio.run(entry.infer("missing", np.zeros((4, 4), np.float32)))
 
 
 def test_runtime_predict_signature_matches_the_reference():

@@ -230,3 +230,63 @@ def test_pipeline_on_second_gpu_while_first_is_current():
     assert np.array_equal(res["labels"].cpu().numpy()[0, 0], O.label(want_mask[0, 0], 2))
     with pytest.raises(ValueError):
         K.normalize(torch.zeros(8, device="cuda:0"), torch.zeros((1, 2), dtype=torch.float64, device=d1))
+
+
+def test_predict_fixed_zmuv_clip_scale_linear_and_integer_input(tmp_path, dev):
+    """`fixed_zero_mean_unit_variance` (scalar and per-channel), `clip`, `scale_linear` in one pre-processing chain, on a
+    uint8 input that is uploaded as uint8 and converted on the device (bioimageio's leading ensure_dtype)."""
+    from bioengine_worker_b200.runtime_deployment import RuntimeDeployment
+
+    rng = np.random.default_rng(12)
+    img8 = rng.integers(0, 256, (1, 1, 96, 128)).astype(np.uint8)
+    pre = [{"id": "ensure_dtype", "kwargs": {"dtype": "float32"}},
+           {"id": "fixed_zero_mean_unit_variance", "kwargs": {"mean": 103.5, "std": 57.25}},
+           {"id": "clip", "kwargs": {"min": -1.5, "max": 1.25}},
+           {"id": "scale_linear", "kwargs": {"gain": 0.5, "offset": 0.125}}]
+    rdf_path, net = write_model(tmp_path, pre, [{"id": "sigmoid"}])
+    rt = RuntimeDeployment.func_or_class()
+    out = asyncio.run(rt.predict(rdf_path, img8))
+    x = img8.astype(np.float32)
+    xn = O.scale_linear(O.clip(O.fixed_zero_mean_unit_variance(x, 103.5, 57.25), -1.5, 1.25), 0.5, 0.125)
+    with torch.no_grad():
+        want = O.sigmoid(net.to(dev)(torch.from_numpy(xn).to(dev)).cpu().numpy())
+    np.testing.assert_allclose(out["mask"], want, rtol=1e-4, atol=1e-6)
+    # the fused form (a single normaliser in the chain goes through the gather): fp64 arithmetic, <= 1e-5 from the fp32 reading
+    sub = tmp_path / "fused"
+    sub.mkdir()
+    rdf2, net2 = write_model(sub, [{"id": "fixed_zero_mean_unit_variance", "kwargs": {"mean": [103.5], "std": [57.25], "axis": "channel"}}], [])
+    out2 = asyncio.run(rt.predict(rdf2, img8))
+    with torch.no_grad():
+        want2 = net2.to(dev)(torch.from_numpy(O.fixed_zero_mean_unit_variance(x, 103.5, 57.25)).to(dev)).cpu().numpy()
+    np.testing.assert_allclose(out2["mask"], want2, rtol=1e-4, atol=1e-5)
+
+
+def test_scale_mean_variance_stays_on_the_device(dev):
+    from bioengine_worker_b200 import kernels as K
+
+    rng = np.random.default_rng(5)
+    x = (rng.standard_normal((2, 3, 40, 56)) * 7 + 3).astype(np.float32)
+    ref = (rng.standard_normal((2, 3, 40, 56)) * 0.5 - 2).astype(np.float32)
+    xd, rd = torch.from_numpy(x).to(dev), torch.from_numpy(ref).to(dev)
+    ref_norm = K.meanvar(rd, 6, 1e-6)[1]
+    got = K.scale_mean_variance(xd, ref_norm, 6, 1e-6).cpu().numpy()
+    want = O.scale_mean_variance(x, ref, axes=(2, 3))
+    np.testing.assert_allclose(got, want, rtol=1e-5, atol=1e-5)
+
+
+def test_predict_validates_the_sample_against_the_rdf(tmp_path, dev):
+    from bioengine_worker_b200.runtime_deployment import RuntimeDeployment
+
+    rdf_path, _ = write_model(tmp_path, [{"id": "zero_mean_unit_variance", "kwargs": {"axes": ["y", "x"]}}], [])
+    rt = RuntimeDeployment.func_or_class()
+    ok = np.zeros((1, 1, 96, 128), np.float32)       # 64 + k * 32 on both axes
+    assert asyncio.run(rt.predict(rdf_path, ok))["mask"].shape == (1, 1, 96, 128)
+    for bad in (np.zeros((1, 2, 96, 128), np.float32),    # two channels, one declared
+                np.zeros((1, 1, 100, 128), np.float32),   # 100 is not 64 + k * 32
+                np.zeros((1, 1, 32, 128), np.float32)):   # below the minimum
+        with pytest.raises(ValueError):
+            asyncio.run(rt.predict(rdf_path, bad))
+    with pytest.raises(ValueError):
+        asyncio.run(rt.predict(rdf_path, {"raw": ok, "extra": ok}))
+    # with blocking any size at least as large as the inner block goes
+    assert asyncio.run(rt.predict(rdf_path, np.zeros((1, 1, 100, 131), np.float32), default_blocksize_parameter=0))["mask"].shape == (1, 1, 100, 131)
