@@ -458,6 +458,7 @@ __device__ __forceinline__ void unite_batch(int32_t* Li, EdgeBatch& q) {
 __global__ void __launch_bounds__(kThreads) ccl_edge_kernel(int32_t* __restrict__ L, const TileEdges* __restrict__ edges,
                                                             Geom g, int tiles_per_image) {
     be_pdl_wait();   // the tile kernel's parents and edge masks
+    be_pdl_launch_dependents();   // the numbering kernel may be placed now: it reads the root bitmap (complete) and waits
     const int wg = blockIdx.x * (kThreads / 32) + (threadIdx.x >> 5);
     const int t = wg >> 2, part = wg & 3;
     if (t >= tiles_per_image) return;
@@ -582,11 +583,14 @@ __global__ void __launch_bounds__(kThreads) ccl_number_kernel(int32_t* __restric
     const int blk = (int)s_ticket;
     int32_t* Li = L + (int64_t)img * vol;
     const int64_t w = (int64_t)blk * kWordsPerBlock + threadIdx.x;
+    // the root bitmap was written by the tile kernel, which had completed before the border-union kernel let this one
+    // start: it is read while that kernel still runs
+    u64 bits = (w < words_per_image) ? __ldcg(rootbits + (int64_t)img * words_per_image + w) : 0ull;
     be_pdl_wait();   // the border unions
+    be_pdl_launch_dependents();   // the resolve kernel may be placed: it fetches its mask words and waits for the numbers
     u64 keep = 0;
     int64_t base = 0;
     if (w < words_per_image) {
-        u64 bits = rootbits[(int64_t)img * words_per_image + w];
         base = (w / wpr) * X + (w % wpr) * kTX;
         // still a root after the border unions?  Four candidates per round, their loads issued together
         while (bits) {
@@ -666,7 +670,6 @@ __global__ void __launch_bounds__(kThreads) ccl_number_kernel(int32_t* __restric
         keep &= keep - 1;
         __stcg(Li + base + b, -(++id) - 1);
     }
-    be_pdl_launch_dependents();
 }
 
 // grid: x = row (z * Y + y), y = blocks of 8-px units along the row, z = image.  The packed mask says which pixels have a
@@ -679,8 +682,9 @@ __global__ void __launch_bounds__(kThreads) ccl_resolve_kernel(const int32_t* __
     if (u >= units_per_row) return;
     const int64_t row = blockIdx.x;
     const int x = u * 8;
-    be_pdl_wait();   // the numbering (and, through it, everything before)
+    // the packed mask is the caller's or the tile kernel's (complete long ago): fetched while the numbering still runs
     const u64 word = __ldg(bitvol + (int64_t)blockIdx.z * words_per_image + row * wpr + (x >> 6));
+    be_pdl_wait();   // the numbering (and, through it, everything before)
     const unsigned bits = (unsigned)(word >> (x & 63)) & 0xffu;
     const int32_t* Li = L + (int64_t)blockIdx.z * vol;
     const int64_t base = row * X + x;

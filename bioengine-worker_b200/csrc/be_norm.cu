@@ -662,6 +662,7 @@ __global__ void __launch_bounds__(kSampleThreads) qsel_sample_kernel(const float
                                                                      SWorkspace w) {
     __shared__ uint32_t key[kSample];
     __shared__ unsigned s_valid;
+    be_pdl_launch_dependents();   // the partition pass may be placed on the other SMs now; it waits for the pivots
     const int64_t seg = blockIdx.x;
     const float* xs = x + seg * seg_len;
     const uint32_t stride = (uint32_t)(seg_len / kSample);  // >= 64

@@ -289,4 +289,4 @@ def test_predict_validates_the_sample_against_the_rdf(tmp_path, dev):
     with pytest.raises(ValueError):
         asyncio.run(rt.predict(rdf_path, {"raw": ok, "extra": ok}))
     # with blocking any size at least as large as the inner block goes
-    assert asyncio.run(rt.predict(rdf_path, np.zeros((1, 1, 100, 131), np.float32), default_blocksize_parameter=0))["mask"].shape == (1, 1, 100, 131)
+    assert asyncio.run(rt.predict(rdf_path, np.zeros((1, 1, 100, 131), np.float32), default_blocksize_parameter=1))["mask"].shape == (1, 1, 100, 131)
