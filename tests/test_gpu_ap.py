@@ -144,3 +144,36 @@ def test_screening_device_loop_capacity_retry_and_low_thresholds(dev):
         ap, tp, _, _ = O.average_precision(gts, preds, threshold=list(thr))
         assert np.array_equal(res["table"][m, :, :3], tp.astype(np.int64))
         assert np.array_equal(res["ap"][m], ap, equal_nan=True)
+
+
+def test_c4_screening_at_full_image_size_matches_oracle(dev):
+    """BASELINE config 4 at its image size: two candidates x four 1024^2 images with ground-truth labels through the
+    device loop (normalise → forward → labels straight from the logits → overlap → matching → table rows) against the
+    oracle's label + average_precision (Hungarian) on the same logits."""
+    from bioengine_worker_b200 import kernels as K
+    from bioengine_worker_b200 import models
+    from bioengine_worker_b200.screening import screen_models
+
+    models.strict_fp32()
+    n, size = 4, 1024
+    imgs, gts = [], []
+    for i in range(n):
+        img, clean = O.synthetic_image((size, size), 120 + 60 * i, seed=4000 + i, with_truth=True)
+        imgs.append(img)
+        gts.append(O.label(clean > 0.5, 2))
+    x = torch.from_numpy(np.stack(imgs)[:, None]).to(dev)
+    xn = K.normalize(x, K.meanvar(x, n, 1e-6)[1])
+    nets = [models.calibrate_head(models.build_model("UNet2d", seed=40, depth=2, initial_features=8).to(dev), xn[:1], foreground=0.15)]
+    level = [float((0.5 * 1000 + 100 - im.mean()) / im.std()) for im in imgs]   # the GT level in normalised units, roughly
+    nets.append(lambda t: (torch.nn.functional.avg_pool2d(t, 5, 1, 2) - float(np.mean(level))) * 8.0)
+    res = screen_models(nets, imgs, gts, device=dev, batch=2)
+    for m, net in enumerate(nets):
+        with torch.no_grad():
+            logits = np.concatenate([net(xn[s:s + 2]).cpu().numpy() for s in range(0, n, 2)])
+        preds = [O.label(O.binarize(O.sigmoid(l), 0.5)[0], 2) for l in logits]
+        ap, tp, _, _ = O.average_precision(gts, preds)
+        assert np.array_equal(res["table"][m, :, :3], tp.astype(np.int64)), m
+        assert np.array_equal(res["table"][m, :, 3], [g.max() for g in gts])
+        assert np.array_equal(res["table"][m, :, 4], [p.max() for p in preds])
+        assert np.array_equal(res["ap"][m], ap, equal_nan=True)
+    assert res["ranking"][0] == 1   # the candidate that segments wins

@@ -181,3 +181,41 @@ def test_c3_full_size_labels_equal_scipy(dev):
         del want
     got8, n8 = K.ccl(mask[None], 3)
     assert torch.equal(got8, K.ccl_bits(bits.reshape(-1), (1, S, S, S), 3)[0])
+
+
+def test_c5_frame_full_size_labels_and_stats_equal_oracle(dev):
+    """BASELINE config 5 at full size: one 2048^2 uint16 frame through upload → ensure_dtype → scale_range → 512-px blocks
+    with a 32-px halo → forward → sigmoid → binarize → 8-connected labels → per-label statistics, against the oracle on the
+    same logits (labels bit-exact, areas and centroid sums exact integers)."""
+    from bioengine_worker_b200 import kernels as K
+    from bioengine_worker_b200 import models
+    from bioengine_worker_b200.pipeline import PipelineSpec, TiledPipeline
+
+    H = W = 2048
+    models.strict_fp32()
+    frame = np.clip(O.synthetic_image((1, 1, H, W), 800, seed=5), 0, 65535).astype(np.uint16)
+    spec = PipelineSpec(block=(512, 512), halo=(32, 32), convention="bioimageio", preprocess="scale_range", sigmoid=True,
+                        connectivity=2, forward_batch=25)
+    pipe = TiledPipeline((1, 1, H, W), spec, device=dev)
+    net = models.build_model("UNet2d", seed=5, depth=2, initial_features=8).to(dev)
+    tiles = pipe.preprocess_and_tile(pipe.upload(frame))
+    models.calibrate_head(net, tiles[::5].contiguous())
+    want_tiles = P.crop_pre(frame.astype(np.float32), (512, 512), (32, 32))
+    assert np.array_equal(tiles.cpu().numpy(), want_tiles)
+    logits = pipe.forward(net, tiles)
+    res = pipe.stitch_and_label(logits)
+    _, mask, labels = P.crop_post(logits.cpu().numpy(), (1, 1, H, W), (512, 512), (32, 32), 2)
+    assert 0.02 < mask.mean() < 0.98
+    assert np.array_equal(res["mask"].cpu().numpy(), mask)
+    assert np.array_equal(res["labels"].cpu().numpy()[:, 0], labels)
+    n = int(res["n_labels"].item())
+    assert n == labels.max()
+    sums, bbox, status = K.label_stats(res["labels"][0], n + 1)
+    assert int(status.item()) == 0
+    s = sums.cpu().numpy()[0]
+    lab = labels[0]
+    ys, xs = np.nonzero(lab)
+    l = lab[ys, xs]
+    assert np.array_equal(s[:, 0], np.bincount(l, minlength=n + 1))                      # areas
+    assert np.array_equal(s[:, 2], np.bincount(l, weights=ys, minlength=n + 1).astype(np.int64))   # sum of y
+    assert np.array_equal(s[:, 3], np.bincount(l, weights=xs, minlength=n + 1).astype(np.int64))   # sum of x
