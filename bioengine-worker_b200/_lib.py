@@ -59,6 +59,11 @@ SIGNATURES = {
     "be_binary_closing_u8": (_i32, [_ptr, _ptr, _i64, _i64, _i64, _ptr, _i32, _ptr, _ptr]),
     "be_edt_workspace_bytes": (_sz, [_i64, _i64, _i64]),
     "be_edt_u8_f64": (_i32, [_ptr, _ptr, _i64, _i64, _i64, _ptr, _ptr]),
+    "be_edt_sq_u8_i32": (_i32, [_ptr, _ptr, _i64, _i64, _i64, _ptr, _ptr]),
+    "be_peak_local_max_workspace_bytes": (_sz, [_i64, _i64]),
+    "be_peak_local_max_i32": (_i32, [_ptr, _ptr, _ptr, _i64, _i64, _i32, _ptr, _ptr]),
+    "be_watershed_workspace_bytes": (_sz, [_i64, _i64]),
+    "be_watershed_i32": (_i32, [_ptr, _i32, _ptr, _ptr, _ptr, _ptr, _i64, _i64, _ptr, _ptr]),
     "be_label_stats_i32": (_i32, [_ptr] + [_i64] * 5 + [_ptr] * 4),
 }
 

@@ -5,19 +5,13 @@ Same `analyze(image, pixel_size_nm, tile_size, overlap)` arguments and the same 
 scipy and skimage on one CPU core; here the image goes to the GPU once and p1/p99 normalisation, reflect-padded tiling,
 the forward, the Gaussian blend, the 0.5 threshold, connected components and the per-label moments all run there.
 
-Of `_prob_to_instances` (ref: analysis_deployment.py:160-176) the deterministic front half runs on the device and matches
-scipy / skimage bit for bit: threshold, `remove_small_objects(min_size=300)`, `binary_closing(disk(4))`, and the exact
-Euclidean distance transform (`prob_to_closed_and_distance`).  The seeded watershed that follows (`peak_local_max`,
-`watershed`) is not ported yet.  `analyze` therefore labels the cleaned mask
-(`cleanup=True`, the default: the closest available to the reference); its instances differ from the reference's in
-three known ways until the watershed exists:
-  * numbering: the watershed's labels follow marker order (raster order of the distance peaks), these follow the raster
-    order of each component's first pixel;
-  * `peak_local_max` excludes peaks within `min_distance` of the border, so a component whose only peak lies within
-    8 px of the border gets no marker and stays 0 in the reference; here it is labelled;
-  * the watershed floods with connectivity 1 and splits touching objects at the distance saddle; the labelling here uses
-    connectivity 2 and never splits a connected component.
-`cleanup=False` labels the thresholded map directly (`measure.label(prob > 0.5)`).
+`_prob_to_instances` (ref: analysis_deployment.py:160-176) runs on the device as well (`kernels.instances_from_mask`):
+threshold, `remove_small_objects(min_size=300)`, `binary_closing(disk(4))`, the exact Euclidean distance transform,
+`peak_local_max(min_distance=8, labels=closed)`, `measure.label` of the peaks and the marker `watershed` on the negated
+distance.  Everything up to the flood matches scipy / skimage bit for bit; the flood matches skimage's order except between
+seeds of exactly equal height inside one connected region, where skimage's order is an accident of its heap layout and the
+kernel uses raster order (be_b200.h) — a few boundary pixels between twin objects.
+`cleanup=False` labels the thresholded map directly (`measure.label(prob > 0.5)`) instead.
 """
 from __future__ import annotations
 
@@ -111,22 +105,12 @@ class MitoAnalysisDeployment:
             self._pipes[key] = TiledPipeline((1, 1, H, W), spec, device=self.device)
         return self._pipes[key]
 
-    @staticmethod
-    def prob_to_closed_and_distance(mask: torch.Tensor, min_size: int = 300, radius: int = 4):
-        """Front half of `_prob_to_instances` on a thresholded (N, Y, X) uint8 mask: remove_small_objects → (empty?) →
-        binary_closing(disk(radius)) → distance_transform_edt.  Returns (closed uint8, dist fp64 or None if nothing is left)."""
-        kept = K.remove_small_objects(mask, min_size)
-        if not bool(kept.any().item()):
-            return kept, None
-        closed = K.binary_closing(kept, K.disk_half_widths(radius))
-        return closed, K.distance_transform_edt(closed)
-
     @schema_method
     async def analyze(self, image, pixel_size_nm: float = 5.0, tile_size: int = 512, overlap: int = 64,
                       as_numpy: bool = False, cleanup: bool = True) -> dict:
         """Same contract as ref: analysis_deployment.py:192-286 (`as_numpy=True` skips the nested-list conversion;
-        `cleanup=True`, the default, applies remove_small_objects(300) and binary_closing(disk(4)) before labelling; see the
-        module docstring for what still differs from the reference's watershed instances)."""
+        `cleanup=True`, the default, is the reference's `_prob_to_instances`: size filter, closing, distance peaks,
+        watershed; `cleanup=False` returns the connected components of the thresholded map)."""
         t0 = time.time()
         if isinstance(image, np.ndarray) and image.dtype.name in K.NUMPY_DEVICE_DTYPES:
             image_np = image   # converted to float32 on the device (same values as the reference's host cast)
@@ -138,9 +122,8 @@ class MitoAnalysisDeployment:
         pipe = self._pipeline(H, W, tile_size, overlap)
         res = pipe.run(image_np[None, None], self._model)
         if cleanup:
-            closed, _ = self.prob_to_closed_and_distance(res["mask"][0])
-            labels3, n_lab = K.ccl(closed, 2)
-            labels_d, n_mito = labels3[0], int(n_lab.item())
+            labels_d, n_seeds = K.instances_from_mask(res["mask"][0, 0])
+            n_mito = int(n_seeds.item())   # every seed keeps its own pixel, so labels.max() is the number of seeds
         else:
             labels_d = res["labels"][0, 0]
             n_mito = int(res["n_labels"].item())

@@ -139,7 +139,9 @@ __global__ void __launch_bounds__(kThreads) edt_columns_kernel(const uint8_t* __
 
 // phase 2: one block per row; thread 0 builds the lower envelope of the parabolas (x - i)^2 + g(i)^2 in shared memory,
 // then all threads evaluate it
-__global__ void __launch_bounds__(kThreads) edt_rows_kernel(const int32_t* __restrict__ g, double* __restrict__ dist, int Y,
+// OUT = double: the distance; OUT = int32_t: its square (exact, saturated) — what the seed detection and the flood order by
+template <typename OUT>
+__global__ void __launch_bounds__(kThreads) edt_rows_kernel(const int32_t* __restrict__ g, OUT* __restrict__ dist, int Y,
                                                             int X) {
     extern __shared__ int smem[];
     int* s = smem;           // parabola apexes of the envelope
@@ -187,7 +189,8 @@ __global__ void __launch_bounds__(kThreads) edt_rows_kernel(const int32_t* __res
         }
         const long long i = s[lo], gi = gs[i];
         const long long d2 = ((long long)x - i) * ((long long)x - i) + gi * gi;
-        dist[row * X + x] = sqrt((double)d2);
+        if constexpr (sizeof(OUT) == 8) dist[row * X + x] = sqrt((double)d2);
+        else dist[row * X + x] = (OUT)min(d2, (long long)INT32_MAX);
     }
 }
 
@@ -263,21 +266,31 @@ extern "C" size_t be_edt_workspace_bytes(int64_t N, int64_t Y, int64_t X) {
     return be_align_up(sizeof(int32_t) * N * Y * X, 256);
 }
 
-extern "C" int be_edt_u8_f64(const uint8_t* mask, double* dist, int64_t N, int64_t Y, int64_t X, void* ws,
-                             be_stream_t stream) {
-    BE_REQUIRE(mask && dist && ws, BE_ERR_INVALID_ARG, "be_edt_u8_f64: null pointer");
-    BE_REQUIRE(N > 0 && Y > 0 && X > 0, BE_ERR_INVALID_ARG, "be_edt_u8_f64: empty input");
-    BE_REQUIRE(N <= 65535, BE_ERR_TOO_LARGE, "be_edt_u8_f64: N %lld > 65535", (long long)N);
-    BE_REQUIRE(X <= 16384 && Y < (1 << 28), BE_ERR_TOO_LARGE, "be_edt_u8_f64: X %lld > 16384 (row envelope lives in shared memory)",
+template <typename OUT>
+static int edt_run(const char* who, const uint8_t* mask, OUT* dist, int64_t N, int64_t Y, int64_t X, void* ws, be_stream_t stream) {
+    BE_REQUIRE(mask && dist && ws, BE_ERR_INVALID_ARG, "%s: null pointer", who);
+    BE_REQUIRE(N > 0 && Y > 0 && X > 0, BE_ERR_INVALID_ARG, "%s: empty input", who);
+    BE_REQUIRE(N <= 65535, BE_ERR_TOO_LARGE, "%s: N %lld > 65535", who, (long long)N);
+    BE_REQUIRE(X <= 16384 && Y < (1 << 28), BE_ERR_TOO_LARGE, "%s: X %lld > 16384 (row envelope lives in shared memory)", who,
                (long long)X);
-    BE_REQUIRE(N * Y < ((int64_t)1 << 31), BE_ERR_TOO_LARGE, "be_edt_u8_f64: too many rows");
+    BE_REQUIRE(N * Y < ((int64_t)1 << 31), BE_ERR_TOO_LARGE, "%s: too many rows", who);
     cudaStream_t s = (cudaStream_t)stream;
     int32_t* g = (int32_t*)ws;
     edt_columns_kernel<<<dim3((unsigned)((X + kThreads - 1) / kThreads), (unsigned)N), kThreads, 0, s>>>(mask, g, (int)Y, X);
     BE_LAUNCH_CHECK();
     const size_t smem = sizeof(int) * 3 * X;
-    BE_CUDA(cudaFuncSetAttribute(edt_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    edt_rows_kernel<<<(unsigned)(N * Y), kThreads, smem, s>>>(g, dist, (int)Y, (int)X);
+    BE_CUDA(cudaFuncSetAttribute(edt_rows_kernel<OUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    edt_rows_kernel<OUT><<<(unsigned)(N * Y), kThreads, smem, s>>>(g, dist, (int)Y, (int)X);
     BE_LAUNCH_CHECK();
     return BE_OK;
+}
+
+extern "C" int be_edt_u8_f64(const uint8_t* mask, double* dist, int64_t N, int64_t Y, int64_t X, void* ws,
+                             be_stream_t stream) {
+    return edt_run<double>("be_edt_u8_f64", mask, dist, N, Y, X, ws, stream);
+}
+
+extern "C" int be_edt_sq_u8_i32(const uint8_t* mask, int32_t* dist2, int64_t N, int64_t Y, int64_t X, void* ws,
+                                be_stream_t stream) {
+    return edt_run<int32_t>("be_edt_sq_u8_i32", mask, dist2, N, Y, X, ws, stream);
 }

@@ -1,0 +1,589 @@
+// Seed detection and marker flooding — the back half of the fibsem post-processing
+// (ref: apps/fibsem-mito-analysis/analysis_deployment.py:171-175):
+//
+//     coords = feature.peak_local_max(dist, min_distance=8, labels=closed)
+//     labels = segmentation.watershed(-dist, measure.label(m), mask=closed)
+//
+//   be_peak_local_max_i32   skimage's peak_local_max on the squared distance (an integer, same order and same ties as
+//                           the fp64 distance): bounding box of the border-stripped mask, separable (2d+1)^2 window
+//                           maximum clipped to that box, "every pixel is a maximum" special case, then the greedy
+//                           thinning to Chebyshev distance >= d.  The greedy pass walks the candidates by (value
+//                           descending, raster order); here a candidate is accepted once every stronger candidate in
+//                           its window is rejected and rejected once one of them is accepted — decisions are final, so
+//                           they can be taken in any order: two grid-wide rounds settle everything except long plateaus
+//                           (ridges of equal distance), which one block finishes round by round.
+//   be_watershed_i32        skimage's flood (connectivity 1, no compactness, no lines): a priority queue ordered by
+//                           (height, push order); a popped pixel gives its label to its unlabelled 4-neighbours (up,
+//                           left, right, down) as it pushes them.  Connected regions of the mask flood independently, so
+//                           one block owns one region and keeps that region's queue as an array in push order.  Per step
+//                           it takes ALL entries of the lowest height at once — their pushes are ordered by (position of
+//                           the pusher, neighbour number), which is the order the sequential flood would give — unless
+//                           one of them uncovers a lower pixel: then only the entries up to and including that one are
+//                           taken, because the sequential flood would run down into the new basin before it returns.
+//                           Contested pixels go to the earliest pusher through a 64-bit atomicMin on (step, position,
+//                           neighbour).  Markers that tie in height leave in raster order (first in, first out); skimage's
+//                           binary heap orders such complete ties by its array layout, which no parallel flood can
+//                           reproduce — the oracle implements both and the tests say where they differ.
+#include "be_common.cuh"
+
+namespace {
+
+constexpr int kThreads = 256;
+
+// ---------------------------------------------------------------------------------------------------------------
+// peak_local_max
+// ---------------------------------------------------------------------------------------------------------------
+
+struct PlmState {
+    int ymin, ymax, xmin, xmax;  // bounding box of the mask pixels at least `d` away from every border (ymax < ymin: none)
+    int dmin;                    // image.min() on the squared distance
+    int not_max;                 // mask pixels inside the box that are below their window maximum
+    int n_cand;                  // candidates written to the list
+    int undecided;
+};
+
+__global__ void plm_init_kernel(PlmState* st) {
+    st->ymin = st->xmin = INT32_MAX;
+    st->ymax = st->xmax = -1;
+    st->dmin = INT32_MAX;
+    st->not_max = 0;
+    st->n_cand = 0;
+    st->undecided = 0;
+}
+
+__global__ void __launch_bounds__(kThreads) plm_roi_kernel(const int32_t* __restrict__ d2, const uint8_t* __restrict__ mask,
+                                                           int Y, int X, int d, PlmState* st) {
+    __shared__ int s[5];
+    if (threadIdx.x == 0) {
+        s[0] = s[2] = INT32_MAX;
+        s[1] = s[3] = -1;
+        s[4] = INT32_MAX;
+    }
+    __syncthreads();
+    const int64_t n = (int64_t)Y * X;
+    int ymin = INT32_MAX, ymax = -1, xmin = INT32_MAX, xmax = -1, dmin = INT32_MAX;
+    for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kThreads) {
+        dmin = min(dmin, d2[i]);
+        if (!mask[i]) continue;
+        const int y = (int)(i / X), x = (int)(i - (int64_t)y * X);
+        if (y < d || y >= Y - d || x < d || x >= X - d) continue;
+        ymin = min(ymin, y);
+        ymax = max(ymax, y);
+        xmin = min(xmin, x);
+        xmax = max(xmax, x);
+    }
+    atomicMin(&s[0], ymin);
+    atomicMax(&s[1], ymax);
+    atomicMin(&s[2], xmin);
+    atomicMax(&s[3], xmax);
+    atomicMin(&s[4], dmin);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        atomicMin(&st->ymin, s[0]);
+        atomicMax(&st->ymax, s[1]);
+        atomicMin(&st->xmin, s[2]);
+        atomicMax(&st->xmax, s[3]);
+        atomicMin(&st->dmin, s[4]);
+    }
+}
+
+// value of a pixel inside the box as the reference sees it: pixels outside the label hold the lowest number
+__device__ __forceinline__ int plm_value(const int32_t* d2, const uint8_t* mask, int64_t i) { return mask[i] ? d2[i] : INT32_MIN; }
+
+__global__ void __launch_bounds__(kThreads) plm_rowmax_kernel(const int32_t* __restrict__ d2, const uint8_t* __restrict__ mask,
+                                                              int32_t* __restrict__ rowmax, int Y, int X, int d,
+                                                              const PlmState* __restrict__ st) {
+    const int ymin = st->ymin, ymax = st->ymax, xmin = st->xmin, xmax = st->xmax;
+    if (ymax < ymin) return;
+    const int bw = xmax - xmin + 1;
+    const int64_t n = (int64_t)(ymax - ymin + 1) * bw;
+    for (int64_t j = (int64_t)blockIdx.x * kThreads + threadIdx.x; j < n; j += (int64_t)gridDim.x * kThreads) {
+        const int y = ymin + (int)(j / bw), x = xmin + (int)(j % bw);
+        const int a = max(x - d, xmin), b = min(x + d, xmax);
+        int m = INT32_MIN;
+        for (int xx = a; xx <= b; ++xx) m = max(m, plm_value(d2, mask, (int64_t)y * X + xx));
+        rowmax[(int64_t)y * X + x] = m;
+    }
+}
+
+// status: 0 no candidate, 1 undecided, 2 accepted, 3 rejected
+__global__ void __launch_bounds__(kThreads) plm_peak_kernel(const int32_t* __restrict__ d2, const uint8_t* __restrict__ mask,
+                                                            const int32_t* __restrict__ rowmax, uint8_t* __restrict__ status,
+                                                            int Y, int X, int d, PlmState* st) {
+    const int ymin = st->ymin, ymax = st->ymax, xmin = st->xmin, xmax = st->xmax, dmin = st->dmin;
+    if (ymax < ymin) return;
+    const int bw = xmax - xmin + 1, bh = ymax - ymin + 1;
+    const bool plain = d == 0 || (bw == 1 && bh == 1);  // footprint or box of one pixel: image > threshold
+    const int64_t n = (int64_t)bh * bw;
+    int not_max = 0;
+    for (int64_t j = (int64_t)blockIdx.x * kThreads + threadIdx.x; j < n; j += (int64_t)gridDim.x * kThreads) {
+        const int y = ymin + (int)(j / bw), x = xmin + (int)(j % bw);
+        const int64_t i = (int64_t)y * X + x;
+        if (!mask[i]) continue;
+        const int v = d2[i];
+        bool is_max = true;
+        if (!plain) {
+            const int a = max(y - d, ymin), b = min(y + d, ymax);
+            int m = INT32_MIN;
+            for (int yy = a; yy <= b; ++yy) m = max(m, rowmax[(int64_t)yy * X + x]);
+            is_max = v == m;
+            not_max += !is_max;
+        }
+        status[i] = (is_max && v > dmin) ? 1 : 0;
+    }
+    if (!plain) {
+        not_max = __reduce_add_sync(0xffffffffu, not_max);
+        if ((threadIdx.x & 31) == 0 && not_max) atomicAdd(&st->not_max, not_max);
+    }
+}
+
+// "trivial image" branch of skimage's _get_peak_mask: when every pixel of the label is a window maximum there are no
+// peaks, except the pixels a binary opening (3x3 cross, outside of the box = 0) removes from the label.
+__global__ void __launch_bounds__(kThreads) plm_trivial_kernel(const int32_t* __restrict__ d2, const uint8_t* __restrict__ mask,
+                                                               uint8_t* __restrict__ status, int Y, int X, int d,
+                                                               const PlmState* __restrict__ st) {
+    const int ymin = st->ymin, ymax = st->ymax, xmin = st->xmin, xmax = st->xmax, dmin = st->dmin;
+    if (ymax < ymin || st->not_max != 0) return;
+    const int bw = xmax - xmin + 1, bh = ymax - ymin + 1;
+    if (d == 0 || (bw == 1 && bh == 1)) return;
+    auto in_label = [&](int y, int x) {
+        return y >= ymin && y <= ymax && x >= xmin && x <= xmax && mask[(int64_t)y * X + x] != 0;
+    };
+    auto eroded = [&](int y, int x) {
+        return in_label(y, x) && in_label(y - 1, x) && in_label(y + 1, x) && in_label(y, x - 1) && in_label(y, x + 1);
+    };
+    const int64_t n = (int64_t)bh * bw;
+    for (int64_t j = (int64_t)blockIdx.x * kThreads + threadIdx.x; j < n; j += (int64_t)gridDim.x * kThreads) {
+        const int y = ymin + (int)(j / bw), x = xmin + (int)(j % bw);
+        const int64_t i = (int64_t)y * X + x;
+        if (!mask[i]) continue;
+        const bool opened = eroded(y, x) || eroded(y - 1, x) || eroded(y + 1, x) || eroded(y, x - 1) || eroded(y, x + 1);
+        status[i] = (!opened && d2[i] > dmin) ? 1 : 0;
+    }
+}
+
+__global__ void __launch_bounds__(kThreads) plm_list_kernel(const uint8_t* __restrict__ status, int32_t* __restrict__ list,
+                                                            int X, PlmState* st) {
+    const int ymin = st->ymin, ymax = st->ymax, xmin = st->xmin, xmax = st->xmax;
+    if (ymax < ymin) return;
+    const int bw = xmax - xmin + 1;
+    const int64_t n = (int64_t)(ymax - ymin + 1) * bw;
+    for (int64_t j = (int64_t)blockIdx.x * kThreads + threadIdx.x; j < n; j += (int64_t)gridDim.x * kThreads) {
+        const int y = ymin + (int)(j / bw), x = xmin + (int)(j % bw);
+        const int64_t i = (int64_t)y * X + x;
+        if (status[i] == 1) list[atomicAdd(&st->n_cand, 1)] = (int32_t)i;
+    }
+}
+
+// One look at candidate i: 2 accept, 3 reject, 1 still waiting for a stronger neighbour.  "Stronger" = larger value, or
+// equal value and earlier in raster order — the order of the reference's stable sort.
+__device__ __forceinline__ int plm_decide(const int32_t* __restrict__ d2, const volatile uint8_t* status, int Y, int X, int d,
+                                          int i) {
+    const int y = i / X, x = i - y * X;
+    const int v = d2[i];
+    bool blocked = false;
+    for (int yy = max(y - d + 1, 0); yy <= min(y + d - 1, Y - 1); ++yy)
+        for (int xx = max(x - d + 1, 0); xx <= min(x + d - 1, X - 1); ++xx) {
+            const int j = yy * X + xx;
+            const int s = status[j];
+            if (s == 0 || s == 3 || j == i) continue;
+            const int w = d2[j];
+            if (w > v || (w == v && j < i)) {
+                if (s == 2) return 3;
+                blocked = true;
+            }
+        }
+    return blocked ? 1 : 2;
+}
+
+__global__ void __launch_bounds__(kThreads) plm_round_kernel(const int32_t* __restrict__ d2, uint8_t* status,
+                                                             const int32_t* __restrict__ list, int Y, int X, int d,
+                                                             const PlmState* __restrict__ st) {
+    const int n = st->n_cand;
+    for (int k = blockIdx.x * kThreads + threadIdx.x; k < n; k += gridDim.x * kThreads) {
+        const int i = list[k];
+        if (status[i] != 1) continue;
+        const int s = plm_decide(d2, status, Y, X, d, i);
+        if (s != 1) status[i] = (uint8_t)s;
+    }
+}
+
+// what the grid-wide rounds left (plateaus): one block, rounds separated by block barriers
+__global__ void __launch_bounds__(1024) plm_finish_kernel(const int32_t* __restrict__ d2, uint8_t* status,
+                                                          int32_t* __restrict__ list, int Y, int X, int d, PlmState* st) {
+    __shared__ int s_n, s_left;
+    const int n = st->n_cand;
+    // compact the undecided ones to the front of the list
+    if (threadIdx.x == 0) s_n = 0;
+    __syncthreads();
+    for (int base = 0; base < n; base += 1024) {
+        const int k = base + threadIdx.x;
+        const int i = k < n ? list[k] : -1;
+        const bool open = i >= 0 && status[i] == 1;
+        __syncthreads();  // everyone has read its slot before slots are overwritten (writes go to positions <= k)
+        if (open) list[atomicAdd(&s_n, 1)] = i;
+        __syncthreads();
+    }
+    int m = s_n;
+    while (m > 0) {
+        if (threadIdx.x == 0) s_left = 0;
+        __syncthreads();
+        for (int k = threadIdx.x; k < m; k += 1024) {
+            const int i = list[k];
+            if (status[i] != 1) continue;
+            const int s = plm_decide(d2, status, Y, X, d, i);
+            if (s != 1) {
+                status[i] = (uint8_t)s;
+                __threadfence_block();
+            } else {
+                atomicAdd(&s_left, 1);
+            }
+        }
+        __syncthreads();
+        m = s_left ? m : 0;
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(kThreads) plm_out_kernel(const uint8_t* __restrict__ status, uint8_t* __restrict__ peaks,
+                                                           int64_t n) {
+    for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kThreads)
+        peaks[i] = status[i] == 2;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// flood
+// ---------------------------------------------------------------------------------------------------------------
+
+constexpr int kPixBits = 27;  // queue entry = height key (32 bits) << 32 | pixel index (27 bits)
+constexpr uint32_t kPixMask = (1u << kPixBits) - 1u;
+
+__device__ __forceinline__ uint32_t height_key(int32_t h, int negate) {
+    return (uint32_t)(negate ? -h : h) ^ 0x80000000u;  // unsigned order = signed order of the height
+}
+
+__global__ void __launch_bounds__(kThreads) ws_area_kernel(const int32_t* __restrict__ comp, const int32_t* __restrict__ markers,
+                                                           int32_t* __restrict__ out, int64_t n, int32_t* __restrict__ area,
+                                                           int32_t* __restrict__ n_seed) {
+    const int lane = threadIdx.x & 31;
+    const int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+    const bool in = i < n;
+    const int32_t c = in ? comp[i] : 0;
+    if (in) {
+        const int32_t m = markers[i];
+        out[i] = m;
+        if (m != 0 && c > 0) atomicAdd(&n_seed[c], 1);
+    }
+    const int32_t cp = __shfl_up_sync(0xffffffffu, c, 1);
+    const bool fg = c > 0;
+    const bool start = fg && (lane == 0 || cp != c);
+    const unsigned brks = __ballot_sync(0xffffffffu, !fg || start);
+    if (!start) return;
+    const unsigned stop = brks & (lane == 31 ? 0u : (0xffffffffu << (lane + 1)));
+    atomicAdd(&area[c], (stop ? (__ffs(stop) - 1) : 32) - lane);  // one atomic per run of equal region ids
+}
+
+// exclusive prefix sum of area[1..n_comp] → offset[c] (one block; regions are few compared with pixels)
+__global__ void __launch_bounds__(1024) ws_offsets_kernel(const int32_t* __restrict__ area, const int32_t* __restrict__ n_comp_p,
+                                                          int64_t cap, int32_t* __restrict__ offset, int32_t* __restrict__ ticket) {
+    __shared__ int s_warp[32];
+    __shared__ int s_carry;
+    const int n_comp = (int)min((int64_t)*n_comp_p, cap - 1);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) {
+        s_carry = 0;
+        *ticket = 0;
+    }
+    __syncthreads();
+    for (int base = 1; base <= n_comp; base += 1024) {
+        const int c = base + threadIdx.x;
+        const int a = c <= n_comp ? area[c] : 0;
+        int v = a;
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, v, o);
+            if (lane >= o) v += t;
+        }
+        if (lane == 31) s_warp[warp] = v;
+        __syncthreads();
+        if (warp == 0) {
+            int w = s_warp[lane];
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, w, o);
+                if (lane >= o) w += t;
+            }
+            s_warp[lane] = w;
+        }
+        __syncthreads();
+        const int excl = s_carry + (warp ? s_warp[warp - 1] : 0) + v - a;
+        if (c <= n_comp) offset[c] = excl;
+        __syncthreads();
+        if (threadIdx.x == 1023) s_carry = excl + a;
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(kThreads) ws_seed_kernel(const int32_t* __restrict__ comp, const int32_t* __restrict__ markers,
+                                                           const int32_t* __restrict__ height, int negate, int64_t n,
+                                                           const int32_t* __restrict__ offset, int32_t* __restrict__ fill,
+                                                           uint64_t* __restrict__ queue) {
+    const int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+    if (i >= n) return;
+    const int32_t c = comp[i];
+    if (c <= 0 || markers[i] == 0) return;
+    const int pos = atomicAdd(&fill[c], 1);
+    queue[offset[c] + pos] = ((uint64_t)height_key(height[i], negate) << 32) | (uint32_t)i;
+}
+
+struct FloodArgs {
+    const int32_t* comp;
+    const int32_t* height;
+    const int32_t* n_comp;
+    const int32_t* offset;
+    const int32_t* n_seed;
+    int32_t* out;
+    uint64_t* qa;
+    uint64_t* qb;
+    unsigned long long* claim;
+    int32_t* ticket;
+    int64_t cap;
+    int Y, X, negate;
+};
+
+__device__ __forceinline__ int block_scan_incl(int v, int* s_warp) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, v, o);
+        if (lane >= o) v += t;
+    }
+    if (lane == 31) s_warp[warp] = v;
+    __syncthreads();
+    int add = 0;
+    for (int w = 0; w < warp; ++w) add += s_warp[w];
+    return v + add;
+}
+
+__global__ void __launch_bounds__(kThreads, 8) ws_flood_kernel(FloodArgs a) {
+    __shared__ int s_c, s_istar, s_npop, s_warp[kThreads / 32], s_tot;
+    __shared__ uint32_t s_hnext;
+    const int tid = threadIdx.x;
+    const int X = a.X, Y = a.Y;
+    const int n_comp = (int)min((int64_t)*a.n_comp, a.cap - 1);
+    const int dq[4] = {-X, -1, 1, X};
+    for (;;) {
+        __syncthreads();
+        if (tid == 0) s_c = atomicAdd(a.ticket, 1) + 1;
+        __syncthreads();
+        const int c = s_c;
+        if (c > n_comp) return;
+        int m = a.n_seed[c];
+        if (m == 0) continue;
+        uint64_t* cur = a.qa + a.offset[c];
+        uint64_t* nxt = a.qb + a.offset[c];
+        // seeds arrived in any order: put them in raster order (their pixel index), find the lowest height
+        if (tid == 0) s_hnext = 0xffffffffu;
+        __syncthreads();
+        for (int i = tid; i < m; i += kThreads) {
+            const uint64_t e = cur[i];
+            const uint32_t p = (uint32_t)e & kPixMask;
+            int rank = 0;
+            for (int j = 0; j < m; ++j) rank += ((uint32_t)cur[j] & kPixMask) < p;
+            nxt[rank] = e;
+            atomicMin(&s_hnext, (uint32_t)(e >> 32));
+        }
+        __syncthreads();
+        {
+            uint64_t* t = cur;
+            cur = nxt;
+            nxt = t;
+        }
+        uint32_t step = 0;
+        while (m > 0) {
+            const uint32_t hmin = s_hnext;
+            const unsigned long long keybase = (unsigned long long)(0xffffffffu - step) << 32;
+            if (tid == 0) {
+                s_istar = INT32_MAX;
+                s_npop = 0;
+            }
+            __syncthreads();
+            // A: every entry of the lowest height claims its free neighbours; note the first that uncovers a lower pixel
+            for (int i = tid; i < m; i += kThreads) {
+                const uint64_t e = cur[i];
+                if ((uint32_t)(e >> 32) != hmin) continue;
+                const int p = (int)((uint32_t)e & kPixMask);
+                const int y = p / X, x = p - y * X;
+                const bool ok[4] = {y > 0, x > 0, x + 1 < X, y + 1 < Y};
+                bool lower = false;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    if (!ok[k]) continue;
+                    const int q = p + dq[k];
+                    if (a.comp[q] != c || a.out[q] != 0) continue;
+                    atomicMin(&a.claim[q], keybase | (unsigned)(i * 4 + k));
+                    lower |= height_key(a.height[q], a.negate) < hmin;
+                }
+                if (lower) atomicMin(&s_istar, i);
+            }
+            __syncthreads();
+            const int istar = s_istar;
+            {
+                int mine = 0;
+                for (int i = tid; i < m; i += kThreads) mine += ((uint32_t)(cur[i] >> 32) == hmin) && i <= istar;
+                mine = __reduce_add_sync(0xffffffffu, mine);
+                if ((tid & 31) == 0 && mine) atomicAdd(&s_npop, mine);
+            }
+            if (tid == 0) s_hnext = 0xffffffffu;
+            __syncthreads();
+            const int kept_total = m - s_npop;
+            // B: survivors keep their order at the front; the pixels won follow, ordered by (winner's position, neighbour)
+            int kept_carry = 0, push_carry = 0;
+            uint32_t hnext = 0xffffffffu;
+            for (int base = 0; base < m; base += kThreads) {
+                const int i = base + tid;
+                uint64_t e = 0;
+                bool popped = false;
+                int won = 0;  // bit k: neighbour k is mine
+                int p = 0;
+                if (i < m) {
+                    e = cur[i];
+                    popped = (uint32_t)(e >> 32) == hmin && i <= istar;
+                    if (popped) {
+                        p = (int)((uint32_t)e & kPixMask);
+                        const int y = p / X, x = p - y * X;
+                        const bool ok[4] = {y > 0, x > 0, x + 1 < X, y + 1 < Y};
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            if (ok[k] && __ldcg(&a.claim[p + dq[k]]) == (keybase | (unsigned)(i * 4 + k))) won |= 1 << k;
+                    }
+                }
+                const int kept = (i < m && !popped) ? 1 : 0;
+                const int packed = kept | (__popc(won) << 16);
+                const int incl = block_scan_incl(packed, s_warp);
+                if (tid == kThreads - 1) s_tot = incl;
+                const int excl = incl - packed;
+                if (kept) {
+                    nxt[kept_carry + (excl & 0xffff)] = e;
+                    hnext = min(hnext, (uint32_t)(e >> 32));
+                }
+                if (won) {
+                    const int32_t label = a.out[p];
+                    int pos = kept_total + push_carry + (excl >> 16);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        if (won & (1 << k)) {
+                            const int q = p + dq[k];
+                            const uint32_t hk = height_key(a.height[q], a.negate);
+                            a.out[q] = label;
+                            nxt[pos++] = ((uint64_t)hk << 32) | (uint32_t)q;
+                            hnext = min(hnext, hk);
+                        }
+                }
+                __syncthreads();
+                kept_carry += s_tot & 0xffff;
+                push_carry += s_tot >> 16;
+                __syncthreads();
+            }
+            hnext = __reduce_min_sync(0xffffffffu, hnext);
+            if ((tid & 31) == 0) atomicMin(&s_hnext, hnext);
+            __syncthreads();
+            m = kept_carry + push_carry;
+            uint64_t* t = cur;
+            cur = nxt;
+            nxt = t;
+            ++step;
+        }
+    }
+}
+
+}  // namespace
+
+extern "C" size_t be_peak_local_max_workspace_bytes(int64_t Y, int64_t X) {
+    if (Y <= 0 || X <= 0) return 256;
+    const size_t n = (size_t)Y * X;
+    return 256 + be_align_up(4 * n, 256) + be_align_up(n, 256) + be_align_up(4 * n, 256);
+}
+
+extern "C" int be_peak_local_max_i32(const int32_t* d2, const uint8_t* mask, uint8_t* peaks, int64_t Y, int64_t X,
+                                     int min_distance, void* ws, be_stream_t stream) {
+    BE_REQUIRE(d2 && mask && peaks && ws, BE_ERR_INVALID_ARG, "be_peak_local_max_i32: null pointer");
+    BE_REQUIRE(Y > 0 && X > 0, BE_ERR_INVALID_ARG, "be_peak_local_max_i32: empty input");
+    BE_REQUIRE(Y * X < ((int64_t)1 << 31), BE_ERR_TOO_LARGE, "be_peak_local_max_i32: more than 2^31 pixels");
+    BE_REQUIRE(min_distance >= 0 && min_distance <= 64, BE_ERR_INVALID_ARG, "be_peak_local_max_i32: min_distance %d not in 0..64",
+               min_distance);
+    cudaStream_t s = (cudaStream_t)stream;
+    const int64_t n = Y * X;
+    char* w = (char*)ws;
+    PlmState* st = (PlmState*)w;
+    w += 256;
+    int32_t* rowmax = (int32_t*)w;
+    w += be_align_up(4 * (size_t)n, 256);
+    uint8_t* status = (uint8_t*)w;
+    w += be_align_up((size_t)n, 256);
+    int32_t* list = (int32_t*)w;
+    const unsigned grid = (unsigned)min((n + kThreads - 1) / kThreads, (int64_t)BE_SM_COUNT * 8);
+    const int d = min_distance;
+    BE_CUDA(cudaMemsetAsync(status, 0, (size_t)n, s));
+    plm_init_kernel<<<1, 1, 0, s>>>(st);
+    BE_LAUNCH_CHECK();
+    plm_roi_kernel<<<grid, kThreads, 0, s>>>(d2, mask, (int)Y, (int)X, d, st);
+    BE_LAUNCH_CHECK();
+    plm_rowmax_kernel<<<grid, kThreads, 0, s>>>(d2, mask, rowmax, (int)Y, (int)X, d, st);
+    BE_LAUNCH_CHECK();
+    plm_peak_kernel<<<grid, kThreads, 0, s>>>(d2, mask, rowmax, status, (int)Y, (int)X, d, st);
+    BE_LAUNCH_CHECK();
+    plm_trivial_kernel<<<grid, kThreads, 0, s>>>(d2, mask, status, (int)Y, (int)X, d, st);
+    BE_LAUNCH_CHECK();
+    plm_list_kernel<<<grid, kThreads, 0, s>>>(status, list, (int)X, st);
+    BE_LAUNCH_CHECK();
+    for (int r = 0; r < 2; ++r) {
+        plm_round_kernel<<<grid, kThreads, 0, s>>>(d2, status, list, (int)Y, (int)X, d, st);
+        BE_LAUNCH_CHECK();
+    }
+    plm_finish_kernel<<<1, 1024, 0, s>>>(d2, status, list, (int)Y, (int)X, d, st);
+    BE_LAUNCH_CHECK();
+    plm_out_kernel<<<grid, kThreads, 0, s>>>(status, peaks, n);
+    BE_LAUNCH_CHECK();
+    return BE_OK;
+}
+
+static int64_t ws_region_cap(int64_t n) { return (n + 1) / 2 + 2; }  // most 4-connected regions n pixels can hold, + id 0
+
+extern "C" size_t be_watershed_workspace_bytes(int64_t Y, int64_t X) {
+    if (Y <= 0 || X <= 0) return 256;
+    const size_t n = (size_t)Y * X;
+    const size_t cap = (size_t)ws_region_cap((int64_t)n);
+    return 256 + 4 * be_align_up(4 * cap, 256) + 3 * be_align_up(8 * n, 256);
+}
+
+extern "C" int be_watershed_i32(const int32_t* height, int negate, const int32_t* markers, const int32_t* regions,
+                                const int32_t* n_regions, int32_t* out, int64_t Y, int64_t X, void* ws, be_stream_t stream) {
+    BE_REQUIRE(height && markers && regions && n_regions && out && ws, BE_ERR_INVALID_ARG, "be_watershed_i32: null pointer");
+    BE_REQUIRE(Y > 0 && X > 0, BE_ERR_INVALID_ARG, "be_watershed_i32: empty input");
+    BE_REQUIRE(Y * X <= (int64_t)kPixMask, BE_ERR_TOO_LARGE, "be_watershed_i32: more than 2^27 pixels");
+    cudaStream_t s = (cudaStream_t)stream;
+    const int64_t n = Y * X, cap = ws_region_cap(n);
+    char* w = (char*)ws;
+    int32_t* ticket = (int32_t*)w;
+    w += 256;
+    const size_t cap_bytes = be_align_up(4 * (size_t)cap, 256), q_bytes = be_align_up(8 * (size_t)n, 256);
+    int32_t* area = (int32_t*)w;
+    int32_t* n_seed = (int32_t*)(w + cap_bytes);
+    int32_t* fill = (int32_t*)(w + 2 * cap_bytes);
+    int32_t* offset = (int32_t*)(w + 3 * cap_bytes);
+    w += 4 * cap_bytes;
+    uint64_t* qa = (uint64_t*)w;
+    uint64_t* qb = (uint64_t*)(w + q_bytes);
+    unsigned long long* claim = (unsigned long long*)(w + 2 * q_bytes);
+    BE_CUDA(cudaMemsetAsync(area, 0, 3 * cap_bytes, s));                 // area, n_seed, fill
+    BE_CUDA(cudaMemsetAsync(claim, 0xff, 8 * (size_t)n, s));
+    const unsigned gpx = (unsigned)((n + kThreads - 1) / kThreads);
+    ws_area_kernel<<<gpx, kThreads, 0, s>>>(regions, markers, out, n, area, n_seed);
+    BE_LAUNCH_CHECK();
+    ws_offsets_kernel<<<1, 1024, 0, s>>>(area, n_regions, cap, offset, ticket);
+    BE_LAUNCH_CHECK();
+    ws_seed_kernel<<<gpx, kThreads, 0, s>>>(regions, markers, height, negate, n, offset, fill, qa);
+    BE_LAUNCH_CHECK();
+    FloodArgs a{regions, height, n_regions, offset, n_seed, out, qa, qb, claim, ticket, cap, (int)Y, (int)X, negate};
+    ws_flood_kernel<<<BE_SM_COUNT * 8, kThreads, 0, s>>>(a);
+    BE_LAUNCH_CHECK();
+    return BE_OK;
+}

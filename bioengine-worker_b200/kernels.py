@@ -482,3 +482,66 @@ def distance_transform_edt(mask: torch.Tensor, ws: Workspace = _default_ws) -> t
     w = ws.get(_lib.query("be_edt_workspace_bytes", N, Y, X), mask.device)
     _lib.call("be_edt_u8_f64", mask.data_ptr(), dist.data_ptr(), N, Y, X, w.data_ptr(), _stream())
     return dist
+
+
+@_on_tensor_device
+def distance_transform_edt_sq(mask: torch.Tensor, ws: Workspace = _default_ws) -> torch.Tensor:
+    """Square of scipy `distance_transform_edt(mask)` as exact int32, for (N, Y, X) uint8 masks."""
+    _check(mask, torch.uint8, "mask")
+    N, Y, X = mask.shape
+    d2 = torch.empty(mask.shape, dtype=torch.int32, device=mask.device)
+    w = ws.get(_lib.query("be_edt_workspace_bytes", N, Y, X), mask.device)
+    _lib.call("be_edt_sq_u8_i32", mask.data_ptr(), d2.data_ptr(), N, Y, X, w.data_ptr(), _stream())
+    return d2
+
+
+@_on_tensor_device
+def peak_local_max(dist2: torch.Tensor, mask: torch.Tensor, min_distance: int, ws: Workspace = _default_ws) -> torch.Tensor:
+    """skimage `peak_local_max(dist, min_distance=d, labels=mask)` on one (Y, X) int32 image (the squared distance) →
+    uint8 image with 1 at the selected coordinates."""
+    _check(dist2, torch.int32, "dist2")
+    _check(mask, torch.uint8, "mask")
+    if dist2.dim() != 2 or mask.shape != dist2.shape:
+        raise ValueError("peak_local_max: dist2 and mask must be (Y, X) tensors of one shape")
+    Y, X = dist2.shape
+    peaks = torch.empty_like(mask)
+    w = ws.get(_lib.query("be_peak_local_max_workspace_bytes", Y, X), mask.device)
+    _lib.call("be_peak_local_max_i32", dist2.data_ptr(), mask.data_ptr(), peaks.data_ptr(), Y, X, int(min_distance),
+              w.data_ptr(), _stream())
+    return peaks
+
+
+@_on_tensor_device
+def watershed(height: torch.Tensor, markers: torch.Tensor, mask: torch.Tensor, negate: bool = False,
+              ws: Workspace = _default_ws) -> torch.Tensor:
+    """skimage `watershed(image, markers, mask=mask)` (connectivity 1) on one (Y, X) image: int32 flood order (`negate`
+    floods by -height), int32 markers, uint8 mask → int32 labels."""
+    _check(height, torch.int32, "height")
+    _check(markers, torch.int32, "markers")
+    _check(mask, torch.uint8, "mask")
+    if height.dim() != 2 or markers.shape != height.shape or mask.shape != height.shape:
+        raise ValueError("watershed: height, markers and mask must be (Y, X) tensors of one shape")
+    Y, X = height.shape
+    regions, n_regions = ccl(mask[None], 1, ws=ws)
+    out = torch.empty_like(markers)
+    w = ws.get(_lib.query("be_watershed_workspace_bytes", Y, X), mask.device)
+    _lib.call("be_watershed_i32", height.data_ptr(), int(bool(negate)), markers.data_ptr(), regions.data_ptr(),
+              n_regions.data_ptr(), out.data_ptr(), Y, X, w.data_ptr(), _stream())
+    return out
+
+
+def instances_from_mask(mask: torch.Tensor, min_size: int = 300, radius: int = 4, min_distance: int = 8,
+                        ws: Workspace = _default_ws):
+    """ref: analysis_deployment.py:160-176 `_prob_to_instances` after the threshold, on one (Y, X) uint8 mask:
+    remove_small_objects → binary_closing(disk) → distance transform → peak_local_max → label(peaks) → watershed.
+    Returns (labels int32 (Y, X), number of seeds as a device tensor).  An empty mask comes back as zeros without a look
+    at it on the host: every stage maps nothing to nothing."""
+    _check(mask, torch.uint8, "mask")
+    if mask.dim() != 2:
+        raise ValueError("instances_from_mask: mask must be a (Y, X) tensor")
+    kept = remove_small_objects(mask[None], min_size, ws=ws)
+    closed = binary_closing(kept, disk_half_widths(radius), ws=ws)
+    d2 = distance_transform_edt_sq(closed, ws=ws)
+    peaks = peak_local_max(d2[0], closed[0], min_distance, ws=ws)
+    markers, n_seeds = ccl(peaks[None], 2, ws=ws)
+    return watershed(d2[0], markers[0], closed[0], negate=True, ws=ws), n_seeds

@@ -285,6 +285,40 @@ int be_binary_closing_u8(const uint8_t* mask, uint8_t* out, int64_t N, int64_t Y
 size_t be_edt_workspace_bytes(int64_t N, int64_t Y, int64_t X);
 int be_edt_u8_f64(const uint8_t* mask, double* dist, int64_t N, int64_t Y, int64_t X, void* ws, be_stream_t stream);
 
+/* The same transform as its exact integer square (saturated at INT32_MAX): the order and the ties of the distance
+ * without a square root — what the seed detection and the flood below work on. */
+int be_edt_sq_u8_i32(const uint8_t* mask, int32_t* dist2, int64_t N, int64_t Y, int64_t X, void* ws, be_stream_t stream);
+
+/* ---- seeds and marker flood (second part) ------------------------------------- */
+
+/* `skimage.feature.peak_local_max(dist, min_distance=d, labels=mask)` with every other argument at its default
+ * (analysis_deployment.py:171), on dist2 = the squared distance (any int32 image whose order is the wanted one):
+ * exclude_border = d, threshold = image minimum, (2d+1)^2 window maximum clipped to the bounding box of the
+ * border-stripped mask, skimage's special case for an image in which every masked pixel is a maximum, and the greedy
+ * thinning of the candidates (value descending, raster order among equals) to Chebyshev distance >= d.
+ *   peaks  [Y*X] uint8 out: 1 at the selected coordinates (the reference's boolean image `m`), 0 elsewhere
+ *   ws     be_peak_local_max_workspace_bytes(Y, X) bytes
+ * No host synchronisation; plateaus longer than the two grid-wide rounds settle are finished by one block. */
+size_t be_peak_local_max_workspace_bytes(int64_t Y, int64_t X);
+int be_peak_local_max_i32(const int32_t* dist2, const uint8_t* mask, uint8_t* peaks, int64_t Y, int64_t X,
+                          int min_distance, void* ws, be_stream_t stream);
+
+/* `skimage.segmentation.watershed(image, markers, mask=mask)` with connectivity 1, no compactness, no watershed line
+ * (analysis_deployment.py:175) for one (Y, X) image, Y*X < 2^27.
+ *   height     [Y*X] int32: the flood order (lower first); negate != 0 floods by -height (pass the squared distance)
+ *   markers    [Y*X] int32: seeds (0 = none); must lie inside the mask to flood
+ *   regions    [Y*X] int32: the mask as its 4-connected components, labelled 1..*n_regions (be_ccl_u8_i32 with
+ *              connectivity 1), 0 outside the mask; regions flood independently, one thread block each
+ *   n_regions  device pointer to the number of regions
+ *   out        [Y*X] int32: markers, grown over the mask; mask pixels no seed reaches stay 0
+ *   ws         be_watershed_workspace_bytes(Y, X) bytes
+ * Pixels leave the queue by (height, push order).  Seeds are pushed in raster order and seeds of equal height leave in
+ * that order; skimage's binary heap orders such complete ties by its array layout instead, so results can differ from
+ * skimage's on the boundary between two basins whose seeds have exactly the same height. */
+size_t be_watershed_workspace_bytes(int64_t Y, int64_t X);
+int be_watershed_i32(const int32_t* height, int negate, const int32_t* markers, const int32_t* regions,
+                     const int32_t* n_regions, int32_t* out, int64_t Y, int64_t X, void* ws, be_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

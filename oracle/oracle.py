@@ -309,6 +309,137 @@ def distance_transform_edt(mask: np.ndarray) -> np.ndarray:
     return ndi.distance_transform_edt(np.asarray(mask) != 0)
 
 
+def _exclude_border(labels: np.ndarray, width: int) -> np.ndarray:
+    out = labels.copy()
+    if width > 0:
+        for ax in range(out.ndim):
+            sl = [slice(None)] * out.ndim
+            sl[ax] = slice(None, width)
+            out[tuple(sl)] = 0
+            sl[ax] = slice(-width, None)
+            out[tuple(sl)] = 0
+    return out
+
+
+def _peak_mask(image: np.ndarray, footprint: np.ndarray, threshold: float, mask: np.ndarray) -> np.ndarray:
+    """skimage.feature.peak._get_peak_mask: pixels that equal the maximum over the footprint (edges replicated) and lie
+    above the threshold; an image in which every masked pixel is such a maximum has no peaks except pixels a binary
+    opening removes."""
+    if footprint.size == 1 or image.size == 1:
+        return image > threshold
+    out = image == ndi.maximum_filter(image, footprint=footprint, mode="nearest")
+    if np.all(out[mask]):
+        out[:] = False
+        out[np.logical_xor(mask, ndi.binary_opening(mask))] = True
+    out &= image > threshold
+    return out
+
+
+def _ensure_spacing(coord: np.ndarray, spacing: float) -> np.ndarray:
+    """skimage._shared.coord.ensure_spacing with p_norm = inf, restated as the greedy pass it performs: walk the points in
+    the given order; a point that is still in play removes every later point at Chebyshev distance < spacing.  (skimage
+    walks batches of growing size through a KD-tree; removed points never remove others, so the batches do not change
+    the outcome.)"""
+    from scipy.spatial import cKDTree
+
+    if len(coord) == 0:
+        return coord
+    near = cKDTree(coord).query_ball_point(coord, r=spacing, p=np.inf)
+    rejected = np.zeros(len(coord), dtype=bool)
+    for i, cand in enumerate(near):
+        if rejected[i]:
+            continue
+        for c in cand:
+            if c != i and np.abs(coord[c] - coord[i]).max() < spacing:
+                rejected[c] = True
+    return coord[~rejected]
+
+
+def peak_local_max(image: np.ndarray, min_distance: int, labels: np.ndarray) -> np.ndarray:
+    """`skimage.feature.peak_local_max(image, min_distance=d, labels=labels)` with every other argument at its default
+    (ref: analysis_deployment.py:171; third-party, PARITY UNPINNED — restated from skimage/feature/peak.py):
+    exclude_border = d on every axis, threshold = image.min(), footprint = ones((2d+1,)*ndim); per label, the bounding box
+    of the border-stripped label is cut out, pixels outside the label are set to the lowest float, peaks are pixels equal
+    to the window maximum (window clipped to the box) above the threshold, sorted by value (descending, stable, so raster
+    order among equals) and thinned to Chebyshev distance >= d.  Returns (n, ndim) coordinates."""
+    image = np.asarray(image)
+    threshold = image.min()
+    footprint = np.ones((2 * min_distance + 1,) * image.ndim, dtype=bool)
+    stripped = _exclude_border(labels.astype(int, casting="safe"), min_distance)
+    found = []
+    for idx, roi in enumerate(ndi.find_objects(stripped)):
+        if roi is None:
+            continue
+        label_mask = labels[roi] == idx + 1
+        obj = image[roi].copy()
+        obj[np.logical_not(label_mask)] = np.finfo(image.dtype).min if np.issubdtype(image.dtype, np.floating) else np.iinfo(image.dtype).min
+        mask = _peak_mask(obj, footprint, threshold, label_mask)
+        coord = np.nonzero(mask)
+        order = np.argsort(-obj[coord], kind="stable")
+        coord = _ensure_spacing(np.transpose(coord)[order], min_distance)
+        for ax, s in enumerate(roi):
+            coord[:, ax] += s.start
+        found.append(coord)
+    return np.vstack(found) if found else np.empty((0, image.ndim), dtype=int)
+
+
+_WS_LIB = None
+
+
+def _watershed_lib():
+    """oracle/watershed.c compiled with gcc into oracle/_build/ (built by __graft_entry__.build(), or here on first use)."""
+    global _WS_LIB
+    if _WS_LIB is None:
+        import ctypes
+        import os
+        import subprocess
+
+        here = os.path.dirname(os.path.abspath(__file__))
+        so = os.path.join(here, "_build", "liboracle_watershed.so")
+        src = os.path.join(here, "watershed.c")
+        if not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
+            os.makedirs(os.path.dirname(so), exist_ok=True)
+            subprocess.run(["gcc", "-O2", "-shared", "-fPIC", "-o", so, src], check=True)
+        lib = ctypes.CDLL(so)
+        lib.oracle_watershed.restype = ctypes.c_int
+        lib.oracle_watershed.argtypes = [ctypes.c_void_p] * 4 + [ctypes.c_int64, ctypes.c_int64, ctypes.c_int]
+        _WS_LIB = lib
+    return _WS_LIB
+
+
+def watershed(image: np.ndarray, markers: np.ndarray, mask: np.ndarray, ties: str = "heap") -> np.ndarray:
+    """`skimage.segmentation.watershed(image, markers, mask=mask)` for 2-D inputs (ref: analysis_deployment.py:175); the
+    flood itself is oracle/watershed.c.  ties="heap": skimage's binary heap decides between markers that tie in value;
+    ties="fifo": first pushed, first popped (what the CUDA flood implements)."""
+    image = np.ascontiguousarray(image, dtype=np.float64)
+    markers = np.ascontiguousarray(markers, dtype=np.int32)
+    mask = np.ascontiguousarray(np.asarray(mask) != 0, dtype=np.uint8)
+    assert image.ndim == 2 and markers.shape == image.shape == mask.shape
+    out = np.empty_like(markers)
+    rc = _watershed_lib().oracle_watershed(image.ctypes.data, markers.ctypes.data, mask.ctypes.data, out.ctypes.data,
+                                           image.shape[0], image.shape[1], {"heap": 0, "fifo": 1}[ties])
+    if rc != 0:
+        raise MemoryError("oracle_watershed")
+    return out
+
+
+def prob_to_instances(prob: np.ndarray, ties: str = "heap", parts: Optional[dict] = None) -> np.ndarray:
+    """ref: analysis_deployment.py:160-176 `_prob_to_instances`, line by line."""
+    binary = remove_small_objects(prob > 0.5, 300)
+    if not binary.any():
+        return np.zeros(prob.shape, dtype=np.int32)
+    closed = binary_closing_disk(binary, 4)
+    dist = distance_transform_edt(closed)
+    coords = peak_local_max(dist, 8, closed)
+    m = np.zeros(closed.shape, dtype=bool)
+    if len(coords):
+        m[tuple(coords.T)] = True
+    markers = label(m)
+    if parts is not None:
+        parts.update(closed=closed, dist=dist, coords=coords, markers=markers)
+    return watershed(-dist, markers, closed, ties).astype(np.int32)
+
+
 def regionprops_table(labels: np.ndarray, pixel_size_nm: float = 5.0) -> Dict[str, list]:
     """The property loop of ref: analysis_deployment.py:256-271, with skimage's definitions (Appendix C):
 

@@ -128,11 +128,11 @@ def test_analyze_matches_fibsem_oracle(dev):
     assert (ar_got[thin] > 1e3).all()
     np.testing.assert_allclose(res["properties"]["eccentricity"], want["eccentricity"], rtol=1e-6, atol=1e-6)
     assert res["image_shape"] == [H, W] and set(res) >= {"labels", "properties", "n_mitochondria", "pixel_size_nm", "model"}
-    # cleaned variant: remove_small_objects(300) + binary_closing(disk(4)) before labelling, as `_prob_to_instances` starts
+    # the default: the reference's `_prob_to_instances` (size filter, closing, distance peaks, watershed)
     res3 = asyncio.run(dep.analyze(img.tolist(), tile_size=tile, overlap=ov, as_numpy=True))   # cleanup=True is the default
-    kept = O.remove_small_objects(prob > 0.5, 300)
-    want3 = O.label(O.binary_closing_disk(kept, 4)) if kept.any() else np.zeros((H, W), np.int32)
+    want3 = O.prob_to_instances(prob, ties="fifo")
     assert np.array_equal(res3["labels"], want3) and res3["n_mitochondria"] == want3.max()
+    assert res3["properties"]["label"] == O.regionprops_table(want3, 5.0)["label"]
     # small image → single untiled call (ref: analysis_deployment.py:247-248)
     small = img[:100, :120]
     res2 = asyncio.run(dep.analyze(small.tolist(), tile_size=128, overlap=32, as_numpy=True, cleanup=False))
