@@ -50,6 +50,10 @@ def main():
         "watershed(regions+flood)": ev(lambda: K.watershed(d2[0], markers[0], closed[0], negate=True)),
         "all": ev(lambda: K.instances_from_mask(mask)),
     }
+    torch.cuda.synchronize()
+    K.watershed(d2[0], markers[0], closed[0], negate=True)
+    torch.cuda.synchronize()
+    st = K._default_ws._buf[:64].view(torch.int64).cpu().numpy()
     t0 = time.perf_counter()
     parts = {}
     want = O.prob_to_instances(prob, ties="fifo", parts=parts)
@@ -57,7 +61,7 @@ def main():
     regions = int(K.ccl(closed, 1)[1].item())
     print(json.dumps({"size": S, "foreground": float(closed.float().mean().item()), "regions": regions,
                       "seeds": int(n_seeds.item()), "ms": {k: round(v, 3) for k, v in t.items()},
-                      "cpu_oracle_ms_one_core": round(cpu * 1e3, 1), "equal_to_oracle": bool(np.array_equal(out.cpu().numpy(), want))}))
+                      "cpu_oracle_ms_one_core": round(cpu * 1e3, 1), "flood_stats[steps,entries,max_queue,max_steps]": None if st is None else st[1:5].tolist(), "equal_to_oracle": bool(np.array_equal(out.cpu().numpy(), want))}))
 
 
 if __name__ == "__main__":

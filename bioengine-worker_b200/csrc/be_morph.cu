@@ -137,60 +137,64 @@ __global__ void __launch_bounds__(kThreads) edt_columns_kernel(const uint8_t* __
     }
 }
 
-// phase 2: one block per row; thread 0 builds the lower envelope of the parabolas (x - i)^2 + g(i)^2 in shared memory,
-// then all threads evaluate it
+// phase 2: one block per row.  A background pixel (g = 0) separates the row: for a pixel between two of them no parabola
+// from beyond either can be the lowest.  So every run of foreground pixels is a problem of its own — one thread builds the
+// lower envelope of the parabolas (x - i)^2 + g(i)^2 of its run and of the background pixel on its left in its own stretch
+// of shared memory, then walks the run back to front; the background pixel on its right is kept out of the stack (its
+// slot belongs to the next run) and enters as a min with (end - x)^2.
 // OUT = double: the distance; OUT = int32_t: its square (exact, saturated) — what the seed detection and the flood order by
 template <typename OUT>
 __global__ void __launch_bounds__(kThreads) edt_rows_kernel(const int32_t* __restrict__ g, OUT* __restrict__ dist, int Y,
                                                             int X) {
     extern __shared__ int smem[];
-    int* s = smem;           // parabola apexes of the envelope
+    int* s = smem;           // parabola apexes of the envelopes
     int* t = smem + X;       // t[q]: first x where s[q] is the lowest
     int* gs = smem + 2 * X;  // this row of g
-    __shared__ int s_q;
     const int64_t row = blockIdx.x;
     const int32_t* gr = g + row * X;
     for (int x = threadIdx.x; x < X; x += kThreads) gs[x] = gr[x];
     __syncthreads();
-    if (threadIdx.x == 0) {
+    auto put = [&](int x, long long d2) {
+        if constexpr (sizeof(OUT) == 8) dist[row * X + x] = sqrt((double)d2);
+        else dist[row * X + x] = (OUT)min(d2, (long long)INT32_MAX);
+    };
+    for (int x0 = threadIdx.x; x0 < X; x0 += kThreads) {
+        if (gs[x0] == 0) {
+            put(x0, 0);
+            continue;
+        }
+        if (x0 > 0 && gs[x0 - 1] != 0) continue;  // not the first pixel of a run
+        int end = x0 + 1;
+        while (end < X && gs[end] != 0) ++end;     // [x0, end) is the run; gs[end] == 0 if end < X
+        const int a = x0 > 0 ? x0 - 1 : 0;         // first candidate: the background pixel on the left, if there is one
         auto f = [&](long long x, long long i) {
             const long long gi = gs[i];
             return (x - i) * (x - i) + gi * gi;
         };
-        int q = 0;
-        s[0] = 0;
-        t[0] = 0;
-        for (int u = 1; u < X; ++u) {
-            while (q >= 0 && f(t[q], s[q]) > f(t[q], u)) --q;
-            if (q < 0) {
-                q = 0;
-                s[0] = u;
+        int q = a;  // stack lives in s[a..], t[a..]
+        s[a] = a;
+        t[a] = a;
+        for (int u = a + 1; u < end; ++u) {
+            while (q >= a && f(t[q], s[q]) > f(t[q], u)) --q;
+            if (q < a) {
+                q = a;
+                s[a] = u;
             } else {
-                // first x where parabola u lies below parabola s[q]
                 const long long i = s[q], gi = gs[i], gu = gs[u];
                 const long long w = 1 + (((long long)u * u - i * i + gu * gu - gi * gi) / (2 * ((long long)u - i)));
-                if (w < X) {
+                if (w < end) {
                     ++q;
                     s[q] = u;
                     t[q] = (int)w;
                 }
             }
         }
-        s_q = q;
-    }
-    __syncthreads();
-    // segment of x: largest q with t[q] <= x (binary search; t is increasing)
-    const int q_max = s_q;
-    for (int x = threadIdx.x; x < X; x += kThreads) {
-        int lo = 0, hi = q_max;
-        while (lo < hi) {
-            const int mid = (lo + hi + 1) >> 1;
-            if (t[mid] <= x) lo = mid; else hi = mid - 1;
+        for (int x = end - 1; x >= x0; --x) {
+            while (q > a && t[q] > x) --q;
+            long long d2 = f(x, s[q]);
+            if (end < X) d2 = min(d2, (long long)(end - x) * (end - x));
+            put(x, d2);
         }
-        const long long i = s[lo], gi = gs[i];
-        const long long d2 = ((long long)x - i) * ((long long)x - i) + gi * gi;
-        if constexpr (sizeof(OUT) == 8) dist[row * X + x] = sqrt((double)d2);
-        else dist[row * X + x] = (OUT)min(d2, (long long)INT32_MAX);
     }
 }
 

@@ -294,6 +294,7 @@ __global__ void __launch_bounds__(1024) ws_offsets_kernel(const int32_t* __restr
         s_carry = 0;
         *ticket = 0;
     }
+    if (threadIdx.x < 8) ((unsigned long long*)(ticket + 2))[threadIdx.x] = 0;
     __syncthreads();
     for (int base = 1; base <= n_comp; base += 1024) {
         const int c = base + threadIdx.x;
@@ -349,21 +350,22 @@ struct FloodArgs {
     int Y, X, negate;
 };
 
-__device__ __forceinline__ int block_scan_incl(int v, int* s_warp) {
+__device__ __forceinline__ unsigned long long block_scan_incl(unsigned long long v, unsigned long long* s_warp) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (int o = 1; o < 32; o <<= 1) {
-        const int t = __shfl_up_sync(0xffffffffu, v, o);
+        const unsigned long long t = __shfl_up_sync(0xffffffffu, v, o);
         if (lane >= o) v += t;
     }
     if (lane == 31) s_warp[warp] = v;
     __syncthreads();
-    int add = 0;
+    unsigned long long add = 0;
     for (int w = 0; w < warp; ++w) add += s_warp[w];
     return v + add;
 }
 
-__global__ void __launch_bounds__(kThreads, 8) ws_flood_kernel(FloodArgs a) {
-    __shared__ int s_c, s_istar, s_npop, s_warp[kThreads / 32], s_tot;
+__global__ void __launch_bounds__(kThreads, 4) ws_flood_kernel(FloodArgs a) {
+    __shared__ int s_c, s_istar;
+    __shared__ unsigned long long s_warp[kThreads / 32], s_tot;
     __shared__ uint32_t s_hnext;
     const int tid = threadIdx.x;
     const int X = a.X, Y = a.Y;
@@ -397,99 +399,126 @@ __global__ void __launch_bounds__(kThreads, 8) ws_flood_kernel(FloodArgs a) {
             nxt = t;
         }
         uint32_t step = 0;
+        unsigned long long sum_m = 0, max_m = 0;
         while (m > 0) {
+            sum_m += (unsigned long long)m;
+            max_m = max(max_m, (unsigned long long)m);
             const uint32_t hmin = s_hnext;
             const unsigned long long keybase = (unsigned long long)(0xffffffffu - step) << 32;
-            if (tid == 0) {
-                s_istar = INT32_MAX;
-                s_npop = 0;
-            }
+            if (tid == 0) s_istar = INT32_MAX;
             __syncthreads();
-            // A: every entry of the lowest height claims its free neighbours; note the first that uncovers a lower pixel
+            // A: every entry of the lowest height claims its free neighbours; note the first that uncovers a lower pixel.
+            // All twelve loads of an entry are issued before any is looked at — the step is a chain of L2 round trips.
             for (int i = tid; i < m; i += kThreads) {
                 const uint64_t e = cur[i];
                 if ((uint32_t)(e >> 32) != hmin) continue;
                 const int p = (int)((uint32_t)e & kPixMask);
                 const int y = p / X, x = p - y * X;
                 const bool ok[4] = {y > 0, x > 0, x + 1 < X, y + 1 < Y};
+                int rc[4], ro[4], rh[4];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const int q = ok[k] ? p + dq[k] : p;
+                    rc[k] = a.comp[q];
+                    ro[k] = a.out[q];
+                    rh[k] = a.height[q];
+                }
                 bool lower = false;
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
-                    if (!ok[k]) continue;
-                    const int q = p + dq[k];
-                    if (a.comp[q] != c || a.out[q] != 0) continue;
-                    atomicMin(&a.claim[q], keybase | (unsigned)(i * 4 + k));
-                    lower |= height_key(a.height[q], a.negate) < hmin;
+                    if (!ok[k] || rc[k] != c || ro[k] != 0) continue;
+                    atomicMin(&a.claim[p + dq[k]], keybase | (unsigned)(i * 4 + k));
+                    lower |= height_key(rh[k], a.negate) < hmin;
                 }
                 if (lower) atomicMin(&s_istar, i);
             }
             __syncthreads();
             const int istar = s_istar;
-            {
-                int mine = 0;
-                for (int i = tid; i < m; i += kThreads) mine += ((uint32_t)(cur[i] >> 32) == hmin) && i <= istar;
-                mine = __reduce_add_sync(0xffffffffu, mine);
-                if ((tid & 31) == 0 && mine) atomicAdd(&s_npop, mine);
-            }
             if (tid == 0) s_hnext = 0xffffffffu;
-            __syncthreads();
-            const int kept_total = m - s_npop;
-            // B: survivors keep their order at the front; the pixels won follow, ordered by (winner's position, neighbour)
-            int kept_carry = 0, push_carry = 0;
-            uint32_t hnext = 0xffffffffu;
-            for (int base = 0; base < m; base += kThreads) {
-                const int i = base + tid;
-                uint64_t e = 0;
-                bool popped = false;
-                int won = 0;  // bit k: neighbour k is mine
-                int p = 0;
-                if (i < m) {
-                    e = cur[i];
-                    popped = (uint32_t)(e >> 32) == hmin && i <= istar;
-                    if (popped) {
-                        p = (int)((uint32_t)e & kPixMask);
-                        const int y = p / X, x = p - y * X;
-                        const bool ok[4] = {y > 0, x > 0, x + 1 < X, y + 1 < Y};
+            // A2: the entries that leave learn which neighbours they won; the answer (4 bits + a "leaves" bit) rides in the
+            // free bits of the entry
+            for (int i = tid; i < m && i <= istar; i += kThreads) {
+                const uint64_t e = cur[i];
+                if ((uint32_t)(e >> 32) != hmin) continue;
+                const int p = (int)((uint32_t)e & kPixMask);
+                const int y = p / X, x = p - y * X;
+                const bool ok[4] = {y > 0, x > 0, x + 1 < X, y + 1 < Y};
+                unsigned long long cl[4];
 #pragma unroll
-                        for (int k = 0; k < 4; ++k)
-                            if (ok[k] && __ldcg(&a.claim[p + dq[k]]) == (keybase | (unsigned)(i * 4 + k))) won |= 1 << k;
-                    }
-                }
-                const int kept = (i < m && !popped) ? 1 : 0;
-                const int packed = kept | (__popc(won) << 16);
-                const int incl = block_scan_incl(packed, s_warp);
-                if (tid == kThreads - 1) s_tot = incl;
-                const int excl = incl - packed;
-                if (kept) {
-                    nxt[kept_carry + (excl & 0xffff)] = e;
+                for (int k = 0; k < 4; ++k) cl[k] = __ldcg(&a.claim[ok[k] ? p + dq[k] : p]);
+                unsigned won = 0x10u;
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    if (ok[k] && cl[k] == (keybase | (unsigned)(i * 4 + k))) won |= 1u << k;
+                cur[i] = e | ((uint64_t)won << kPixBits);
+            }
+            __syncthreads();
+            // B: survivors keep their order at the front; the pixels won follow, ordered by (winner's position, neighbour).
+            // A thread owns a contiguous stretch of the queue, so one block-wide scan per step places everything; a
+            // leaving entry gets the position of its first push written over its height.
+            const int L = (m + kThreads - 1) / kThreads;
+            const int lo = min(tid * L, m), hi = min(lo + L, m);
+            int kept = 0, push = 0;
+            for (int i = lo; i < hi; ++i) {
+                const unsigned flags = ((uint32_t)cur[i]) >> kPixBits;
+                if (flags) push += __popc(flags & 0xfu);
+                else ++kept;
+            }
+            const unsigned long long packed = (unsigned long long)kept | ((unsigned long long)push << 32);
+            const unsigned long long incl = block_scan_incl(packed, s_warp);
+            if (tid == kThreads - 1) s_tot = incl;
+            __syncthreads();
+            const int kept_total = (int)(uint32_t)s_tot, push_total = (int)(s_tot >> 32);
+            int kept_pos = (int)(uint32_t)(incl - packed), push_pos = kept_total + (int)((incl - packed) >> 32);
+            uint32_t hnext = 0xffffffffu;
+            for (int i = lo; i < hi; ++i) {
+                const uint64_t e = cur[i];
+                const unsigned flags = ((uint32_t)e) >> kPixBits;
+                if (flags) {
+                    cur[i] = ((uint64_t)(uint32_t)push_pos << 32) | (uint32_t)e;
+                    push_pos += __popc(flags & 0xfu);
+                } else {
+                    nxt[kept_pos++] = e;
                     hnext = min(hnext, (uint32_t)(e >> 32));
                 }
-                if (won) {
-                    const int32_t label = a.out[p];
-                    int pos = kept_total + push_carry + (excl >> 16);
+            }
+            __syncthreads();
+            // C: the leaving entries label and push what they won
+            for (int i = tid; i < m && i <= istar; i += kThreads) {
+                const uint64_t e = cur[i];
+                const unsigned flags = ((uint32_t)e) >> kPixBits;
+                if (!(flags & 0xfu)) continue;
+                const int p = (int)((uint32_t)e & kPixMask);
+                int pos = (int)(e >> 32);
+                const int32_t label = a.out[p];
+                int rh[4];
 #pragma unroll
-                    for (int k = 0; k < 4; ++k)
-                        if (won & (1 << k)) {
-                            const int q = p + dq[k];
-                            const uint32_t hk = height_key(a.height[q], a.negate);
-                            a.out[q] = label;
-                            nxt[pos++] = ((uint64_t)hk << 32) | (uint32_t)q;
-                            hnext = min(hnext, hk);
-                        }
-                }
-                __syncthreads();
-                kept_carry += s_tot & 0xffff;
-                push_carry += s_tot >> 16;
-                __syncthreads();
+                for (int k = 0; k < 4; ++k) rh[k] = a.height[(flags & (1u << k)) ? p + dq[k] : p];
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    if (flags & (1u << k)) {
+                        const int q = p + dq[k];
+                        const uint32_t hk = height_key(rh[k], a.negate);
+                        a.out[q] = label;
+                        nxt[pos++] = ((uint64_t)hk << 32) | (uint32_t)q;
+                        hnext = min(hnext, hk);
+                    }
             }
             hnext = __reduce_min_sync(0xffffffffu, hnext);
             if ((tid & 31) == 0) atomicMin(&s_hnext, hnext);
             __syncthreads();
-            m = kept_carry + push_carry;
+            m = kept_total + push_total;
             uint64_t* t = cur;
             cur = nxt;
             nxt = t;
             ++step;
+        }
+        if (tid == 0) {  // diagnostics next to the ticket: steps, entries walked, longest queue, most steps of one region
+            unsigned long long* stats = (unsigned long long*)(a.ticket + 2);
+            atomicAdd(&stats[0], (unsigned long long)step);
+            atomicAdd(&stats[1], sum_m);
+            atomicMax(&stats[2], max_m);
+            atomicMax(&stats[3], (unsigned long long)step);
         }
     }
 }
@@ -583,7 +612,7 @@ extern "C" int be_watershed_i32(const int32_t* height, int negate, const int32_t
     ws_seed_kernel<<<gpx, kThreads, 0, s>>>(regions, markers, height, negate, n, offset, fill, qa);
     BE_LAUNCH_CHECK();
     FloodArgs a{regions, height, n_regions, offset, n_seed, out, qa, qb, claim, ticket, cap, (int)Y, (int)X, negate};
-    ws_flood_kernel<<<BE_SM_COUNT * 8, kThreads, 0, s>>>(a);
+    ws_flood_kernel<<<BE_SM_COUNT * 4, kThreads, 0, s>>>(a);
     BE_LAUNCH_CHECK();
     return BE_OK;
 }

@@ -121,6 +121,25 @@ def test_watershed_random_heights_match_oracle(dev, seed, levels):
         assert (O.watershed(h.astype(np.float64), mk, mask, ties="heap") != want).mean() < 1e-3
 
 
+@pytest.mark.parametrize("levels", [3, 1000])
+def test_watershed_long_queues(dev, levels):
+    """One open region of 1.2e5 pixels with noise heights: the queue of waiting pixels grows to tens of thousands of
+    entries and shrinks again (many entries per thread in every pass over the queue)."""
+    K = _K()
+    rng = np.random.default_rng(levels)
+    shape = (300, 400)
+    h = rng.integers(0, levels, size=shape).astype(np.int32)
+    mask = np.ones(shape, dtype=bool)
+    mk = np.zeros(shape, dtype=np.int32)
+    for l, (y, x) in enumerate(zip(rng.integers(0, 300, 7), rng.integers(0, 400, 7)), start=1):
+        mk[y, x] = l
+    want = O.watershed(h.astype(np.float64), mk, mask, ties="fifo")
+    got = K.watershed(torch.from_numpy(h).to(dev), torch.from_numpy(mk).to(dev), torch.from_numpy(mask.astype(np.uint8)).to(dev))
+    assert np.array_equal(got.cpu().numpy(), want)
+    st = K._default_ws._buf[:64].view(torch.int64).cpu().numpy()
+    assert st[3] > 3072          # longest queue
+
+
 def test_watershed_multi_pixel_seeds_and_unreached_regions(dev):
     K = _K()
     rng = np.random.default_rng(5)
