@@ -95,6 +95,27 @@ def build_model(name: str, seed: int = 0, **kwargs) -> nn.Module:
     return model
 
 
+def build_from_source(root, source: str, callable_name: str, **kwargs) -> nn.Module:
+    """The architecture a model package ships as a python file (`architecture: {source: unet.py, callable: UNet}`; what
+    bioimageio.core imports for `ArchitectureFromFile`): import the file from the package directory, call the class."""
+    import importlib.util
+    from pathlib import Path
+
+    root = Path(root).resolve()
+    path = (root / source).resolve()
+    if root not in path.parents or not path.is_file():
+        raise FileNotFoundError(f"architecture source {source!r} is not a file inside the model package {root}")
+    spec = importlib.util.spec_from_file_location(f"_b200_model_{abs(hash(str(path)))}", path)
+    module = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(module)
+    if not hasattr(module, callable_name):
+        raise ValueError(f"{source} does not define {callable_name!r}")
+    model = getattr(module, callable_name)(**kwargs).eval()
+    for p in model.parameters():
+        p.requires_grad_(False)
+    return model
+
+
 def strict_fp32() -> None:
     """The path is specified in fp32: no TF32 inside the forward either."""
     torch.backends.cudnn.allow_tf32 = False

@@ -2,8 +2,10 @@
 
 Understands the parts of model RDF 0.5 (and the 0.4 spellings of the same things) that drive
 `predict_sample_with[out]_blocking`: input/output ids and axes, pre-/post-processing op lists,
-parameterised input sizes (`size: {min, step}`), output halo, and the `pytorch_state_dict` weights entry.  A full
-reader (SizeReference scale/offset, reference tensors, dataset statistics) is row f2 of SURVEY §8f.
+parameterised input sizes (`size: {min, step}`), output halo, packaged test tensors, and the `pytorch_state_dict` weights
+entry with its architecture — a callable of this package (`UNet2d`, `UNet3d`) or a class in a source file of the model
+package.  Output sizes follow the input's (`SizeReference` with scale 1, offset 0); other scales and dataset-mode
+statistics are not read (row f2 of SURVEY §8f).
 """
 from __future__ import annotations
 
@@ -30,6 +32,7 @@ class TensorSpec:
     size_step: Dict[str, int] = field(default_factory=dict)  # spatial axis id -> step (0 = fixed)
     halo: Dict[str, int] = field(default_factory=dict)
     n_channels: Optional[int] = None            # from `channel_names` / a fixed channel size, if declared
+    test_tensor: Optional[str] = None           # packaged example (`test_tensor.source`, or 0.4 `test_inputs/outputs`)
 
 
 @dataclass
@@ -42,6 +45,7 @@ class ModelSpec:
     arch_kwargs: Dict[str, Any]
     weights_source: Optional[str]
     seed: int = 0
+    arch_source: Optional[str] = None           # python file inside the package that defines `architecture`
 
 
 def _ops(entries) -> List[Op]:
@@ -102,6 +106,9 @@ def _tensor(entry: Dict[str, Any], is_output: bool) -> TensorSpec:
             if "halo" in ax:
                 spec.halo[l] = int(ax["halo"])
     spec.axes = "".join(letters)
+    tt = entry.get("test_tensor")
+    if isinstance(tt, dict) and tt.get("source"):
+        spec.test_tensor = str(tt["source"])
     data = entry.get("data")
     if isinstance(data, dict) and "type" in data:
         spec.dtype = str(data["type"])
@@ -119,13 +126,23 @@ def load_model_spec(rdf_path: str) -> ModelSpec:
     if not weights:
         raise ValueError("only `pytorch_state_dict` weights are supported by the B200 runtime")
     arch = weights.get("architecture") or {}
-    callable_ = arch.get("callable") if isinstance(arch, dict) else str(arch)
-    if isinstance(arch, str):
-        callable_ = arch.split(":")[-1]
+    source = None
+    if isinstance(arch, dict):      # 0.5: {callable, kwargs} with `source: file.py` (ArchitectureFromFile) or without
+        callable_ = arch.get("callable")
+        source = arch.get("source")
+    else:                           # 0.4: "file.py:ClassName" or a bare class name
+        callable_ = str(arch).split(":")[-1]
+        if ":" in str(arch):
+            source = str(arch).rsplit(":", 1)[0]
     kwargs = dict((arch.get("kwargs") if isinstance(arch, dict) else None) or weights.get("kwargs") or {})
+    inputs = [_tensor(e, False) for e in rdf["inputs"]]
+    outputs = [_tensor(e, True) for e in rdf["outputs"]]
+    for specs, key in ((inputs, "test_inputs"), (outputs, "test_outputs")):   # 0.4 keeps the examples at top level
+        for t, src in zip(specs, rdf.get(key) or []):
+            t.test_tensor = t.test_tensor or str(src)
     return ModelSpec(
-        root=path.parent, name=str(rdf.get("name", path.parent.name)),
-        inputs=[_tensor(e, False) for e in rdf["inputs"]], outputs=[_tensor(e, True) for e in rdf["outputs"]],
+        root=path.parent, name=str(rdf.get("name", path.parent.name)), inputs=inputs, outputs=outputs,
         architecture=str(callable_), arch_kwargs=kwargs, weights_source=weights.get("source"),
         seed=int((rdf.get("config") or {}).get("b200", {}).get("seed", 0)),
+        arch_source=str(source) if source else None,
     )

@@ -51,7 +51,10 @@ class _LoadedModel:
 
     def __init__(self, spec: ModelSpec, device: torch.device, blocksize_parameter: Optional[int]):
         self.spec, self.device, self.n = spec, device, blocksize_parameter
-        self.net = models.build_model(spec.architecture, seed=spec.seed, **spec.arch_kwargs)
+        if spec.arch_source:     # the package ships its own architecture file
+            self.net = models.build_from_source(spec.root, spec.arch_source, spec.architecture, **spec.arch_kwargs)
+        else:
+            self.net = models.build_model(spec.architecture, seed=spec.seed, **spec.arch_kwargs)
         if spec.weights_source:
             src = spec.root / spec.weights_source
             if not src.exists():
@@ -74,15 +77,33 @@ class RuntimeDeployment:
     # === model test ===
 
     async def test(self, rdf_path: str, additional_requirements: Optional[List[str]] = None) -> dict:
-        """Load the model and run it once on a zero sample of its minimum shape (the zoo's test tensors are not
-        available offline, ref: runtime_deployment.py:86-99)."""
+        """ref: runtime_deployment.py:86-99 (`bioimageio.core.test_model`): run the model on its packaged test inputs and
+        compare with its packaged test outputs (absolute 1.5e-4 — bioimageio's `decimal=4` — plus 1e-3 relative).  A
+        package without test tensors is run once on a zero sample of its minimum shape (status "passed" = it ran)."""
+        if additional_requirements is not None and not isinstance(additional_requirements, list):
+            raise ValueError("additional_requirements must be a list of strings.")
         spec = load_model_spec(rdf_path)
-        inp = spec.inputs[0]
-        spatial = [max(inp.size_min.get(a, 64), 16) for a in inp.axes if a in "zyx"]
-        x = np.zeros([1, spec.arch_kwargs.get("in_channels", 1)] + spatial, np.float32)
-        out = await self.predict(rdf_path, x)
-        return {"status": "passed", "name": spec.name,
-                "details": [{"name": k, "shape": list(v.shape), "dtype": str(v.dtype)} for k, v in out.items()]}
+        have_tests = all(t.test_tensor and (spec.root / t.test_tensor).exists() for t in spec.inputs + spec.outputs)
+        if not have_tests:
+            arrays = {}
+            for inp in spec.inputs:
+                spatial = [max(inp.size_min.get(a, 64), 16) for a in inp.axes if a in "zyx"]
+                arrays[inp.id] = np.zeros([1, inp.n_channels or spec.arch_kwargs.get("in_channels", 1)] + spatial, np.float32)
+            out = await self.predict(rdf_path, arrays)
+            return {"status": "passed", "name": spec.name, "tested_against": "zero sample (no packaged test tensors)",
+                    "details": [{"name": k, "shape": list(v.shape), "dtype": str(v.dtype)} for k, v in out.items()]}
+        arrays = {inp.id: np.load(spec.root / inp.test_tensor) for inp in spec.inputs}
+        out = await self.predict(rdf_path, arrays)
+        details, ok = [], True
+        for o in spec.outputs:
+            want, got = np.load(spec.root / o.test_tensor), out[o.id]
+            same_shape = tuple(want.shape) == tuple(got.shape)
+            close = same_shape and bool(np.allclose(got.astype(np.float64), want.astype(np.float64), rtol=1e-3, atol=1.5e-4))
+            ok &= close
+            details.append({"name": o.id, "shape": list(got.shape), "dtype": str(got.dtype), "status": "passed" if close else "failed",
+                            "max_abs_diff": float(np.abs(got.astype(np.float64) - want).max()) if same_shape else None})
+        return {"status": "passed" if ok else "failed", "name": spec.name, "tested_against": "packaged test tensors",
+                "details": details}
 
     # === prediction ===
 
@@ -230,27 +251,40 @@ class RuntimeDeployment:
             if not blocking and step == 0 and size != lo:
                 raise ValueError(f"input {inp.id!r}: axis {a} has size {size}, the model needs exactly {lo}")
 
-    def _predict_one(self, loaded: _LoadedModel, x_np: np.ndarray, blocking: bool) -> Dict[str, np.ndarray]:
+    def _predict_sample(self, loaded: _LoadedModel, arrays: Dict[str, np.ndarray], blocking: bool) -> Dict[str, np.ndarray]:
+        """One sample = one array per declared input tensor (ref: `create_sample_for_model`, runtime_deployment.py:270-274)
+        → `{output_id: ndarray}` for every declared output.  All inputs share the batch size and the spatial shape (they
+        are tiled with one geometry); every input has its own pre-processing, every output its own post-processing."""
         spec = loaded.spec
-        inp, outp = spec.inputs[0], spec.outputs[0]
-        x_host = self._to_ncsp(x_np, inp.axes)
-        self._validate_sample(x_host, inp, blocking)
-        x = K.to_float32(torch.from_numpy(x_host).to(loaded.device, non_blocking=True))
-        N, C = x.shape[:2]
+        inp0 = spec.inputs[0]
+        xs = []
+        for inp in spec.inputs:
+            x_host = self._to_ncsp(np.asarray(arrays[inp.id]), inp.axes)
+            if x_host.size == 0:
+                raise ValueError("empty input")
+            self._validate_sample(x_host, inp, blocking)
+            xs.append(K.to_float32(torch.from_numpy(x_host).to(loaded.device, non_blocking=True)))
+        x = xs[0]
+        N = x.shape[0]
         spatial = tuple(x.shape[2:])
-        sp_axes = [a for a in inp.axes if a in "zyx"]
+        for inp, xi in zip(spec.inputs[1:], xs[1:]):
+            if xi.shape[0] != N or tuple(xi.shape[2:]) != spatial:
+                raise ValueError(f"input {inp.id!r} has batch/spatial shape {(xi.shape[0],) + tuple(xi.shape[2:])}, "
+                                 f"input {inp0.id!r} has {(N,) + spatial}: inputs are tiled together and must agree")
+        sp_axes = [a for a in inp0.axes if a in "zyx"]
+        halos = [tuple(o.halo.get(a, 0) for a in sp_axes) for o in spec.outputs]
+        if len(set(halos)) != 1:
+            raise ValueError(f"outputs declare different halos {halos}; one block geometry serves all outputs")
         if blocking:
-            block = tuple(inp.size_min.get(a, s) + loaded.n * inp.size_step.get(a, 0) for a, s in zip(sp_axes, spatial))
-            halo = tuple(outp.halo.get(a, 0) for a in sp_axes)
+            block = tuple(inp0.size_min.get(a, s) + loaded.n * inp0.size_step.get(a, 0) for a, s in zip(sp_axes, spatial))
+            halo = halos[0]
             if any(s < b - 2 * h for s, b, h in zip(spatial, block, halo)):
                 raise ValueError(f"sample {spatial} is smaller than the block {block} minus halo")
         else:
             block, halo = spatial, (0,) * len(spatial)
 
-        pre = [o for o in inp.ops if o.name != "ensure_dtype"]
-        post = [o for o in outp.ops if o.name != "ensure_dtype"]
-        ref_norms = self._reference_norms(pre + post, {str(inp.id): x})   # before x is normalised in place
-        fused_norm = len(pre) == 1 and pre[0].name in _NORMALISERS
+        all_ops = [o for t in spec.inputs + spec.outputs for o in t.ops]
+        ref_norms = self._reference_norms(all_ops, {str(i.id): xi for i, xi in zip(spec.inputs, xs)})  # before normalising
         key = (tuple(x.shape), block, halo)
         pipe = loaded.pipelines.get(key)
         if pipe is None:
@@ -258,13 +292,50 @@ class RuntimeDeployment:
                                                               preprocess="none", label=False), device=loaded.device)
             loaded.pipelines[key] = pipe
         # whole-sample pre-processing first (statistics are per sample, never per block), fused into the gather
-        if fused_norm:
-            norm, mode = self._norm_params(x, pre[0], N, C)
-            tiles = K.tile_gather(x, pipe.axes, norm=norm, norm_mode=mode, out=pipe.tiles)
+        tiles = []
+        for j, (inp, xi) in enumerate(zip(spec.inputs, xs)):
+            pre = [o for o in inp.ops if o.name != "ensure_dtype"]
+            out_buf = pipe.tiles if j == 0 and xi.shape[1] == x.shape[1] else None
+            if len(pre) == 1 and pre[0].name in _NORMALISERS:
+                norm, mode = self._norm_params(xi, pre[0], N, xi.shape[1])
+                tiles.append(K.tile_gather(xi, pipe.axes, norm=norm, norm_mode=mode, out=out_buf))
+            else:
+                tiles.append(K.tile_gather(self._run_ops_unfused(xi, pre, N, xi.shape[1], ref_norms), pipe.axes, out=out_buf))
+        if len(tiles) == 1:
+            raw = pipe.forward(loaded.net, tiles[0])
         else:
-            tiles = K.tile_gather(self._run_ops_unfused(x, pre, N, C, ref_norms), pipe.axes, out=pipe.tiles)
-        logits = pipe.forward(loaded.net, tiles)
-        out_shape = (N, logits.shape[1]) + spatial
+            fb = max(1, int(pipe.spec.forward_batch))
+            raw = self._gather_outputs([loaded.net(*[t[i:i + fb] for t in tiles]) for i in range(0, tiles[0].shape[0], fb)])
+        logits_by_output = self._outputs_in_order(raw, spec)
+        return {str(o.id): self._finish_output(pipe, lg.contiguous(), o, N, spatial, ref_norms)
+                for o, lg in zip(spec.outputs, logits_by_output)}
+
+    @staticmethod
+    def _gather_outputs(chunks):
+        """Per-chunk network results (tensor, tuple / list or dict of tensors) → the same structure over all tiles."""
+        first = chunks[0]
+        if isinstance(first, torch.Tensor):
+            return torch.cat(chunks)
+        if isinstance(first, dict):
+            return {k: torch.cat([c[k] for c in chunks]) for k in first}
+        return [torch.cat([c[j] for c in chunks]) for j in range(len(first))]
+
+    @staticmethod
+    def _outputs_in_order(raw, spec: ModelSpec) -> List[torch.Tensor]:
+        if isinstance(raw, torch.Tensor):
+            raw = [raw]
+        if isinstance(raw, dict):
+            missing = [o.id for o in spec.outputs if o.id not in raw]
+            if missing:
+                raise ValueError(f"the network returned no tensor named {missing}")
+            raw = [raw[o.id] for o in spec.outputs]
+        if len(raw) != len(spec.outputs):
+            raise ValueError(f"the network returned {len(raw)} tensor(s), the model declares {len(spec.outputs)} output(s)")
+        return list(raw)
+
+    def _finish_output(self, pipe: TiledPipeline, logits: torch.Tensor, outp, N: int, spatial, ref_norms) -> np.ndarray:
+        post = [o for o in outp.ops if o.name != "ensure_dtype"]
+        out_shape = (N, logits.shape[1]) + tuple(spatial)
         names = [o.name for o in post]
         if names in (["sigmoid"], ["binarize"], ["sigmoid", "binarize"], []):
             epi = _lib.BE_EPI_SIGMOID if "sigmoid" in names else _lib.BE_EPI_NONE
@@ -289,7 +360,26 @@ class RuntimeDeployment:
         have = [a for a in "bc" if a in outp.axes] + [a for a in "zyx" if a in outp.axes]
         if "".join(have) != outp.axes and len(have) == arr.ndim:
             arr = np.transpose(arr, [have.index(a) for a in outp.axes])
-        return {str(outp.id): arr}
+        return arr
+
+    @staticmethod
+    def _sample_arrays(inputs, spec: ModelSpec) -> Dict[str, np.ndarray]:
+        """`create_sample_for_model`'s input handling: one array for a one-input model, else `{input_id: array}` naming
+        every declared input and nothing else."""
+        ids = [i.id for i in spec.inputs]
+        if not isinstance(inputs, dict):
+            if len(ids) != 1:
+                raise ValueError(f"the model declares {len(ids)} input tensors {ids}; pass a dict with one array each")
+            return {ids[0]: inputs}
+        if len(ids) == 1 and len(inputs) == 1 and ids[0] not in inputs:
+            return {ids[0]: next(iter(inputs.values()))}   # a single unnamed-by-id array for a single input
+        unknown = [k for k in inputs if k not in ids]
+        missing = [k for k in ids if k not in inputs]
+        if missing:
+            raise ValueError(f"inputs must contain tensor(s) {missing}")
+        if unknown:
+            raise ValueError(f"unknown input tensor(s) {unknown}; the model declares {ids}")
+        return {k: inputs[k] for k in ids}
 
     async def predict(
         self,
@@ -309,23 +399,11 @@ class RuntimeDeployment:
                                                     default_blocksize_parameter=default_blocksize_parameter,
                                                     latest_remote_modified=latest_remote_modified)
             loaded = await self._create_prediction_pipeline(cache_key)
-            if len(loaded.spec.inputs) != 1:
-                raise ValueError(f"model declares {len(loaded.spec.inputs)} input tensors; the in-package architectures take one")
-            if isinstance(inputs, dict):
-                want = loaded.spec.inputs[0].id
-                unknown = [k for k in inputs if k != want]
-                if want not in inputs and len(inputs) != 1:
-                    raise ValueError(f"inputs must contain tensor {want!r}")
-                if want in inputs and unknown:
-                    raise ValueError(f"unknown input tensor(s) {unknown}; the model declares only {want!r}")
-                x = inputs[want] if want in inputs else next(iter(inputs.values()))
-            else:
-                x = inputs
-            x = np.asarray(x)
-            if x.size == 0:
+            arrays = self._sample_arrays(inputs, loaded.spec)
+            if any(np.asarray(v).size == 0 for v in arrays.values()):
                 raise ValueError("empty input")
             logger.info(f"Running inference for sample '{sample_id}'")
-            return self._predict_one(loaded, x, blocking=bool(default_blocksize_parameter))
+            return self._predict_sample(loaded, arrays, blocking=bool(default_blocksize_parameter))
         except Exception as e:
             torch.cuda.empty_cache()
             err_type = type(e).__name__

@@ -15,7 +15,9 @@ PARITY, row by row:
     installable here (bioimageio.core==0.10.0, xarray==2025.1.2, scikit-image, cellpose==4.0.7; pins at
     apps/model-runner/runtime_deployment.py:16-28 and apps/cellpose-finetuning/main.py:3608): scale_range /
     zero_mean_unit_variance / pointwise ops (a6-a9), halo blocking and reassembly (a5), labelling numbering (a13),
-    regionprops (a14), average_precision (a15).  No reference test holds a numeric known answer for them (§8c).  They
+    regionprops (a14), average_precision (a15), and the skimage half of the fibsem post-processing (f3: peak_local_max,
+    watershed — restated here and in oracle/watershed.c from skimage's published algorithm, including both orders in
+    which seeds of equal height may leave its heap).  No reference test holds a numeric known answer for them (§8c).  They
     call the same numpy/scipy routines those packages call, follow their published behaviour, and
     are held to hand-derived known answers in tests/test_oracle_golden.py (6x6 masks, quantile lerp, shifted last block,
     reflect padding, IoU = 0.5 ties, rectangle moments) plus seeded vectors in tests/golden/ (make_golden.py).

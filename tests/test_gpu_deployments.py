@@ -290,3 +290,141 @@ def test_predict_validates_the_sample_against_the_rdf(tmp_path, dev):
         asyncio.run(rt.predict(rdf_path, {"raw": ok, "extra": ok}))
     # with blocking any size at least as large as the inner block goes
     assert asyncio.run(rt.predict(rdf_path, np.zeros((1, 1, 100, 131), np.float32), default_blocksize_parameter=1))["mask"].shape == (1, 1, 100, 131)
+
+
+_TWO_IN_TWO_OUT = '''
+import torch
+import torch.nn as nn
+
+
+class TwoHeads(nn.Module):
+    """Two input tensors (1 and 2 channels), two outputs (a logit map and a 3-channel feature map); receptive field 5."""
+
+    def __init__(self, width=6):
+        super().__init__()
+        self.a = nn.Conv2d(1, width, 3, padding=1)
+        self.b = nn.Conv2d(2, width, 3, padding=1)
+        self.mix = nn.Conv2d(2 * width, width, 3, padding=1)
+        self.logit = nn.Conv2d(width, 1, 1)
+        self.feat = nn.Conv2d(width, 3, 1)
+
+    def forward(self, raw, aux):
+        h = torch.relu(self.mix(torch.cat([torch.relu(self.a(raw)), torch.relu(self.b(aux))], dim=1)))
+        return self.logit(h) * 40.0, self.feat(h)
+'''
+
+
+def write_two_input_package(root, with_tests_from=None):
+    """A model package that ships its own architecture file, two inputs with different pre-processing, two outputs with
+    different post-processing and (optionally) test tensors."""
+    import importlib.util
+
+    (root / "net.py").write_text(_TWO_IN_TWO_OUT)
+    spec = importlib.util.spec_from_file_location("two_heads_for_test", root / "net.py")
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    torch.manual_seed(11)
+    net = mod.TwoHeads(width=6).eval()
+    with torch.no_grad():    # centre the logit head on a probe so the mask is neither empty nor full
+        g = torch.Generator().manual_seed(12)
+        probe = net(torch.randn((1, 1, 64, 64), generator=g), torch.rand((1, 2, 64, 64), generator=g) * 1.5 - 0.75)[0]
+        net.logit.bias.sub_(probe.median() / 40.0)
+    torch.save(net.state_dict(), root / "weights.pt")
+    sp = lambda halo=None: [{"type": "space", "id": a, **({"halo": halo} if halo is not None else {"size": {"min": 32, "step": 16}})} for a in "yx"]
+    rdf = {
+        "format_version": "0.5.3", "type": "model", "name": "two-heads",
+        "inputs": [
+            {"id": "raw", "axes": [{"type": "batch"}, {"type": "channel", "channel_names": ["em"]}] + sp(),
+             "preprocessing": [{"id": "zero_mean_unit_variance", "kwargs": {"axes": ["y", "x"]}}]},
+            {"id": "aux", "axes": [{"type": "batch"}, {"type": "channel", "channel_names": ["u", "v"]}] + sp(),
+             "preprocessing": [{"id": "scale_linear", "kwargs": {"gain": 0.5, "offset": -1.0}},
+                               {"id": "clip", "kwargs": {"min": -0.75, "max": 0.75}}]},
+        ],
+        "outputs": [
+            {"id": "mask", "data": {"type": "uint8"},
+             "axes": [{"type": "batch"}, {"type": "channel", "channel_names": ["fg"]}] + sp(8),
+             "postprocessing": [{"id": "sigmoid"}, {"id": "binarize", "kwargs": {"threshold": 0.5}}]},
+            {"id": "features", "data": {"type": "float32"},
+             "axes": [{"type": "batch"}, {"type": "channel", "channel_names": ["f0", "f1", "f2"]}] + sp(8),
+             "postprocessing": [{"id": "scale_linear", "kwargs": {"gain": 2.0, "offset": 0.25}}]},
+        ],
+        "weights": {"pytorch_state_dict": {"source": "weights.pt",
+                                           "architecture": {"source": "net.py", "callable": "TwoHeads", "kwargs": {"width": 6}}}},
+    }
+    if with_tests_from is not None:
+        for t, arr in zip(rdf["inputs"] + rdf["outputs"], with_tests_from):
+            np.save(root / f"test_{t['id']}.npy", arr)
+            t["test_tensor"] = {"source": f"test_{t['id']}.npy"}
+    (root / "rdf.yaml").write_text(yaml.safe_dump(rdf))
+    return str(root / "rdf.yaml"), net
+
+
+def _two_heads_oracle(net, raw, aux, dev, block=None, halo=None):
+    """The reference order on the CPU: whole-sample pre-processing per input → (halo blocks) → network → (inner-region
+    reassembly) → post-processing per output."""
+    a = O.zero_mean_unit_variance(raw, axes=(2, 3))
+    b = O.clip(O.scale_linear(aux, 0.5, -1.0), -0.75, 0.75)
+    if block is not None:
+        a, b = O.blocks_tensor(a, block, halo), O.blocks_tensor(b, block, halo)
+    with torch.no_grad():
+        lg, ft = net.to(dev)(torch.from_numpy(a).to(dev), torch.from_numpy(b).to(dev))
+    lg, ft = lg.cpu().numpy(), ft.cpu().numpy()
+    if block is not None:
+        lg = O.from_blocks(lg, (raw.shape[0], 1) + raw.shape[2:], block, halo)
+        ft = O.from_blocks(ft, (raw.shape[0], 3) + raw.shape[2:], block, halo)
+    return O.binarize(O.sigmoid(lg), 0.5), O.scale_linear(ft, 2.0, 0.25)
+
+
+def test_predict_two_inputs_two_outputs_with_the_packages_own_architecture(tmp_path, dev):
+    from bioengine_worker_b200 import models
+    from bioengine_worker_b200.runtime_deployment import RuntimeDeployment
+
+    models.strict_fp32()
+    rng = np.random.default_rng(4)
+    raw = (O.gaussian_blobs((144, 176), 25, seed=4)[None, None] * 90 + 10 + rng.standard_normal((1, 1, 144, 176))).astype(np.float32)
+    aux = rng.uniform(-1, 4, size=(1, 2, 144, 176)).astype(np.float32)
+    rdf_path, net = write_two_input_package(tmp_path)
+    rt = RuntimeDeployment.func_or_class()
+    # whole sample (144 = 32 + 7*16, 176 = 32 + 9*16)
+    out = asyncio.run(rt.predict(rdf_path, {"raw": raw, "aux": aux}))
+    mask, feat = _two_heads_oracle(net, raw, aux, dev)
+    assert list(out) == ["mask", "features"] and out["mask"].dtype == np.uint8 and out["features"].shape == (1, 3, 144, 176)
+    assert 0.05 < mask.mean() < 0.95
+    assert np.array_equal(out["mask"], mask)
+    np.testing.assert_allclose(out["features"], feat, rtol=1e-5, atol=1e-6)
+    # blocks of 32 + 2*16 = 64 with the outputs' 8-px halo: the network's receptive field (5) fits inside the halo
+    outb = asyncio.run(rt.predict(rdf_path, {"aux": aux, "raw": raw}, default_blocksize_parameter=2))
+    maskb, featb = _two_heads_oracle(net, raw, aux, dev, (64, 64), (8, 8))
+    assert np.array_equal(outb["mask"], maskb)
+    np.testing.assert_allclose(outb["features"], featb, rtol=1e-5, atol=1e-6)
+    # what create_sample_for_model rejects
+    for bad in (raw, {"raw": raw}, {"raw": raw, "aux": aux, "more": aux}, {"raw": raw, "aux": aux[:, :, :128]},
+                {"raw": raw, "aux": aux[:, :1]}):
+        with pytest.raises(ValueError):
+            asyncio.run(rt.predict(rdf_path, bad))
+
+
+def test_model_test_uses_the_packaged_test_tensors(tmp_path, dev):
+    """`RuntimeDeployment.test` = bioimageio.core.test_model: run the packaged test inputs, compare with the packaged test
+    outputs; a package whose outputs do not reproduce fails."""
+    from bioengine_worker_b200 import models
+    from bioengine_worker_b200.runtime_deployment import RuntimeDeployment
+
+    models.strict_fp32()
+    rng = np.random.default_rng(5)
+    raw = rng.normal(50, 20, size=(1, 1, 64, 80)).astype(np.float32)
+    aux = rng.uniform(-1, 4, size=(1, 2, 64, 80)).astype(np.float32)
+    good, bad = tmp_path / "good", tmp_path / "bad"
+    good.mkdir(), bad.mkdir()
+    _, net = write_two_input_package(good)
+    mask, feat = _two_heads_oracle(net, raw, aux, dev)
+    rdf_good, _ = write_two_input_package(good, with_tests_from=(raw, aux, mask, feat))
+    rdf_bad, _ = write_two_input_package(bad, with_tests_from=(raw, aux, mask, feat + 0.01))
+    rt = RuntimeDeployment.func_or_class()
+    rep = asyncio.run(rt.test(rdf_good))
+    assert rep["status"] == "passed" and rep["tested_against"] == "packaged test tensors"
+    assert [d["status"] for d in rep["details"]] == ["passed", "passed"]
+    rep = asyncio.run(rt.test(rdf_bad))
+    assert rep["status"] == "failed" and [d["status"] for d in rep["details"]] == ["passed", "failed"]
+    with pytest.raises(ValueError):
+        asyncio.run(rt.test(rdf_good, additional_requirements="numpy"))
