@@ -335,3 +335,22 @@ def test_pipeline_takes_uint16_frames(dev):
     pipe.run_stream(frames, fwd, host_l, host_n).synchronize()
     for l in host_l:
         assert np.array_equal(l.numpy(), a["labels"].cpu().numpy())
+
+
+def test_quantile_of_a_volume_sized_segment(dev):
+    """2^26 + 12345 elements in one segment (the 8192-element sample path; C3's 512^3 volume is twice this): exact order
+    statistics against numpy, with hot voxels and a constant stretch in the data."""
+    from bioengine_worker_b200 import kernels as K
+
+    rng = np.random.default_rng(26)
+    n = (1 << 26) + 12345
+    x = rng.normal(120.0, 40.0, size=n).astype(np.float32)
+    x[rng.integers(0, n, 50000)] = 65535.0
+    x[1000:200000] = 77.0
+    q = np.array([0.01, 0.5, 0.99, 0.998])
+    want = np.quantile(x.astype(np.float64), q)
+    xt = torch.from_numpy(x).to(dev)
+    for qa in (q[[0, 2]], q[[1, 3]]):
+        got, _ = K.quantile(xt, 1, torch.tensor(qa, dtype=torch.float64, device=dev), 1e-6)
+        assert np.array_equal(got.cpu().numpy()[0], np.quantile(x.astype(np.float64), qa))
+    assert want[3] > want[2] > want[1] > want[0]
