@@ -715,6 +715,138 @@ __global__ void __launch_bounds__(kSampleThreads) qsel_sample_kernel(const float
 }
 
 // the single streaming pass: classify every element against the (<= 2) brackets of its segment
+// The pivots of a segment without a sort: the block reads the 2048 sample positions and picks the 2 NQ wanted order
+// statistics with an 8-bit radix select — rounds of {shared-memory histogram per wanted rank, one warp per rank walks its
+// 256 bins} — instead of the 66 compare-exchange stages of a bitonic sort (sample kernel 12.9 -> ~8 us).  (Doing this in
+// every block of the partition pass, to save the launch, was no faster: 592 blocks fetching the same 2048 sectors.)
+// Digits are cut from (key - lowest sample key), starting at the top bit of the sample's key range: an image's values
+// share their leading exponent bits, and digits taken from the raw key would send the whole sample to one or two bins
+// (2048 atomics on one shared-memory word).  Same sample positions and ranks as qsel_sample_kernel, hence the same
+// pivots as its sorted array gives.
+template <int NQ, int kThreads>
+__device__ __forceinline__ void qsel_own_pivots(const float* __restrict__ xs, int64_t seg_len, int64_t seg,
+                                                const double* __restrict__ q, float* flo, float* fhi) {
+    constexpr int kSel = 2 * NQ, kPer = kSample / kThreads;
+    __shared__ unsigned s_hist[kSel][256];
+    __shared__ unsigned s_pref[kSel];
+    __shared__ int s_rank[kSel];
+    __shared__ unsigned s_valid, s_min, s_nmax;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) {
+        s_valid = 0;
+        s_min = 0xffffffffu;
+        s_nmax = 0xffffffffu;
+    }
+    __syncthreads();
+    const uint32_t stride = (uint32_t)(seg_len / kSample);
+    uint32_t key[kPer];
+    unsigned okmask = 0, kmin = 0xffffffffu, nkmax = 0xffffffffu;
+#pragma unroll
+    for (int j = 0; j < kPer; ++j) {
+        const int i = tid + j * kThreads;
+        const int64_t pos = (int64_t)i * stride + hash32((uint32_t)i * 0x9e3779b9u + (uint32_t)seg) % stride;
+        const float v = __ldg(xs + pos);
+        key[j] = f32_to_key(v);
+        if (v == v) {   // NaNs rank last and are never wanted: they stay out of the histograms
+            okmask |= 1u << j;
+            kmin = min(kmin, key[j]);
+            nkmax = min(nkmax, ~key[j]);
+        }
+    }
+    const unsigned valid = __reduce_add_sync(0xffffffffu, (unsigned)__popc(okmask));
+    kmin = __reduce_min_sync(0xffffffffu, kmin);
+    nkmax = __reduce_min_sync(0xffffffffu, nkmax);
+    if (lane == 0) {
+        atomicAdd(&s_valid, valid);
+        atomicMin(&s_min, kmin);
+        atomicMin(&s_nmax, nkmax);
+    }
+    __syncthreads();
+    const int mv = (int)s_valid;
+    const unsigned base = s_min, range = mv > 0 ? ~s_nmax - s_min : 0u;
+    if (tid < kSel) {
+        const int i = tid >> 1, side = tid & 1;
+        int rank = -1;
+        if (mv > 0) {
+            const double qi = fmin(fmax(q[i], 0.0), 1.0);
+            const double sp = qi * (double)(mv - 1);
+            const int d = (int)(4.0 * sqrt((double)mv * qi * (1.0 - qi))) + 4;   // misses about once in 1e5 calls
+            const int lo = (int)floor(sp) - d, hi = (int)ceil(sp) + 1 + d;
+            if (side == 0 && lo >= 0) rank = lo;
+            if (side == 1 && hi < mv) rank = hi;
+        }
+        s_rank[tid] = rank;
+        s_pref[tid] = 0;
+    }
+#pragma unroll
+    for (int j = 0; j < kPer; ++j) key[j] -= base;
+    const int bits = 32 - __clz(range | 1u);
+    int prev = 32;   // bits [prev, 32) of (key - base) are settled
+    for (int shift = max(bits - 8, 0);; shift = max(shift - 8, 0)) {
+        for (int b = tid; b < kSel * 256; b += kThreads) (&s_hist[0][0])[b] = 0;
+        __syncthreads();
+#pragma unroll
+        for (int sel = 0; sel < kSel; ++sel) {
+            if (s_rank[sel] < 0) continue;
+            const unsigned pref = s_pref[sel];
+#pragma unroll
+            for (int j = 0; j < kPer; ++j)
+                if (((okmask >> j) & 1u) && (prev >= 32 || (key[j] >> prev) == (pref >> prev)))
+                    atomicAdd(&s_hist[sel][(key[j] >> shift) & 255u], 1u);
+        }
+        __syncthreads();
+        if (warp < kSel && s_rank[warp] >= 0) {
+            unsigned c[8], tot = 0;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                c[j] = s_hist[warp][lane * 8 + j];
+                tot += c[j];
+            }
+            unsigned incl = tot;
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned t = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += t;
+            }
+            unsigned cum = incl - tot;
+            const unsigned r = (unsigned)s_rank[warp];
+            if (r >= cum && r < cum + tot) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    if (r < cum + c[j]) {
+                        s_pref[warp] |= (unsigned)(lane * 8 + j) << shift;   // bits shared with the last digit agree
+                        s_rank[warp] = (int)(r - cum);
+                        break;
+                    }
+                    cum += c[j];
+                }
+            }
+        }
+        __syncthreads();
+        prev = shift;
+        if (shift == 0) break;
+    }
+#pragma unroll
+    for (int i = 0; i < NQ; ++i) {
+        flo[i] = s_rank[2 * i] >= 0 ? key_to_f32(s_pref[2 * i] + base) : __int_as_float(0xff800000);
+        fhi[i] = s_rank[2 * i + 1] >= 0 ? key_to_f32(s_pref[2 * i + 1] + base) : __int_as_float(0x7f800000);
+    }
+}
+
+// one block per segment: the pivots of its NQ quantiles into the task records
+template <int NQ>
+__global__ void __launch_bounds__(kSampleThreads) qsel_pivot_kernel(const float* __restrict__ x, int64_t seg_len,
+                                                                    const double* __restrict__ q, SWorkspace w) {
+    be_pdl_launch_dependents();   // the partition pass may be placed now; it waits for the pivots
+    const int64_t seg = blockIdx.x;
+    float flo[NQ], fhi[NQ];
+    qsel_own_pivots<NQ, kSampleThreads>(x + seg * seg_len, seg_len, seg, q, flo, fhi);
+    if ((int)threadIdx.x < NQ) {
+        QTask* t = &w.tasks[seg * NQ + threadIdx.x];
+        t->flo = flo[threadIdx.x];
+        t->fhi = fhi[threadIdx.x];
+    }
+}
+
 template <int NQ>
 __global__ void __launch_bounds__(kThreads, 4) qsel_partition_kernel(const float* __restrict__ x, int64_t seg_len, int bps,
                                                                   int64_t chunk, const double* __restrict__ q,
@@ -725,7 +857,7 @@ __global__ void __launch_bounds__(kThreads, 4) qsel_partition_kernel(const float
     const float* xs = x + seg * seg_len;
     QTask* tasks = w.tasks + seg * NQ;
     float flo[NQ], fhi[NQ];
-    be_pdl_wait();   // the sample kernel's pivots
+    be_pdl_wait();   // the pivots
 #pragma unroll
     for (int i = 0; i < NQ; ++i) {
         flo[i] = tasks[i].flo;
@@ -1476,14 +1608,23 @@ static int quantile_sampled(const float* x, int64_t n_seg, int64_t seg_len, cons
         double* qs = quant + s0 * n_q;
         double* nr = norm ? norm + s0 * 2 : nullptr;
         BE_CUDA(cudaMemsetAsync(ws, 0, w.zero_bytes, s));
-        if (seg_len >= kSampleLargeLen) qsel_sample_kernel<kSampleLarge><<<(unsigned)ns, kSampleThreads, 0, s>>>(xs, seg_len, q, n_q, w);
-        else qsel_sample_kernel<kSample><<<(unsigned)ns, kSampleThreads, 0, s>>>(xs, seg_len, q, n_q, w);
-        BE_LAUNCH_CHECK();
         const dim3 grid(sp.bps, (unsigned)ns);
-        if (n_q == 1)
+        if (seg_len >= kSampleLargeLen) {   // volumes: an 8192-element sample, sorted by a kernel of its own
+            qsel_sample_kernel<kSampleLarge><<<(unsigned)ns, kSampleThreads, 0, s>>>(xs, seg_len, q, n_q, w);
+            BE_LAUNCH_CHECK();
+            if (n_q == 1)
+                BE_CUDA(be_launch_pdl(qsel_partition_kernel<1>, grid, dim3(kThreads), 0, s, xs, seg_len, sp.bps, sp.chunk, q, w, ns));
+            else
+                BE_CUDA(be_launch_pdl(qsel_partition_kernel<2>, grid, dim3(kThreads), 0, s, xs, seg_len, sp.bps, sp.chunk, q, w, ns));
+        } else if (n_q == 1) {              // images: pivots by a radix select on the 2048-element sample
+            qsel_pivot_kernel<1><<<(unsigned)ns, kSampleThreads, 0, s>>>(xs, seg_len, q, w);
+            BE_LAUNCH_CHECK();
             BE_CUDA(be_launch_pdl(qsel_partition_kernel<1>, grid, dim3(kThreads), 0, s, xs, seg_len, sp.bps, sp.chunk, q, w, ns));
-        else
+        } else {
+            qsel_pivot_kernel<2><<<(unsigned)ns, kSampleThreads, 0, s>>>(xs, seg_len, q, w);
+            BE_LAUNCH_CHECK();
             BE_CUDA(be_launch_pdl(qsel_partition_kernel<2>, grid, dim3(kThreads), 0, s, xs, seg_len, sp.bps, sp.chunk, q, w, ns));
+        }
         {
             const int n_cta = select_cluster_size();
             BE_REQUIRE(n_cta > 0, BE_ERR_CUDA, "be_quantile_f32: the device cannot run a thread-block cluster of 8");
