@@ -46,6 +46,8 @@ struct Geom {
     int ty_log2;  // TY = 1 << ty_log2 (6 in 2-D, 3 in 3-D); TZ = kRows >> ty_log2
     int tiles_x, tiles_y, tiles_z;
     int conn;
+    unsigned* scan_zero;   // tickets + look-back states of the numbering: cleared by the tile kernel's blocks, a slice each
+    int scan_words;
 };
 
 struct TileEdges {
@@ -152,7 +154,13 @@ __global__ void __launch_bounds__(kThreads, 8) ccl_tile_kernel(const void* __res
     int32_t* Li = L + (int64_t)img * vol;
     __shared__ u64 rroot[kRows];
     if (threadIdx.x < kRows) rroot[threadIdx.x] = 0;
-    be_pdl_wait();   // the kernel that wrote the mask
+    be_pdl_wait();   // the kernel that wrote the mask (and, before it, the last user of the numbering's scan states)
+    {
+        const int n_blocks = gridDim.x * gridDim.y * gridDim.z;
+        const int lin = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+        const int per = (g.scan_words + n_blocks - 1) / n_blocks;
+        for (int i = lin * per + threadIdx.x; i < min((lin + 1) * per, g.scan_words); i += kThreads) g.scan_zero[i] = 0u;
+    }
 
     // ---- A: rows -> bit masks ----
     if (IN == kInBits) {
@@ -797,21 +805,21 @@ static int ccl_run(const char* who, int in_kind, const void* input, Epilogue epi
     cudaStream_t s = (cudaStream_t)stream;
     const CclWorkspace w = carve_ccl_ws(ws, N, Z, Y, X);
 
-    BE_CUDA(cudaMemsetAsync(w.tickets, 0, w.scan_bytes, s));
+    g.scan_zero = w.tickets;
+    g.scan_words = (int)(w.scan_bytes / sizeof(unsigned));
     BE_REQUIRE(g.tiles_y <= 65535 && (int64_t)g.tiles_z * N <= 65535, BE_ERR_TOO_LARGE,
                "%s: tile grid (%d, %d, %lld) exceeds the launch limits", who, g.tiles_x, g.tiles_y, (long long)g.tiles_z * N);
     const dim3 grid((unsigned)g.tiles_x, (unsigned)g.tiles_y, (unsigned)(g.tiles_z * N));
     TileEdges* edges = ndim == 2 ? w.edges : nullptr;
     // a bit-packed input whose rows are whole words is used in place of the workspace copy of the mask
     const u64* bitvol = (in_kind == kInBits && (X % kTX) == 0) ? (const u64*)input : w.bitvol;
-    // (the memset above sits between this launch and the previous kernel, so this one starts a new chain)
+    // no memset in this call: the tile kernel is chained to whatever ran before it like the kernels after it
     if (in_kind == kInBits)
-        ccl_tile_kernel<kInBits><<<grid, kThreads, 0, s>>>(input, epi, w.L, w.rootbits, w.bitvol, edges, g);
+        BE_CUDA(be_launch_pdl(ccl_tile_kernel<kInBits>, grid, dim3(kThreads), 0, s, input, epi, w.L, w.rootbits, w.bitvol, edges, g));
     else if (in_kind == kInF32)
-        ccl_tile_kernel<kInF32><<<grid, kThreads, 0, s>>>(input, epi, w.L, w.rootbits, w.bitvol, edges, g);
+        BE_CUDA(be_launch_pdl(ccl_tile_kernel<kInF32>, grid, dim3(kThreads), 0, s, input, epi, w.L, w.rootbits, w.bitvol, edges, g));
     else
-        ccl_tile_kernel<kInU8><<<grid, kThreads, 0, s>>>(input, epi, w.L, w.rootbits, w.bitvol, edges, g);
-    BE_LAUNCH_CHECK();
+        BE_CUDA(be_launch_pdl(ccl_tile_kernel<kInU8>, grid, dim3(kThreads), 0, s, input, epi, w.L, w.rootbits, w.bitvol, edges, g));
     // the following kernels are chained to their predecessor with programmatic stream serialization (see pdl_wait)
     cudaLaunchAttribute pdl[1];
     pdl[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;

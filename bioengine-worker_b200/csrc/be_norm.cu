@@ -836,8 +836,16 @@ __device__ __forceinline__ void qsel_own_pivots(const float* __restrict__ xs, in
 template <int NQ>
 __global__ void __launch_bounds__(kSampleThreads) qsel_pivot_kernel(const float* __restrict__ x, int64_t seg_len,
                                                                     const double* __restrict__ q, SWorkspace w) {
+    be_pdl_wait();                // whatever wrote x, and the last reader of the task records
     be_pdl_launch_dependents();   // the partition pass may be placed now; it waits for the pivots
     const int64_t seg = blockIdx.x;
+    // this segment's counters and task records start from zero (no memset between this kernel and the one before it)
+    if (threadIdx.x == 0) w.counters[seg] = w.nan_count[seg] = w.seg_done[seg] = 0u;
+    {
+        uint32_t* t32 = reinterpret_cast<uint32_t*>(w.tasks + seg * NQ);
+        for (int i = threadIdx.x; i < (int)(NQ * sizeof(QTask) / sizeof(uint32_t)); i += kSampleThreads) t32[i] = 0u;
+    }
+    __syncthreads();
     float flo[NQ], fhi[NQ];
     qsel_own_pivots<NQ, kSampleThreads>(x + seg * seg_len, seg_len, seg, q, flo, fhi);
     if ((int)threadIdx.x < NQ) {
@@ -1607,9 +1615,9 @@ static int quantile_sampled(const float* x, int64_t n_seg, int64_t seg_len, cons
         const float* xs = x + s0 * seg_len;
         double* qs = quant + s0 * n_q;
         double* nr = norm ? norm + s0 * 2 : nullptr;
-        BE_CUDA(cudaMemsetAsync(ws, 0, w.zero_bytes, s));
         const dim3 grid(sp.bps, (unsigned)ns);
         if (seg_len >= kSampleLargeLen) {   // volumes: an 8192-element sample, sorted by a kernel of its own
+            BE_CUDA(cudaMemsetAsync(ws, 0, w.zero_bytes, s));
             qsel_sample_kernel<kSampleLarge><<<(unsigned)ns, kSampleThreads, 0, s>>>(xs, seg_len, q, n_q, w);
             BE_LAUNCH_CHECK();
             if (n_q == 1)
@@ -1617,12 +1625,10 @@ static int quantile_sampled(const float* x, int64_t n_seg, int64_t seg_len, cons
             else
                 BE_CUDA(be_launch_pdl(qsel_partition_kernel<2>, grid, dim3(kThreads), 0, s, xs, seg_len, sp.bps, sp.chunk, q, w, ns));
         } else if (n_q == 1) {              // images: pivots by a radix select on the 2048-element sample
-            qsel_pivot_kernel<1><<<(unsigned)ns, kSampleThreads, 0, s>>>(xs, seg_len, q, w);
-            BE_LAUNCH_CHECK();
+            BE_CUDA(be_launch_pdl(qsel_pivot_kernel<1>, dim3((unsigned)ns), dim3(kSampleThreads), 0, s, xs, seg_len, q, w));
             BE_CUDA(be_launch_pdl(qsel_partition_kernel<1>, grid, dim3(kThreads), 0, s, xs, seg_len, sp.bps, sp.chunk, q, w, ns));
         } else {
-            qsel_pivot_kernel<2><<<(unsigned)ns, kSampleThreads, 0, s>>>(xs, seg_len, q, w);
-            BE_LAUNCH_CHECK();
+            BE_CUDA(be_launch_pdl(qsel_pivot_kernel<2>, dim3((unsigned)ns), dim3(kSampleThreads), 0, s, xs, seg_len, q, w));
             BE_CUDA(be_launch_pdl(qsel_partition_kernel<2>, grid, dim3(kThreads), 0, s, xs, seg_len, sp.bps, sp.chunk, q, w, ns));
         }
         {
