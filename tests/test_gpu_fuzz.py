@@ -100,3 +100,53 @@ def test_fuzz_quantiles(case, dev):
         warnings.simplefilter("ignore")
         want = np.nanquantile(x, q, axis=1, method="linear").T
     assert np.array_equal(got.cpu().numpy(), want, equal_nan=True), (case, n_seg, seg_len, kind, q)
+
+
+@pytest.mark.parametrize("case", range(24 * _X))
+def test_fuzz_peaks_and_flood(case, dev):
+    """Random small masks (blobs, bars, noise, borders) through peak_local_max and the marker flood, random integer
+    landscapes through the flood alone — against the oracle's restatement of skimage (first-in-first-out tie order)."""
+    import scipy.ndimage as ndi
+
+    rng = np.random.default_rng(7000 + case)
+    H, W = int(rng.integers(20, 140)), int(rng.integers(20, 160))
+    kind = case % 4
+    if kind == 0:     # smooth blobs
+        mask = ndi.gaussian_filter(rng.standard_normal((H, W)), rng.uniform(2, 6)) > rng.uniform(-0.02, 0.05)
+    elif kind == 1:   # bars and boxes: plateaus of the distance, tied seeds
+        mask = np.zeros((H, W), dtype=bool)
+        for _ in range(int(rng.integers(2, 8))):
+            y, x = int(rng.integers(0, H - 4)), int(rng.integers(0, W - 4))
+            mask[y:y + int(rng.integers(3, 30)), x:x + int(rng.integers(3, 60))] = True
+    elif kind == 2:   # dense noise, then closed: thin and ragged
+        mask = ndi.binary_closing(rng.random((H, W)) < rng.uniform(0.2, 0.6), iterations=1)
+    else:             # everything, or nearly
+        mask = rng.random((H, W)) < 0.995
+    d = int(rng.choice([1, 2, 3, 8, 8, 8]))
+    dist = O.distance_transform_edt(mask)
+    want = O.peak_local_max(dist, d, mask)
+    m = torch.from_numpy(mask.astype(np.uint8)).to(dev)
+    d2 = K().distance_transform_edt_sq(m[None])[0]
+    peaks = K().peak_local_max(d2, m, d).cpu().numpy()
+    want_img = np.zeros((H, W), dtype=np.uint8)
+    if len(want):
+        want_img[tuple(want.T)] = 1
+    assert np.array_equal(peaks, want_img), (case, kind, d)
+    markers = O.label(want_img)
+    flood = O.watershed(-dist, markers, mask, ties="fifo")
+    got = K().watershed(d2, torch.from_numpy(markers).to(dev), m, negate=True).cpu().numpy()
+    assert np.array_equal(got, flood), (case, kind, d)
+    # an arbitrary landscape with arbitrary seeds (some of them several pixels large)
+    h = rng.integers(0, int(rng.choice([2, 5, 50, 5000])), size=(H, W)).astype(np.int32)
+    mk = np.zeros((H, W), dtype=np.int32)
+    ys, xs = np.nonzero(mask)
+    if len(ys):
+        for l in range(1, int(rng.integers(1, 12)) + 1):
+            j = int(rng.integers(0, len(ys)))
+            y, x = ys[j], xs[j]
+            blob = np.zeros((H, W), dtype=bool)
+            blob[y:y + int(rng.integers(1, 3)), x:x + int(rng.integers(1, 4))] = True
+            mk[blob & mask & (mk == 0)] = l
+    flood = O.watershed(h.astype(np.float64), mk, mask, ties="fifo")
+    got = K().watershed(torch.from_numpy(h).to(dev), torch.from_numpy(mk).to(dev), m).cpu().numpy()
+    assert np.array_equal(got, flood), (case, kind, "landscape")
