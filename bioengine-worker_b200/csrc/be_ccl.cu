@@ -298,60 +298,44 @@ __global__ void __launch_bounds__(kThreads, 8) ccl_tile_kernel(const void* __res
         }
     }
     __syncthreads();
-    // ---- C2: every run takes its root's label (a non-root slot is read by nobody else, so this is done in place);
-    //          a root run flags its first pixel in the root bitmap ----
+    // ---- C2 / D: every run writes its root's label over its pixels (the per-pixel parents: they exist only where the
+    //          mask has pixels, nobody reads the rest); a root run flags its first pixel in the root bitmap.  Done per run,
+    //          not per 4-pixel unit: a speckled mask has fewer runs than units with a set pixel, and a run needs no
+    //          bit-twiddling to find out whose label it carries ----
     {
         const int r = threadIdx.x >> 2, part = threadIdx.x & 3;
+        const u64 m = rmask[r];
         const int n_runs = __popcll(rstart[r]);
+        const int64_t row_base = ((z0 + (r >> g.ty_log2)) * g.Y + (y0 + (r & ty_mask))) * g.X + x0;
+        int32_t* row = Li + row_base;
+        const bool vec_ok = ((g.X & 3) == 0) && ((((uintptr_t)Li) & 15) == 0);   // x0 is a multiple of 64
         u64 roots = 0;
         for (int k = part; k < n_runs; k += 4) {
             const unsigned id = r * 32 + k;
             const unsigned root = parent[id];
-            if (root == id)
-                roots |= 1ull << xstart[id];
-            else
-                glab[id] = glab[root];
+            const int x = xstart[id];
+            if (root == id) roots |= 1ull << x;
+            const int32_t lab = glab[root];
+            const u64 rest = ~(m >> x);
+            const int len = rest ? __ffsll((long long)rest) - 1 : 64;
+            if (len < 8 || !vec_ok) {
+                for (int j = 0; j < len; ++j) row[x + j] = lab;
+            } else {   // long runs (blob-like masks): 16-byte stores between an unaligned head and tail
+                int j = x;
+                const int end = x + len;
+                for (; j & 3; ++j) row[j] = lab;
+                const int4 v = make_int4(lab, lab, lab, lab);
+                for (; j + 4 <= end; j += 4) *reinterpret_cast<int4*>(row + j) = v;
+                for (; j < end; ++j) row[j] = lab;
+            }
         }
         if (roots) atomicOr(&rroot[r], roots);
     }
     __syncthreads();
 
-    // ---- D: per-pixel parents, 4 pixels per lane (one 16-byte store), two rows per warp instruction ----
+    // ---- bitmaps out: the root bitmap and, unless the input can be used in place, the packed mask ----
     {
         const int64_t wpr = g.tiles_x;
-        const int lane16 = lane & 15, sub = lane >> 4;
-        const int x4 = lane16 * 4;
-        const bool vec_ok = ((g.X & 3) == 0) && ((((uintptr_t)Li) & 15) == 0);
-        // the warp's eight rows are consecutive in y (2-D: 64 rows of one plane; 3-D: one 8-row plane of the tile)
-        const int r0 = warp * 8 + sub;
-        const int64_t zw = z0 + (r0 >> g.ty_log2), yw = y0 + (r0 & ty_mask);
-        int32_t* row = Li + (zw * g.Y + yw) * g.X + x0 + x4;
-#pragma unroll
-        for (int it = 0; it < 4; ++it, row += 2 * g.X) {
-            const int r = r0 + it * 2;
-            const bool row_ok = zw < g.Z && yw + it * 2 < g.Y;
-            const u64 m = rmask[r], s = rstart[r];
-            const unsigned m4 = (unsigned)(m >> x4) & 0xfu, s4 = (unsigned)(s >> x4) & 0xfu;
-            if (m4 == 0) continue;   // parents exist only where the mask has pixels: nobody reads the rest
-            // four pixels hold at most two runs: A = the one containing the first set pixel, B = a second one starting
-            // inside the unit (its index is A's + 1)
-            const int f = __ffs(m4) - 1;
-            const int idxA = r * 32 + __popcll(s & ((1ull << x4) - 1ull)) - 1 + (int)((s4 >> f) & 1u);
-            const unsigned runA = m4 & ~(m4 + (1u << f)), runB = m4 & ~runA;
-            const int32_t labA = glab[idxA], labB = runB ? glab[idxA + 1] : -1;
-            int32_t v[4];
-#pragma unroll
-            for (int j = 0; j < 4; ++j) v[j] = ((runA >> j) & 1u) ? labA : (((runB >> j) & 1u) ? labB : -1);
-            if (!row_ok) continue;
-            if (vec_ok && x0 + x4 + 4 <= g.X) {
-                *reinterpret_cast<int4*>(row) = make_int4(v[0], v[1], v[2], v[3]);
-            } else {
-#pragma unroll
-                for (int j = 0; j < 4; ++j)
-                    if (x0 + x4 + j < g.X) row[j] = v[j];
-            }
-        }
-        __syncwarp();  // the 8 rows of this warp's band were written by this warp only
         if (lane < 8) {
             const int r = warp * 8 + lane;
             const int64_t z = z0 + (r >> g.ty_log2), y = y0 + (r & ty_mask);

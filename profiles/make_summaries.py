@@ -6,7 +6,7 @@ The first launch of every kernel name in the capture is used (the capture starts
 import csv, json, re, sys
 
 STAGES = {
-    "quantile_select": ["qsel_sample_kernel", "qsel_partition_kernel", "qsel_cluster_kernel"],
+    "quantile_select": ["qsel_pivot_kernel", "qsel_sample_kernel", "qsel_partition_kernel", "qsel_cluster_kernel"],
     "normalise+tile_gather": ["tile_gather_tma_kernel", "tile_gather_kernel"],
     "blend_stitch+sigmoid+binarize": ["stitch_blend_mask2d_kernel", "stitch_blend_rows_kernel", "stitch_blend_kernel"],
     "ccl": ["ccl_tile_kernel", "ccl_edge_kernel", "ccl_number_kernel", "ccl_resolve_kernel"],
