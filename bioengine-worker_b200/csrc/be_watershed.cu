@@ -20,8 +20,9 @@
 //                           the pusher, neighbour number), which is the order the sequential flood would give — unless
 //                           one of them uncovers a lower pixel: then only the entries up to and including that one are
 //                           taken, because the sequential flood would run down into the new basin before it returns.
-//                           Contested pixels go to the earliest pusher through a 64-bit atomicMin on (step, position,
-//                           neighbour).  Markers that tie in height leave in raster order (first in, first out); skimage's
+//                           A contested pixel goes to the entry around it that was pushed first (every queued pixel carries
+//                           its push number), which each entry works out for itself from the records of the pixels two
+//                           steps away.  Markers that tie in height leave in raster order (first in, first out); skimage's
 //                           binary heap orders such complete ties by its array layout, which no parallel flood can
 //                           reproduce — the oracle implements both and the tests say where they differ.
 #include "be_common.cuh"
@@ -344,11 +345,13 @@ struct FloodArgs {
     int32_t* out;
     uint64_t* qa;
     uint64_t* qb;
-    unsigned long long* claim;
+    unsigned long long* rec;   // per pixel: height key << 32 | gone << 31 | push number (all ones: never queued)
     int32_t* ticket;
     int64_t cap;
     int Y, X, negate;
 };
+
+constexpr int kFloodThreads = 512;   // threads of a flood block: the passes over a long queue are per-thread loops
 
 __device__ __forceinline__ unsigned long long block_scan_incl(unsigned long long v, unsigned long long* s_warp) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -363,9 +366,9 @@ __device__ __forceinline__ unsigned long long block_scan_incl(unsigned long long
     return v + add;
 }
 
-__global__ void __launch_bounds__(kThreads, 4) ws_flood_kernel(FloodArgs a) {
+__global__ void __launch_bounds__(kFloodThreads, 2) ws_flood_kernel(FloodArgs a) {
     __shared__ int s_c, s_istar;
-    __shared__ unsigned long long s_warp[kThreads / 32], s_tot;
+    __shared__ unsigned long long s_warp[kFloodThreads / 32], s_tot;
     __shared__ uint32_t s_hnext;
     const int tid = threadIdx.x;
     const int X = a.X, Y = a.Y;
@@ -381,15 +384,18 @@ __global__ void __launch_bounds__(kThreads, 4) ws_flood_kernel(FloodArgs a) {
         if (m == 0) continue;
         uint64_t* cur = a.qa + a.offset[c];
         uint64_t* nxt = a.qb + a.offset[c];
-        // seeds arrived in any order: put them in raster order (their pixel index), find the lowest height
+        // seeds arrived in any order: put them in raster order (their pixel index), find the lowest height.  Every pixel
+        // that enters the queue gets a record (height key, push number): the push number is its place in the queue order
+        // for good, whatever position it holds in the array
         if (tid == 0) s_hnext = 0xffffffffu;
         __syncthreads();
-        for (int i = tid; i < m; i += kThreads) {
+        for (int i = tid; i < m; i += kFloodThreads) {
             const uint64_t e = cur[i];
             const uint32_t p = (uint32_t)e & kPixMask;
             int rank = 0;
             for (int j = 0; j < m; ++j) rank += ((uint32_t)cur[j] & kPixMask) < p;
             nxt[rank] = e;
+            a.rec[p] = (e & 0xffffffff00000000ull) | (unsigned)rank;
             atomicMin(&s_hnext, (uint32_t)(e >> 32));
         }
         __syncthreads();
@@ -398,18 +404,19 @@ __global__ void __launch_bounds__(kThreads, 4) ws_flood_kernel(FloodArgs a) {
             cur = nxt;
             nxt = t;
         }
-        uint32_t step = 0;
+        uint32_t step = 0, pushed = (uint32_t)m;   // push numbers handed out so far
         unsigned long long sum_m = 0, max_m = 0;
         while (m > 0) {
             sum_m += (unsigned long long)m;
             max_m = max(max_m, (unsigned long long)m);
             const uint32_t hmin = s_hnext;
-            const unsigned long long keybase = (unsigned long long)(0xffffffffu - step) << 32;
             if (tid == 0) s_istar = INT32_MAX;
             __syncthreads();
-            // A: every entry of the lowest height claims its free neighbours; note the first that uncovers a lower pixel.
-            // All twelve loads of an entry are issued before any is looked at — the step is a chain of L2 round trips.
-            for (int i = tid; i < m; i += kThreads) {
+            // A: every entry of the lowest height looks at its four neighbours and at THEIR other neighbours.  A free
+            // neighbour q goes to the entry with the lowest push number among the lowest-height entries around q — the one
+            // the sequential flood pops first — so an entry knows what it wins without asking anybody: all its loads (4 x
+            // {region, label, height} + its own and 8 second-ring records) are issued together, one round trip to L2.
+            for (int i = tid; i < m; i += kFloodThreads) {
                 const uint64_t e = cur[i];
                 if ((uint32_t)(e >> 32) != hmin) continue;
                 const int p = (int)((uint32_t)e & kPixMask);
@@ -420,53 +427,52 @@ __global__ void __launch_bounds__(kThreads, 4) ws_flood_kernel(FloodArgs a) {
                 for (int k = 0; k < 4; ++k) {
                     const int q = ok[k] ? p + dq[k] : p;
                     rc[k] = a.comp[q];
-                    ro[k] = a.out[q];
+                    ro[k] = __ldcg(a.out + q);
                     rh[k] = a.height[q];
                 }
+                // second ring: U2, UL, UR, L2, R2, DL, DR, D2
+                const bool ok2[8] = {y > 1, ok[0] && ok[1], ok[0] && ok[2], x > 1, x + 2 < X, ok[3] && ok[1], ok[3] && ok[2], y + 2 < Y};
+                const int d2[8] = {-2 * X, -X - 1, -X + 1, -2, 2, X - 1, X + 1, 2 * X};
+                unsigned long long r2[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) r2[j] = ok2[j] ? __ldcg(a.rec + (p + d2[j])) : ~0ull;
+                const uint32_t my = (uint32_t)__ldcg(a.rec + p) & 0x7fffffffu;
+                // does a waiting lowest-height entry with an earlier push number sit on that pixel?
+                auto beats = [&](unsigned long long r) {
+                    return (uint32_t)(r >> 32) == hmin && !((uint32_t)r & 0x80000000u) && ((uint32_t)r & 0x7fffffffu) < my;
+                };
+                const bool lose[4] = {beats(r2[0]) || beats(r2[1]) || beats(r2[2]),    // up:    U2, UL, UR
+                                      beats(r2[1]) || beats(r2[3]) || beats(r2[5]),    // left:  UL, L2, DL
+                                      beats(r2[2]) || beats(r2[4]) || beats(r2[6]),    // right: UR, R2, DR
+                                      beats(r2[5]) || beats(r2[6]) || beats(r2[7])};   // down:  DL, DR, D2
+                unsigned won = 0x10u;   // bit 4: "is a lowest-height entry"; bits 0..3: neighbour k is mine
                 bool lower = false;
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
                     if (!ok[k] || rc[k] != c || ro[k] != 0) continue;
-                    atomicMin(&a.claim[p + dq[k]], keybase | (unsigned)(i * 4 + k));
+                    if (!lose[k]) won |= 1u << k;
                     lower |= height_key(rh[k], a.negate) < hmin;
                 }
+                cur[i] = e | ((uint64_t)won << kPixBits);
                 if (lower) atomicMin(&s_istar, i);
             }
             __syncthreads();
             const int istar = s_istar;
             if (tid == 0) s_hnext = 0xffffffffu;
-            // A2: the entries that leave learn which neighbours they won; the answer (4 bits + a "leaves" bit) rides in the
-            // free bits of the entry
-            for (int i = tid; i < m && i <= istar; i += kThreads) {
-                const uint64_t e = cur[i];
-                if ((uint32_t)(e >> 32) != hmin) continue;
-                const int p = (int)((uint32_t)e & kPixMask);
-                const int y = p / X, x = p - y * X;
-                const bool ok[4] = {y > 0, x > 0, x + 1 < X, y + 1 < Y};
-                unsigned long long cl[4];
-#pragma unroll
-                for (int k = 0; k < 4; ++k) cl[k] = __ldcg(&a.claim[ok[k] ? p + dq[k] : p]);
-                unsigned won = 0x10u;
-#pragma unroll
-                for (int k = 0; k < 4; ++k)
-                    if (ok[k] && cl[k] == (keybase | (unsigned)(i * 4 + k))) won |= 1u << k;
-                cur[i] = e | ((uint64_t)won << kPixBits);
-            }
-            __syncthreads();
             // B: survivors keep their order at the front; the pixels won follow, ordered by (winner's position, neighbour).
             // A thread owns a contiguous stretch of the queue, so one block-wide scan per step places everything; a
             // leaving entry gets the position of its first push written over its height.
-            const int L = (m + kThreads - 1) / kThreads;
+            const int L = (m + kFloodThreads - 1) / kFloodThreads;
             const int lo = min(tid * L, m), hi = min(lo + L, m);
             int kept = 0, push = 0;
             for (int i = lo; i < hi; ++i) {
                 const unsigned flags = ((uint32_t)cur[i]) >> kPixBits;
-                if (flags) push += __popc(flags & 0xfu);
+                if (flags && i <= istar) push += __popc(flags & 0xfu);
                 else ++kept;
             }
             const unsigned long long packed = (unsigned long long)kept | ((unsigned long long)push << 32);
             const unsigned long long incl = block_scan_incl(packed, s_warp);
-            if (tid == kThreads - 1) s_tot = incl;
+            if (tid == kFloodThreads - 1) s_tot = incl;
             __syncthreads();
             const int kept_total = (int)(uint32_t)s_tot, push_total = (int)(s_tot >> 32);
             int kept_pos = (int)(uint32_t)(incl - packed), push_pos = kept_total + (int)((incl - packed) >> 32);
@@ -474,23 +480,25 @@ __global__ void __launch_bounds__(kThreads, 4) ws_flood_kernel(FloodArgs a) {
             for (int i = lo; i < hi; ++i) {
                 const uint64_t e = cur[i];
                 const unsigned flags = ((uint32_t)e) >> kPixBits;
-                if (flags) {
+                if (flags && i <= istar) {
                     cur[i] = ((uint64_t)(uint32_t)push_pos << 32) | (uint32_t)e;
                     push_pos += __popc(flags & 0xfu);
                 } else {
-                    nxt[kept_pos++] = e;
+                    nxt[kept_pos++] = e & ~((uint64_t)0x1fu << kPixBits);
                     hnext = min(hnext, (uint32_t)(e >> 32));
                 }
             }
             __syncthreads();
-            // C: the leaving entries label and push what they won
-            for (int i = tid; i < m && i <= istar; i += kThreads) {
+            // C: the leaving entries are marked as gone, label and push what they won
+            for (int i = tid; i < m && i <= istar; i += kFloodThreads) {
                 const uint64_t e = cur[i];
                 const unsigned flags = ((uint32_t)e) >> kPixBits;
-                if (!(flags & 0xfu)) continue;
+                if (!flags) continue;
                 const int p = (int)((uint32_t)e & kPixMask);
+                a.rec[p] = ((unsigned long long)hmin << 32) | 0x80000000ull;
+                if (!(flags & 0xfu)) continue;
                 int pos = (int)(e >> 32);
-                const int32_t label = a.out[p];
+                const int32_t label = __ldcg(a.out + p);
                 int rh[4];
 #pragma unroll
                 for (int k = 0; k < 4; ++k) rh[k] = a.height[(flags & (1u << k)) ? p + dq[k] : p];
@@ -500,6 +508,7 @@ __global__ void __launch_bounds__(kThreads, 4) ws_flood_kernel(FloodArgs a) {
                         const int q = p + dq[k];
                         const uint32_t hk = height_key(rh[k], a.negate);
                         a.out[q] = label;
+                        a.rec[q] = ((unsigned long long)hk << 32) | (pushed + (uint32_t)(pos - kept_total));
                         nxt[pos++] = ((uint64_t)hk << 32) | (uint32_t)q;
                         hnext = min(hnext, hk);
                     }
@@ -508,6 +517,7 @@ __global__ void __launch_bounds__(kThreads, 4) ws_flood_kernel(FloodArgs a) {
             if ((tid & 31) == 0) atomicMin(&s_hnext, hnext);
             __syncthreads();
             m = kept_total + push_total;
+            pushed += (uint32_t)push_total;
             uint64_t* t = cur;
             cur = nxt;
             nxt = t;
@@ -601,9 +611,9 @@ extern "C" int be_watershed_i32(const int32_t* height, int negate, const int32_t
     w += 4 * cap_bytes;
     uint64_t* qa = (uint64_t*)w;
     uint64_t* qb = (uint64_t*)(w + q_bytes);
-    unsigned long long* claim = (unsigned long long*)(w + 2 * q_bytes);
+    unsigned long long* rec = (unsigned long long*)(w + 2 * q_bytes);
     BE_CUDA(cudaMemsetAsync(area, 0, 3 * cap_bytes, s));                 // area, n_seed, fill
-    BE_CUDA(cudaMemsetAsync(claim, 0xff, 8 * (size_t)n, s));
+    BE_CUDA(cudaMemsetAsync(rec, 0xff, 8 * (size_t)n, s));
     const unsigned gpx = (unsigned)((n + kThreads - 1) / kThreads);
     ws_area_kernel<<<gpx, kThreads, 0, s>>>(regions, markers, out, n, area, n_seed);
     BE_LAUNCH_CHECK();
@@ -611,8 +621,8 @@ extern "C" int be_watershed_i32(const int32_t* height, int negate, const int32_t
     BE_LAUNCH_CHECK();
     ws_seed_kernel<<<gpx, kThreads, 0, s>>>(regions, markers, height, negate, n, offset, fill, qa);
     BE_LAUNCH_CHECK();
-    FloodArgs a{regions, height, n_regions, offset, n_seed, out, qa, qb, claim, ticket, cap, (int)Y, (int)X, negate};
-    ws_flood_kernel<<<BE_SM_COUNT * 4, kThreads, 0, s>>>(a);
+    FloodArgs a{regions, height, n_regions, offset, n_seed, out, qa, qb, rec, ticket, cap, (int)Y, (int)X, negate};
+    ws_flood_kernel<<<BE_SM_COUNT * 2, kFloodThreads, 0, s>>>(a);
     BE_LAUNCH_CHECK();
     return BE_OK;
 }
