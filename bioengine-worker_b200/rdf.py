@@ -4,8 +4,8 @@ Understands the parts of model RDF 0.5 (and the 0.4 spellings of the same things
 `predict_sample_with[out]_blocking`: input/output ids and axes, pre-/post-processing op lists,
 parameterised input sizes (`size: {min, step}`), output halo, packaged test tensors, and the `pytorch_state_dict` weights
 entry with its architecture — a callable of this package (`UNet2d`, `UNet3d`) or a class in a source file of the model
-package.  Output sizes follow the input's (`SizeReference` with scale 1, offset 0); other scales and dataset-mode
-statistics are not read (row f2 of SURVEY §8f).
+package.  Output sizes follow an input's through `SizeReference` and the axes' `scale` (0.4: `shape.reference_tensor` /
+`scale`); dataset-mode statistics are not read (row f2 of SURVEY §8f).
 """
 from __future__ import annotations
 
@@ -33,6 +33,9 @@ class TensorSpec:
     halo: Dict[str, int] = field(default_factory=dict)
     n_channels: Optional[int] = None            # from `channel_names` / a fixed channel size, if declared
     test_tensor: Optional[str] = None           # packaged example (`test_tensor.source`, or 0.4 `test_inputs/outputs`)
+    scale: Dict[str, float] = field(default_factory=dict)     # spatial axis id -> physical size of one pixel (default 1)
+    size_ref: Dict[str, Tuple[str, str, int]] = field(default_factory=dict)   # axis -> (tensor id, axis id, offset)
+    ref_scale: Dict[str, float] = field(default_factory=dict)  # 0.4 outputs: size = reference size * scale + 2 * offset
 
 
 @dataclass
@@ -86,6 +89,12 @@ def _tensor(entry: Dict[str, Any], is_output: bool) -> TensorSpec:
         if isinstance(shape, dict) and "min" in shape:
             spec.size_min = {a: int(m) for a, m in zip(axes, shape["min"]) if a in "zyx"}
             spec.size_step = {a: int(s) for a, s in zip(axes, shape.get("step", [0] * len(axes))) if a in "zyx"}
+        if isinstance(shape, dict) and "reference_tensor" in shape:   # implicit output shape
+            ref = str(shape["reference_tensor"])
+            for a, sc, off in zip(axes, shape.get("scale", [1.0] * len(axes)), shape.get("offset", [0] * len(axes))):
+                if a in "zyx":
+                    spec.ref_scale[a] = float(sc)
+                    spec.size_ref[a] = (ref, a, int(round(2 * float(off))))
         return spec
     letters = []
     for ax in axes or []:
@@ -103,6 +112,10 @@ def _tensor(entry: Dict[str, Any], is_output: bool) -> TensorSpec:
                 spec.size_min[l], spec.size_step[l] = int(size["min"]), int(size.get("step", 0))
             elif isinstance(size, int):
                 spec.size_min[l], spec.size_step[l] = int(size), 0
+            elif isinstance(size, dict) and "tensor_id" in size:   # SizeReference
+                spec.size_ref[l] = (str(size["tensor_id"]), str(size.get("axis_id", l)), int(size.get("offset", 0)))
+            if "scale" in ax:
+                spec.scale[l] = float(ax["scale"])
             if "halo" in ax:
                 spec.halo[l] = int(ax["halo"])
     spec.axes = "".join(letters)

@@ -18,6 +18,7 @@ import json
 import logging
 import os
 from collections import OrderedDict
+from fractions import Fraction
 from pathlib import Path
 from typing import Dict, List, Literal, Optional, Union
 
@@ -272,7 +273,13 @@ class RuntimeDeployment:
                 raise ValueError(f"input {inp.id!r} has batch/spatial shape {(xi.shape[0],) + tuple(xi.shape[2:])}, "
                                  f"input {inp0.id!r} has {(N,) + spatial}: inputs are tiled together and must agree")
         sp_axes = [a for a in inp0.axes if a in "zyx"]
-        halos = [tuple(o.halo.get(a, 0) for a in sp_axes) for o in spec.outputs]
+        ratios = [self._output_ratio(spec, o, sp_axes) for o in spec.outputs]      # output pixels per input pixel, per axis
+        halos = []
+        for o, r in zip(spec.outputs, ratios):   # an output's halo is given in its own pixels: bring it to input pixels
+            h = [Fraction(o.halo.get(a, 0)) / ra for a, ra in zip(sp_axes, r)]
+            if any(v.denominator != 1 for v in h):
+                raise ValueError(f"output {o.id!r}: halo {o.halo} is not a whole number of input pixels at scale {[float(x) for x in r]}")
+            halos.append(tuple(int(v) for v in h))
         if len(set(halos)) != 1:
             raise ValueError(f"outputs declare different halos {halos}; one block geometry serves all outputs")
         if blocking:
@@ -307,8 +314,69 @@ class RuntimeDeployment:
             fb = max(1, int(pipe.spec.forward_batch))
             raw = self._gather_outputs([loaded.net(*[t[i:i + fb] for t in tiles]) for i in range(0, tiles[0].shape[0], fb)])
         logits_by_output = self._outputs_in_order(raw, spec)
-        return {str(o.id): self._finish_output(pipe, lg.contiguous(), o, N, spatial, ref_norms)
-                for o, lg in zip(spec.outputs, logits_by_output)}
+        results = {}
+        for o, lg, r in zip(spec.outputs, logits_by_output, ratios):
+            axes, out_spatial = self._output_axes(pipe, r, spatial, block, halo, tuple(lg.shape[2:]), o.id)
+            results[str(o.id)] = self._finish_output(axes, lg.contiguous(), o, N, out_spatial, ref_norms)
+        return results
+
+    @staticmethod
+    def _output_ratio(spec: ModelSpec, outp, sp_axes) -> List[Fraction]:
+        """Output pixels per input pixel along every spatial axis: bioimageio's `SizeReference` gives
+        size_out = size_ref * scale_ref / scale_out + offset (0.5; `scale` = physical size of a pixel) or
+        size_out = size_ref * scale + 2 * offset (0.4 implicit output shape).  Offsets other than 0 (valid convolutions that
+        shrink the output) are not supported: such models declare a halo instead."""
+        by_id = {t.id: t for t in spec.inputs}
+        out = []
+        for a in sp_axes:
+            ref = outp.size_ref.get(a)
+            r = Fraction(1)
+            if ref is not None:
+                tensor_id, axis_id, offset = ref
+                if offset != 0:
+                    raise ValueError(f"output {outp.id!r}: size offset {offset} on axis {a} is not supported")
+                if a in outp.ref_scale:
+                    r = Fraction(outp.ref_scale[a]).limit_denominator(64)
+                else:
+                    src = by_id.get(tensor_id)
+                    if src is None:
+                        raise ValueError(f"output {outp.id!r} takes its size from {tensor_id!r}, which is not an input")
+                    r = (Fraction(src.scale.get(axis_id, 1.0)).limit_denominator(64)
+                         / Fraction(outp.scale.get(a, 1.0)).limit_denominator(64))
+            elif a in outp.scale:
+                r = 1 / Fraction(outp.scale[a]).limit_denominator(64)
+            if r <= 0:
+                raise ValueError(f"output {outp.id!r}: scale {float(r)} on axis {a}")
+            out.append(r)
+        return out
+
+    @staticmethod
+    def _output_axes(pipe: TiledPipeline, ratio, spatial, block, halo, tile_spatial, out_id):
+        """The stitcher's per-axis tables in OUTPUT pixels.  At scale 1 they are the gather's; otherwise the same blocks
+        scaled: block, halo, inner region and sample size times the ratio (all must stay whole numbers), cached per output."""
+        if all(r == 1 for r in ratio):
+            if tuple(tile_spatial) != tuple(block):
+                raise ValueError(f"output {out_id!r}: the network returned tiles of {tuple(tile_spatial)} for blocks of {tuple(block)}")
+            return pipe.axes, tuple(spatial)
+        cache = pipe.__dict__.setdefault("_scaled_axes", {})
+        key = (out_id, tuple(ratio))
+        if key not in cache:
+            from . import geometry as G
+
+            dims = []
+            for s_, b_, h_, r in zip(spatial, block, halo, ratio):
+                vals = [Fraction(s_) * r, Fraction(b_) * r, Fraction(h_) * r]
+                if any(v.denominator != 1 for v in vals):
+                    raise ValueError(f"output {out_id!r}: sample {s_} / block {b_} / halo {h_} do not scale by {float(r)} to whole pixels")
+                dims.append(tuple(int(v) for v in vals))
+            axes = [G.bioimageio_axis(s_, b_, h_) for s_, b_, h_ in dims]
+            if len(axes) == 2:
+                axes = [G.identity_axis(1)] + axes
+            cache[key] = ([K.DeviceAxis(a, pipe.device) for a in axes], tuple(d[0] for d in dims), tuple(d[1] for d in dims))
+        axes, out_spatial, out_block = cache[key]
+        if tuple(tile_spatial) != out_block:
+            raise ValueError(f"output {out_id!r}: the network returned tiles of {tuple(tile_spatial)}, the description implies {out_block}")
+        return axes, out_spatial
 
     @staticmethod
     def _gather_outputs(chunks):
@@ -333,7 +401,7 @@ class RuntimeDeployment:
             raise ValueError(f"the network returned {len(raw)} tensor(s), the model declares {len(spec.outputs)} output(s)")
         return list(raw)
 
-    def _finish_output(self, pipe: TiledPipeline, logits: torch.Tensor, outp, N: int, spatial, ref_norms) -> np.ndarray:
+    def _finish_output(self, axes, logits: torch.Tensor, outp, N: int, spatial, ref_norms) -> np.ndarray:
         post = [o for o in outp.ops if o.name != "ensure_dtype"]
         out_shape = (N, logits.shape[1]) + tuple(spatial)
         names = [o.name for o in post]
@@ -341,12 +409,12 @@ class RuntimeDeployment:
             epi = _lib.BE_EPI_SIGMOID if "sigmoid" in names else _lib.BE_EPI_NONE
             if "binarize" in names:
                 thr = float(post[-1].kwargs["threshold"])
-                _, mask = K.stitch_crop(logits, out_shape, pipe.axes, epi, thr, want_out=False, want_mask=True)
+                _, mask = K.stitch_crop(logits, out_shape, axes, epi, thr, want_out=False, want_mask=True)
                 result = mask
             else:
-                result, _ = K.stitch_crop(logits, out_shape, pipe.axes, epi)
+                result, _ = K.stitch_crop(logits, out_shape, axes, epi)
         else:
-            stitched, _ = K.stitch_crop(logits, out_shape, pipe.axes)
+            stitched, _ = K.stitch_crop(logits, out_shape, axes)
             result = self._run_ops_unfused(stitched, post, N, logits.shape[1], ref_norms)
         want_dtype = getattr(torch, outp.dtype, torch.float32)
         if result.dtype == want_dtype:

@@ -428,3 +428,84 @@ def test_model_test_uses_the_packaged_test_tensors(tmp_path, dev):
     assert rep["status"] == "failed" and [d["status"] for d in rep["details"]] == ["passed", "failed"]
     with pytest.raises(ValueError):
         asyncio.run(rt.test(rdf_good, additional_requirements="numpy"))
+
+
+_RESAMPLERS = '''
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+
+class Up2(nn.Module):
+    """3x3 convolution, then nearest-neighbour upsampling by 2: output twice the input size."""
+    def __init__(self):
+        super().__init__()
+        self.conv = nn.Conv2d(1, 2, 3, padding=1)
+
+    def forward(self, x):
+        return F.interpolate(self.conv(x), scale_factor=2, mode="nearest")
+
+
+class Down2(nn.Module):
+    """3x3 convolution, then 2x2 average pooling: output half the input size."""
+    def __init__(self):
+        super().__init__()
+        self.conv = nn.Conv2d(1, 1, 3, padding=1)
+
+    def forward(self, x):
+        return F.avg_pool2d(self.conv(x), 2)
+'''
+
+
+@pytest.mark.parametrize("name,pixel,halo_out,factor", [("Up2", 0.5, 4, 2.0), ("Down2", 2.0, 2, 0.5)])
+def test_predict_output_of_another_size(tmp_path, dev, name, pixel, halo_out, factor):
+    """Outputs whose size is the input's times a factor (`SizeReference` + axis `scale`): the blocks, their halo and the
+    reassembly are in output pixels on the way out."""
+    import importlib.util
+
+    from bioengine_worker_b200 import models
+    from bioengine_worker_b200.runtime_deployment import RuntimeDeployment
+
+    models.strict_fp32()
+    (tmp_path / "net.py").write_text(_RESAMPLERS)
+    spec = importlib.util.spec_from_file_location("resamplers_for_test", tmp_path / "net.py")
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    torch.manual_seed(21)
+    net = getattr(mod, name)().eval()
+    torch.save(net.state_dict(), tmp_path / "weights.pt")
+    rdf = {
+        "format_version": "0.5.3", "type": "model", "name": name,
+        "inputs": [{"id": "raw", "axes": [{"type": "batch"}, {"type": "channel", "channel_names": ["c"]}]
+                    + [{"type": "space", "id": a, "size": {"min": 32, "step": 16}} for a in "yx"],
+                    "preprocessing": [{"id": "zero_mean_unit_variance", "kwargs": {"axes": ["y", "x"]}}]}],
+        "outputs": [{"id": "out", "data": {"type": "float32"},
+                     "axes": [{"type": "batch"}, {"type": "channel", "channel_names": [f"o{i}" for i in range(2 if name == "Up2" else 1)]}]
+                     + [{"type": "space", "id": a, "scale": pixel, "halo": halo_out, "size": {"tensor_id": "raw", "axis_id": a}} for a in "yx"]}],
+        "weights": {"pytorch_state_dict": {"source": "weights.pt", "architecture": {"source": "net.py", "callable": name}}},
+    }
+    (tmp_path / "rdf.yaml").write_text(yaml.safe_dump(rdf))
+    rng = np.random.default_rng(8)
+    x = rng.normal(10, 3, size=(1, 1, 144, 176)).astype(np.float32)
+    pre = O.zero_mean_unit_variance(x, axes=(2, 3))
+    rt = RuntimeDeployment.func_or_class()
+    out = asyncio.run(rt.predict(str(tmp_path / "rdf.yaml"), x))["out"]
+    with torch.no_grad():
+        want = net.to(dev)(torch.from_numpy(pre).to(dev)).cpu().numpy()
+    assert out.shape == want.shape == (1, want.shape[1], int(144 * factor), int(176 * factor))
+    np.testing.assert_allclose(out, want, rtol=1e-5, atol=1e-6)
+    # blocks of 32 + 2*16 = 64 input pixels; the halo is declared in output pixels
+    outb = asyncio.run(rt.predict(str(tmp_path / "rdf.yaml"), x, default_blocksize_parameter=2))["out"]
+    halo_in = int(halo_out / factor)
+    tiles = O.blocks_tensor(pre, (64, 64), (halo_in, halo_in))
+    with torch.no_grad():
+        t_out = net(torch.from_numpy(tiles).to(dev)).cpu().numpy()
+    bo = int(64 * factor)
+    wantb = O.from_blocks(t_out, want.shape, (bo, bo), (halo_out, halo_out))
+    np.testing.assert_allclose(outb, wantb, rtol=1e-5, atol=1e-6)
+    # away from the image border (reflect-padded halo there, zero padding in the whole-sample run) the halo covers the
+    # network's receptive field and the two runs agree
+    np.testing.assert_allclose(outb[..., 8:-8, 8:-8], want[..., 8:-8, 8:-8], rtol=1e-4, atol=1e-5)
+    if name == "Down2":   # 150 is 32 + k*16 for no k, and with blocking 150 * 0.5 is fine but 151 is not whole
+        with pytest.raises(ValueError):
+            asyncio.run(rt.predict(str(tmp_path / "rdf.yaml"), x[:, :, :143], default_blocksize_parameter=2))

@@ -99,3 +99,26 @@ def test_architecture_from_the_package(tmp_path):
         models.build_from_source(tmp_path, "../outside.py", "Tiny")
     with pytest.raises(FileNotFoundError):
         models.build_from_source(tmp_path, "nope.py", "Tiny")
+
+
+def test_output_ratio_from_size_reference(tmp_path):
+    from fractions import Fraction
+
+    rdf = {"inputs": [{"id": "raw", "axes": [{"type": "batch"}, {"type": "channel", "channel_names": ["c"]},
+                                              {"type": "space", "id": "y", "scale": 2.0, "size": {"min": 32, "step": 16}},
+                                              {"type": "space", "id": "x", "size": {"min": 32, "step": 16}}]}],
+           "outputs": [{"id": "o", "axes": [{"type": "batch"}, {"type": "channel", "channel_names": ["c"]},
+                                             {"type": "space", "id": "y", "scale": 1.0, "size": {"tensor_id": "raw", "axis_id": "y"}},
+                                             {"type": "space", "id": "x", "scale": 4.0, "size": {"tensor_id": "raw", "axis_id": "x"}}]}],
+           "weights": {"pytorch_state_dict": {"architecture": {"callable": "UNet2d"}}}}
+    spec = load_model_spec(_write(tmp_path, rdf))
+    assert RuntimeDeployment._output_ratio(spec, spec.outputs[0], ["y", "x"]) == [Fraction(2), Fraction(1, 4)]
+    rdf["outputs"][0]["axes"][2]["size"]["offset"] = -4
+    with pytest.raises(ValueError):
+        spec = load_model_spec(_write(tmp_path, rdf))
+        RuntimeDeployment._output_ratio(spec, spec.outputs[0], ["y", "x"])
+    old = {"inputs": [{"name": "i", "axes": "bcyx", "shape": {"min": [1, 1, 32, 32], "step": [0, 0, 16, 16]}}],
+           "outputs": [{"name": "o", "axes": "bcyx", "shape": {"reference_tensor": "i", "scale": [1, 1, 2, 0.5], "offset": [0, 0, 0, 0]}}],
+           "weights": {"pytorch_state_dict": {"architecture": "UNet2d"}}}
+    spec = load_model_spec(_write(tmp_path, old))
+    assert RuntimeDeployment._output_ratio(spec, spec.outputs[0], ["y", "x"]) == [Fraction(2), Fraction(1, 2)]
