@@ -152,6 +152,21 @@ def scale_linear(x, gain, offset, out=None):
 
 
 @_on_tensor_device
+def scale_linear_per_channel(x: torch.Tensor, gain, offset, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """bioimageio `scale_linear` with `gain` / `offset` given per channel (lists along the channel axis; a scalar is
+    repeated): y[n, c] = x[n, c] * gain[c] + offset[c] in float32, for an (N, C, ...) tensor."""
+    _check(x, torch.float32, "x")
+    N, C = x.shape[:2]
+    g = np.broadcast_to(np.asarray(gain, dtype=np.float64).reshape(-1), (C,)) if np.ndim(gain) else np.full(C, float(gain))
+    o = np.broadcast_to(np.asarray(offset, dtype=np.float64).reshape(-1), (C,)) if np.ndim(offset) else np.full(C, float(offset))
+    params = torch.from_numpy(np.tile(np.stack([o, g], axis=1), (N, 1))).to(x.device)   # [N*C][offset, gain]
+    y = out if out is not None else torch.empty_like(x)
+    n_seg, seg_len = _segments(x, N * C)
+    _lib.call("be_scale_linear_seg_f32", x.data_ptr(), y.data_ptr(), n_seg, seg_len, params.data_ptr(), _stream())
+    return y
+
+
+@_on_tensor_device
 def scale_mean_variance(x: torch.Tensor, ref_norm: torch.Tensor, n_seg: int, eps: float = 1e-6,
                         out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """bioimageio `scale_mean_variance`: (x - mean) / (std + eps) * (ref_std + eps) + ref_mean per segment.

@@ -179,14 +179,33 @@ class RuntimeDeployment:
             elif op.name == "clip":
                 x = K.clip(x, float(k["min"]), float(k["max"]), out=x)
             elif op.name == "scale_linear":
-                x = K.scale_linear(x, float(k.get("gain", 1.0)), float(k.get("offset", 0.0)), out=x)
+                gain, offset = k.get("gain", 1.0), k.get("offset", 0.0)
+                if isinstance(gain, (list, tuple)) or isinstance(offset, (list, tuple)):   # one value per channel
+                    self._check_per_channel(op, (gain, offset), c)
+                    x = K.scale_linear_per_channel(x, gain, offset, out=x)
+                else:
+                    x = K.scale_linear(x, float(gain), float(offset), out=x)
             elif op.name == "sigmoid":
                 x = K.sigmoid(x, out=x)
             elif op.name == "binarize":
-                x = K.to_float32(K.binarize(x, float(k["threshold"])))
+                thr = k["threshold"]
+                if isinstance(thr, (list, tuple)):   # x > t[c]  ⇔  x - t[c] > 0 (a float subtraction keeps the sign exactly)
+                    self._check_per_channel(op, (thr,), c)
+                    x = K.to_float32(K.binarize(K.scale_linear_per_channel(x, 1.0, [-float(t) for t in thr]), 0.0))
+                else:
+                    x = K.to_float32(K.binarize(x, float(thr)))
             else:
                 raise ValueError(f"unsupported processing op {op.name!r}")
         return x
+
+    @staticmethod
+    def _check_per_channel(op: Op, values, c: int) -> None:
+        axis = op.kwargs.get("axis", "channel")
+        if axis not in ("c", "channel"):
+            raise ValueError(f"{op.name}: parameters along axis {axis!r} are not supported (channel only)")
+        for v in values:
+            if isinstance(v, (list, tuple)) and len(v) != c:
+                raise ValueError(f"{op.name}: {len(v)} values for {c} channel(s)")
 
     @staticmethod
     def _segments_of(op: Op, n: int, c: int) -> int:

@@ -509,3 +509,27 @@ def test_predict_output_of_another_size(tmp_path, dev, name, pixel, halo_out, fa
     if name == "Down2":   # 150 is 32 + k*16 for no k, and with blocking 150 * 0.5 is fine but 151 is not whole
         with pytest.raises(ValueError):
             asyncio.run(rt.predict(str(tmp_path / "rdf.yaml"), x[:, :, :143], default_blocksize_parameter=2))
+
+
+def test_per_channel_scale_linear_and_binarize(dev):
+    """bioimageio `scale_linear` / `binarize` with one value per channel (`axis: channel`)."""
+    from bioengine_worker_b200.rdf import Op
+    from bioengine_worker_b200.runtime_deployment import RuntimeDeployment
+
+    rt = RuntimeDeployment.func_or_class()
+    rng = np.random.default_rng(3)
+    x = rng.normal(0, 2, size=(2, 3, 37, 41)).astype(np.float32)
+    gain, offset, thr = [0.5, 2.0, -1.25], [1.0, -3.0, 0.125], [0.1, -2.0, 1.5]
+    xt = torch.from_numpy(x).to(dev)
+    y = rt._run_ops_unfused(xt.clone(), [Op("scale_linear", {"gain": gain, "offset": offset, "axis": "channel"})], 2, 3)
+    want = x * np.asarray(gain, np.float32)[None, :, None, None] + np.asarray(offset, np.float32)[None, :, None, None]
+    assert np.array_equal(y.cpu().numpy(), want.astype(np.float32))
+    y = rt._run_ops_unfused(xt.clone(), [Op("scale_linear", {"gain": 3.0, "offset": offset})], 2, 3)
+    assert np.array_equal(y.cpu().numpy(), (x * np.float32(3.0) + np.asarray(offset, np.float32)[None, :, None, None]).astype(np.float32))
+    x[0, 1, 0, :3] = [-2.0, np.nextafter(np.float32(-2.0), np.float32(0)), np.nextafter(np.float32(-2.0), np.float32(-3))]   # on / beside a threshold
+    b = rt._run_ops_unfused(torch.from_numpy(x).to(dev), [Op("binarize", {"threshold": thr, "axis": "channel"})], 2, 3)
+    assert np.array_equal(b.cpu().numpy(), (x > np.asarray(thr, np.float32)[None, :, None, None]).astype(np.float32))
+    with pytest.raises(ValueError):
+        rt._run_ops_unfused(xt.clone(), [Op("scale_linear", {"gain": [1.0, 2.0]})], 2, 3)
+    with pytest.raises(ValueError):
+        rt._run_ops_unfused(xt.clone(), [Op("binarize", {"threshold": thr, "axis": "x"})], 2, 3)
