@@ -265,11 +265,14 @@ __device__ __forceinline__ uint32_t height_key(int32_t h, int negate) {
 
 __global__ void __launch_bounds__(kThreads) ws_area_kernel(const int32_t* __restrict__ comp, const int32_t* __restrict__ markers,
                                                            int32_t* __restrict__ out, int64_t n, int32_t* __restrict__ area,
-                                                           int32_t* __restrict__ n_seed) {
+                                                           int32_t* __restrict__ n_seed, const int32_t* __restrict__ n_comp_p,
+                                                           int64_t cap) {
     const int lane = threadIdx.x & 31;
     const int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x;
     const bool in = i < n;
-    const int32_t c = in ? comp[i] : 0;
+    const int32_t n_comp = (int32_t)min((int64_t)*n_comp_p, cap - 1);
+    int32_t c = in ? comp[i] : 0;
+    if (c > n_comp) c = 0;   // a region id beyond the stated count is treated as outside the mask (no table is that long)
     if (in) {
         const int32_t m = markers[i];
         out[i] = m;
@@ -327,11 +330,12 @@ __global__ void __launch_bounds__(1024) ws_offsets_kernel(const int32_t* __restr
 __global__ void __launch_bounds__(kThreads) ws_seed_kernel(const int32_t* __restrict__ comp, const int32_t* __restrict__ markers,
                                                            const int32_t* __restrict__ height, int negate, int64_t n,
                                                            const int32_t* __restrict__ offset, int32_t* __restrict__ fill,
-                                                           uint64_t* __restrict__ queue) {
+                                                           uint64_t* __restrict__ queue, const int32_t* __restrict__ n_comp_p,
+                                                           int64_t cap) {
     const int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x;
     if (i >= n) return;
     const int32_t c = comp[i];
-    if (c <= 0 || markers[i] == 0) return;
+    if (c <= 0 || c > (int32_t)min((int64_t)*n_comp_p, cap - 1) || markers[i] == 0) return;
     const int pos = atomicAdd(&fill[c], 1);
     queue[offset[c] + pos] = ((uint64_t)height_key(height[i], negate) << 32) | (uint32_t)i;
 }
@@ -615,11 +619,11 @@ extern "C" int be_watershed_i32(const int32_t* height, int negate, const int32_t
     BE_CUDA(cudaMemsetAsync(area, 0, 3 * cap_bytes, s));                 // area, n_seed, fill
     BE_CUDA(cudaMemsetAsync(rec, 0xff, 8 * (size_t)n, s));
     const unsigned gpx = (unsigned)((n + kThreads - 1) / kThreads);
-    ws_area_kernel<<<gpx, kThreads, 0, s>>>(regions, markers, out, n, area, n_seed);
+    ws_area_kernel<<<gpx, kThreads, 0, s>>>(regions, markers, out, n, area, n_seed, n_regions, cap);
     BE_LAUNCH_CHECK();
     ws_offsets_kernel<<<1, 1024, 0, s>>>(area, n_regions, cap, offset, ticket);
     BE_LAUNCH_CHECK();
-    ws_seed_kernel<<<gpx, kThreads, 0, s>>>(regions, markers, height, negate, n, offset, fill, qa);
+    ws_seed_kernel<<<gpx, kThreads, 0, s>>>(regions, markers, height, negate, n, offset, fill, qa, n_regions, cap);
     BE_LAUNCH_CHECK();
     FloodArgs a{regions, height, n_regions, offset, n_seed, out, qa, qb, rec, ticket, cap, (int)Y, (int)X, negate};
     ws_flood_kernel<<<BE_SM_COUNT * 2, kFloodThreads, 0, s>>>(a);

@@ -309,9 +309,11 @@ int be_peak_local_max_i32(const int32_t* dist2, const uint8_t* mask, uint8_t* pe
  *   markers    [Y*X] int32: seeds (0 = none); must lie inside the mask to flood
  *   regions    [Y*X] int32: the mask as its 4-connected components, labelled 1..*n_regions (be_ccl_u8_i32 with
  *              connectivity 1), 0 outside the mask; regions flood independently, one thread block each
- *   n_regions  device pointer to the number of regions
+ *   n_regions  device pointer to the number of regions (ids beyond it count as outside the mask)
  *   out        [Y*X] int32: markers, grown over the mask; mask pixels no seed reaches stay 0
  *   ws         be_watershed_workspace_bytes(Y, X) bytes
+ * A region's seeds are put in raster order by its block with a rank sort: quadratic in the seeds of ONE region (fine for
+ * the handful a distance map yields, slow for a region with many thousands of seed pixels).
  * Pixels leave the queue by (height, push order).  Seeds are pushed in raster order and seeds of equal height leave in
  * that order; skimage's binary heap orders such complete ties by its array layout instead, so results can differ from
  * skimage's on the boundary between two basins whose seeds have exactly the same height. */
