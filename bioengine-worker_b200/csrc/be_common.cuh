@@ -213,6 +213,13 @@ static __device__ __forceinline__ void bulk_g2s(unsigned dst, const void* src, u
                  "l"(src), "r"(bytes), "r"(bar)
                  : "memory");
 }
+// one box of a 2-D tensor map (inner coordinate x, outer coordinate y) into shared memory: a single instruction for a
+// whole stage of rows, where the per-row bulk copies above are bound by the copy engine's instruction rate
+static __device__ __forceinline__ void tensor_g2s_2d(unsigned dst, const void* tmap, int x, int y, unsigned bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                 ::"r"(dst), "l"(tmap), "r"(x), "r"(y), "r"(bar)
+                 : "memory");
+}
 // Waits with a suspend-time hint: the warp sleeps in hardware until the phase completes (or the hint runs out), so a copy
 // warp that is a whole ring ahead does not burn issue slots polling — with plain try_wait the polling loop was a fifth
 // of all instructions the blend kernel issued.

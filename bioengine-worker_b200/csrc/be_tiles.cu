@@ -11,6 +11,8 @@
 // shared memory.
 #include <stdlib.h>
 
+#include <cuda.h>   // CUtensorMap and the encode entry point's signature; the entry point itself is fetched at run time
+
 #include "be_common.cuh"
 
 namespace {
@@ -175,7 +177,8 @@ __global__ void __launch_bounds__(kCopyThreads, 3) tile_gather_tma_kernel(const 
                                                                        const int32_t* __restrict__ xsrc,
                                                                        const double* __restrict__ norm, int norm_mode,
                                                                        float clip_lo, float clip_hi, int units_per_row,
-                                                                       int rows_per_band, int bands, unsigned n_items) {
+                                                                       int rows_per_band, int bands, unsigned n_items,
+                                                                       const __grid_constant__ CUtensorMap tmap, int use_tmap) {
     be_pdl_wait();   // the statistics kernel that wrote `norm`
     extern __shared__ __align__(128) unsigned char s_stage[];   // kGatherStages * kGatherStageBytes
     __shared__ __align__(8) unsigned long long s_bar[2 * kGatherStages];
@@ -214,7 +217,9 @@ __global__ void __launch_bounds__(kCopyThreads, 3) tile_gather_tma_kernel(const 
             const GatherItem it = gather_item(item, d, cz_count, bands, rows_per_band);
             if (!((s_ok[it.kx >> 5] >> (it.kx & 31)) & 1u)) continue;
             const int64_t sz = zsrc[it.kz * d.Bz + it.iz];
-            const float* plane = img + ((it.n * d.C + it.c) * d.Z + sz) * d.Y * d.X + xsrc[it.kx * d.Bx];
+            const int x_first = xsrc[it.kx * d.Bx];
+            const int64_t plane_row = ((it.n * d.C + it.c) * d.Z + sz) * d.Y;   // row of the image seen as one (rows, X) matrix
+            const float* plane = img + plane_row * d.X + x_first;
             const int32_t* ys = ysrc + it.ky * d.By;
             const int n_steps = (it.iy1 - it.iy0 + r_stage - 1) / r_stage;
             for (int g = 0; g < n_steps; ++g) {
@@ -224,12 +229,32 @@ __global__ void __launch_bounds__(kCopyThreads, 3) tile_gather_tma_kernel(const 
                 int64_t off[2];
 #pragma unroll
                 for (int k = 0; k < 2; ++k) off[k] = (lane + 32 * k < rows) ? (int64_t)ys[row0 + lane + 32 * k] * d.X : 0;
+                // a full stage of consecutive image rows (every tile away from the bottom border) is ONE box of the tensor
+                // map: one instruction instead of one bulk copy per 1-KB row
+                bool box = use_tmap && rows == r_stage && r_stage <= 64;
+                if (box) {
+                    const int64_t first = (int64_t)ys[row0] * d.X;
+                    bool run = true;
+#pragma unroll
+                    for (int k = 0; k < 2; ++k)
+                        if (lane + 32 * k < rows) run &= off[k] == first + (int64_t)(lane + 32 * k) * d.X;
+                    box = __all_sync(0xffffffffu, run);
+                }
                 mbar_wait(bar0 + 8 * (kGatherStages + st), par ^ 1);
                 if (lane == 0) {
                     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic reads before async writes
                     mbar_expect_tx(bar0 + 8 * st, rows * row_bytes);
+                    if (box)
+                        tensor_g2s_2d(smem0 + st * kGatherStageBytes, &tmap, x_first, (int)(plane_row + ys[row0]), bar0 + 8 * st);
                 }
                 __syncwarp();
+                if (box) {
+                    if (++st == kGatherStages) {
+                        st = 0;
+                        par ^= 1;
+                    }
+                    continue;
+                }
 #pragma unroll
                 for (int k = 0; k < 2; ++k)
                     if (lane + 32 * k < rows)
@@ -993,6 +1018,27 @@ int stitch_grid(const char* who, const Dims& d, int upr, dim3* grid) {
 
 }  // namespace
 
+// cuTensorMapEncodeTiled through the runtime's driver entry-point query: no link against libcuda
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn tensor_map_encoder() {
+    static EncodeTiledFn fn = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        const char* off = getenv("BE_B200_NO_TENSORMAP");
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (!(off && off[0] == '1') && cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = (EncodeTiledFn)p;
+        else
+            cudaGetLastError();
+    }
+    return fn;
+}
+
 extern "C" int be_tile_gather_f32(const float* img, float* tiles, int64_t N, int64_t C, int64_t Z, int64_t Y, int64_t X,
                                   int Tz, int Ty, int Tx, int Bz, int By, int Bx, const int32_t* zsrc,
                                   const int32_t* ysrc, const int32_t* xsrc, const double* norm, int norm_mode, int clip,
@@ -1026,6 +1072,21 @@ extern "C" int be_tile_gather_f32(const float* img, float* tiles, int64_t N, int
     if (tma) {
         // work items of two stages of rows each; one wave of persistent blocks walks them
         const int r_stage = kThreads / upr * kGatherSweeps;
+        // the image as one (N*C*Z*Y, X) matrix behind a tensor map with a box of one stage (r_stage rows x Bx pixels)
+        CUtensorMap tmap;
+        memset(&tmap, 0, sizeof(tmap));
+        int use_tmap = 0;
+        if (Bx <= 256 && r_stage <= 64 && N * C * Z * Y < ((int64_t)1 << 31) && X < ((int64_t)1 << 31)) {
+            if (EncodeTiledFn encode = tensor_map_encoder()) {
+                const cuuint64_t dims[2] = {(cuuint64_t)X, (cuuint64_t)(N * C * Z * Y)};
+                const cuuint64_t strides[1] = {(cuuint64_t)X * sizeof(float)};
+                const cuuint32_t box[2] = {(cuuint32_t)Bx, (cuuint32_t)r_stage};
+                const cuuint32_t estr[2] = {1, 1};
+                use_tmap = encode(&tmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(img), dims, strides, box, estr,
+                                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+            }
+        }
         const int rpb = 2 * r_stage;
         const int nb = (By + rpb - 1) / rpb;
         const int64_t n_items = n_tiles * C * Bz * nb;
@@ -1035,15 +1096,15 @@ extern "C" int be_tile_gather_f32(const float* img, float* tiles, int64_t N, int
         if (norm_mode && clip) {
             BE_CUDA(cudaFuncSetAttribute(tile_gather_tma_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             BE_CUDA(be_launch_pdl(tile_gather_tma_kernel<true, true>, dim3(blocks), dim3(kCopyThreads), smem, s, img, tiles, d, zsrc, ysrc, xsrc, norm, norm_mode,
-                                                                                 clip_lo, clip_hi, upr, rpb, nb, (unsigned)n_items));
+                                                                                 clip_lo, clip_hi, upr, rpb, nb, (unsigned)n_items, tmap, use_tmap));
         } else if (norm_mode) {
             BE_CUDA(cudaFuncSetAttribute(tile_gather_tma_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             BE_CUDA(be_launch_pdl(tile_gather_tma_kernel<true, false>, dim3(blocks), dim3(kCopyThreads), smem, s, img, tiles, d, zsrc, ysrc, xsrc, norm, norm_mode,
-                                                                                  0.f, 0.f, upr, rpb, nb, (unsigned)n_items));
+                                                                                  0.f, 0.f, upr, rpb, nb, (unsigned)n_items, tmap, use_tmap));
         } else {
             BE_CUDA(cudaFuncSetAttribute(tile_gather_tma_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             BE_CUDA(be_launch_pdl(tile_gather_tma_kernel<false, false>, dim3(blocks), dim3(kCopyThreads), smem, s, img, tiles, d, zsrc, ysrc, xsrc, norm, 0, 0.f,
-                                                                                   0.f, upr, rpb, nb, (unsigned)n_items));
+                                                                                   0.f, upr, rpb, nb, (unsigned)n_items, tmap, use_tmap));
         }
     } else if (norm_mode && clip)
         tile_gather_kernel<true, true><<<grid, kThreads, 0, s>>>(img, tiles, d, zsrc, ysrc, xsrc, norm, norm_mode, clip_lo,

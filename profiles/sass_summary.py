@@ -2,7 +2,7 @@
 
 usage: python profiles/sass_summary.py > profiles/sass_summary.txt
 Lists, per kernel, the instruction count and the counts of the opcodes that tell how a kernel moves and computes:
-UBLKCP (cp.async.bulk, the TMA bulk-copy engine), UTMALDG / UTMASTG (tensor-map TMA; none: no tensor maps are used),
+UBLKCP (cp.async.bulk, the TMA bulk-copy engine), UTMALDG / UTMASTG (tensor-map TMA: the gather fetches whole stages of rows as 2-D boxes),
 SYNCS (mbarrier), LDGSTS (cp.async), LDG / STG / LDS / STS / ATOMS / ATOMG / RED, F2F (fp32 <-> fp64 conversions), DADD /
 DMUL / DFMA (fp64 arithmetic), MUFU, REDUX / VOTE / SHFL / MATCH (warp collectives), ACQBULK / griddepcontrol shows as
 ACQBULK-free `BAR`-less waits; the tensor-core opcodes (UTC*MMA, HMMA, ...) are listed to show there are none."""
