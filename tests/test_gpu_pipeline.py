@@ -219,3 +219,26 @@ def test_c5_frame_full_size_labels_and_stats_equal_oracle(dev):
     assert np.array_equal(s[:, 0], np.bincount(l, minlength=n + 1))                      # areas
     assert np.array_equal(s[:, 2], np.bincount(l, weights=ys, minlength=n + 1).astype(np.int64))   # sum of y
     assert np.array_equal(s[:, 3], np.bincount(l, weights=xs, minlength=n + 1).astype(np.int64))   # sum of x
+
+
+def test_c2_path_on_an_image_four_times_the_benchmark_size(dev):
+    """8192 x 8192 (67 M pixels, 1849 tiles of 256 px, 485 MB of tiles): quantiles, tiles, the mask-only blend, the packed
+    mask and the labels against the oracle on identical stand-in logits — index arithmetic beyond 2^26 elements per image
+    and 2^28 tile elements, ragged last tiles (8192 = 42 * 192 + 128)."""
+    from bioengine_worker_b200.pipeline import PipelineSpec, TiledPipeline
+
+    S, B, ov = 8192, 256, 64
+    img = O.synthetic_image((1, 1, S, S), 3000, seed=8)
+    pipe = TiledPipeline((1, 1, S, S), PipelineSpec(block=(B, B), halo=(32, 32), convention="fibsem", overlap=(ov, ov),
+                                                    preprocess="scale_range", connectivity=2), device=dev)
+    tiles = pipe.preprocess_and_tile(torch.from_numpy(img).to(dev))
+    want_tiles = P.c2_pre(img, B, ov)
+    assert tiles.shape == want_tiles.shape == (43 * 43, 1, B, B)
+    assert np.array_equal(tiles.cpu().numpy(), want_tiles)
+    logits = ((tiles - 0.15) * 9.0).contiguous()       # stand-in for the forward: blobs above the threshold
+    res = pipe.stitch_and_label(logits)
+    _, mask, labels = P.c2_post(logits.cpu().numpy(), (S, S), B, ov, 2)
+    assert 0.01 < mask.mean() < 0.6
+    assert np.array_equal(res["mask"].cpu().numpy()[0, 0], mask)
+    assert np.array_equal(res["labels"].cpu().numpy()[0, 0], labels)
+    assert int(res["n_labels"].item()) == labels.max() > 1000
