@@ -4,7 +4,7 @@ cache_size_in_gb=50.0`, :1056-1060), `infer(...)` with the reference's signature
 call into the runtime replica as `runtime_deployment.predict.remote(...)` (:1969-1977), and the lifecycle hooks the builder
 looks for (`async_init`, `test_deployment`, `check_health`; ref: bioengine/apps/builder.py:669-890).
 
-Only the data path is mirrored: resolve the inputs (ndarray, dict of ndarrays, or a local `.npy` / image path), find the
+Only the data path is mirrored: resolve the inputs (ndarray, dict of ndarrays, a direct URL or a local `.npy` / image path), find the
 model package on disk, forward to `RuntimeDeployment.predict`, optionally hand the result back as a file instead of an
 array.  Model download / LRU disk cache / test-report publishing / S3 presigned URLs (entry_deployment.py:72-1009,
 1265-1300, 1821-1867) are control plane and storage — out of scope; a deployment that needs them keeps the
@@ -66,13 +66,14 @@ class EntryDeployment:
 
     @staticmethod
     def _load_image_from_source(source: str) -> np.ndarray:
-        """ref: entry_deployment.py:1196-1263 restricted to local files (`file://` prefix accepted): `.npy`, `.png`,
-        `.tif(f)`, `.jp(e)g`, decoded as `imageio.v3.imread` would; same exceptions (ValueError for an unsupported
-        extension or unreadable content, FileNotFoundError for a missing file)."""
-        from .io import load_image
+        """ref: entry_deployment.py:1196-1263 for direct `http(s)://` URLs and local files (`file://` prefix accepted):
+        `.npy`, `.png`, `.tif(f)`, `.jp(e)g`, decoded as `imageio.v3.imread` would; same exceptions (ValueError for an
+        unsupported extension or unreadable content, FileNotFoundError for a missing / expired source).  Temporary paths of
+        the reference's `get_upload_url` (presigned S3) are the storage service's business, not resolved here."""
+        from .io import fetch_image, load_image
 
         if source.startswith(("http://", "https://")):
-            raise ValueError("remote inputs are resolved by the reference EntryDeployment; pass an array or a local file path")
+            return fetch_image(source)
         return load_image(source[7:] if source.startswith("file://") else source)
 
     @schema_method
@@ -97,10 +98,13 @@ class EntryDeployment:
         """Execute inference on a locally available bioimage.io model (same arguments and result as the reference's
         `infer`, ref: entry_deployment.py:1869-1990)."""
         self._check_runtime_available()
-        if isinstance(inputs, str):
-            inputs = self._load_image_from_source(inputs)
+        import asyncio
+
+        if isinstance(inputs, str):   # downloads and decoding off the event loop, as the reference does
+            inputs = await asyncio.to_thread(self._load_image_from_source, inputs)
         elif isinstance(inputs, dict):
-            inputs = {k: (self._load_image_from_source(v) if isinstance(v, str) else v) for k, v in inputs.items()}
+            inputs = {k: (await asyncio.to_thread(self._load_image_from_source, v) if isinstance(v, str) else v)
+                      for k, v in inputs.items()}
         rdf_path = self._rdf_path(model_id)
         try:
             outputs = await call_handle(

@@ -104,3 +104,42 @@ def load_image(path: str) -> np.ndarray:
         raise FileNotFoundError(f"Source '{path}' does not exist or has expired.")
     with open(path, "rb") as f:
         return decode_image(f.read(), ext)
+
+
+def fetch_image(url: str, timeout: float = 30.0, retries: int = 3) -> np.ndarray:
+    """A direct `http(s)://` source → ndarray, as ref: entry_deployment.py:1217-1258 does it: the extension (query string
+    stripped) must be a supported one (ValueError before anything is fetched); 404 → FileNotFoundError("... does not exist
+    or has expired."); any other failure to download → FileNotFoundError("Failed to download source ..."); content that
+    does not parse → ValueError.  Transient failures (connection errors, 5xx) are retried like the reference's
+    `_get_url_with_retry`."""
+    import os
+    import time
+    import urllib.error
+    import urllib.request
+
+    ext = os.path.splitext(url.split("?")[0])[1].lower()
+    if ext not in SUPPORTED_FILE_TYPES:
+        raise ValueError(f"Unsupported file extension '{ext}' in source '{url}'. Supported extensions: {SUPPORTED_FILE_TYPES}")
+    if not url.startswith(("http://", "https://")):
+        raise ValueError(f"not an http(s) source: '{url}'")
+    data, last = None, None
+    for attempt in range(max(1, retries)):
+        try:
+            with urllib.request.urlopen(url, timeout=timeout) as resp:
+                data = resp.read()
+            break
+        except urllib.error.HTTPError as e:
+            if e.code == 404:
+                raise FileNotFoundError(f"Source '{url}' does not exist or has expired.") from e
+            last = e
+            if e.code < 500:   # a client error will not go away
+                break
+        except (urllib.error.URLError, OSError) as e:
+            last = e
+        time.sleep(0.2 * (attempt + 1))
+    if data is None:
+        raise FileNotFoundError(f"Failed to download source '{url}': {last}") from last
+    try:
+        return decode_image(data, ext)
+    except ValueError as e:
+        raise ValueError(f"Failed to parse image from source '{url}': {e}") from e

@@ -55,3 +55,48 @@ def test_errors_match_the_reference(tmp_path):
     bad.write_bytes(b"not an image")
     with pytest.raises(ValueError, match="Failed to parse image"):
         bio.load_image(str(bad))
+
+
+def test_fetch_image_over_http(tmp_path):
+    """Direct URL sources (ref: entry_deployment.py:1217-1258) against a local HTTP server: .npy and .png contents, the
+    query string ignored for the extension, 404 → FileNotFoundError, unsupported extension / unreadable content →
+    ValueError, nobody listening → FileNotFoundError."""
+    import functools
+    import http.server
+    import threading
+
+    import cv2
+
+    from bioengine_worker_b200.io import fetch_image
+
+    rng = np.random.default_rng(0)
+    arr = rng.normal(size=(5, 7)).astype(np.float32)
+    img = rng.integers(0, 65535, size=(9, 11), dtype=np.uint16)
+    np.save(tmp_path / "a.npy", arr)
+    cv2.imwrite(str(tmp_path / "b.png"), img)
+    (tmp_path / "broken.png").write_bytes(b"not a png")
+    (tmp_path / "c.txt").write_text("x")
+
+    class Quiet(http.server.SimpleHTTPRequestHandler):
+        def log_message(self, *a):
+            pass
+
+    srv = http.server.ThreadingHTTPServer(("127.0.0.1", 0), functools.partial(Quiet, directory=str(tmp_path)))
+    port = srv.server_address[1]
+    t = threading.Thread(target=srv.serve_forever, daemon=True)
+    t.start()
+    try:
+        base = f"http://127.0.0.1:{port}"
+        assert np.array_equal(fetch_image(f"{base}/a.npy"), arr)
+        assert np.array_equal(fetch_image(f"{base}/b.png?X-Amz-Signature=abc"), img)
+        with pytest.raises(FileNotFoundError, match="does not exist or has expired"):
+            fetch_image(f"{base}/missing.npy", retries=1)
+        with pytest.raises(ValueError, match="Unsupported file extension"):
+            fetch_image(f"{base}/c.txt")
+        with pytest.raises(ValueError, match="Failed to parse image"):
+            fetch_image(f"{base}/broken.png")
+    finally:
+        srv.shutdown()
+        srv.server_close()
+    with pytest.raises(FileNotFoundError, match="Failed to download"):
+        fetch_image(f"http://127.0.0.1:{port}/a.npy", timeout=2.0, retries=1)   # the server is gone
