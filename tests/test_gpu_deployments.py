@@ -160,8 +160,10 @@ def test_entry_deployment_infer_mirrors_the_reference_call(tmp_path, dev):
     assert np.array_equal(np.load(via_file["mask"][7:]), direct["mask"])
     with pytest.raises(FileNotFoundError):
         asyncio.run(entry.infer("no-such-model", img))
-    with pytest.raises(ValueError):
-        asyncio.run(entry.infer("tiny-unet", "https://example.org/x.npy"))
+    with pytest.raises(ValueError):      # the extension is checked before anything is fetched
+        asyncio.run(entry.infer("tiny-unet", "https://example.org/x.bmp"))
+    with pytest.raises(FileNotFoundError):   # nothing listens there: the source cannot be downloaded
+        asyncio.run(entry.infer("tiny-unet", "http://127.0.0.1:9/x.npy"))
 
 
 def test_npy_wire_path_round_trip(tmp_path, dev):
