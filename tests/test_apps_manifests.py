@@ -14,6 +14,7 @@ APPS = Path(__file__).resolve().parents[1] / "apps"
 @pytest.mark.parametrize("app,methods", [
     ("model-runner-b200", {"EntryDeployment": ["infer"], "RuntimeDeployment": ["predict", "test"]}),
     ("fibsem-mito-analysis-b200", {"MitoAnalysisDeployment": ["analyze"]}),
+    ("model-screening-b200", {"ScreeningEntry": ["screen"], "ScreeningWorker": ["score_shard"]}),
 ])
 def test_manifest_deployments_resolve(app, methods):
     man = yaml.safe_load((APPS / app / "manifest.yaml").read_text())
@@ -89,3 +90,57 @@ def test_runtime_predict_signature_matches_the_reference():
     # ref: apps/model-runner/runtime_deployment.py:234-243
     assert names == ["self", "rdf_path", "inputs", "weights_format", "device", "default_blocksize_parameter", "sample_id",
                      "latest_remote_modified"]
+
+
+def test_screening_entry_fans_out_and_merges_integer_tables():
+    """The entry asks every shard (as `handle.score_shard.remote(...)`), sums the int64 tables and ranks: a fake worker that
+    answers from a known table shows the merge is exact and the ranking follows the mean AP at the first threshold."""
+    import asyncio
+
+    import numpy as np
+
+    from bioengine_worker_b200.screening_deployment import ScreeningEntry, rank_from_table
+
+    n_models, n_images, thr = 3, 7, [0.5, 0.75]
+    rng = np.random.default_rng(0)
+    n_true = rng.integers(5, 40, size=n_images)
+    full = np.zeros((n_models, n_images, 4), dtype=np.int64)
+    for m in range(n_models):
+        n_pred = n_true + rng.integers(-3, 4, size=n_images)
+        tp50 = np.minimum(n_true, n_pred) - rng.integers(0, 4, size=n_images) - 2 * m     # model 0 is the best
+        full[m, :, 0], full[m, :, 1] = np.maximum(tp50, 0), np.maximum(tp50 - 3, 0)
+        full[m, :, 2], full[m, :, 3] = n_true, n_pred
+    asked = []
+
+    class Method:
+        def __init__(self, fn):
+            self.remote = fn
+
+    class FakeHandle:   # like a DeploymentHandle: methods are only reachable as `.remote`
+        def __init__(self):
+            async def score_shard(**kw):
+                asked.append((kw["shard"], kw["n_shards"]))
+                nm, ni, nt = len(kw["rdf_paths"]), len(kw["images"]), len(kw["thresholds"])
+                t = np.zeros((nm, ni, nt + 2), dtype=np.int64)
+                if (nm, ni, nt + 2) == full.shape:
+                    t[:, kw["shard"]::kw["n_shards"]] = full[:, kw["shard"]::kw["n_shards"]]
+                return t
+            self.score_shard = Method(score_shard)
+
+    entry = ScreeningEntry(FakeHandle(), n_shards=4)
+    res = asyncio.run(entry.screen([f"m{i}/rdf.yaml" for i in range(n_models)], [np.zeros((4, 4))] * n_images,
+                                   [np.zeros((4, 4), np.int32)] * n_images, thr))
+    assert sorted(asked) == [(s, 4) for s in range(4)]
+    assert np.array_equal(res["table"], full)
+    want = rank_from_table(full, thr)
+    assert np.array_equal(res["ap"], want["ap"]) and res["ranking_index"] == want["ranking"].tolist()
+    assert res["ranking"][0] == "m0/rdf.yaml"
+    tp, nt, npred = full[0, :, 0], full[0, :, 2], full[0, :, 3]
+    np.testing.assert_allclose(res["ap"][0, :, 0], (tp / (nt + npred - tp)).astype(np.float32), rtol=1e-6)
+    # fewer images than shards: one shard per image
+    asked.clear()
+    asyncio.run(entry.screen(["m0/rdf.yaml"], [np.zeros((4, 4))] * 2, [np.zeros((4, 4), np.int32)] * 2))
+    assert sorted(asked) == [(0, 2), (1, 2)]
+    import pytest as _pytest
+    with _pytest.raises(ValueError):
+        asyncio.run(entry.screen(["m0/rdf.yaml"], [np.zeros((4, 4))] * 2, [np.zeros((4, 4), np.int32)]))

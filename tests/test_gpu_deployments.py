@@ -535,3 +535,49 @@ def test_per_channel_scale_linear_and_binarize(dev):
         rt._run_ops_unfused(xt.clone(), [Op("scale_linear", {"gain": [1.0, 2.0]})], 2, 3)
     with pytest.raises(ValueError):
         rt._run_ops_unfused(xt.clone(), [Op("binarize", {"threshold": thr, "axis": "x"})], 2, 3)
+
+
+def test_screening_app_equals_single_process_screening(tmp_path, dev):
+    """The screening app (entry → 3 shards on a worker object) against `screen_models` in one process and the oracle's AP:
+    same integer table, same AP, same ranking; images given as arrays and as .npy sources."""
+    from bioengine_worker_b200 import models
+    from bioengine_worker_b200.screening import screen_models
+    from bioengine_worker_b200.screening_deployment import ScreeningEntry, ScreeningWorker
+
+    models.strict_fp32()
+    n, size = 7, 160
+    imgs, gts = [], []
+    for i in range(n):
+        img, clean = O.synthetic_image((size, size), 14 + i, seed=500 + i, with_truth=True)
+        imgs.append(img)
+        gts.append(O.label(clean > 0.5, 2))
+    probe = O.zero_mean_unit_variance(imgs[0][None, None], axes=(1, 2, 3))
+    rdfs = []
+    for m in range(2):
+        d = tmp_path / f"model{m}"
+        d.mkdir()
+        rdf_path, _ = write_model(d, [], [], seed=60 + m, calibrate_on=probe if m == 0 else -probe)
+        rdfs.append(rdf_path)
+    worker = ScreeningWorker.func_or_class(batch=3)
+    entry = ScreeningEntry.func_or_class(worker, n_shards=3)
+    sources = []
+    for i, img in enumerate(imgs):     # every other image travels as a file
+        if i % 2:
+            np.save(tmp_path / f"img{i}.npy", img)
+            sources.append(str(tmp_path / f"img{i}.npy"))
+        else:
+            sources.append(img)
+    res = asyncio.run(entry.screen(rdfs, sources, gts, [0.5, 0.75]))
+    nets = [worker._net(p, dev) for p in rdfs]
+    one = screen_models(nets, imgs, gts, thresholds=(0.5, 0.75), device=dev, batch=4)
+    assert res["n_shards"] == 3
+    assert np.array_equal(res["table"], one["table"])
+    assert np.array_equal(res["ap"], one["ap"], equal_nan=True) and res["ranking_index"] == one["ranking"].tolist()
+    x = torch.from_numpy(np.stack([O.zero_mean_unit_variance(im[None, None], axes=(1, 2, 3))[0] for im in imgs])).to(dev)
+    with torch.no_grad():
+        logits = nets[0](x).cpu().numpy()
+    preds = [O.label(O.binarize(O.sigmoid(l), 0.5)[0], 2) for l in logits]
+    ap, tp, _, _ = O.average_precision(gts, preds, threshold=[0.5, 0.75])
+    assert np.array_equal(res["table"][0, :, :2], tp.astype(np.int64))
+    assert np.array_equal(res["ap"][0], ap, equal_nan=True)
+    assert sum(p.max() for p in preds) > 0
