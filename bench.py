@@ -325,6 +325,10 @@ def run_b200(args):
         raise SystemExit("bench.py needs a CUDA device (no CPU fallback)")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    # pinned staging buffers belong on the NUMA node of this rank's GPU (every rank streams through host memory)
+    from bioengine_worker_b200.hostbind import bind_host_to_gpu
+
+    host_binding = bind_host_to_gpu(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     models.strict_fp32()
@@ -572,6 +576,7 @@ def run_b200(args):
             "with_forward_Mpx_s": px / ((ms_per_step + forward_ms) * 1e-3) / 1e6,
             "clocks": clocks,
             "host_cpus": os.cpu_count(),
+            "host_binding": host_binding,
             "parity": parity,
             "screening": screening,
         }
