@@ -51,6 +51,20 @@ def main():
     ap, tp, fp, fn = O.average_precision([t], [p], threshold=[0.5, 0.75, 0.9])
     np.savez_compressed(os.path.join(OUT, "metric.npz"), true=t, pred=p, overlap=O.label_overlap(t, p), ap=ap, tp=tp,
                         fp=fp, fn=fn)
+    # 5. fibsem instance post-processing (size filter → closing → EDT → peaks → markers → flood): touching blobs, and a
+    #    mask with twin discs and straight bars whose seeds tie in height (the two tie orders differ there)
+    blobs = np.clip(O.gaussian_blobs((160, 200), 14, sigma=(6.0, 14.0), seed=5) * 1.3, 0, 1).astype(np.float32)
+    yy, xx = np.mgrid[:120, :160]
+    twins = (((yy - 40) ** 2 + (xx - 40) ** 2 <= 15**2) | ((yy - 40) ** 2 + (xx - 66) ** 2 <= 15**2)).astype(np.float32)
+    twins[80:92, 20:140] = 1.0
+    out = {}
+    for name, prob in (("blobs", blobs), ("twins", twins)):
+        parts = {}
+        fifo = O.prob_to_instances(prob, ties="fifo", parts=parts)
+        out.update({f"{name}_prob": prob, f"{name}_closed": parts["closed"], f"{name}_dist2": np.rint(parts["dist"] ** 2).astype(np.int32),
+                    f"{name}_peaks": parts["coords"].astype(np.int32), f"{name}_markers": parts["markers"],
+                    f"{name}_fifo": fifo, f"{name}_heap": O.prob_to_instances(prob, ties="heap")})
+    np.savez_compressed(os.path.join(OUT, "instances.npz"), **out)
     print("golden vectors written to", OUT)
 
 

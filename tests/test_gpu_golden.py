@@ -84,3 +84,21 @@ def test_golden_metric(dev):
     ap, tp, fp, fn = average_precision([mt["true"]], [mt["pred"]], threshold=[0.5, 0.75, 0.9], device=dev)
     assert np.array_equal(tp, mt["tp"]) and np.array_equal(fp, mt["fp"]) and np.array_equal(fn, mt["fn"])
     assert np.array_equal(ap, mt["ap"], equal_nan=True)
+
+
+def test_golden_instances(dev):
+    """Committed vectors of the fibsem post-processing: closing, squared distance, peaks, markers and the flood."""
+    z = np.load(os.path.join(GOLD, "instances.npz"))
+    for name in ("blobs", "twins"):
+        mask = torch.from_numpy((z[f"{name}_prob"] > 0.5).astype(np.uint8)).to(dev)
+        kept = K().remove_small_objects(mask[None], 300)
+        closed = K().binary_closing(kept, K().disk_half_widths(4))
+        assert np.array_equal(closed.cpu().numpy()[0].astype(bool), z[f"{name}_closed"]), name
+        d2 = K().distance_transform_edt_sq(closed)
+        assert np.array_equal(d2.cpu().numpy()[0], z[f"{name}_dist2"]), name
+        peaks = K().peak_local_max(d2[0], closed[0], 8).cpu().numpy()
+        want = np.zeros(peaks.shape, np.uint8)
+        want[tuple(z[f"{name}_peaks"].T)] = 1
+        assert np.array_equal(peaks, want), name
+        got, n = K().instances_from_mask(mask)
+        assert np.array_equal(got.cpu().numpy(), z[f"{name}_fifo"]) and int(n.item()) == z[f"{name}_markers"].max(), name

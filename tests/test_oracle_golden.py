@@ -140,3 +140,12 @@ def test_committed_vectors_reproduce():
     assert np.array_equal(O.label_overlap(mt["true"], mt["pred"]), mt["overlap"])
     ap, tp, fp, fn = O.average_precision([mt["true"]], [mt["pred"]], threshold=[0.5, 0.75, 0.9])
     assert np.array_equal(tp, mt["tp"]) and np.array_equal(ap, mt["ap"], equal_nan=True)
+    z = np.load(os.path.join(G, "instances.npz"))
+    for name in ("blobs", "twins"):
+        parts = {}
+        assert np.array_equal(O.prob_to_instances(z[f"{name}_prob"], ties="fifo", parts=parts), z[f"{name}_fifo"])
+        assert np.array_equal(O.prob_to_instances(z[f"{name}_prob"], ties="heap"), z[f"{name}_heap"])
+        assert np.array_equal(parts["coords"], z[f"{name}_peaks"]) and np.array_equal(parts["markers"], z[f"{name}_markers"])
+        assert np.array_equal(parts["closed"], z[f"{name}_closed"])
+    assert np.array_equal(z["blobs_fifo"], z["blobs_heap"])            # no tied seeds there
+    assert 0 < (z["twins_fifo"] != z["twins_heap"]).sum() < 200         # tied seeds: the two orders part on a few boundary pixels
