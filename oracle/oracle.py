@@ -455,7 +455,9 @@ def regionprops_table(labels: np.ndarray, pixel_size_nm: float = 5.0) -> Dict[st
     for l in range(1, n + 1):
         if objs[l - 1] is None:
             continue
-        ys, xs = np.nonzero(labels == l)
+        sl = objs[l - 1]   # skimage works on the bounding-box crop as well; the coordinates are put back in the image frame
+        ys, xs = np.nonzero(labels[sl] == l)
+        ys, xs = ys + sl[0].start, xs + sl[1].start
         area = float(ys.size)
         cy, cx = ys.mean(), xs.mean()
         dy, dx = ys - cy, xs - cx
