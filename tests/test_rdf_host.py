@@ -122,3 +122,17 @@ def test_output_ratio_from_size_reference(tmp_path):
            "weights": {"pytorch_state_dict": {"architecture": "UNet2d"}}}
     spec = load_model_spec(_write(tmp_path, old))
     assert RuntimeDeployment._output_ratio(spec, spec.outputs[0], ["y", "x"]) == [Fraction(2), Fraction(1, 2)]
+
+
+def test_host_binding_is_a_no_op_without_nvml(monkeypatch):
+    """`bind_host_to_gpu` never raises: without NVML (this container) or with the switch set it reports why it did nothing."""
+    import os
+
+    from bioengine_worker_b200.hostbind import bind_host_to_gpu
+
+    before = os.sched_getaffinity(0)
+    info = bind_host_to_gpu(0)
+    assert isinstance(info["bound"], bool) and (info["bound"] or "reason" in info)
+    monkeypatch.setenv("BE_B200_NO_NUMA_BIND", "1")
+    assert bind_host_to_gpu(0)["reason"].startswith("disabled")
+    assert os.sched_getaffinity(0) == before or info["bound"]
