@@ -45,11 +45,36 @@ def main():
                 ev[i - 3][1].record()
         torch.cuda.synchronize()
         ms = float(np.median([a.elapsed_time(b) for a, b in ev]))
+        # the four C-ABI calls on their own (same flush, same events)
+        from bioengine_worker_b200 import kernels as K
+
+        q = torch.tensor([0.01, 0.998], dtype=torch.float64, device=dev)
+        _, norm = K.quantile(x, 1, q, 1e-6, ws=pipe.ws)
+        _, _, bits = K.stitch_blend(logits, (1, 1, S, S), pipe.axes, pipe.windows, 1, 0.5, want_out=False, want_bits=True,
+                                    window=pipe.window_table)
+        calls = {"quantiles": lambda: K.quantile(x, 1, q, 1e-6, ws=pipe.ws),
+                 "gather": lambda: K.tile_gather(x, pipe.axes, norm=norm, norm_mode=1, out=pipe.tiles),
+                 "blend": lambda: K.stitch_blend(logits, (1, 1, S, S), pipe.axes, pipe.windows, 1, 0.5, want_out=False,
+                                                 want_bits=True, window=pipe.window_table),
+                 "labels": lambda: K.ccl_bits(bits, (1, S, S), 2, ws=pipe.ws)}
+        stage = {}
+        for name, fn in calls.items():
+            ts = []
+            for i in range(8):
+                flush.fill_(i)
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record()
+                fn()
+                b.record()
+                torch.cuda.synchronize()
+                if i >= 2:
+                    ts.append(a.elapsed_time(b))
+            stage[name] = round(float(np.median(ts)), 4)
         E = pipe.n_tiles * 256 * 256 / (S * S)
         alg = (14 + 8 * E) * S * S
         rows.append({"size": S, "tiles": pipe.n_tiles, "ms": round(ms, 4), "Gpx_s": round(S * S / ms / 1e6, 1),
                      "alg_TB_s": round(alg / ms / 1e9, 3), "components": n_comp,
-                     "foreground": round(float(res["labels"].gt(0).float().mean().item()), 3)})
+                     "foreground": round(float(res["labels"].gt(0).float().mean().item()), 3), "stage_ms": stage})
         del pipe, tiles, logits, res, x
         torch.cuda.empty_cache()
     print(json.dumps({"path": "scale_range p1/p99.8 -> 256-px tiles overlap 64 -> blend + sigmoid + binarize (mask only) -> 8-conn labels",
