@@ -5,7 +5,7 @@ Understands the parts of model RDF 0.5 (and the 0.4 spellings of the same things
 parameterised input sizes (`size: {min, step}`), output halo, packaged test tensors, and the `pytorch_state_dict` weights
 entry with its architecture — a callable of this package (`UNet2d`, `UNet3d`) or a class in a source file of the model
 package.  Output sizes follow an input's through `SizeReference` and the axes' `scale` (0.4: `shape.reference_tensor` /
-`scale`); dataset-mode statistics are not read (row f2 of SURVEY §8f).
+`scale`); statistics over the batch axis / `mode: per_dataset` use the samples of the call (row f2 of SURVEY §8f).
 """
 from __future__ import annotations
 

@@ -236,16 +236,22 @@ class RuntimeDeployment:
         k = op.kwargs
         axes = k.get("axes")
         joint_c = axes is None or any(a in ("c", "channel") for a in axes)
-        if axes is not None and any(a in ("b", "batch") for a in axes):
-            raise ValueError("statistics over the batch axis are not supported")
+        # statistics that include the batch axis (`axes` naming it, or 0.4's `mode: per_dataset`, whose "dataset" inside one
+        # predict call is the samples of that call): one set of numbers for all samples, applied to each of them
+        over_batch = (axes is not None and any(a in ("b", "batch") for a in axes)) or k.get("mode") == "per_dataset"
         n_seg, mode = (n, 2) if joint_c else (n * c, 1)
         eps = float(k.get("eps", 1e-6))
-        if op.name == "scale_range":
-            q = torch.tensor([float(k.get("min_percentile", 0.0)) / 100.0, float(k.get("max_percentile", 100.0)) / 100.0],
-                             dtype=torch.float64, device=x.device)
-            return K.quantile(x, n_seg, q, eps)[1], mode
-        if op.name == "zero_mean_unit_variance":
-            return K.meanvar(x, n_seg, eps)[1], mode
+        if op.name in ("scale_range", "zero_mean_unit_variance"):
+            xs, n_stat = x, n_seg
+            if over_batch:
+                xs, n_stat = (x, 1) if joint_c else (x.transpose(0, 1).contiguous(), c)
+            if op.name == "scale_range":
+                q = torch.tensor([float(k.get("min_percentile", 0.0)) / 100.0, float(k.get("max_percentile", 100.0)) / 100.0],
+                                 dtype=torch.float64, device=x.device)
+                norm = K.quantile(xs, n_stat, q, eps)[1]
+            else:
+                norm = K.meanvar(xs, n_stat, eps)[1]
+            return (norm.repeat(n, 1).contiguous() if over_batch else norm), mode
         mean, std = k["mean"], k["std"]
         if isinstance(mean, (list, tuple)):
             vals = [[float(m), float(s) + eps] for m, s in zip(mean, std)] * n

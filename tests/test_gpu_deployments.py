@@ -581,3 +581,30 @@ def test_screening_app_equals_single_process_screening(tmp_path, dev):
     assert np.array_equal(res["table"][0, :, :2], tp.astype(np.int64))
     assert np.array_equal(res["ap"][0], ap, equal_nan=True)
     assert sum(p.max() for p in preds) > 0
+
+
+def test_statistics_over_the_batch_axis(dev):
+    """`axes` naming the batch axis (0.5) / `mode: per_dataset` (0.4): one set of percentiles or mean / std for all samples
+    of the call, per channel or jointly, applied to every sample."""
+    from bioengine_worker_b200 import kernels as K
+    from bioengine_worker_b200.rdf import Op
+    from bioengine_worker_b200.runtime_deployment import RuntimeDeployment
+
+    rng = np.random.default_rng(12)
+    x = (rng.normal(0, 1, size=(3, 2, 40, 56)) * np.array([1.0, 5.0])[None, :, None, None]
+         + np.array([0.0, 10.0, -4.0])[:, None, None, None]).astype(np.float32)
+    xt = torch.from_numpy(x).to(dev)
+    cases = [
+        (Op("zero_mean_unit_variance", {"axes": ["batch", "y", "x"]}), O.zero_mean_unit_variance(x, axes=(0, 2, 3))),
+        (Op("zero_mean_unit_variance", {"axes": ["b", "c", "y", "x"]}), O.zero_mean_unit_variance(x, axes=(0, 1, 2, 3))),
+        (Op("zero_mean_unit_variance", {"mode": "per_dataset", "axes": ["c", "y", "x"]}), O.zero_mean_unit_variance(x, axes=(0, 1, 2, 3))),
+        (Op("scale_range", {"axes": ["batch", "y", "x"], "min_percentile": 2.0, "max_percentile": 99.0}),
+         O.scale_range(x, 2.0, 99.0, axes=(0, 2, 3))),
+        (Op("scale_range", {"axes": ["batch", "channel", "y", "x"], "min_percentile": 1.0, "max_percentile": 99.8}),
+         O.scale_range(x, 1.0, 99.8, axes=(0, 1, 2, 3))),
+    ]
+    for op, want in cases:
+        norm, mode = RuntimeDeployment._norm_params(xt, op, 3, 2)
+        got = K.normalize(xt.clone(), norm).cpu().numpy()
+        np.testing.assert_allclose(got, want, rtol=1e-5, atol=1e-6, err_msg=str(op.kwargs))
+        assert norm.shape[0] == (3 if mode == 2 else 6)
