@@ -117,22 +117,54 @@ __global__ void __launch_bounds__(kThreads) morph_kernel(const unsigned* __restr
 
 constexpr int kInf = 1 << 29;
 
-// phase 1: g(y, x) = distance to the nearest zero pixel in column x (kInf if the column has none)
-__global__ void __launch_bounds__(kThreads) edt_columns_kernel(const uint8_t* __restrict__ mask, int32_t* __restrict__ g,
-                                                               int Y, int64_t X) {
+// phase 1: g(y, x) = distance to the nearest zero pixel in column x (kInf if the column has none).  A column is cut into
+// chunks of 64 rows so that a 2048-px-wide image keeps 65 536 threads busy instead of 2048: first every (column, chunk) notes
+// the first and last zero row of its chunk, then it finds the nearest zero above and below among its neighbours' notes
+// (usually the adjacent chunk) and walks its 64 rows down and up with the mask bits it kept from the first walk.
+constexpr int kEdtChunk = 64;
+
+__global__ void __launch_bounds__(kThreads) edt_col_marks_kernel(const uint8_t* __restrict__ mask, int2* __restrict__ marks,
+                                                                 int Y, int64_t X, int n_chunks) {
     const int64_t x = (int64_t)blockIdx.x * kThreads + threadIdx.x;
     if (x >= X) return;
-    const uint8_t* m = mask + (int64_t)blockIdx.y * Y * X;
-    int32_t* gp = g + (int64_t)blockIdx.y * Y * X;
-    int d = kInf;
-    for (int y = 0; y < Y; ++y) {
-        d = m[(int64_t)y * X + x] ? min(d + 1, kInf) : 0;
-        gp[(int64_t)y * X + x] = d;
+    const int chunk = blockIdx.y;
+    const uint8_t* m = mask + (int64_t)blockIdx.z * Y * X;
+    const int y0 = chunk * kEdtChunk, y1 = min(y0 + kEdtChunk, Y);
+    int first0 = -1, last0 = -1;
+    for (int y = y0; y < y1; ++y) {
+        if (!m[(int64_t)y * X + x]) {
+            if (first0 < 0) first0 = y;
+            last0 = y;
+        }
     }
-    d = kInf;
-    for (int y = Y - 1; y >= 0; --y) {
+    marks[((int64_t)blockIdx.z * n_chunks + chunk) * X + x] = make_int2(first0, last0);
+}
+
+__global__ void __launch_bounds__(kThreads) edt_col_dist_kernel(const uint8_t* __restrict__ mask, const int2* __restrict__ marks,
+                                                                int32_t* __restrict__ g, int Y, int64_t X, int n_chunks) {
+    const int64_t x = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+    if (x >= X) return;
+    const int chunk = blockIdx.y;
+    const uint8_t* m = mask + (int64_t)blockIdx.z * Y * X;
+    int32_t* gp = g + (int64_t)blockIdx.z * Y * X;
+    const int2* mk = marks + (int64_t)blockIdx.z * n_chunks * X + x;
+    int above = -1, below = -1;   // nearest zero rows outside this chunk
+    for (int c = chunk - 1; c >= 0 && above < 0; --c) above = mk[(int64_t)c * X].y;
+    for (int c = chunk + 1; c < n_chunks && below < 0; ++c) below = mk[(int64_t)c * X].x;
+    const int y0 = chunk * kEdtChunk, y1 = min(y0 + kEdtChunk, Y);
+    unsigned long long fg = 0;   // the chunk's mask bits, kept for the walk back up
+    int last = above;
+    for (int y = y0; y < y1; ++y) {
+        const bool on = m[(int64_t)y * X + x] != 0;
+        fg |= (unsigned long long)on << (y - y0);
+        if (!on) last = y;
+        gp[(int64_t)y * X + x] = last < 0 ? kInf : y - last;
+    }
+    int next = below;
+    for (int y = y1 - 1; y >= y0; --y) {
+        if (!((fg >> (y - y0)) & 1ull)) next = y;
+        const int d = next < 0 ? kInf : next - y;
         const int64_t i = (int64_t)y * X + x;
-        d = m[i] ? min(d + 1, kInf) : 0;
         if (d < gp[i]) gp[i] = d;
     }
 }
@@ -267,7 +299,8 @@ extern "C" int be_binary_closing_u8(const uint8_t* mask, uint8_t* out, int64_t N
 
 extern "C" size_t be_edt_workspace_bytes(int64_t N, int64_t Y, int64_t X) {
     if (N <= 0 || Y <= 0 || X <= 0) return 256;
-    return be_align_up(sizeof(int32_t) * N * Y * X, 256);
+    const int64_t n_chunks = (Y + kEdtChunk - 1) / kEdtChunk;
+    return be_align_up(sizeof(int32_t) * N * Y * X, 256) + be_align_up(sizeof(int2) * N * n_chunks * X, 256);
 }
 
 template <typename OUT>
@@ -280,7 +313,13 @@ static int edt_run(const char* who, const uint8_t* mask, OUT* dist, int64_t N, i
     BE_REQUIRE(N * Y < ((int64_t)1 << 31), BE_ERR_TOO_LARGE, "%s: too many rows", who);
     cudaStream_t s = (cudaStream_t)stream;
     int32_t* g = (int32_t*)ws;
-    edt_columns_kernel<<<dim3((unsigned)((X + kThreads - 1) / kThreads), (unsigned)N), kThreads, 0, s>>>(mask, g, (int)Y, X);
+    int2* marks = (int2*)((char*)ws + be_align_up(sizeof(int32_t) * N * Y * X, 256));
+    const int n_chunks = (int)((Y + kEdtChunk - 1) / kEdtChunk);
+    BE_REQUIRE(n_chunks <= 65535, BE_ERR_TOO_LARGE, "%s: Y %lld too large", who, (long long)Y);
+    const dim3 cgrid((unsigned)((X + kThreads - 1) / kThreads), (unsigned)n_chunks, (unsigned)N);
+    edt_col_marks_kernel<<<cgrid, kThreads, 0, s>>>(mask, marks, (int)Y, X, n_chunks);
+    BE_LAUNCH_CHECK();
+    edt_col_dist_kernel<<<cgrid, kThreads, 0, s>>>(mask, marks, g, (int)Y, X, n_chunks);
     BE_LAUNCH_CHECK();
     const size_t smem = sizeof(int) * 3 * X;
     BE_CUDA(cudaFuncSetAttribute(edt_rows_kernel<OUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
