@@ -429,6 +429,10 @@ __global__ void __launch_bounds__(kFloodThreads, 2) ws_flood_kernel(FloodArgs a)
             // neighbour q goes to the entry with the lowest push number among the lowest-height entries around q — the one
             // the sequential flood pops first — so an entry knows what it wins without asking anybody: all its loads (4 x
             // {region, label, height} + its own and 8 second-ring records) are issued together, one round trip to L2.
+            // what the push phase (C) needs of this thread's first such entry — its label and its neighbours' heights — is
+            // loaded here as well and kept in registers: most steps take a handful of entries, one per thread at most, and
+            // C then costs no second round trip
+            int st_i = -1, st_label = 0, st_h[4] = {0, 0, 0, 0};
             for (int i = tid; i < m; i += kFloodThreads) {
                 const uint64_t e = cur[i];
                 if ((uint32_t)(e >> 32) != hmin) continue;
@@ -442,6 +446,12 @@ __global__ void __launch_bounds__(kFloodThreads, 2) ws_flood_kernel(FloodArgs a)
                     rc[k] = a.comp[q];
                     ro[k] = __ldcg(a.out + q);
                     rh[k] = a.height[q];
+                }
+                if (st_i < 0) {
+                    st_i = i;
+                    st_label = __ldcg(a.out + p);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) st_h[k] = rh[k];
                 }
                 // second ring: U2, UL, UR, L2, R2, DL, DR, D2
                 const bool ok2[8] = {y > 1, ok[0] && ok[1], ok[0] && ok[2], x > 1, x + 2 < X, ok[3] && ok[1], ok[3] && ok[2], y + 2 < Y};
@@ -511,10 +521,13 @@ __global__ void __launch_bounds__(kFloodThreads, 2) ws_flood_kernel(FloodArgs a)
                 a.rec[p] = ((unsigned long long)hmin << 32) | 0x80000000ull;
                 if (!(flags & 0xfu)) continue;
                 int pos = (int)(e >> 32);
-                const int32_t label = __ldcg(a.out + p);
-                int rh[4];
+                int32_t label = st_label;
+                int rh[4] = {st_h[0], st_h[1], st_h[2], st_h[3]};
+                if (i != st_i) {   // a thread's second, third ... entry of one step: loaded now
+                    label = __ldcg(a.out + p);
 #pragma unroll
-                for (int k = 0; k < 4; ++k) rh[k] = a.height[(flags & (1u << k)) ? p + dq[k] : p];
+                    for (int k = 0; k < 4; ++k) rh[k] = a.height[(flags & (1u << k)) ? p + dq[k] : p];
+                }
 #pragma unroll
                 for (int k = 0; k < 4; ++k)
                     if (flags & (1u << k)) {
