@@ -184,50 +184,65 @@ __global__ void __launch_bounds__(kThreads) edt_rows_kernel(const int32_t* __res
     int* gs = smem + 2 * X;  // this row of g
     const int64_t row = blockIdx.x;
     const int32_t* gr = g + row * X;
-    for (int x = threadIdx.x; x < X; x += kThreads) gs[x] = gr[x];
-    __syncthreads();
+    int big = 0;
+    for (int x = threadIdx.x; x < X; x += kThreads) {
+        const int v = gr[x];
+        gs[x] = v;
+        big |= v >= 16384;
+    }
+    // with every column distance of the row below 2^14 (and X <= 2^14) all squares and their sums fit 32 bits: the envelope
+    // then costs 32-bit multiplies and one 32-bit division per parabola instead of 64-bit ones (a row whose columns hold no
+    // zero at all carries kInf and takes the wide path)
+    big = __syncthreads_or(big);
     auto put = [&](int x, long long d2) {
         if constexpr (sizeof(OUT) == 8) dist[row * X + x] = sqrt((double)d2);
         else dist[row * X + x] = (OUT)min(d2, (long long)INT32_MAX);
     };
-    for (int x0 = threadIdx.x; x0 < X; x0 += kThreads) {
-        if (gs[x0] == 0) {
-            put(x0, 0);
-            continue;
-        }
-        if (x0 > 0 && gs[x0 - 1] != 0) continue;  // not the first pixel of a run
-        int end = x0 + 1;
-        while (end < X && gs[end] != 0) ++end;     // [x0, end) is the run; gs[end] == 0 if end < X
-        const int a = x0 > 0 ? x0 - 1 : 0;         // first candidate: the background pixel on the left, if there is one
-        auto f = [&](long long x, long long i) {
-            const long long gi = gs[i];
-            return (x - i) * (x - i) + gi * gi;
-        };
-        int q = a;  // stack lives in s[a..], t[a..]
-        s[a] = a;
-        t[a] = a;
-        for (int u = a + 1; u < end; ++u) {
-            while (q >= a && f(t[q], s[q]) > f(t[q], u)) --q;
-            if (q < a) {
-                q = a;
-                s[a] = u;
-            } else {
-                const long long i = s[q], gi = gs[i], gu = gs[u];
-                const long long w = 1 + (((long long)u * u - i * i + gu * gu - gi * gi) / (2 * ((long long)u - i)));
-                if (w < end) {
-                    ++q;
-                    s[q] = u;
-                    t[q] = (int)w;
+    auto rows_of = [&](auto tag) {
+        using T = decltype(tag);
+        for (int x0 = threadIdx.x; x0 < X; x0 += kThreads) {
+            if (gs[x0] == 0) {
+                put(x0, 0);
+                continue;
+            }
+            if (x0 > 0 && gs[x0 - 1] != 0) continue;  // not the first pixel of a run
+            int end = x0 + 1;
+            while (end < X && gs[end] != 0) ++end;     // [x0, end) is the run; gs[end] == 0 if end < X
+            const int a = x0 > 0 ? x0 - 1 : 0;         // first candidate: the background pixel on the left, if there is one
+            auto f = [&](T x, T i) {
+                const T gi = gs[i];
+                return (x - i) * (x - i) + gi * gi;
+            };
+            int q = a;  // stack lives in s[a..], t[a..]
+            s[a] = a;
+            t[a] = a;
+            for (int u = a + 1; u < end; ++u) {
+                while (q >= a && f(t[q], s[q]) > f(t[q], u)) --q;
+                if (q < a) {
+                    q = a;
+                    s[a] = u;
+                } else {
+                    const T i = s[q], gi = gs[i], gu = gs[u];
+                    const T w = 1 + (((T)u * u - i * i + gu * gu - gi * gi) / (2 * ((T)u - i)));
+                    if (w < end) {
+                        ++q;
+                        s[q] = u;
+                        t[q] = (int)w;
+                    }
                 }
             }
+            for (int x = end - 1; x >= x0; --x) {
+                while (q > a && t[q] > x) --q;
+                T d2 = f(x, s[q]);
+                if (end < X) d2 = min(d2, (T)(end - x) * (T)(end - x));
+                put(x, (long long)d2);
+            }
         }
-        for (int x = end - 1; x >= x0; --x) {
-            while (q > a && t[q] > x) --q;
-            long long d2 = f(x, s[q]);
-            if (end < X) d2 = min(d2, (long long)(end - x) * (end - x));
-            put(x, d2);
-        }
-    }
+    };
+    if (big)
+        rows_of((long long)0);
+    else
+        rows_of((int)0);
 }
 
 }  // namespace
